@@ -1,0 +1,673 @@
+// oracle.cpp — CPU restatement of the reference's overdue-task sweep and creator filter.
+//
+// TEST INFRASTRUCTURE ONLY.  Nothing in the product path (aca-dotnet-workshop_b200/, include/)
+// may include, link, load or call this file; it is the checker used by tests/, by
+// __graft_entry__.smoke() and by bench.py's cpu_baseline / --impl reference legs.
+//
+// PARITY UNPINNED: the reference ships no tests, golden vectors or fixtures for this path
+//  and no .NET runtime exists on this box or the GPU box, so this
+// restatement cannot be checked against a run of the reference.  It is written line by line
+// from the cited C# and from documented .NET 9 BCL behaviour; the only
+// pins are the JSON date samples in the workshop docs (docs/aca/05-aca-dapr-pubsubapi/index.md:65-66)
+// and the seed-row shape (Api/Services/FakeTasksManager.cs:12-24), both covered in tests/.
+//
+// Reference files restated here (paths under /root/reference):
+//   Api = TasksTracker.TasksManager.Backend.Api, Svc = TasksTracker.Processor.Backend.Svc
+//   Api/Models/TaskModel.cs:3-13                     -> struct TaskModel
+//   Api/Services/FakeTasksManager.cs:10-25           -> FakeTasksManager::GenerateRandomTasks
+//   Api/Services/FakeTasksManager.cs:68-72           -> FakeTasksManager::GetTasksByCreator
+//   Api/Services/FakeTasksManager.cs:102-105         -> FakeTasksManager::MarkOverdueTasks (throws)
+//   Api/Services/FakeTasksManager.cs:107-112         -> FakeTasksManager::GetYesterdaysDueTasks
+//   Api/Services/TasksStoreManager.cs:54-69          -> TasksStoreManager::GetTasksByCreator
+//   Api/Services/TasksStoreManager.cs:104-139        -> TasksStoreManager::GetYesterdaysDueTasks
+//   Api/Services/TasksStoreManager.cs:141-149        -> TasksStoreManager::MarkOverdueTasks
+//   Api/Utilities/DateTimeConverter.cs:26-29         -> FormatConverter
+//   Svc/Controllers/ScheduledTasksManagerController.cs:19-46 -> CheckOverDueTasksJob
+//
+// The data structures are deliberately the reference's: a List<TaskModel> of heap objects
+// with UTF-16 strings, scanned sequentially on one thread (LINQ-to-objects is sequential),
+// so timing this code is the honest "reference CPU path" baseline.
+
+#include <algorithm>
+#include <atomic>
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <thread>
+#include <unordered_map>
+#include <vector>
+
+#include "../include/tt_synth.h"
+
+namespace {
+
+constexpr int64_t kTicksPerDay = 864000000000LL;
+constexpr int64_t kTicksPerSecond = 10000000LL;
+constexpr uint64_t kTicksMask = 0x3FFFFFFFFFFFFFFFULL;
+
+// ---- System.DateTime -------------------------------------------
+struct DateTime {
+  uint64_t dateData = 0;  // ticks | kind << 62
+  DateTime() = default;
+  explicit DateTime(uint64_t raw) : dateData(raw) {}
+  DateTime(int64_t ticks, uint32_t kind) : dateData((uint64_t)ticks | ((uint64_t)kind << 62)) {}
+  int64_t Ticks() const { return (int64_t)(dateData & kTicksMask); }
+  uint32_t Kind() const { return (uint32_t)(dateData >> 62); }
+  // DateTime.Date: time-of-day removed, Kind kept
+  DateTime Date() const { int64_t t = Ticks(); return DateTime(t - t % kTicksPerDay, Kind()); }
+  DateTime AddDays(int d) const { return DateTime(Ticks() + (int64_t)d * kTicksPerDay, Kind()); }
+  DateTime AddMinutes(int m) const { return DateTime(Ticks() + (int64_t)m * 60 * kTicksPerSecond, Kind()); }
+  // Equals / operator> / CompareTo compare ticks only and ignore Kind
+  bool Equals(const DateTime& o) const { return Ticks() == o.Ticks(); }
+  bool operator>(const DateTime& o) const { return Ticks() > o.Ticks(); }
+};
+
+struct Civil { int y, m, d, hh, mm, ss; int64_t frac; };
+
+Civil ToCivil(int64_t ticks) {
+  int64_t days = ticks / kTicksPerDay;  // days since 0001-01-01
+  int64_t tod = ticks % kTicksPerDay;
+  // days since 1970-01-01, then the usual era arithmetic (proleptic Gregorian)
+  int64_t z = days - 719162 + 719468;
+  int64_t era = (z >= 0 ? z : z - 146096) / 146097;
+  int64_t doe = z - era * 146097;
+  int64_t yoe = (doe - doe / 1460 + doe / 36524 - doe / 146096) / 365;
+  int64_t y = yoe + era * 400;
+  int64_t doy = doe - (365 * yoe + yoe / 4 - yoe / 100);
+  int64_t mp = (5 * doy + 2) / 153;
+  int64_t d = doy - (153 * mp + 2) / 5 + 1;
+  int64_t m = mp < 10 ? mp + 3 : mp - 9;
+  if (m <= 2) y += 1;
+  Civil c;
+  c.y = (int)y; c.m = (int)m; c.d = (int)d;
+  int64_t secs = tod / kTicksPerSecond;
+  c.frac = tod % kTicksPerSecond;
+  c.hh = (int)(secs / 3600); c.mm = (int)(secs / 60 % 60); c.ss = (int)(secs % 60);
+  return c;
+}
+
+// value.ToString("yyyy-MM-ddTHH:mm:ss") — Api/Utilities/DateTimeConverter.cs:26-29.
+// Drops the fraction, the Kind and any offset.
+std::string FormatConverter(const DateTime& v) {
+  Civil c = ToCivil(v.Ticks());
+  char buf[40];
+  snprintf(buf, sizeof buf, "%04d-%02d-%02dT%02d:%02d:%02d", c.y, c.m, c.d, c.hh, c.mm, c.ss);
+  return buf;
+}
+
+// System.Text.Json's default DateTime writer (what Dapr's SaveStateAsync<TaskModel> stores,
+// Api/Services/TasksStoreManager.cs:35): ISO 8601 extended; ".fffffff" with trailing zeros
+// trimmed only when the sub-second part is non-zero; "Z" for Utc, "+hh:mm"/"-hh:mm" for
+// Local, nothing for Unspecified.  Samples: docs/aca/05-aca-dapr-pubsubapi/index.md:65-66.
+std::string FormatSystemTextJson(const DateTime& v, int local_offset_min) {
+  Civil c = ToCivil(v.Ticks());
+  char buf[64];
+  int n = snprintf(buf, sizeof buf, "%04d-%02d-%02dT%02d:%02d:%02d", c.y, c.m, c.d, c.hh, c.mm, c.ss);
+  if (c.frac != 0) {
+    char f[16];
+    snprintf(f, sizeof f, "%07lld", (long long)c.frac);
+    int len = 7;
+    while (len > 0 && f[len - 1] == '0') --len;
+    buf[n++] = '.';
+    memcpy(buf + n, f, len);
+    n += len;
+  }
+  if (v.Kind() == TT_KIND_UTC) {
+    buf[n++] = 'Z';
+  } else if (v.Kind() == TT_KIND_LOCAL) {
+    int off = local_offset_min;
+    char sign = off < 0 ? '-' : '+';
+    if (off < 0) off = -off;
+    n += snprintf(buf + n, sizeof buf - n, "%c%02d:%02d", sign, off / 60, off % 60);
+  }
+  buf[n] = 0;
+  return buf;
+}
+
+// ---- System.Guid (Appendix A.5): canonical big-endian bytes <-> "D" string ---------------
+struct Guid {
+  uint8_t b[16];
+  bool Equals(const Guid& o) const { return memcmp(b, o.b, 16) == 0; }
+  std::string ToString() const {
+    static const char* hex = "0123456789abcdef";
+    std::string s;
+    for (int i = 0; i < 16; ++i) {
+      if (i == 4 || i == 6 || i == 8 || i == 10) s.push_back('-');
+      s.push_back(hex[b[i] >> 4]);
+      s.push_back(hex[b[i] & 15]);
+    }
+    return s;
+  }
+};
+
+std::u16string Utf8ToUtf16(const char* p, int len) {
+  std::u16string out;
+  int i = 0;
+  while (i < len) {
+    uint32_t c = (uint8_t)p[i];
+    uint32_t cp;
+    int extra;
+    if (c < 0x80) { cp = c; extra = 0; }
+    else if ((c >> 5) == 6) { cp = c & 0x1F; extra = 1; }
+    else if ((c >> 4) == 14) { cp = c & 0x0F; extra = 2; }
+    else if ((c >> 3) == 30) { cp = c & 0x07; extra = 3; }
+    else { cp = 0xFFFD; extra = 0; }
+    int j = 0;
+    for (; j < extra && i + 1 + j < len && (((uint8_t)p[i + 1 + j]) >> 6) == 2; ++j)
+      cp = (cp << 6) | ((uint8_t)p[i + 1 + j] & 0x3F);
+    if (j < extra) cp = 0xFFFD;
+    i += 1 + j;
+    if (cp >= 0x10000) {
+      cp -= 0x10000;
+      out.push_back((char16_t)(0xD800 + (cp >> 10)));
+      out.push_back((char16_t)(0xDC00 + (cp & 0x3FF)));
+    } else {
+      out.push_back((char16_t)cp);
+    }
+  }
+  return out;
+}
+
+// ---- Api/Models/TaskModel.cs:3-13 -------------------------------------------------------
+struct TaskModel {
+  Guid TaskId;
+  std::u16string TaskName;
+  std::u16string TaskCreatedBy;
+  DateTime TaskCreatedOn;
+  DateTime TaskDueDate;
+  std::u16string TaskAssignedTo;
+  bool IsCompleted = false;
+  bool IsOverDue = false;
+  int64_t row = -1;  // insertion index; test bookkeeping, not a reference field
+};
+
+struct NotImplementedException {};
+
+// Clock inputs the reference reads from the environment, made explicit.
+struct Clock {
+  int64_t today_local_ticks;  // DateTime.Today (local midnight, Kind Local)
+  int64_t run_at_utc_ticks;   // DateTime.UtcNow in the cron handler
+  int local_offset_min;       // local UTC offset, only used to print Kind=Local values
+  bool string_eq;             // STORE: compare JSON strings (faithful) or ticks/kind (fast)
+};
+
+using TaskList = std::vector<TaskModel*>;
+
+// string.Equals(string): ordinal, case-sensitive UTF-16 code-unit equality (Appendix A.4)
+inline bool OrdinalEquals(const std::u16string& a, const std::u16string& b) {
+  return a.size() == b.size() && memcmp(a.data(), b.data(), a.size() * sizeof(char16_t)) == 0;
+}
+
+// ---- Api/Services/FakeTasksManager.cs ---------------------------------------------------
+struct FakeTasksManager {
+  const TaskList& _tasksList;  // List<TaskModel> _tasksList (:7)
+
+  // :107-112  _tasksList.Where(t => t.TaskDueDate.Equals(DateTime.Today.AddDays(-1))).ToList()
+  TaskList GetYesterdaysDueTasks(const Clock& clk) const {
+    DateTime yesterday = DateTime(clk.today_local_ticks, TT_KIND_LOCAL).AddDays(-1);
+    TaskList tasksList;
+    for (TaskModel* t : _tasksList)
+      if (t->TaskDueDate.Equals(yesterday)) tasksList.push_back(t);
+    return tasksList;
+  }
+
+  // :102-105
+  void MarkOverdueTasks(const TaskList&) const { throw NotImplementedException(); }
+
+  // :68-72  Where(TaskCreatedBy.Equals(createdBy)).OrderByDescending(TaskCreatedOn).ToList()
+  TaskList GetTasksByCreator(const std::u16string& createdBy) const {
+    TaskList tasksList;
+    for (TaskModel* t : _tasksList)
+      if (OrdinalEquals(t->TaskCreatedBy, createdBy)) tasksList.push_back(t);
+    // OrderByDescending is a stable sort: equal keys keep source order
+    std::stable_sort(tasksList.begin(), tasksList.end(), [](const TaskModel* a, const TaskModel* b) {
+      return a->TaskCreatedOn.Ticks() > b->TaskCreatedOn.Ticks();
+    });
+    return tasksList;
+  }
+};
+
+// ---- Api/Services/TasksStoreManager.cs --------------------------------------------------
+// The Dapr state store is modelled as the documents in insertion order plus a key index
+// (key = TaskId.ToString(), :35).  The store-side EQ filter is exact string equality on the
+// stored JSON value.
+struct TasksStoreManager {
+  TaskList* docs;
+  std::unordered_map<std::string, int64_t>* keys;
+
+  static bool EqDueDate(const TaskModel* t, const DateTime& yesterday, const std::string& literal, const Clock& clk) {
+    if (clk.string_eq) return FormatSystemTextJson(t->TaskDueDate, clk.local_offset_min) == literal;
+    // equivalent arithmetic form: whole-second midnight of that day, Kind Unspecified
+    return t->TaskDueDate.Ticks() == yesterday.Ticks() && t->TaskDueDate.Kind() == TT_KIND_UNSPECIFIED;
+  }
+
+  // :104-139
+  std::vector<TaskModel> GetYesterdaysDueTasks(const Clock& clk) const {
+    DateTime yesterday = DateTime(clk.today_local_ticks, TT_KIND_LOCAL).AddDays(-1);  // :119
+    std::string jsonDate = FormatConverter(yesterday);                                // :121 (quotes implied)
+    std::vector<const TaskModel*> queryResults;                                       // :130 QueryStateAsync
+    for (const TaskModel* t : *docs)
+      if (EqDueDate(t, yesterday, jsonDate, clk)) queryResults.push_back(t);
+    std::vector<TaskModel> tasksList;
+    for (const TaskModel* q : queryResults)                                          // :133-135
+      if (q->IsCompleted == false && q->IsOverDue == false) tasksList.push_back(*q);  // deserialised copies
+    std::stable_sort(tasksList.begin(), tasksList.end(), [](const TaskModel& a, const TaskModel& b) {
+      return a.TaskCreatedOn.Ticks() < b.TaskCreatedOn.Ticks();                       // :136 OrderBy, stable
+    });
+    return tasksList;
+  }
+
+  // :141-149  foreach: IsOverDue = true; SaveStateAsync(key = TaskId.ToString(), whole record)
+  // Returns the number of keys that were not present (the reference would create them).
+  int64_t MarkOverdueTasks(std::vector<TaskModel>& overDueTasksList) const {
+    int64_t created = 0;
+    for (TaskModel& taskModel : overDueTasksList) {
+      taskModel.IsOverDue = true;
+      auto it = keys->find(taskModel.TaskId.ToString());
+      if (it == keys->end()) { ++created; continue; }  // upsert of an unknown key: counted, not stored
+      TaskModel* doc = (*docs)[it->second];
+      int64_t row = doc->row;
+      *doc = taskModel;  // the whole record is overwritten with the caller's copy
+      doc->row = row;
+    }
+    return created;
+  }
+
+  // :54-69
+  std::vector<TaskModel> GetTasksByCreator(const std::u16string& createdBy) const {
+    std::vector<TaskModel> tasksList;
+    for (const TaskModel* t : *docs)
+      if (OrdinalEquals(t->TaskCreatedBy, createdBy)) tasksList.push_back(*t);
+    std::stable_sort(tasksList.begin(), tasksList.end(), [](const TaskModel& a, const TaskModel& b) {
+      return a.TaskCreatedOn.Ticks() > b.TaskCreatedOn.Ticks();                       // :66 OrderByDescending
+    });
+    return tasksList;
+  }
+};
+
+struct OracleTable {
+  TaskList rows;  // owns the TaskModel objects
+  std::unordered_map<std::string, int64_t> keys;
+  bool keys_built = false;
+  ~OracleTable() { for (TaskModel* t : rows) delete t; }
+  void BuildKeys() {
+    if (keys_built) return;
+    keys.reserve(rows.size() * 2);
+    for (TaskModel* t : rows) keys[t->TaskId.ToString()] = t->row;
+    keys_built = true;
+  }
+  void Add(TaskModel* t) { t->row = (int64_t)rows.size(); rows.push_back(t); keys_built = false; }
+};
+
+void GuidFromHiLo(uint64_t hi, uint64_t lo, Guid* g) {
+  for (int i = 0; i < 8; ++i) g->b[i] = (uint8_t)(hi >> (56 - 8 * i));
+  for (int i = 0; i < 8; ++i) g->b[8 + i] = (uint8_t)(lo >> (56 - 8 * i));
+}
+
+TaskModel* SynthTask(const tt_synth_cfg* cfg, uint64_t grow) {
+  tt_synth_row r = tt_synth_make(cfg, grow);
+  TaskModel* t = new TaskModel();
+  GuidFromHiLo(r.id_hi, r.id_lo, &t->TaskId);
+  char buf[48];
+  int n = tt_synth_creator(r.creator, buf);
+  t->TaskCreatedBy = Utf8ToUtf16(buf, n);
+  char name[48];
+  int nn = snprintf(name, sizeof name, "Task number: %llu", (unsigned long long)grow);
+  t->TaskName = Utf8ToUtf16(name, nn);
+  t->TaskCreatedOn = DateTime(r.created_raw);
+  t->TaskDueDate = DateTime(r.due_raw);
+  t->IsCompleted = r.completed;
+  t->IsOverDue = r.overdue;
+  return t;
+}
+
+}  // namespace
+
+extern "C" {
+
+typedef struct OracleTable orc_table;
+
+#define ORC_MODE_FAKE 0
+#define ORC_MODE_STORE 1
+
+orc_table* orc_create(void) { return new OracleTable(); }
+void orc_destroy(orc_table* t) { delete t; }
+int64_t orc_count(orc_table* t) { return (int64_t)t->rows.size(); }
+
+int64_t orc_add(orc_table* t, const uint8_t* id16, const char* name, int32_t name_len, const char* created_by,
+                int32_t created_by_len, const char* assigned, int32_t assigned_len, uint64_t created_raw,
+                uint64_t due_raw, int32_t completed, int32_t overdue) {
+  TaskModel* m = new TaskModel();
+  memcpy(m->TaskId.b, id16, 16);
+  m->TaskName = Utf8ToUtf16(name, name_len);
+  m->TaskCreatedBy = Utf8ToUtf16(created_by, created_by_len);
+  m->TaskAssignedTo = Utf8ToUtf16(assigned, assigned_len);
+  m->TaskCreatedOn = DateTime(created_raw);
+  m->TaskDueDate = DateTime(due_raw);
+  m->IsCompleted = completed != 0;
+  m->IsOverDue = overdue != 0;
+  t->Add(m);
+  return m->row;
+}
+
+int64_t orc_add_synth(orc_table* t, const tt_synth_cfg* cfg, uint64_t first_row, uint64_t n) {
+  t->rows.reserve(t->rows.size() + n);
+  for (uint64_t i = 0; i < n; ++i) t->Add(SynthTask(cfg, first_row + i));
+  return (int64_t)t->rows.size();
+}
+
+// Api/Services/FakeTasksManager.cs:10-25 with the clock and the RNG injected.  TaskIds are
+// v4-shaped values from a splitmix stream (Guid.NewGuid() is random in the reference).
+void orc_seed_fake(orc_table* t, int64_t now_utc_ticks, uint64_t rng_seed) {
+  DateTime now(now_utc_ticks, TT_KIND_UTC);
+  for (int i = 0; i < 10; ++i) {
+    TaskModel* m = new TaskModel();
+    uint64_t hi = tt_mix64(rng_seed + 2 * i), lo = tt_mix64(rng_seed + 2 * i + 1);
+    hi = (hi & ~0xF000ULL) | 0x4000ULL;
+    lo = (lo & 0x3FFFFFFFFFFFFFFFULL) | 0x8000000000000000ULL;
+    GuidFromHiLo(hi, lo, &m->TaskId);
+    char buf[64];
+    int n = snprintf(buf, sizeof buf, "Task number: %d", i);
+    m->TaskName = Utf8ToUtf16(buf, n);
+    const char* by = "tjoudeh@bitoftech.net";
+    m->TaskCreatedBy = Utf8ToUtf16(by, (int)strlen(by));
+    m->TaskCreatedOn = now.AddMinutes(i);
+    m->TaskDueDate = now.AddDays(i);
+    n = snprintf(buf, sizeof buf, "assignee%d@mail.com", (int)(tt_mix64(rng_seed + 100 + i) % 50));
+    m->TaskAssignedTo = Utf8ToUtf16(buf, n);
+    t->Add(m);
+  }
+}
+
+static Clock MakeClock(int64_t today, int64_t run_at, int32_t off, int32_t string_eq) {
+  Clock c;
+  c.today_local_ticks = today;
+  c.run_at_utc_ticks = run_at;
+  c.local_offset_min = off;
+  c.string_eq = string_eq != 0;
+  return c;
+}
+
+static int64_t Emit(const std::vector<int64_t>& rows, uint32_t* out, int64_t cap) {
+  for (int64_t i = 0; i < (int64_t)rows.size() && i < cap; ++i) out[i] = (uint32_t)rows[i];
+  return (int64_t)rows.size();
+}
+
+// ITasksManager.GetYesterdaysDueTasks — returns the count; writes up to cap row numbers in
+// the order the reference's list has.
+int64_t orc_get_yesterdays_due(orc_table* t, int32_t mode, int64_t today_local_ticks, int32_t local_offset_min,
+                               int32_t string_eq, uint32_t* out_rows, int64_t cap) {
+  Clock clk = MakeClock(today_local_ticks, 0, local_offset_min, string_eq);
+  std::vector<int64_t> rows;
+  if (mode == ORC_MODE_FAKE) {
+    FakeTasksManager m{t->rows};
+    for (TaskModel* x : m.GetYesterdaysDueTasks(clk)) rows.push_back(x->row);
+  } else {
+    TasksStoreManager m{&t->rows, &t->keys};
+    for (const TaskModel& x : m.GetYesterdaysDueTasks(clk)) rows.push_back(x.row);
+  }
+  return Emit(rows, out_rows, cap);
+}
+
+// Svc/Controllers/ScheduledTasksManagerController.cs:19-46 — the whole cron tick:
+// GET api/overduetasks -> keep runAt.Date > TaskDueDate.Date -> POST markoverdue if any.
+// Returns 0, or 1 when the manager threw NotImplementedException (FAKE mode with survivors).
+int32_t orc_cron_job(orc_table* t, int32_t mode, int64_t today_local_ticks, int64_t run_at_utc_ticks,
+                     int32_t local_offset_min, int32_t string_eq, int64_t* n_listed, int64_t* n_overdue,
+                     uint32_t* out_rows, int64_t cap) {
+  Clock clk = MakeClock(today_local_ticks, run_at_utc_ticks, local_offset_min, string_eq);
+  DateTime runAt(clk.run_at_utc_ticks, TT_KIND_UTC);  // :22
+  std::vector<int64_t> listed;
+  int32_t status = 0;
+  if (mode == ORC_MODE_FAKE) {
+    FakeTasksManager m{t->rows};
+    TaskList tasksList = m.GetYesterdaysDueTasks(clk);  // :28
+    TaskList overdueTasksList;
+    for (TaskModel* taskModel : tasksList) {            // :32-38
+      listed.push_back(taskModel->row);
+      if (runAt.Date() > taskModel->TaskDueDate.Date()) overdueTasksList.push_back(taskModel);
+    }
+    *n_overdue = (int64_t)overdueTasksList.size();
+    if (overdueTasksList.size() > 0) {                  // :40-45
+      try { m.MarkOverdueTasks(overdueTasksList); } catch (const NotImplementedException&) { status = 1; }
+    }
+  } else {
+    t->BuildKeys();
+    TasksStoreManager m{&t->rows, &t->keys};
+    std::vector<TaskModel> tasksList = m.GetYesterdaysDueTasks(clk);
+    std::vector<TaskModel> overdueTasksList;
+    for (TaskModel& taskModel : tasksList) {
+      listed.push_back(taskModel.row);
+      if (runAt.Date() > taskModel.TaskDueDate.Date()) overdueTasksList.push_back(taskModel);
+    }
+    *n_overdue = (int64_t)overdueTasksList.size();
+    if (overdueTasksList.size() > 0) m.MarkOverdueTasks(overdueTasksList);
+  }
+  *n_listed = (int64_t)listed.size();
+  Emit(listed, out_rows, cap);
+  return status;
+}
+
+// ITasksManager.MarkOverdueTasks(list) addressed by TaskId.  Returns 0, or 1 if it threw
+// (FAKE).  *n_missing = ids with no stored record.
+int32_t orc_mark_overdue(orc_table* t, int32_t mode, const uint8_t* ids16, int64_t n, int64_t* n_missing) {
+  *n_missing = 0;
+  if (mode == ORC_MODE_FAKE) {
+    try { FakeTasksManager{t->rows}.MarkOverdueTasks(TaskList()); } catch (const NotImplementedException&) { return 1; }
+    return 0;
+  }
+  t->BuildKeys();
+  TasksStoreManager m{&t->rows, &t->keys};
+  std::vector<TaskModel> list;
+  for (int64_t i = 0; i < n; ++i) {
+    Guid g;
+    memcpy(g.b, ids16 + 16 * i, 16);
+    auto it = t->keys.find(g.ToString());
+    if (it != t->keys.end()) {
+      list.push_back(*t->rows[it->second]);  // the caller's copy of the stored record
+    } else {
+      TaskModel x;
+      x.TaskId = g;
+      list.push_back(x);
+    }
+  }
+  *n_missing = m.MarkOverdueTasks(list);
+  return 0;
+}
+
+int64_t orc_get_by_creator(orc_table* t, int32_t mode, const char* utf8, int32_t len, uint32_t* out_rows, int64_t cap) {
+  std::u16string createdBy = Utf8ToUtf16(utf8, len);
+  std::vector<int64_t> rows;
+  if (mode == ORC_MODE_FAKE) {
+    FakeTasksManager m{t->rows};
+    for (TaskModel* x : m.GetTasksByCreator(createdBy)) rows.push_back(x->row);
+  } else {
+    TasksStoreManager m{&t->rows, &t->keys};
+    for (const TaskModel& x : m.GetTasksByCreator(createdBy)) rows.push_back(x.row);
+  }
+  return Emit(rows, out_rows, cap);
+}
+
+void orc_get_flags(orc_table* t, uint8_t* completed, uint8_t* overdue) {
+  for (size_t i = 0; i < t->rows.size(); ++i) {
+    completed[i] = t->rows[i]->IsCompleted;
+    overdue[i] = t->rows[i]->IsOverDue;
+  }
+}
+
+void orc_set_flags(orc_table* t, int64_t row, int32_t completed, int32_t overdue) {
+  t->rows[row]->IsCompleted = completed != 0;
+  t->rows[row]->IsOverDue = overdue != 0;
+}
+
+// Column export so tests can load the same rows into the device table.
+void orc_export(orc_table* t, uint8_t* ids16, uint64_t* created_raw, uint64_t* due_raw) {
+  for (size_t i = 0; i < t->rows.size(); ++i) {
+    memcpy(ids16 + 16 * i, t->rows[i]->TaskId.b, 16);
+    created_raw[i] = t->rows[i]->TaskCreatedOn.dateData;
+    due_raw[i] = t->rows[i]->TaskDueDate.dateData;
+  }
+}
+
+// UTF-8 of TaskCreatedBy for one row (ASCII / BMP only is enough for the tests). Returns length.
+int32_t orc_created_by(orc_table* t, int64_t row, char* out, int32_t cap) {
+  const std::u16string& s = t->rows[row]->TaskCreatedBy;
+  int32_t n = 0;
+  for (char16_t c : s) {
+    if (c < 0x80) { if (n < cap) out[n] = (char)c; n += 1; }
+    else if (c < 0x800) { if (n + 1 < cap) { out[n] = (char)(0xC0 | (c >> 6)); out[n + 1] = (char)(0x80 | (c & 0x3F)); } n += 2; }
+    else { if (n + 2 < cap) { out[n] = (char)(0xE0 | (c >> 12)); out[n + 1] = (char)(0x80 | ((c >> 6) & 0x3F)); out[n + 2] = (char)(0x80 | (c & 0x3F)); } n += 3; }
+  }
+  return n;
+}
+
+int32_t orc_format_stj(uint64_t raw, int32_t local_offset_min, char* out, int32_t cap) {
+  std::string s = FormatSystemTextJson(DateTime(raw), local_offset_min);
+  snprintf(out, cap, "%s", s.c_str());
+  return (int32_t)s.size();
+}
+
+int32_t orc_format_converter(uint64_t raw, char* out, int32_t cap) {
+  std::string s = FormatConverter(DateTime(raw));
+  snprintf(out, cap, "%s", s.c_str());
+  return (int32_t)s.size();
+}
+
+void orc_guid_string(const uint8_t* id16, char* out37) {
+  Guid g;
+  memcpy(g.b, id16, 16);
+  std::string s = g.ToString();
+  memcpy(out37, s.c_str(), 37);
+}
+
+// ---- full-size checker: the same predicates applied to rows generated on the fly ----------
+// (no table is stored; used for the 1 B-row parity properties).  Rows are independent, so the
+// range is split over threads and the partial sums combined; every quantity is order-free.
+typedef struct orc_stream_out {
+  int64_t n_listed;           // rows GetYesterdaysDueTasks returns
+  int64_t n_marked;           // rows whose IsOverDue the cron tick sets
+  uint64_t xor_id_hi, xor_id_lo;  // XOR of the listed TaskIds
+  uint64_t sum_rows;          // sum of listed shard-local row numbers (mod 2^64)
+  int64_t overdue_after;      // popcount of IsOverDue after the tick
+  int64_t completed;          // popcount of IsCompleted
+  int32_t threw;              // FAKE mode with survivors
+} orc_stream_out;
+
+void orc_stream_sweep(const tt_synth_cfg* cfg, uint64_t first_row, uint64_t n, int32_t mode, int64_t today_local_ticks,
+                      int64_t run_at_utc_ticks, int32_t threads, orc_stream_out* out) {
+  if (threads < 1) threads = 1;
+  std::vector<orc_stream_out> part(threads);
+  std::vector<std::thread> pool;
+  DateTime yesterday = DateTime(today_local_ticks, TT_KIND_LOCAL).AddDays(-1);
+  DateTime runAt(run_at_utc_ticks, TT_KIND_UTC);
+  for (int th = 0; th < threads; ++th) {
+    pool.emplace_back([&, th]() {
+      orc_stream_out o;
+      memset(&o, 0, sizeof o);
+      uint64_t lo = n * th / threads, hi = n * (th + 1) / threads;
+      for (uint64_t i = lo; i < hi; ++i) {
+        tt_synth_row r = tt_synth_make(cfg, first_row + i);
+        DateTime due(r.due_raw);
+        bool listed;
+        if (mode == ORC_MODE_FAKE) listed = due.Equals(yesterday);
+        else listed = due.Ticks() == yesterday.Ticks() && due.Kind() == TT_KIND_UNSPECIFIED && !r.completed && !r.overdue;
+        bool overdue = r.overdue;
+        if (listed) {
+          o.n_listed++;
+          o.xor_id_hi ^= r.id_hi;
+          o.xor_id_lo ^= r.id_lo;
+          o.sum_rows += i;
+          if (runAt.Date() > due.Date()) {
+            o.n_marked++;
+            if (mode == ORC_MODE_STORE) overdue = true;
+          }
+        }
+        o.overdue_after += overdue;
+        o.completed += r.completed;
+      }
+      part[th] = o;
+    });
+  }
+  for (auto& t : pool) t.join();
+  memset(out, 0, sizeof *out);
+  for (auto& o : part) {
+    out->n_listed += o.n_listed;
+    out->n_marked += o.n_marked;
+    out->xor_id_hi ^= o.xor_id_hi;
+    out->xor_id_lo ^= o.xor_id_lo;
+    out->sum_rows += o.sum_rows;
+    out->overdue_after += o.overdue_after;
+    out->completed += o.completed;
+  }
+  if (mode == ORC_MODE_FAKE) {
+    out->threw = out->n_marked > 0;
+    // the throw happens before any state change; nothing is marked in FAKE mode
+  }
+}
+
+// ---- "best-effort CPU" context number: the same sweep over SoA columns on all cores -------
+// (not the reference's algorithm layout; reported beside the LINQ-faithful number)
+typedef struct orc_soa {
+  int64_t n;
+  uint64_t* due_raw;
+  uint8_t* completed;
+  uint8_t* overdue;
+} orc_soa;
+
+orc_soa* orc_soa_create(const tt_synth_cfg* cfg, uint64_t first_row, int64_t n, int32_t threads) {
+  orc_soa* s = new orc_soa();
+  s->n = n;
+  s->due_raw = new uint64_t[n];
+  s->completed = new uint8_t[n];
+  s->overdue = new uint8_t[n];
+  if (threads < 1) threads = 1;
+  std::vector<std::thread> pool;
+  for (int th = 0; th < threads; ++th)
+    pool.emplace_back([=]() {
+      for (int64_t i = n * th / threads; i < n * (th + 1) / threads; ++i) {
+        tt_synth_row r = tt_synth_make(cfg, first_row + (uint64_t)i);
+        s->due_raw[i] = r.due_raw;
+        s->completed[i] = r.completed;
+        s->overdue[i] = r.overdue;
+      }
+    });
+  for (auto& t : pool) t.join();
+  return s;
+}
+
+void orc_soa_destroy(orc_soa* s) {
+  delete[] s->due_raw;
+  delete[] s->completed;
+  delete[] s->overdue;
+  delete s;
+}
+
+// STORE-mode tick over the SoA copy: list + mark.  Returns the hit count; out_rows (cap >= n
+// is not required: hits beyond cap are counted but not stored).
+int64_t orc_soa_sweep(orc_soa* s, int64_t today_local_ticks, int64_t run_at_utc_ticks, int32_t threads,
+                      uint32_t* out_rows, int64_t cap) {
+  if (threads < 1) threads = 1;
+  const uint64_t yraw = (uint64_t)(today_local_ticks - kTicksPerDay);  // Kind Unspecified = top bits 0
+  const bool mark = run_at_utc_ticks / kTicksPerDay > (today_local_ticks - kTicksPerDay) / kTicksPerDay;
+  std::atomic<int64_t> cursor{0};
+  std::vector<std::thread> pool;
+  for (int th = 0; th < threads; ++th)
+    pool.emplace_back([&, th]() {
+      std::vector<uint32_t> local;
+      int64_t lo = s->n * th / threads, hi = s->n * (th + 1) / threads;
+      for (int64_t i = lo; i < hi; ++i) {
+        if (s->due_raw[i] == yraw && !s->completed[i] && !s->overdue[i]) {
+          local.push_back((uint32_t)i);
+          if (mark) s->overdue[i] = 1;
+        }
+      }
+      int64_t at = cursor.fetch_add((int64_t)local.size());
+      for (size_t k = 0; k < local.size(); ++k)
+        if (at + (int64_t)k < cap) out_rows[at + k] = local[k];
+    });
+  for (auto& t : pool) t.join();
+  return cursor.load();
+}
+
+}  // extern "C"
