@@ -1,0 +1,877 @@
+// tasktable.cu — the C ABI of include/tasktable.h over the sm_100a kernels.
+//
+// Host side: table lifetime, synthetic fill / SoA load, result objects, the resumable sweep
+// driver.  No CPU implementation of any ITasksManager operation lives here: if CUDA is not
+// usable every call fails with TT_ERR_CUDA.
+
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "../../include/tasktable.h"
+#include "creator.cuh"
+#include "order.cuh"
+#include "sweep.cuh"
+#include "tt_bits.h"
+
+namespace {
+
+thread_local std::string g_err = "";
+
+int32_t fail(int32_t code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  g_err = buf;
+  return code;
+}
+
+#define TT_CUDA(expr)                                                                              \
+  do {                                                                                             \
+    cudaError_t e_ = (expr);                                                                       \
+    if (e_ != cudaSuccess) {                                                                       \
+      cudaGetLastError();                                                                          \
+      return fail(e_ == cudaErrorMemoryAllocation ? TT_ERR_OOM : TT_ERR_CUDA, "%s: %s (%s:%d)", #expr, \
+                  cudaGetErrorString(e_), __FILE__, __LINE__);                                     \
+    }                                                                                              \
+  } while (0)
+
+constexpr int64_t kMaxRows = 1ll << 31;
+
+inline int64_t round_up(int64_t x, int64_t m) { return (x + m - 1) / m * m; }
+
+}  // namespace
+
+struct tt_table {
+  int device = 0;
+  std::mutex mu;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  int sm_count = 148;
+
+  int64_t n = 0, n_pad = 0;
+  // hot columns
+  uint32_t* due_code = nullptr;
+  uint32_t* completed = nullptr;
+  uint32_t* overdue = nullptr;
+  uint64_t* creator_hash = nullptr;
+  // cold columns
+  uint4* task_id = nullptr;
+  uint64_t* created_raw = nullptr;
+  uint64_t* due_raw = nullptr;
+  uint32_t* creator_ref = nullptr;
+  // creator dictionary
+  uint32_t n_creators = 0;
+  uint32_t* creator_off = nullptr;
+  uint8_t* creator_pool = nullptr;
+  uint64_t pool_bytes = 0;
+  bool ids_sorted = false;
+  uint32_t* id_order = nullptr;  // rows sorted by TaskId when the table itself is not
+
+  // sweep scratch: one status word per tile + control block (device) and its pinned mirror
+  unsigned long long* tile_status = nullptr;
+  int64_t tile_status_cap = 0;
+  tt::SweepCtl* ctl = nullptr;
+  tt::SweepCtl* h_ctl = nullptr;
+  // small device/pinned scratch for reductions and the creator filter
+  unsigned long long* d_small = nullptr;  // 16 words
+  unsigned long long* h_small = nullptr;
+  uint8_t* d_query = nullptr;  // creator-filter query bytes
+  size_t d_query_cap = 0;
+};
+
+struct tt_result {
+  tt_table* t = nullptr;
+  int64_t n = 0;
+  int64_t cap = 0;
+  uint32_t* d_rows = nullptr;
+  uint4* d_ids = nullptr;
+};
+
+namespace {
+
+struct DeviceGuard {
+  int prev = -1;
+  explicit DeviceGuard(int dev) {
+    cudaGetDevice(&prev);
+    if (prev != dev) cudaSetDevice(dev);
+  }
+  ~DeviceGuard() {
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+};
+
+void free_columns(tt_table* t) {
+  cudaFree(t->due_code);
+  cudaFree(t->completed);
+  cudaFree(t->overdue);
+  cudaFree(t->creator_hash);
+  cudaFree(t->task_id);
+  cudaFree(t->created_raw);
+  cudaFree(t->due_raw);
+  cudaFree(t->creator_ref);
+  cudaFree(t->creator_off);
+  cudaFree(t->creator_pool);
+  cudaFree(t->id_order);
+  cudaFree(t->tile_status);
+  t->due_code = t->completed = t->overdue = nullptr;
+  t->creator_hash = nullptr;
+  t->task_id = nullptr;
+  t->created_raw = t->due_raw = nullptr;
+  t->creator_ref = t->creator_off = t->id_order = nullptr;
+  t->creator_pool = nullptr;
+  t->tile_status = nullptr;
+  t->tile_status_cap = 0;
+  t->n = t->n_pad = 0;
+}
+
+int32_t alloc_columns(tt_table* t, int64_t n) {
+  if (t->n_pad != 0) return fail(TT_ERR_STATE, "table already holds %lld rows", (long long)t->n);
+  if (n < 0 || n > kMaxRows) return fail(TT_ERR_ARG, "row count %lld outside [0, 2^31]", (long long)n);
+  int64_t np = std::max<int64_t>(round_up(n, TT_TILE_ROWS), TT_TILE_ROWS);
+  TT_CUDA(cudaMalloc(&t->due_code, np * 4));
+  TT_CUDA(cudaMalloc(&t->completed, np / 8));
+  TT_CUDA(cudaMalloc(&t->overdue, np / 8));
+  TT_CUDA(cudaMalloc(&t->creator_hash, np * 8));
+  TT_CUDA(cudaMalloc(&t->task_id, np * 16));
+  TT_CUDA(cudaMalloc(&t->created_raw, np * 8));
+  TT_CUDA(cudaMalloc(&t->due_raw, np * 8));
+  TT_CUDA(cudaMalloc(&t->creator_ref, np * 4));
+  t->tile_status_cap = np / TT_TILE_ROWS;
+  TT_CUDA(cudaMalloc(&t->tile_status, t->tile_status_cap * 8));
+  // padding rows never match and carry no flags
+  TT_CUDA(cudaMemsetAsync(t->due_code, 0xFF, np * 4, t->stream));
+  TT_CUDA(cudaMemsetAsync(t->completed, 0, np / 8, t->stream));
+  TT_CUDA(cudaMemsetAsync(t->overdue, 0, np / 8, t->stream));
+  TT_CUDA(cudaMemsetAsync(t->creator_hash, 0, np * 8, t->stream));
+  TT_CUDA(cudaMemsetAsync(t->task_id, 0, np * 16, t->stream));
+  TT_CUDA(cudaMemsetAsync(t->created_raw, 0, np * 8, t->stream));
+  TT_CUDA(cudaMemsetAsync(t->due_raw, 0, np * 8, t->stream));
+  TT_CUDA(cudaMemsetAsync(t->creator_ref, 0, np * 4, t->stream));
+  t->n = n;
+  t->n_pad = np;
+  return TT_OK;
+}
+
+int32_t upload_dictionary(tt_table* t, uint32_t n_creators, const uint32_t* off, const uint8_t* pool) {
+  t->n_creators = n_creators;
+  t->pool_bytes = n_creators ? off[n_creators] : 0;
+  TT_CUDA(cudaMalloc(&t->creator_off, ((size_t)n_creators + 1) * 4));
+  TT_CUDA(cudaMalloc(&t->creator_pool, std::max<uint64_t>(t->pool_bytes, 16)));
+  TT_CUDA(cudaMemcpyAsync(t->creator_off, off, ((size_t)n_creators + 1) * 4, cudaMemcpyHostToDevice, t->stream));
+  if (t->pool_bytes)
+    TT_CUDA(cudaMemcpyAsync(t->creator_pool, pool, t->pool_bytes, cudaMemcpyHostToDevice, t->stream));
+  return TT_OK;
+}
+
+// ---- small kernels --------------------------------------------------------------------------
+
+// Synthetic fill: one thread per row, a warp covers one flag word.
+__global__ void fill_synth_kernel(tt_synth_cfg cfg, uint64_t first_row, int64_t n, uint32_t* due_code,
+                                  uint32_t* completed, uint32_t* overdue, uint64_t* creator_hash, uint4* task_id,
+                                  uint64_t* created_raw, uint64_t* due_raw, uint32_t* creator_ref,
+                                  const uint64_t* dict_hash) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;  // grid covers a multiple of 32 rows
+  bool live = i < n;
+  bool c = false, o = false;
+  if (live) {
+    tt_synth_row r = tt_synth_make(&cfg, first_row + (uint64_t)i);
+    due_code[i] = tt_pack_due(r.due_raw);
+    due_raw[i] = r.due_raw;
+    created_raw[i] = r.created_raw;
+    creator_ref[i] = r.creator;
+    creator_hash[i] = dict_hash[r.creator];
+    // canonical big-endian bytes 0..15 laid out in memory order: x = bytes 0..3, ...
+    uint4 id;
+    id.x = __byte_perm((uint32_t)(r.id_hi >> 32), 0, 0x0123);
+    id.y = __byte_perm((uint32_t)r.id_hi, 0, 0x0123);
+    id.z = __byte_perm((uint32_t)(r.id_lo >> 32), 0, 0x0123);
+    id.w = __byte_perm((uint32_t)r.id_lo, 0, 0x0123);
+    task_id[i] = id;
+    c = r.completed;
+    o = r.overdue;
+  }
+  uint32_t cw = __ballot_sync(0xFFFFFFFFu, c), ow = __ballot_sync(0xFFFFFFFFu, o);
+  if ((threadIdx.x & 31) == 0 && i < ((n + 31) & ~31ll)) {
+    completed[i >> 5] = cw;
+    overdue[i >> 5] = ow;
+  }
+}
+
+__global__ void hash_rows_kernel(const uint32_t* creator_ref, const uint64_t* dict_hash, uint64_t* creator_hash,
+                                 int64_t n) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) creator_hash[i] = dict_hash[creator_ref[i]];
+}
+
+// popcount of both flag planes -> out[0], out[1]
+__global__ void count_flags_kernel(const uint32_t* completed, const uint32_t* overdue, int64_t words,
+                                   unsigned long long* out) {
+  unsigned long long c = 0, o = 0;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < words; i += (int64_t)gridDim.x * blockDim.x) {
+    c += __popc(completed[i]);
+    o += __popc(overdue[i]);
+  }
+  for (int d = 16; d > 0; d >>= 1) {
+    c += __shfl_xor_sync(0xFFFFFFFFu, c, d);
+    o += __shfl_xor_sync(0xFFFFFFFFu, o, d);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    atomicAdd(out + 0, c);
+    atomicAdd(out + 1, o);
+  }
+}
+
+__device__ __forceinline__ uint64_t be64(uint32_t a, uint32_t b) {
+  return ((uint64_t)__byte_perm(a, 0, 0x0123) << 32) | __byte_perm(b, 0, 0x0123);
+}
+
+// XOR of ids (as big-endian hi/lo u64) and sum of rows -> out[0..2]
+__global__ void digest_kernel(const uint32_t* rows, const uint4* ids, int64_t n, unsigned long long* out) {
+  unsigned long long xh = 0, xl = 0, sr = 0;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    uint4 id = ids[i];
+    xh ^= be64(id.x, id.y);
+    xl ^= be64(id.z, id.w);
+    sr += rows[i];
+  }
+  for (int d = 16; d > 0; d >>= 1) {
+    xh ^= __shfl_xor_sync(0xFFFFFFFFu, xh, d);
+    xl ^= __shfl_xor_sync(0xFFFFFFFFu, xl, d);
+    sr += __shfl_xor_sync(0xFFFFFFFFu, sr, d);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    atomicXor(out + 0, xh);
+    atomicXor(out + 1, xl);
+    atomicAdd(out + 2, sr);
+  }
+}
+
+template <typename T>
+__global__ void gather_field_kernel(const uint32_t* rows, const T* col, T* out, int64_t n) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = col[rows[i]];
+}
+
+__global__ void gather_bit_kernel(const uint32_t* rows, const uint32_t* plane, uint8_t* out, int64_t n) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) {
+    uint32_t r = rows[i];
+    out[i] = (plane[r >> 5] >> (r & 31)) & 1u;
+  }
+}
+
+inline unsigned grid_for(int64_t n, int block) { return (unsigned)std::max<int64_t>(1, (n + block - 1) / block); }
+
+// ---- the resumable sweep driver -------------------------------------------------------------
+
+int32_t check_clock(int64_t today_local_ticks, uint32_t* yesterday) {
+  if (today_local_ticks < TT_TICKS_PER_DAY || today_local_ticks % TT_TICKS_PER_DAY != 0)
+    return fail(TT_ERR_ARG, "today_local_ticks must be a midnight (DateTime.Today) on or after 0001-01-02");
+  int64_t day = today_local_ticks / TT_TICKS_PER_DAY - 1;
+  if (day > (int64_t)TT_DUE_DAY_MASK) return fail(TT_ERR_ARG, "today_local_ticks beyond DateTime.MaxValue");
+  *yesterday = (uint32_t)day;
+  return TT_OK;
+}
+
+// Launches the sweep kernel over rows [first_row, n) on `stream`, waits, fills *st.
+int32_t sweep_run(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_ticks, int64_t run_at_utc_ticks,
+                  int64_t first_row, uint32_t* d_rows, uint4* d_ids, int64_t cap, tt_sweep_stats* st,
+                  cudaStream_t stream) {
+  memset(st, 0, sizeof *st);
+  if (mode != TT_MODE_FAKE && mode != TT_MODE_STORE) return fail(TT_ERR_ARG, "mode must be TT_MODE_FAKE or TT_MODE_STORE");
+  uint32_t yesterday = 0;
+  int32_t rc = check_clock(today_local_ticks, &yesterday);
+  if (rc) return rc;
+  if (first_row < 0 || first_row % TT_TILE_ROWS != 0 || (first_row > t->n && first_row != t->n_pad))
+    return fail(TT_ERR_ARG, "first_row must be a multiple of %d inside the table", TT_TILE_ROWS);
+  if (cap < 0) return fail(TT_ERR_ARG, "negative capacity");
+  const bool mark = (flags & TT_SWEEP_MARK) != 0;
+  // ScheduledTasksManagerController.cs:34 — runAt.Date > TaskDueDate.Date; for listed rows the
+  // right-hand side is yesterday's day number (see sweep.cuh).
+  const bool survive = run_at_utc_ticks / TT_TICKS_PER_DAY > (int64_t)yesterday;
+  if (t->n == 0 || first_row >= t->n) {
+    st->resume_row = t->n;
+    return TT_OK;
+  }
+  const uint32_t first_tile = (uint32_t)(first_row / TT_TILE_ROWS);
+  const uint32_t num_tiles = (uint32_t)(t->n_pad / TT_TILE_ROWS) - first_tile;
+
+  tt::SweepParams p;
+  p.due_code = t->due_code;
+  p.completed = t->completed;
+  p.overdue = t->overdue;
+  p.task_id = t->task_id;
+  p.out_rows = d_rows;
+  p.out_ids = d_ids;
+  p.tile_status = t->tile_status;
+  p.ctl = t->ctl;
+  p.cap = d_rows ? (unsigned long long)cap : ~0ull;
+  p.first_tile = first_tile;
+  p.num_tiles = num_tiles;
+  p.mask = mode == TT_MODE_FAKE ? TT_MASK_FAKE : TT_MASK_STORE;
+  p.yesterday = yesterday;
+  // FAKE mode never mutates: MarkOverdueTasks throws before touching the list (FakeTasksManager.cs:104)
+  p.mark_enable = (mark && survive && mode == TT_MODE_STORE) ? 1u : 0u;
+
+  tt::SweepCtl init;
+  init.tile_counter = 0;
+  init.pad = 0;
+  init.total = 0;
+  init.overflow = ~0ull;
+  *t->h_ctl = init;
+  TT_CUDA(cudaMemcpyAsync(t->ctl, t->h_ctl, sizeof init, cudaMemcpyHostToDevice, stream));
+  TT_CUDA(cudaMemsetAsync(t->tile_status, 0, (size_t)num_tiles * 8, stream));
+  const unsigned grid = (unsigned)std::min<int64_t>(num_tiles, (int64_t)t->sm_count * tt::kSweepCtasPerSm);
+  TT_CUDA(cudaEventRecord(t->ev0, stream));
+  if (mode == TT_MODE_STORE) {
+    if (p.mark_enable)
+      tt::sweep_kernel<true, true><<<grid, tt::kSweepThreads, 0, stream>>>(p);
+    else
+      tt::sweep_kernel<true, false><<<grid, tt::kSweepThreads, 0, stream>>>(p);
+  } else {
+    tt::sweep_kernel<false, false><<<grid, tt::kSweepThreads, 0, stream>>>(p);
+  }
+  TT_CUDA(cudaGetLastError());
+  TT_CUDA(cudaEventRecord(t->ev1, stream));
+  TT_CUDA(cudaMemcpyAsync(t->h_ctl, t->ctl, sizeof init, cudaMemcpyDeviceToHost, stream));
+  TT_CUDA(cudaStreamSynchronize(stream));
+  TT_CUDA(cudaEventElapsedTime(&st->kernel_ms, t->ev0, t->ev1));
+  st->launches = 1;
+  st->n_listed = (int64_t)t->h_ctl->total;
+  if (t->h_ctl->overflow == ~0ull) {
+    st->n_stored = d_rows ? st->n_listed : 0;
+    st->resume_row = t->n;
+  } else {
+    st->n_stored = (int64_t)(t->h_ctl->overflow & 0xFFFFFFFFull);
+    st->resume_row = (int64_t)(t->h_ctl->overflow >> 32) * TT_TILE_ROWS;
+  }
+  st->n_marked = p.mark_enable ? (d_rows ? st->n_stored : st->n_listed) : 0;
+  if (mode == TT_MODE_FAKE && mark && survive) st->n_marked = 0;
+  if (t->h_ctl->overflow != ~0ull)
+    return fail(TT_ERR_CAPACITY, "%lld hits do not fit in %lld; resume at row %lld", (long long)st->n_listed,
+                (long long)cap, (long long)st->resume_row);
+  return TT_OK;
+}
+
+int32_t result_alloc(tt_table* t, int64_t cap, tt_result** out) {
+  tt_result* r = new (std::nothrow) tt_result();
+  if (!r) return fail(TT_ERR_OOM, "out of host memory");
+  r->t = t;
+  r->cap = std::max<int64_t>(cap, 1);
+  cudaError_t e = cudaMalloc(&r->d_rows, r->cap * 4);
+  if (e == cudaSuccess) e = cudaMalloc(&r->d_ids, r->cap * 16);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    cudaFree(r->d_rows);
+    delete r;
+    return fail(TT_ERR_OOM, "result buffers for %lld hits: %s", (long long)cap, cudaGetErrorString(e));
+  }
+  *out = r;
+  return TT_OK;
+}
+
+void result_release(tt_result* r) {
+  if (!r) return;
+  cudaFree(r->d_rows);
+  cudaFree(r->d_ids);
+  delete r;
+}
+
+// Sweep into a library-owned result, growing and resuming when the first guess is too small.
+int32_t sweep_owned(tt_table* t, int32_t mode, int32_t flags, int64_t today, int64_t run_at, tt_result** out,
+                    tt_sweep_stats* total) {
+  memset(total, 0, sizeof *total);
+  tt_result* r = nullptr;
+  int64_t guess = std::min<int64_t>(t->n, std::max<int64_t>(65536, t->n / 16));
+  int32_t rc = result_alloc(t, guess, &r);
+  if (rc) return rc;
+  int64_t first_row = 0;
+  for (int pass = 0; pass < 64; ++pass) {
+    tt_sweep_stats st;
+    rc = sweep_run(t, mode, flags, today, run_at, first_row, r->d_rows + r->n, r->d_ids + r->n, r->cap - r->n, &st,
+                   t->stream);
+    total->kernel_ms += st.kernel_ms;
+    total->launches += st.launches;
+    if (rc != TT_OK && rc != TT_ERR_CAPACITY) {
+      result_release(r);
+      return rc;
+    }
+    r->n += st.n_stored;
+    total->n_marked += st.n_marked;
+    if (rc == TT_OK) {
+      total->n_listed = r->n;
+      total->n_stored = r->n;
+      total->resume_row = t->n;
+      *out = r;
+      return TT_OK;
+    }
+    // grow to exactly what the remaining rows need, keep what is already listed
+    tt_result* g = nullptr;
+    rc = result_alloc(t, r->n + (st.n_listed - st.n_stored), &g);
+    if (rc) {
+      result_release(r);
+      return rc;
+    }
+    if (r->n) {
+      cudaMemcpyAsync(g->d_rows, r->d_rows, r->n * 4, cudaMemcpyDeviceToDevice, t->stream);
+      cudaMemcpyAsync(g->d_ids, r->d_ids, r->n * 16, cudaMemcpyDeviceToDevice, t->stream);
+      cudaStreamSynchronize(t->stream);
+    }
+    g->n = r->n;
+    result_release(r);
+    r = g;
+    first_row = st.resume_row;
+  }
+  result_release(r);
+  return fail(TT_ERR_STATE, "sweep did not converge");
+}
+
+}  // namespace
+
+// =============================================================================================
+extern "C" {
+
+const char* tt_last_error(void) { return g_err.c_str(); }
+
+int32_t tt_create(int32_t device, tt_table** out) {
+  if (!out) return fail(TT_ERR_ARG, "out is null");
+  *out = nullptr;
+  int count = 0;
+  TT_CUDA(cudaGetDeviceCount(&count));
+  if (device < 0 || device >= count) return fail(TT_ERR_ARG, "device %d not in [0, %d)", device, count);
+  DeviceGuard g(device);
+  tt_table* t = new (std::nothrow) tt_table();
+  if (!t) return fail(TT_ERR_OOM, "out of host memory");
+  t->device = device;
+  cudaDeviceProp prop;
+  TT_CUDA(cudaGetDeviceProperties(&prop, device));
+  t->sm_count = prop.multiProcessorCount;
+  TT_CUDA(cudaStreamCreateWithFlags(&t->stream, cudaStreamNonBlocking));
+  TT_CUDA(cudaEventCreate(&t->ev0));
+  TT_CUDA(cudaEventCreate(&t->ev1));
+  TT_CUDA(cudaMalloc(&t->ctl, sizeof(tt::SweepCtl)));
+  TT_CUDA(cudaMallocHost(&t->h_ctl, sizeof(tt::SweepCtl)));
+  TT_CUDA(cudaMalloc(&t->d_small, 16 * 8));
+  TT_CUDA(cudaMallocHost(&t->h_small, 16 * 8));
+  *out = t;
+  return TT_OK;
+}
+
+int32_t tt_destroy(tt_table* t) {
+  if (!t) return TT_OK;
+  {
+    DeviceGuard g(t->device);
+    cudaStreamSynchronize(t->stream);
+    free_columns(t);
+    cudaFree(t->ctl);
+    cudaFreeHost(t->h_ctl);
+    cudaFree(t->d_small);
+    cudaFreeHost(t->h_small);
+    cudaFree(t->d_query);
+    cudaEventDestroy(t->ev0);
+    cudaEventDestroy(t->ev1);
+    cudaStreamDestroy(t->stream);
+  }
+  delete t;
+  return TT_OK;
+}
+
+int32_t tt_row_count(tt_table* t, int64_t* n) {
+  if (!t || !n) return fail(TT_ERR_ARG, "null argument");
+  *n = t->n;
+  return TT_OK;
+}
+
+int32_t tt_generate(tt_table* t, const tt_synth_cfg* cfg, uint64_t first_row, uint64_t n_rows) {
+  if (!t || !cfg) return fail(TT_ERR_ARG, "null argument");
+  if (cfg->n_creators == 0) return fail(TT_ERR_ARG, "n_creators must be > 0");
+  if (cfg->today_local_ticks < 400 * TT_TICKS_PER_DAY || cfg->today_local_ticks % TT_TICKS_PER_DAY)
+    return fail(TT_ERR_ARG, "cfg.today_local_ticks must be a midnight");
+  std::lock_guard<std::mutex> lk(t->mu);
+  DeviceGuard g(t->device);
+  int32_t rc = alloc_columns(t, (int64_t)n_rows);
+  if (rc) return rc;
+  // creator dictionary: strings, offsets and hashes built once on the host (ingest, not hot path)
+  const uint32_t nc = cfg->n_creators;
+  std::vector<uint32_t> off(nc + 1);
+  std::vector<uint8_t> pool;
+  pool.reserve((size_t)nc * 26);
+  std::vector<uint64_t> hash(nc);
+  char buf[48];
+  for (uint32_t k = 0; k < nc; ++k) {
+    int len = tt_synth_creator(k, buf);
+    off[k] = (uint32_t)pool.size();
+    pool.insert(pool.end(), buf, buf + len);
+    hash[k] = tt_hash64((const uint8_t*)buf, (uint32_t)len);
+  }
+  off[nc] = (uint32_t)pool.size();
+  rc = upload_dictionary(t, nc, off.data(), pool.data());
+  if (rc) return rc;
+  uint64_t* d_hash = nullptr;
+  TT_CUDA(cudaMalloc(&d_hash, (size_t)nc * 8));
+  TT_CUDA(cudaMemcpyAsync(d_hash, hash.data(), (size_t)nc * 8, cudaMemcpyHostToDevice, t->stream));
+  if (n_rows) {
+    int64_t threads = round_up((int64_t)n_rows, 32);
+    fill_synth_kernel<<<grid_for(threads, 256), 256, 0, t->stream>>>(
+        *cfg, first_row, (int64_t)n_rows, t->due_code, t->completed, t->overdue, t->creator_hash, t->task_id,
+        t->created_raw, t->due_raw, t->creator_ref, d_hash);
+    TT_CUDA(cudaGetLastError());
+  }
+  TT_CUDA(cudaStreamSynchronize(t->stream));
+  cudaFree(d_hash);
+  t->ids_sorted = true;  // tt_synth_make: TaskId grows with the row
+  return TT_OK;
+}
+
+int32_t tt_load_soa(tt_table* t, const tt_soa_view* v) {
+  if (!t || !v) return fail(TT_ERR_ARG, "null argument");
+  if (v->n < 0) return fail(TT_ERR_ARG, "negative row count");
+  if (v->n > 0 && (!v->task_id || !v->created_raw || !v->due_raw || !v->completed || !v->overdue || !v->creator_ref))
+    return fail(TT_ERR_ARG, "null column");
+  if (v->n > 0 && (v->n_creators == 0 || !v->creator_off || (!v->creator_pool && v->creator_off[v->n_creators] != 0)))
+    return fail(TT_ERR_ARG, "creator dictionary missing");
+  for (int64_t i = 0; i < v->n; ++i)
+    if (v->creator_ref[i] >= v->n_creators) return fail(TT_ERR_ARG, "creator_ref[%lld] out of range", (long long)i);
+  std::lock_guard<std::mutex> lk(t->mu);
+  DeviceGuard g(t->device);
+  const int64_t n = v->n;
+  int32_t rc = alloc_columns(t, n);
+  if (rc) return rc;
+  // encode the hot columns on the host (ingest path)
+  std::vector<uint32_t> code(n), cw((n + 31) / 32, 0), ow((n + 31) / 32, 0);
+  for (int64_t i = 0; i < n; ++i) {
+    code[i] = tt_pack_due(v->due_raw[i]);
+    if (v->completed[i]) cw[i >> 5] |= 1u << (i & 31);
+    if (v->overdue[i]) ow[i >> 5] |= 1u << (i & 31);
+  }
+  const uint32_t nc = v->n_creators;
+  std::vector<uint64_t> hash(std::max<uint32_t>(nc, 1));
+  for (uint32_t k = 0; k < nc; ++k) {
+    if (v->creator_off[k + 1] < v->creator_off[k]) return fail(TT_ERR_ARG, "creator_off not ascending");
+    hash[k] = tt_hash64(v->creator_pool + v->creator_off[k], v->creator_off[k + 1] - v->creator_off[k]);
+  }
+  static const uint32_t zero_off[1] = {0};
+  rc = upload_dictionary(t, nc, nc ? v->creator_off : zero_off, v->creator_pool);
+  if (rc) return rc;
+  // is the table already in TaskId order?  (then mark-by-id can search it directly)
+  bool sorted = true;
+  for (int64_t i = 1; i < n && sorted; ++i) sorted = memcmp(v->task_id + 16 * (i - 1), v->task_id + 16 * i, 16) < 0;
+  t->ids_sorted = sorted;
+  if (!sorted && n) {
+    std::vector<uint32_t> order(n);
+    for (int64_t i = 0; i < n; ++i) order[i] = (uint32_t)i;
+    const uint8_t* ids = v->task_id;
+    std::stable_sort(order.begin(), order.end(),
+                     [ids](uint32_t a, uint32_t b) { return memcmp(ids + 16 * (size_t)a, ids + 16 * (size_t)b, 16) < 0; });
+    TT_CUDA(cudaMalloc(&t->id_order, n * 4));
+    TT_CUDA(cudaMemcpyAsync(t->id_order, order.data(), n * 4, cudaMemcpyHostToDevice, t->stream));
+    TT_CUDA(cudaStreamSynchronize(t->stream));
+  }
+  if (n) {
+    uint64_t* d_hash = nullptr;
+    TT_CUDA(cudaMalloc(&d_hash, hash.size() * 8));
+    TT_CUDA(cudaMemcpyAsync(d_hash, hash.data(), hash.size() * 8, cudaMemcpyHostToDevice, t->stream));
+    TT_CUDA(cudaMemcpyAsync(t->due_code, code.data(), n * 4, cudaMemcpyHostToDevice, t->stream));
+    TT_CUDA(cudaMemcpyAsync(t->completed, cw.data(), cw.size() * 4, cudaMemcpyHostToDevice, t->stream));
+    TT_CUDA(cudaMemcpyAsync(t->overdue, ow.data(), ow.size() * 4, cudaMemcpyHostToDevice, t->stream));
+    TT_CUDA(cudaMemcpyAsync(t->task_id, v->task_id, n * 16, cudaMemcpyHostToDevice, t->stream));
+    TT_CUDA(cudaMemcpyAsync(t->created_raw, v->created_raw, n * 8, cudaMemcpyHostToDevice, t->stream));
+    TT_CUDA(cudaMemcpyAsync(t->due_raw, v->due_raw, n * 8, cudaMemcpyHostToDevice, t->stream));
+    TT_CUDA(cudaMemcpyAsync(t->creator_ref, v->creator_ref, n * 4, cudaMemcpyHostToDevice, t->stream));
+    hash_rows_kernel<<<grid_for(n, 256), 256, 0, t->stream>>>(t->creator_ref, d_hash, t->creator_hash, n);
+    TT_CUDA(cudaGetLastError());
+    TT_CUDA(cudaStreamSynchronize(t->stream));
+    cudaFree(d_hash);
+  }
+  TT_CUDA(cudaStreamSynchronize(t->stream));
+  return TT_OK;
+}
+
+// ---- ITasksManager operations ---------------------------------------------------------------
+
+int32_t tt_get_yesterdays_due(tt_table* t, int32_t mode, int64_t today_local_ticks, tt_result** out) {
+  if (!t || !out) return fail(TT_ERR_ARG, "null argument");
+  *out = nullptr;
+  std::lock_guard<std::mutex> lk(t->mu);
+  DeviceGuard g(t->device);
+  tt_sweep_stats st;
+  tt_result* r = nullptr;
+  int32_t rc = sweep_owned(t, mode, TT_SWEEP_LIST_ONLY, today_local_ticks, 0, &r, &st);
+  if (rc) return rc;
+  if (mode == TT_MODE_STORE && r->n > 1) {
+    // TasksStoreManager.cs:136 — OrderBy(TaskCreatedOn), stable; ties keep row order
+    rc = tt::order_by_created(t->stream, t->created_raw, t->task_id, r->d_rows, r->d_ids, r->n, /*descending=*/false);
+    if (rc != 0) {
+      result_release(r);
+      return fail(TT_ERR_CUDA, "order_by_created failed: %s", cudaGetErrorString((cudaError_t)rc));
+    }
+  }
+  *out = r;
+  return TT_OK;
+}
+
+int32_t tt_sweep(tt_table* t, int32_t mode, int64_t today_local_ticks, int64_t run_at_utc_ticks, tt_result** out,
+                 int64_t* n_marked) {
+  if (!t || !out) return fail(TT_ERR_ARG, "null argument");
+  *out = nullptr;
+  if (n_marked) *n_marked = 0;
+  std::lock_guard<std::mutex> lk(t->mu);
+  DeviceGuard g(t->device);
+  tt_sweep_stats st;
+  tt_result* r = nullptr;
+  int32_t rc = sweep_owned(t, mode, TT_SWEEP_MARK, today_local_ticks, run_at_utc_ticks, &r, &st);
+  if (rc) return rc;
+  *out = r;
+  if (n_marked) *n_marked = st.n_marked;
+  if (mode == TT_MODE_FAKE && r->n > 0 && run_at_utc_ticks / TT_TICKS_PER_DAY > today_local_ticks / TT_TICKS_PER_DAY - 1)
+    return fail(TT_ERR_NOT_IMPLEMENTED,
+                "FAKE mode: MarkOverdueTasks throws NotImplementedException (FakeTasksManager.cs:104); %lld tasks listed",
+                (long long)r->n);
+  return TT_OK;
+}
+
+int32_t tt_sweep_device(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_ticks,
+                        int64_t run_at_utc_ticks, int64_t first_row, uint32_t* d_rows, void* d_ids, int64_t cap,
+                        tt_sweep_stats* h_stats, void* stream) {
+  if (!t || !h_stats) return fail(TT_ERR_ARG, "null argument");
+  std::lock_guard<std::mutex> lk(t->mu);
+  DeviceGuard g(t->device);
+  return sweep_run(t, mode, flags, today_local_ticks, run_at_utc_ticks, first_row, d_rows, (uint4*)d_ids, cap, h_stats,
+                   stream ? (cudaStream_t)stream : t->stream);
+}
+
+int32_t tt_mark_overdue(tt_table* t, int32_t mode, const uint8_t* ids16, int64_t n, int64_t* n_marked,
+                        int64_t* n_missing) {
+  if (!t || n < 0 || (n > 0 && !ids16)) return fail(TT_ERR_ARG, "bad argument");
+  if (n_marked) *n_marked = 0;
+  if (n_missing) *n_missing = 0;
+  if (mode == TT_MODE_FAKE)
+    return fail(TT_ERR_NOT_IMPLEMENTED, "FAKE mode: MarkOverdueTasks throws NotImplementedException (FakeTasksManager.cs:104)");
+  if (mode != TT_MODE_STORE) return fail(TT_ERR_ARG, "mode must be TT_MODE_FAKE or TT_MODE_STORE");
+  if (n == 0) return TT_OK;
+  std::lock_guard<std::mutex> lk(t->mu);
+  DeviceGuard g(t->device);
+  uint4* d_ids = nullptr;
+  TT_CUDA(cudaMalloc(&d_ids, n * 16));
+  cudaError_t e = cudaMemcpyAsync(d_ids, ids16, n * 16, cudaMemcpyHostToDevice, t->stream);
+  if (e == cudaSuccess) e = cudaMemsetAsync(t->d_small, 0, 16, t->stream);
+  if (e == cudaSuccess) {
+    tt::mark_by_id_kernel<<<grid_for(n, 128), 128, 0, t->stream>>>(d_ids, n, t->task_id, t->id_order, t->n, t->overdue,
+                                                                   t->d_small);
+    e = cudaGetLastError();
+  }
+  if (e == cudaSuccess) e = cudaMemcpyAsync(t->h_small, t->d_small, 16, cudaMemcpyDeviceToHost, t->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(t->stream);
+  cudaFree(d_ids);
+  TT_CUDA(e);
+  if (n_marked) *n_marked = (int64_t)t->h_small[0];
+  if (n_missing) *n_missing = (int64_t)t->h_small[1];
+  return TT_OK;
+}
+
+int32_t tt_get_by_creator(tt_table* t, const char* utf8, int32_t len, tt_result** out) {
+  if (!t || !out || len < 0 || (len > 0 && !utf8)) return fail(TT_ERR_ARG, "bad argument");
+  *out = nullptr;
+  std::lock_guard<std::mutex> lk(t->mu);
+  DeviceGuard g(t->device);
+  if ((size_t)len > t->d_query_cap) {
+    cudaFree(t->d_query);
+    t->d_query = nullptr;
+    t->d_query_cap = 0;
+    size_t want = std::max<size_t>(4096, (size_t)len);
+    TT_CUDA(cudaMalloc(&t->d_query, want));
+    t->d_query_cap = want;
+  }
+  tt_result* r = nullptr;
+  // first guess: a creator rarely owns more than this many rows; grows on overflow
+  int64_t cap = std::min<int64_t>(std::max<int64_t>(t->n, 1), 4096);
+  for (int pass = 0; pass < 2; ++pass) {
+    int32_t rc = result_alloc(t, cap, &r);
+    if (rc) return rc;
+    int64_t found = 0;
+    cudaError_t e = tt::creator_filter(t->stream, t->sm_count, t->creator_hash, t->creator_ref, t->creator_off,
+                                       t->creator_pool, t->n, t->n_pad, (const uint8_t*)utf8, (uint32_t)len, t->d_query, r->d_rows,
+                                       cap, t->d_small, t->h_small, &found);
+    if (e != cudaSuccess) {
+      result_release(r);
+      cudaGetLastError();
+      return fail(TT_ERR_CUDA, "creator_filter: %s", cudaGetErrorString(e));
+    }
+    if (found <= cap) {
+      r->n = found;
+      break;
+    }
+    result_release(r);
+    r = nullptr;
+    cap = found;
+  }
+  if (!r) return fail(TT_ERR_STATE, "creator filter did not converge");
+  if (r->n > 0) {
+    // FakeTasksManager.cs:70 / TasksStoreManager.cs:66 — OrderByDescending(TaskCreatedOn), stable.
+    // The filter emits candidates unordered; sorting the rows first restores source order for ties.
+    int rc = tt::order_by_created(t->stream, t->created_raw, t->task_id, r->d_rows, r->d_ids, r->n, /*descending=*/true,
+                                  /*rows_unordered=*/true);
+    if (rc != 0) {
+      result_release(r);
+      return fail(TT_ERR_CUDA, "order_by_created failed: %s", cudaGetErrorString((cudaError_t)rc));
+    }
+  }
+  *out = r;
+  return TT_OK;
+}
+
+// ---- results --------------------------------------------------------------------------------
+
+int32_t tt_result_count(const tt_result* r, int64_t* n) {
+  if (!r || !n) return fail(TT_ERR_ARG, "null argument");
+  *n = r->n;
+  return TT_OK;
+}
+
+int32_t tt_result_rows(tt_result* r, uint32_t* out) {
+  if (!r || (r->n && !out)) return fail(TT_ERR_ARG, "null argument");
+  DeviceGuard g(r->t->device);
+  if (r->n) TT_CUDA(cudaMemcpy(out, r->d_rows, r->n * 4, cudaMemcpyDeviceToHost));
+  return TT_OK;
+}
+
+int32_t tt_result_ids(tt_result* r, uint8_t* out16) {
+  if (!r || (r->n && !out16)) return fail(TT_ERR_ARG, "null argument");
+  DeviceGuard g(r->t->device);
+  if (r->n) TT_CUDA(cudaMemcpy(out16, r->d_ids, r->n * 16, cudaMemcpyDeviceToHost));
+  return TT_OK;
+}
+
+int32_t tt_result_field(tt_result* r, int32_t field, void* out) {
+  if (!r || (r->n && !out)) return fail(TT_ERR_ARG, "null argument");
+  if (r->n == 0) return TT_OK;
+  tt_table* t = r->t;
+  std::lock_guard<std::mutex> lk(t->mu);
+  DeviceGuard g(t->device);
+  size_t width = (field == TT_FIELD_CREATED_RAW || field == TT_FIELD_DUE_RAW) ? 8 : (field == TT_FIELD_CREATOR_REF ? 4 : 1);
+  void* d_out = nullptr;
+  TT_CUDA(cudaMalloc(&d_out, r->n * width));
+  const unsigned grid = grid_for(r->n, 256);
+  switch (field) {
+    case TT_FIELD_CREATED_RAW:
+      gather_field_kernel<uint64_t><<<grid, 256, 0, t->stream>>>(r->d_rows, t->created_raw, (uint64_t*)d_out, r->n);
+      break;
+    case TT_FIELD_DUE_RAW:
+      gather_field_kernel<uint64_t><<<grid, 256, 0, t->stream>>>(r->d_rows, t->due_raw, (uint64_t*)d_out, r->n);
+      break;
+    case TT_FIELD_CREATOR_REF:
+      gather_field_kernel<uint32_t><<<grid, 256, 0, t->stream>>>(r->d_rows, t->creator_ref, (uint32_t*)d_out, r->n);
+      break;
+    case TT_FIELD_COMPLETED:
+      gather_bit_kernel<<<grid, 256, 0, t->stream>>>(r->d_rows, t->completed, (uint8_t*)d_out, r->n);
+      break;
+    case TT_FIELD_OVERDUE:
+      gather_bit_kernel<<<grid, 256, 0, t->stream>>>(r->d_rows, t->overdue, (uint8_t*)d_out, r->n);
+      break;
+    default:
+      cudaFree(d_out);
+      return fail(TT_ERR_ARG, "unknown field %d", field);
+  }
+  cudaError_t e = cudaGetLastError();
+  if (e == cudaSuccess) e = cudaMemcpyAsync(out, d_out, r->n * width, cudaMemcpyDeviceToHost, t->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(t->stream);
+  cudaFree(d_out);
+  TT_CUDA(e);
+  return TT_OK;
+}
+
+int32_t tt_result_free(tt_result* r) {
+  if (!r) return TT_OK;
+  DeviceGuard g(r->t->device);
+  result_release(r);
+  return TT_OK;
+}
+
+int32_t tt_result_digest(tt_result* r, uint64_t* xor_id_hi, uint64_t* xor_id_lo, uint64_t* sum_rows) {
+  if (!r) return fail(TT_ERR_ARG, "null argument");
+  tt_table* t = r->t;
+  std::lock_guard<std::mutex> lk(t->mu);
+  DeviceGuard g(t->device);
+  TT_CUDA(cudaMemsetAsync(t->d_small, 0, 24, t->stream));
+  if (r->n) {
+    digest_kernel<<<(unsigned)std::min<int64_t>(grid_for(r->n, 256), 4 * t->sm_count), 256, 0, t->stream>>>(
+        r->d_rows, r->d_ids, r->n, t->d_small);
+    TT_CUDA(cudaGetLastError());
+  }
+  TT_CUDA(cudaMemcpyAsync(t->h_small, t->d_small, 24, cudaMemcpyDeviceToHost, t->stream));
+  TT_CUDA(cudaStreamSynchronize(t->stream));
+  if (xor_id_hi) *xor_id_hi = t->h_small[0];
+  if (xor_id_lo) *xor_id_lo = t->h_small[1];
+  if (sum_rows) *sum_rows = t->h_small[2];
+  return TT_OK;
+}
+
+// ---- state access -----------------------------------------------------------------------------
+
+int32_t tt_snapshot_flags(tt_table* t, uint8_t* completed_bits, uint8_t* overdue_bits) {
+  if (!t) return fail(TT_ERR_ARG, "null argument");
+  std::lock_guard<std::mutex> lk(t->mu);
+  DeviceGuard g(t->device);
+  size_t bytes = (size_t)(t->n + 7) / 8;
+  if (bytes == 0) return TT_OK;
+  if (completed_bits) TT_CUDA(cudaMemcpyAsync(completed_bits, t->completed, bytes, cudaMemcpyDefault, t->stream));
+  if (overdue_bits) TT_CUDA(cudaMemcpyAsync(overdue_bits, t->overdue, bytes, cudaMemcpyDefault, t->stream));
+  TT_CUDA(cudaStreamSynchronize(t->stream));
+  return TT_OK;
+}
+
+int32_t tt_restore_flags(tt_table* t, const uint8_t* completed_bits, const uint8_t* overdue_bits) {
+  if (!t) return fail(TT_ERR_ARG, "null argument");
+  std::lock_guard<std::mutex> lk(t->mu);
+  DeviceGuard g(t->device);
+  size_t bytes = (size_t)(t->n + 7) / 8;
+  if (bytes == 0) return TT_OK;
+  if (completed_bits) TT_CUDA(cudaMemcpyAsync(t->completed, completed_bits, bytes, cudaMemcpyDefault, t->stream));
+  if (overdue_bits) TT_CUDA(cudaMemcpyAsync(t->overdue, overdue_bits, bytes, cudaMemcpyDefault, t->stream));
+  TT_CUDA(cudaStreamSynchronize(t->stream));
+  return TT_OK;
+}
+
+int32_t tt_count_flags(tt_table* t, int64_t* n_completed, int64_t* n_overdue) {
+  if (!t) return fail(TT_ERR_ARG, "null argument");
+  std::lock_guard<std::mutex> lk(t->mu);
+  DeviceGuard g(t->device);
+  TT_CUDA(cudaMemsetAsync(t->d_small, 0, 16, t->stream));
+  int64_t words = t->n_pad / 32;
+  if (words) {
+    count_flags_kernel<<<(unsigned)std::min<int64_t>(grid_for(words, 256), 4 * t->sm_count), 256, 0, t->stream>>>(
+        t->completed, t->overdue, words, t->d_small);
+    TT_CUDA(cudaGetLastError());
+  }
+  TT_CUDA(cudaMemcpyAsync(t->h_small, t->d_small, 16, cudaMemcpyDeviceToHost, t->stream));
+  TT_CUDA(cudaStreamSynchronize(t->stream));
+  if (n_completed) *n_completed = (int64_t)t->h_small[0];
+  if (n_overdue) *n_overdue = (int64_t)t->h_small[1];
+  return TT_OK;
+}
+
+int32_t tt_get_device_view(tt_table* t, tt_device_view* out) {
+  if (!t || !out) return fail(TT_ERR_ARG, "null argument");
+  out->n = t->n;
+  out->n_padded = t->n_pad;
+  out->due_code = t->due_code;
+  out->completed = t->completed;
+  out->overdue = t->overdue;
+  out->creator_hash = t->creator_hash;
+  out->task_id = t->task_id;
+  out->created_raw = t->created_raw;
+  out->device = t->device;
+  return TT_OK;
+}
+
+}  // extern "C"

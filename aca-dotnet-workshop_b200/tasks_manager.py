@@ -1,0 +1,128 @@
+"""GpuTasksManager — the reference's ITasksManager, served from the HBM-resident task table.
+
+Host-side mirror of Api/Services/ITasksManager.cs:5-15 for the three methods on the hot path
+(GetYesterdaysDueTasks :14, MarkOverdueTasks :13, GetTasksByCreator :7) plus the cron
+handler that drives them (Svc/Controllers/ScheduledTasksManagerController.cs:19-46).  Method
+names, argument meaning and error behaviour follow the reference: FAKE mode's
+MarkOverdueTasks raises (NotImplementedException, Api/Services/FakeTasksManager.cs:102-105);
+STORE mode follows Api/Services/TasksStoreManager.cs.  The C# wrapper in INTEGRATION.md has
+the same shape over the same C ABI.
+
+Only columns a kernel reads live on the device; TaskName / TaskAssignedTo stay here, keyed
+by row, and are re-attached when TaskModel objects are rebuilt from a result.
+"""
+import uuid
+from dataclasses import dataclass
+from typing import List, Optional
+
+import numpy as np
+
+from . import tasktable as tt
+
+KIND_UNSPECIFIED, KIND_UTC, KIND_LOCAL = 0, 1, 2
+_TICKS_MASK = (1 << 62) - 1
+
+
+@dataclass
+class TaskModel:
+    """Api/Models/TaskModel.cs:3-13.  DateTime fields are .NET dateData (ticks | kind << 62)."""
+
+    TaskId: uuid.UUID
+    TaskName: str = ""
+    TaskCreatedBy: str = ""
+    TaskCreatedOn: int = 0
+    TaskDueDate: int = 0
+    TaskAssignedTo: str = ""
+    IsCompleted: bool = False
+    IsOverDue: bool = False
+
+
+def date_data(ticks, kind=KIND_UNSPECIFIED):
+    return (ticks & _TICKS_MASK) | (kind << 62)
+
+
+class GpuTasksManager:
+    """Drop-in for FakeTasksManager / TasksStoreManager on the sweep and creator-filter path.
+
+    mode = tt.MODE_FAKE or tt.MODE_STORE selects which reference implementation's semantics
+    are reproduced (they differ: SURVEY.md §0).  The clock is injected: `today_local_ticks`
+    stands for DateTime.Today, `run_at_utc_ticks` for DateTime.UtcNow in the cron handler.
+    """
+
+    def __init__(self, tasks: List[TaskModel], mode=tt.MODE_STORE, device=0):
+        self.mode = mode
+        self._names = [t.TaskName for t in tasks]
+        self._assignees = [t.TaskAssignedTo for t in tasks]
+        creators = {}
+        refs = np.empty(len(tasks), dtype=np.uint32)
+        for i, t in enumerate(tasks):
+            b = t.TaskCreatedBy.encode("utf-8")
+            refs[i] = creators.setdefault(b, len(creators))
+        self._creators = list(creators.keys())
+        ids = np.frombuffer(b"".join(t.TaskId.bytes for t in tasks), dtype=np.uint8).reshape(-1, 16)
+        self._table = tt.TaskTable(device).load_soa(
+            ids,
+            np.array([t.TaskCreatedOn for t in tasks], dtype=np.uint64),
+            np.array([t.TaskDueDate for t in tasks], dtype=np.uint64),
+            np.array([t.IsCompleted for t in tasks], dtype=np.uint8),
+            np.array([t.IsOverDue for t in tasks], dtype=np.uint8),
+            refs,
+            self._creators or [b""],
+        )
+
+    @property
+    def table(self):
+        return self._table
+
+    def _materialise(self, result) -> List[TaskModel]:
+        rows = result.rows()
+        ids = result.ids()
+        created = result.field(tt.FIELD_CREATED_RAW)
+        due = result.field(tt.FIELD_DUE_RAW)
+        comp = result.field(tt.FIELD_COMPLETED)
+        over = result.field(tt.FIELD_OVERDUE)
+        ref = result.field(tt.FIELD_CREATOR_REF)
+        out = []
+        for k, r in enumerate(rows.tolist()):
+            out.append(TaskModel(uuid.UUID(bytes=ids[k].tobytes()), self._names[r], self._creators[ref[k]].decode("utf-8"),
+                                 int(created[k]), int(due[k]), self._assignees[r], bool(comp[k]), bool(over[k])))
+        result.free()
+        return out
+
+    # ITasksManager.cs:14
+    def GetYesterdaysDueTasks(self, today_local_ticks=tt.DEFAULT_TODAY) -> List[TaskModel]:
+        return self._materialise(self._table.get_yesterdays_due(self.mode, today_local_ticks))
+
+    # ITasksManager.cs:13
+    def MarkOverdueTasks(self, overDueTasksList: List[TaskModel]) -> None:
+        ids = np.frombuffer(b"".join(t.TaskId.bytes for t in overDueTasksList), dtype=np.uint8).reshape(-1, 16)
+        if self.mode == tt.MODE_FAKE:
+            self._table.mark_overdue(self.mode, ids)  # raises NotImplementedInReference
+        if len(overDueTasksList):
+            self._table.mark_overdue(self.mode, ids)
+        for t in overDueTasksList:  # TasksStoreManager.cs:146 mutates the caller's objects too
+            t.IsOverDue = True
+
+    # ITasksManager.cs:7
+    def GetTasksByCreator(self, createdBy: str) -> List[TaskModel]:
+        return self._materialise(self._table.get_by_creator(createdBy))
+
+    # Svc/Controllers/ScheduledTasksManagerController.cs:19-46, unfused: three calls like the reference
+    def CheckOverDueTasksJob(self, run_at_utc_ticks=tt.DEFAULT_RUN_AT, today_local_ticks=tt.DEFAULT_TODAY) -> int:
+        tasksList = self.GetYesterdaysDueTasks(today_local_ticks)
+        run_date = (run_at_utc_ticks & _TICKS_MASK) // tt.TICKS_PER_DAY
+        overdueTasksList = [t for t in tasksList if run_date > (t.TaskDueDate & _TICKS_MASK) // tt.TICKS_PER_DAY]
+        if len(overdueTasksList) > 0:
+            self.MarkOverdueTasks(overdueTasksList)
+        return len(overdueTasksList)
+
+    # the same tick as one device pass (tt_sweep)
+    def SweepOverdueTasks(self, run_at_utc_ticks=tt.DEFAULT_RUN_AT, today_local_ticks=tt.DEFAULT_TODAY):
+        result, n_marked, threw = self._table.sweep(self.mode, today_local_ticks, run_at_utc_ticks)
+        tasks = self._materialise(result)
+        if threw:
+            raise tt.NotImplementedInReference(tt.TT_ERR_NOT_IMPLEMENTED, "MarkOverdueTasks (FAKE mode)")
+        return tasks, n_marked
+
+    def close(self):
+        self._table.close()

@@ -1,0 +1,338 @@
+"""ctypes binding of libtasktable.so — one function per entry point of include/tasktable.h.
+
+This is the same binding surface a C# ``[DllImport]`` wrapper uses: plain
+pointers and sizes.  The library is loaded from this directory (built in-tree by
+``make`` / ``__graft_entry__.build()``); a missing library is an ImportError-like
+``TaskTableError`` at first use, never a silent fallback.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+MODE_FAKE = 0
+MODE_STORE = 1
+SWEEP_LIST_ONLY = 0
+SWEEP_MARK = 1
+
+TT_OK = 0
+TT_ERR_ARG = -1
+TT_ERR_CUDA = -2
+TT_ERR_OOM = -3
+TT_ERR_NOT_IMPLEMENTED = -4
+TT_ERR_CAPACITY = -5
+TT_ERR_STATE = -6
+
+FIELD_CREATED_RAW = 1
+FIELD_DUE_RAW = 2
+FIELD_COMPLETED = 3
+FIELD_OVERDUE = 4
+FIELD_CREATOR_REF = 5
+
+TICKS_PER_DAY = 864000000000
+DEFAULT_TODAY = 639295200000000000  # 2026-11-06T00:00:00
+DEFAULT_RUN_AT = DEFAULT_TODAY + 5 * 60 * 10_000_000
+TILE_ROWS = 8192
+
+# every symbol include/tasktable.h declares (tests check the library exports all of them)
+EXPORTS = [
+    "tt_create", "tt_destroy", "tt_last_error", "tt_generate", "tt_load_soa", "tt_row_count",
+    "tt_get_yesterdays_due", "tt_mark_overdue", "tt_sweep", "tt_get_by_creator",
+    "tt_result_count", "tt_result_rows", "tt_result_ids", "tt_result_field", "tt_result_free",
+    "tt_snapshot_flags", "tt_restore_flags", "tt_count_flags", "tt_result_digest",
+    "tt_sweep_device", "tt_get_device_view",
+]
+
+
+class TaskTableError(RuntimeError):
+    def __init__(self, code, text):
+        super().__init__(f"tasktable error {code}: {text}")
+        self.code = code
+
+
+class NotImplementedInReference(TaskTableError):
+    """FAKE mode: FakeTasksManager.MarkOverdueTasks throws NotImplementedException
+    (Api/Services/FakeTasksManager.cs:102-105)."""
+
+
+class SynthCfg(C.Structure):
+    """tt_synth_cfg (include/tt_synth.h)."""
+
+    _fields_ = [
+        ("seed", C.c_uint64),
+        ("n_total", C.c_uint64),
+        ("today_local_ticks", C.c_int64),
+        ("ppm_due_yesterday", C.c_uint32),
+        ("ppm_adversarial", C.c_uint32),
+        ("ppm_completed", C.c_uint32),
+        ("ppm_overdue_past", C.c_uint32),
+        ("ppm_created_dup", C.c_uint32),
+        ("ppm_timed_due", C.c_uint32),
+        ("n_creators", C.c_uint32),
+        ("reserved", C.c_uint32),
+    ]
+
+
+def default_cfg(seed, n_total, **kw):
+    """BASELINE.json config-5 mix: 5 % due yesterday, 1 % adversarial, 50 % completed."""
+    cfg = SynthCfg(seed, n_total, DEFAULT_TODAY, 50000, 10000, 500000, 100000, 1000, 100000, 1000000, 0)
+    for k, v in kw.items():
+        setattr(cfg, k, v)
+    return cfg
+
+
+class SoaView(C.Structure):
+    _fields_ = [
+        ("n", C.c_int64),
+        ("task_id", C.c_void_p),
+        ("created_raw", C.c_void_p),
+        ("due_raw", C.c_void_p),
+        ("completed", C.c_void_p),
+        ("overdue", C.c_void_p),
+        ("creator_ref", C.c_void_p),
+        ("n_creators", C.c_uint32),
+        ("creator_off", C.c_void_p),
+        ("creator_pool", C.c_void_p),
+    ]
+
+
+class SweepStats(C.Structure):
+    _fields_ = [
+        ("n_listed", C.c_int64),
+        ("n_stored", C.c_int64),
+        ("n_marked", C.c_int64),
+        ("resume_row", C.c_int64),
+        ("kernel_ms", C.c_float),
+        ("launches", C.c_int32),
+    ]
+
+
+class DeviceView(C.Structure):
+    _fields_ = [
+        ("n", C.c_int64),
+        ("n_padded", C.c_int64),
+        ("due_code", C.c_void_p),
+        ("completed", C.c_void_p),
+        ("overdue", C.c_void_p),
+        ("creator_hash", C.c_void_p),
+        ("task_id", C.c_void_p),
+        ("created_raw", C.c_void_p),
+        ("device", C.c_int32),
+    ]
+
+
+def lib_path():
+    return os.path.join(HERE, "libtasktable.so")
+
+
+_lib = None
+
+
+def lib():
+    """Loads libtasktable.so (RTLD_LOCAL).  Raises if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = lib_path()
+    if not os.path.exists(path):
+        raise TaskTableError(TT_ERR_STATE, f"{path} is missing: run `make` (or __graft_entry__.build()); "
+                                           "there is no CPU fallback")
+    L = C.CDLL(path)
+    vp, i32, i64, u64 = C.c_void_p, C.c_int32, C.c_int64, C.c_uint64
+    P = C.POINTER
+    L.tt_last_error.restype = C.c_char_p
+    L.tt_last_error.argtypes = []
+    L.tt_create.argtypes = [i32, P(vp)]
+    L.tt_destroy.argtypes = [vp]
+    L.tt_generate.argtypes = [vp, P(SynthCfg), u64, u64]
+    L.tt_load_soa.argtypes = [vp, P(SoaView)]
+    L.tt_row_count.argtypes = [vp, P(i64)]
+    L.tt_get_yesterdays_due.argtypes = [vp, i32, i64, P(vp)]
+    L.tt_mark_overdue.argtypes = [vp, i32, vp, i64, P(i64), P(i64)]
+    L.tt_sweep.argtypes = [vp, i32, i64, i64, P(vp), P(i64)]
+    L.tt_get_by_creator.argtypes = [vp, C.c_char_p, i32, P(vp)]
+    L.tt_result_count.argtypes = [vp, P(i64)]
+    L.tt_result_rows.argtypes = [vp, vp]
+    L.tt_result_ids.argtypes = [vp, vp]
+    L.tt_result_field.argtypes = [vp, i32, vp]
+    L.tt_result_free.argtypes = [vp]
+    L.tt_snapshot_flags.argtypes = [vp, vp, vp]
+    L.tt_restore_flags.argtypes = [vp, vp, vp]
+    L.tt_count_flags.argtypes = [vp, P(i64), P(i64)]
+    L.tt_result_digest.argtypes = [vp, P(u64), P(u64), P(u64)]
+    L.tt_sweep_device.argtypes = [vp, i32, i32, i64, i64, i64, vp, vp, i64, P(SweepStats), vp]
+    L.tt_get_device_view.argtypes = [vp, P(DeviceView)]
+    for name in EXPORTS:
+        if name != "tt_last_error":
+            getattr(L, name).restype = i32
+    _lib = L
+    return L
+
+
+def _check(rc, allow=()):
+    if rc == TT_OK or rc in allow:
+        return rc
+    text = lib().tt_last_error().decode(errors="replace")
+    if rc == TT_ERR_NOT_IMPLEMENTED:
+        raise NotImplementedInReference(rc, text)
+    raise TaskTableError(rc, text)
+
+
+def _ptr(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+class Result:
+    """tt_result: the hit list of one query, resident on the device until fetched."""
+
+    def __init__(self, handle):
+        self._h = handle
+        n = C.c_int64(0)
+        _check(lib().tt_result_count(self._h, C.byref(n)))
+        self.count = n.value
+
+    def rows(self):
+        out = np.empty(self.count, dtype=np.uint32)
+        _check(lib().tt_result_rows(self._h, _ptr(out)))
+        return out
+
+    def ids(self):
+        out = np.empty((self.count, 16), dtype=np.uint8)
+        _check(lib().tt_result_ids(self._h, _ptr(out)))
+        return out
+
+    def field(self, field):
+        dt = {FIELD_CREATED_RAW: np.uint64, FIELD_DUE_RAW: np.uint64, FIELD_COMPLETED: np.uint8,
+              FIELD_OVERDUE: np.uint8, FIELD_CREATOR_REF: np.uint32}[field]
+        out = np.empty(self.count, dtype=dt)
+        _check(lib().tt_result_field(self._h, field, _ptr(out)))
+        return out
+
+    def digest(self):
+        hi, lo, s = C.c_uint64(0), C.c_uint64(0), C.c_uint64(0)
+        _check(lib().tt_result_digest(self._h, C.byref(hi), C.byref(lo), C.byref(s)))
+        return hi.value, lo.value, s.value
+
+    def free(self):
+        if self._h:
+            lib().tt_result_free(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+class TaskTable:
+    """tt_table: one shard of the task table, resident in the HBM of one GPU."""
+
+    def __init__(self, device=0):
+        h = C.c_void_p()
+        _check(lib().tt_create(device, C.byref(h)))
+        self._h = h
+        self.device = device
+
+    # -- filling ---------------------------------------------------------------------------
+    def generate(self, cfg, first_row, n_rows):
+        _check(lib().tt_generate(self._h, C.byref(cfg), first_row, n_rows))
+        return self
+
+    def load_soa(self, task_id, created_raw, due_raw, completed, overdue, creator_ref, creators):
+        """creators: list of bytes (the distinct TaskCreatedBy strings, UTF-8)."""
+        n = len(created_raw)
+        ids = np.ascontiguousarray(task_id, dtype=np.uint8).reshape(n, 16) if n else np.zeros((0, 16), np.uint8)
+        cr = np.ascontiguousarray(created_raw, dtype=np.uint64)
+        du = np.ascontiguousarray(due_raw, dtype=np.uint64)
+        co = np.ascontiguousarray(completed, dtype=np.uint8)
+        ov = np.ascontiguousarray(overdue, dtype=np.uint8)
+        ref = np.ascontiguousarray(creator_ref, dtype=np.uint32)
+        off = np.zeros(len(creators) + 1, dtype=np.uint32)
+        off[1:] = np.cumsum([len(c) for c in creators], dtype=np.uint64) if creators else 0
+        pool = np.frombuffer(b"".join(creators) or b"\0", dtype=np.uint8).copy()
+        v = SoaView(n, _ptr(ids), _ptr(cr), _ptr(du), _ptr(co), _ptr(ov), _ptr(ref), len(creators), _ptr(off),
+                    _ptr(pool))
+        _check(lib().tt_load_soa(self._h, C.byref(v)))
+        return self
+
+    def __len__(self):
+        n = C.c_int64(0)
+        _check(lib().tt_row_count(self._h, C.byref(n)))
+        return n.value
+
+    # -- ITasksManager operations ----------------------------------------------------------
+    def get_yesterdays_due(self, mode, today=DEFAULT_TODAY):
+        r = C.c_void_p()
+        _check(lib().tt_get_yesterdays_due(self._h, mode, today, C.byref(r)))
+        return Result(r)
+
+    def mark_overdue(self, mode, ids16):
+        ids = np.ascontiguousarray(ids16, dtype=np.uint8).reshape(-1, 16)
+        marked, missing = C.c_int64(0), C.c_int64(0)
+        _check(lib().tt_mark_overdue(self._h, mode, _ptr(ids), ids.shape[0], C.byref(marked), C.byref(missing)))
+        return marked.value, missing.value
+
+    def sweep(self, mode, today=DEFAULT_TODAY, run_at=DEFAULT_RUN_AT):
+        """-> (result, n_marked, threw) ; threw mirrors FAKE mode's NotImplementedException."""
+        r = C.c_void_p()
+        marked = C.c_int64(0)
+        rc = _check(lib().tt_sweep(self._h, mode, today, run_at, C.byref(r), C.byref(marked)),
+                    allow=(TT_ERR_NOT_IMPLEMENTED,))
+        return Result(r), marked.value, rc == TT_ERR_NOT_IMPLEMENTED
+
+    def get_by_creator(self, created_by):
+        b = created_by.encode() if isinstance(created_by, str) else bytes(created_by)
+        r = C.c_void_p()
+        _check(lib().tt_get_by_creator(self._h, b, len(b), C.byref(r)))
+        return Result(r)
+
+    # -- device-resident sweep ---------------------------------------------------------------
+    def sweep_device(self, mode, flags, d_rows, d_ids, cap, today=DEFAULT_TODAY, run_at=DEFAULT_RUN_AT, first_row=0,
+                     stream=None, allow_capacity=False):
+        """d_rows / d_ids: device addresses (int).  Returns (SweepStats, rc)."""
+        st = SweepStats()
+        rc = lib().tt_sweep_device(self._h, mode, flags, today, run_at, first_row, d_rows, d_ids, cap, C.byref(st),
+                                   stream)
+        _check(rc, allow=(TT_ERR_CAPACITY,) if allow_capacity else ())
+        return st, rc
+
+    # -- state -----------------------------------------------------------------------------------
+    def snapshot_flags(self):
+        nb = (len(self) + 7) // 8
+        c = np.zeros(nb, dtype=np.uint8)
+        o = np.zeros(nb, dtype=np.uint8)
+        _check(lib().tt_snapshot_flags(self._h, _ptr(c), _ptr(o)))
+        return c, o
+
+    def flags_bytes(self):
+        """(completed, overdue) as one byte per row."""
+        n = len(self)
+        c, o = self.snapshot_flags()
+        return (np.unpackbits(c, bitorder="little")[:n], np.unpackbits(o, bitorder="little")[:n])
+
+    def restore_flags(self, completed_bits=None, overdue_bits=None):
+        _check(lib().tt_restore_flags(self._h, _ptr(completed_bits), _ptr(overdue_bits)))
+
+    def count_flags(self):
+        c, o = C.c_int64(0), C.c_int64(0)
+        _check(lib().tt_count_flags(self._h, C.byref(c), C.byref(o)))
+        return c.value, o.value
+
+    def device_view(self):
+        v = DeviceView()
+        _check(lib().tt_get_device_view(self._h, C.byref(v)))
+        return v
+
+    def close(self):
+        if self._h:
+            lib().tt_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -1,0 +1,195 @@
+/* tasktable.h — C ABI of the B200-native task table (libtasktable.so).
+ *
+ * This is the drop-in boundary for the one data-parallel path of
+ * chsakell/aca-dotnet-workshop: the cron-driven overdue-task sweep and the creator filter
+ * behind ITasksManager (Api/Services/ITasksManager.cs:5-15; "Api" =
+ * TasksTracker.TasksManager.Backend.Api, "Svc" = TasksTracker.Processor.Backend.Svc under
+ * /root/reference).  A C# ITasksManager implementation P/Invokes these entry points
+ * (INTEGRATION.md shows the [DllImport] stubs); every signature uses plain pointers and
+ * sizes only.  All functions return an int32 status (TT_OK = 0, negative = error) and never
+ * throw; tt_last_error() gives the text for the calling thread.
+ *
+ * The table lives in HBM as a structure of arrays:
+ *   hot  : due_code u32/row (day number + "time of day != 0" bit + DateTimeKind),
+ *          completed and overdue bit-planes (1 bit/row each), creator_hash u64/row
+ *   cold : task_id 16 B/row, created_raw and due_raw u64/row (.NET dateData), creator_ref
+ *          u32/row into a creator dictionary (offset table + UTF-8 pool)
+ * Rows keep the caller's order (the reference's list order); row numbers are shard-local.
+ *
+ * Thread safety: one tt_table may be shared by all request threads (the reference registers
+ * its manager as a singleton, Api/Program.cs:13); calls on the same table are serialised by
+ * an internal lock.  tt_result objects are independent of the lock once returned.
+ *
+ * There is no CPU fallback: every operation runs as CUDA kernels on the table's device and
+ * fails with TT_ERR_CUDA if no device is usable.
+ */
+#ifndef TASKTABLE_H
+#define TASKTABLE_H
+
+#include <stdint.h>
+
+#include "tt_synth.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TT_OK 0
+#define TT_ERR_ARG (-1)             /* bad argument (null, negative size, today not a midnight, ...) */
+#define TT_ERR_CUDA (-2)            /* CUDA runtime / launch failure, text in tt_last_error()        */
+#define TT_ERR_OOM (-3)             /* device or pinned-host allocation failed                       */
+#define TT_ERR_NOT_IMPLEMENTED (-4) /* FAKE-mode MarkOverdueTasks: Api/Services/FakeTasksManager.cs:102-105 throws */
+#define TT_ERR_CAPACITY (-5)        /* caller-provided output buffer too small; call is resumable    */
+#define TT_ERR_STATE (-6)           /* table empty / already loaded / result of another table        */
+
+/* Which reference implementation's semantics to follow (they differ, SURVEY.md §0 finding 1):
+ * FAKE  = Api/Services/FakeTasksManager.cs:107-112  tick equality only, source order, Mark throws
+ * STORE = Api/Services/TasksStoreManager.cs:104-149 exact "yyyy-MM-ddT00:00:00" match, pending
+ *         rows only, ordered by TaskCreatedOn, Mark sets IsOverDue                              */
+#define TT_MODE_FAKE 0
+#define TT_MODE_STORE 1
+
+typedef struct tt_table tt_table;
+typedef struct tt_result tt_result;
+
+/* Host-side structure-of-arrays view handed to tt_load_soa.  One entry per TaskModel
+ * (Api/Models/TaskModel.cs:3-13); TaskName / TaskAssignedTo are not touched by any kernel and
+ * stay with the host wrapper. */
+typedef struct tt_soa_view {
+  int64_t n;                   /* rows                                                          */
+  const uint8_t* task_id;      /* 16*n bytes, canonical big-endian order of Guid.ToString("D")  */
+  const uint64_t* created_raw; /* TaskCreatedOn as .NET dateData (ticks | kind<<62)             */
+  const uint64_t* due_raw;     /* TaskDueDate  as .NET dateData                                 */
+  const uint8_t* completed;    /* IsCompleted, one byte per row (0/1)                           */
+  const uint8_t* overdue;      /* IsOverDue,   one byte per row (0/1)                           */
+  const uint32_t* creator_ref; /* index of the row's TaskCreatedBy in the dictionary below      */
+  uint32_t n_creators;         /* dictionary entries                                            */
+  const uint32_t* creator_off; /* n_creators+1 byte offsets into creator_pool                   */
+  const uint8_t* creator_pool; /* UTF-8 bytes of the distinct TaskCreatedBy strings             */
+} tt_soa_view;
+
+/* Fields tt_result_field can gather for the rows of a result. */
+#define TT_FIELD_CREATED_RAW 1 /* uint64 per row */
+#define TT_FIELD_DUE_RAW 2     /* uint64 per row */
+#define TT_FIELD_COMPLETED 3   /* uint8  per row */
+#define TT_FIELD_OVERDUE 4     /* uint8  per row (state when the result was produced is NOT kept: current state) */
+#define TT_FIELD_CREATOR_REF 5 /* uint32 per row */
+
+/* ---- lifetime -------------------------------------------------------------------------- */
+
+/* Replaces the reference's `new FakeTasksManager()` / DI construction (Api/Program.cs:13).
+ * `device` is the CUDA ordinal that will hold this table (one table per GPU shard). */
+int32_t tt_create(int32_t device, tt_table** out);
+int32_t tt_destroy(tt_table* t);
+
+/* Text of the last error raised on the calling thread (never NULL). */
+const char* tt_last_error(void);
+
+/* Fills the table on the device with rows [first_row, first_row + n_rows) of the synthetic
+ * table described by cfg (include/tt_synth.h) — the stand-in for
+ * FakeTasksManager.GenerateRandomTasks (Api/Services/FakeTasksManager.cs:10-25) at benchmark
+ * sizes.  first_row/n_rows select this shard's TaskId range. */
+int32_t tt_generate(tt_table* t, const tt_synth_cfg* cfg, uint64_t first_row, uint64_t n_rows);
+
+/* Loads caller rows (the reference's _tasksList / state-store documents) into HBM. */
+int32_t tt_load_soa(tt_table* t, const tt_soa_view* v);
+
+int32_t tt_row_count(tt_table* t, int64_t* n);
+
+/* ---- the ITasksManager operations on the path ------------------------------------------- */
+
+/* ITasksManager.GetYesterdaysDueTasks (Api/Services/ITasksManager.cs:14);
+ * FAKE: FakeTasksManager.cs:107-112 (source order), STORE: TasksStoreManager.cs:104-139
+ * (pending rows, ascending TaskCreatedOn, ties in row order).  `today_local_ticks` is
+ * DateTime.Today (local midnight) in ticks.  Does not modify the table. */
+int32_t tt_get_yesterdays_due(tt_table* t, int32_t mode, int64_t today_local_ticks, tt_result** out);
+
+/* ITasksManager.MarkOverdueTasks (ITasksManager.cs:13; TasksStoreManager.cs:141-149): sets
+ * IsOverDue for every listed TaskId that is in the table.  ids16 = 16*n bytes in canonical
+ * order.  FAKE mode returns TT_ERR_NOT_IMPLEMENTED like the reference.  *n_missing counts ids
+ * with no row (the reference would upsert a new document for them; this table does not). */
+int32_t tt_mark_overdue(tt_table* t, int32_t mode, const uint8_t* ids16, int64_t n, int64_t* n_marked,
+                        int64_t* n_missing);
+
+/* The whole cron tick in one device pass — replaces the three-process round trip of
+ * Svc/Controllers/ScheduledTasksManagerController.cs:19-46: GetYesterdaysDueTasks, keep
+ * rows with runAt.Date > TaskDueDate.Date (:34), MarkOverdueTasks if any survive (:40-45).
+ * *out lists what GetYesterdaysDueTasks returned (row order); *n_marked = rows whose
+ * IsOverDue was set.  FAKE mode with survivors returns TT_ERR_NOT_IMPLEMENTED (the result is
+ * still produced, the table is unchanged), as the reference's cron handler would observe. */
+int32_t tt_sweep(tt_table* t, int32_t mode, int64_t today_local_ticks, int64_t run_at_utc_ticks, tt_result** out,
+                 int64_t* n_marked);
+
+/* ITasksManager.GetTasksByCreator (ITasksManager.cs:7; FakeTasksManager.cs:68-72,
+ * TasksStoreManager.cs:54-69): ordinal byte-exact match of TaskCreatedBy (64-bit hash scan,
+ * then the candidate's string is compared), descending TaskCreatedOn, ties in row order. */
+int32_t tt_get_by_creator(tt_table* t, const char* utf8, int32_t len, tt_result** out);
+
+/* ---- results --------------------------------------------------------------------------- */
+
+int32_t tt_result_count(const tt_result* r, int64_t* n);
+/* shard-local row numbers, uint32 per hit */
+int32_t tt_result_rows(tt_result* r, uint32_t* out);
+/* TaskIds, 16 bytes per hit */
+int32_t tt_result_ids(tt_result* r, uint8_t* out16);
+/* any other column for the hits (TT_FIELD_*) */
+int32_t tt_result_field(tt_result* r, int32_t field, void* out);
+int32_t tt_result_free(tt_result* r);
+
+/* ---- state access used by the parity tests and by the benchmark's per-step reset --------- */
+
+/* Bit-planes, (n+7)/8 bytes each, bit (r & 7) of byte (r >> 3) = row r.  Either may be NULL.
+ * The buffers may be host (pageable or pinned) or device memory (copied with cudaMemcpyDefault). */
+int32_t tt_snapshot_flags(tt_table* t, uint8_t* completed_bits, uint8_t* overdue_bits);
+int32_t tt_restore_flags(tt_table* t, const uint8_t* completed_bits, const uint8_t* overdue_bits);
+/* Population counts of the two planes (computed on the device). */
+int32_t tt_count_flags(tt_table* t, int64_t* n_completed, int64_t* n_overdue);
+/* Order-free digest of a result computed on the device: XOR of the TaskIds (hi = bytes 0..7,
+ * lo = bytes 8..15, big-endian) and the sum of the row numbers.  Lets the 1 B-row parity test
+ * compare with the streaming oracle without moving 25 M ids to the host. */
+int32_t tt_result_digest(tt_result* r, uint64_t* xor_id_hi, uint64_t* xor_id_lo, uint64_t* sum_rows);
+
+/* ---- device-resident form of the sweep (no allocation, no host copy of the hits) ---------
+ * Same kernel as tt_sweep, writing into caller-owned DEVICE buffers on a caller stream
+ * (cudaStream_t passed as void*; NULL = the table's own stream).  d_rows: uint32[cap],
+ * d_ids: 16*cap bytes (may be NULL to skip the TaskId gather).  h_stats (host memory,
+ * filled when the call returns; the call synchronises the stream).  If the hits do not fit
+ * in cap the call returns TT_ERR_CAPACITY: rows before stats->resume_row were processed
+ * completely (listed and, in a marking sweep, marked); call again with first_row =
+ * stats->resume_row to continue. */
+typedef struct tt_sweep_stats {
+  int64_t n_listed;   /* hits in [first_row, n): what GetYesterdaysDueTasks returns            */
+  int64_t n_stored;   /* hits actually written to d_rows / d_ids                               */
+  int64_t n_marked;   /* rows whose IsOverDue was set                                          */
+  int64_t resume_row; /* == row count when complete                                            */
+  float kernel_ms;    /* CUDA-event time of the sweep kernel on its stream                      */
+  int32_t launches;   /* kernels launched by this call                                          */
+} tt_sweep_stats;
+
+#define TT_SWEEP_MARK 1     /* apply the cron predicate and set IsOverDue (the fused tick)      */
+#define TT_SWEEP_LIST_ONLY 0 /* GetYesterdaysDueTasks only                                        */
+
+int32_t tt_sweep_device(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_ticks,
+                        int64_t run_at_utc_ticks, int64_t first_row, uint32_t* d_rows, void* d_ids, int64_t cap,
+                        tt_sweep_stats* h_stats, void* stream);
+
+/* Device addresses of the table's columns, for callers that exchange shard results over
+ * NCCL or reset state between benchmark steps.  Any out pointer may be NULL. */
+typedef struct tt_device_view {
+  int64_t n;           /* rows                      */
+  int64_t n_padded;    /* rows allocated (tile multiple) */
+  void* due_code;      /* uint32[n_padded]          */
+  void* completed;     /* uint32[n_padded/32]       */
+  void* overdue;       /* uint32[n_padded/32]       */
+  void* creator_hash;  /* uint64[n_padded]          */
+  void* task_id;       /* 16 B * n_padded           */
+  void* created_raw;   /* uint64[n_padded]          */
+  int32_t device;
+} tt_device_view;
+int32_t tt_get_device_view(tt_table* t, tt_device_view* out);
+
+#ifdef __cplusplus
+}
+#endif
+
+#endif /* TASKTABLE_H */

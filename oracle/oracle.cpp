@@ -496,6 +496,16 @@ void orc_get_flags(orc_table* t, uint8_t* completed, uint8_t* overdue) {
   }
 }
 
+// The state store's key index exists before the cron tick runs; build it outside timed regions.
+void orc_build_keys(orc_table* t) { t->BuildKeys(); }
+
+void orc_set_all_flags(orc_table* t, const uint8_t* completed, const uint8_t* overdue) {
+  for (size_t i = 0; i < t->rows.size(); ++i) {
+    t->rows[i]->IsCompleted = completed[i] != 0;
+    t->rows[i]->IsOverDue = overdue[i] != 0;
+  }
+}
+
 void orc_set_flags(orc_table* t, int64_t row, int32_t completed, int32_t overdue) {
   t->rows[row]->IsCompleted = completed != 0;
   t->rows[row]->IsOverDue = overdue != 0;
@@ -634,6 +644,18 @@ orc_soa* orc_soa_create(const tt_synth_cfg* cfg, uint64_t first_row, int64_t n, 
     });
   for (auto& t : pool) t.join();
   return s;
+}
+
+void orc_soa_reset(orc_soa* s, const tt_synth_cfg* cfg, uint64_t first_row, int32_t threads) {
+  if (threads < 1) threads = 1;
+  std::vector<std::thread> pool;
+  int64_t n = s->n;
+  for (int th = 0; th < threads; ++th)
+    pool.emplace_back([=]() {
+      for (int64_t i = n * th / threads; i < n * (th + 1) / threads; ++i)
+        s->overdue[i] = tt_synth_make(cfg, first_row + (uint64_t)i).overdue;
+    });
+  for (auto& t : pool) t.join();
 }
 
 void orc_soa_destroy(orc_soa* s) {

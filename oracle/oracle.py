@@ -101,6 +101,9 @@ def lib():
     L.orc_get_by_creator.restype = i64
     L.orc_get_flags.argtypes = [vp, vp, vp]
     L.orc_set_flags.argtypes = [vp, i64, i32, i32]
+    L.orc_build_keys.argtypes = [vp]
+    L.orc_set_all_flags.argtypes = [vp, vp, vp]
+    L.orc_soa_reset.argtypes = [vp, C.POINTER(SynthCfg), u64, i32]
     L.orc_export.argtypes = [vp, vp, vp, vp]
     L.orc_created_by.argtypes = [vp, i64, C.c_char_p, i32]
     L.orc_created_by.restype = i32
@@ -185,6 +188,15 @@ class OracleTable:
         self._l.orc_get_flags(self._h, _ptr(c), _ptr(o))
         return c, o
 
+    def build_keys(self):
+        self._l.orc_build_keys(self._h)
+
+    def set_all_flags(self, completed, overdue):
+        c = np.ascontiguousarray(completed, dtype=np.uint8)
+        o = np.ascontiguousarray(overdue, dtype=np.uint8)
+        assert c.size == len(self) and o.size == len(self)
+        self._l.orc_set_all_flags(self._h, _ptr(c), _ptr(o))
+
     def set_flags(self, row, completed, overdue):
         self._l.orc_set_flags(self._h, row, int(completed), int(overdue))
 
@@ -236,7 +248,11 @@ class SoaTable:
         self._l = lib()
         self.n = n
         self.threads = threads or (os.cpu_count() or 1)
+        self._cfg, self._first = cfg, first_row
         self._h = C.c_void_p(self._l.orc_soa_create(C.byref(cfg), first_row, n, self.threads))
+
+    def reset(self):
+        self._l.orc_soa_reset(self._h, C.byref(self._cfg), self._first, self.threads)
 
     def sweep(self, today=DEFAULT_TODAY, run_at=DEFAULT_RUN_AT, cap=None):
         cap = cap or self.n
