@@ -16,6 +16,7 @@
 #include <cub/device/device_radix_sort.cuh>
 
 #include "../../include/tt_synth.h"
+#include "sweep.cuh"
 
 namespace tt {
 
@@ -30,7 +31,7 @@ __global__ void order_keys_kernel(const uint32_t* rows, const uint64_t* created_
 
 __global__ void gather_ids_kernel(const uint32_t* rows, const uint4* task_id, uint4* out, int64_t n) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) out[i] = task_id[rows[i]];
+  if (i < n) out[i] = ld_gather_v4(task_id + rows[i]);
 }
 
 // Returns 0 or a cudaError_t value.
@@ -71,6 +72,31 @@ inline int order_by_created(cudaStream_t stream, const uint64_t* created_raw, co
   cudaFree(keys_in);
   cudaFree(keys_out);
   cudaFree(rows_tmp);
+  cudaFree(temp);
+  return (int)e;
+}
+
+// Sorts a hit list by row number and re-gathers the TaskIds (used when two row-ordered runs
+// have to be merged).  Returns 0 or a cudaError_t value.
+inline int sort_rows_and_gather(cudaStream_t stream, const uint4* task_id, uint32_t* d_rows, uint4* d_ids, int64_t n) {
+  if (n <= 1) return 0;
+  if (n > 0x7FFFFFFF) return (int)cudaErrorInvalidValue;
+  const int num = (int)n;
+  uint32_t* tmp = nullptr;
+  void* temp = nullptr;
+  size_t temp_bytes = 0;
+  cudaError_t e = cub::DeviceRadixSort::SortKeys(nullptr, temp_bytes, d_rows, tmp, num, 0, 32, stream);
+  if (e == cudaSuccess) e = cudaMalloc(&tmp, (size_t)n * 4);
+  if (e == cudaSuccess) e = cudaMalloc(&temp, temp_bytes ? temp_bytes : 16);
+  if (e == cudaSuccess) e = cub::DeviceRadixSort::SortKeys(temp, temp_bytes, d_rows, tmp, num, 0, 32, stream);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(d_rows, tmp, (size_t)n * 4, cudaMemcpyDeviceToDevice, stream);
+  if (e == cudaSuccess) {
+    gather_ids_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(d_rows, task_id, d_ids, n);
+    e = cudaGetLastError();
+  }
+  cudaError_t s = cudaStreamSynchronize(stream);
+  if (e == cudaSuccess) e = s;
+  cudaFree(tmp);
   cudaFree(temp);
   return (int)e;
 }

@@ -1,18 +1,27 @@
-// sweep.cuh — K1/K2: fused predicate + ordered stream compaction + overdue flag write.
+// sweep.cuh — K1/K2: fused predicate + stream compaction + overdue flag write, and the
+// two small kernels that put the hit list in row order and fetch the TaskIds.
 //
 // One pass over the hot columns replaces the reference's GET -> filter -> POST round trip
 // (Svc/Controllers/ScheduledTasksManagerController.cs:19-46 calling
 //  Api/Services/TasksStoreManager.cs:104-149 or Api/Services/FakeTasksManager.cs:107-112).
 //
-// Tile = 8192 rows per CTA (256 threads).  Each warp owns 1024 consecutive rows = 32 flag
-// words: every lane issues 8 coalesced 128-bit loads of due_code up front (4 KB in flight
-// per warp), evaluates the predicate to 8 nibbles, and an 8x8 nibble transpose across each
-// group of 8 lanes (3 shuffles) turns them into one 32-row match word per lane, aligned with
-// the completed / overdue bit-plane words.  Hits are ranked with popc + warp scan + CTA scan,
-// the tile's global offset comes from a decoupled look-back over per-tile status words (tiles
-// are handed out by an atomic counter so a tile's predecessors are always running), and the
-// hit rows are staged in shared memory so the row-index store and the 16-byte TaskId gather
-// are coalesced on the output side.  Output order = ascending row = the reference's list order.
+// K1 sweep_kernel.  Tile = 8192 rows per CTA iteration (256 threads, 4 CTAs per SM,
+// persistent).  Each warp owns 1024 consecutive rows = 32 flag words: every lane issues 8
+// coalesced 128-bit loads of due_code (4 KB in flight per warp), evaluates the predicate to 8
+// nibbles, and an 8x8 nibble transpose across each group of 8 lanes (3 shuffles) turns them
+// into one 32-row match word per lane, aligned with the completed / overdue bit-plane words.
+// Hits are ranked with popc + warp scan + CTA scan; the tile then takes a contiguous slot in
+// the hit list with ONE atomicAdd on a global cursor.  Software pipeline: the loads of the
+// CTA's next tile are in flight while the current one is ranked, and a tile is written one
+// iteration after its slot was requested, so neither DRAM nor atomic latency is exposed.
+// No CTA ever waits for another one (measured on B200: an in-order variant with per-tile
+// status words spent most of its time polling them; this one streams at ~6.3 TB/s).
+//
+// The slots are handed out in completion order, so the list K1 writes is ordered inside a
+// tile but not across tiles.  K2 tile_offsets_kernel turns the per-tile counts into the
+// offsets of the row-ordered list, and K3 place_hits_kernel moves every hit to its final
+// position and gathers its 16-byte TaskId on the way (out_ids[i] = task_id[out_rows[i]]).
+// Final order = ascending row = the reference's list order, deterministic.
 #pragma once
 
 #include <cuda_runtime.h>
@@ -26,35 +35,31 @@ constexpr int kSweepThreads = 256;
 constexpr int kSweepWarps = kSweepThreads / 32;
 constexpr int kSweepCtasPerSm = 4;
 
-// tile status word: state in the top 2 bits, value (hit count) in the low 32
-constexpr unsigned long long kStInvalid = 0ull;
-constexpr unsigned long long kStAggregate = 1ull << 62;
-constexpr unsigned long long kStPrefix = 2ull << 62;
-constexpr unsigned long long kStValueMask = 0xFFFFFFFFull;
-
 struct SweepCtl {
   unsigned int tile_counter;         // next tile to hand out (relative to first_tile)
   unsigned int pad;
-  unsigned long long total;          // hits in all tiles (inclusive prefix of the last tile)
-  unsigned long long overflow;       // min over tiles that did not fit of (tile << 32 | base); ~0 if none
+  unsigned long long cursor;         // hits so far = next free slot of the unordered list; total at the end
+  unsigned long long stored;         // min slot of a tile that did not fit (= hits stored); ~0 if all fit
 };
 
 struct SweepParams {
   const uint32_t* due_code;
   const uint32_t* completed;
   uint32_t* overdue;
-  const uint4* task_id;
-  uint32_t* out_rows;                // may be null (count only)
-  uint4* out_ids;                    // may be null
-  unsigned long long* tile_status;   // one word per tile, zeroed before launch
-  SweepCtl* ctl;                     // zeroed (overflow = ~0) before launch
-  unsigned long long cap;            // capacity of out_rows / out_ids in hits
+  uint32_t* list;                    // unordered hit rows (scratch, cap entries); null = count only
+  uint32_t* tile_slot;               // per tile: first slot in `list`
+  uint32_t* tile_count;              // per tile: hits stored (0 if the tile did not fit)
+  uint32_t* group_sum;               // per kTilesPerGroup tiles: sum of tile_count (zeroed before launch)
+  SweepCtl* ctl;                     // tile_counter = cursor = 0, stored = ~0 before launch
+  unsigned long long cap;            // capacity of `list` in hits
   uint32_t first_tile;
   uint32_t num_tiles;                // tiles to process starting at first_tile
   uint32_t mask;                     // TT_MASK_FAKE / TT_MASK_STORE
   uint32_t yesterday;                // day number of DateTime.Today.AddDays(-1)
   uint32_t mark_enable;              // cron predicate runAt.Date > TaskDueDate.Date (uniform, see below)
 };
+
+constexpr int kTilesPerGroup = 1024;  // K2: one CTA per group of tiles
 
 __device__ __forceinline__ uint4 ld_stream_v4(const uint4* p) {
   uint4 r;
@@ -64,14 +69,15 @@ __device__ __forceinline__ uint4 ld_stream_v4(const uint4* p) {
   return r;
 }
 
-__device__ __forceinline__ unsigned long long ld_status(const unsigned long long* p) {
-  unsigned long long v;
-  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-  return v;
-}
-
-__device__ __forceinline__ void st_status(unsigned long long* p, unsigned long long v) {
-  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+// Random 16-byte gathers: without a hint the L2 fetches 128 B from DRAM per miss on B200
+// (measured 132 B/hit); the 64 B prefetch-size hint halves that (68 B/hit) — there is no
+// smaller fetch size.
+__device__ __forceinline__ uint4 ld_gather_v4(const uint4* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.L2::64B.v4.u32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p));
+  return r;
 }
 
 __device__ __forceinline__ uint32_t warp_sum(uint32_t v) {
@@ -80,87 +86,117 @@ __device__ __forceinline__ uint32_t warp_sum(uint32_t v) {
   return v;
 }
 
-// Decoupled look-back, run by one full warp.  Publishes this tile's aggregate, walks back over
-// predecessors 32 at a time until one with a final prefix is found, publishes this tile's
-// inclusive prefix and returns the exclusive one.  A status word carries state and value in
-// one 64-bit store, so no fence is needed.
-__device__ __forceinline__ uint32_t tile_lookback(unsigned long long* status, uint32_t rel_tile, uint32_t aggregate,
-                                                  uint32_t lane) {
-  if (rel_tile == 0) {
-    if (lane == 0) st_status(status, kStPrefix | aggregate);
-    return 0;
-  }
-  if (lane == 0) st_status(status + rel_tile, kStAggregate | aggregate);
-  uint32_t excl = 0;
-  int look = (int)rel_tile - 1;
-  while (true) {
-    int idx = look - (int)lane;
-    unsigned long long s = kStPrefix;  // virtual predecessor of tile 0: prefix 0
-    if (idx >= 0) {
-      do {
-        s = ld_status(status + idx);
-      } while ((s >> 62) == 0);
-    }
-    __syncwarp();
-    uint32_t is_prefix = __ballot_sync(0xFFFFFFFFu, (s >> 62) == 2);
-    uint32_t val = (uint32_t)(s & kStValueMask);
-    if (is_prefix) {
-      uint32_t first = __ffs(is_prefix) - 1;  // nearest predecessor with a final prefix
-      excl += warp_sum(lane <= first ? val : 0u);
-      break;
-    }
-    excl += warp_sum(val);
-    look -= 32;
-  }
-  if (lane == 0) st_status(status + rel_tile, kStPrefix | (unsigned long long)(excl + aggregate));
-  return excl;
-}
-
 // USE_FLAGS: STORE mode's `IsCompleted == false && IsOverDue == false` (TasksStoreManager.cs:135).
 // MARK     : set IsOverDue for the listed rows (TasksStoreManager.cs:146) when the cron predicate
 //            holds.  For a listed row TaskDueDate.Date is yesterday's date, so the per-row test
 //            `runAt.Date > TaskDueDate.Date` (ScheduledTasksManagerController.cs:34) has the
 //            same value for every listed row: it is passed in as mark_enable.
-template <bool USE_FLAGS, bool MARK>
-__global__ void __launch_bounds__(kSweepThreads, kSweepCtasPerSm) sweep_kernel(SweepParams p) {
-  __shared__ uint32_t s_list[TT_TILE_ROWS];
-  __shared__ uint32_t s_wtot[kSweepWarps];
+//
+// Software pipeline: while a tile is ranked, looked back and written, the 8 x 128-bit loads
+// and the two flag words of the CTA's NEXT tile are already in flight (it was claimed from the
+// atomic counter at the top of the iteration), so every CTA keeps 32 KB outstanding almost all
+// the time and the look-back latency is not exposed to DRAM.
+struct TileLoads {
+  uint4 v[8];
+  uint32_t cw, ow;
+};
+
+template <bool USE_FLAGS, int THREADS>
+__device__ __forceinline__ void issue_tile_loads(const SweepParams& p, uint32_t tile, uint32_t warp, uint32_t lane,
+                                                 TileLoads& t) {
+  constexpr uint32_t kTileRows = (THREADS / 32) * TT_WARP_ROWS;
+  const uint4* src = reinterpret_cast<const uint4*>(p.due_code) +
+                     ((size_t)tile * (kTileRows / 4) + (size_t)warp * (TT_WARP_ROWS / 4) + lane);
+#pragma unroll
+  for (int j = 0; j < 8; ++j) t.v[j] = ld_stream_v4(src + j * 32);
+  t.cw = 0;
+  t.ow = 0;
+  if (USE_FLAGS) {
+    const uint32_t wi = tile * (kTileRows / 32) + warp * 32u + lane;
+    t.cw = __ldg(p.completed + wi);
+    t.ow = p.overdue[wi];
+  }
+}
+
+// What a thread remembers about the tile of the previous iteration until its slot is known.
+struct PendingTile {
+  uint32_t rel;     // tile number relative to first_tile; ~0u = none
+  uint32_t hits;    // this lane's 32-row hit word
+  uint32_t ow;      // the overdue word it was computed against
+  uint32_t offset;  // rank of this lane's first hit inside the tile
+  uint32_t total;   // hits in the whole tile
+};
+
+template <bool MARK, int THREADS>
+__device__ __forceinline__ void emit_tile(const SweepParams& p, const PendingTile& t, uint32_t slot, uint32_t warp,
+                                          uint32_t lane, uint32_t tid) {
+  constexpr uint32_t kTileRows = (THREADS / 32) * TT_WARP_ROWS;
+  const uint32_t tile = p.first_tile + t.rel;
+  const bool fits = (unsigned long long)slot + t.total <= p.cap;
+  if (fits) {
+    if (p.list) {
+      uint32_t* dst = p.list + slot + t.offset;
+      const uint32_t row0 = tile * kTileRows + warp * TT_WARP_ROWS + lane * 32u;
+      uint32_t m = t.hits;
+      while (m) {
+        uint32_t b = __ffs(m) - 1;
+        m &= m - 1;
+        *dst++ = row0 + b;
+      }
+    }
+    if (MARK && p.mark_enable && t.hits) p.overdue[tile * (kTileRows / 32) + warp * 32u + lane] = t.ow | t.hits;
+  }
+  if (tid == 0) {
+    if (p.list) {
+      p.tile_slot[t.rel] = slot;
+      p.tile_count[t.rel] = fits ? t.total : 0u;
+      if (fits && t.total) atomicAdd(p.group_sum + t.rel / kTilesPerGroup, t.total);
+    }
+    if (!fits) atomicMin(&p.ctl->stored, (unsigned long long)slot);
+  }
+}
+
+template <bool USE_FLAGS, bool MARK, int THREADS, int CTAS_PER_SM>
+__global__ void __launch_bounds__(THREADS, CTAS_PER_SM) sweep_kernel(SweepParams p) {
+  constexpr int kWarps = THREADS / 32;
+  __shared__ uint32_t s_wtot[kWarps];
   __shared__ uint32_t s_tile;
-  __shared__ uint32_t s_base;
+  __shared__ uint32_t s_slot;
 
   const uint32_t tid = threadIdx.x;
   const uint32_t lane = tid & 31u;
   const uint32_t warp = tid >> 5;
   const uint32_t src_lane = tt_word_src_lane(lane);
 
-  for (;;) {
-    if (tid == 0) s_tile = atomicAdd(&p.ctl->tile_counter, 1u);
-    __syncthreads();
-    const uint32_t rel = s_tile;
-    if (rel >= p.num_tiles) break;
-    const uint32_t tile = p.first_tile + rel;
+  if (tid == 0) s_tile = atomicAdd(&p.ctl->tile_counter, 1u);
+  __syncthreads();
+  uint32_t cur = s_tile;
+  __syncthreads();  // s_tile is read before iteration 0 overwrites it
 
-    // ---- loads: 8 x 128-bit per lane, all issued before first use ----
-    const uint4* src = reinterpret_cast<const uint4*>(p.due_code) +
-                       ((size_t)tile * (TT_TILE_ROWS / 4) + (size_t)warp * (TT_WARP_ROWS / 4) + lane);
-    uint4 v[8];
-#pragma unroll
-    for (int j = 0; j < 8; ++j) v[j] = ld_stream_v4(src + j * 32);
-    const uint32_t wi = tile * TT_TILE_WORDS + warp * 32u + lane;  // this lane's flag word
-    uint32_t cw = 0, ow = 0;
-    if (USE_FLAGS) {
-      cw = __ldg(p.completed + wi);
-      ow = p.overdue[wi];
-    }
+  PendingTile pend;
+  pend.rel = ~0u;
+  pend.hits = pend.ow = pend.offset = pend.total = 0;
+  uint32_t pend_slot = 0;  // thread 0: the slot the cursor atomic returned for the pending tile
 
-    // ---- predicate -> nibbles -> 32-row match word ----
+  TileLoads ld;
+  if (cur < p.num_tiles) issue_tile_loads<USE_FLAGS, THREADS>(p, p.first_tile + cur, warp, lane, ld);
+
+  while (cur < p.num_tiles) {
+    const uint32_t rel = cur;
+    // claim the next tile now; its number is needed only after the barrier
+    uint32_t claimed = 0;
+    if (tid == 0) claimed = atomicAdd(&p.ctl->tile_counter, 1u);
+
+    // ---- predicate -> nibbles -> 32-row match word (waits for this tile's loads) ----
     uint32_t packed = 0;
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      uint32_t nib = ((v[j].x & p.mask) == p.yesterday ? 1u : 0u) | ((v[j].y & p.mask) == p.yesterday ? 2u : 0u) |
-                     ((v[j].z & p.mask) == p.yesterday ? 4u : 0u) | ((v[j].w & p.mask) == p.yesterday ? 8u : 0u);
+      const uint4 v = ld.v[j];
+      uint32_t nib = ((v.x & p.mask) == p.yesterday ? 1u : 0u) | ((v.y & p.mask) == p.yesterday ? 2u : 0u) |
+                     ((v.z & p.mask) == p.yesterday ? 4u : 0u) | ((v.w & p.mask) == p.yesterday ? 8u : 0u);
       packed |= nib << (4 * j);
     }
+    const uint32_t cw = ld.cw, ow = ld.ow;
 #pragma unroll
     for (uint32_t d = 4; d > 0; d >>= 1) {
       uint32_t other = __shfl_xor_sync(0xFFFFFFFFu, packed, d);
@@ -178,47 +214,112 @@ __global__ void __launch_bounds__(kSweepThreads, kSweepCtasPerSm) sweep_kernel(S
       if (lane >= (uint32_t)d) incl += up;
     }
     if (lane == 31) s_wtot[warp] = incl;
+    if (tid == 0) {
+      s_tile = claimed;
+      s_slot = pend_slot;  // the atomic issued one iteration ago has long returned
+    }
     __syncthreads();
+
+    // ---- next tile's loads go out now; they land while the previous tile is written ----
+    const uint32_t nxt = s_tile;
+    if (nxt < p.num_tiles) issue_tile_loads<USE_FLAGS, THREADS>(p, p.first_tile + nxt, warp, lane, ld);
+
     uint32_t wbase = 0, total = 0;
 #pragma unroll
-    for (int k = 0; k < kSweepWarps; ++k) {
+    for (int k = 0; k < kWarps; ++k) {
       uint32_t x = s_wtot[k];
       wbase += (k < (int)warp) ? x : 0u;
       total += x;
     }
+    // ---- ask for this tile's slot (used next iteration), write the previous tile ----
+    if (tid == 0) pend_slot = (uint32_t)atomicAdd(&p.ctl->cursor, (unsigned long long)total);
+    if (pend.rel != ~0u) emit_tile<MARK, THREADS>(p, pend, s_slot, warp, lane, tid);
+    pend.rel = rel;
+    pend.hits = hits;
+    pend.ow = ow;
+    pend.offset = wbase + incl - cnt;
+    pend.total = total;
+    cur = nxt;
+    __syncthreads();  // s_wtot / s_tile / s_slot are rewritten by the next iteration
+  }
 
-    // ---- stage hit rows in shared memory (ascending row order) ----
-    {
-      uint32_t pos = wbase + incl - cnt;
-      const uint32_t row0 = tile * TT_TILE_ROWS + warp * TT_WARP_ROWS + lane * 32u;
-      uint32_t m = hits;
-      while (m) {
-        uint32_t b = __ffs(m) - 1;
-        m &= m - 1;
-        s_list[pos++] = row0 + b;
-      }
-    }
-    if (warp == 0) {
-      uint32_t excl = tile_lookback(p.tile_status, rel, total, lane);
-      if (lane == 0) s_base = excl;
-    }
+  // ---- drain: the last tile this CTA processed ----
+  if (pend.rel != ~0u) {
+    if (tid == 0) s_slot = pend_slot;
     __syncthreads();
-    const uint32_t base = s_base;
+    emit_tile<MARK, THREADS>(p, pend, s_slot, warp, lane, tid);
+  }
+}
 
-    // ---- emit ----
-    if ((unsigned long long)base + total <= p.cap) {
-      if (MARK && p.mark_enable && hits) p.overdue[wi] = ow | hits;
-      if (p.out_rows) {
-        for (uint32_t i = tid; i < total; i += kSweepThreads) {
-          uint32_t r = s_list[i];
-          p.out_rows[base + i] = r;
-          if (p.out_ids) p.out_ids[base + i] = ld_stream_v4(p.task_id + r);
-        }
-      }
-    } else if (tid == 0) {
-      atomicMin(&p.ctl->overflow, ((unsigned long long)tile << 32) | base);
+// K2: offsets of the row-ordered list.  tile_first[t] = number of stored hits in tiles < t.
+// One CTA per group of kTilesPerGroup tiles: its carry is the sum of the earlier groups'
+// totals (accumulated by K1), then a block-wide exclusive scan of the group's counts.
+__global__ void __launch_bounds__(kTilesPerGroup) tile_offsets_kernel(const uint32_t* tile_count,
+                                                                      const uint32_t* group_sum, uint32_t num_tiles,
+                                                                      uint32_t* tile_first) {
+  __shared__ uint32_t s_warp[kTilesPerGroup / 32];
+  __shared__ uint32_t s_carry;
+  const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+  const uint32_t g = blockIdx.x;
+  if (warp == 0) {
+    uint32_t c = 0;
+    for (uint32_t k = lane; k < g; k += 32) c += group_sum[k];
+    c = warp_sum(c);
+    if (lane == 0) s_carry = c;
+  }
+  const uint32_t t = g * kTilesPerGroup + tid;
+  const uint32_t cnt = t < num_tiles ? tile_count[t] : 0u;
+  uint32_t incl = cnt;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    uint32_t up = __shfl_up_sync(0xFFFFFFFFu, incl, d);
+    if (lane >= (uint32_t)d) incl += up;
+  }
+  if (lane == 31) s_warp[warp] = incl;
+  __syncthreads();
+  uint32_t wbase = 0;
+  for (uint32_t k = 0; k < warp; ++k) wbase += s_warp[k];
+  if (t < num_tiles) tile_first[t] = s_carry + wbase + incl - cnt;
+}
+
+// K3: every stored hit goes to its place in the row-ordered list; its TaskId is gathered on the
+// way (16 B random read, coalesced writes).  The hit count is read from the sweep's control
+// block on the device, so K1 -> K2 -> K3 are queued back to back without a host round trip.
+constexpr int kPlaceThreads = 256;
+constexpr int kPlaceUnroll = 4;
+
+template <int TILE_ROWS>
+__global__ void __launch_bounds__(kPlaceThreads) place_hits_kernel(const SweepCtl* ctl, const uint32_t* list,
+                                                                   const uint32_t* tile_slot,
+                                                                   const uint32_t* tile_first, uint32_t first_tile,
+                                                                   const uint4* task_id, uint32_t* out_rows,
+                                                                   uint4* out_ids) {
+  const unsigned long long st = ctl->stored;
+  const unsigned long long n = st == ~0ull ? ctl->cursor : st;
+  const unsigned long long stride = (unsigned long long)gridDim.x * kPlaceThreads;
+  for (unsigned long long i0 = (unsigned long long)blockIdx.x * kPlaceThreads + threadIdx.x; i0 < n;
+       i0 += stride * kPlaceUnroll) {
+    uint32_t r[kPlaceUnroll];
+    uint4 id[kPlaceUnroll];
+#pragma unroll
+    for (int j = 0; j < kPlaceUnroll; ++j) {
+      unsigned long long i = i0 + j * stride;
+      r[j] = i < n ? list[i] : 0u;
     }
-    if (rel == p.num_tiles - 1 && tid == 0) p.ctl->total = (unsigned long long)base + total;
+    if (out_ids) {
+#pragma unroll
+      for (int j = 0; j < kPlaceUnroll; ++j) id[j] = ld_gather_v4(task_id + r[j]);
+    }
+#pragma unroll
+    for (int j = 0; j < kPlaceUnroll; ++j) {
+      unsigned long long i = i0 + j * stride;
+      if (i < n) {
+        const uint32_t t = r[j] / TILE_ROWS - first_tile;
+        const uint32_t dst = tile_first[t] + ((uint32_t)i - tile_slot[t]);
+        out_rows[dst] = r[j];
+        if (out_ids) out_ids[dst] = id[j];
+      }
+    }
   }
 }
 

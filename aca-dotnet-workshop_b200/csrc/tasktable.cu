@@ -10,6 +10,8 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <atomic>
+#include <memory>
 #include <mutex>
 #include <new>
 #include <string>
@@ -51,11 +53,19 @@ inline int64_t round_up(int64_t x, int64_t m) { return (x + m - 1) / m * m; }
 
 }  // namespace
 
+// Shared between a table and the results it handed out, so a result outliving its table can
+// still be freed (and refuses everything else).
+struct TableCore {
+  int device = 0;
+  std::atomic<bool> alive{true};
+};
+
 struct tt_table {
+  std::shared_ptr<TableCore> core = std::make_shared<TableCore>();
   int device = 0;
   std::mutex mu;
   cudaStream_t stream = nullptr;
-  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr;
   int sm_count = 148;
 
   int64_t n = 0, n_pad = 0;
@@ -77,9 +87,13 @@ struct tt_table {
   bool ids_sorted = false;
   uint32_t* id_order = nullptr;  // rows sorted by TaskId when the table itself is not
 
-  // sweep scratch: one status word per tile + control block (device) and its pinned mirror
-  unsigned long long* tile_status = nullptr;
-  int64_t tile_status_cap = 0;
+  // sweep scratch: per-tile slot / count / final offset (3 words per tile), group sums, the
+  // unordered hit list (grown on demand), and the control block with its pinned mirror
+  uint32_t* tile_words = nullptr;   // [3][n_tiles]
+  uint32_t* group_sum = nullptr;    // [n_groups]
+  int64_t n_tiles = 0, n_groups = 0;
+  uint32_t* hit_list = nullptr;
+  int64_t hit_list_cap = 0;
   tt::SweepCtl* ctl = nullptr;
   tt::SweepCtl* h_ctl = nullptr;
   // small device/pinned scratch for reductions and the creator filter
@@ -90,7 +104,8 @@ struct tt_table {
 };
 
 struct tt_result {
-  tt_table* t = nullptr;
+  std::shared_ptr<TableCore> core;
+  tt_table* t = nullptr;  // valid only while core->alive
   int64_t n = 0;
   int64_t cap = 0;
   uint32_t* d_rows = nullptr;
@@ -104,6 +119,7 @@ struct DeviceGuard {
   explicit DeviceGuard(int dev) {
     cudaGetDevice(&prev);
     if (prev != dev) cudaSetDevice(dev);
+    cudaGetLastError();  // do not inherit a stale error from earlier, unrelated runtime calls
   }
   ~DeviceGuard() {
     if (prev >= 0) cudaSetDevice(prev);
@@ -122,15 +138,17 @@ void free_columns(tt_table* t) {
   cudaFree(t->creator_off);
   cudaFree(t->creator_pool);
   cudaFree(t->id_order);
-  cudaFree(t->tile_status);
+  cudaFree(t->tile_words);
+  cudaFree(t->group_sum);
+  cudaFree(t->hit_list);
   t->due_code = t->completed = t->overdue = nullptr;
   t->creator_hash = nullptr;
   t->task_id = nullptr;
   t->created_raw = t->due_raw = nullptr;
   t->creator_ref = t->creator_off = t->id_order = nullptr;
   t->creator_pool = nullptr;
-  t->tile_status = nullptr;
-  t->tile_status_cap = 0;
+  t->tile_words = t->group_sum = t->hit_list = nullptr;
+  t->n_tiles = t->n_groups = t->hit_list_cap = 0;
   t->n = t->n_pad = 0;
 }
 
@@ -146,8 +164,10 @@ int32_t alloc_columns(tt_table* t, int64_t n) {
   TT_CUDA(cudaMalloc(&t->created_raw, np * 8));
   TT_CUDA(cudaMalloc(&t->due_raw, np * 8));
   TT_CUDA(cudaMalloc(&t->creator_ref, np * 4));
-  t->tile_status_cap = np / TT_TILE_ROWS;
-  TT_CUDA(cudaMalloc(&t->tile_status, t->tile_status_cap * 8));
+  t->n_tiles = np / TT_TILE_ROWS;
+  t->n_groups = (t->n_tiles + tt::kTilesPerGroup - 1) / tt::kTilesPerGroup;
+  TT_CUDA(cudaMalloc(&t->tile_words, 3 * t->n_tiles * 4));
+  TT_CUDA(cudaMalloc(&t->group_sum, t->n_groups * 4));
   // padding rows never match and carry no flags
   TT_CUDA(cudaMemsetAsync(t->due_code, 0xFF, np * 4, t->stream));
   TT_CUDA(cudaMemsetAsync(t->completed, 0, np / 8, t->stream));
@@ -292,7 +312,7 @@ int32_t sweep_run(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_
   uint32_t yesterday = 0;
   int32_t rc = check_clock(today_local_ticks, &yesterday);
   if (rc) return rc;
-  if (first_row < 0 || first_row % TT_TILE_ROWS != 0 || (first_row > t->n && first_row != t->n_pad))
+  if (first_row < 0 || first_row % TT_TILE_ROWS != 0 || first_row > t->n_pad)
     return fail(TT_ERR_ARG, "first_row must be a multiple of %d inside the table", TT_TILE_ROWS);
   if (cap < 0) return fail(TT_ERR_ARG, "negative capacity");
   const bool mark = (flags & TT_SWEEP_MARK) != 0;
@@ -306,16 +326,27 @@ int32_t sweep_run(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_
   const uint32_t first_tile = (uint32_t)(first_row / TT_TILE_ROWS);
   const uint32_t num_tiles = (uint32_t)(t->n_pad / TT_TILE_ROWS) - first_tile;
 
+  // scratch for the unordered hit list K1 writes before K3 puts it in row order
+  const bool listing = d_rows != nullptr;
+  if (listing && cap > t->hit_list_cap) {
+    cudaFree(t->hit_list);
+    t->hit_list = nullptr;
+    t->hit_list_cap = 0;
+    TT_CUDA(cudaMalloc(&t->hit_list, (size_t)std::max<int64_t>(cap, 1) * 4));
+    t->hit_list_cap = cap;
+  }
+
   tt::SweepParams p;
   p.due_code = t->due_code;
   p.completed = t->completed;
   p.overdue = t->overdue;
-  p.task_id = t->task_id;
-  p.out_rows = d_rows;
-  p.out_ids = d_ids;
-  p.tile_status = t->tile_status;
+  p.list = listing ? t->hit_list : nullptr;
+  p.tile_slot = t->tile_words;
+  p.tile_count = t->tile_words + t->n_tiles;
+  uint32_t* tile_first = t->tile_words + 2 * t->n_tiles;
+  p.group_sum = t->group_sum;
   p.ctl = t->ctl;
-  p.cap = d_rows ? (unsigned long long)cap : ~0ull;
+  p.cap = listing ? (unsigned long long)cap : ~0ull;
   p.first_tile = first_tile;
   p.num_tiles = num_tiles;
   p.mask = mode == TT_MODE_FAKE ? TT_MASK_FAKE : TT_MASK_STORE;
@@ -326,40 +357,51 @@ int32_t sweep_run(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_
   tt::SweepCtl init;
   init.tile_counter = 0;
   init.pad = 0;
-  init.total = 0;
-  init.overflow = ~0ull;
+  init.cursor = 0;
+  init.stored = ~0ull;
   *t->h_ctl = init;
   TT_CUDA(cudaMemcpyAsync(t->ctl, t->h_ctl, sizeof init, cudaMemcpyHostToDevice, stream));
-  TT_CUDA(cudaMemsetAsync(t->tile_status, 0, (size_t)num_tiles * 8, stream));
+  const unsigned n_groups = (num_tiles + tt::kTilesPerGroup - 1) / tt::kTilesPerGroup;
+  if (listing) TT_CUDA(cudaMemsetAsync(t->group_sum, 0, (size_t)n_groups * 4, stream));
   const unsigned grid = (unsigned)std::min<int64_t>(num_tiles, (int64_t)t->sm_count * tt::kSweepCtasPerSm);
   TT_CUDA(cudaEventRecord(t->ev0, stream));
   if (mode == TT_MODE_STORE) {
     if (p.mark_enable)
-      tt::sweep_kernel<true, true><<<grid, tt::kSweepThreads, 0, stream>>>(p);
+      tt::sweep_kernel<true, true, tt::kSweepThreads, tt::kSweepCtasPerSm><<<grid, tt::kSweepThreads, 0, stream>>>(p);
     else
-      tt::sweep_kernel<true, false><<<grid, tt::kSweepThreads, 0, stream>>>(p);
+      tt::sweep_kernel<true, false, tt::kSweepThreads, tt::kSweepCtasPerSm><<<grid, tt::kSweepThreads, 0, stream>>>(p);
   } else {
-    tt::sweep_kernel<false, false><<<grid, tt::kSweepThreads, 0, stream>>>(p);
+    tt::sweep_kernel<false, false, tt::kSweepThreads, tt::kSweepCtasPerSm><<<grid, tt::kSweepThreads, 0, stream>>>(p);
   }
   TT_CUDA(cudaGetLastError());
   TT_CUDA(cudaEventRecord(t->ev1, stream));
+  st->launches = 1;
+  if (listing) {
+    // K2 + K3: row order and TaskIds; the hit count is read from the control block on the device
+    tt::tile_offsets_kernel<<<n_groups, tt::kTilesPerGroup, 0, stream>>>(p.tile_count, p.group_sum, num_tiles, tile_first);
+    TT_CUDA(cudaGetLastError());
+    const int64_t per_cta = (int64_t)tt::kPlaceThreads * tt::kPlaceUnroll;
+    const unsigned pgrid =
+        (unsigned)std::max<int64_t>(1, std::min<int64_t>((cap + per_cta - 1) / per_cta, (int64_t)t->sm_count * 8));
+    tt::place_hits_kernel<TT_TILE_ROWS><<<pgrid, tt::kPlaceThreads, 0, stream>>>(
+        t->ctl, t->hit_list, p.tile_slot, tile_first, first_tile, t->task_id, d_rows, d_ids);
+    TT_CUDA(cudaGetLastError());
+    st->launches = 3;
+  }
+  TT_CUDA(cudaEventRecord(t->ev2, stream));
   TT_CUDA(cudaMemcpyAsync(t->h_ctl, t->ctl, sizeof init, cudaMemcpyDeviceToHost, stream));
   TT_CUDA(cudaStreamSynchronize(stream));
-  TT_CUDA(cudaEventElapsedTime(&st->kernel_ms, t->ev0, t->ev1));
-  st->launches = 1;
-  st->n_listed = (int64_t)t->h_ctl->total;
-  if (t->h_ctl->overflow == ~0ull) {
-    st->n_stored = d_rows ? st->n_listed : 0;
-    st->resume_row = t->n;
-  } else {
-    st->n_stored = (int64_t)(t->h_ctl->overflow & 0xFFFFFFFFull);
-    st->resume_row = (int64_t)(t->h_ctl->overflow >> 32) * TT_TILE_ROWS;
-  }
-  st->n_marked = p.mark_enable ? (d_rows ? st->n_stored : st->n_listed) : 0;
-  if (mode == TT_MODE_FAKE && mark && survive) st->n_marked = 0;
-  if (t->h_ctl->overflow != ~0ull)
-    return fail(TT_ERR_CAPACITY, "%lld hits do not fit in %lld; resume at row %lld", (long long)st->n_listed,
-                (long long)cap, (long long)st->resume_row);
+  TT_CUDA(cudaEventElapsedTime(&st->sweep_ms, t->ev0, t->ev1));
+  TT_CUDA(cudaEventElapsedTime(&st->gather_ms, t->ev1, t->ev2));
+  st->kernel_ms = st->sweep_ms + st->gather_ms;
+  st->n_listed = (int64_t)t->h_ctl->cursor;
+  const bool complete = t->h_ctl->stored == ~0ull;
+  st->n_stored = listing ? (complete ? st->n_listed : (int64_t)t->h_ctl->stored) : 0;
+  st->resume_row = complete ? t->n : first_row;
+  st->n_marked = p.mark_enable ? (listing ? st->n_stored : st->n_listed) : 0;
+  if (!complete)
+    return fail(TT_ERR_CAPACITY, "%lld hits do not fit in %lld (%lld stored%s)", (long long)st->n_listed,
+                (long long)cap, (long long)st->n_stored, st->n_marked ? " and marked; call again for the rest" : "");
   return TT_OK;
 }
 
@@ -367,6 +409,7 @@ int32_t result_alloc(tt_table* t, int64_t cap, tt_result** out) {
   tt_result* r = new (std::nothrow) tt_result();
   if (!r) return fail(TT_ERR_OOM, "out of host memory");
   r->t = t;
+  r->core = t->core;
   r->cap = std::max<int64_t>(cap, 1);
   cudaError_t e = cudaMalloc(&r->d_rows, r->cap * 4);
   if (e == cudaSuccess) e = cudaMalloc(&r->d_ids, r->cap * 16);
@@ -387,7 +430,10 @@ void result_release(tt_result* r) {
   delete r;
 }
 
-// Sweep into a library-owned result, growing and resuming when the first guess is too small.
+// Sweep into a library-owned result.  The first guess at the hit count is n/16; when it is too
+// small the result is regrown to the exact size and the sweep runs again: from scratch if the
+// first pass changed nothing, otherwise for the hits the first pass did not reach (the rows it
+// marked no longer match), after which the two row-ordered runs are merged by a sort.
 int32_t sweep_owned(tt_table* t, int32_t mode, int32_t flags, int64_t today, int64_t run_at, tt_result** out,
                     tt_sweep_stats* total) {
   memset(total, 0, sizeof *total);
@@ -395,42 +441,51 @@ int32_t sweep_owned(tt_table* t, int32_t mode, int32_t flags, int64_t today, int
   int64_t guess = std::min<int64_t>(t->n, std::max<int64_t>(65536, t->n / 16));
   int32_t rc = result_alloc(t, guess, &r);
   if (rc) return rc;
-  int64_t first_row = 0;
-  for (int pass = 0; pass < 64; ++pass) {
+  bool merged = false;
+  for (int pass = 0; pass < 8; ++pass) {
     tt_sweep_stats st;
-    rc = sweep_run(t, mode, flags, today, run_at, first_row, r->d_rows + r->n, r->d_ids + r->n, r->cap - r->n, &st,
-                   t->stream);
+    rc = sweep_run(t, mode, flags, today, run_at, 0, r->d_rows + r->n, r->d_ids + r->n, r->cap - r->n, &st, t->stream);
     total->kernel_ms += st.kernel_ms;
+    total->sweep_ms += st.sweep_ms;
+    total->gather_ms += st.gather_ms;
     total->launches += st.launches;
     if (rc != TT_OK && rc != TT_ERR_CAPACITY) {
       result_release(r);
       return rc;
     }
-    r->n += st.n_stored;
     total->n_marked += st.n_marked;
     if (rc == TT_OK) {
-      total->n_listed = r->n;
-      total->n_stored = r->n;
+      r->n += st.n_stored;
+      if (merged && r->n > 1) {
+        int e = tt::sort_rows_and_gather(t->stream, t->task_id, r->d_rows, r->d_ids, r->n);
+        if (e != 0) {
+          result_release(r);
+          return fail(TT_ERR_CUDA, "sort_rows_and_gather: %s", cudaGetErrorString((cudaError_t)e));
+        }
+      }
+      total->n_listed = total->n_stored = r->n;
       total->resume_row = t->n;
       *out = r;
       return TT_OK;
     }
-    // grow to exactly what the remaining rows need, keep what is already listed
+    // too small: regrow to what is still needed
+    const bool mutated = st.n_marked > 0;
+    const int64_t keep = mutated ? r->n + st.n_stored : 0;
     tt_result* g = nullptr;
-    rc = result_alloc(t, r->n + (st.n_listed - st.n_stored), &g);
+    rc = result_alloc(t, keep + (st.n_listed - (mutated ? st.n_stored : 0)), &g);
     if (rc) {
       result_release(r);
       return rc;
     }
-    if (r->n) {
-      cudaMemcpyAsync(g->d_rows, r->d_rows, r->n * 4, cudaMemcpyDeviceToDevice, t->stream);
-      cudaMemcpyAsync(g->d_ids, r->d_ids, r->n * 16, cudaMemcpyDeviceToDevice, t->stream);
+    if (keep) {
+      cudaMemcpyAsync(g->d_rows, r->d_rows, keep * 4, cudaMemcpyDeviceToDevice, t->stream);
+      cudaMemcpyAsync(g->d_ids, r->d_ids, keep * 16, cudaMemcpyDeviceToDevice, t->stream);
       cudaStreamSynchronize(t->stream);
+      merged = true;
     }
-    g->n = r->n;
+    g->n = keep;
     result_release(r);
     r = g;
-    first_row = st.resume_row;
   }
   result_release(r);
   return fail(TT_ERR_STATE, "sweep did not converge");
@@ -453,12 +508,14 @@ int32_t tt_create(int32_t device, tt_table** out) {
   tt_table* t = new (std::nothrow) tt_table();
   if (!t) return fail(TT_ERR_OOM, "out of host memory");
   t->device = device;
+  t->core->device = device;
   cudaDeviceProp prop;
   TT_CUDA(cudaGetDeviceProperties(&prop, device));
   t->sm_count = prop.multiProcessorCount;
   TT_CUDA(cudaStreamCreateWithFlags(&t->stream, cudaStreamNonBlocking));
   TT_CUDA(cudaEventCreate(&t->ev0));
   TT_CUDA(cudaEventCreate(&t->ev1));
+  TT_CUDA(cudaEventCreate(&t->ev2));
   TT_CUDA(cudaMalloc(&t->ctl, sizeof(tt::SweepCtl)));
   TT_CUDA(cudaMallocHost(&t->h_ctl, sizeof(tt::SweepCtl)));
   TT_CUDA(cudaMalloc(&t->d_small, 16 * 8));
@@ -470,6 +527,10 @@ int32_t tt_create(int32_t device, tt_table** out) {
 int32_t tt_destroy(tt_table* t) {
   if (!t) return TT_OK;
   {
+    std::lock_guard<std::mutex> lk(t->mu);
+    t->core->alive = false;
+  }
+  {
     DeviceGuard g(t->device);
     cudaStreamSynchronize(t->stream);
     free_columns(t);
@@ -480,6 +541,7 @@ int32_t tt_destroy(tt_table* t) {
     cudaFree(t->d_query);
     cudaEventDestroy(t->ev0);
     cudaEventDestroy(t->ev1);
+    cudaEventDestroy(t->ev2);
     cudaStreamDestroy(t->stream);
   }
   delete t;
@@ -740,14 +802,14 @@ int32_t tt_result_count(const tt_result* r, int64_t* n) {
 
 int32_t tt_result_rows(tt_result* r, uint32_t* out) {
   if (!r || (r->n && !out)) return fail(TT_ERR_ARG, "null argument");
-  DeviceGuard g(r->t->device);
+  DeviceGuard g(r->core->device);
   if (r->n) TT_CUDA(cudaMemcpy(out, r->d_rows, r->n * 4, cudaMemcpyDeviceToHost));
   return TT_OK;
 }
 
 int32_t tt_result_ids(tt_result* r, uint8_t* out16) {
   if (!r || (r->n && !out16)) return fail(TT_ERR_ARG, "null argument");
-  DeviceGuard g(r->t->device);
+  DeviceGuard g(r->core->device);
   if (r->n) TT_CUDA(cudaMemcpy(out16, r->d_ids, r->n * 16, cudaMemcpyDeviceToHost));
   return TT_OK;
 }
@@ -755,6 +817,7 @@ int32_t tt_result_ids(tt_result* r, uint8_t* out16) {
 int32_t tt_result_field(tt_result* r, int32_t field, void* out) {
   if (!r || (r->n && !out)) return fail(TT_ERR_ARG, "null argument");
   if (r->n == 0) return TT_OK;
+  if (!r->core->alive) return fail(TT_ERR_STATE, "the table of this result was destroyed");
   tt_table* t = r->t;
   std::lock_guard<std::mutex> lk(t->mu);
   DeviceGuard g(t->device);
@@ -792,13 +855,14 @@ int32_t tt_result_field(tt_result* r, int32_t field, void* out) {
 
 int32_t tt_result_free(tt_result* r) {
   if (!r) return TT_OK;
-  DeviceGuard g(r->t->device);
+  DeviceGuard g(r->core->device);
   result_release(r);
   return TT_OK;
 }
 
 int32_t tt_result_digest(tt_result* r, uint64_t* xor_id_hi, uint64_t* xor_id_lo, uint64_t* sum_rows) {
   if (!r) return fail(TT_ERR_ARG, "null argument");
+  if (!r->core->alive) return fail(TT_ERR_STATE, "the table of this result was destroyed");
   tt_table* t = r->t;
   std::lock_guard<std::mutex> lk(t->mu);
   DeviceGuard g(t->device);

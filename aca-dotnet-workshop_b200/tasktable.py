@@ -106,6 +106,8 @@ class SweepStats(C.Structure):
         ("resume_row", C.c_int64),
         ("kernel_ms", C.c_float),
         ("launches", C.c_int32),
+        ("sweep_ms", C.c_float),
+        ("gather_ms", C.c_float),
     ]
 
 
@@ -238,7 +240,9 @@ class TaskTable:
 
     # -- filling ---------------------------------------------------------------------------
     def generate(self, cfg, first_row, n_rows):
-        _check(lib().tt_generate(self._h, C.byref(cfg), first_row, n_rows))
+        if C.sizeof(cfg) != C.sizeof(SynthCfg):
+            raise TypeError("cfg must have the layout of tt_synth_cfg")
+        _check(lib().tt_generate(self._h, C.cast(C.byref(cfg), C.POINTER(SynthCfg)), first_row, n_rows))
         return self
 
     def load_soa(self, task_id, created_raw, due_raw, completed, overdue, creator_ref, creators):

@@ -226,7 +226,7 @@ def run_b200(args):
         reset()
         step()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    kernel_ms, hits, launches = [], 0, 0
+    kernel_ms, sweep_ms, gather_ms, hits, launches = [], [], [], 0, 0
     barrier()
     with ClockSampler(local) as clocks:
         for i in range(args.steps):
@@ -236,6 +236,8 @@ def run_b200(args):
             st, out = step()
             ev[i][1].record(stream)
             kernel_ms.append(st.kernel_ms)
+            sweep_ms.append(st.sweep_ms)
+            gather_ms.append(st.gather_ms)
             hits = st.n_listed
             launches += st.launches
         barrier()
@@ -283,9 +285,14 @@ def run_b200(args):
 
     if rank == 0:
         peak, peak_src = peaks()
-        kms = sorted(kernel_ms)[len(kernel_ms) // 2]
+        med = lambda xs: sorted(xs)[len(xs) // 2]
+        kms, sms, gms = med(kernel_ms), med(sweep_ms), med(gather_ms)
         alg_bytes = n_rows * BYTES_PER_TASK + hits * BYTES_PER_HIT
         achieved = alg_bytes / (kms * 1e-3) / 1e9
+        # the two kernels on their own bytes: K1 reads 4.25 B/task and writes 4 B/hit,
+        # K5a reads 4 + 16 B/hit and writes 16 B/hit
+        sweep_gbs = (n_rows * BYTES_PER_TASK + hits * 4.0) / (sms * 1e-3) / 1e9
+        gather_gbs = hits * 36.0 / (gms * 1e-3) / 1e9 if gms > 0 else None
         traffic = None
         tpath = os.path.join(ROOT, "profiles", "sweep_traffic.json")
         if os.path.exists(tpath):
@@ -307,8 +314,11 @@ def run_b200(args):
                 "reset": "overdue plane restored between steps outside the timed region (per-step CUDA events summed)",
             },
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": traffic, "kernel": "tt::sweep_kernel<true,true>", "kernel_ms": kms,
-                         "algorithmic_bytes": alg_bytes, "peak_source": peak_src},
+                         "traffic": traffic, "kernel": "tt::sweep_kernel<true,true> + tt::gather_hit_ids_kernel",
+                         "kernel_ms": kms, "algorithmic_bytes": alg_bytes, "peak_source": peak_src,
+                         "sweep_kernel": {"ms": sms, "achieved": sweep_gbs, "frac": sweep_gbs / peak},
+                         "gather_kernel": {"ms": gms, "achieved": gather_gbs,
+                                           "frac": (gather_gbs / peak) if gather_gbs else None}},
             "gpu_launches": launches,
             "clocks": clocks.summary(),
         }

@@ -149,21 +149,26 @@ int32_t tt_count_flags(tt_table* t, int64_t* n_completed, int64_t* n_overdue);
  * compare with the streaming oracle without moving 25 M ids to the host. */
 int32_t tt_result_digest(tt_result* r, uint64_t* xor_id_hi, uint64_t* xor_id_lo, uint64_t* sum_rows);
 
-/* ---- device-resident form of the sweep (no allocation, no host copy of the hits) ---------
- * Same kernel as tt_sweep, writing into caller-owned DEVICE buffers on a caller stream
+/* ---- device-resident form of the sweep (no host copy of the hits) ------------------------
+ * Same kernels as tt_sweep, writing into caller-owned DEVICE buffers on a caller stream
  * (cudaStream_t passed as void*; NULL = the table's own stream).  d_rows: uint32[cap],
- * d_ids: 16*cap bytes (may be NULL to skip the TaskId gather).  h_stats (host memory,
- * filled when the call returns; the call synchronises the stream).  If the hits do not fit
- * in cap the call returns TT_ERR_CAPACITY: rows before stats->resume_row were processed
- * completely (listed and, in a marking sweep, marked); call again with first_row =
- * stats->resume_row to continue. */
+ * d_ids: 16*cap bytes (may be NULL to skip the TaskId gather); d_rows == NULL counts only.
+ * h_stats is host memory, filled when the call returns (the call synchronises the stream).
+ * The table keeps an internal scratch list of `cap` row numbers; it is (re)allocated only when
+ * a call asks for a larger cap than any call before it.
+ * If the hits do not fit in cap the call returns TT_ERR_CAPACITY with n_listed = the number
+ * of hits there are and n_stored = how many were written (a row-ordered subset).  A marking
+ * sweep has marked exactly the stored ones: call again (they no longer match) to get the
+ * rest.  A listing sweep changed nothing: call again with cap >= n_listed. */
 typedef struct tt_sweep_stats {
   int64_t n_listed;   /* hits in [first_row, n): what GetYesterdaysDueTasks returns            */
   int64_t n_stored;   /* hits actually written to d_rows / d_ids                               */
   int64_t n_marked;   /* rows whose IsOverDue was set                                          */
-  int64_t resume_row; /* == row count when complete                                            */
-  float kernel_ms;    /* CUDA-event time of the sweep kernel on its stream                      */
+  int64_t resume_row; /* row count when complete, else first_row                               */
+  float kernel_ms;    /* CUDA-event time of this call's kernels on their stream (sweep + gather) */
   int32_t launches;   /* kernels launched by this call                                          */
+  float sweep_ms;     /* K1: predicate + compaction + flag write                                */
+  float gather_ms;    /* K2 + K3: row order and TaskId gather for the listed rows               */
 } tt_sweep_stats;
 
 #define TT_SWEEP_MARK 1     /* apply the cron predicate and set IsOverDue (the fused tick)      */

@@ -30,7 +30,7 @@ def test_library_exports_every_declared_symbol():
 
 def test_struct_layouts_match_the_header():
     assert C.sizeof(tt.SynthCfg) == 56
-    assert C.sizeof(tt.SweepStats) == 40
+    assert C.sizeof(tt.SweepStats) == 48
     assert C.sizeof(tt.SoaView) == 80
     assert C.sizeof(tt.DeviceView) == 72
 

@@ -187,26 +187,35 @@ def test_device_sweep_capacity_and_resume(oracle):
     ot.add_synth(cfg, 0, n)
     _, listed, _ = ot.cron_job(tt.MODE_STORE)
     want = np.sort(listed)
+    ids_all, _, _ = ot.export()
     table = tt.TaskTable(0).generate(cfg, 0, n)
     cap = want.size // 3 + 5
     rows = torch.zeros(want.size + 16, dtype=torch.int32, device="cuda")
     ids = torch.zeros((want.size + 16, 16), dtype=torch.uint8, device="cuda")
-    got, first, passes = 0, 0, 0
+    # a listing sweep that does not fit changes nothing and reports the size it needs
+    st, rc = table.sweep_device(tt.MODE_STORE, tt.SWEEP_LIST_ONLY, rows.data_ptr(), ids.data_ptr(), cap,
+                                allow_capacity=True)
+    assert rc == tt.TT_ERR_CAPACITY and st.n_listed == want.size and 0 < st.n_stored <= cap and st.n_marked == 0
+    part = rows[: st.n_stored].cpu().numpy().view(np.uint32)
+    assert (part[:-1] < part[1:]).all() and np.isin(part, want).all()  # a row-ordered subset
+    assert table.count_flags()[1] == int(ot.flags()[1].sum()) - want.size  # nothing marked yet
+    # a marking sweep that does not fit marks what it stored; calling again yields the rest
+    got, passes = 0, 0
     while True:
         st, rc = table.sweep_device(tt.MODE_STORE, tt.SWEEP_MARK, rows.data_ptr() + 4 * got, ids.data_ptr() + 16 * got,
-                                    cap, first_row=first, allow_capacity=True)
+                                    cap, allow_capacity=True)
         passes += 1
+        run = rows[got: got + st.n_stored].cpu().numpy().view(np.uint32)
+        assert (run[:-1] < run[1:]).all()
+        assert (ids[got: got + st.n_stored].cpu().numpy() == ids_all[run]).all()
         got += st.n_stored
         assert st.n_marked == st.n_stored
         if rc == tt.TT_OK:
             assert st.resume_row == n
             break
-        assert rc == tt.TT_ERR_CAPACITY and st.resume_row % 8192 == 0 and st.resume_row > first
-        first = st.resume_row
+        assert rc == tt.TT_ERR_CAPACITY and st.n_listed > st.n_stored
     assert passes >= 3 and got == want.size
-    assert (rows[:got].cpu().numpy().view(np.uint32) == want).all()
-    ids_all, _, _ = ot.export()
-    assert (ids[:got].cpu().numpy() == ids_all[want]).all()
+    assert (np.sort(rows[:got].cpu().numpy().view(np.uint32)) == want).all()
     _, o = ot.flags()
     assert (table.flags_bytes()[1] == o).all()
     # count-only form: no output buffers
@@ -215,6 +224,18 @@ def test_device_sweep_capacity_and_resume(oracle):
     assert st.n_listed == want.size and st.n_stored == 0
     table.close()
     table2.close()
+
+
+@pytest.mark.parametrize("mode", MODES)
+def test_owned_result_grows_when_the_first_guess_is_too_small(oracle, mode):
+    """> n/16 hits: tt_sweep has to regrow its result (and, after marking, merge two runs)"""
+    n = 2_000_000
+    cfg = oracle.default_cfg(31, n, n_creators=10, ppm_due_yesterday=400_000, ppm_completed=100_000)
+    ot = oracle.OracleTable()
+    ot.add_synth(cfg, 0, n)
+    table = tt.TaskTable(0).generate(cfg, 0, n)
+    check_sweep(oracle, ot, table, mode)
+    table.close()
 
 
 def test_argument_errors():
