@@ -34,6 +34,69 @@ def shard_rows(n_total, world, rank):
     return (n_total * rank) // world, (n_total * (rank + 1)) // world
 
 
+class HitExchange:
+    """Persistent buffers for the cross-shard exchange, so the timed path allocates nothing.
+
+    After a shard's sweep, `run` all-gathers the per-shard hit counts (8 bytes per rank) and
+    gathers the hit row numbers (uint32, shard-local) and optionally the TaskIds on rank `dst`
+    with grouped send/recv at the exclusive-scan offsets of the counts (NCCL has no gather-v).
+    On `dst` the local hits are expected to be in `rows_all[:count]` / `ids_all[:count]` already
+    (rank dst's offset is 0 when dst == 0), so the sweep can write them in place.
+    """
+
+    def __init__(self, plan, cap_per_rank, device, with_ids=False, dst=0, group=None):
+        self.plan, self.cap, self.dst, self.group, self.with_ids = plan, cap_per_rank, dst, group, with_ids
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        n = cap_per_rank * (self.world if self.rank == dst else 1)
+        self.rows_all = torch.empty(n, dtype=torch.int32, device=device)
+        self.ids_all = torch.empty((n, 16), dtype=torch.uint8, device=device) if with_ids else None
+        self._mine = torch.zeros(1, dtype=torch.int64, device=device)
+        self._counts = torch.zeros(self.world, dtype=torch.int64, device=device)
+        self._host = torch.zeros(1, dtype=torch.int64)
+        if device.type == "cuda":
+            self._host = self._host.pin_memory()
+
+    def run(self, count):
+        """-> list of per-shard counts (every rank).  On dst, rows_all / ids_all hold all hits."""
+        if self.world == 1:
+            return [count]
+        assert self.dst == 0, "in-place layout assumes the root is rank 0"
+        self._host[0] = count
+        self._mine.copy_(self._host, non_blocking=True)
+        dist.all_gather_into_tensor(self._counts, self._mine, group=self.group)
+        counts = self._counts.tolist()
+        offs = [0]
+        for c in counts:
+            offs.append(offs[-1] + c)
+        ops = []
+        if self.rank == self.dst:
+            for r in range(self.world):
+                if r == self.dst or counts[r] == 0:
+                    continue
+                ops.append(dist.P2POp(dist.irecv, self.rows_all[offs[r]:offs[r + 1]], r, self.group))
+                if self.with_ids:
+                    ops.append(dist.P2POp(dist.irecv, self.ids_all[offs[r]:offs[r + 1]], r, self.group))
+        elif count > 0:
+            ops.append(dist.P2POp(dist.isend, self.rows_all[:count], self.dst, self.group))
+            if self.with_ids:
+                ops.append(dist.P2POp(dist.isend, self.ids_all[:count], self.dst, self.group))
+        if ops:
+            for w in dist.batch_isend_irecv(ops):
+                w.wait()
+        return counts
+
+    def global_rows(self, counts):
+        """dst only: global row numbers (int64, ascending) from the gathered shard-local ones."""
+        total = sum(counts)
+        glob = self.rows_all[:total].to(torch.int64) & 0xFFFFFFFF
+        off = 0
+        for r, c in enumerate(counts):
+            glob[off:off + c] += shard_rows(self.plan.n_total, self.world, r)[0]
+            off += c
+        return glob
+
+
 def exchange_hits(local_rows, count, plan, ids=None, dst=0, group=None):
     """Gathers every shard's hit list on rank `dst`.
 

@@ -200,11 +200,13 @@ def run_b200(args):
     pristine = torch.empty(nbytes, dtype=torch.uint8, device=dev)
     tt._check(tt.lib().tt_snapshot_flags(table._h, None, pristine.data_ptr()))
     cap = int(n_rows * 0.032) + 65536
-    d_rows = torch.empty(cap, dtype=torch.int32, device=dev)
-    d_ids = torch.empty((cap, 16), dtype=torch.uint8, device=dev)
+    with_ids = args.exchange == "ids"
+    # the exchange owns the output buffers: on rank 0 the local hits land at offset 0 in place
+    ex = pkg.HitExchange(plan, cap, dev, with_ids=True)
+    d_rows, d_ids = ex.rows_all, ex.ids_all
+    ex.with_ids = with_ids
     stream = torch.cuda.Stream(device=dev)  # non-default: its handle is what the C ABI launches on
     torch.cuda.set_stream(stream)
-    with_ids = args.exchange == "ids"
 
     def reset():
         tt._check(tt.lib().tt_restore_flags(table._h, None, pristine.data_ptr()))
@@ -214,7 +216,7 @@ def run_b200(args):
                                    stream=stream.cuda_stream)
         out = None
         if world > 1 and args.exchange != "none":
-            out = pkg.exchange_hits(d_rows, st.n_stored, plan, ids=d_ids if with_ids else None)
+            out = ex.run(st.n_stored)
         return st, out
 
     def barrier():
@@ -287,17 +289,23 @@ def run_b200(args):
         peak, peak_src = peaks()
         med = lambda xs: sorted(xs)[len(xs) // 2]
         kms, sms, gms = med(kernel_ms), med(sweep_ms), med(gather_ms)
-        alg_bytes = n_rows * BYTES_PER_TASK + hits * BYTES_PER_HIT
-        achieved = alg_bytes / (kms * 1e-3) / 1e9
-        # the two kernels on their own bytes: K1 reads 4.25 B/task and writes 4 B/hit,
-        # K5a reads 4 + 16 B/hit and writes 16 B/hit
-        sweep_gbs = (n_rows * BYTES_PER_TASK + hits * 4.0) / (sms * 1e-3) / 1e9
-        gather_gbs = hits * 36.0 / (gms * 1e-3) / 1e9 if gms > 0 else None
+        # Dominant kernel = K1 sweep_kernel: it reads 4.25 B/task and writes one u32 row per hit.
+        # K2+K3 (row order + TaskId gather) read 4 B + 16 B and write 4 B + 16 B per hit.
+        # The whole step is SURVEY.md 8(d)'s figure: 4.25 B/task + 36 B/hit (+ the 8 B/hit of the
+        # intermediate list, which is not counted).
+        sweep_bytes = n_rows * BYTES_PER_TASK + hits * 4.0
+        place_bytes = hits * 40.0
+        step_bytes = n_rows * BYTES_PER_TASK + hits * BYTES_PER_HIT
+        achieved = sweep_bytes / (sms * 1e-3) / 1e9
+        step_gbs = step_bytes / (kms * 1e-3) / 1e9
+        place_gbs = place_bytes / (gms * 1e-3) / 1e9 if gms > 0 else None
         traffic = None
         tpath = os.path.join(ROOT, "profiles", "sweep_traffic.json")
         if os.path.exists(tpath):
             try:
-                traffic = json.load(open(tpath)).get("dram_bytes_per_launch")
+                tj = json.load(open(tpath))
+                if tj.get("rows") == n_rows:
+                    traffic = tj.get("dram_bytes_per_launch")
             except Exception:
                 pass
         line = {
@@ -314,11 +322,15 @@ def run_b200(args):
                 "reset": "overdue plane restored between steps outside the timed region (per-step CUDA events summed)",
             },
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": traffic, "kernel": "tt::sweep_kernel<true,true> + tt::gather_hit_ids_kernel",
-                         "kernel_ms": kms, "algorithmic_bytes": alg_bytes, "peak_source": peak_src,
-                         "sweep_kernel": {"ms": sms, "achieved": sweep_gbs, "frac": sweep_gbs / peak},
-                         "gather_kernel": {"ms": gms, "achieved": gather_gbs,
-                                           "frac": (gather_gbs / peak) if gather_gbs else None}},
+                         "traffic": traffic, "kernel": "tt::sweep_kernel<true,true,256,4> (K1, dominant)",
+                         "kernel_ms": sms, "algorithmic_bytes": sweep_bytes,
+                         "bytes_per_unit": "4.25 B/task + 4 B/hit", "peak_source": peak_src,
+                         "step": {"kernels": "K1 sweep + K2 tile_offsets + K3 place_hits", "ms": kms,
+                                  "algorithmic_bytes": step_bytes, "bytes_per_unit": "4.25 B/task + 36 B/hit",
+                                  "achieved": step_gbs, "frac": step_gbs / peak},
+                         "place_kernels": {"ms": gms, "achieved": place_gbs,
+                                           "frac": (place_gbs / peak) if place_gbs else None,
+                                           "note": "random 16 B TaskId gathers cost 64 B of DRAM each"}},
             "gpu_launches": launches,
             "clocks": clocks.summary(),
         }

@@ -1,0 +1,64 @@
+"""Run under torchrun: every rank sweeps its TaskId-range shard on its own GPU, the hit counts
+and hit ids are exchanged over NCCL, and rank 0 checks the global answer against the streaming
+oracle (count, XOR of TaskIds, sum of global rows, ascending order)."""
+import importlib
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+pkg = importlib.import_module("aca-dotnet-workshop_b200")
+tt = pkg.tasktable
+
+
+def main():
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    n_total = int(sys.argv[1]) if len(sys.argv) > 1 else 64_000_000
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    plan = pkg.ShardPlan(n_total, world, rank)
+    cfg = pkg.default_cfg(0x5EED0002, n_total)
+    table = pkg.TaskTable(local).generate(cfg, plan.first_row, plan.n_rows)
+    cap = int(plan.n_rows * 0.032) + 65536
+    d_rows = torch.empty(cap, dtype=torch.int32, device=dev)
+    d_ids = torch.empty((cap, 16), dtype=torch.uint8, device=dev)
+    stream = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(stream)
+    st, _ = table.sweep_device(tt.MODE_STORE, tt.SWEEP_MARK, d_rows.data_ptr(), d_ids.data_ptr(), cap,
+                               stream=stream.cuda_stream)
+    counts, glob, gids = pkg.exchange_hits(d_rows, st.n_stored, plan, ids=d_ids)
+    ok = True
+    if rank == 0:
+        from oracle import oracle as orc
+
+        want = orc.stream_sweep(orc.default_cfg(0x5EED0002, n_total), 0, n_total, orc.MODE_STORE)
+        g = glob.cpu().numpy()
+        ids = gids.cpu().numpy()
+        hi = int(np.bitwise_xor.reduce(np.ascontiguousarray(ids[:, :8]).view(">u8").ravel().astype(np.uint64)))
+        lo = int(np.bitwise_xor.reduce(np.ascontiguousarray(ids[:, 8:]).view(">u8").ravel().astype(np.uint64)))
+        ok = (sum(counts) == want.n_listed == g.size and (g[:-1] < g[1:]).all()
+              and int(g.astype(np.uint64).sum() & np.uint64(2**64 - 1)) == want.sum_rows
+              and (hi, lo) == (want.xor_id_hi, want.xor_id_lo))
+        print("multigpu_check", "OK" if ok else "MISMATCH", "world", world, "counts", counts, "listed", want.n_listed)
+    flag = torch.tensor([1 if ok else 0], device=dev)
+    dist.broadcast(flag, 0)
+    # per-shard flag planes against the oracle's popcount for that shard
+    from oracle import oracle as orc
+
+    mine = orc.stream_sweep(orc.default_cfg(0x5EED0002, n_total), plan.first_row, plan.n_rows, orc.MODE_STORE)
+    good = table.count_flags() == (mine.completed, mine.overdue_after) and st.n_listed == mine.n_listed
+    allgood = torch.tensor([1 if good else 0], device=dev)
+    dist.all_reduce(allgood, op=dist.ReduceOp.MIN)
+    table.close()
+    dist.barrier()
+    dist.destroy_process_group()
+    sys.exit(0 if flag.item() == 1 and allgood.item() == 1 else 1)
+
+
+if __name__ == "__main__":
+    main()

@@ -61,7 +61,17 @@ def _worker(rank, world, port, n_total, with_ids, q):
     ids_t = torch.zeros((local.size + pad, 16), dtype=torch.uint8)
     ids_t[: local.size] = torch.from_numpy(ids_all[local])
     counts, glob, gids = pkg.exchange_hits(rows_t, int(local.size), plan, ids=ids_t if with_ids else None)
+    # the persistent-buffer form used by bench.py must give the same answer
+    ex = pkg.HitExchange(plan, local.size + pad + 4000, torch.device("cpu"), with_ids=with_ids)
+    ex.rows_all[: local.size] = rows_t[: local.size]
+    if with_ids:
+        ex.ids_all[: local.size] = ids_t[: local.size]
+    counts2 = ex.run(int(local.size))
+    assert counts2 == counts
     if rank == 0:
+        assert (ex.global_rows(counts2) == glob).all()
+        if with_ids:
+            assert (ex.ids_all[: sum(counts2)] == gids).all()
         q.put((counts, glob.numpy(), gids.numpy() if gids is not None else None))
     else:
         assert glob is None
