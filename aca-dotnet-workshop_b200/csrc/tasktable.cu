@@ -939,3 +939,145 @@ int32_t tt_get_device_view(tt_table* t, tt_device_view* out) {
 }
 
 }  // extern "C"
+
+// ---- the sweep with its working memory in a fixed device array ---------------------------------
+//
+// For callers that cannot allocate (see include/tasktable.h).  Everything tt_sweep_device keeps
+// in table-owned, growable buffers lives here in one file-scope array:
+//   [0, 256)      SweepCtl
+//   [256, 512)    group sums (TT_STATIC_MAX_ROWS / 8192 / 1024 = 2 words used)
+//   [512, ...)    tile_slot, tile_count, tile_first: 3 x 2048 words
+//   [25088, ...)  intermediate hit list: TT_STATIC_MAX_HITS words
+// In host code the array's name is only a handle for cudaGetSymbolAddress — it is not a device
+// address — so the address is looked up once per device and handed to the kernels as a pointer.
+namespace {
+
+constexpr size_t kStaticTiles = TT_STATIC_MAX_ROWS / TT_TILE_ROWS;
+constexpr size_t kStaticGroupOff = 256;
+constexpr size_t kStaticTileOff = 512;
+constexpr size_t kStaticListOff = kStaticTileOff + 3 * kStaticTiles * 4;
+constexpr size_t kStaticBytes = kStaticListOff + (size_t)TT_STATIC_MAX_HITS * 4;
+static_assert(kStaticListOff % 256 == 0, "hit list must stay 256-byte aligned");
+
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticBytes];
+
+// Device code may name the array directly.  Puts the control block and the group sums back
+// into their start state; the per-tile words and the list are fully rewritten by every sweep.
+__global__ void static_scratch_reset_kernel() {
+  tt::SweepCtl* ctl = reinterpret_cast<tt::SweepCtl*>(g_static_scratch);
+  uint32_t* groups = reinterpret_cast<uint32_t*>(g_static_scratch + kStaticGroupOff);
+  if (threadIdx.x == 0) {
+    ctl->tile_counter = 0;
+    ctl->pad = 0;
+    ctl->cursor = 0;
+    ctl->stored = ~0ull;
+  }
+  if (threadIdx.x < (256 / 4)) groups[threadIdx.x] = 0;
+}
+
+constexpr int kMaxDevices = 64;
+std::mutex g_static_mu;
+unsigned char* g_static_addr[kMaxDevices] = {};
+int g_static_sms[kMaxDevices] = {};
+
+}  // namespace
+
+extern "C" int32_t tt_sweep_static(const tt_device_view* cols, int32_t mode, int32_t flags, int64_t today_local_ticks,
+                                   int64_t run_at_utc_ticks, uint32_t* d_rows, void* d_ids, int64_t cap,
+                                   tt_sweep_stats* h_stats, void* stream_) {
+  if (!cols || !h_stats) return fail(TT_ERR_ARG, "null argument");
+  memset(h_stats, 0, sizeof *h_stats);
+  if (mode != TT_MODE_FAKE && mode != TT_MODE_STORE) return fail(TT_ERR_ARG, "mode must be TT_MODE_FAKE or TT_MODE_STORE");
+  uint32_t yesterday = 0;
+  int32_t rc = check_clock(today_local_ticks, &yesterday);
+  if (rc) return rc;
+  if (cols->n < 0 || cols->n_padded < cols->n || cols->n_padded % TT_TILE_ROWS != 0)
+    return fail(TT_ERR_ARG, "columns must be padded to a multiple of %d rows", TT_TILE_ROWS);
+  if (cols->n_padded > TT_STATIC_MAX_ROWS)
+    return fail(TT_ERR_ARG, "tt_sweep_static handles at most %d rows (got %lld); use tt_sweep_device", TT_STATIC_MAX_ROWS,
+                (long long)cols->n_padded);
+  if (cap < 0 || cap > TT_STATIC_MAX_HITS)
+    return fail(TT_ERR_ARG, "tt_sweep_static handles at most %d hits (cap %lld); use tt_sweep_device", TT_STATIC_MAX_HITS,
+                (long long)cap);
+  if (cols->device < 0 || cols->device >= kMaxDevices) return fail(TT_ERR_ARG, "device %d out of range", cols->device);
+  if (cols->n > 0 && (!cols->due_code || !cols->completed || !cols->overdue || (d_ids && !cols->task_id)))
+    return fail(TT_ERR_ARG, "null column");
+  if (cols->n == 0) {
+    h_stats->resume_row = 0;
+    return TT_OK;
+  }
+  std::lock_guard<std::mutex> lk(g_static_mu);  // one sweep at a time owns the fixed array
+  DeviceGuard g(cols->device);
+  const int dev = cols->device;
+  if (!g_static_addr[dev]) {
+    // set-up, once per device, with that device current
+    void* addr = nullptr;
+    TT_CUDA(cudaGetSymbolAddress(&addr, g_static_scratch));
+    int sms = 0;
+    TT_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    g_static_sms[dev] = sms;
+    g_static_addr[dev] = static_cast<unsigned char*>(addr);
+  }
+  unsigned char* base = g_static_addr[dev];
+  cudaStream_t stream = (cudaStream_t)stream_;
+  const bool mark = (flags & TT_SWEEP_MARK) != 0;
+  const bool survive = run_at_utc_ticks / TT_TICKS_PER_DAY > (int64_t)yesterday;
+  const bool listing = d_rows != nullptr;
+  const uint32_t num_tiles = (uint32_t)(cols->n_padded / TT_TILE_ROWS);
+
+  tt::SweepParams p;
+  p.due_code = static_cast<const uint32_t*>(cols->due_code);
+  p.completed = static_cast<const uint32_t*>(cols->completed);
+  p.overdue = static_cast<uint32_t*>(cols->overdue);
+  p.list = listing ? reinterpret_cast<uint32_t*>(base + kStaticListOff) : nullptr;
+  p.tile_slot = reinterpret_cast<uint32_t*>(base + kStaticTileOff);
+  p.tile_count = p.tile_slot + kStaticTiles;
+  uint32_t* tile_first = p.tile_slot + 2 * kStaticTiles;
+  p.group_sum = reinterpret_cast<uint32_t*>(base + kStaticGroupOff);
+  p.ctl = reinterpret_cast<tt::SweepCtl*>(base);
+  p.cap = listing ? (unsigned long long)cap : ~0ull;
+  p.first_tile = 0;
+  p.num_tiles = num_tiles;
+  p.mask = mode == TT_MODE_FAKE ? TT_MASK_FAKE : TT_MASK_STORE;
+  p.yesterday = yesterday;
+  p.mark_enable = (mark && survive && mode == TT_MODE_STORE) ? 1u : 0u;
+
+  static_scratch_reset_kernel<<<1, 64, 0, stream>>>();
+  TT_CUDA(cudaGetLastError());
+  const unsigned grid = (unsigned)std::min<int64_t>(num_tiles, (int64_t)g_static_sms[dev] * tt::kSweepCtasPerSm);
+  if (mode == TT_MODE_STORE) {
+    if (p.mark_enable)
+      tt::sweep_kernel<true, true, tt::kSweepThreads, tt::kSweepCtasPerSm><<<grid, tt::kSweepThreads, 0, stream>>>(p);
+    else
+      tt::sweep_kernel<true, false, tt::kSweepThreads, tt::kSweepCtasPerSm><<<grid, tt::kSweepThreads, 0, stream>>>(p);
+  } else {
+    tt::sweep_kernel<false, false, tt::kSweepThreads, tt::kSweepCtasPerSm><<<grid, tt::kSweepThreads, 0, stream>>>(p);
+  }
+  TT_CUDA(cudaGetLastError());
+  h_stats->launches = 2;
+  if (listing) {
+    const unsigned n_groups = (num_tiles + tt::kTilesPerGroup - 1) / tt::kTilesPerGroup;
+    tt::tile_offsets_kernel<<<n_groups, tt::kTilesPerGroup, 0, stream>>>(p.tile_count, p.group_sum, num_tiles, tile_first);
+    TT_CUDA(cudaGetLastError());
+    const int64_t per_cta = (int64_t)tt::kPlaceThreads * tt::kPlaceUnroll;
+    const unsigned pgrid = (unsigned)std::max<int64_t>(
+        1, std::min<int64_t>((cap + per_cta - 1) / per_cta, (int64_t)g_static_sms[dev] * 8));
+    tt::place_hits_kernel<TT_TILE_ROWS><<<pgrid, tt::kPlaceThreads, 0, stream>>>(
+        p.ctl, p.list, p.tile_slot, tile_first, 0, static_cast<const uint4*>(cols->task_id), d_rows,
+        static_cast<uint4*>(d_ids));
+    TT_CUDA(cudaGetLastError());
+    h_stats->launches = 4;
+  }
+  tt::SweepCtl done;  // read back into the caller's stack: no pinned buffer is created for it
+  TT_CUDA(cudaMemcpyAsync(&done, base, sizeof done, cudaMemcpyDeviceToHost, stream));
+  TT_CUDA(cudaStreamSynchronize(stream));
+  h_stats->n_listed = (int64_t)done.cursor;
+  const bool complete = done.stored == ~0ull;
+  h_stats->n_stored = listing ? (complete ? h_stats->n_listed : (int64_t)done.stored) : 0;
+  h_stats->resume_row = complete ? cols->n : 0;
+  h_stats->n_marked = p.mark_enable ? (listing ? h_stats->n_stored : h_stats->n_listed) : 0;
+  if (!complete)
+    return fail(TT_ERR_CAPACITY, "%lld hits do not fit in %lld (%lld stored%s)", (long long)h_stats->n_listed,
+                (long long)cap, (long long)h_stats->n_stored, h_stats->n_marked ? " and marked; call again for the rest" : "");
+  return TT_OK;
+}

@@ -35,6 +35,8 @@ TICKS_PER_DAY = 864000000000
 DEFAULT_TODAY = 639295200000000000  # 2026-11-06T00:00:00
 DEFAULT_RUN_AT = DEFAULT_TODAY + 5 * 60 * 10_000_000
 TILE_ROWS = 8192
+STATIC_MAX_ROWS = 16777216  # TT_STATIC_MAX_ROWS
+STATIC_MAX_HITS = 1048576   # TT_STATIC_MAX_HITS
 
 # every symbol include/tasktable.h declares (tests check the library exports all of them)
 EXPORTS = [
@@ -42,7 +44,7 @@ EXPORTS = [
     "tt_get_yesterdays_due", "tt_mark_overdue", "tt_sweep", "tt_get_by_creator",
     "tt_result_count", "tt_result_rows", "tt_result_ids", "tt_result_field", "tt_result_free",
     "tt_snapshot_flags", "tt_restore_flags", "tt_count_flags", "tt_result_digest",
-    "tt_sweep_device", "tt_get_device_view",
+    "tt_sweep_device", "tt_get_device_view", "tt_sweep_static",
 ]
 
 
@@ -166,6 +168,7 @@ def lib():
     L.tt_result_digest.argtypes = [vp, P(u64), P(u64), P(u64)]
     L.tt_sweep_device.argtypes = [vp, i32, i32, i64, i64, i64, vp, vp, i64, P(SweepStats), vp]
     L.tt_get_device_view.argtypes = [vp, P(DeviceView)]
+    L.tt_sweep_static.argtypes = [P(DeviceView), i32, i32, i64, i64, vp, vp, i64, P(SweepStats), vp]
     for name in EXPORTS:
         if name != "tt_last_error":
             getattr(L, name).restype = i32
@@ -300,6 +303,19 @@ class TaskTable:
         st = SweepStats()
         rc = lib().tt_sweep_device(self._h, mode, flags, today, run_at, first_row, d_rows, d_ids, cap, C.byref(st),
                                    stream)
+        _check(rc, allow=(TT_ERR_CAPACITY,) if allow_capacity else ())
+        return st, rc
+
+    def sweep_static(self, mode, flags, d_rows, d_ids, cap, today=DEFAULT_TODAY, run_at=DEFAULT_RUN_AT, stream=None,
+                     allow_capacity=False):
+        """tt_sweep_static: the sweep for callers that cannot allocate device memory.  It runs the
+        same kernels as sweep_device over this table's columns, but keeps all working memory in
+        the library's fixed ~4 MB device array, so the table must have at most STATIC_MAX_ROWS
+        rows and cap at most STATIC_MAX_HITS (larger sizes raise TaskTableError, TT_ERR_ARG).
+        Returns (SweepStats, rc) like sweep_device; the timing fields stay 0."""
+        view = self.device_view()
+        st = SweepStats()
+        rc = lib().tt_sweep_static(C.byref(view), mode, flags, today, run_at, d_rows, d_ids, cap, C.byref(st), stream)
         _check(rc, allow=(TT_ERR_CAPACITY,) if allow_capacity else ())
         return st, rc
 

@@ -193,6 +193,39 @@ typedef struct tt_device_view {
 } tt_device_view;
 int32_t tt_get_device_view(tt_table* t, tt_device_view* out);
 
+/* ---- sweep without any allocation ----------------------------------------------------------
+ * This entry point has no counterpart in the reference.  It exists for hosts that cannot let a
+ * library allocate device memory while they are serving: a process that handed the whole GPU to
+ * its own memory pool at start-up (cudaMalloc would simply fail), or a request path that must not
+ * run into the device-wide synchronisation and the unpredictable latency of cudaMalloc/cudaFree.
+ * tt_sweep_device keeps its working memory in the table and grows it on demand; this variant
+ * runs the same kernels with all of that working memory (control block, per-tile words and the
+ * intermediate hit list) in one fixed array that is part of the library image — about 4 MB that
+ * every GPU which loads the library holds until the process exits.  It calls no cudaMalloc,
+ * cudaFree, event/stream creation or any other allocating routine.
+ *
+ * The price is a size limit: cols->n_padded <= TT_STATIC_MAX_ROWS and cap <= TT_STATIC_MAX_HITS,
+ * anything larger is refused with TT_ERR_ARG before a kernel is launched.
+ *
+ * cols   : the table's columns as device pointers (from tt_get_device_view, or the caller's own
+ *          arrays in the same layout: padded to a multiple of 8192 rows, padding rows with
+ *          due_code 0xFFFFFFFF and zero flag bits).  cols->device must own the memory.
+ * d_rows : uint32[cap] device memory, d_ids: 16*cap bytes or NULL; d_rows == NULL counts only.
+ * Results, error codes and the meaning of TT_ERR_CAPACITY are those of tt_sweep_device; the
+ * timing fields of h_stats stay 0 (timing would need events).
+ *
+ * The first call on each device looks up the device address of the fixed array; make that first
+ * call before any stream capture is started.  All calls share the array and it keeps whatever
+ * the previous call left in it; each call re-initialises the words that must start at zero, and
+ * calls from several threads are serialised inside the library.  Two calls that nevertheless
+ * overlap on the GPU (for example from two processes' worth of streams in one context created
+ * behind the library's back) would race on it. */
+#define TT_STATIC_MAX_ROWS 16777216 /* 2048 tiles of 8192 rows */
+#define TT_STATIC_MAX_HITS 1048576
+int32_t tt_sweep_static(const tt_device_view* cols, int32_t mode, int32_t flags, int64_t today_local_ticks,
+                        int64_t run_at_utc_ticks, uint32_t* d_rows, void* d_ids, int64_t cap,
+                        tt_sweep_stats* h_stats, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
