@@ -15,6 +15,7 @@
 #include <mutex>
 #include <new>
 #include <string>
+#include <unordered_map>
 #include <vector>
 
 #include "../../include/tasktable.h"
@@ -99,8 +100,24 @@ struct tt_table {
   // small device/pinned scratch for reductions and the creator filter
   unsigned long long* d_small = nullptr;  // 16 words
   unsigned long long* h_small = nullptr;
-  uint8_t* d_query = nullptr;  // creator-filter query bytes
+  uint8_t* d_query = nullptr;  // creator filter: the query set (hashes, offsets, strings, slot table)
   size_t d_query_cap = 0;
+  unsigned long long* d_pairs = nullptr;  // creator filter: unordered (query, row) matches (large results)
+  int64_t d_pairs_cap = 0;
+  uint32_t* d_lists = nullptr;            // creator filter: per-query match lists [queries][kListCap]
+  int64_t d_lists_queries = 0;
+  uint32_t* d_qcount = nullptr;  // per-query match counts (kMaxQueries words) + pinned mirror
+  uint32_t* h_qcount = nullptr;
+  tt_op_stats last_op = {};
+};
+
+// One device allocation, shared by the results that point into it (a batch of creator queries
+// returns one result per query over a single block).
+struct DeviceBlock {
+  void* p = nullptr;
+  ~DeviceBlock() {
+    if (p) cudaFree(p);
+  }
 };
 
 struct tt_result {
@@ -110,6 +127,7 @@ struct tt_result {
   int64_t cap = 0;
   uint32_t* d_rows = nullptr;
   uint4* d_ids = nullptr;
+  std::shared_ptr<DeviceBlock> block;
 };
 
 namespace {
@@ -411,24 +429,33 @@ int32_t result_alloc(tt_table* t, int64_t cap, tt_result** out) {
   r->t = t;
   r->core = t->core;
   r->cap = std::max<int64_t>(cap, 1);
-  cudaError_t e = cudaMalloc(&r->d_rows, r->cap * 4);
-  if (e == cudaSuccess) e = cudaMalloc(&r->d_ids, r->cap * 16);
+  r->block = std::make_shared<DeviceBlock>();
+  cudaError_t e = cudaMalloc(&r->block->p, (size_t)r->cap * 20);  // ids (16 B each) first, then rows
   if (e != cudaSuccess) {
     cudaGetLastError();
-    cudaFree(r->d_rows);
     delete r;
     return fail(TT_ERR_OOM, "result buffers for %lld hits: %s", (long long)cap, cudaGetErrorString(e));
   }
+  r->d_ids = static_cast<uint4*>(r->block->p);
+  r->d_rows = reinterpret_cast<uint32_t*>(static_cast<unsigned char*>(r->block->p) + (size_t)r->cap * 16);
   *out = r;
   return TT_OK;
 }
 
-void result_release(tt_result* r) {
-  if (!r) return;
-  cudaFree(r->d_rows);
-  cudaFree(r->d_ids);
-  delete r;
+// A result over [first, first + n) of another result's buffers (shares the allocation).
+tt_result* result_slice(const tt_result* whole, int64_t first, int64_t n) {
+  tt_result* r = new (std::nothrow) tt_result();
+  if (!r) return nullptr;
+  r->t = whole->t;
+  r->core = whole->core;
+  r->n = r->cap = n;
+  r->d_rows = whole->d_rows + first;
+  r->d_ids = whole->d_ids + first;
+  r->block = whole->block;
+  return r;
 }
+
+void result_release(tt_result* r) { delete r; }  // the block goes with its last result
 
 // Sweep into a library-owned result.  The first guess at the hit count is n/16; when it is too
 // small the result is regrown to the exact size and the sweep runs again: from scratch if the
@@ -520,6 +547,8 @@ int32_t tt_create(int32_t device, tt_table** out) {
   TT_CUDA(cudaMallocHost(&t->h_ctl, sizeof(tt::SweepCtl)));
   TT_CUDA(cudaMalloc(&t->d_small, 16 * 8));
   TT_CUDA(cudaMallocHost(&t->h_small, 16 * 8));
+  TT_CUDA(cudaMalloc(&t->d_qcount, tt::kMaxQueries * 4));
+  TT_CUDA(cudaMallocHost(&t->h_qcount, tt::kMaxQueries * 4));
   *out = t;
   return TT_OK;
 }
@@ -539,6 +568,10 @@ int32_t tt_destroy(tt_table* t) {
     cudaFree(t->d_small);
     cudaFreeHost(t->h_small);
     cudaFree(t->d_query);
+    cudaFree(t->d_pairs);
+    cudaFree(t->d_lists);
+    cudaFree(t->d_qcount);
+    cudaFreeHost(t->h_qcount);
     cudaEventDestroy(t->ev0);
     cudaEventDestroy(t->ev1);
     cudaEventDestroy(t->ev2);
@@ -741,54 +774,218 @@ int32_t tt_mark_overdue(tt_table* t, int32_t mode, const uint8_t* ids16, int64_t
   return TT_OK;
 }
 
-int32_t tt_get_by_creator(tt_table* t, const char* utf8, int32_t len, tt_result** out) {
-  if (!t || !out || len < 0 || (len > 0 && !utf8)) return fail(TT_ERR_ARG, "bad argument");
-  *out = nullptr;
+int32_t tt_get_by_creators(tt_table* t, const char* const* utf8, const int32_t* lens, int32_t nq, tt_result** out) {
+  if (!t || !out || !utf8 || !lens || nq < 1) return fail(TT_ERR_ARG, "bad argument");
+  if (nq > tt::kMaxQueries) return fail(TT_ERR_ARG, "at most %d creators per batch", tt::kMaxQueries);
+  for (int32_t i = 0; i < nq; ++i) {
+    out[i] = nullptr;
+    if (lens[i] < 0 || (lens[i] > 0 && !utf8[i])) return fail(TT_ERR_ARG, "bad query %d", i);
+  }
   std::lock_guard<std::mutex> lk(t->mu);
   DeviceGuard g(t->device);
-  if ((size_t)len > t->d_query_cap) {
+  t->last_op = tt_op_stats{};
+  t->last_op.queries = nq;
+
+  // ---- the query set, built on the host: distinct strings, their hashes and the slot table ----
+  std::vector<int32_t> uniq_of(nq);
+  std::vector<int32_t> first_of;  // distinct query -> index of its first occurrence
+  {
+    std::unordered_map<std::string, int32_t> seen;
+    for (int32_t i = 0; i < nq; ++i) {
+      std::string key(utf8[i] ? utf8[i] : "", (size_t)lens[i]);
+      auto it = seen.find(key);
+      if (it == seen.end()) {
+        it = seen.emplace(std::move(key), (int32_t)first_of.size()).first;
+        first_of.push_back(i);
+      }
+      uniq_of[i] = it->second;
+    }
+  }
+  const uint32_t nu = (uint32_t)first_of.size();
+  uint32_t slots = 1024;
+  while (slots < 16 * nu && slots < tt::kMaxSlots) slots <<= 1;
+  std::vector<uint64_t> hash(nu), slot_key(slots, 0);
+  std::vector<uint32_t> off(nu + 1, 0), slot_val(slots, tt::kSlotEmpty);
+  std::vector<uint8_t> pool;
+  for (uint32_t u = 0; u < nu; ++u) {
+    const int32_t i = first_of[u];
+    hash[u] = tt_hash64((const uint8_t*)utf8[i], (uint32_t)lens[i]);
+    pool.insert(pool.end(), (const uint8_t*)utf8[i], (const uint8_t*)utf8[i] + lens[i]);
+    off[u + 1] = (uint32_t)pool.size();
+    uint32_t s = tt::slot_of(hash[u], slots);
+    while (slot_val[s] != tt::kSlotEmpty) s = (s + 1) & (slots - 1);
+    slot_key[s] = hash[u];
+    slot_val[s] = (tt::tag_of(hash[u]) << 10) | u;
+  }
+  // one device buffer: [hash nu*8][slot_key slots*8][off (nu+1)*4][slot_val slots*4][pool]
+  const size_t o_hash = 0, o_skey = o_hash + (size_t)nu * 8, o_off = o_skey + (size_t)slots * 8,
+               o_sval = o_off + ((size_t)nu + 1) * 4, o_pool = o_sval + (size_t)slots * 4;
+  const size_t qbytes = o_pool + std::max<size_t>(pool.size(), 1);
+  std::vector<uint8_t> host(qbytes, 0);
+  memcpy(&host[o_hash], hash.data(), (size_t)nu * 8);
+  memcpy(&host[o_skey], slot_key.data(), (size_t)slots * 8);
+  memcpy(&host[o_off], off.data(), ((size_t)nu + 1) * 4);
+  memcpy(&host[o_sval], slot_val.data(), (size_t)slots * 4);
+  if (!pool.empty()) memcpy(&host[o_pool], pool.data(), pool.size());
+  if (qbytes > t->d_query_cap) {
     cudaFree(t->d_query);
     t->d_query = nullptr;
     t->d_query_cap = 0;
-    size_t want = std::max<size_t>(4096, (size_t)len);
+    const size_t want = std::max<size_t>(262144, qbytes);
     TT_CUDA(cudaMalloc(&t->d_query, want));
     t->d_query_cap = want;
   }
-  tt_result* r = nullptr;
-  // first guess: a creator rarely owns more than this many rows; grows on overflow
-  int64_t cap = std::min<int64_t>(std::max<int64_t>(t->n, 1), 4096);
-  for (int pass = 0; pass < 2; ++pass) {
-    int32_t rc = result_alloc(t, cap, &r);
+  if ((int64_t)nu > t->d_lists_queries) {
+    cudaFree(t->d_lists);
+    t->d_lists = nullptr;
+    t->d_lists_queries = 0;
+    const int64_t want = std::max<int64_t>(64, nu);
+    TT_CUDA(cudaMalloc(&t->d_lists, (size_t)want * tt::kListCap * 4));
+    t->d_lists_queries = want;
+  }
+  TT_CUDA(cudaMemcpyAsync(t->d_query, host.data(), qbytes, cudaMemcpyHostToDevice, t->stream));
+  tt::QuerySet qs;
+  qs.hash = reinterpret_cast<const uint64_t*>(t->d_query + o_hash);
+  qs.slot_key = reinterpret_cast<const uint64_t*>(t->d_query + o_skey);
+  qs.off = reinterpret_cast<const uint32_t*>(t->d_query + o_off);
+  qs.slot_val = reinterpret_cast<const uint32_t*>(t->d_query + o_sval);
+  qs.pool = t->d_query + o_pool;
+  qs.slots = slots;
+  qs.nq = nu;
+  const size_t smem = nu == 1 ? 0 : (size_t)slots * 12;
+  static bool opted = false;
+  if (!opted) {
+    TT_CUDA(cudaFuncSetAttribute(tt::creator_scan_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)tt::kMaxSlots * 12));
+    TT_CUDA(cudaFuncSetAttribute(tt::order_lists_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 tt::kListOrderCap * 12));
+    opted = true;
+  }
+
+  // ---- K4: one pass over the hash column for the whole batch.  First into per-query lists (one
+  // CTA per query orders them afterwards); if some creator has more than kListCap tasks, once
+  // more into a pair list that the general ordering path takes. ----
+  const int64_t n_pairs = t->n_pad / 2;
+  const int64_t per_cta = (int64_t)tt::kCreatorThreads * tt::kCreatorUnroll;
+  const unsigned grid = (unsigned)std::max<int64_t>(
+      1, std::min<int64_t>((n_pairs + per_cta - 1) / per_cta, (int64_t)t->sm_count * 8));
+  auto scan = [&](const tt::MatchSink& sink) -> int32_t {
+    TT_CUDA(cudaMemsetAsync(t->d_small, 0, 16, t->stream));
+    TT_CUDA(cudaMemsetAsync(t->d_qcount, 0, (size_t)nu * 4, t->stream));
+    TT_CUDA(cudaEventRecord(t->ev0, t->stream));
+    if (nu == 1)
+      tt::creator_scan_kernel<true><<<grid, tt::kCreatorThreads, 0, t->stream>>>(
+          reinterpret_cast<const ulonglong2*>(t->creator_hash), t->n, n_pairs, qs, t->creator_ref, t->creator_off,
+          t->creator_pool, sink);
+    else
+      tt::creator_scan_kernel<false><<<grid, tt::kCreatorThreads, smem, t->stream>>>(
+          reinterpret_cast<const ulonglong2*>(t->creator_hash), t->n, n_pairs, qs, t->creator_ref, t->creator_off,
+          t->creator_pool, sink);
+    TT_CUDA(cudaGetLastError());
+    TT_CUDA(cudaEventRecord(t->ev1, t->stream));
+    TT_CUDA(cudaMemcpyAsync(t->h_small, t->d_small, 16, cudaMemcpyDeviceToHost, t->stream));
+    TT_CUDA(cudaMemcpyAsync(t->h_qcount, t->d_qcount, (size_t)nu * 4, cudaMemcpyDeviceToHost, t->stream));
+    TT_CUDA(cudaStreamSynchronize(t->stream));
+    float ms = 0;
+    TT_CUDA(cudaEventElapsedTime(&ms, t->ev0, t->ev1));
+    t->last_op.scan_ms += ms;
+    t->last_op.launches += 1;
+    return TT_OK;
+  };
+
+  int64_t found = 0;
+  bool lists_ok = true;
+  std::vector<uint32_t> count(nu, 0);
+  if (t->n > 0) {
+    tt::MatchSink sink{t->d_lists, t->d_qcount, nullptr, 0, t->d_small};
+    int32_t rc = scan(sink);
     if (rc) return rc;
-    int64_t found = 0;
-    cudaError_t e = tt::creator_filter(t->stream, t->sm_count, t->creator_hash, t->creator_ref, t->creator_off,
-                                       t->creator_pool, t->n, t->n_pad, (const uint8_t*)utf8, (uint32_t)len, t->d_query, r->d_rows,
-                                       cap, t->d_small, t->h_small, &found);
-    if (e != cudaSuccess) {
-      result_release(r);
+    found = (int64_t)t->h_small[0];
+    t->last_op.candidates = (int64_t)t->h_small[1];
+    for (uint32_t u = 0; u < nu; ++u) {
+      count[u] = t->h_qcount[u];
+      lists_ok = lists_ok && count[u] <= tt::kListCap;
+    }
+    if (!lists_ok) {
+      if (found > t->d_pairs_cap) {
+        cudaFree(t->d_pairs);
+        t->d_pairs = nullptr;
+        t->d_pairs_cap = 0;
+        TT_CUDA(cudaMalloc(&t->d_pairs, (size_t)found * 8));
+        t->d_pairs_cap = found;
+      }
+      tt::MatchSink psink{nullptr, t->d_qcount, t->d_pairs, t->d_pairs_cap, t->d_small};
+      rc = scan(psink);
+      if (rc) return rc;
+      if ((int64_t)t->h_small[0] != found) return fail(TT_ERR_STATE, "table changed during a creator query");
+    }
+  }
+  t->last_op.matches = found;
+
+  // ---- K5: order every query's matches by TaskCreatedOn descending (stable), gather TaskIds ----
+  tt_result* whole = nullptr;
+  int32_t rc = result_alloc(t, std::max<int64_t>(found, 1), &whole);
+  if (rc) return rc;
+  whole->n = found;
+  if (found > 0) {
+    TT_CUDA(cudaEventRecord(t->ev0, t->stream));
+    if (lists_ok) {
+      tt::order_lists_kernel<<<nu, tt::kListOrderThreads, tt::kListOrderCap * 12, t->stream>>>(t->d_lists, t->d_qcount, t->created_raw,
+                                                                        t->task_id, 1, whole->d_rows, whole->d_ids);
+      cudaError_t ce = cudaGetLastError();
+      if (ce != cudaSuccess) {
+        result_release(whole);
+        return fail(TT_ERR_CUDA, "order_lists_kernel: %s", cudaGetErrorString(ce));
+      }
+    } else {
+      cudaMemsetAsync(t->d_qcount, 0, (size_t)nu * 4, t->stream);
+      int e = tt::order_pairs(t->stream, t->d_pairs, found, t->created_raw, t->task_id, /*descending=*/true,
+                              whole->d_rows, whole->d_ids, t->d_qcount);
+      if (e != 0) {
+        result_release(whole);
+        cudaGetLastError();
+        return fail(TT_ERR_CUDA, "order_pairs: %s", cudaGetErrorString((cudaError_t)e));
+      }
+    }
+    cudaEventRecord(t->ev1, t->stream);
+    cudaError_t ce = cudaStreamSynchronize(t->stream);
+    if (ce != cudaSuccess) {
+      result_release(whole);
       cudaGetLastError();
-      return fail(TT_ERR_CUDA, "creator_filter: %s", cudaGetErrorString(e));
+      return fail(TT_ERR_CUDA, "creator result ordering: %s", cudaGetErrorString(ce));
     }
-    if (found <= cap) {
-      r->n = found;
-      break;
-    }
-    result_release(r);
-    r = nullptr;
-    cap = found;
+    cudaEventElapsedTime(&t->last_op.order_ms, t->ev0, t->ev1);
+    t->last_op.launches += 1;
   }
-  if (!r) return fail(TT_ERR_STATE, "creator filter did not converge");
-  if (r->n > 0) {
-    // FakeTasksManager.cs:70 / TasksStoreManager.cs:66 — OrderByDescending(TaskCreatedOn), stable.
-    // The filter emits candidates unordered; sorting the rows first restores source order for ties.
-    int rc = tt::order_by_created(t->stream, t->created_raw, t->task_id, r->d_rows, r->d_ids, r->n, /*descending=*/true,
-                                  /*rows_unordered=*/true);
-    if (rc != 0) {
-      result_release(r);
-      return fail(TT_ERR_CUDA, "order_by_created failed: %s", cudaGetErrorString((cudaError_t)rc));
+  std::vector<int64_t> first(nu + 1, 0);
+  for (uint32_t u = 0; u < nu; ++u) first[u + 1] = first[u] + count[u];
+  for (int32_t i = 0; i < nq; ++i) {
+    const int32_t u = uniq_of[i];
+    out[i] = result_slice(whole, first[u], count[u]);
+    if (!out[i]) {
+      for (int32_t k = 0; k < i; ++k) {
+        result_release(out[k]);
+        out[k] = nullptr;
+      }
+      result_release(whole);
+      return fail(TT_ERR_OOM, "out of host memory");
     }
   }
-  *out = r;
+  result_release(whole);  // the slices keep the block alive
+  return TT_OK;
+}
+
+int32_t tt_get_by_creator(tt_table* t, const char* utf8, int32_t len, tt_result** out) {
+  if (!out) return fail(TT_ERR_ARG, "bad argument");
+  const char* q[1] = {utf8 ? utf8 : ""};
+  const int32_t l[1] = {len};
+  return tt_get_by_creators(t, q, l, 1, out);
+}
+
+int32_t tt_last_op_stats(tt_table* t, tt_op_stats* out) {
+  if (!t || !out) return fail(TT_ERR_ARG, "null argument");
+  std::lock_guard<std::mutex> lk(t->mu);
+  *out = t->last_op;
   return TT_OK;
 }
 

@@ -44,7 +44,7 @@ EXPORTS = [
     "tt_get_yesterdays_due", "tt_mark_overdue", "tt_sweep", "tt_get_by_creator",
     "tt_result_count", "tt_result_rows", "tt_result_ids", "tt_result_field", "tt_result_free",
     "tt_snapshot_flags", "tt_restore_flags", "tt_count_flags", "tt_result_digest",
-    "tt_sweep_device", "tt_get_device_view", "tt_sweep_static",
+    "tt_sweep_device", "tt_get_device_view", "tt_sweep_static", "tt_get_by_creators", "tt_last_op_stats",
 ]
 
 
@@ -113,6 +113,17 @@ class SweepStats(C.Structure):
     ]
 
 
+class OpStats(C.Structure):
+    _fields_ = [
+        ("scan_ms", C.c_float),
+        ("order_ms", C.c_float),
+        ("candidates", C.c_int64),
+        ("matches", C.c_int64),
+        ("launches", C.c_int32),
+        ("queries", C.c_int32),
+    ]
+
+
 class DeviceView(C.Structure):
     _fields_ = [
         ("n", C.c_int64),
@@ -157,6 +168,8 @@ def lib():
     L.tt_mark_overdue.argtypes = [vp, i32, vp, i64, P(i64), P(i64)]
     L.tt_sweep.argtypes = [vp, i32, i64, i64, P(vp), P(i64)]
     L.tt_get_by_creator.argtypes = [vp, C.c_char_p, i32, P(vp)]
+    L.tt_get_by_creators.argtypes = [vp, P(C.c_char_p), P(i32), i32, P(vp)]
+    L.tt_last_op_stats.argtypes = [vp, P(OpStats)]
     L.tt_result_count.argtypes = [vp, P(i64)]
     L.tt_result_rows.argtypes = [vp, vp]
     L.tt_result_ids.argtypes = [vp, vp]
@@ -295,6 +308,21 @@ class TaskTable:
         r = C.c_void_p()
         _check(lib().tt_get_by_creator(self._h, b, len(b), C.byref(r)))
         return Result(r)
+
+    def get_by_creators(self, creators):
+        """One table pass for a whole batch of creators -> list of Result, one per query."""
+        bs = [c.encode() if isinstance(c, str) else bytes(c) for c in creators]
+        n = len(bs)
+        arr = (C.c_char_p * n)(*bs)
+        lens = (C.c_int32 * n)(*[len(b) for b in bs])
+        out = (C.c_void_p * n)()
+        _check(lib().tt_get_by_creators(self._h, arr, lens, n, out))
+        return [Result(C.c_void_p(out[i])) for i in range(n)]
+
+    def last_op_stats(self):
+        st = OpStats()
+        _check(lib().tt_last_op_stats(self._h, C.byref(st)))
+        return st
 
     # -- device-resident sweep ---------------------------------------------------------------
     def sweep_device(self, mode, flags, d_rows, d_ids, cap, today=DEFAULT_TODAY, run_at=DEFAULT_RUN_AT, first_row=0,

@@ -43,6 +43,9 @@ def parse():
     ap.add_argument("--cpu-sample-rows", type=int, default=8_000_000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--workload", default="sweep", choices=["sweep", "sweep10m", "creator", "mixed"],
+                    help="sweep = the headline (BASELINE.json metric); the others are the remaining configs of "
+                         "SURVEY.md 8(d): sweep10m = config 2, creator = config 4, mixed = config 5 (per GPU)")
     return ap.parse_args()
 
 
@@ -346,9 +349,145 @@ def run_b200(args):
         dist.destroy_process_group()
 
 
+# --------------------------------------------------------------------------------------------------
+def run_extra(args):
+    """The other configs of SURVEY.md 8(d) on one GPU (not the driver's headline line)."""
+    import numpy as np
+    import torch
+
+    pkg = importlib.import_module("aca-dotnet-workshop_b200")
+    tt = pkg.tasktable
+    torch.cuda.set_device(0)
+    dev = torch.device("cuda", 0)
+    peak, peak_src = peaks()
+    stream = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(stream)
+    med = lambda xs: sorted(xs)[len(xs) // 2]
+    flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+
+    if args.workload == "sweep10m":
+        n = 10_000_000
+        cfg = pkg.default_cfg(0x5EED0001, n)
+        table = pkg.TaskTable(0).generate(cfg, 0, n)
+        nbytes = (n + 7) // 8
+        pristine = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+        tt._check(tt.lib().tt_snapshot_flags(table._h, None, pristine.data_ptr()))
+        cap = int(n * 0.032) + 65536
+        d_rows = torch.empty(cap, dtype=torch.int32, device=dev)
+        d_ids = torch.empty((cap, 16), dtype=torch.uint8, device=dev)
+        wall, kms, sms = [], [], []
+        for i in range(args.warmup + args.steps):
+            tt._check(tt.lib().tt_restore_flags(table._h, None, pristine.data_ptr()))
+            flush.zero_()  # L2 flush: the 42.5 MB of hot columns would otherwise stay in the 126 MB L2
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            st, _ = table.sweep_device(tt.MODE_STORE, tt.SWEEP_MARK, d_rows.data_ptr(), d_ids.data_ptr(), cap,
+                                       stream=stream.cuda_stream)
+            dt = time.perf_counter() - t0
+            if i >= args.warmup:
+                wall.append(dt * 1e3)
+                kms.append(st.kernel_ms)
+                sms.append(st.sweep_ms)
+        hits = st.n_listed
+        line = {"metric": METRIC, "workload": "config 2: 10M-task sweep, 1 GPU, L2 flushed between steps",
+                "value": n / (med(wall) * 1e-3), "unit": UNIT, "ms_per_step_wall": med(wall), "kernel_ms": med(kms),
+                "sweep_kernel_ms": med(sms), "hits": hits,
+                "roofline": {"bound": "hbm", "achieved": (n * BYTES_PER_TASK + hits * 4) / (med(sms) * 1e-3) / 1e9,
+                             "peak": peak, "unit": "GB/s",
+                             "frac": (n * BYTES_PER_TASK + hits * 4) / (med(sms) * 1e-3) / 1e9 / peak,
+                             "note": "K1 alone; 7.9 us at peak, so launch latency dominates at this size"}}
+        print(json.dumps(line))
+        table.close()
+        return
+
+    if args.workload == "creator":
+        n, n_creators = 100_000_000, 1_000_000
+        cfg = pkg.default_cfg(0x5EED0003, n, n_creators=n_creators)
+        table = pkg.TaskTable(0).generate(cfg, 0, n)
+        rng = np.random.default_rng(3)
+        ks = rng.integers(0, n_creators, size=1000)
+        names = [("user%07d@mail%d.example" % (k, k % 97)).encode() for k in ks]
+        names += [b"absent%d@nowhere.example" % i for i in range(10)]
+        single_scan, single_wall, hits = [], [], 0
+        for i, q in enumerate(names[:200]):
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            r = table.get_by_creator(q)
+            single_wall.append((time.perf_counter() - t0) * 1e3)
+            single_scan.append(table.last_op_stats().scan_ms)
+            hits += r.count
+            r.free()
+        batch = {}
+        for q in (16, 64, 256, 1000):
+            scans, walls = [], []
+            for rep in range(5):
+                t0 = time.perf_counter()
+                rs = table.get_by_creators(names[:q])
+                walls.append((time.perf_counter() - t0) * 1e3)
+                st = table.last_op_stats()
+                scans.append(st.scan_ms)
+                for r in rs:
+                    r.free()
+            batch[q] = {"scan_ms": med(scans), "order_ms": st.order_ms, "wall_ms": med(walls), "matches": st.matches,
+                        "candidates": st.candidates, "queries_per_sec": q / (med(walls) * 1e-3),
+                        "GBps": n * 8 / (med(scans) * 1e-3) / 1e9}
+        sc = med(single_scan[5:])
+        line = {"metric": "creator_filter_rows_per_sec", "workload": "config 4: GetTasksByCreator over 100M tasks, 1M creators",
+                "value": n / (sc * 1e-3), "unit": "rows/s", "scan_ms": sc, "wall_ms_per_query": med(single_wall[5:]),
+                "avg_hits_per_query": hits / 200,
+                "roofline": {"bound": "hbm", "achieved": n * 8 / (sc * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                             "frac": n * 8 / (sc * 1e-3) / 1e9 / peak, "kernel": "tt::creator_scan_kernel<true>",
+                             "algorithmic_bytes": n * 8, "note": "8 B/row hash column; inputs 800 MB >> L2"},
+                "batch": batch}
+        print(json.dumps(line))
+        table.close()
+        return
+
+    if args.workload == "mixed":
+        n = args.rows
+        cfg = pkg.default_cfg(SEED, n)
+        table = pkg.TaskTable(0).generate(cfg, 0, n)
+        nbytes = (n + 7) // 8
+        pristine = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+        tt._check(tt.lib().tt_snapshot_flags(table._h, None, pristine.data_ptr()))
+        cap = int(n * 0.032) + 65536
+        d_rows = torch.empty(cap, dtype=torch.int32, device=dev)
+        d_ids = torch.empty((cap, 16), dtype=torch.uint8, device=dev)
+        rng = np.random.default_rng(5)
+        names = [("user%07d@mail%d.example" % (k, k % 97)).encode() for k in rng.integers(0, 1_000_000, size=64)]
+        wall, sweep_k, scan_k, order_k = [], [], [], []
+        for i in range(args.warmup + args.steps):
+            tt._check(tt.lib().tt_restore_flags(table._h, None, pristine.data_ptr()))
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            st, _ = table.sweep_device(tt.MODE_STORE, tt.SWEEP_MARK, d_rows.data_ptr(), d_ids.data_ptr(), cap,
+                                       stream=stream.cuda_stream)
+            rs = table.get_by_creators(names)
+            dt = time.perf_counter() - t0
+            op = table.last_op_stats()
+            for r in rs:
+                r.free()
+            if i >= args.warmup:
+                wall.append(dt * 1e3)
+                sweep_k.append(st.kernel_ms)
+                scan_k.append(op.scan_ms)
+                order_k.append(op.order_ms)
+        line = {"metric": "mixed_cron_batch_ms", "workload": f"config 5 per GPU: {n}-task sweep + 64 creator filters (one batch)",
+                "value": med(wall), "unit": "ms", "higher_is_better": False, "sweep_kernels_ms": med(sweep_k),
+                "creator_scan_ms": med(scan_k), "creator_order_ms": med(order_k), "hits": st.n_listed,
+                "creator_matches": op.matches,
+                "roofline": {"bound": "hbm", "unit": "GB/s", "peak": peak,
+                             "creator_scan_achieved": n * 8 / (med(scan_k) * 1e-3) / 1e9,
+                             "creator_scan_frac": n * 8 / (med(scan_k) * 1e-3) / 1e9 / peak}}
+        print(json.dumps(line))
+        table.close()
+
+
 if __name__ == "__main__":
     a = parse()
     if a.impl == "reference":
         run_reference(a)
+    elif a.workload != "sweep":
+        run_extra(a)
     else:
         run_b200(a)

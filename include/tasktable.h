@@ -125,6 +125,22 @@ int32_t tt_sweep(tt_table* t, int32_t mode, int64_t today_local_ticks, int64_t r
  * then the candidate's string is compared), descending TaskCreatedOn, ties in row order. */
 int32_t tt_get_by_creator(tt_table* t, const char* utf8, int32_t len, tt_result** out);
 
+/* The same for a batch of creators in ONE pass over the table (the hash column is read once for
+ * all of them): out[i] receives the result of query i, nq <= 1024.  No reference counterpart as
+ * a single call — it is GetTasksByCreator (ITasksManager.cs:7) for nq concurrent requests. */
+int32_t tt_get_by_creators(tt_table* t, const char* const* utf8, const int32_t* lens, int32_t nq, tt_result** out);
+
+/* Device timings of the last tt_get_by_creator(s) call on this table. */
+typedef struct tt_op_stats {
+  float scan_ms;      /* K4 hash-column scan + exact confirm                                   */
+  float order_ms;     /* K5 ordering + TaskId gather of the matches                             */
+  int64_t candidates; /* rows whose 64-bit hash matched a query                                 */
+  int64_t matches;    /* rows whose string matched (all queries together)                       */
+  int32_t launches;
+  int32_t queries;
+} tt_op_stats;
+int32_t tt_last_op_stats(tt_table* t, tt_op_stats* out);
+
 /* ---- results --------------------------------------------------------------------------- */
 
 int32_t tt_result_count(const tt_result* r, int64_t* n);

@@ -58,7 +58,48 @@ int main(int argc, char** argv) {
   run("library sweep 256thr x4/SM", 4, [&](int g) { sweep_kernel<true, true, 256, 4><<<g, 256>>>(p); });
   run("library sweep 256thr x3/SM", 3, [&](int g) { sweep_kernel<true, true, 256, 4><<<g, 256>>>(p); });
   run("library sweep 256thr x2/SM", 2, [&](int g) { sweep_kernel<true, true, 256, 4><<<g, 256>>>(p); });
-  p.list = nullptr;
-  run("library sweep count-only x4/SM", 4, [&](int g) { sweep_kernel<true, false, 256, 4><<<g, 256>>>(p); });
+  // ---- can K3 (random TaskId gathers) overlap K1 (streaming) on the same DRAM? ----
+  {
+    uint4* ids; uint4* out_ids; uint32_t *out_rows, *tfirst, *over2;
+    CK(cudaMalloc(&ids, NP * 16)); CK(cudaMalloc(&out_ids, NP / 16 * 16)); CK(cudaMalloc(&out_rows, NP / 16 * 4));
+    CK(cudaMalloc(&tfirst, NP / 8192 * 4)); CK(cudaMalloc(&over2, NP / 8));
+    CK(cudaMemset(ids, 7, NP * 16));
+    cudaStream_t s1, s2; cudaStreamCreateWithFlags(&s1, cudaStreamNonBlocking); cudaStreamCreateWithFlags(&s2, cudaStreamNonBlocking);
+    // one K1 run to produce the list + tile words, then K2
+    auto reset = [&](uint32_t* ov) {
+      cudaMemset(ov, 0, NP / 8);
+      SweepCtl init; init.tile_counter = 0; init.pad = 0; init.cursor = 0; init.stored = ~0ull;
+      cudaMemcpy(ctl, &init, sizeof init, cudaMemcpyHostToDevice); cudaMemset(gsum, 0, 4096);
+    };
+    reset(over);
+    sweep_kernel<true, true, 256, 4><<<592, 256>>>(p);
+    unsigned ng = (p.num_tiles + kTilesPerGroup - 1) / kTilesPerGroup;
+    tile_offsets_kernel<<<ng, kTilesPerGroup>>>(p.tile_count, p.group_sum, p.num_tiles, tfirst);
+    CK(cudaDeviceSynchronize());
+    // a second control block + list for the concurrent K1 so that the K3 inputs stay intact
+    SweepCtl* ctl2; uint32_t *rows2, *ubase2, *tcount2, *gsum2;
+    CK(cudaMalloc(&ctl2, sizeof(SweepCtl))); CK(cudaMalloc(&rows2, NP / 16 * 4)); CK(cudaMalloc(&ubase2, NP / 8192 * 4));
+    CK(cudaMalloc(&tcount2, NP / 8192 * 4)); CK(cudaMalloc(&gsum2, 4096));
+    SweepParams p2 = p; p2.ctl = ctl2; p2.list = rows2; p2.tile_slot = ubase2; p2.tile_count = tcount2; p2.group_sum = gsum2; p2.overdue = over2;
+    cudaEvent_t e0, e1, e2, e3; cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventCreate(&e2); cudaEventCreate(&e3);
+    for (int mode = 0; mode < 3; ++mode) {
+      float best = 1e9f, bk1 = 0, bk3 = 0;
+      for (int r = 0; r < 4; ++r) {
+        cudaMemset(over2, 0, NP / 8);
+        SweepCtl init; init.tile_counter = 0; init.pad = 0; init.cursor = 0; init.stored = ~0ull;
+        cudaMemcpy(ctl2, &init, sizeof init, cudaMemcpyHostToDevice); cudaMemset(gsum2, 0, 4096);
+        cudaDeviceSynchronize();
+        cudaEventRecord(e0, s1); cudaEventRecord(e2, s2);
+        if (mode != 1) sweep_kernel<true, true, 256, 4><<<592, 256, 0, s1>>>(p2);
+        if (mode != 0) place_hits_kernel<8192><<<148 * 8, 256, 0, s2>>>(ctl, rows, p.tile_slot, tfirst, 0, ids, out_rows, out_ids);
+        cudaEventRecord(e1, s1); cudaEventRecord(e3, s2);
+        cudaDeviceSynchronize();
+        float k1, k3; cudaEventElapsedTime(&k1, e0, e1); cudaEventElapsedTime(&k3, e2, e3);
+        float tot = std::max(k1, k3);
+        if (tot < best) { best = tot; bk1 = k1; bk3 = k3; }
+      }
+      printf("%-40s total %8.3f ms (K1 %.3f, K3 %.3f)\n", mode == 0 ? "K1 alone" : mode == 1 ? "K3 alone" : "K1 || K3 on two streams", best, bk1, bk3);
+    }
+  }
   return 0;
 }

@@ -22,7 +22,7 @@ def declared_symbols():
 def test_library_exports_every_declared_symbol():
     L = tt.lib()
     names = declared_symbols()
-    assert len(names) >= 21
+    assert len(names) >= 24
     for name in names:
         assert hasattr(L, name), f"{name} declared in include/tasktable.h but not exported"
     assert set(names) == set(tt.EXPORTS)
@@ -33,6 +33,7 @@ def test_struct_layouts_match_the_header():
     assert C.sizeof(tt.SweepStats) == 48
     assert C.sizeof(tt.SoaView) == 80
     assert C.sizeof(tt.DeviceView) == 72
+    assert C.sizeof(tt.OpStats) == 32
 
 
 def test_no_cpu_fallback_without_gpu():

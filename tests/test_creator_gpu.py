@@ -66,6 +66,55 @@ def test_creator_filter_matches_oracle(oracle):
     table.close()
 
 
+def test_creator_batch_matches_oracle(oracle):
+    """64+ creators in one table pass: duplicates, absent names, near misses, and a big batch"""
+    n = 400_000
+    cfg = oracle.default_cfg(0x5EED0003, n, n_creators=4000, ppm_created_dup=100_000)
+    ot = oracle.OracleTable()
+    ot.add_synth(cfg, 0, n)
+    table = tt.TaskTable(0).generate(cfg, 0, n)
+    ids_all, _, _ = ot.export()
+    rng = np.random.default_rng(5)
+    for nq in (3, 64, 700):
+        queries = [ot.created_by(int(r)) for r in rng.integers(0, n, size=nq - 2)]
+        queries += [b"nobody@nowhere.example", queries[0]]  # an absent creator and a repeated one
+        results = table.get_by_creators(queries)
+        st = table.last_op_stats()
+        assert len(results) == nq and st.queries == nq and st.scan_ms > 0
+        total = 0
+        for q, res in zip(queries, results):
+            want = ot.get_by_creator(oracle.MODE_FAKE, q)
+            rows = res.rows()
+            assert rows.tolist() == want.tolist(), q
+            assert (res.ids() == ids_all[rows]).all()
+            total += rows.size
+        assert st.matches == sum(ot.get_by_creator(oracle.MODE_FAKE, q).size for q in set(queries))
+        for res in results:
+            res.free()
+    # a batch whose total result is too large for the single-CTA ordering path
+    few = tt.TaskTable(0).generate(oracle.default_cfg(13, 200_000, n_creators=5, ppm_created_dup=200_000), 0, 200_000)
+    ot2 = oracle.OracleTable()
+    ot2.add_synth(oracle.default_cfg(13, 200_000, n_creators=5, ppm_created_dup=200_000), 0, 200_000)
+    qs = [ot2.created_by(k) for k in range(20)]
+    for q, res in zip(qs, few.get_by_creators(qs)):
+        assert res.rows().tolist() == ot2.get_by_creator(oracle.MODE_FAKE, q).tolist()
+    table.close()
+    few.close()
+
+
+def test_colliding_queries_in_one_batch(oracle):
+    a, b = colliding_pair()
+    TPD = tt.TICKS_PER_DAY
+    ot = oracle.OracleTable()
+    who = [a, b, a, b"carol@x.example", b, a]
+    for i, w in enumerate(who):
+        ot.add(bytes([i + 1] * 16), "n", w, "z", (tt.DEFAULT_TODAY - TPD + i) | (1 << 62), tt.DEFAULT_TODAY - TPD)
+    table = load_from_oracle(ot)
+    ra, rb, rc = table.get_by_creators([a, b, b"carol@x.example"])
+    assert ra.rows().tolist() == [5, 2, 0] and rb.rows().tolist() == [4, 1] and rc.rows().tolist() == [3]
+    table.close()
+
+
 def test_creator_ties_keep_source_order(oracle):
     n = 60_000
     cfg = oracle.default_cfg(12, n, n_creators=7, ppm_created_dup=300_000)
