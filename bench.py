@@ -60,7 +60,7 @@ def peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks and throttle reasons while the timed region runs (NVML, 20 ms period)."""
+    """nvidia-smi clocks and throttle reasons while the timed region runs (NVML, 2 ms period)."""
 
     REASONS = {0x1: "gpu_idle", 0x2: "applications_clocks_setting", 0x4: "sw_power_cap", 0x8: "hw_slowdown",
                0x10: "sync_boost", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
@@ -92,7 +92,7 @@ class ClockSampler:
                         self.reasons.add(name)
             except Exception:
                 pass
-            time.sleep(0.02)
+            time.sleep(0.002)
 
     def __enter__(self):
         if self._nv:
