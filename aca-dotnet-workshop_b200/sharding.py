@@ -7,6 +7,7 @@ and the hit identifiers (variable-length gather to the root) cross NVLink.  The 
 written against torch.distributed so the same code runs over NCCL on GPUs and over gloo in
 the CPU tests.
 """
+import os
 from dataclasses import dataclass
 
 import torch
@@ -56,6 +57,43 @@ class HitExchange:
         self._host = torch.zeros(1, dtype=torch.int64)
         if device.type == "cuda":
             self._host = self._host.pin_memory()
+        self._flag = torch.zeros(1, dtype=torch.int32, device=device)
+        self.peer_rows = self.peer_ids = None
+        self.transport = "nccl send/recv"
+        # Opt-in only: on the 2 x B200 box measured in round 1 the mapped copy ran at PCIe speed
+        # (2.96 ms per 100 MB against 0.63 ms for NCCL send/recv), so send/recv stays the default.
+        if device.type == "cuda" and self.world > 1 and os.environ.get("TT_EXCHANGE_PEER", "0") == "1":
+            self._map_root_buffers()
+
+    def _map_root_buffers(self):
+        """Maps the root's receive buffers into every other process (CUDA IPC through torch's own
+        tensor sharing), so a shard can store its hit ids straight into the root's HBM over
+        NVLink with one device-to-device copy instead of a NCCL send/recv pair.  Falls back to
+        send/recv if the mapping cannot be set up; every rank takes the same decision."""
+        from torch.multiprocessing.reductions import reduce_tensor
+
+        ok = 1
+        payload = [None]
+        try:
+            if self.rank == self.dst:
+                payload[0] = (reduce_tensor(self.rows_all), reduce_tensor(self.ids_all) if self.ids_all is not None else None)
+            dist.broadcast_object_list(payload, src=self.dst, group=self.group)
+            if self.rank != self.dst:
+                (fn, a), ids = payload[0]
+                self.peer_rows = fn(*a)
+                if ids is not None:
+                    self.peer_ids = ids[0](*ids[1])
+                probe = torch.zeros(4, dtype=torch.int32, device=self.rows_all.device)
+                self.peer_rows[self.cap * self.rank: self.cap * self.rank + 4].copy_(probe)  # touch the mapping
+                torch.cuda.synchronize()
+        except Exception:
+            ok = 0
+        agree = torch.tensor([ok], dtype=torch.int32, device=self.rows_all.device)
+        dist.all_reduce(agree, op=dist.ReduceOp.MIN, group=self.group)
+        if int(agree.item()) == 1:
+            self.transport = "peer copy over NVLink (CUDA IPC mapping of the root's buffers)"
+        else:
+            self.peer_rows = self.peer_ids = None
 
     def run(self, count):
         """-> list of per-shard counts (every rank).  On dst, rows_all / ids_all hold all hits."""
@@ -69,6 +107,15 @@ class HitExchange:
         offs = [0]
         for c in counts:
             offs.append(offs[-1] + c)
+        if self.transport.startswith("peer"):
+            # every shard stores its ids at its offset in the root's buffers, then a one-word
+            # all-reduce (stream-ordered after the copy) tells the root that everything has landed
+            if self.rank != self.dst and count > 0:
+                self.peer_rows[offs[self.rank]:offs[self.rank] + count].copy_(self.rows_all[:count], non_blocking=True)
+                if self.with_ids:
+                    self.peer_ids[offs[self.rank]:offs[self.rank] + count].copy_(self.ids_all[:count], non_blocking=True)
+            dist.all_reduce(self._flag, group=self.group)
+            return counts
         ops = []
         if self.rank == self.dst:
             for r in range(self.world):

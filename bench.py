@@ -335,6 +335,10 @@ def run_b200(args):
                                            "frac": (place_gbs / peak) if place_gbs else None,
                                            "note": "random 16 B TaskId gathers cost 64 B of DRAM each"}},
             "gpu_launches": launches,
+            "exchange": {"what": (args.exchange if world > 1 else "none"), "transport": ex.transport if world > 1 else None,
+                         "ms": med([a - b for a, b in zip(step_ms, kernel_ms)]),
+                         "note": "per-step time outside the three sweep kernels on rank 0: launch/sync overhead, "
+                                 "count all-gather and the hit id gather (N > 1)"},
             "clocks": clocks.summary(),
         }
         if e2e:

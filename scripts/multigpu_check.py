@@ -32,6 +32,17 @@ def main():
     st, _ = table.sweep_device(tt.MODE_STORE, tt.SWEEP_MARK, d_rows.data_ptr(), d_ids.data_ptr(), cap,
                                stream=stream.cuda_stream)
     counts, glob, gids = pkg.exchange_hits(d_rows, st.n_stored, plan, ids=d_ids)
+    # the persistent-buffer exchange bench.py uses (peer copy when the mapping works) must agree
+    ex = pkg.HitExchange(plan, cap, dev, with_ids=True)
+    ex.rows_all[: st.n_stored] = d_rows[: st.n_stored]
+    ex.ids_all[: st.n_stored] = d_ids[: st.n_stored]
+    counts2 = ex.run(st.n_stored)
+    torch.cuda.synchronize()
+    same = counts2 == counts
+    if rank == 0:
+        same = same and bool((ex.global_rows(counts2) == glob).all()) and bool((ex.ids_all[: sum(counts2)] == gids).all())
+        print("exchange transport:", ex.transport, "agrees" if same else "DIFFERS")
+    assert same
     ok = True
     if rank == 0:
         from oracle import oracle as orc
