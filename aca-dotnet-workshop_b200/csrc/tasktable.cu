@@ -21,6 +21,7 @@
 #include "../../include/tasktable.h"
 #include "creator.cuh"
 #include "order.cuh"
+#include "point.cuh"
 #include "sweep.cuh"
 #include "tt_bits.h"
 
@@ -87,6 +88,16 @@ struct tt_table {
   uint64_t pool_bytes = 0;
   bool ids_sorted = false;
   uint32_t* id_order = nullptr;  // rows sorted by TaskId when the table itself is not
+  // point operations: live-row count, capacity of the creator dictionary on the device and its
+  // host mirror (built on the first insert)
+  int64_t n_live = 0;
+  size_t creator_off_cap = 0, creator_pool_cap = 0;
+  bool dict_mirrored = false;
+  std::vector<uint32_t> h_creator_off;
+  std::vector<uint8_t> h_creator_pool;
+  std::unordered_map<std::string, uint32_t> h_creator_index;
+  uint8_t last_id[16] = {};
+  bool last_id_known = false;
 
   // sweep scratch: per-tile slot / count / final offset (3 words per tile), group sums, the
   // unordered hit list (grown on demand), and the control block with its pinned mirror
@@ -196,6 +207,7 @@ int32_t alloc_columns(tt_table* t, int64_t n) {
   TT_CUDA(cudaMemsetAsync(t->due_raw, 0, np * 8, t->stream));
   TT_CUDA(cudaMemsetAsync(t->creator_ref, 0, np * 4, t->stream));
   t->n = n;
+  t->n_live = n;
   t->n_pad = np;
   return TT_OK;
 }
@@ -203,8 +215,10 @@ int32_t alloc_columns(tt_table* t, int64_t n) {
 int32_t upload_dictionary(tt_table* t, uint32_t n_creators, const uint32_t* off, const uint8_t* pool) {
   t->n_creators = n_creators;
   t->pool_bytes = n_creators ? off[n_creators] : 0;
-  TT_CUDA(cudaMalloc(&t->creator_off, ((size_t)n_creators + 1) * 4));
-  TT_CUDA(cudaMalloc(&t->creator_pool, std::max<uint64_t>(t->pool_bytes, 16)));
+  t->creator_off_cap = (size_t)n_creators + 1;
+  t->creator_pool_cap = std::max<uint64_t>(t->pool_bytes, 16);
+  TT_CUDA(cudaMalloc(&t->creator_off, t->creator_off_cap * 4));
+  TT_CUDA(cudaMalloc(&t->creator_pool, t->creator_pool_cap));
   TT_CUDA(cudaMemcpyAsync(t->creator_off, off, ((size_t)n_creators + 1) * 4, cudaMemcpyHostToDevice, t->stream));
   if (t->pool_bytes)
     TT_CUDA(cudaMemcpyAsync(t->creator_pool, pool, t->pool_bytes, cudaMemcpyHostToDevice, t->stream));
@@ -1132,6 +1146,275 @@ int32_t tt_get_device_view(tt_table* t, tt_device_view* out) {
   out->task_id = t->task_id;
   out->created_raw = t->created_raw;
   out->device = t->device;
+  return TT_OK;
+}
+
+}  // extern "C"
+
+// ---- single-row operations (ITasksManager.cs:8-12) ----------------------------------------------
+
+namespace {
+
+uint4 id_to_uint4(const uint8_t* id16) {
+  uint4 v;
+  memcpy(&v, id16, 16);
+  return v;
+}
+
+// Row of the first live task with this id, or -1.
+int32_t find_row(tt_table* t, const uint8_t* id16, int64_t* row) {
+  *row = -1;
+  if (t->n == 0) return TT_OK;
+  TT_CUDA(cudaMemsetAsync(t->d_small, 0xFF, 8, t->stream));
+  const int sorted = (t->ids_sorted || t->id_order) ? 1 : 0;
+  const unsigned grid = sorted ? 1u : (unsigned)std::min<int64_t>(grid_for(t->n, 256), (int64_t)t->sm_count * 8);
+  tt::find_id_kernel<<<grid, 256, 0, t->stream>>>(id_to_uint4(id16), t->task_id, t->creator_ref,
+                                                   t->ids_sorted ? nullptr : t->id_order, t->n, sorted,
+                                                   reinterpret_cast<unsigned int*>(t->d_small));
+  TT_CUDA(cudaGetLastError());
+  TT_CUDA(cudaMemcpyAsync(t->h_small, t->d_small, 8, cudaMemcpyDeviceToHost, t->stream));
+  TT_CUDA(cudaStreamSynchronize(t->stream));
+  const uint32_t r = (uint32_t)(t->h_small[0] & 0xFFFFFFFFull);
+  if (r != 0xFFFFFFFFu) *row = r;
+  return TT_OK;
+}
+
+int32_t poke(tt_table* t, const tt::RowPoke& p) {
+  tt::poke_row_kernel<<<1, 1, 0, t->stream>>>(p, t->due_code, t->completed, t->overdue, t->creator_hash, t->task_id,
+                                             t->created_raw, t->due_raw, t->creator_ref);
+  TT_CUDA(cudaGetLastError());
+  TT_CUDA(cudaStreamSynchronize(t->stream));
+  return TT_OK;
+}
+
+template <typename T>
+int32_t grow_buffer(tt_table* t, T** buf, size_t old_count, size_t new_count, int fill) {
+  T* fresh = nullptr;
+  TT_CUDA(cudaMalloc(&fresh, new_count * sizeof(T)));
+  TT_CUDA(cudaMemsetAsync(fresh, fill, new_count * sizeof(T), t->stream));
+  if (*buf && old_count) TT_CUDA(cudaMemcpyAsync(fresh, *buf, old_count * sizeof(T), cudaMemcpyDeviceToDevice, t->stream));
+  TT_CUDA(cudaStreamSynchronize(t->stream));
+  cudaFree(*buf);
+  *buf = fresh;
+  return TT_OK;
+}
+
+// Doubles the row capacity (simple and unoptimised: every column is reallocated and copied).
+int32_t grow_rows(tt_table* t) {
+  const int64_t old_pad = t->n_pad, np = std::max<int64_t>(2 * old_pad, TT_TILE_ROWS);
+  if (np > kMaxRows) return fail(TT_ERR_OOM, "table is at its maximum of 2^31 rows");
+  int32_t rc;
+  if ((rc = grow_buffer(t, &t->due_code, old_pad, np, 0xFF))) return rc;
+  if ((rc = grow_buffer(t, &t->completed, old_pad / 32, np / 32, 0))) return rc;
+  if ((rc = grow_buffer(t, &t->overdue, old_pad / 32, np / 32, 0))) return rc;
+  if ((rc = grow_buffer(t, &t->creator_hash, old_pad, np, 0))) return rc;
+  if ((rc = grow_buffer(t, &t->task_id, old_pad, np, 0))) return rc;
+  if ((rc = grow_buffer(t, &t->created_raw, old_pad, np, 0))) return rc;
+  if ((rc = grow_buffer(t, &t->due_raw, old_pad, np, 0))) return rc;
+  if ((rc = grow_buffer(t, &t->creator_ref, old_pad, np, 0))) return rc;
+  cudaFree(t->tile_words);
+  cudaFree(t->group_sum);
+  t->tile_words = t->group_sum = nullptr;
+  t->n_tiles = np / TT_TILE_ROWS;
+  t->n_groups = (t->n_tiles + tt::kTilesPerGroup - 1) / tt::kTilesPerGroup;
+  TT_CUDA(cudaMalloc(&t->tile_words, 3 * t->n_tiles * 4));
+  TT_CUDA(cudaMalloc(&t->group_sum, t->n_groups * 4));
+  t->n_pad = np;
+  return TT_OK;
+}
+
+// Host mirror of the creator dictionary, built once from the device copy.
+int32_t mirror_dictionary(tt_table* t) {
+  if (t->dict_mirrored) return TT_OK;
+  t->h_creator_off.assign((size_t)t->n_creators + 1, 0);
+  t->h_creator_pool.assign(t->pool_bytes, 0);
+  if (t->n_creators) {
+    TT_CUDA(cudaMemcpy(t->h_creator_off.data(), t->creator_off, ((size_t)t->n_creators + 1) * 4, cudaMemcpyDeviceToHost));
+    if (t->pool_bytes) TT_CUDA(cudaMemcpy(t->h_creator_pool.data(), t->creator_pool, t->pool_bytes, cudaMemcpyDeviceToHost));
+  }
+  t->h_creator_index.clear();
+  t->h_creator_index.reserve((size_t)t->n_creators * 2 + 16);
+  for (uint32_t k = 0; k < t->n_creators; ++k)
+    t->h_creator_index.emplace(std::string((const char*)t->h_creator_pool.data() + t->h_creator_off[k],
+                                           t->h_creator_off[k + 1] - t->h_creator_off[k]), k);
+  t->dict_mirrored = true;
+  return TT_OK;
+}
+
+// Dictionary index of a creator string, appending it (host mirror and device arrays) if new.
+int32_t intern_creator(tt_table* t, const char* utf8, int32_t len, uint32_t* ref) {
+  int32_t rc = mirror_dictionary(t);
+  if (rc) return rc;
+  std::string key(utf8 ? utf8 : "", (size_t)len);
+  auto it = t->h_creator_index.find(key);
+  if (it != t->h_creator_index.end()) {
+    *ref = it->second;
+    return TT_OK;
+  }
+  if (t->n_creators == 0xFFFFFFFEu) return fail(TT_ERR_OOM, "creator dictionary is full");
+  const uint32_t k = t->n_creators;
+  const uint32_t start = (uint32_t)t->pool_bytes;
+  if ((size_t)k + 2 > t->creator_off_cap) {
+    const size_t want = std::max<size_t>(2 * t->creator_off_cap, 1024);
+    if ((rc = grow_buffer(t, &t->creator_off, (size_t)k + 1, want, 0))) return rc;
+    t->creator_off_cap = want;
+  }
+  if (t->pool_bytes + (size_t)len > t->creator_pool_cap) {
+    const size_t want = std::max<size_t>(2 * t->creator_pool_cap, t->pool_bytes + (size_t)len + 65536);
+    if ((rc = grow_buffer(t, &t->creator_pool, (size_t)t->pool_bytes, want, 0))) return rc;
+    t->creator_pool_cap = want;
+  }
+  if (t->h_creator_off.empty()) t->h_creator_off.push_back(0);
+  t->h_creator_pool.insert(t->h_creator_pool.end(), key.begin(), key.end());
+  t->h_creator_off.push_back(start + (uint32_t)len);
+  const uint32_t tail[2] = {start, start + (uint32_t)len};
+  TT_CUDA(cudaMemcpyAsync(t->creator_off + k, tail, 8, cudaMemcpyHostToDevice, t->stream));
+  if (len) TT_CUDA(cudaMemcpyAsync(t->creator_pool + start, key.data(), (size_t)len, cudaMemcpyHostToDevice, t->stream));
+  TT_CUDA(cudaStreamSynchronize(t->stream));
+  t->h_creator_index.emplace(std::move(key), k);
+  t->n_creators = k + 1;
+  t->pool_bytes += (uint64_t)len;
+  *ref = k;
+  return TT_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int32_t tt_get_by_id(tt_table* t, const uint8_t* id16, tt_result** out) {
+  if (!t || !id16 || !out) return fail(TT_ERR_ARG, "null argument");
+  *out = nullptr;
+  std::lock_guard<std::mutex> lk(t->mu);
+  DeviceGuard g(t->device);
+  int64_t row = -1;
+  int32_t rc = find_row(t, id16, &row);
+  if (rc) return rc;
+  tt_result* r = nullptr;
+  rc = result_alloc(t, 1, &r);
+  if (rc) return rc;
+  if (row >= 0) {
+    const uint32_t r32 = (uint32_t)row;
+    cudaError_t e = cudaMemcpyAsync(r->d_rows, &r32, 4, cudaMemcpyHostToDevice, t->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(r->d_ids, id16, 16, cudaMemcpyHostToDevice, t->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(t->stream);
+    if (e != cudaSuccess) {
+      result_release(r);
+      TT_CUDA(e);
+    }
+    r->n = 1;
+  }
+  *out = r;
+  return TT_OK;
+}
+
+int32_t tt_mark_completed(tt_table* t, const uint8_t* id16, int32_t* found) {
+  if (!t || !id16) return fail(TT_ERR_ARG, "null argument");
+  if (found) *found = 0;
+  std::lock_guard<std::mutex> lk(t->mu);
+  DeviceGuard g(t->device);
+  int64_t row = -1;
+  int32_t rc = find_row(t, id16, &row);
+  if (rc || row < 0) return rc;
+  tt::RowPoke p = {};
+  p.row = (uint32_t)row;
+  p.set_completed = 1;
+  p.completed = 1;
+  if ((rc = poke(t, p))) return rc;
+  if (found) *found = 1;
+  return TT_OK;
+}
+
+int32_t tt_update_task(tt_table* t, const uint8_t* id16, uint64_t due_raw, int32_t* found) {
+  if (!t || !id16) return fail(TT_ERR_ARG, "null argument");
+  if (found) *found = 0;
+  std::lock_guard<std::mutex> lk(t->mu);
+  DeviceGuard g(t->device);
+  int64_t row = -1;
+  int32_t rc = find_row(t, id16, &row);
+  if (rc || row < 0) return rc;
+  tt::RowPoke p = {};
+  p.row = (uint32_t)row;
+  p.set_due = 1;
+  p.due_raw = due_raw;
+  p.due_code = tt_pack_due(due_raw);
+  if ((rc = poke(t, p))) return rc;
+  if (found) *found = 1;
+  return TT_OK;
+}
+
+int32_t tt_delete_task(tt_table* t, const uint8_t* id16, int32_t* found) {
+  if (!t || !id16) return fail(TT_ERR_ARG, "null argument");
+  if (found) *found = 0;
+  std::lock_guard<std::mutex> lk(t->mu);
+  DeviceGuard g(t->device);
+  int64_t row = -1;
+  int32_t rc = find_row(t, id16, &row);
+  if (rc || row < 0) return rc;
+  // the row stays as a tombstone: it can match no sweep, no creator and no id any more
+  tt::RowPoke p = {};
+  p.row = (uint32_t)row;
+  p.set_due = p.set_creator = p.set_completed = p.set_overdue = 1;
+  p.due_raw = 0;
+  p.due_code = TT_DUE_PAD;
+  p.creator_ref = tt::kRowDeleted;
+  p.creator_hash = 0;
+  if ((rc = poke(t, p))) return rc;
+  t->n_live -= 1;
+  if (found) *found = 1;
+  return TT_OK;
+}
+
+int32_t tt_insert_task(tt_table* t, const uint8_t* id16, uint64_t created_raw, uint64_t due_raw, const char* created_by,
+                       int32_t len, int64_t* row_out) {
+  if (!t || !id16 || len < 0 || (len > 0 && !created_by)) return fail(TT_ERR_ARG, "bad argument");
+  std::lock_guard<std::mutex> lk(t->mu);
+  DeviceGuard g(t->device);
+  int32_t rc;
+  if (t->n_pad == 0) {
+    if ((rc = alloc_columns(t, 0))) return rc;
+    static const uint32_t zero_off[1] = {0};
+    if ((rc = upload_dictionary(t, 0, zero_off, nullptr))) return rc;
+    TT_CUDA(cudaStreamSynchronize(t->stream));
+    t->ids_sorted = true;
+  }
+  if (t->n >= kMaxRows) return fail(TT_ERR_OOM, "table is at its maximum of 2^31 rows");
+  if (t->n == t->n_pad && (rc = grow_rows(t))) return rc;
+  uint32_t ref = 0;
+  if ((rc = intern_creator(t, created_by, len, &ref))) return rc;
+  // does the table stay in TaskId order?  (then lookups keep using the binary search)
+  if (t->ids_sorted && t->n > 0) {
+    if (!t->last_id_known) {
+      TT_CUDA(cudaMemcpy(t->last_id, t->task_id + (t->n - 1), 16, cudaMemcpyDeviceToHost));
+      t->last_id_known = true;
+    }
+    if (memcmp(t->last_id, id16, 16) >= 0) t->ids_sorted = false;
+  }
+  if (!t->ids_sorted && t->id_order) {  // the TaskId index no longer covers every row: scan instead
+    cudaFree(t->id_order);
+    t->id_order = nullptr;
+  }
+  memcpy(t->last_id, id16, 16);
+  t->last_id_known = true;
+  tt::RowPoke p = {};
+  p.row = (uint32_t)t->n;
+  p.set_id = p.set_created = p.set_due = p.set_creator = p.set_completed = p.set_overdue = 1;
+  p.id = id_to_uint4(id16);
+  p.created_raw = created_raw;
+  p.due_raw = due_raw;
+  p.due_code = tt_pack_due(due_raw);
+  p.creator_ref = ref;
+  p.creator_hash = tt_hash64((const uint8_t*)created_by, (uint32_t)len);
+  if ((rc = poke(t, p))) return rc;
+  if (row_out) *row_out = t->n;
+  t->n += 1;
+  t->n_live += 1;
+  return TT_OK;
+}
+
+int32_t tt_live_count(tt_table* t, int64_t* n) {
+  if (!t || !n) return fail(TT_ERR_ARG, "null argument");
+  *n = t->n_live;
   return TT_OK;
 }
 

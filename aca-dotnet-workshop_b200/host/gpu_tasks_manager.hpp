@@ -57,11 +57,17 @@ struct TasksManagerException : std::runtime_error {
   TasksManagerException(int32_t c, const std::string& m) : std::runtime_error(m), code(c) {}
 };
 
-// The three methods of ITasksManager that are on the accelerated path.  (The CRUD point
-// operations of the interface are not data-parallel and are out of scope)
+// Api/Services/ITasksManager.cs:5-15, method for method (Task<T> becomes T: the calls block).
 struct ITasksManager {
   virtual ~ITasksManager() = default;
   virtual std::vector<TaskModel> GetTasksByCreator(const std::string& createdBy) = 0;
+  virtual bool GetTaskById(const Guid& taskId, TaskModel* out) = 0;  // false = the reference's null
+  virtual Guid CreateNewTask(const std::string& taskName, const std::string& createdBy, const std::string& assignedTo,
+                             DateTime dueDate) = 0;
+  virtual bool UpdateTask(const Guid& taskId, const std::string& taskName, const std::string& assignedTo,
+                          DateTime dueDate) = 0;
+  virtual bool MarkTaskCompleted(const Guid& taskId) = 0;
+  virtual bool DeleteTask(const Guid& taskId) = 0;
   virtual void MarkOverdueTasks(std::vector<TaskModel>& overDueTasksList) = 0;
   virtual std::vector<TaskModel> GetYesterdaysDueTasks() = 0;
 };
@@ -82,6 +88,8 @@ class TaskTableLibrary {
     TT_BIND(tt_get_yesterdays_due); TT_BIND(tt_mark_overdue); TT_BIND(tt_sweep); TT_BIND(tt_get_by_creator);
     TT_BIND(tt_result_count); TT_BIND(tt_result_rows); TT_BIND(tt_result_ids); TT_BIND(tt_result_field);
     TT_BIND(tt_result_free);
+    TT_BIND(tt_get_by_id); TT_BIND(tt_insert_task); TT_BIND(tt_update_task); TT_BIND(tt_mark_completed);
+    TT_BIND(tt_delete_task);
 #undef TT_BIND
   }
   ~TaskTableLibrary() { if (h_) dlclose(h_); }
@@ -98,6 +106,11 @@ class TaskTableLibrary {
   decltype(&::tt_result_ids) tt_result_ids;
   decltype(&::tt_result_field) tt_result_field;
   decltype(&::tt_result_free) tt_result_free;
+  decltype(&::tt_get_by_id) tt_get_by_id;
+  decltype(&::tt_insert_task) tt_insert_task;
+  decltype(&::tt_update_task) tt_update_task;
+  decltype(&::tt_mark_completed) tt_mark_completed;
+  decltype(&::tt_delete_task) tt_delete_task;
 
  private:
   void* must(const char* name) {
@@ -170,6 +183,63 @@ class GpuTasksManager : public ITasksManager {
     return materialise(r);
   }
 
+  // ---- the single-row methods (FakeTasksManager.cs:32-100 / TasksStoreManager.cs:22-102) ----
+  bool GetTaskById(const Guid& taskId, TaskModel* out) override {
+    tt_result* r = nullptr;
+    check(lib_->tt_get_by_id(table_, taskId.data(), &r));
+    std::vector<TaskModel> found = materialise(r);
+    if (found.empty()) return false;
+    if (out) *out = found[0];
+    return true;
+  }
+
+  Guid CreateNewTask(const std::string& taskName, const std::string& createdBy, const std::string& assignedTo,
+                     DateTime dueDate) override {
+    Guid id = NewGuid();
+    int64_t row = -1;
+    check(lib_->tt_insert_task(table_, id.data(), (uint64_t)clock_->utc_now_ticks | (1ull << 62), dueDate.dateData,
+                               createdBy.data(), (int32_t)createdBy.size(), &row));
+    bool known = false;
+    for (const std::string& c : creators_) known = known || c == createdBy;
+    if (!known) creators_.push_back(createdBy);  // the library appends new creators in the same order
+    names_.push_back(taskName);
+    assignees_.push_back(assignedTo);
+    return id;
+  }
+
+  bool UpdateTask(const Guid& taskId, const std::string& taskName, const std::string& assignedTo,
+                  DateTime dueDate) override {
+    tt_result* r = nullptr;
+    check(lib_->tt_get_by_id(table_, taskId.data(), &r));
+    int64_t n = 0;
+    uint32_t row = 0;
+    check(lib_->tt_result_count(r, &n));
+    if (n) check(lib_->tt_result_rows(r, &row));
+    lib_->tt_result_free(r);
+    if (!n) {
+      if (mode_ == TT_MODE_STORE)  // TasksStoreManager.cs:88 dereferences the missing document
+        throw std::logic_error("NullReferenceException");
+      return false;
+    }
+    names_[row] = taskName;
+    assignees_[row] = assignedTo;
+    int32_t found = 0;
+    check(lib_->tt_update_task(table_, taskId.data(), dueDate.dateData, &found));
+    return found != 0;
+  }
+
+  bool MarkTaskCompleted(const Guid& taskId) override {
+    int32_t found = 0;
+    check(lib_->tt_mark_completed(table_, taskId.data(), &found));
+    return found != 0;
+  }
+
+  bool DeleteTask(const Guid& taskId) override {
+    int32_t found = 0;
+    check(lib_->tt_delete_task(table_, taskId.data(), &found));
+    return mode_ == TT_MODE_STORE ? true : found != 0;  // DeleteStateAsync answers true either way
+  }
+
   // The whole tick as one device pass (tt_sweep).  Returns the listed tasks; *n_marked = rows set.
   std::vector<TaskModel> SweepOverdueTasks(int64_t* n_marked) {
     tt_result* r = nullptr;
@@ -181,6 +251,19 @@ class GpuTasksManager : public ITasksManager {
   }
 
  private:
+  // Guid.NewGuid(): RFC 4122 version 4 from a splitmix stream (deterministic for the demo)
+  Guid NewGuid() {
+    Guid g;
+    for (int half = 0; half < 2; ++half) {
+      uint64_t v = tt_mix64(guid_state_++);
+      for (int i = 0; i < 8; ++i) g[8 * half + i] = (uint8_t)(v >> (8 * i));
+    }
+    g[6] = (uint8_t)((g[6] & 0x0F) | 0x40);
+    g[8] = (uint8_t)((g[8] & 0x3F) | 0x80);
+    return g;
+  }
+  uint64_t guid_state_ = 0x1234;
+
   void check(int32_t rc) {
     if (rc == TT_OK) return;
     if (rc == TT_ERR_NOT_IMPLEMENTED) throw NotImplementedException();

@@ -61,6 +61,15 @@ int main(int argc, char** argv) {
       printf("\nann:");
       for (const TaskModel& t : manager.GetTasksByCreator("ann@x.io")) printf(" %s%s", t.TaskName.c_str(), t.IsOverDue ? "*" : "");
       printf("\n");
+      // the single-row methods of the interface
+      Guid id = manager.CreateNewTask("Task new", "ann@x.io", "q@y.z", dt(TT_DEFAULT_TODAY_TICKS - TT_TICKS_PER_DAY, 0));
+      TaskModel got;
+      bool found = manager.GetTaskById(id, &got);
+      bool done = manager.MarkTaskCompleted(id);
+      manager.GetTaskById(id, &got);
+      printf("new: found=%d name=%s completed=%d", found, got.TaskName.c_str(), got.IsCompleted);
+      bool del = manager.DeleteTask(id), again = manager.DeleteTask(id);
+      printf(" marked=%d deleted=%d again=%d gone=%d\n", done, del, again, !manager.GetTaskById(id, nullptr));
     }
   } catch (const std::exception& e) {
     fprintf(stderr, "error: %s\n", e.what());

@@ -49,8 +49,10 @@ class GpuTasksManager:
     stands for DateTime.Today, `run_at_utc_ticks` for DateTime.UtcNow in the cron handler.
     """
 
-    def __init__(self, tasks: List[TaskModel], mode=tt.MODE_STORE, device=0):
+    def __init__(self, tasks: List[TaskModel], mode=tt.MODE_STORE, device=0, new_guid=uuid.uuid4, utc_now=None):
         self.mode = mode
+        self._new_guid = new_guid            # Guid.NewGuid()
+        self._utc_now = utc_now or (lambda: date_data(tt.DEFAULT_RUN_AT, KIND_UTC))  # DateTime.UtcNow
         self._names = [t.TaskName for t in tasks]
         self._assignees = [t.TaskAssignedTo for t in tasks]
         creators = {}
@@ -58,7 +60,7 @@ class GpuTasksManager:
         for i, t in enumerate(tasks):
             b = t.TaskCreatedBy.encode("utf-8")
             refs[i] = creators.setdefault(b, len(creators))
-        self._creators = list(creators.keys())
+        self._creators = list(creators.keys()) or [b""]  # mirrors the library's dictionary, index for index
         ids = np.frombuffer(b"".join(t.TaskId.bytes for t in tasks), dtype=np.uint8).reshape(-1, 16)
         self._table = tt.TaskTable(device).load_soa(
             ids,
@@ -67,7 +69,7 @@ class GpuTasksManager:
             np.array([t.IsCompleted for t in tasks], dtype=np.uint8),
             np.array([t.IsOverDue for t in tasks], dtype=np.uint8),
             refs,
-            self._creators or [b""],
+            self._creators,
         )
 
     @property
@@ -84,10 +86,59 @@ class GpuTasksManager:
         ref = result.field(tt.FIELD_CREATOR_REF)
         out = []
         for k, r in enumerate(rows.tolist()):
-            out.append(TaskModel(uuid.UUID(bytes=ids[k].tobytes()), self._names[r], self._creators[ref[k]].decode("utf-8"),
+            out.append(TaskModel(uuid.UUID(bytes=ids[k].tobytes()), self._names[r], self._creator_name(int(ref[k])),
                                  int(created[k]), int(due[k]), self._assignees[r], bool(comp[k]), bool(over[k])))
         result.free()
         return out
+
+    def _creator_name(self, ref):
+        return self._creators[ref].decode("utf-8")
+
+    # ITasksManager.cs:8
+    def GetTaskById(self, taskId: uuid.UUID) -> Optional[TaskModel]:
+        found = self._materialise(self._table.get_by_id(taskId.bytes))
+        return found[0] if found else None
+
+    # ITasksManager.cs:9 — FakeTasksManager.cs:32-47 / TasksStoreManager.cs:22-38
+    def CreateNewTask(self, taskName: str, createdBy: str, assignedTo: str, dueDate: int) -> uuid.UUID:
+        task_id = self._new_guid()
+        b = createdBy.encode("utf-8")
+        if b not in self._creator_set():
+            self._creators.append(b)  # the library appends new creators in the same order
+            self._creator_lookup.add(b)
+        row = self._table.insert_task(task_id.bytes, self._utc_now(), dueDate, b)
+        assert row == len(self._names)
+        self._names.append(taskName)
+        self._assignees.append(assignedTo)
+        return task_id
+
+    def _creator_set(self):
+        if not hasattr(self, "_creator_lookup"):
+            self._creator_lookup = set(self._creators)
+        return self._creator_lookup
+
+    # ITasksManager.cs:10 — FakeTasksManager.cs:87-100 / TasksStoreManager.cs:84-102
+    def UpdateTask(self, taskId: uuid.UUID, taskName: str, assignedTo: str, dueDate: int) -> bool:
+        res = self._table.get_by_id(taskId.bytes)
+        rows = res.rows()
+        res.free()
+        if rows.size == 0:
+            if self.mode == tt.MODE_STORE:
+                # TasksStoreManager.cs:88 dereferences the missing document before its null check
+                raise AttributeError("NullReferenceException: Object reference not set to an instance of an object")
+            return False
+        self._names[int(rows[0])] = taskName
+        self._assignees[int(rows[0])] = assignedTo
+        return self._table.update_task(taskId.bytes, dueDate)
+
+    # ITasksManager.cs:11
+    def MarkTaskCompleted(self, taskId: uuid.UUID) -> bool:
+        return self._table.mark_completed(taskId.bytes)
+
+    # ITasksManager.cs:12 — the state-store version reports true whether or not the key existed
+    def DeleteTask(self, taskId: uuid.UUID) -> bool:
+        found = self._table.delete_task(taskId.bytes)
+        return True if self.mode == tt.MODE_STORE else found
 
     # ITasksManager.cs:14
     def GetYesterdaysDueTasks(self, today_local_ticks=tt.DEFAULT_TODAY) -> List[TaskModel]:

@@ -45,6 +45,7 @@ EXPORTS = [
     "tt_result_count", "tt_result_rows", "tt_result_ids", "tt_result_field", "tt_result_free",
     "tt_snapshot_flags", "tt_restore_flags", "tt_count_flags", "tt_result_digest",
     "tt_sweep_device", "tt_get_device_view", "tt_sweep_static", "tt_get_by_creators", "tt_last_op_stats",
+    "tt_get_by_id", "tt_insert_task", "tt_update_task", "tt_mark_completed", "tt_delete_task", "tt_live_count",
 ]
 
 
@@ -170,6 +171,12 @@ def lib():
     L.tt_get_by_creator.argtypes = [vp, C.c_char_p, i32, P(vp)]
     L.tt_get_by_creators.argtypes = [vp, P(C.c_char_p), P(i32), i32, P(vp)]
     L.tt_last_op_stats.argtypes = [vp, P(OpStats)]
+    L.tt_get_by_id.argtypes = [vp, vp, P(vp)]
+    L.tt_insert_task.argtypes = [vp, vp, u64, u64, C.c_char_p, i32, P(i64)]
+    L.tt_update_task.argtypes = [vp, vp, u64, P(i32)]
+    L.tt_mark_completed.argtypes = [vp, vp, P(i32)]
+    L.tt_delete_task.argtypes = [vp, vp, P(i32)]
+    L.tt_live_count.argtypes = [vp, P(i64)]
     L.tt_result_count.argtypes = [vp, P(i64)]
     L.tt_result_rows.argtypes = [vp, vp]
     L.tt_result_ids.argtypes = [vp, vp]
@@ -323,6 +330,49 @@ class TaskTable:
         st = OpStats()
         _check(lib().tt_last_op_stats(self._h, C.byref(st)))
         return st
+
+    # -- single-row operations (ITasksManager.cs:8-12) -----------------------------------------
+    @staticmethod
+    def _id(task_id):
+        a = np.frombuffer(bytes(task_id), dtype=np.uint8).copy()
+        assert a.size == 16
+        return a
+
+    def get_by_id(self, task_id):
+        r = C.c_void_p()
+        a = self._id(task_id)
+        _check(lib().tt_get_by_id(self._h, _ptr(a), C.byref(r)))
+        return Result(r)
+
+    def insert_task(self, task_id, created_raw, due_raw, created_by):
+        b = created_by.encode() if isinstance(created_by, str) else bytes(created_by)
+        row = C.c_int64(-1)
+        a = self._id(task_id)
+        _check(lib().tt_insert_task(self._h, _ptr(a), created_raw, due_raw, b, len(b), C.byref(row)))
+        return row.value
+
+    def update_task(self, task_id, due_raw):
+        f = C.c_int32(0)
+        a = self._id(task_id)
+        _check(lib().tt_update_task(self._h, _ptr(a), due_raw, C.byref(f)))
+        return bool(f.value)
+
+    def mark_completed(self, task_id):
+        f = C.c_int32(0)
+        a = self._id(task_id)
+        _check(lib().tt_mark_completed(self._h, _ptr(a), C.byref(f)))
+        return bool(f.value)
+
+    def delete_task(self, task_id):
+        f = C.c_int32(0)
+        a = self._id(task_id)
+        _check(lib().tt_delete_task(self._h, _ptr(a), C.byref(f)))
+        return bool(f.value)
+
+    def live_count(self):
+        n = C.c_int64(0)
+        _check(lib().tt_live_count(self._h, C.byref(n)))
+        return n.value
 
     # -- device-resident sweep ---------------------------------------------------------------
     def sweep_device(self, mode, flags, d_rows, d_ids, cap, today=DEFAULT_TODAY, run_at=DEFAULT_RUN_AT, first_row=0,

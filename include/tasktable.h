@@ -141,6 +141,32 @@ typedef struct tt_op_stats {
 } tt_op_stats;
 int32_t tt_last_op_stats(tt_table* t, tt_op_stats* out);
 
+/* ---- the single-row operations of ITasksManager ------------------------------------------
+ * Not data-parallel and kept simple (a lookup kernel + a one-thread field write); they exist so
+ * the table can stand behind the whole interface.  TaskName / TaskAssignedTo stay with the host
+ * wrapper, and so does generating the Guid and reading the clock.  *found = 1 if a task with
+ * that id exists (the reference's `true` / non-null result), 0 otherwise. */
+
+/* ITasksManager.GetTaskById (ITasksManager.cs:8; FakeTasksManager.cs:62-66,
+ * TasksStoreManager.cs:47-52): a result with one row, or an empty one. */
+int32_t tt_get_by_id(tt_table* t, const uint8_t* id16, tt_result** out);
+/* ITasksManager.CreateNewTask (ITasksManager.cs:9; FakeTasksManager.cs:32-47,
+ * TasksStoreManager.cs:22-38): appends a pending task at the end of the list; *row = its row. */
+int32_t tt_insert_task(tt_table* t, const uint8_t* id16, uint64_t created_raw, uint64_t due_raw, const char* created_by_utf8,
+                       int32_t len, int64_t* row);
+/* ITasksManager.UpdateTask (ITasksManager.cs:10; FakeTasksManager.cs:87-100,
+ * TasksStoreManager.cs:84-102): the due date is the only updated field a kernel reads. */
+int32_t tt_update_task(tt_table* t, const uint8_t* id16, uint64_t due_raw, int32_t* found);
+/* ITasksManager.MarkTaskCompleted (ITasksManager.cs:11; FakeTasksManager.cs:74-85,
+ * TasksStoreManager.cs:71-82). */
+int32_t tt_mark_completed(tt_table* t, const uint8_t* id16, int32_t* found);
+/* ITasksManager.DeleteTask (ITasksManager.cs:12; FakeTasksManager.cs:49-60,
+ * TasksStoreManager.cs:40-45).  The row becomes a tombstone; row numbers of other tasks and
+ * their relative order do not change. */
+int32_t tt_delete_task(tt_table* t, const uint8_t* id16, int32_t* found);
+/* Tasks in the table, not counting deleted ones (tt_row_count counts rows, tombstones included). */
+int32_t tt_live_count(tt_table* t, int64_t* n);
+
 /* ---- results --------------------------------------------------------------------------- */
 
 int32_t tt_result_count(const tt_result* r, int64_t* n);

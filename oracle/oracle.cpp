@@ -15,6 +15,8 @@
 //   Api = TasksTracker.TasksManager.Backend.Api, Svc = TasksTracker.Processor.Backend.Svc
 //   Api/Models/TaskModel.cs:3-13                     -> struct TaskModel
 //   Api/Services/FakeTasksManager.cs:10-25           -> FakeTasksManager::GenerateRandomTasks
+//   Api/Services/FakeTasksManager.cs:32-100          -> FakeTasksManager point operations (Create/Delete/GetById/MarkCompleted/Update)
+//   Api/Services/TasksStoreManager.cs:22-102         -> TasksStoreManager point operations
 //   Api/Services/FakeTasksManager.cs:68-72           -> FakeTasksManager::GetTasksByCreator
 //   Api/Services/FakeTasksManager.cs:102-105         -> FakeTasksManager::MarkOverdueTasks (throws)
 //   Api/Services/FakeTasksManager.cs:107-112         -> FakeTasksManager::GetYesterdaysDueTasks
@@ -180,9 +182,11 @@ struct TaskModel {
   bool IsCompleted = false;
   bool IsOverDue = false;
   int64_t row = -1;  // insertion index; test bookkeeping, not a reference field
+  bool deleted = false;  // bookkeeping: removed from the list / store
 };
 
 struct NotImplementedException {};
+struct NullReferenceException {};
 
 // Clock inputs the reference reads from the environment, made explicit.
 struct Clock {
@@ -202,6 +206,30 @@ inline bool OrdinalEquals(const std::u16string& a, const std::u16string& b) {
 // ---- Api/Services/FakeTasksManager.cs ---------------------------------------------------
 struct FakeTasksManager {
   const TaskList& _tasksList;  // List<TaskModel> _tasksList (:7)
+
+  // :62-66  _tasksList.FirstOrDefault(t => t.TaskId.Equals(taskId))
+  TaskModel* GetTaskById(const Guid& taskId) const {
+    for (TaskModel* t : _tasksList)
+      if (t->TaskId.Equals(taskId)) return t;
+    return nullptr;
+  }
+  // :74-85
+  bool MarkTaskCompleted(const Guid& taskId) const {
+    TaskModel* task = GetTaskById(taskId);
+    if (task != nullptr) { task->IsCompleted = true; return true; }
+    return false;
+  }
+  // :87-100
+  bool UpdateTask(const Guid& taskId, const std::u16string& taskName, const std::u16string& assignedTo, DateTime dueDate) const {
+    TaskModel* task = GetTaskById(taskId);
+    if (task != nullptr) {
+      task->TaskName = taskName;
+      task->TaskAssignedTo = assignedTo;
+      task->TaskDueDate = dueDate;
+      return true;
+    }
+    return false;
+  }
 
   // :107-112  _tasksList.Where(t => t.TaskDueDate.Equals(DateTime.Today.AddDays(-1))).ToList()
   TaskList GetYesterdaysDueTasks(const Clock& clk) const {
@@ -233,8 +261,31 @@ struct FakeTasksManager {
 // (key = TaskId.ToString(), :35).  The store-side EQ filter is exact string equality on the
 // stored JSON value.
 struct TasksStoreManager {
-  TaskList* docs;
-  std::unordered_map<std::string, int64_t>* keys;
+  TaskList* docs;                                   // the stored documents, in store order
+  std::unordered_map<std::string, int64_t>* keys;   // key -> insertion index
+  TaskList* by_row;                                 // insertion index -> document
+
+  // :47-52  GetStateAsync<TaskModel>(key): the stored document or null
+  TaskModel* GetTaskById(const Guid& taskId) const {
+    for (TaskModel* t : *docs)
+      if (t->TaskId.Equals(taskId)) return t;
+    return nullptr;
+  }
+  // :71-82
+  bool MarkTaskCompleted(const Guid& taskId) const {
+    TaskModel* taskModel = GetTaskById(taskId);
+    if (taskModel != nullptr) { taskModel->IsCompleted = true; return true; }
+    return false;
+  }
+  // :84-102 — `taskModel.TaskAssignedTo` is read before the null check (:88): a missing id throws
+  bool UpdateTask(const Guid& taskId, const std::u16string& taskName, const std::u16string& assignedTo, DateTime dueDate) const {
+    TaskModel* taskModel = GetTaskById(taskId);
+    if (taskModel == nullptr) throw NullReferenceException();
+    taskModel->TaskName = taskName;
+    taskModel->TaskAssignedTo = assignedTo;
+    taskModel->TaskDueDate = dueDate;
+    return true;
+  }
 
   static bool EqDueDate(const TaskModel* t, const DateTime& yesterday, const std::string& literal, const Clock& clk) {
     if (clk.string_eq) return FormatSystemTextJson(t->TaskDueDate, clk.local_offset_min) == literal;
@@ -266,7 +317,7 @@ struct TasksStoreManager {
       taskModel.IsOverDue = true;
       auto it = keys->find(taskModel.TaskId.ToString());
       if (it == keys->end()) { ++created; continue; }  // upsert of an unknown key: counted, not stored
-      TaskModel* doc = (*docs)[it->second];
+      TaskModel* doc = (*by_row)[it->second];
       int64_t row = doc->row;
       *doc = taskModel;  // the whole record is overwritten with the caller's copy
       doc->row = row;
@@ -287,17 +338,25 @@ struct TasksStoreManager {
 };
 
 struct OracleTable {
-  TaskList rows;  // owns the TaskModel objects
+  TaskList rows;  // every task ever added, by insertion index; owns the TaskModel objects
+  TaskList live;  // the reference's _tasksList / the store's documents, in list order
   std::unordered_map<std::string, int64_t> keys;
   bool keys_built = false;
   ~OracleTable() { for (TaskModel* t : rows) delete t; }
   void BuildKeys() {
     if (keys_built) return;
-    keys.reserve(rows.size() * 2);
-    for (TaskModel* t : rows) keys[t->TaskId.ToString()] = t->row;
+    keys.clear();
+    keys.reserve(live.size() * 2);
+    for (TaskModel* t : live) keys[t->TaskId.ToString()] = t->row;
     keys_built = true;
   }
-  void Add(TaskModel* t) { t->row = (int64_t)rows.size(); rows.push_back(t); keys_built = false; }
+  void Add(TaskModel* t) { t->row = (int64_t)rows.size(); rows.push_back(t); live.push_back(t); keys_built = false; }
+  // List<T>.Remove(item) / DeleteStateAsync(key): later items keep their relative order
+  void Remove(TaskModel* t) {
+    live.erase(std::find(live.begin(), live.end(), t));
+    t->deleted = true;
+    keys_built = false;
+  }
 };
 
 void GuidFromHiLo(uint64_t hi, uint64_t lo, Guid* g) {
@@ -401,10 +460,10 @@ int64_t orc_get_yesterdays_due(orc_table* t, int32_t mode, int64_t today_local_t
   Clock clk = MakeClock(today_local_ticks, 0, local_offset_min, string_eq);
   std::vector<int64_t> rows;
   if (mode == ORC_MODE_FAKE) {
-    FakeTasksManager m{t->rows};
+    FakeTasksManager m{t->live};
     for (TaskModel* x : m.GetYesterdaysDueTasks(clk)) rows.push_back(x->row);
   } else {
-    TasksStoreManager m{&t->rows, &t->keys};
+    TasksStoreManager m{&t->live, &t->keys, &t->rows};
     for (const TaskModel& x : m.GetYesterdaysDueTasks(clk)) rows.push_back(x.row);
   }
   return Emit(rows, out_rows, cap);
@@ -421,7 +480,7 @@ int32_t orc_cron_job(orc_table* t, int32_t mode, int64_t today_local_ticks, int6
   std::vector<int64_t> listed;
   int32_t status = 0;
   if (mode == ORC_MODE_FAKE) {
-    FakeTasksManager m{t->rows};
+    FakeTasksManager m{t->live};
     TaskList tasksList = m.GetYesterdaysDueTasks(clk);  // :28
     TaskList overdueTasksList;
     for (TaskModel* taskModel : tasksList) {            // :32-38
@@ -434,7 +493,7 @@ int32_t orc_cron_job(orc_table* t, int32_t mode, int64_t today_local_ticks, int6
     }
   } else {
     t->BuildKeys();
-    TasksStoreManager m{&t->rows, &t->keys};
+    TasksStoreManager m{&t->live, &t->keys, &t->rows};
     std::vector<TaskModel> tasksList = m.GetYesterdaysDueTasks(clk);
     std::vector<TaskModel> overdueTasksList;
     for (TaskModel& taskModel : tasksList) {
@@ -454,11 +513,11 @@ int32_t orc_cron_job(orc_table* t, int32_t mode, int64_t today_local_ticks, int6
 int32_t orc_mark_overdue(orc_table* t, int32_t mode, const uint8_t* ids16, int64_t n, int64_t* n_missing) {
   *n_missing = 0;
   if (mode == ORC_MODE_FAKE) {
-    try { FakeTasksManager{t->rows}.MarkOverdueTasks(TaskList()); } catch (const NotImplementedException&) { return 1; }
+    try { FakeTasksManager{t->live}.MarkOverdueTasks(TaskList()); } catch (const NotImplementedException&) { return 1; }
     return 0;
   }
   t->BuildKeys();
-  TasksStoreManager m{&t->rows, &t->keys};
+  TasksStoreManager m{&t->live, &t->keys, &t->rows};
   std::vector<TaskModel> list;
   for (int64_t i = 0; i < n; ++i) {
     Guid g;
@@ -480,10 +539,10 @@ int64_t orc_get_by_creator(orc_table* t, int32_t mode, const char* utf8, int32_t
   std::u16string createdBy = Utf8ToUtf16(utf8, len);
   std::vector<int64_t> rows;
   if (mode == ORC_MODE_FAKE) {
-    FakeTasksManager m{t->rows};
+    FakeTasksManager m{t->live};
     for (TaskModel* x : m.GetTasksByCreator(createdBy)) rows.push_back(x->row);
   } else {
-    TasksStoreManager m{&t->rows, &t->keys};
+    TasksStoreManager m{&t->live, &t->keys, &t->rows};
     for (const TaskModel& x : m.GetTasksByCreator(createdBy)) rows.push_back(x.row);
   }
   return Emit(rows, out_rows, cap);
@@ -491,13 +550,59 @@ int64_t orc_get_by_creator(orc_table* t, int32_t mode, const char* utf8, int32_t
 
 void orc_get_flags(orc_table* t, uint8_t* completed, uint8_t* overdue) {
   for (size_t i = 0; i < t->rows.size(); ++i) {
-    completed[i] = t->rows[i]->IsCompleted;
-    overdue[i] = t->rows[i]->IsOverDue;
+    completed[i] = !t->rows[i]->deleted && t->rows[i]->IsCompleted;
+    overdue[i] = !t->rows[i]->deleted && t->rows[i]->IsOverDue;
   }
+}
+
+int64_t orc_live_count(orc_table* t) { return (int64_t)t->live.size(); }
+
+// ---- ITasksManager point operations.  mode selects the implementation; return values:
+// get_by_id -> row or -1; mark_completed / update / delete -> 1 true, 0 false, 2 = the reference
+// throws (TasksStoreManager.UpdateTask on a missing id: NullReferenceException, :88).
+int64_t orc_get_by_id(orc_table* t, int32_t mode, const uint8_t* id16) {
+  Guid g;
+  memcpy(g.b, id16, 16);
+  TaskModel* m = mode == ORC_MODE_FAKE ? FakeTasksManager{t->live}.GetTaskById(g)
+                                       : TasksStoreManager{&t->live, &t->keys, &t->rows}.GetTaskById(g);
+  return m ? m->row : -1;
+}
+
+int32_t orc_mark_completed(orc_table* t, int32_t mode, const uint8_t* id16) {
+  Guid g;
+  memcpy(g.b, id16, 16);
+  return mode == ORC_MODE_FAKE ? FakeTasksManager{t->live}.MarkTaskCompleted(g)
+                               : TasksStoreManager{&t->live, &t->keys, &t->rows}.MarkTaskCompleted(g);
+}
+
+int32_t orc_update_task(orc_table* t, int32_t mode, const uint8_t* id16, const char* name, int32_t name_len,
+                        const char* assigned, int32_t assigned_len, uint64_t due_raw) {
+  Guid g;
+  memcpy(g.b, id16, 16);
+  std::u16string n = Utf8ToUtf16(name, name_len), a = Utf8ToUtf16(assigned, assigned_len);
+  if (mode == ORC_MODE_FAKE) return FakeTasksManager{t->live}.UpdateTask(g, n, a, DateTime(due_raw));
+  try {
+    return TasksStoreManager{&t->live, &t->keys, &t->rows}.UpdateTask(g, n, a, DateTime(due_raw));
+  } catch (const NullReferenceException&) {
+    return 2;
+  }
+}
+
+// FakeTasksManager.cs:49-60 (FirstOrDefault + Remove -> true/false);
+// TasksStoreManager.cs:40-45 (DeleteStateAsync, returns true whether or not the key existed)
+int32_t orc_delete_task(orc_table* t, int32_t mode, const uint8_t* id16) {
+  Guid g;
+  memcpy(g.b, id16, 16);
+  TaskModel* m = FakeTasksManager{t->live}.GetTaskById(g);
+  if (m) t->Remove(m);
+  return mode == ORC_MODE_FAKE ? (m != nullptr) : 1;
 }
 
 // The state store's key index exists before the cron tick runs; build it outside timed regions.
 void orc_build_keys(orc_table* t) { t->BuildKeys(); }
+
+// CreateNewTask (FakeTasksManager.cs:32-47 / TasksStoreManager.cs:22-38) is orc_add with the Guid and
+// the clock supplied by the caller.
 
 void orc_set_all_flags(orc_table* t, const uint8_t* completed, const uint8_t* overdue) {
   for (size_t i = 0; i < t->rows.size(); ++i) {

@@ -102,6 +102,13 @@ def lib():
     L.orc_get_flags.argtypes = [vp, vp, vp]
     L.orc_set_flags.argtypes = [vp, i64, i32, i32]
     L.orc_build_keys.argtypes = [vp]
+    L.orc_live_count.argtypes = [vp]
+    L.orc_live_count.restype = i64
+    L.orc_get_by_id.argtypes = [vp, i32, vp]
+    L.orc_get_by_id.restype = i64
+    L.orc_mark_completed.argtypes = [vp, i32, vp]
+    L.orc_update_task.argtypes = [vp, i32, vp, C.c_char_p, i32, C.c_char_p, i32, u64]
+    L.orc_delete_task.argtypes = [vp, i32, vp]
     L.orc_set_all_flags.argtypes = [vp, vp, vp]
     L.orc_soa_reset.argtypes = [vp, C.POINTER(SynthCfg), u64, i32]
     L.orc_export.argtypes = [vp, vp, vp, vp]
@@ -187,6 +194,27 @@ class OracleTable:
         o = np.empty(n, dtype=np.uint8)
         self._l.orc_get_flags(self._h, _ptr(c), _ptr(o))
         return c, o
+
+    # -- ITasksManager point operations (return codes: see oracle.cpp) --
+    def live_count(self):
+        return self._l.orc_live_count(self._h)
+
+    def get_by_id(self, mode, task_id):
+        a = np.frombuffer(bytes(task_id), dtype=np.uint8).copy()
+        return self._l.orc_get_by_id(self._h, mode, _ptr(a))
+
+    def mark_completed(self, mode, task_id):
+        a = np.frombuffer(bytes(task_id), dtype=np.uint8).copy()
+        return self._l.orc_mark_completed(self._h, mode, _ptr(a))
+
+    def update_task(self, mode, task_id, name, assigned_to, due_raw):
+        a = np.frombuffer(bytes(task_id), dtype=np.uint8).copy()
+        nb, ab = name.encode(), assigned_to.encode()
+        return self._l.orc_update_task(self._h, mode, _ptr(a), nb, len(nb), ab, len(ab), due_raw)
+
+    def delete_task(self, mode, task_id):
+        a = np.frombuffer(bytes(task_id), dtype=np.uint8).copy()
+        return self._l.orc_delete_task(self._h, mode, _ptr(a))
 
     def build_keys(self):
         self._l.orc_build_keys(self._h)

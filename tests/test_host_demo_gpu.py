@@ -13,10 +13,12 @@ EXPECTED = """STORE due: Task 8 Task 0 Task 9
 cron marked 3
 after:
 ann: Task 0* Task 4 Task 2 Task 10 Task 6 Task 8*
+new: found=1 name=Task new completed=1 marked=1 deleted=1 again=1 gone=1
 FAKE due: Task 0 Task 2 Task 3 Task 4 Task 5 Task 8 Task 9
 cron threw NotImplementedException
 after: Task 0 Task 2 Task 3 Task 4 Task 5 Task 8 Task 9
 ann: Task 0 Task 4 Task 2 Task 10 Task 6 Task 8
+new: found=1 name=Task new completed=1 marked=1 deleted=1 again=0 gone=1
 """
 
 

@@ -217,3 +217,29 @@ def test_soa_multicore_sweep_agrees(oracle):
     assert cnt == ref.n_listed and int(np.sort(rows).astype(np.uint64).sum()) == ref.sum_rows
     cnt2, _ = s.sweep()
     assert cnt2 == 0
+
+
+def test_point_operations_follow_the_two_implementations(oracle):
+    # FakeTasksManager.cs:32-100 / TasksStoreManager.cs:22-102
+    for mode in (oracle.MODE_FAKE, oracle.MODE_STORE):
+        t = build_kat(oracle)
+        missing = gid(200)
+        assert t.get_by_id(mode, gid(3)) == 2 and t.get_by_id(mode, missing) == -1
+        assert t.mark_completed(mode, gid(1)) == 1 and t.mark_completed(mode, missing) == 0
+        assert t.flags()[0][0] == 1
+        # completed row 0 no longer listed by the store implementation; the fake one ignores flags
+        assert t.get_yesterdays_due(mode, TODAY).tolist() == ([0, 2, 3, 4, 5, 8, 9] if mode == oracle.MODE_FAKE else [8, 9])
+        assert t.update_task(mode, gid(8), "n", "a", raw(YDAY)) == 1   # row 7 (due today) moves to yesterday
+        assert 7 in t.get_yesterdays_due(mode, TODAY).tolist()
+        # a missing id: false from the fake list, NullReferenceException from the store code (:88)
+        assert t.update_task(mode, missing, "n", "a", raw(YDAY)) == (0 if mode == oracle.MODE_FAKE else 2)
+        # DeleteTask: found/not found from the list; always true from the store
+        assert t.delete_task(mode, gid(9)) == 1 and t.get_by_id(mode, gid(9)) == -1
+        assert t.delete_task(mode, gid(9)) == (0 if mode == oracle.MODE_FAKE else 1)
+        assert len(t) == 11 and t.live_count() == 10
+        assert 8 not in t.get_yesterdays_due(mode, TODAY).tolist()
+        # CreateNewTask appends at the end of the list
+        row = t.add(gid(50), "new", "a@b.c", "x", raw(TODAY - 5, UTC), raw(YDAY))
+        assert row == 11 and t.get_yesterdays_due(oracle.MODE_FAKE, TODAY).tolist()[-1] == 11
+        threw, listed, n_over = t.cron_job(mode, TODAY, TODAY + 3000000000)
+        assert threw == (mode == oracle.MODE_FAKE) and n_over == listed.size

@@ -1,0 +1,125 @@
+"""The single-row operations of ITasksManager (GetTaskById, CreateNewTask, UpdateTask,
+MarkTaskCompleted, DeleteTask) on the device table, against the oracle — and the sweep and the
+creator filter after a random mix of them."""
+import uuid
+
+import numpy as np
+import pytest
+
+from helpers import load_from_oracle, tt
+
+pytestmark = pytest.mark.gpu
+TPD = tt.TICKS_PER_DAY
+TODAY = tt.DEFAULT_TODAY
+YDAY = TODAY - TPD
+
+
+def same_state(oracle, ot, table, mode):
+    c, o = ot.flags()
+    gc, go = table.flags_bytes()
+    assert (gc == c).all() and (go == o).all()
+    assert len(table) == len(ot) and table.live_count() == ot.live_count()
+    want = ot.get_yesterdays_due(mode, TODAY)
+    got = table.get_yesterdays_due(mode, TODAY).rows()
+    assert got.tolist() == want.tolist()
+
+
+@pytest.mark.parametrize("mode", [tt.MODE_FAKE, tt.MODE_STORE])
+def test_random_mix_of_point_operations(oracle, mode):
+    rng = np.random.default_rng(17 + mode)
+    n0 = 20_000
+    cfg = oracle.default_cfg(99, n0, n_creators=40)
+    ot = oracle.OracleTable()
+    ot.add_synth(cfg, 0, n0)
+    table = load_from_oracle(ot)
+    ids, _, _ = ot.export()
+    known = [bytes(ids[i]) for i in range(n0)]
+    creators = [ot.created_by(i) for i in range(40)] + [b"new.person@example.org", b"someone.else@example.org"]
+    for step in range(300):
+        op = rng.integers(0, 6)
+        tid = known[int(rng.integers(0, len(known)))] if rng.random() < 0.9 else uuid.uuid4().bytes
+        if op == 0:  # CreateNewTask
+            new = uuid.uuid4().bytes
+            who = creators[int(rng.integers(0, len(creators)))]
+            due = int(rng.choice([YDAY, YDAY + 5, TODAY, YDAY | (1 << 62)]))
+            created = (TODAY - int(rng.integers(1, 10**9))) | (1 << 62)
+            row = ot.add(new, "t", who, "a", created, due)
+            assert table.insert_task(new, created, due, who) == row
+            known.append(new)
+        elif op == 1:  # GetTaskById
+            res = table.get_by_id(tid)
+            want = ot.get_by_id(mode, tid)
+            assert (res.rows().tolist() == [want]) if want >= 0 else res.count == 0
+            if want >= 0:
+                assert res.ids()[0].tobytes() == tid
+        elif op == 2:  # MarkTaskCompleted
+            assert table.mark_completed(tid) == bool(ot.mark_completed(mode, tid))
+        elif op == 3:  # UpdateTask
+            due = int(rng.choice([YDAY, TODAY + TPD, YDAY + 1]))
+            want = ot.update_task(mode, tid, "renamed", "moved", due)
+            got = table.update_task(tid, due)
+            assert got == (want == 1)  # want == 2: the store implementation throws on a missing id
+        elif op == 4:  # DeleteTask
+            existed = ot.get_by_id(mode, tid) >= 0
+            want = ot.delete_task(mode, tid)  # the store version answers true either way
+            assert want == (existed if mode == tt.MODE_FAKE else 1)
+            assert table.delete_task(tid) == existed
+        else:  # GetTasksByCreator
+            who = creators[int(rng.integers(0, len(creators)))]
+            assert table.get_by_creator(who).rows().tolist() == ot.get_by_creator(mode, who).tolist()
+        if step % 50 == 49:
+            same_state(oracle, ot, table, mode)
+    same_state(oracle, ot, table, mode)
+    # the cron tick on the edited table
+    threw, listed, n_over = ot.cron_job(mode)
+    res, n_marked, gthrew = table.sweep(mode)
+    assert gthrew == threw and (res.rows() == np.sort(listed)).all()
+    assert n_marked == (n_over if mode == tt.MODE_STORE else 0)
+    same_state(oracle, ot, table, mode)
+    table.close()
+
+
+def test_table_grows_from_empty(oracle):
+    """CreateNewTask on an empty manager, past one tile of capacity (the columns are regrown)"""
+    ot = oracle.OracleTable()
+    table = tt.TaskTable(0)
+    rng = np.random.default_rng(3)
+    ids = []
+    for i in range(8192 + 300):
+        tid = uuid.UUID(int=(i + 1) << 64 | 0x4000_8000_0000_0000_0000 | i, version=None).bytes if i % 7 else uuid.uuid4().bytes
+        who = b"grow%d@example.org" % (i % 13)
+        due = YDAY if i % 5 == 0 else TODAY
+        created = (TODAY - int(rng.integers(1, 10**9))) | (1 << 62)
+        assert table.insert_task(tid, created, due, who) == ot.add(tid, "t", who, "a", created, due)
+        ids.append(tid)
+    assert len(table) == 8492 and table.live_count() == 8492
+    for mode in (tt.MODE_FAKE, tt.MODE_STORE):
+        assert table.get_yesterdays_due(mode).rows().tolist() == ot.get_yesterdays_due(mode).tolist()
+    assert table.get_by_creator(b"grow5@example.org").rows().tolist() == ot.get_by_creator(0, b"grow5@example.org").tolist()
+    for k in (0, 1, 8191, 8192, 8491):
+        assert table.get_by_id(ids[k]).rows().tolist() == [k]
+    table.close()
+
+
+def test_manager_mirror_full_interface(oracle):
+    """GpuTasksManager: all eight ITasksManager methods, FAKE semantics (the registered default)"""
+    import importlib
+
+    pkg = importlib.import_module("aca-dotnet-workshop_b200")
+    clock = [tt.DEFAULT_RUN_AT]
+    mgr = pkg.GpuTasksManager([], mode=tt.MODE_FAKE, utc_now=lambda: clock[0] | (1 << 62))
+    a = mgr.CreateNewTask("first", "ann@x.io", "bob@x.io", YDAY)
+    clock[0] += 10
+    b = mgr.CreateNewTask("second", "ann@x.io", "cy@x.io", TODAY)
+    clock[0] += 10
+    c = mgr.CreateNewTask("third", "dan@x.io", "cy@x.io", YDAY)
+    assert [t.TaskName for t in mgr.GetTasksByCreator("ann@x.io")] == ["second", "first"]
+    assert mgr.GetTaskById(b).TaskAssignedTo == "cy@x.io" and mgr.GetTaskById(uuid.uuid4()) is None
+    assert [t.TaskName for t in mgr.GetYesterdaysDueTasks()] == ["first", "third"]
+    assert mgr.MarkTaskCompleted(a) and mgr.GetTaskById(a).IsCompleted and not mgr.MarkTaskCompleted(uuid.uuid4())
+    assert mgr.UpdateTask(c, "third!", "eve@x.io", TODAY) and not mgr.UpdateTask(uuid.uuid4(), "x", "y", TODAY)
+    assert [t.TaskName for t in mgr.GetYesterdaysDueTasks()] == ["first"]
+    assert mgr.GetTaskById(c).TaskName == "third!" and mgr.GetTaskById(c).TaskAssignedTo == "eve@x.io"
+    assert mgr.DeleteTask(a) and not mgr.DeleteTask(a)
+    assert mgr.GetYesterdaysDueTasks() == [] and [t.TaskName for t in mgr.GetTasksByCreator("ann@x.io")] == ["second"]
+    mgr.close()
