@@ -3,29 +3,38 @@
 // Replaces `.OrderBy(o => o.TaskCreatedOn)` (Api/Services/TasksStoreManager.cs:136) and
 // `.OrderByDescending(o => o.TaskCreatedOn)` (Api/Services/FakeTasksManager.cs:70,
 // TasksStoreManager.cs:66).  LINQ's OrderBy is a stable sort on DateTime.Ticks, so equal keys
-// keep their source order: the hit rows arrive in ascending row order and an LSD radix sort
-// (stable) of the 62-bit tick key preserves that; "descending" sorts the complemented key,
-// which keeps ties in source order exactly as OrderByDescending does.
-// The radix sort itself is CUB's DeviceRadixSort (library code, compiled here for sm_100a);
-// it runs over the hits only (H rows), never over the table.
+// keep their source order: the hit rows arrive in ascending row order and the LSD radix sort of
+// radix.cuh (stable) of the 62-bit tick key preserves that; "descending" sorts the complemented
+// key, which keeps ties in source order exactly as OrderByDescending does.  Small per-query
+// results are ordered by one CTA with a bitonic network on (key, row) instead.  The sort runs
+// over the hits only (H rows), never over the table.
 #pragma once
 
 #include <cuda_runtime.h>
 #include <stdint.h>
 
-#include <cub/device/device_radix_sort.cuh>
-
 #include "../../include/tt_synth.h"
+#include "radix.cuh"
 #include "sweep.cuh"
 
 namespace tt {
 
-__global__ void order_keys_kernel(const uint32_t* rows, const uint64_t* created_raw, uint64_t* keys, int64_t n,
-                                  int descending) {
+__global__ void order_keys_kernel(const uint32_t* rows, const uint64_t* created_raw, unsigned long long* keys,
+                                  uint32_t* vals, int64_t n, int descending) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) {
-    uint64_t k = created_raw[rows[i]] & TT_TICKS_MASK;
+    const uint32_t r = rows[i];
+    uint64_t k = ld_gather_u64(created_raw + r) & TT_TICKS_MASK;
     keys[i] = descending ? (~k & TT_TICKS_MASK) : k;
+    vals[i] = r;
+  }
+}
+
+__global__ void row_keys_kernel(const uint32_t* rows, unsigned long long* keys, uint32_t* vals, int64_t n) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) {
+    keys[i] = rows[i];
+    vals[i] = rows[i];
   }
 }
 
@@ -34,46 +43,60 @@ __global__ void gather_ids_kernel(const uint32_t* rows, const uint4* task_id, ui
   if (i < n) out[i] = ld_gather_v4(task_id + rows[i]);
 }
 
-// Returns 0 or a cudaError_t value.
-inline int order_by_created(cudaStream_t stream, const uint64_t* created_raw, const uint4* task_id, uint32_t* d_rows,
-                            uint4* d_ids, int64_t n, bool descending, bool rows_unordered = false) {
+// rows_out[i] = rows_sorted[i]; ids_out[i] = task_id[rows_sorted[i]]
+__global__ void emit_rows_ids_kernel(const uint32_t* rows_sorted, const uint4* task_id, uint32_t* rows_out, uint4* ids_out,
+                                     int64_t n) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) {
+    const uint32_t r = rows_sorted[i];
+    rows_out[i] = r;
+    ids_out[i] = ld_gather_v4(task_id + r);
+  }
+}
+
+// Sorts a hit list by row number and re-gathers the TaskIds (used when two row-ordered runs
+// have to be merged, and as the first step for unordered candidate lists).
+// Returns 0 or a cudaError_t value; synchronises the stream.
+inline int sort_rows_and_gather(cudaStream_t stream, SortScratch& sc, const uint4* task_id, uint32_t* d_rows,
+                                uint4* d_ids, int64_t n) {
   if (n <= 0) return 0;
-  if (n > 0x7FFFFFFF) return (int)cudaErrorInvalidValue;
-  const int num = (int)n;
-  uint64_t *keys_in = nullptr, *keys_out = nullptr;
-  uint32_t* rows_tmp = nullptr;
-  void* temp = nullptr;
-  size_t temp_pairs = 0, temp_keys = 0;
-  cudaError_t e = cub::DeviceRadixSort::SortPairs(nullptr, temp_pairs, keys_in, keys_out, d_rows, rows_tmp, num, 0, 62, stream);
-  if (e == cudaSuccess) e = cub::DeviceRadixSort::SortKeys(nullptr, temp_keys, d_rows, rows_tmp, num, 0, 32, stream);
-  size_t temp_bytes = temp_pairs > temp_keys ? temp_pairs : temp_keys;
-  if (e == cudaSuccess) e = cudaMalloc(&keys_in, (size_t)n * 8);
-  if (e == cudaSuccess) e = cudaMalloc(&keys_out, (size_t)n * 8);
-  if (e == cudaSuccess) e = cudaMalloc(&rows_tmp, (size_t)n * 4);
-  if (e == cudaSuccess) e = cudaMalloc(&temp, temp_bytes ? temp_bytes : 16);
+  cudaError_t e = sc.reserve(n);
+  if (e != cudaSuccess) return (int)e;
   const unsigned grid = (unsigned)((n + 255) / 256);
-  if (e == cudaSuccess && rows_unordered) {
-    e = cub::DeviceRadixSort::SortKeys(temp, temp_bytes, d_rows, rows_tmp, num, 0, 32, stream);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(d_rows, rows_tmp, (size_t)n * 4, cudaMemcpyDeviceToDevice, stream);
+  row_keys_kernel<<<grid, 256, 0, stream>>>(d_rows, sc.keys[0], sc.vals[0], n);
+  int w = 0;
+  e = radix_sort_pairs(stream, sc, n, 32, &w);
+  if (e != cudaSuccess) return (int)e;
+  emit_rows_ids_kernel<<<grid, 256, 0, stream>>>(sc.vals[w], task_id, d_rows, d_ids, n);
+  e = cudaGetLastError();
+  cudaError_t s2 = cudaStreamSynchronize(stream);
+  return (int)(e != cudaSuccess ? e : s2);
+}
+
+// Orders d_rows (ascending row order on entry, or any order with rows_unordered) by
+// TaskCreatedOn, stable, and rewrites d_rows / d_ids.  Returns 0 or a cudaError_t value.
+inline int order_by_created(cudaStream_t stream, SortScratch& sc, const uint64_t* created_raw, const uint4* task_id,
+                            uint32_t* d_rows, uint4* d_ids, int64_t n, bool descending, bool rows_unordered = false) {
+  if (n <= 0) return 0;
+  if (rows_unordered) {
+    int rc = sort_rows_and_gather(stream, sc, task_id, d_rows, d_ids, n);
+    if (rc) return rc;
   }
-  if (e == cudaSuccess) {
-    order_keys_kernel<<<grid, 256, 0, stream>>>(d_rows, created_raw, keys_in, n, descending ? 1 : 0);
-    e = cudaGetLastError();
-  }
-  if (e == cudaSuccess)
-    e = cub::DeviceRadixSort::SortPairs(temp, temp_bytes, keys_in, keys_out, d_rows, rows_tmp, num, 0, 62, stream);
-  if (e == cudaSuccess) e = cudaMemcpyAsync(d_rows, rows_tmp, (size_t)n * 4, cudaMemcpyDeviceToDevice, stream);
-  if (e == cudaSuccess) {
-    gather_ids_kernel<<<grid, 256, 0, stream>>>(d_rows, task_id, d_ids, n);
-    e = cudaGetLastError();
-  }
-  cudaError_t s = cudaStreamSynchronize(stream);
-  if (e == cudaSuccess) e = s;
-  cudaFree(keys_in);
-  cudaFree(keys_out);
-  cudaFree(rows_tmp);
-  cudaFree(temp);
-  return (int)e;
+  cudaError_t e = sc.reserve(n);
+  if (e != cudaSuccess) return (int)e;
+  const unsigned grid = (unsigned)((n + 255) / 256);
+  order_keys_kernel<<<grid, 256, 0, stream>>>(d_rows, created_raw, sc.keys[0], sc.vals[0], n, descending ? 1 : 0);
+  e = cudaGetLastError();
+  if (e != cudaSuccess) return (int)e;
+  int bits = 62, w = 0;
+  e = radix_significant_bits(stream, sc, n, &bits);
+  if (e != cudaSuccess) return (int)e;
+  e = radix_sort_pairs(stream, sc, n, bits, &w);
+  if (e != cudaSuccess) return (int)e;
+  emit_rows_ids_kernel<<<grid, 256, 0, stream>>>(sc.vals[w], task_id, d_rows, d_ids, n);
+  e = cudaGetLastError();
+  cudaError_t s2 = cudaStreamSynchronize(stream);
+  return (int)(e != cudaSuccess ? e : s2);
 }
 
 // ---- ordering the creator filter's (query, row) pairs ------------------------------------------
@@ -197,26 +220,48 @@ __global__ void __launch_bounds__(kListOrderThreads) order_lists_kernel(const ui
   }
 }
 
-__global__ void pair_keys_kernel(const unsigned long long* pairs, int64_t n, const uint64_t* created_raw, int descending,
-                                 unsigned long long* hi, unsigned long long* lo) {
+// Large results: two stable radix sorts over an index permutation — first by the low key word,
+// then by the high one — followed by one kernel that writes rows, TaskIds and per-query counts.
+__global__ void pair_lo_keys_kernel(const unsigned long long* pairs, int64_t n, const uint64_t* created_raw,
+                                    int descending, unsigned long long* keys, uint32_t* vals) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) pair_keys(pairs[i], created_raw, descending, hi[i], lo[i]);
+  if (i < n) {
+    unsigned long long hi, lo;
+    pair_keys(pairs[i], created_raw, descending, hi, lo);
+    keys[i] = lo;
+    vals[i] = (uint32_t)i;
+  }
 }
 
-__global__ void pair_finish_kernel(const unsigned long long* hi, const unsigned long long* lo, int64_t n,
+__global__ void pair_hi_keys_kernel(const unsigned long long* pairs, const uint32_t* perm, int64_t n,
+                                    const uint64_t* created_raw, int descending, unsigned long long* keys,
+                                    uint32_t* vals) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) {
+    unsigned long long hi, lo;
+    const uint32_t src = perm[i];
+    pair_keys(pairs[src], created_raw, descending, hi, lo);
+    keys[i] = hi;
+    vals[i] = src;
+  }
+}
+
+__global__ void pair_finish_kernel(const unsigned long long* pairs, const uint32_t* perm, int64_t n,
                                    const uint4* task_id, uint32_t* out_rows, uint4* out_ids, uint32_t* q_count) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) {
-    const uint32_t row = (uint32_t)lo[i];
+    const unsigned long long p = pairs[perm[i]];
+    const uint32_t row = (uint32_t)p;
     out_rows[i] = row;
     out_ids[i] = ld_gather_v4(task_id + row);
-    atomicAdd(q_count + (uint32_t)(hi[i] >> 54), 1u);
+    atomicAdd(q_count + (uint32_t)(p >> 32), 1u);
   }
 }
 
 // q_count (device, one word per query) must be zero on entry.  Returns 0 or a cudaError_t value.
-inline int order_pairs(cudaStream_t stream, const unsigned long long* pairs, int64_t n, const uint64_t* created_raw,
-                       const uint4* task_id, bool descending, uint32_t* out_rows, uint4* out_ids, uint32_t* q_count) {
+inline int order_pairs(cudaStream_t stream, SortScratch& sc, const unsigned long long* pairs, int64_t n,
+                       const uint64_t* created_raw, const uint4* task_id, bool descending, uint32_t* out_rows,
+                       uint4* out_ids, uint32_t* q_count) {
   if (n <= 0) return 0;
   if (n <= kSmallOrderMax) {
     int n2 = 2;
@@ -233,62 +278,24 @@ inline int order_pairs(cudaStream_t stream, const unsigned long long* pairs, int
                                                                      descending ? 1 : 0, out_rows, out_ids, q_count);
     return (int)cudaGetLastError();
   }
-  if (n > 0x7FFFFFFF) return (int)cudaErrorInvalidValue;
-  // large result: two stable LSD passes over the two key words (CUB DeviceRadixSort, hits only)
-  const int num = (int)n;
-  unsigned long long *hi = nullptr, *lo = nullptr, *hi2 = nullptr, *lo2 = nullptr;
-  void* temp = nullptr;
-  size_t temp_bytes = 0;
-  cudaError_t e = cub::DeviceRadixSort::SortPairs(nullptr, temp_bytes, lo, lo2, hi, hi2, num, 0, 64, stream);
-  if (e == cudaSuccess) e = cudaMalloc(&hi, (size_t)n * 8);
-  if (e == cudaSuccess) e = cudaMalloc(&lo, (size_t)n * 8);
-  if (e == cudaSuccess) e = cudaMalloc(&hi2, (size_t)n * 8);
-  if (e == cudaSuccess) e = cudaMalloc(&lo2, (size_t)n * 8);
-  if (e == cudaSuccess) e = cudaMalloc(&temp, temp_bytes ? temp_bytes : 16);
+  if (n > 0xFFFFFFFFll) return (int)cudaErrorInvalidValue;
+  cudaError_t e = sc.reserve(n);
+  if (e != cudaSuccess) return (int)e;
   const unsigned grid = (unsigned)((n + 255) / 256);
-  if (e == cudaSuccess) {
-    pair_keys_kernel<<<grid, 256, 0, stream>>>(pairs, n, created_raw, descending ? 1 : 0, hi, lo);
-    e = cudaGetLastError();
-  }
-  if (e == cudaSuccess) e = cub::DeviceRadixSort::SortPairs(temp, temp_bytes, lo, lo2, hi, hi2, num, 0, 40, stream);
-  if (e == cudaSuccess) e = cub::DeviceRadixSort::SortPairs(temp, temp_bytes, hi2, hi, lo2, lo, num, 0, 64, stream);
-  if (e == cudaSuccess) {
-    pair_finish_kernel<<<grid, 256, 0, stream>>>(hi, lo, n, task_id, out_rows, out_ids, q_count);
-    e = cudaGetLastError();
-  }
+  int w = 0;
+  pair_lo_keys_kernel<<<grid, 256, 0, stream>>>(pairs, n, created_raw, descending ? 1 : 0, sc.keys[0], sc.vals[0]);
+  e = radix_sort_pairs(stream, sc, n, 40, &w);
+  if (e != cudaSuccess) return (int)e;
+  // the permutation so far sits in vals[w]; the next sort starts from buffer 0 again (if w == 0
+  // every thread reads perm[i] and writes vals[0][i] = the same value, so aliasing is harmless)
+  const uint32_t* perm = sc.vals[w];
+  pair_hi_keys_kernel<<<grid, 256, 0, stream>>>(pairs, perm, n, created_raw, descending ? 1 : 0, sc.keys[0], sc.vals[0]);
+  e = radix_sort_pairs(stream, sc, n, 64, &w);
+  if (e != cudaSuccess) return (int)e;
+  pair_finish_kernel<<<grid, 256, 0, stream>>>(pairs, sc.vals[w], n, task_id, out_rows, out_ids, q_count);
+  e = cudaGetLastError();
   cudaError_t s2 = cudaStreamSynchronize(stream);
-  if (e == cudaSuccess) e = s2;
-  cudaFree(hi);
-  cudaFree(lo);
-  cudaFree(hi2);
-  cudaFree(lo2);
-  cudaFree(temp);
-  return (int)e;
-}
-
-// Sorts a hit list by row number and re-gathers the TaskIds (used when two row-ordered runs
-// have to be merged).  Returns 0 or a cudaError_t value.
-inline int sort_rows_and_gather(cudaStream_t stream, const uint4* task_id, uint32_t* d_rows, uint4* d_ids, int64_t n) {
-  if (n <= 1) return 0;
-  if (n > 0x7FFFFFFF) return (int)cudaErrorInvalidValue;
-  const int num = (int)n;
-  uint32_t* tmp = nullptr;
-  void* temp = nullptr;
-  size_t temp_bytes = 0;
-  cudaError_t e = cub::DeviceRadixSort::SortKeys(nullptr, temp_bytes, d_rows, tmp, num, 0, 32, stream);
-  if (e == cudaSuccess) e = cudaMalloc(&tmp, (size_t)n * 4);
-  if (e == cudaSuccess) e = cudaMalloc(&temp, temp_bytes ? temp_bytes : 16);
-  if (e == cudaSuccess) e = cub::DeviceRadixSort::SortKeys(temp, temp_bytes, d_rows, tmp, num, 0, 32, stream);
-  if (e == cudaSuccess) e = cudaMemcpyAsync(d_rows, tmp, (size_t)n * 4, cudaMemcpyDeviceToDevice, stream);
-  if (e == cudaSuccess) {
-    gather_ids_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(d_rows, task_id, d_ids, n);
-    e = cudaGetLastError();
-  }
-  cudaError_t s = cudaStreamSynchronize(stream);
-  if (e == cudaSuccess) e = s;
-  cudaFree(tmp);
-  cudaFree(temp);
-  return (int)e;
+  return (int)(e != cudaSuccess ? e : s2);
 }
 
 }  // namespace tt

@@ -80,6 +80,12 @@ __device__ __forceinline__ uint4 ld_gather_v4(const uint4* p) {
   return r;
 }
 
+__device__ __forceinline__ uint64_t ld_gather_u64(const uint64_t* p) {
+  uint64_t r;
+  asm volatile("ld.global.nc.L1::no_allocate.L2::64B.u64 %0, [%1];" : "=l"(r) : "l"(p));
+  return r;
+}
+
 __device__ __forceinline__ uint32_t warp_sum(uint32_t v) {
 #pragma unroll
   for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, d);

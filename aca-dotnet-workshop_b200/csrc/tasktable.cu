@@ -120,6 +120,7 @@ struct tt_table {
   uint32_t* d_qcount = nullptr;  // per-query match counts (kMaxQueries words) + pinned mirror
   uint32_t* h_qcount = nullptr;
   tt_op_stats last_op = {};
+  tt::SortScratch sort;  // K5 radix sort buffers, grow-only
 };
 
 // One device allocation, shared by the results that point into it (a batch of creator queries
@@ -498,7 +499,7 @@ int32_t sweep_owned(tt_table* t, int32_t mode, int32_t flags, int64_t today, int
     if (rc == TT_OK) {
       r->n += st.n_stored;
       if (merged && r->n > 1) {
-        int e = tt::sort_rows_and_gather(t->stream, t->task_id, r->d_rows, r->d_ids, r->n);
+        int e = tt::sort_rows_and_gather(t->stream, t->sort, t->task_id, r->d_rows, r->d_ids, r->n);
         if (e != 0) {
           result_release(r);
           return fail(TT_ERR_CUDA, "sort_rows_and_gather: %s", cudaGetErrorString((cudaError_t)e));
@@ -581,6 +582,7 @@ int32_t tt_destroy(tt_table* t) {
     cudaFreeHost(t->h_ctl);
     cudaFree(t->d_small);
     cudaFreeHost(t->h_small);
+    t->sort.release();
     cudaFree(t->d_query);
     cudaFree(t->d_pairs);
     cudaFree(t->d_lists);
@@ -719,7 +721,7 @@ int32_t tt_get_yesterdays_due(tt_table* t, int32_t mode, int64_t today_local_tic
   if (rc) return rc;
   if (mode == TT_MODE_STORE && r->n > 1) {
     // TasksStoreManager.cs:136 — OrderBy(TaskCreatedOn), stable; ties keep row order
-    rc = tt::order_by_created(t->stream, t->created_raw, t->task_id, r->d_rows, r->d_ids, r->n, /*descending=*/false);
+    rc = tt::order_by_created(t->stream, t->sort, t->created_raw, t->task_id, r->d_rows, r->d_ids, r->n, /*descending=*/false);
     if (rc != 0) {
       result_release(r);
       return fail(TT_ERR_CUDA, "order_by_created failed: %s", cudaGetErrorString((cudaError_t)rc));
@@ -953,7 +955,7 @@ int32_t tt_get_by_creators(tt_table* t, const char* const* utf8, const int32_t* 
       }
     } else {
       cudaMemsetAsync(t->d_qcount, 0, (size_t)nu * 4, t->stream);
-      int e = tt::order_pairs(t->stream, t->d_pairs, found, t->created_raw, t->task_id, /*descending=*/true,
+      int e = tt::order_pairs(t->stream, t->sort, t->d_pairs, found, t->created_raw, t->task_id, /*descending=*/true,
                               whole->d_rows, whole->d_ids, t->d_qcount);
       if (e != 0) {
         result_release(whole);
