@@ -1422,6 +1422,160 @@ int32_t tt_live_count(tt_table* t, int64_t* n) {
 
 }  // extern "C"
 
+// ---- snapshot: the table as a file (checkpoint / resume) ------------------
+//
+// The reference keeps its tasks in a state store (Dapr SaveStateAsync, TasksStoreManager.cs:35)
+// or loses them on restart (FakeTasksManager).  The resident table is saved column by column in
+// its device layout, so loading is a straight copy: no re-encoding, no re-hashing.
+
+namespace {
+
+struct SnapshotHeader {
+  char magic[8];  // "TTSNAP01"
+  int64_t n, n_pad, n_live;
+  uint64_t pool_bytes;
+  uint32_t n_creators;
+  uint32_t ids_sorted;
+  uint32_t tile_rows;
+  uint32_t reserved;
+};
+
+constexpr size_t kSnapChunk = 64u << 20;
+
+int32_t snap_write(FILE* f, const void* dev, size_t bytes, void* stage, cudaStream_t stream) {
+  const unsigned char* p = static_cast<const unsigned char*>(dev);
+  for (size_t off = 0; off < bytes; off += kSnapChunk) {
+    const size_t m = std::min(kSnapChunk, bytes - off);
+    TT_CUDA(cudaMemcpyAsync(stage, p + off, m, cudaMemcpyDeviceToHost, stream));
+    TT_CUDA(cudaStreamSynchronize(stream));
+    if (fwrite(stage, 1, m, f) != m) return fail(TT_ERR_STATE, "short write to snapshot");
+  }
+  return TT_OK;
+}
+
+int32_t snap_read(FILE* f, void* dev, size_t bytes, void* stage, cudaStream_t stream) {
+  unsigned char* p = static_cast<unsigned char*>(dev);
+  for (size_t off = 0; off < bytes; off += kSnapChunk) {
+    const size_t m = std::min(kSnapChunk, bytes - off);
+    if (fread(stage, 1, m, f) != m) return fail(TT_ERR_STATE, "snapshot is truncated");
+    TT_CUDA(cudaMemcpyAsync(p + off, stage, m, cudaMemcpyHostToDevice, stream));
+    TT_CUDA(cudaStreamSynchronize(stream));
+  }
+  return TT_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int32_t tt_save_snapshot(tt_table* t, const char* path) {
+  if (!t || !path) return fail(TT_ERR_ARG, "null argument");
+  std::lock_guard<std::mutex> lk(t->mu);
+  DeviceGuard g(t->device);
+  if (t->n_pad == 0) return fail(TT_ERR_STATE, "the table is empty");
+  FILE* f = fopen(path, "wb");
+  if (!f) return fail(TT_ERR_ARG, "cannot open %s for writing", path);
+  void* stage = nullptr;
+  if (cudaMallocHost(&stage, kSnapChunk) != cudaSuccess) {
+    cudaGetLastError();
+    fclose(f);
+    return fail(TT_ERR_OOM, "no pinned staging buffer");
+  }
+  SnapshotHeader h = {};
+  memcpy(h.magic, "TTSNAP01", 8);
+  h.n = t->n;
+  h.n_pad = t->n_pad;
+  h.n_live = t->n_live;
+  h.pool_bytes = t->pool_bytes;
+  h.n_creators = t->n_creators;
+  h.ids_sorted = t->ids_sorted ? 1u : 0u;
+  h.tile_rows = TT_TILE_ROWS;
+  int32_t rc = fwrite(&h, sizeof h, 1, f) == 1 ? TT_OK : fail(TT_ERR_STATE, "short write to snapshot");
+  const size_t np = (size_t)t->n_pad;
+  if (!rc) rc = snap_write(f, t->due_code, np * 4, stage, t->stream);
+  if (!rc) rc = snap_write(f, t->completed, np / 8, stage, t->stream);
+  if (!rc) rc = snap_write(f, t->overdue, np / 8, stage, t->stream);
+  if (!rc) rc = snap_write(f, t->creator_hash, np * 8, stage, t->stream);
+  if (!rc) rc = snap_write(f, t->task_id, np * 16, stage, t->stream);
+  if (!rc) rc = snap_write(f, t->created_raw, np * 8, stage, t->stream);
+  if (!rc) rc = snap_write(f, t->due_raw, np * 8, stage, t->stream);
+  if (!rc) rc = snap_write(f, t->creator_ref, np * 4, stage, t->stream);
+  if (!rc) rc = snap_write(f, t->creator_off, ((size_t)t->n_creators + 1) * 4, stage, t->stream);
+  if (!rc && t->pool_bytes) rc = snap_write(f, t->creator_pool, t->pool_bytes, stage, t->stream);
+  cudaFreeHost(stage);
+  if (fclose(f) != 0 && !rc) rc = fail(TT_ERR_STATE, "closing %s failed", path);
+  return rc;
+}
+
+int32_t tt_load_snapshot(tt_table* t, const char* path) {
+  if (!t || !path) return fail(TT_ERR_ARG, "null argument");
+  std::lock_guard<std::mutex> lk(t->mu);
+  DeviceGuard g(t->device);
+  if (t->n_pad != 0) return fail(TT_ERR_STATE, "table already holds %lld rows", (long long)t->n);
+  FILE* f = fopen(path, "rb");
+  if (!f) return fail(TT_ERR_ARG, "cannot open %s", path);
+  SnapshotHeader h;
+  if (fread(&h, sizeof h, 1, f) != 1 || memcmp(h.magic, "TTSNAP01", 8) != 0 || h.tile_rows != TT_TILE_ROWS ||
+      h.n < 0 || h.n > h.n_pad || h.n_pad % TT_TILE_ROWS != 0 || h.n_pad > kMaxRows) {
+    fclose(f);
+    return fail(TT_ERR_ARG, "%s is not a task table snapshot", path);
+  }
+  void* stage = nullptr;
+  if (cudaMallocHost(&stage, kSnapChunk) != cudaSuccess) {
+    cudaGetLastError();
+    fclose(f);
+    return fail(TT_ERR_OOM, "no pinned staging buffer");
+  }
+  int32_t rc = alloc_columns(t, h.n_pad);  // exactly the saved capacity
+  const size_t np = (size_t)h.n_pad;
+  if (!rc) rc = snap_read(f, t->due_code, np * 4, stage, t->stream);
+  if (!rc) rc = snap_read(f, t->completed, np / 8, stage, t->stream);
+  if (!rc) rc = snap_read(f, t->overdue, np / 8, stage, t->stream);
+  if (!rc) rc = snap_read(f, t->creator_hash, np * 8, stage, t->stream);
+  if (!rc) rc = snap_read(f, t->task_id, np * 16, stage, t->stream);
+  if (!rc) rc = snap_read(f, t->created_raw, np * 8, stage, t->stream);
+  if (!rc) rc = snap_read(f, t->due_raw, np * 8, stage, t->stream);
+  if (!rc) rc = snap_read(f, t->creator_ref, np * 4, stage, t->stream);
+  if (!rc) {
+    t->n = h.n;
+    t->n_live = h.n_live;
+    t->n_creators = h.n_creators;
+    t->pool_bytes = h.pool_bytes;
+    t->creator_off_cap = (size_t)h.n_creators + 1;
+    t->creator_pool_cap = std::max<uint64_t>(h.pool_bytes, 16);
+    t->ids_sorted = h.ids_sorted != 0;
+    cudaError_t e = cudaMalloc(&t->creator_off, t->creator_off_cap * 4);
+    if (e == cudaSuccess) e = cudaMalloc(&t->creator_pool, t->creator_pool_cap);
+    if (e != cudaSuccess) {
+      cudaGetLastError();
+      rc = fail(TT_ERR_OOM, "creator dictionary: %s", cudaGetErrorString(e));
+    }
+  }
+  if (!rc) rc = snap_read(f, t->creator_off, ((size_t)h.n_creators + 1) * 4, stage, t->stream);
+  if (!rc && h.pool_bytes) rc = snap_read(f, t->creator_pool, h.pool_bytes, stage, t->stream);
+  cudaFreeHost(stage);
+  fclose(f);
+  if (rc) {
+    free_columns(t);
+    return rc;
+  }
+  if (!t->ids_sorted && t->n > 0) {
+    // rebuild the TaskId index on the host (ingest path, like tt_load_soa)
+    std::vector<uint8_t> ids((size_t)t->n * 16);
+    TT_CUDA(cudaMemcpy(ids.data(), t->task_id, ids.size(), cudaMemcpyDeviceToHost));
+    std::vector<uint32_t> order((size_t)t->n);
+    for (int64_t i = 0; i < t->n; ++i) order[i] = (uint32_t)i;
+    const uint8_t* p = ids.data();
+    std::stable_sort(order.begin(), order.end(),
+                     [p](uint32_t a, uint32_t b) { return memcmp(p + 16 * (size_t)a, p + 16 * (size_t)b, 16) < 0; });
+    TT_CUDA(cudaMalloc(&t->id_order, (size_t)t->n * 4));
+    TT_CUDA(cudaMemcpy(t->id_order, order.data(), (size_t)t->n * 4, cudaMemcpyHostToDevice));
+  }
+  return TT_OK;
+}
+
+}  // extern "C"
+
 // ---- the sweep with its working memory in a fixed device array ---------------------------------
 //
 // For callers that cannot allocate (see include/tasktable.h).  Everything tt_sweep_device keeps

@@ -46,6 +46,7 @@ EXPORTS = [
     "tt_snapshot_flags", "tt_restore_flags", "tt_count_flags", "tt_result_digest",
     "tt_sweep_device", "tt_get_device_view", "tt_sweep_static", "tt_get_by_creators", "tt_last_op_stats",
     "tt_get_by_id", "tt_insert_task", "tt_update_task", "tt_mark_completed", "tt_delete_task", "tt_live_count",
+    "tt_save_snapshot", "tt_load_snapshot",
 ]
 
 
@@ -177,6 +178,8 @@ def lib():
     L.tt_mark_completed.argtypes = [vp, vp, P(i32)]
     L.tt_delete_task.argtypes = [vp, vp, P(i32)]
     L.tt_live_count.argtypes = [vp, P(i64)]
+    L.tt_save_snapshot.argtypes = [vp, C.c_char_p]
+    L.tt_load_snapshot.argtypes = [vp, C.c_char_p]
     L.tt_result_count.argtypes = [vp, P(i64)]
     L.tt_result_rows.argtypes = [vp, vp]
     L.tt_result_ids.argtypes = [vp, vp]
@@ -418,6 +421,13 @@ class TaskTable:
         c, o = C.c_int64(0), C.c_int64(0)
         _check(lib().tt_count_flags(self._h, C.byref(c), C.byref(o)))
         return c.value, o.value
+
+    def save_snapshot(self, path):
+        _check(lib().tt_save_snapshot(self._h, os.fsencode(path)))
+
+    def load_snapshot(self, path):
+        _check(lib().tt_load_snapshot(self._h, os.fsencode(path)))
+        return self
 
     def device_view(self):
         v = DeviceView()

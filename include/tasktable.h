@@ -235,6 +235,14 @@ typedef struct tt_device_view {
 } tt_device_view;
 int32_t tt_get_device_view(tt_table* t, tt_device_view* out);
 
+/* ---- snapshot ---------------------------------------------------------------------------------
+ * Saves / restores the whole table (all columns, flags, creator dictionary, tombstones) as one
+ * file in the device layout — the counterpart of the reference keeping its tasks in a state store
+ * across restarts (Api/Services/TasksStoreManager.cs:35 SaveStateAsync).  tt_load_snapshot needs
+ * an empty table on the same kind of build (same tile size). */
+int32_t tt_save_snapshot(tt_table* t, const char* path);
+int32_t tt_load_snapshot(tt_table* t, const char* path);
+
 /* ---- sweep without any allocation ----------------------------------------------------------
  * This entry point has no counterpart in the reference.  It exists for hosts that cannot let a
  * library allocate device memory while they are serving: a process that handed the whole GPU to

@@ -123,3 +123,40 @@ def test_manager_mirror_full_interface(oracle):
     assert mgr.DeleteTask(a) and not mgr.DeleteTask(a)
     assert mgr.GetYesterdaysDueTasks() == [] and [t.TaskName for t in mgr.GetTasksByCreator("ann@x.io")] == ["second"]
     mgr.close()
+
+
+def test_snapshot_roundtrip(oracle, tmp_path):
+    """save -> load into a fresh table: every query answers the same, tombstones and edits included"""
+    n = 120_000
+    cfg = oracle.default_cfg(55, n, n_creators=300)
+    ot = oracle.OracleTable()
+    ot.add_synth(cfg, 0, n)
+    table = tt.TaskTable(0).generate(cfg, 0, n)
+    ids, _, _ = ot.export()
+    for k in (5, 77, 4000):
+        assert table.delete_task(bytes(ids[k])) and ot.delete_task(oracle.MODE_STORE, bytes(ids[k]))
+    new = uuid.uuid4().bytes  # lands out of TaskId order: the reloaded table must rebuild its id index
+    created = (TODAY - 12345) | (1 << 62)
+    assert table.insert_task(new, created, YDAY, b"late@example.org") == ot.add(new, "t", b"late@example.org", "a", created, YDAY)
+    table.sweep(tt.MODE_STORE)
+    ot.cron_job(oracle.MODE_STORE)
+    path = str(tmp_path / "tasks.snap")
+    table.save_snapshot(path)
+    again = tt.TaskTable(0).load_snapshot(path)
+    assert len(again) == len(table) == len(ot) and again.live_count() == ot.live_count()
+    assert (again.snapshot_flags()[0] == table.snapshot_flags()[0]).all()
+    assert (again.snapshot_flags()[1] == table.snapshot_flags()[1]).all()
+    for mode in (tt.MODE_FAKE, tt.MODE_STORE):
+        a, b = again.get_yesterdays_due(mode), table.get_yesterdays_due(mode)
+        assert (a.rows() == b.rows()).all() and (a.ids() == b.ids()).all()
+        assert a.rows().tolist() == ot.get_yesterdays_due(mode).tolist()
+    for who in (ot.created_by(3), b"late@example.org", b"nobody"):
+        assert again.get_by_creator(who).rows().tolist() == ot.get_by_creator(oracle.MODE_FAKE, who).tolist()
+    assert again.get_by_id(new).rows().tolist() == [n] and again.get_by_id(bytes(ids[77])).count == 0
+    assert again.get_by_id(bytes(ids[78])).rows().tolist() == [78]
+    with pytest.raises(tt.TaskTableError):
+        again.load_snapshot(path)  # not empty any more
+    with pytest.raises(tt.TaskTableError):
+        tt.TaskTable(0).load_snapshot(str(tmp_path / "missing.snap"))
+    table.close()
+    again.close()
