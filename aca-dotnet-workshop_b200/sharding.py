@@ -58,6 +58,8 @@ class HitExchange:
         if device.type == "cuda":
             self._host = self._host.pin_memory()
         self._flag = torch.zeros(1, dtype=torch.int32, device=device)
+        self.parts = int(os.environ.get("TT_EXCHANGE_PARTS", "1"))
+        self.send_cap = cap_per_rank  # entries every shard sends in run_fixed (see tune_send_cap)
         self.peer_rows = self.peer_ids = None
         self.transport = "nccl send/recv"
         # Opt-in only: on the 2 x B200 box measured in round 1 the mapped copy ran at PCIe speed
@@ -116,22 +118,81 @@ class HitExchange:
                     self.peer_ids[offs[self.rank]:offs[self.rank] + count].copy_(self.ids_all[:count], non_blocking=True)
             dist.all_reduce(self._flag, group=self.group)
             return counts
+        # every payload goes as `parts` send/recv pairs of one grouped launch, so NCCL can spread a
+        # large message over several channels
+        parts = self.parts
+
+        def pieces(lo, hi):
+            step = max(1, -(-(hi - lo) // parts))
+            return [(a, min(a + step, hi)) for a in range(lo, hi, step)]
+
         ops = []
         if self.rank == self.dst:
             for r in range(self.world):
                 if r == self.dst or counts[r] == 0:
                     continue
-                ops.append(dist.P2POp(dist.irecv, self.rows_all[offs[r]:offs[r + 1]], r, self.group))
-                if self.with_ids:
-                    ops.append(dist.P2POp(dist.irecv, self.ids_all[offs[r]:offs[r + 1]], r, self.group))
+                for a, b in pieces(offs[r], offs[r + 1]):
+                    ops.append(dist.P2POp(dist.irecv, self.rows_all[a:b], r, self.group))
+                    if self.with_ids:
+                        ops.append(dist.P2POp(dist.irecv, self.ids_all[a:b], r, self.group))
         elif count > 0:
-            ops.append(dist.P2POp(dist.isend, self.rows_all[:count], self.dst, self.group))
-            if self.with_ids:
-                ops.append(dist.P2POp(dist.isend, self.ids_all[:count], self.dst, self.group))
+            for a, b in pieces(0, count):
+                ops.append(dist.P2POp(dist.isend, self.rows_all[a:b], self.dst, self.group))
+                if self.with_ids:
+                    ops.append(dist.P2POp(dist.isend, self.ids_all[a:b], self.dst, self.group))
         if ops:
             for w in dist.batch_isend_irecv(ops):
                 w.wait()
         return counts
+
+    def tune_send_cap(self, observed_max_count, slack=1.1):
+        """Collective.  Shrinks the fixed message of run_fixed from the buffer capacity to
+        `slack` x the largest hit count any shard has seen so far (call it after warm-up)."""
+        want = torch.tensor([int(observed_max_count * slack) + 1024], dtype=torch.int64, device=self.rows_all.device)
+        if self.world > 1:
+            dist.all_reduce(want, op=dist.ReduceOp.MAX, group=self.group)
+        self.send_cap = min(self.cap, int(want.item()))
+        return self.send_cap
+
+    def run_fixed(self, count):
+        """Single-phase variant: every shard sends its whole `cap`-sized buffer into the root's slot
+        r*cap and its count into counts[r] in ONE grouped send/recv, so no count all-gather and no
+        host synchronisation precede the transfer (the price: cap instead of count entries travel).
+        Returns the device tensor of counts on the root (None elsewhere); rows of shard r are
+        rows_all[r*cap : r*cap + counts[r]].  A shard whose count exceeds send_cap raises."""
+        if count > self.send_cap:
+            raise RuntimeError(f"{count} hits exceed the agreed message size {self.send_cap}; use run() or tune_send_cap")
+        if self.world == 1:
+            self._counts[0] = count
+            return self._counts
+        assert self.dst == 0
+        self._host[0] = count
+        self._mine.copy_(self._host, non_blocking=True)
+        ops = []
+        if self.rank == self.dst:
+            self._counts[0:1].copy_(self._mine)
+            for r in range(1, self.world):
+                ops.append(dist.P2POp(dist.irecv, self._counts[r:r + 1], r, self.group))
+                ops.append(dist.P2POp(dist.irecv, self.rows_all[r * self.cap:r * self.cap + self.send_cap], r, self.group))
+                if self.with_ids:
+                    ops.append(dist.P2POp(dist.irecv, self.ids_all[r * self.cap:r * self.cap + self.send_cap], r, self.group))
+        else:
+            ops.append(dist.P2POp(dist.isend, self._mine, self.dst, self.group))
+            ops.append(dist.P2POp(dist.isend, self.rows_all[:self.send_cap], self.dst, self.group))
+            if self.with_ids:
+                ops.append(dist.P2POp(dist.isend, self.ids_all[:self.send_cap], self.dst, self.group))
+        for w in dist.batch_isend_irecv(ops):
+            w.wait()
+        return self._counts if self.rank == self.dst else None
+
+    def global_rows_fixed(self, counts):
+        """dst only: ascending global row numbers from the fixed-slot layout of run_fixed."""
+        cs = counts.tolist()
+        parts = []
+        for r, c in enumerate(cs):
+            seg = self.rows_all[r * self.cap: r * self.cap + c].to(torch.int64) & 0xFFFFFFFF
+            parts.append(seg + shard_rows(self.plan.n_total, self.world, r)[0])
+        return torch.cat(parts) if parts else torch.empty(0, dtype=torch.int64)
 
     def global_rows(self, counts):
         """dst only: global row numbers (int64, ascending) from the gathered shard-local ones."""

@@ -40,6 +40,9 @@ def parse():
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
     ap.add_argument("--exchange", default="rows", choices=["rows", "ids", "none"],
                     help="what the shards send to rank 0 after the sweep (N > 1)")
+    ap.add_argument("--exchange-mode", default="fixed", choices=["exact", "fixed"],
+                    help="exact: count all-gather, then count-sized send/recv; fixed: one grouped send/recv of "
+                         "capacity-sized buffers into fixed slots on rank 0")
     ap.add_argument("--cpu-sample-rows", type=int, default=8_000_000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -219,7 +222,7 @@ def run_b200(args):
                                    stream=stream.cuda_stream)
         out = None
         if world > 1 and args.exchange != "none":
-            out = ex.run(st.n_stored)
+            out = ex.run_fixed(st.n_stored) if args.exchange_mode == "fixed" else ex.run(st.n_stored)
         return st, out
 
     def barrier():
@@ -227,9 +230,13 @@ def run_b200(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    for _ in range(args.warmup):
+    seen = 0
+    for w in range(args.warmup):
         reset()
-        step()
+        if w == args.warmup - 1 and world > 1:
+            ex.tune_send_cap(seen)  # the fixed exchange message: 1.1 x the largest count seen in warm-up
+        st_w, _ = step()
+        seen = max(seen, st_w.n_stored)
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     kernel_ms, sweep_ms, gather_ms, hits, launches = [], [], [], 0, 0
     barrier()
@@ -335,7 +342,7 @@ def run_b200(args):
                                            "frac": (place_gbs / peak) if place_gbs else None,
                                            "note": "random 16 B TaskId gathers cost 64 B of DRAM each"}},
             "gpu_launches": launches,
-            "exchange": {"what": (args.exchange if world > 1 else "none"), "transport": ex.transport if world > 1 else None,
+            "exchange": {"what": (args.exchange if world > 1 else "none"), "transport": ex.transport if world > 1 else None, "mode": args.exchange_mode if world > 1 else None,
                          "ms": med([a - b for a, b in zip(step_ms, kernel_ms)]),
                          "note": "per-step time outside the three sweep kernels on rank 0: launch/sync overhead, "
                                  "count all-gather and the hit id gather (N > 1)"},

@@ -62,12 +62,17 @@ def _worker(rank, world, port, n_total, with_ids, q):
     ids_t[: local.size] = torch.from_numpy(ids_all[local])
     counts, glob, gids = pkg.exchange_hits(rows_t, int(local.size), plan, ids=ids_t if with_ids else None)
     # the persistent-buffer form used by bench.py must give the same answer
-    ex = pkg.HitExchange(plan, local.size + pad + 4000, torch.device("cpu"), with_ids=with_ids)
+    ex = pkg.HitExchange(plan, 6000, torch.device("cpu"), with_ids=with_ids)  # same capacity on every rank
     ex.rows_all[: local.size] = rows_t[: local.size]
     if with_ids:
         ex.ids_all[: local.size] = ids_t[: local.size]
     counts2 = ex.run(int(local.size))
     assert counts2 == counts
+    assert ex.tune_send_cap(int(local.size)) < 6000
+    fixed = ex.run_fixed(int(local.size))
+    if rank == 0:
+        assert fixed.tolist() == counts and (ex.global_rows_fixed(fixed) == glob).all()
+        ex.rows_all[: local.size] = rows_t[: local.size]  # run_fixed left the exact layout untouched only in slot 0
     if rank == 0:
         assert (ex.global_rows(counts2) == glob).all()
         if with_ids:
