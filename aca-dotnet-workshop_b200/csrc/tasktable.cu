@@ -60,6 +60,11 @@ inline int64_t round_up(int64_t x, int64_t m) { return (x + m - 1) / m * m; }
 struct TableCore {
   int device = 0;
   std::atomic<bool> alive{true};
+  // one spare result allocation: the block of the last freed result is kept for the next one, so a
+  // steady stream of queries does not pay cudaMalloc / cudaFree (both synchronise the device)
+  std::mutex pool_mu;
+  void* spare = nullptr;
+  size_t spare_bytes = 0;
 };
 
 struct tt_table {
@@ -127,7 +132,17 @@ struct tt_table {
 // returns one result per query over a single block).
 struct DeviceBlock {
   void* p = nullptr;
+  size_t bytes = 0;
+  std::shared_ptr<TableCore> core;
   ~DeviceBlock() {
+    if (!p) return;
+    if (core) {
+      std::lock_guard<std::mutex> lk(core->pool_mu);
+      if (core->alive && (!core->spare || core->spare_bytes < bytes)) {  // keep the larger of the two
+        std::swap(core->spare, p);
+        std::swap(core->spare_bytes, bytes);
+      }
+    }
     if (p) cudaFree(p);
   }
 };
@@ -445,7 +460,18 @@ int32_t result_alloc(tt_table* t, int64_t cap, tt_result** out) {
   r->core = t->core;
   r->cap = std::max<int64_t>(cap, 1);
   r->block = std::make_shared<DeviceBlock>();
-  cudaError_t e = cudaMalloc(&r->block->p, (size_t)r->cap * 20);  // ids (16 B each) first, then rows
+  r->block->core = t->core;
+  r->block->bytes = (size_t)r->cap * 20;  // ids (16 B each) first, then rows
+  {
+    std::lock_guard<std::mutex> lk(t->core->pool_mu);
+    if (t->core->spare && t->core->spare_bytes >= r->block->bytes && t->core->spare_bytes <= 4 * r->block->bytes + (1u << 20)) {
+      r->block->p = t->core->spare;
+      r->block->bytes = t->core->spare_bytes;
+      t->core->spare = nullptr;
+      t->core->spare_bytes = 0;
+    }
+  }
+  cudaError_t e = r->block->p ? cudaSuccess : cudaMalloc(&r->block->p, r->block->bytes);
   if (e != cudaSuccess) {
     cudaGetLastError();
     delete r;
@@ -571,8 +597,13 @@ int32_t tt_create(int32_t device, tt_table** out) {
 int32_t tt_destroy(tt_table* t) {
   if (!t) return TT_OK;
   {
+    DeviceGuard g(t->device);
     std::lock_guard<std::mutex> lk(t->mu);
+    std::lock_guard<std::mutex> lk2(t->core->pool_mu);
     t->core->alive = false;
+    cudaFree(t->core->spare);
+    t->core->spare = nullptr;
+    t->core->spare_bytes = 0;
   }
   {
     DeviceGuard g(t->device);
