@@ -1,5 +1,8 @@
-// sweep_lab.cu — development harness: ordering strategies for the sweep's compaction, timed on
-// synthetic columns (5 % matches, 50 % completed).  Not part of the product.
+// sweep_lab.cu — development harness, not part of the product: times the library's sweep kernel at
+// several grid sizes on synthetic columns (5 % matches, 50 % completed) and checks whether K3 (random
+// TaskId gathers) can overlap K1 (streaming) on two streams.  Earlier versions of this file also
+// carried the in-order compaction variants (decoupled look-back, published-count scan) whose timings
+// are recorded in profiles/r1_summary.md; they were removed together with those kernels.
 #include <cuda_runtime.h>
 #include <cstdio>
 #include <cstdint>
@@ -19,17 +22,15 @@ __global__ void fill(uint32_t* due, uint32_t* comp, uint32_t* over, int64_t n, u
   if ((threadIdx.x & 31) == 0) { comp[i >> 5] = c; over[i >> 5] = 0; }
 }
 
-struct LabCtl { unsigned int tile_counter; unsigned int pad; unsigned long long cursor; };
-
 int main(int argc, char** argv) {
   const int64_t N = argc > 1 ? atoll(argv[1]) : (1ll << 30);
   const int64_t NP = (N + 32767) / 32768 * 32768;
   const uint32_t yday = 739924;
-  uint32_t *due, *comp, *over, *rows, *status, *ubase, *tcount, *gsum; SweepCtl* ctl; LabCtl* lctl;
+  uint32_t *due, *comp, *over, *rows, *status, *ubase, *tcount, *gsum; SweepCtl* ctl;
   CK(cudaMalloc(&due, NP * 4)); CK(cudaMalloc(&comp, NP / 8)); CK(cudaMalloc(&over, NP / 8));
   CK(cudaMalloc(&rows, NP / 16 * 4)); CK(cudaMalloc(&status, (NP / 8192 + 4) * 4));
   CK(cudaMalloc(&ubase, NP / 8192 * 4)); CK(cudaMalloc(&tcount, NP / 8192 * 4));
-  CK(cudaMalloc(&ctl, sizeof(SweepCtl))); CK(cudaMalloc(&lctl, sizeof(LabCtl)));
+  CK(cudaMalloc(&ctl, sizeof(SweepCtl)));
   CK(cudaMemset(due, 0xFF, NP * 4));
   fill<<<(unsigned)((NP + 255) / 256), 256>>>(due, comp, over, N, yday);
   CK(cudaDeviceSynchronize());
@@ -44,13 +45,11 @@ int main(int argc, char** argv) {
       SweepCtl init; init.tile_counter = 0; init.pad = 0; init.cursor = 0; init.stored = ~0ull;
       cudaMemset(gsum, 0, 4096);
       cudaMemcpy(ctl, &init, sizeof init, cudaMemcpyHostToDevice);
-      cudaMemset(lctl, 0, sizeof(LabCtl));
       cudaMemset(status, 0, (NP / 8192 + 4) * 4);
       cudaEventRecord(a); launch(148 * grid_mult); cudaEventRecord(b); cudaEventSynchronize(b);
       float ms; cudaEventElapsedTime(&ms, a, b); best = std::min(best, ms);
       SweepCtl h; cudaMemcpy(&h, ctl, sizeof h, cudaMemcpyDeviceToHost);
-      LabCtl lh; cudaMemcpy(&lh, lctl, sizeof lh, cudaMemcpyDeviceToHost);
-      total = h.cursor; (void)lh;
+      total = h.cursor;
     }
     printf("%-40s %8.3f ms  %7.1f GB/s  hits=%llu  err=%s\n", name, best, N * 4.25 / best / 1e6, total, cudaGetErrorString(cudaGetLastError()));
   };
