@@ -6,8 +6,8 @@
 // whose hash equals a query's is a candidate and its dictionary string is compared byte for byte
 // with that query (ordinal, case-sensitive — equal UTF-8 bytes <=> equal UTF-16 code units), so
 // hash collisions never reach the result.  With more than one query the hashes sit in a small
-// open-addressing table in shared memory (load factor <= 1/4): the common row costs one 32-bit
-// shared-memory probe.
+// open-addressing table in shared memory (1024 to 8192 slots, load factor 1/64 for up to 128
+// queries): the common row costs one 32-bit shared-memory probe.
 // K3m replaces the per-task upsert loop of Api/Services/TasksStoreManager.cs:143-148: each
 // listed TaskId is located by binary search over the TaskId-ordered rows and its overdue bit
 // is set with one atomicOr.

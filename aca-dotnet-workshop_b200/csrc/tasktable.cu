@@ -850,7 +850,10 @@ int32_t tt_get_by_creators(tt_table* t, const char* const* utf8, const int32_t* 
   }
   const uint32_t nu = (uint32_t)first_of.size();
   uint32_t slots = 1024;
-  while (slots < 16 * nu && slots < tt::kMaxSlots) slots <<= 1;
+  // load factor 1/64 up to 64 queries; 4096 slots (48 KB) keep 4 CTAs per SM, the 8192-slot table
+  // (2 CTAs per SM) only pays off for very large batches
+  while (slots < 64 * nu && slots < 4096) slots <<= 1;
+  if (nu > 512) slots = tt::kMaxSlots;
   std::vector<uint64_t> hash(nu), slot_key(slots, 0);
   std::vector<uint32_t> off(nu + 1, 0), slot_val(slots, tt::kSlotEmpty);
   std::vector<uint8_t> pool;
