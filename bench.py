@@ -368,15 +368,16 @@ def run_extra(args):
 
     pkg = importlib.import_module("aca-dotnet-workshop_b200")
     tt = pkg.tasktable
-    torch.cuda.set_device(0)
-    dev = torch.device("cuda", 0)
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
     peak, peak_src = peaks()
     stream = torch.cuda.Stream(device=dev)
     torch.cuda.set_stream(stream)
     med = lambda xs: sorted(xs)[len(xs) // 2]
-    flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
 
     if args.workload == "sweep10m":
+        flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
         n = 10_000_000
         cfg = pkg.default_cfg(0x5EED0001, n)
         table = pkg.TaskTable(0).generate(cfg, 0, n)
@@ -455,25 +456,54 @@ def run_extra(args):
         return
 
     if args.workload == "mixed":
-        n = args.rows
-        cfg = pkg.default_cfg(SEED, n)
-        table = pkg.TaskTable(0).generate(cfg, 0, n)
+        # BASELINE.json config 5: ONE 1 B-task table (args.rows) sharded by TaskId range over the
+        # GPUs; per tick: sweep + hit id gather on rank 0, then 64 creator filters as one batch on
+        # every shard and a sum of the per-creator match counts.
+        import torch.distributed as dist
+
+        world = int(os.environ.get("WORLD_SIZE", "1"))
+        rank = int(os.environ.get("RANK", "0"))
+        if world > 1:
+            dist.init_process_group("nccl", device_id=dev)
+        n_total = args.rows
+        plan = pkg.ShardPlan(n_total, world, rank)
+        n = plan.n_rows
+        cfg = pkg.default_cfg(SEED, n_total)
+        table = pkg.TaskTable(local).generate(cfg, plan.first_row, n)
         nbytes = (n + 7) // 8
         pristine = torch.empty(nbytes, dtype=torch.uint8, device=dev)
         tt._check(tt.lib().tt_snapshot_flags(table._h, None, pristine.data_ptr()))
         cap = int(n * 0.032) + 65536
-        d_rows = torch.empty(cap, dtype=torch.int32, device=dev)
+        ex = pkg.HitExchange(plan, cap, dev, with_ids=False)
         d_ids = torch.empty((cap, 16), dtype=torch.uint8, device=dev)
         rng = np.random.default_rng(5)
         names = [("user%07d@mail%d.example" % (k, k % 97)).encode() for k in rng.integers(0, 1_000_000, size=64)]
-        wall, sweep_k, scan_k, order_k = [], [], [], []
+        counts_dev = torch.zeros(64, dtype=torch.int64, device=dev)
+        counts_host = torch.zeros(64, dtype=torch.int64).pin_memory()
+
+        def sync_all():
+            if world > 1:
+                dist.barrier()
+            torch.cuda.synchronize()
+
+        wall, sweep_k, scan_k, order_k, matches = [], [], [], [], 0
         for i in range(args.warmup + args.steps):
             tt._check(tt.lib().tt_restore_flags(table._h, None, pristine.data_ptr()))
-            torch.cuda.synchronize()
+            if i == args.warmup - 1 and world > 1:
+                ex.tune_send_cap(int(n * 0.0255))
+            sync_all()
             t0 = time.perf_counter()
-            st, _ = table.sweep_device(tt.MODE_STORE, tt.SWEEP_MARK, d_rows.data_ptr(), d_ids.data_ptr(), cap,
+            st, _ = table.sweep_device(tt.MODE_STORE, tt.SWEEP_MARK, ex.rows_all.data_ptr(), d_ids.data_ptr(), cap,
                                        stream=stream.cuda_stream)
+            if world > 1:
+                ex.run_fixed(st.n_stored)
             rs = table.get_by_creators(names)
+            for k, r in enumerate(rs):
+                counts_host[k] = r.count
+            counts_dev.copy_(counts_host, non_blocking=True)
+            if world > 1:
+                dist.all_reduce(counts_dev)
+            sync_all()
             dt = time.perf_counter() - t0
             op = table.last_op_stats()
             for r in rs:
@@ -483,15 +513,27 @@ def run_extra(args):
                 sweep_k.append(st.kernel_ms)
                 scan_k.append(op.scan_ms)
                 order_k.append(op.order_ms)
-        line = {"metric": "mixed_cron_batch_ms", "workload": f"config 5 per GPU: {n}-task sweep + 64 creator filters (one batch)",
-                "value": med(wall), "unit": "ms", "higher_is_better": False, "sweep_kernels_ms": med(sweep_k),
-                "creator_scan_ms": med(scan_k), "creator_order_ms": med(order_k), "hits": st.n_listed,
-                "creator_matches": op.matches,
-                "roofline": {"bound": "hbm", "unit": "GB/s", "peak": peak,
-                             "creator_scan_achieved": n * 8 / (med(scan_k) * 1e-3) / 1e9,
-                             "creator_scan_frac": n * 8 / (med(scan_k) * 1e-3) / 1e9 / peak}}
-        print(json.dumps(line))
+                matches = int(counts_dev.sum().item())
+        w = torch.tensor([med(wall)], dtype=torch.float64, device=dev)
+        hits = torch.tensor([st.n_listed], dtype=torch.int64, device=dev)
+        if world > 1:
+            dist.all_reduce(w, op=dist.ReduceOp.MAX)
+            dist.all_reduce(hits)
+        if rank == 0:
+            line = {"metric": "mixed_cron_batch_ms", "n_gpus": world,
+                    "workload": f"config 5: {n_total}-task table over {world} GPU(s), sweep + hit id gather + 64 creator "
+                                "filters (one batch per shard) + match-count all-reduce",
+                    "value": float(w.item()), "unit": "ms", "higher_is_better": False, "rows_per_gpu": n,
+                    "sweep_kernels_ms": med(sweep_k), "creator_scan_ms": med(scan_k), "creator_order_ms": med(order_k),
+                    "hits": int(hits.item()), "creator_matches": matches,
+                    "roofline": {"bound": "hbm", "unit": "GB/s", "peak": peak,
+                                 "creator_scan_achieved": n * 8 / (med(scan_k) * 1e-3) / 1e9,
+                                 "creator_scan_frac": n * 8 / (med(scan_k) * 1e-3) / 1e9 / peak}}
+            print(json.dumps(line))
         table.close()
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
 
 
 if __name__ == "__main__":
