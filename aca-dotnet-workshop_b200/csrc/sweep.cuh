@@ -329,4 +329,21 @@ __global__ void __launch_bounds__(kPlaceThreads) place_hits_kernel(const SweepCt
   }
 }
 
+// ---- compact form of a row-ordered hit list (for the cross-shard exchange) --------------------
+// A hit is its tile (implied by per-tile counts) and a 13-bit offset inside the tile: 2 bytes per
+// hit instead of 4, plus 4 bytes per tile.  pack: off16[i] = rows[i] % tile; the per-tile counts
+// are the ones K1 recorded.  expand: one warp per tile rebuilds the row numbers.
+__global__ void pack_hits16_kernel(const uint32_t* rows, int64_t n, uint16_t* off16) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) off16[i] = (uint16_t)(rows[i] & (TT_TILE_ROWS - 1));
+}
+
+__global__ void expand_hits16_kernel(const uint32_t* tile_count, const uint32_t* tile_first, uint32_t num_tiles,
+                                     const uint16_t* off16, uint32_t* rows_out) {
+  const uint32_t t = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (t >= num_tiles) return;
+  const uint32_t first = tile_first[t], cnt = tile_count[t];
+  for (uint32_t k = threadIdx.x & 31u; k < cnt; k += 32) rows_out[first + k] = t * TT_TILE_ROWS + off16[first + k];
+}
+
 }  // namespace tt

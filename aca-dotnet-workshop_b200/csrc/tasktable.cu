@@ -1610,6 +1610,46 @@ int32_t tt_load_snapshot(tt_table* t, const char* path) {
 
 }  // extern "C"
 
+// ---- compact hit lists for the cross-shard exchange ------------------------------------------------
+
+extern "C" {
+
+int32_t tt_pack_hits(tt_table* t, const uint32_t* d_rows, int64_t n, uint16_t* d_off16, uint32_t* d_tile_count,
+                     int64_t* n_tiles, void* stream_) {
+  if (!t || !n_tiles || n < 0 || (n > 0 && (!d_rows || !d_off16)) || !d_tile_count) return fail(TT_ERR_ARG, "bad argument");
+  std::lock_guard<std::mutex> lk(t->mu);
+  DeviceGuard g(t->device);
+  cudaStream_t stream = stream_ ? (cudaStream_t)stream_ : t->stream;
+  *n_tiles = t->n_pad / TT_TILE_ROWS;
+  if (t->n_pad == 0) return TT_OK;
+  // per-tile counts as the last complete sweep recorded them (tile_words[1])
+  TT_CUDA(cudaMemcpyAsync(d_tile_count, t->tile_words + t->n_tiles, (size_t)*n_tiles * 4, cudaMemcpyDeviceToDevice, stream));
+  if (n) {
+    tt::pack_hits16_kernel<<<grid_for(n, 256), 256, 0, stream>>>(d_rows, n, d_off16);
+    TT_CUDA(cudaGetLastError());
+  }
+  return TT_OK;
+}
+
+int32_t tt_expand_hits(int32_t device, const uint32_t* d_tile_count, int64_t n_tiles, const uint16_t* d_off16,
+                       uint32_t* d_scratch, uint32_t* d_rows_out, void* stream_) {
+  if (n_tiles < 0 || (n_tiles > 0 && (!d_tile_count || !d_scratch || !d_rows_out))) return fail(TT_ERR_ARG, "bad argument");
+  if (n_tiles == 0) return TT_OK;
+  DeviceGuard g(device);
+  cudaStream_t stream = (cudaStream_t)stream_;
+  const uint32_t nt = (uint32_t)n_tiles;
+  const uint32_t groups = (nt + tt::kTilesPerGroup - 1) / tt::kTilesPerGroup;
+  uint32_t* tile_first = d_scratch;        // [n_tiles]
+  uint32_t* group_sum = d_scratch + nt;    // [groups]
+  tt::group_reduce_kernel<<<groups, tt::kTilesPerGroup, 0, stream>>>(d_tile_count, nt, group_sum);
+  tt::tile_offsets_kernel<<<groups, tt::kTilesPerGroup, 0, stream>>>(d_tile_count, group_sum, nt, tile_first);
+  tt::expand_hits16_kernel<<<(nt + 7) / 8, 256, 0, stream>>>(d_tile_count, tile_first, nt, d_off16, d_rows_out);
+  TT_CUDA(cudaGetLastError());
+  return TT_OK;
+}
+
+}  // extern "C"
+
 // ---- the sweep with its working memory in a fixed device array ---------------------------------
 //
 // For callers that cannot allocate (see include/tasktable.h).  Everything tt_sweep_device keeps

@@ -185,6 +185,55 @@ class HitExchange:
             w.wait()
         return self._counts if self.rank == self.dst else None
 
+    # ---- compact form: 2 bytes per hit (in-tile offsets) + 4 bytes per tile (hit counts) ------------
+    def enable_compact(self, tile_rows=8192):
+        """Allocates the buffers of run_fixed_compact.  Every rank must call it."""
+        rows_max = max(shard_rows(self.plan.n_total, self.world, r)[1] - shard_rows(self.plan.n_total, self.world, r)[0]
+                       for r in range(self.world))
+        self.tile_rows = tile_rows
+        self.n_tiles = max(1, -(-rows_max // tile_rows))
+        k = self.world if self.rank == self.dst else 1
+        dev = self.rows_all.device
+        self.off16_all = torch.zeros(k * self.cap, dtype=torch.int16, device=dev)
+        self.tile_counts_all = torch.zeros(k * self.n_tiles, dtype=torch.int32, device=dev)
+        return self
+
+    def run_fixed_compact(self, count):
+        """Like run_fixed, but what travels is the compact form produced by TaskTable.pack_hits into
+        off16_all[:count] / tile_counts_all[:n_tiles]: send_cap 2-byte offsets + n_tiles counts per shard."""
+        if count > self.send_cap:
+            raise RuntimeError(f"{count} hits exceed the agreed message size {self.send_cap}")
+        if self.world == 1:
+            self._counts[0] = count
+            return self._counts
+        self._host[0] = count
+        self._mine.copy_(self._host, non_blocking=True)
+        ops, nt, cap = [], self.n_tiles, self.cap
+        wire = self.off16_all.view(torch.uint8)  # NCCL has no 16-bit integer type: the offsets travel as bytes
+        if self.rank == self.dst:
+            self._counts[0:1].copy_(self._mine)
+            for r in range(1, self.world):
+                ops.append(dist.P2POp(dist.irecv, self._counts[r:r + 1], r, self.group))
+                ops.append(dist.P2POp(dist.irecv, self.tile_counts_all[r * nt:(r + 1) * nt], r, self.group))
+                ops.append(dist.P2POp(dist.irecv, wire[2 * r * cap:2 * (r * cap + self.send_cap)], r, self.group))
+        else:
+            ops.append(dist.P2POp(dist.isend, self._mine, self.dst, self.group))
+            ops.append(dist.P2POp(dist.isend, self.tile_counts_all[:nt], self.dst, self.group))
+            ops.append(dist.P2POp(dist.isend, wire[:2 * self.send_cap], self.dst, self.group))
+        for w in dist.batch_isend_irecv(ops):
+            w.wait()
+        return self._counts if self.rank == self.dst else None
+
+    def global_rows_compact(self, counts, expand):
+        """dst only: ascending global row numbers from the compact layout.  `expand(tile_counts, off16,
+        n_hits)` must return the shard-local rows as an int tensor (tasktable.expand_hits on a GPU)."""
+        parts = []
+        for r, c in enumerate(counts.tolist()):
+            local = expand(self.tile_counts_all[r * self.n_tiles:(r + 1) * self.n_tiles],
+                           self.off16_all[r * self.cap:r * self.cap + c], c)
+            parts.append((local.to(torch.int64) & 0xFFFFFFFF) + shard_rows(self.plan.n_total, self.world, r)[0])
+        return torch.cat(parts) if parts else torch.empty(0, dtype=torch.int64)
+
     def global_rows_fixed(self, counts):
         """dst only: ascending global row numbers from the fixed-slot layout of run_fixed."""
         cs = counts.tolist()

@@ -46,7 +46,7 @@ EXPORTS = [
     "tt_snapshot_flags", "tt_restore_flags", "tt_count_flags", "tt_result_digest",
     "tt_sweep_device", "tt_get_device_view", "tt_sweep_static", "tt_get_by_creators", "tt_last_op_stats",
     "tt_get_by_id", "tt_insert_task", "tt_update_task", "tt_mark_completed", "tt_delete_task", "tt_live_count",
-    "tt_save_snapshot", "tt_load_snapshot",
+    "tt_save_snapshot", "tt_load_snapshot", "tt_pack_hits", "tt_expand_hits",
 ]
 
 
@@ -178,6 +178,8 @@ def lib():
     L.tt_mark_completed.argtypes = [vp, vp, P(i32)]
     L.tt_delete_task.argtypes = [vp, vp, P(i32)]
     L.tt_live_count.argtypes = [vp, P(i64)]
+    L.tt_pack_hits.argtypes = [vp, vp, i64, vp, vp, P(i64), vp]
+    L.tt_expand_hits.argtypes = [i32, vp, i64, vp, vp, vp, vp]
     L.tt_save_snapshot.argtypes = [vp, C.c_char_p]
     L.tt_load_snapshot.argtypes = [vp, C.c_char_p]
     L.tt_result_count.argtypes = [vp, P(i64)]
@@ -253,6 +255,11 @@ class Result:
             self.free()
         except Exception:
             pass
+
+
+def expand_hits(device, d_tile_count, n_tiles, d_off16, d_scratch, d_rows_out, stream=None):
+    """Inverse of TaskTable.pack_hits on any device (device addresses)."""
+    _check(lib().tt_expand_hits(device, d_tile_count, n_tiles, d_off16, d_scratch, d_rows_out, stream))
 
 
 class TaskTable:
@@ -421,6 +428,13 @@ class TaskTable:
         c, o = C.c_int64(0), C.c_int64(0)
         _check(lib().tt_count_flags(self._h, C.byref(c), C.byref(o)))
         return c.value, o.value
+
+    def pack_hits(self, d_rows, n, d_off16, d_tile_count, stream=None):
+        """Compact form of the hit list of the last sweep_device call: 2-byte in-tile offsets + per-tile
+        counts (device addresses).  Returns the number of tiles."""
+        nt = C.c_int64(0)
+        _check(lib().tt_pack_hits(self._h, d_rows, n, d_off16, d_tile_count, C.byref(nt), stream))
+        return nt.value
 
     def save_snapshot(self, path):
         _check(lib().tt_save_snapshot(self._h, os.fsencode(path)))

@@ -38,8 +38,9 @@ def parse():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--rows", type=int, default=1_000_000_000, help="rows per GPU (weak) or in total (strong)")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
-    ap.add_argument("--exchange", default="rows", choices=["rows", "ids", "none"],
-                    help="what the shards send to rank 0 after the sweep (N > 1)")
+    ap.add_argument("--exchange", default="compact", choices=["compact", "rows", "ids", "none"],
+                    help="what the shards send to rank 0 after the sweep (N > 1): compact = the hit rows as 2-byte "
+                         "in-tile offsets + per-tile counts, rows = u32 row numbers, ids = rows + 16-byte TaskIds")
     ap.add_argument("--exchange-mode", default="fixed", choices=["exact", "fixed"],
                     help="exact: count all-gather, then count-sized send/recv; fixed: one grouped send/recv of "
                          "capacity-sized buffers into fixed slots on rank 0")
@@ -211,6 +212,8 @@ def run_b200(args):
     ex = pkg.HitExchange(plan, cap, dev, with_ids=True)
     d_rows, d_ids = ex.rows_all, ex.ids_all
     ex.with_ids = with_ids
+    if args.exchange == "compact":
+        ex.enable_compact()
     stream = torch.cuda.Stream(device=dev)  # non-default: its handle is what the C ABI launches on
     torch.cuda.set_stream(stream)
 
@@ -221,7 +224,11 @@ def run_b200(args):
         st, _ = table.sweep_device(tt.MODE_STORE, tt.SWEEP_MARK, d_rows.data_ptr(), d_ids.data_ptr(), cap,
                                    stream=stream.cuda_stream)
         out = None
-        if world > 1 and args.exchange != "none":
+        if world > 1 and args.exchange == "compact":
+            table.pack_hits(d_rows.data_ptr(), st.n_stored, ex.off16_all.data_ptr(), ex.tile_counts_all.data_ptr(),
+                            stream=stream.cuda_stream)
+            out = ex.run_fixed_compact(st.n_stored)
+        elif world > 1 and args.exchange != "none":
             out = ex.run_fixed(st.n_stored) if args.exchange_mode == "fixed" else ex.run(st.n_stored)
         return st, out
 
@@ -251,7 +258,7 @@ def run_b200(args):
             sweep_ms.append(st.sweep_ms)
             gather_ms.append(st.gather_ms)
             hits = st.n_listed
-            launches += st.launches
+            launches += st.launches + (1 if world > 1 and args.exchange == "compact" else 0)
         barrier()
     step_ms = [a.elapsed_time(b) for a, b in ev]
     total_ms = torch.tensor([sum(step_ms)], dtype=torch.float64, device=dev)

@@ -235,6 +235,20 @@ typedef struct tt_device_view {
 } tt_device_view;
 int32_t tt_get_device_view(tt_table* t, tt_device_view* out);
 
+/* ---- compact hit lists (what shards exchange) ---------------------------------
+ * A row-ordered hit list is equivalent to "hits per 8192-row tile" + a 13-bit offset per hit:
+ * 2 bytes per hit instead of 4.  No reference counterpart (the reference ships whole TaskModel
+ * objects as JSON between its processes, Svc/Controllers/ScheduledTasksManagerController.cs:28,44).
+ * tt_pack_hits   : after a complete tt_sweep_device call on this table, writes d_off16[i] = offset of
+ *                  d_rows[i] in its tile (i < n) and copies the per-tile hit counts of that sweep
+ *                  (uint32 per tile, *n_tiles of them = n_padded / 8192) into d_tile_count.
+ * tt_expand_hits : the inverse, on any device: rebuilds the shard-local row numbers.  d_scratch needs
+ *                  n_tiles + n_tiles/1024 + 1 uint32 of device memory. */
+int32_t tt_pack_hits(tt_table* t, const uint32_t* d_rows, int64_t n, uint16_t* d_off16, uint32_t* d_tile_count,
+                     int64_t* n_tiles, void* stream);
+int32_t tt_expand_hits(int32_t device, const uint32_t* d_tile_count, int64_t n_tiles, const uint16_t* d_off16,
+                       uint32_t* d_scratch, uint32_t* d_rows_out, void* stream);
+
 /* ---- snapshot ---------------------------------------------------------------------------------
  * Saves / restores the whole table (all columns, flags, creator dictionary, tombstones) as one
  * file in the device layout — the counterpart of the reference keeping its tasks in a state store

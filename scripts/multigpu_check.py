@@ -43,6 +43,27 @@ def main():
         same = same and bool((ex.global_rows(counts2) == glob).all()) and bool((ex.ids_all[: sum(counts2)] == gids).all())
         print("exchange transport:", ex.transport, "agrees" if same else "DIFFERS")
     assert same
+    # the compact exchange (2-byte offsets + per-tile counts), expanded again on rank 0
+    ex.enable_compact()
+    ex.tune_send_cap(st.n_stored)
+    table.pack_hits(d_rows.data_ptr(), st.n_stored, ex.off16_all.data_ptr(), ex.tile_counts_all.data_ptr(),
+                    stream=stream.cuda_stream)
+    cdev = ex.run_fixed_compact(st.n_stored)
+    torch.cuda.synchronize()
+    if rank == 0:
+        scratch = torch.empty(ex.n_tiles + ex.n_tiles // 1024 + 8, dtype=torch.int32, device=dev)
+
+        def expand(tile_counts, off16, n_hits):
+            out = torch.empty(max(n_hits, 1), dtype=torch.int32, device=dev)
+            tt.expand_hits(local, tile_counts.data_ptr(), ex.n_tiles, off16.data_ptr(), scratch.data_ptr(), out.data_ptr(),
+                           stream.cuda_stream)
+            torch.cuda.synchronize()
+            return out[:n_hits]
+
+        g2 = ex.global_rows_compact(cdev, expand)
+        ok2 = cdev.tolist() == counts and bool((g2 == glob).all())
+        print("compact exchange", "agrees" if ok2 else "DIFFERS")
+        assert ok2
     ok = True
     if rank == 0:
         from oracle import oracle as orc

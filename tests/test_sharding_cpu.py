@@ -70,7 +70,17 @@ def _worker(rank, world, port, n_total, with_ids, q):
     assert counts2 == counts
     assert ex.tune_send_cap(int(local.size)) < 6000
     fixed = ex.run_fixed(int(local.size))
+    # compact transport (the packing itself is a device kernel; here the same encoding in numpy)
+    ex.enable_compact()
+    tc = np.bincount(local // 8192, minlength=ex.n_tiles).astype(np.int32)
+    ex.tile_counts_all[: ex.n_tiles] = torch.from_numpy(tc)
+    ex.off16_all[: local.size] = torch.from_numpy((local % 8192).astype(np.int16))
+    cdev = ex.run_fixed_compact(int(local.size))
     if rank == 0:
+        def expand(tile_counts, off16, n_hits):
+            t = np.repeat(np.arange(ex.n_tiles), tile_counts.numpy())
+            return torch.from_numpy((t * 8192 + off16.numpy().astype(np.int64)[:n_hits]).astype(np.int64))
+        assert cdev.tolist() == counts and (ex.global_rows_compact(cdev, expand) == glob).all()
         assert fixed.tolist() == counts and (ex.global_rows_fixed(fixed) == glob).all()
         ex.rows_all[: local.size] = rows_t[: local.size]  # run_fixed left the exact layout untouched only in slot 0
     if rank == 0:

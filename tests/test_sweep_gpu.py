@@ -270,3 +270,30 @@ def test_full_size_properties_1b(oracle, mode):
     res2, n2, _ = table.sweep(mode)
     assert (res2.count, n2) == ((0, 0) if mode == tt.MODE_STORE else (want.n_listed, 0))
     table.close()
+
+
+def test_compact_hit_list_roundtrip(oracle):
+    """tt_pack_hits / tt_expand_hits: 2-byte in-tile offsets + per-tile counts rebuild the row list"""
+    import torch
+
+    n = 700_001
+    cfg = oracle.default_cfg(41, n, n_creators=10)
+    table = tt.TaskTable(0).generate(cfg, 0, n)
+    cap = 40_000
+    rows = torch.zeros(cap, dtype=torch.int32, device="cuda")
+    st, _ = table.sweep_device(tt.MODE_STORE, tt.SWEEP_LIST_ONLY, rows.data_ptr(), None, cap)
+    nt_cap = (n + 8191) // 8192
+    off16 = torch.zeros(cap, dtype=torch.int16, device="cuda")
+    counts = torch.zeros(nt_cap, dtype=torch.int32, device="cuda")
+    nt = table.pack_hits(rows.data_ptr(), st.n_stored, off16.data_ptr(), counts.data_ptr())
+    torch.cuda.synchronize()
+    assert nt == nt_cap and int(counts.sum()) == st.n_stored
+    want = rows[: st.n_stored].cpu().numpy().view(np.uint32)
+    assert (off16[: st.n_stored].cpu().numpy().view(np.uint16) == want % 8192).all()
+    assert (np.bincount(want // 8192, minlength=nt) == counts.cpu().numpy()).all()
+    back = torch.full((cap,), -1, dtype=torch.int32, device="cuda")
+    scratch = torch.empty(nt + nt // 1024 + 8, dtype=torch.int32, device="cuda")
+    tt.expand_hits(0, counts.data_ptr(), nt, off16.data_ptr(), scratch.data_ptr(), back.data_ptr())
+    torch.cuda.synchronize()
+    assert (back[: st.n_stored].cpu().numpy().view(np.uint32) == want).all()
+    table.close()
