@@ -27,4 +27,4 @@ from .tasktable import (  # noqa: F401
     lib_path,
 )
 from .tasks_manager import GpuTasksManager, TaskModel  # noqa: F401
-from .sharding import HitExchange, ShardPlan, exchange_hits, shard_rows  # noqa: F401
+from .sharding import HitExchange, PushExchange, ShardPlan, exchange_hits, push_slot_layout, shard_rows  # noqa: F401

@@ -351,10 +351,21 @@ int32_t check_clock(int64_t today_local_ticks, uint32_t* yesterday) {
   return TT_OK;
 }
 
+// Which K3 a plain sweep uses: the tile-ordered place_group_kernel (default; measured 0.49 ms for
+// 25 M hits on B200) or the older hit-ordered place_hits_kernel (0.55 ms; TT_PLACE_KERNEL=hits,
+// read once, kept for A/B timing).
+bool place_by_group() {
+  static const bool by_group = [] {
+    const char* e = getenv("TT_PLACE_KERNEL");
+    return e ? strcmp(e, "hits") != 0 : true;
+  }();
+  return by_group;
+}
+
 // Launches the sweep kernel over rows [first_row, n) on `stream`, waits, fills *st.
 int32_t sweep_run(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_ticks, int64_t run_at_utc_ticks,
                   int64_t first_row, uint32_t* d_rows, uint4* d_ids, int64_t cap, tt_sweep_stats* st,
-                  cudaStream_t stream) {
+                  cudaStream_t stream, const tt::PushTarget* push = nullptr) {
   memset(st, 0, sizeof *st);
   if (mode != TT_MODE_FAKE && mode != TT_MODE_STORE) return fail(TT_ERR_ARG, "mode must be TT_MODE_FAKE or TT_MODE_STORE");
   uint32_t yesterday = 0;
@@ -375,7 +386,7 @@ int32_t sweep_run(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_
   const uint32_t num_tiles = (uint32_t)(t->n_pad / TT_TILE_ROWS) - first_tile;
 
   // scratch for the unordered hit list K1 writes before K3 puts it in row order
-  const bool listing = d_rows != nullptr;
+  const bool listing = d_rows != nullptr || push != nullptr;
   if (listing && cap > t->hit_list_cap) {
     cudaFree(t->hit_list);
     t->hit_list = nullptr;
@@ -428,11 +439,20 @@ int32_t sweep_run(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_
     // K2 + K3: row order and TaskIds; the hit count is read from the control block on the device
     tt::tile_offsets_kernel<<<n_groups, tt::kTilesPerGroup, 0, stream>>>(p.tile_count, p.group_sum, num_tiles, tile_first);
     TT_CUDA(cudaGetLastError());
-    const int64_t per_cta = (int64_t)tt::kPlaceThreads * tt::kPlaceUnroll;
-    const unsigned pgrid =
-        (unsigned)std::max<int64_t>(1, std::min<int64_t>((cap + per_cta - 1) / per_cta, (int64_t)t->sm_count * 8));
-    tt::place_hits_kernel<TT_TILE_ROWS><<<pgrid, tt::kPlaceThreads, 0, stream>>>(
-        t->ctl, t->hit_list, p.tile_slot, tile_first, first_tile, t->task_id, d_rows, d_ids);
+    if (push || place_by_group()) {
+      // K3g: tile-ordered placement, optionally fused with the push of the compact form (sweep.cuh)
+      const tt::PushTarget none = {nullptr, nullptr, nullptr};
+      const unsigned ggrid = (num_tiles + tt::kGroupTiles - 1) / tt::kGroupTiles;
+      tt::place_group_kernel<TT_TILE_ROWS><<<ggrid, tt::kGroupThreads, 0, stream>>>(
+          t->ctl, t->hit_list, p.tile_slot, p.tile_count, tile_first, num_tiles, t->task_id, d_rows, d_ids,
+          push ? *push : none);
+    } else {
+      const int64_t per_cta = (int64_t)tt::kPlaceThreads * tt::kPlaceUnroll;
+      const unsigned pgrid =
+          (unsigned)std::max<int64_t>(1, std::min<int64_t>((cap + per_cta - 1) / per_cta, (int64_t)t->sm_count * 8));
+      tt::place_hits_kernel<TT_TILE_ROWS><<<pgrid, tt::kPlaceThreads, 0, stream>>>(
+          t->ctl, t->hit_list, p.tile_slot, tile_first, first_tile, t->task_id, d_rows, d_ids);
+    }
     TT_CUDA(cudaGetLastError());
     st->launches = 3;
   }
@@ -790,6 +810,71 @@ int32_t tt_sweep_device(tt_table* t, int32_t mode, int32_t flags, int64_t today_
   DeviceGuard g(t->device);
   return sweep_run(t, mode, flags, today_local_ticks, run_at_utc_ticks, first_row, d_rows, (uint4*)d_ids, cap, h_stats,
                    stream ? (cudaStream_t)stream : t->stream);
+}
+
+int32_t tt_sweep_push(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_ticks, int64_t run_at_utc_ticks,
+                      uint32_t* d_rows, void* d_ids, int64_t cap, const tt_push_target* target, tt_sweep_stats* h_stats,
+                      void* stream) {
+  if (!t || !h_stats || !target) return fail(TT_ERR_ARG, "null argument");
+  if (!target->off16 || !target->tile_count || !target->count) return fail(TT_ERR_ARG, "push target has a null buffer");
+  if ((uintptr_t)target->off16 % 16 != 0) return fail(TT_ERR_ARG, "push target off16 must be 16-byte aligned");
+  if (d_ids && !d_rows) return fail(TT_ERR_ARG, "d_ids without d_rows");
+  std::lock_guard<std::mutex> lk(t->mu);
+  DeviceGuard g(t->device);
+  tt::PushTarget push;
+  push.off16 = static_cast<uint16_t*>(target->off16);
+  push.tile_count = static_cast<uint32_t*>(target->tile_count);
+  push.count = static_cast<unsigned long long*>(target->count);
+  return sweep_run(t, mode, flags, today_local_ticks, run_at_utc_ticks, 0, d_rows, (uint4*)d_ids, cap, h_stats,
+                   stream ? (cudaStream_t)stream : t->stream, &push);
+}
+
+// ---- peer-mapped buffers (CUDA IPC) ----------------------------------------------------------
+
+int32_t tt_peer_alloc(int32_t device, uint64_t bytes, void** d_ptr, tt_peer_handle* handle) {
+  if (!d_ptr || !handle || bytes == 0) return fail(TT_ERR_ARG, "bad argument");
+  static_assert(sizeof(cudaIpcMemHandle_t) <= sizeof(tt_peer_handle), "handle too small");
+  *d_ptr = nullptr;
+  DeviceGuard g(device);
+  void* p = nullptr;
+  TT_CUDA(cudaMalloc(&p, bytes));
+  cudaError_t e = cudaMemset(p, 0, bytes);
+  cudaIpcMemHandle_t h;
+  if (e == cudaSuccess) e = cudaIpcGetMemHandle(&h, p);
+  if (e != cudaSuccess) {
+    cudaFree(p);
+    TT_CUDA(e);
+  }
+  memset(handle, 0, sizeof *handle);
+  memcpy(handle->bytes, &h, sizeof h);
+  *d_ptr = p;
+  return TT_OK;
+}
+
+int32_t tt_peer_open(int32_t device, const tt_peer_handle* handle, void** d_ptr) {
+  if (!d_ptr || !handle) return fail(TT_ERR_ARG, "bad argument");
+  *d_ptr = nullptr;
+  DeviceGuard g(device);
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle->bytes, sizeof h);
+  void* p = nullptr;
+  TT_CUDA(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+  *d_ptr = p;
+  return TT_OK;
+}
+
+int32_t tt_peer_close(int32_t device, void* d_ptr) {
+  if (!d_ptr) return TT_OK;
+  DeviceGuard g(device);
+  TT_CUDA(cudaIpcCloseMemHandle(d_ptr));
+  return TT_OK;
+}
+
+int32_t tt_peer_free(int32_t device, void* d_ptr) {
+  if (!d_ptr) return TT_OK;
+  DeviceGuard g(device);
+  TT_CUDA(cudaFree(d_ptr));
+  return TT_OK;
 }
 
 int32_t tt_mark_overdue(tt_table* t, int32_t mode, const uint8_t* ids16, int64_t n, int64_t* n_marked,

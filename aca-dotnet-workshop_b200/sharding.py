@@ -45,11 +45,12 @@ class HitExchange:
     (rank dst's offset is 0 when dst == 0), so the sweep can write them in place.
     """
 
-    def __init__(self, plan, cap_per_rank, device, with_ids=False, dst=0, group=None):
+    def __init__(self, plan, cap_per_rank, device, with_ids=False, dst=0, group=None, root_slots=True):
         self.plan, self.cap, self.dst, self.group, self.with_ids = plan, cap_per_rank, dst, group, with_ids
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
-        n = cap_per_rank * (self.world if self.rank == dst else 1)
+        # root_slots=False: only this shard's own output buffers (the fused exchange has its own receive buffer)
+        n = cap_per_rank * (self.world if self.rank == dst and root_slots else 1)
         self.rows_all = torch.empty(n, dtype=torch.int32, device=device)
         self.ids_all = torch.empty((n, 16), dtype=torch.uint8, device=device) if with_ids else None
         self._mine = torch.zeros(1, dtype=torch.int64, device=device)
@@ -252,6 +253,116 @@ class HitExchange:
             glob[off:off + c] += shard_rows(self.plan.n_total, self.world, r)[0]
             off += c
         return glob
+
+
+def push_slot_layout(n_tiles, cap):
+    """Byte layout of one shard's slot in the root's receive buffer for the fused exchange:
+    [hit count, u64, in its own 256 B][per-tile counts, u32 x n_tiles][in-tile offsets, u16 x cap],
+    every part 256-byte aligned.  -> (off_tile_count, off_off16, slot_bytes)."""
+    up = lambda x: (x + 255) // 256 * 256
+    o_cnt = 256
+    o_off = o_cnt + up(4 * n_tiles)
+    return o_cnt, o_off, o_off + up(2 * cap)
+
+
+class _DeviceSpan:
+    """Raw device memory as a __cuda_array_interface__ object, so torch can view it without copying."""
+
+    def __init__(self, ptr, n, typestr):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": typestr, "data": (ptr, False), "version": 3}
+
+
+class PushExchange:
+    """The exchange fused into the sweep (TaskTable.sweep_push, include/tasktable.h tt_sweep_push).
+
+    The root shard owns one receive buffer with a slot per shard (push_slot_layout); every other
+    process maps it with CUDA IPC.  A shard's sweep stores the compact form of its hit list
+    straight into its slot — over NVLink when the slot is on another GPU — from the same kernel
+    that puts its hits in row order and gathers their TaskIds, so the transfer hides behind that
+    kernel's HBM gathers and no collective moves data.  `fence()` (a one-word all-reduce, stream
+    ordered after the sweep) is the only cross-process step: when it returns on the root, every
+    slot is complete.  Collective constructor: every rank must create it."""
+
+    def __init__(self, plan, cap_per_rank, device_index, dst=0, group=None, tile_rows=8192):
+        from . import tasktable as tt
+
+        self._tt, self.plan, self.dst, self.group, self.device_index = tt, plan, dst, group, device_index
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.cap = (cap_per_rank + 7) // 8 * 8
+        rows_max = max(shard_rows(plan.n_total, self.world, r)[1] - shard_rows(plan.n_total, self.world, r)[0]
+                       for r in range(self.world))
+        self.n_tiles = max(1, -(-rows_max // tile_rows))
+        self.o_cnt, self.o_off, self.slot_bytes = push_slot_layout(self.n_tiles, self.cap)
+        self.owner = self.rank == dst
+        self.base = 0
+        payload = [None]
+        if self.owner:
+            try:
+                self.base, payload[0] = tt.peer_alloc(device_index, self.world * self.slot_bytes)
+            except tt.TaskTableError as e:  # the other ranks are waiting in the broadcast: tell them
+                payload[0] = str(e)
+        if self.world > 1:
+            dist.broadcast_object_list(payload, src=dst, group=group)
+        if not isinstance(payload[0], bytes):
+            raise RuntimeError(f"root could not allocate the receive buffer: {payload[0]}")
+        if not self.owner:
+            self.base = tt.peer_open(device_index, payload[0])
+        self.slot = self.base + self.rank * self.slot_bytes
+        self._flag = torch.zeros(1, dtype=torch.int32, device=torch.device("cuda", device_index))
+        self._scratch = None
+
+    def sweep(self, table, mode, flags, d_rows, d_ids, stream=None, **kw):
+        """This shard's cron tick; its compact hit list lands in the root's slot.  -> SweepStats."""
+        st, _ = table.sweep_push(mode, flags, d_rows, d_ids, self.cap, self.slot + self.o_off, self.slot + self.o_cnt,
+                                 self.slot, stream=stream, **kw)
+        return st
+
+    def fence(self):
+        """Stream-ordered after the sweep on every rank; afterwards the root may read all slots."""
+        if self.world > 1:
+            dist.all_reduce(self._flag, group=self.group)
+
+    # ---- root side -------------------------------------------------------------------------------
+    def _view(self, r, off, n, typestr, dtype):
+        assert self.owner
+        return torch.as_tensor(_DeviceSpan(self.base + r * self.slot_bytes + off, n, typestr),
+                               device=torch.device("cuda", self.device_index)).view(dtype)
+
+    def counts(self):
+        """root: hits stored by each shard (python list; reads the device)."""
+        return [int(self._view(r, 0, 1, "<i8", torch.int64).item()) for r in range(self.world)]
+
+    def shard_rows_local(self, r, count, stream=None):
+        """root: shard r's hit rows (shard-local, ascending) rebuilt from its slot."""
+        dev = torch.device("cuda", self.device_index)
+        if self._scratch is None:
+            self._scratch = torch.empty(self.n_tiles + self.n_tiles // 1024 + 8, dtype=torch.int32, device=dev)
+        out = torch.empty(max(count, 1), dtype=torch.int32, device=dev)
+        slot = self.base + r * self.slot_bytes
+        self._tt.expand_hits(self.device_index, slot + self.o_cnt, self.n_tiles, slot + self.o_off,
+                             self._scratch.data_ptr(), out.data_ptr(), stream)
+        torch.cuda.synchronize(dev)
+        return out[:count]
+
+    def global_rows(self, stream=None):
+        """root: all shards' hits as ascending global row numbers (int64)."""
+        parts = []
+        for r, c in enumerate(self.counts()):
+            local = self.shard_rows_local(r, c, stream)
+            parts.append((local.to(torch.int64) & 0xFFFFFFFF) + shard_rows(self.plan.n_total, self.world, r)[0])
+        return torch.cat(parts)
+
+    def close(self):
+        if not self.base:
+            return
+        if self.world > 1:
+            dist.barrier(group=self.group)  # nobody may still be storing into the buffer
+        if self.owner:
+            self._tt.peer_free(self.device_index, self.base)
+        else:
+            self._tt.peer_close(self.device_index, self.base)
+        self.base = 0
 
 
 def exchange_hits(local_rows, count, plan, ids=None, dst=0, group=None):

@@ -47,6 +47,7 @@ EXPORTS = [
     "tt_sweep_device", "tt_get_device_view", "tt_sweep_static", "tt_get_by_creators", "tt_last_op_stats",
     "tt_get_by_id", "tt_insert_task", "tt_update_task", "tt_mark_completed", "tt_delete_task", "tt_live_count",
     "tt_save_snapshot", "tt_load_snapshot", "tt_pack_hits", "tt_expand_hits",
+    "tt_sweep_push", "tt_peer_alloc", "tt_peer_open", "tt_peer_close", "tt_peer_free",
 ]
 
 
@@ -140,6 +141,15 @@ class DeviceView(C.Structure):
     ]
 
 
+class PushTarget(C.Structure):
+    """tt_push_target: where tt_sweep_push stores the compact hit list (device addresses)."""
+    _fields_ = [("off16", C.c_void_p), ("tile_count", C.c_void_p), ("count", C.c_void_p)]
+
+
+class PeerHandle(C.Structure):
+    _fields_ = [("bytes", C.c_uint8 * 64)]
+
+
 def lib_path():
     return os.path.join(HERE, "libtasktable.so")
 
@@ -194,6 +204,11 @@ def lib():
     L.tt_sweep_device.argtypes = [vp, i32, i32, i64, i64, i64, vp, vp, i64, P(SweepStats), vp]
     L.tt_get_device_view.argtypes = [vp, P(DeviceView)]
     L.tt_sweep_static.argtypes = [P(DeviceView), i32, i32, i64, i64, vp, vp, i64, P(SweepStats), vp]
+    L.tt_sweep_push.argtypes = [vp, i32, i32, i64, i64, vp, vp, i64, P(PushTarget), P(SweepStats), vp]
+    L.tt_peer_alloc.argtypes = [i32, u64, P(vp), P(PeerHandle)]
+    L.tt_peer_open.argtypes = [i32, P(PeerHandle), P(vp)]
+    L.tt_peer_close.argtypes = [i32, vp]
+    L.tt_peer_free.argtypes = [i32, vp]
     for name in EXPORTS:
         if name != "tt_last_error":
             getattr(L, name).restype = i32
@@ -255,6 +270,30 @@ class Result:
             self.free()
         except Exception:
             pass
+
+
+def peer_alloc(device, nbytes):
+    """-> (device address, 64-byte handle) of zeroed device memory other processes can map."""
+    p, h = C.c_void_p(0), PeerHandle()
+    _check(lib().tt_peer_alloc(device, nbytes, C.byref(p), C.byref(h)))
+    return p.value, bytes(h.bytes)
+
+
+def peer_open(device, handle_bytes):
+    """Maps memory another process allocated with peer_alloc; -> device address valid on `device`."""
+    h = PeerHandle()
+    C.memmove(h.bytes, handle_bytes, 64)
+    p = C.c_void_p(0)
+    _check(lib().tt_peer_open(device, C.byref(h), C.byref(p)))
+    return p.value
+
+
+def peer_close(device, ptr):
+    _check(lib().tt_peer_close(device, ptr))
+
+
+def peer_free(device, ptr):
+    _check(lib().tt_peer_free(device, ptr))
 
 
 def expand_hits(device, d_tile_count, n_tiles, d_off16, d_scratch, d_rows_out, stream=None):
@@ -391,6 +430,18 @@ class TaskTable:
         st = SweepStats()
         rc = lib().tt_sweep_device(self._h, mode, flags, today, run_at, first_row, d_rows, d_ids, cap, C.byref(st),
                                    stream)
+        _check(rc, allow=(TT_ERR_CAPACITY,) if allow_capacity else ())
+        return st, rc
+
+    def sweep_push(self, mode, flags, d_rows, d_ids, cap, off16, tile_count, count, today=DEFAULT_TODAY,
+                   run_at=DEFAULT_RUN_AT, stream=None, allow_capacity=False):
+        """tt_sweep_push: sweep_device whose placement kernel also stores the compact hit list
+        (off16 / tile_count / count: device addresses, possibly peer-mapped memory of the root GPU).
+        d_rows / d_ids may be None."""
+        target = PushTarget(off16, tile_count, count)
+        st = SweepStats()
+        rc = lib().tt_sweep_push(self._h, mode, flags, today, run_at, d_rows, d_ids, cap, C.byref(target), C.byref(st),
+                                 stream)
         _check(rc, allow=(TT_ERR_CAPACITY,) if allow_capacity else ())
         return st, rc
 

@@ -38,9 +38,11 @@ def parse():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--rows", type=int, default=1_000_000_000, help="rows per GPU (weak) or in total (strong)")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
-    ap.add_argument("--exchange", default="compact", choices=["compact", "rows", "ids", "none"],
-                    help="what the shards send to rank 0 after the sweep (N > 1): compact = the hit rows as 2-byte "
-                         "in-tile offsets + per-tile counts, rows = u32 row numbers, ids = rows + 16-byte TaskIds")
+    ap.add_argument("--exchange", default="push", choices=["push", "compact", "rows", "ids", "none"],
+                    help="how the shards' hit lists reach rank 0 (N > 1): push = the sweep's placement kernel stores "
+                         "the compact form (2-byte in-tile offsets + per-tile counts) straight into rank 0's buffer "
+                         "over NVLink (tt_sweep_push); compact / rows / ids = NCCL send/recv after the sweep of the "
+                         "compact form, the u32 row numbers, or rows + 16-byte TaskIds")
     ap.add_argument("--exchange-mode", default="fixed", choices=["exact", "fixed"],
                     help="exact: count all-gather, then count-sized send/recv; fixed: one grouped send/recv of "
                          "capacity-sized buffers into fixed slots on rank 0")
@@ -206,13 +208,27 @@ def run_b200(args):
     nbytes = (n_rows + 7) // 8
     pristine = torch.empty(nbytes, dtype=torch.uint8, device=dev)
     tt._check(tt.lib().tt_snapshot_flags(table._h, None, pristine.data_ptr()))
-    cap = int(n_rows * 0.032) + 65536
+    cap = (int(n_rows * 0.032) + 65536 + 7) // 8 * 8
     with_ids = args.exchange == "ids"
+    exchange = args.exchange if world > 1 else "none"
+    pex = None
+    if exchange == "push":
+        # every rank takes the same decision: the fused exchange needs the root's buffer mapped everywhere
+        try:
+            pex = pkg.PushExchange(plan, cap, local)
+            ok = 1
+        except Exception as e:  # noqa: BLE001 - e.g. CUDA IPC not permitted in this container
+            print(f"[rank {rank}] fused exchange unavailable ({e}); using the NCCL compact exchange", file=sys.stderr)
+            ok = 0
+        agree = torch.tensor([ok], dtype=torch.int32, device=dev)
+        dist.all_reduce(agree, op=dist.ReduceOp.MIN)
+        if int(agree.item()) == 0:
+            pex, exchange = None, "compact"
     # the exchange owns the output buffers: on rank 0 the local hits land at offset 0 in place
-    ex = pkg.HitExchange(plan, cap, dev, with_ids=True)
+    ex = pkg.HitExchange(plan, cap, dev, with_ids=True, root_slots=(exchange != "push"))
     d_rows, d_ids = ex.rows_all, ex.ids_all
     ex.with_ids = with_ids
-    if args.exchange == "compact":
+    if exchange == "compact":
         ex.enable_compact()
     stream = torch.cuda.Stream(device=dev)  # non-default: its handle is what the C ABI launches on
     torch.cuda.set_stream(stream)
@@ -221,14 +237,19 @@ def run_b200(args):
         tt._check(tt.lib().tt_restore_flags(table._h, None, pristine.data_ptr()))
 
     def step():
+        if exchange == "push":
+            st = pex.sweep(table, tt.MODE_STORE, tt.SWEEP_MARK, d_rows.data_ptr(), d_ids.data_ptr(),
+                           stream=stream.cuda_stream)
+            pex.fence()
+            return st, None
         st, _ = table.sweep_device(tt.MODE_STORE, tt.SWEEP_MARK, d_rows.data_ptr(), d_ids.data_ptr(), cap,
                                    stream=stream.cuda_stream)
         out = None
-        if world > 1 and args.exchange == "compact":
+        if world > 1 and exchange == "compact":
             table.pack_hits(d_rows.data_ptr(), st.n_stored, ex.off16_all.data_ptr(), ex.tile_counts_all.data_ptr(),
                             stream=stream.cuda_stream)
             out = ex.run_fixed_compact(st.n_stored)
-        elif world > 1 and args.exchange != "none":
+        elif world > 1 and exchange != "none":
             out = ex.run_fixed(st.n_stored) if args.exchange_mode == "fixed" else ex.run(st.n_stored)
         return st, out
 
@@ -240,7 +261,7 @@ def run_b200(args):
     seen = 0
     for w in range(args.warmup):
         reset()
-        if w == args.warmup - 1 and world > 1:
+        if w == args.warmup - 1 and world > 1 and exchange != "push":
             ex.tune_send_cap(seen)  # the fixed exchange message: 1.1 x the largest count seen in warm-up
         st_w, _ = step()
         seen = max(seen, st_w.n_stored)
@@ -258,7 +279,7 @@ def run_b200(args):
             sweep_ms.append(st.sweep_ms)
             gather_ms.append(st.gather_ms)
             hits = st.n_listed
-            launches += st.launches + (1 if world > 1 and args.exchange == "compact" else 0)
+            launches += st.launches + (1 if exchange == "compact" else 0)
         barrier()
     step_ms = [a.elapsed_time(b) for a, b in ev]
     total_ms = torch.tensor([sum(step_ms)], dtype=torch.float64, device=dev)
@@ -334,7 +355,7 @@ def run_b200(args):
                             "config-5 mix: 5% due yesterday, 1% adversarial inexact, 50% completed",
                 "rows_per_gpu": n_rows, "n_total": n_total, "hits_per_step": int(hits_all.item()),
                 "sharding": "TaskId range" if world > 1 else "single shard",
-                "exchange": (args.exchange if world > 1 else "none"),
+                "exchange": exchange,
                 "l2": f"inputs {n_rows * BYTES_PER_TASK / 1e6:.0f} MB per step vs 126 MB L2; overdue plane rewritten between steps",
                 "reset": "overdue plane restored between steps outside the timed region (per-step CUDA events summed)",
             },
@@ -349,7 +370,11 @@ def run_b200(args):
                                            "frac": (place_gbs / peak) if place_gbs else None,
                                            "note": "random 16 B TaskId gathers cost 64 B of DRAM each"}},
             "gpu_launches": launches,
-            "exchange": {"what": (args.exchange if world > 1 else "none"), "transport": ex.transport if world > 1 else None, "mode": args.exchange_mode if world > 1 else None,
+            "exchange": {"what": exchange,
+                         "transport": (None if world == 1 else "stores from the placement kernel into rank 0's HBM over "
+                                       "NVLink (CUDA IPC mapping) + one-word all-reduce" if exchange == "push"
+                                       else ex.transport),
+                         "mode": args.exchange_mode if world > 1 and exchange != "push" else None,
                          "ms": med([a - b for a, b in zip(step_ms, kernel_ms)]),
                          "note": "per-step time outside the three sweep kernels on rank 0: launch/sync overhead, "
                                  "count all-gather and the hit id gather (N > 1)"},
@@ -361,6 +386,8 @@ def run_b200(args):
             base = cpu_reference_run(args.cpu_sample_rows, 3, 1)
             line["cpu_baseline"] = {k: base[k] for k in ("value", "unit", "cores", "kind", "sample", "parallel_soa")}
         print(json.dumps(line))
+    if pex:
+        pex.close()
     table.close()
     if world > 1:
         dist.barrier()

@@ -249,6 +249,39 @@ int32_t tt_pack_hits(tt_table* t, const uint32_t* d_rows, int64_t n, uint16_t* d
 int32_t tt_expand_hits(int32_t device, const uint32_t* d_tile_count, int64_t n_tiles, const uint16_t* d_off16,
                        uint32_t* d_scratch, uint32_t* d_rows_out, void* stream);
 
+/* ---- the sweep fused with the cross-shard exchange -----------------------------
+ * tt_sweep_push is tt_sweep_device over the whole table whose last kernel, while it puts the hits
+ * in row order and gathers their TaskIds, also stores the COMPACT form of the result (the layout of
+ * tt_pack_hits: off16[i] for the n_stored hits, one count per 8192-row tile, and the hit count)
+ * into `target`.  The target buffers may belong to another GPU: the root shard allocates them with
+ * tt_peer_alloc, every other process maps them with tt_peer_open (CUDA IPC; stores travel over
+ * NVLink) and passes the mapped addresses of ITS slot.  The exchange then needs no pass of its own
+ * and no collective: once every shard's call has returned and the processes have met at a barrier,
+ * the root reads all slots (tt_expand_hits rebuilds row numbers).  d_rows / d_ids (this shard's own
+ * copy of the result) may both be NULL.  Replaces, for one box, the JSON hop of the hit list between
+ * the reference's processes (Svc/Controllers/ScheduledTasksManagerController.cs:28,44).
+ * target->off16 must be 16-byte aligned and hold `cap` entries. */
+typedef struct tt_push_target {
+  void* off16;      /* uint16[cap]                          */
+  void* tile_count; /* uint32[n_padded / 8192]               */
+  void* count;      /* uint64[1]: hits stored (= n_stored)   */
+} tt_push_target;
+int32_t tt_sweep_push(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_ticks, int64_t run_at_utc_ticks,
+                      uint32_t* d_rows, void* d_ids, int64_t cap, const tt_push_target* target,
+                      tt_sweep_stats* h_stats, void* stream);
+
+/* Device memory that other processes on the box can map.  tt_peer_alloc: cudaMalloc (zeroed) on
+ * `device` + an exportable handle (64 opaque bytes, send them to the other processes any way you
+ * like); tt_peer_open: maps it for kernels running on `device` of the calling process (peer access
+ * is enabled as needed); close what you opened, free what you allocated.  No reference counterpart. */
+typedef struct tt_peer_handle {
+  uint8_t bytes[64];
+} tt_peer_handle;
+int32_t tt_peer_alloc(int32_t device, uint64_t bytes, void** d_ptr, tt_peer_handle* handle);
+int32_t tt_peer_open(int32_t device, const tt_peer_handle* handle, void** d_ptr);
+int32_t tt_peer_close(int32_t device, void* d_ptr);
+int32_t tt_peer_free(int32_t device, void* d_ptr);
+
 /* ---- snapshot ---------------------------------------------------------------------------------
  * Saves / restores the whole table (all columns, flags, creator dictionary, tombstones) as one
  * file in the device layout — the counterpart of the reference keeping its tasks in a state store

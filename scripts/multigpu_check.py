@@ -64,6 +64,30 @@ def main():
         ok2 = cdev.tolist() == counts and bool((g2 == glob).all())
         print("compact exchange", "agrees" if ok2 else "DIFFERS")
         assert ok2
+    # the fused exchange: a fresh copy of the shard, swept by tt_sweep_push straight into rank 0's buffer
+    table_p = pkg.TaskTable(local).generate(cfg, plan.first_row, plan.n_rows)
+    pex = pkg.PushExchange(plan, cap, local)
+    p_rows = torch.empty(pex.cap, dtype=torch.int32, device=dev)
+    p_ids = torch.empty((pex.cap, 16), dtype=torch.uint8, device=dev)
+    for tick in range(2):  # the second tick finds nothing: the slots must be overwritten, not appended to
+        stp = pex.sweep(table_p, tt.MODE_STORE, tt.SWEEP_MARK, p_rows.data_ptr(), p_ids.data_ptr(), stream=stream.cuda_stream)
+        pex.fence()
+        torch.cuda.synchronize()
+        ok3 = True
+        if tick == 0:
+            ok3 = (stp.n_stored == st.n_stored and bool((p_rows[: stp.n_stored] == d_rows[: st.n_stored]).all())
+                   and bool((p_ids[: stp.n_stored] == d_ids[: st.n_stored]).all()))
+            if rank == 0:
+                ok3 = ok3 and pex.counts() == counts and bool((pex.global_rows(stream.cuda_stream) == glob).all())
+        else:
+            ok3 = stp.n_listed == 0 and (rank != 0 or pex.counts() == [0] * world)
+        if rank == 0:
+            print("fused push exchange tick", tick, "agrees" if ok3 else "DIFFERS")
+        assert ok3
+        dist.barrier()
+    assert table_p.count_flags() == table.count_flags()
+    pex.close()
+    table_p.close()
     ok = True
     if rank == 0:
         from oracle import oracle as orc

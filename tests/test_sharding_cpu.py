@@ -117,3 +117,12 @@ def test_exchange_over_gloo_matches_global_oracle(oracle, world, with_ids):
     if with_ids:
         ids_all, _, _ = whole.export()
         assert (gids == ids_all[want]).all()
+
+
+def test_push_slot_layout_is_aligned_and_disjoint():
+    """the slot a shard pushes into: count, per-tile counts and 2-byte offsets never overlap and the
+    offsets start 16-byte aligned (tt_sweep_push stores them as 16-byte vectors)"""
+    for n_tiles, cap in ((1, 8), (37, 40_000), (122_071, 32_065_536)):
+        o_cnt, o_off, total = pkg.push_slot_layout(n_tiles, cap)
+        assert o_cnt >= 8 and o_off >= o_cnt + 4 * n_tiles and total >= o_off + 2 * cap
+        assert o_cnt % 256 == 0 and o_off % 256 == 0 and total % 256 == 0
