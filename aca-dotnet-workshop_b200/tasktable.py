@@ -76,7 +76,7 @@ class SynthCfg(C.Structure):
         ("ppm_created_dup", C.c_uint32),
         ("ppm_timed_due", C.c_uint32),
         ("n_creators", C.c_uint32),
-        ("reserved", C.c_uint32),
+        ("n_names", C.c_uint32),
     ]
 
 

@@ -12,6 +12,9 @@
  *                   (Ui/Pages/Tasks/Create.cshtml:22) or a queue message with a time of
  *                   day (Svc/Controllers/ExternalTasksProcessorController.cs:29-33)
  *   TaskCreatedBy   an e-mail-like string          (Api/Services/FakeTasksManager.cs:18)
+ *   TaskName        "Task number: {i}"             (Api/Services/FakeTasksManager.cs:16); one name
+ *                   in eight carries characters JSON has to escape
+ *   TaskAssignedTo  "assignee{rnd.Next(50)}@mail.com" (Api/Services/FakeTasksManager.cs:21)
  *
  * DateTime values use .NET's internal 64-bit "dateData": ticks (100 ns since
  * 0001-01-01T00:00:00) in the low 62 bits, DateTimeKind in the top 2 bits.
@@ -48,7 +51,7 @@ typedef struct tt_synth_cfg {
   uint32_t ppm_created_dup;    /* TaskCreatedOn copied from the previous row (sort ties)    */
   uint32_t ppm_timed_due;      /* among other rows: due date carries a time of day, Kind Utc */
   uint32_t n_creators;         /* distinct TaskCreatedBy values                             */
-  uint32_t reserved;
+  uint32_t n_names;            /* distinct TaskName values (0 = 1 000 000); row r has name r % n_names */
 } tt_synth_cfg;
 
 typedef struct tt_synth_row {
@@ -72,7 +75,7 @@ TT_HD tt_synth_cfg tt_synth_default(uint64_t seed, uint64_t n_total) {
   c.ppm_created_dup = 1000;
   c.ppm_timed_due = 100000;
   c.n_creators = 1000000;
-  c.reserved = 0;
+  c.n_names = 0;
   return c;
 }
 
@@ -174,6 +177,57 @@ TT_HD int tt_synth_creator(uint32_t k, char* out) {
   out[p++] = (char)('0' + v % 10);
   const char* tail = ".example";
   for (int i = 0; i < 8; ++i) out[p++] = tail[i];
+  return p;
+}
+
+/* TaskName / TaskAssignedTo of a row, as indices into two small dictionaries (the strings never
+ * reach the sweep or the filter; they only matter when a result is written out as JSON). */
+#define TT_SYNTH_ASSIGNEES 50u
+TT_HD uint32_t tt_synth_n_names(const tt_synth_cfg* c) { return c->n_names ? c->n_names : 1000000u; }
+TT_HD uint32_t tt_synth_name_ref(const tt_synth_cfg* c, uint64_t row) { return (uint32_t)(row % tt_synth_n_names(c)); }
+TT_HD uint32_t tt_synth_assignee_ref(const tt_synth_cfg* c, uint64_t row) {
+  return tt_range(tt_draw(c->seed, row, 7), TT_SYNTH_ASSIGNEES);
+}
+
+TT_HD int tt_synth_put_uint(uint32_t v, char* out) {
+  char tmp[10];
+  int nd = 0, p = 0;
+  do { tmp[nd++] = (char)('0' + v % 10); v /= 10; } while (v);
+  while (nd) out[p++] = tmp[--nd];
+  return p;
+}
+
+/* Name k: "Task number: {k}"; when k % 8 == 5: `Task "{k}" <urgent> & caf\u00e9 \\ {k}` + TAB, i.e. a
+ * quote, HTML-sensitive characters, a two-byte UTF-8 character, a backslash and a control
+ * character.  Writes at most 64 bytes (UTF-8, no terminator); returns the length. */
+TT_HD int tt_synth_name(uint32_t k, char* out) {
+  int p = 0;
+  if (k % 8 != 5) {
+    const char* head = "Task number: ";
+    for (int i = 0; i < 13; ++i) out[p++] = head[i];
+    p += tt_synth_put_uint(k, out + p);
+    return p;
+  }
+  const char* a = "Task \"";
+  for (int i = 0; i < 6; ++i) out[p++] = a[i];
+  p += tt_synth_put_uint(k, out + p);
+  const char* b = "\" <urgent> & caf";
+  for (int i = 0; i < 16; ++i) out[p++] = b[i];
+  out[p++] = (char)0xC3; out[p++] = (char)0xA9; /* U+00E9 */
+  out[p++] = ' '; out[p++] = '\\'; out[p++] = ' ';
+  p += tt_synth_put_uint(k, out + p);
+  out[p++] = '\t';
+  return p;
+}
+
+/* Assignee k: "assignee{k}@mail.com".  At most 24 bytes; returns the length. */
+TT_HD int tt_synth_assignee(uint32_t k, char* out) {
+  int p = 0;
+  const char* a = "assignee";
+  for (int i = 0; i < 8; ++i) out[p++] = a[i];
+  p += tt_synth_put_uint(k, out + p);
+  const char* b = "@mail.com";
+  for (int i = 0; i < 9; ++i) out[p++] = b[i];
   return p;
 }
 
