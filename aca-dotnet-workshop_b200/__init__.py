@@ -16,6 +16,9 @@ from .tasktable import (  # noqa: F401
     DEFAULT_TODAY,
     DEFAULT_RUN_AT,
     DeviceView,
+    JSON_DOCUMENT,
+    JSON_RESPONSE,
+    JsonText,
     NotImplementedInReference,
     Result,
     SweepStats,

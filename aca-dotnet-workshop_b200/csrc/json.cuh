@@ -1,0 +1,479 @@
+// json.cuh — K6: a result list written as the JSON the reference's controllers return.
+//
+// The step right after the sweep / the creator filter: the reference's
+// OverdueTasksController.Get (Api/Controllers/OverdueTasksController.cs:22-26) and
+// TasksController.Get (Api/Controllers/TasksController.cs:21-25) return List<TaskModel>, which
+// ASP.NET Core serialises with System.Text.Json: camelCase property names in declaration order
+// (Api/Models/TaskModel.cs:5-12), no whitespace, Guid in "D" form, DateTime in ISO 8601 extended
+// form (sample: docs/aca/05-aca-dapr-pubsubapi/index.md:60-69).  Two encoders occur in the
+// reference:
+//   kJsonResponse  the MVC output formatter (JavaScriptEncoder.UnsafeRelaxedJsonEscaping)
+//   kJsonDocument  Dapr's SaveStateAsync / PublishEventAsync / InvokeMethodAsync bodies
+//                  (Api/Services/TasksStoreManager.cs:35,155; JavaScriptEncoder.Default)
+//
+// Strings are dictionary-encoded on the device, so escaping is done ONCE per dictionary entry
+// (esc_len / esc_write kernels, cached in the table) and the per-hit work is pure copying:
+// K6a json_len_kernel sizes every record (dictionary lengths + date lengths), a two-level scan
+// turns the sizes into byte offsets, and K6b json_emit_kernel lets each thread format one
+// record into shared memory (literals from constant memory, TaskId hex, pre-escaped strings as
+// 32-bit words, dates, booleans); the CTA then streams its contiguous piece of the text to HBM
+// with 16-byte stores.  All byte work, HBM-bound: ≈270 B written per hit, ≈7 scattered reads.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "sweep.cuh"
+
+namespace tt {
+
+constexpr int kJsonResponse = 0;
+constexpr int kJsonDocument = 1;
+
+// ---- escaping one Unicode scalar -----------------------------------------------------------
+// Returns how a scalar is written: 0 = as is, 1 = backslash + *short_ch, 2 = \uXXXX,
+// 3 = \uXXXX\uXXXX (surrogate pair).  System.Text.Json's published rules (assumptions of record in
+// DESIGN.md §8): both encoders escape controls, '"' and '\\' and every supplementary-plane
+// scalar; Default additionally escapes the HTML-sensitive ASCII characters and everything
+// outside Basic Latin; UnsafeRelaxed keeps BMP text except controls, separators (Zs other than
+// U+0020, Zl, Zp), private-use and non-characters.
+__device__ __forceinline__ int json_escape_kind(uint32_t cp, int flavor, uint8_t* short_ch) {
+  if (cp < 0x20) {
+    switch (cp) {
+      case 8: *short_ch = 'b'; return 1;
+      case 9: *short_ch = 't'; return 1;
+      case 10: *short_ch = 'n'; return 1;
+      case 12: *short_ch = 'f'; return 1;
+      case 13: *short_ch = 'r'; return 1;
+      default: return 2;
+    }
+  }
+  if (cp == '\\') { *short_ch = '\\'; return 1; }
+  if (cp == '"') {
+    if (flavor == kJsonResponse) { *short_ch = '"'; return 1; }
+    return 2;
+  }
+  if (cp < 0x7F) {
+    if (flavor == kJsonDocument && (cp == '&' || cp == '\'' || cp == '+' || cp == '<' || cp == '>' || cp == '`')) return 2;
+    return 0;
+  }
+  if (cp >= 0x10000) return 3;
+  if (flavor == kJsonDocument || cp <= 0x9F) return 2;
+  if (cp == 0xA0 || cp == 0x1680 || (cp >= 0x2000 && cp <= 0x200A) || cp == 0x2028 || cp == 0x2029 || cp == 0x202F ||
+      cp == 0x205F || cp == 0x3000)
+    return 2;
+  if ((cp >= 0xD800 && cp <= 0xF8FF) || (cp >= 0xFDD0 && cp <= 0xFDEF) || cp >= 0xFFFE) return 2;
+  return 0;
+}
+
+__device__ __forceinline__ uint8_t hex_upper(uint32_t x) { return (uint8_t)(x < 10 ? '0' + x : 'A' + x - 10); }
+__device__ __forceinline__ uint8_t hex_lower(uint32_t x) { return (uint8_t)(x < 10 ? '0' + x : 'a' + x - 10); }
+
+__device__ __forceinline__ void put_u4(uint8_t* o, uint32_t unit) {
+  o[0] = '\\';
+  o[1] = 'u';
+  o[2] = hex_upper((unit >> 12) & 15);
+  o[3] = hex_upper((unit >> 8) & 15);
+  o[4] = hex_upper((unit >> 4) & 15);
+  o[5] = hex_upper(unit & 15);
+}
+
+// Escapes s[0, len) (UTF-8).  WRITE = false only measures.  Returns the escaped length, or ~0u
+// if the bytes are not well-formed UTF-8 (a lead byte without its continuation bytes).
+template <bool WRITE>
+__device__ uint32_t json_escape(const uint8_t* s, uint32_t len, int flavor, uint8_t* out) {
+  uint32_t i = 0, o = 0;
+  while (i < len) {
+    const uint32_t c = s[i];
+    uint32_t cp = c, extra = 0;
+    if (c >= 0x80) {
+      if ((c >> 5) == 6) { cp = c & 0x1F; extra = 1; }
+      else if ((c >> 4) == 14) { cp = c & 0x0F; extra = 2; }
+      else if ((c >> 3) == 30) { cp = c & 0x07; extra = 3; }
+      else return ~0u;
+      if (i + extra >= len) return ~0u;
+      for (uint32_t j = 1; j <= extra; ++j) {
+        const uint32_t d = s[i + j];
+        if ((d >> 6) != 2) return ~0u;
+        cp = (cp << 6) | (d & 0x3F);
+      }
+    }
+    uint8_t sc = 0;
+    const int kind = json_escape_kind(cp, flavor, &sc);
+    if (kind == 0) {
+      if (WRITE)
+        for (uint32_t j = 0; j <= extra; ++j) out[o + j] = s[i + j];
+      o += extra + 1;
+    } else if (kind == 1) {
+      if (WRITE) { out[o] = '\\'; out[o + 1] = sc; }
+      o += 2;
+    } else if (kind == 2) {
+      if (WRITE) put_u4(out + o, cp);
+      o += 6;
+    } else {
+      if (WRITE) {
+        const uint32_t v = cp - 0x10000;
+        put_u4(out + o, 0xD800 + (v >> 10));
+        put_u4(out + o + 6, 0xDC00 + (v & 0x3FF));
+      }
+      o += 12;
+    }
+    i += extra + 1;
+  }
+  return o;
+}
+
+// One dictionary entry's escaped form: where it starts in the escaped pool (in 32-bit words, so
+// the emitter can read it with aligned word loads) and its length in bytes.
+struct EscEntry {
+  uint32_t word_off;
+  uint32_t len;
+};
+
+constexpr uint32_t kEscMaxLen = 1u << 20;  // longest escaped string the emitter accepts
+
+// Pass 1 over a dictionary: escaped length of every entry.  err[0] |= 1 on malformed UTF-8 or an
+// over-long entry, err[1] = one offending entry.
+__global__ void esc_len_kernel(const uint32_t* off, const uint8_t* pool, uint32_t n, int flavor, uint32_t* len_out,
+                               uint32_t* err) {
+  const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const uint32_t a = off[k], b = off[k + 1];
+  uint32_t l = json_escape<false>(pool + a, b - a, flavor, nullptr);
+  if (l == ~0u || l > kEscMaxLen) {
+    atomicOr(err, 1u);
+    err[1] = k;
+    l = 0;
+  }
+  len_out[k] = l;
+}
+
+// Pass 2 (after the scan of the word counts): writes the escaped bytes.
+__global__ void esc_write_kernel(const uint32_t* off, const uint8_t* pool, uint32_t n, int flavor,
+                                 const EscEntry* entry, uint32_t* esc_pool) {
+  const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const uint32_t a = off[k], b = off[k + 1];
+  uint8_t* dst = reinterpret_cast<uint8_t*>(esc_pool + entry[k].word_off);
+  const uint32_t l = entry[k].len;
+  if (l) json_escape<true>(pool + a, b - a, flavor, dst);
+  for (uint32_t j = l; j < ((l + 3) & ~3u); ++j) dst[j] = 0;  // padding of the last word
+}
+
+// ---- a small generic scan: u32 weights -> u64 exclusive offsets ------------------------------
+// Level 1: one CTA per 1024 elements writes their sum; level 2: ONE CTA walks the block sums
+// (n / 1024 of them) and leaves their exclusive scan in place + the grand total; the consumer
+// kernels redo the cheap in-block scan themselves.
+constexpr int kScanBlock = 1024;
+
+__device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t v, uint32_t* s_warp, uint32_t* total) {
+  const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+  uint32_t incl = v;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    uint32_t up = __shfl_up_sync(0xFFFFFFFFu, incl, d);
+    if (lane >= (uint32_t)d) incl += up;
+  }
+  if (lane == 31) s_warp[warp] = incl;
+  __syncthreads();
+  uint32_t base = 0, tot = 0;
+  const uint32_t nw = (blockDim.x + 31) >> 5;
+  for (uint32_t w = 0; w < nw; ++w) {
+    const uint32_t x = s_warp[w];
+    base += w < warp ? x : 0u;
+    tot += x;
+  }
+  __syncthreads();  // s_warp may be reused by the caller's next scan
+  if (total) *total = tot;
+  return base + incl - v;
+}
+
+// weights of a dictionary: words of each escaped entry
+__global__ void __launch_bounds__(kScanBlock) esc_block_sum_kernel(const uint32_t* len, uint32_t n, uint64_t* block_sum) {
+  __shared__ uint32_t s_warp[32];
+  const uint32_t k = blockIdx.x * kScanBlock + threadIdx.x;
+  const uint32_t w = k < n ? (len[k] + 3) >> 2 : 0u;
+  uint32_t tot;
+  block_exclusive_scan(w, s_warp, &tot);
+  if (threadIdx.x == 0) block_sum[blockIdx.x] = tot;
+}
+
+// in place: block_sum[b] <- sum of the blocks before b; block_sum[nb] <- total
+__global__ void __launch_bounds__(1024) scan_block_sums_kernel(uint64_t* block_sum, uint32_t nb) {
+  __shared__ uint64_t s_warp[32];
+  __shared__ uint64_t s_carry;
+  const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+  if (threadIdx.x == 0) s_carry = 0;
+  __syncthreads();
+  for (uint32_t b0 = 0; b0 < nb; b0 += 1024) {
+    const uint32_t b = b0 + threadIdx.x;
+    const uint64_t v = b < nb ? block_sum[b] : 0ull;
+    uint64_t incl = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      uint64_t up = __shfl_up_sync(0xFFFFFFFFu, incl, d);
+      if (lane >= (uint32_t)d) incl += up;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    uint64_t base = s_carry;
+    for (uint32_t w = 0; w < warp; ++w) base += s_warp[w];
+    if (b < nb) block_sum[b] = base + incl - v;
+    __syncthreads();
+    if (threadIdx.x == 1023) s_carry = base + incl;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) block_sum[nb] = s_carry;
+}
+
+__global__ void __launch_bounds__(kScanBlock) esc_entries_kernel(const uint32_t* len, uint32_t n, const uint64_t* block_base,
+                                                                 EscEntry* entry) {
+  __shared__ uint32_t s_warp[32];
+  const uint32_t k = blockIdx.x * kScanBlock + threadIdx.x;
+  const uint32_t l = k < n ? len[k] : 0u;
+  const uint32_t local = block_exclusive_scan((l + 3) >> 2, s_warp, nullptr);
+  if (k < n) {
+    EscEntry e;
+    e.word_off = (uint32_t)(block_base[blockIdx.x] + local);
+    e.len = l;
+    entry[k] = e;
+  }
+}
+
+// ---- the record ---------------------------------------------------------------------------
+// {"taskId":"<36>","taskName":"..","taskCreatedBy":"..","taskCreatedOn":"..","taskDueDate":"..",
+//  "taskAssignedTo":"..","isCompleted":false,"isOverDue":false}
+// preceded by '[' (first record) or ',' and, for the last record, followed by ']'.
+__constant__ char kJsonLit[] =
+    "{\"taskId\":\""            // 0, 11
+    "\",\"taskName\":\""        // 11, 14
+    "\",\"taskCreatedBy\":\""   // 25, 19
+    "\",\"taskCreatedOn\":\""   // 44, 19
+    "\",\"taskDueDate\":\""     // 63, 17
+    "\",\"taskAssignedTo\":\""  // 80, 20
+    "\",\"isCompleted\":"       // 100, 16
+    ",\"isOverDue\":"           // 116, 13
+    "true"                      // 129, 4
+    "false";                    // 133, 5
+constexpr uint32_t kJsonFixed = 1 + 11 + 36 + 14 + 19 + 19 + 17 + 20 + 16 + 13 + 1;  // lead + literals + id + '}'
+
+struct JsonParams {
+  const uint32_t* rows;      // the result's row numbers
+  const uint4* ids;          // the result's TaskIds (same order)
+  int64_t n;
+  const uint64_t* created_raw;
+  const uint64_t* due_raw;
+  const uint32_t* completed;
+  const uint32_t* overdue;
+  const uint32_t* ref[3];    // name, creator, assignee: row -> dictionary entry (null = empty strings)
+  uint32_t dict_n[3];        // entries in each dictionary (a ref beyond it writes an empty string)
+  const EscEntry* entry[3];
+  const uint32_t* esc_pool[3];
+  int32_t local_offset_min;  // UTC offset used to print Kind = Local values
+  uint64_t* block_base;      // [blocks + 1]
+  uint8_t* out;
+};
+
+__device__ __forceinline__ uint32_t datetime_len(uint64_t raw) {
+  const uint64_t ticks = raw & 0x3FFFFFFFFFFFFFFFull;
+  const uint32_t kind = (uint32_t)(raw >> 62);
+  uint32_t frac = (uint32_t)(ticks % 10000000ull);
+  uint32_t l = 19;
+  if (frac) {
+    l += 8;
+    while (frac % 10 == 0) { frac /= 10; --l; }
+  }
+  return l + (kind == 1 ? 1u : kind >= 2 ? 6u : 0u);
+}
+
+__device__ __forceinline__ void put2(uint8_t* o, uint32_t v) {
+  o[0] = (uint8_t)('0' + v / 10);
+  o[1] = (uint8_t)('0' + v % 10);
+}
+
+// "yyyy-MM-ddTHH:mm:ss[.fffffff][Z|+hh:mm]" (System.Text.Json's DateTime writer); returns the length
+__device__ uint32_t datetime_write(uint64_t raw, int32_t local_offset_min, uint8_t* o) {
+  const uint64_t ticks = raw & 0x3FFFFFFFFFFFFFFFull;
+  const uint32_t kind = (uint32_t)(raw >> 62);
+  const uint64_t days = ticks / 864000000000ull;
+  const uint64_t tod = ticks % 864000000000ull;
+  // civil date from days since 0001-01-01 (proleptic Gregorian, era arithmetic)
+  const uint32_t z = (uint32_t)days + 306;  // days since 0000-03-01
+  const uint32_t era = z / 146097;
+  const uint32_t doe = z - era * 146097;
+  const uint32_t yoe = (doe - doe / 1460 + doe / 36524 - doe / 146096) / 365;
+  uint32_t y = yoe + era * 400;
+  const uint32_t doy = doe - (365 * yoe + yoe / 4 - yoe / 100);
+  const uint32_t mp = (5 * doy + 2) / 153;
+  const uint32_t d = doy - (153 * mp + 2) / 5 + 1;
+  const uint32_t m = mp < 10 ? mp + 3 : mp - 9;
+  if (m <= 2) y += 1;
+  const uint32_t secs = (uint32_t)(tod / 10000000ull);
+  uint32_t frac = (uint32_t)(tod % 10000000ull);
+  put2(o, y / 100);
+  put2(o + 2, y % 100);
+  o[4] = '-';
+  put2(o + 5, m);
+  o[7] = '-';
+  put2(o + 8, d);
+  o[10] = 'T';
+  put2(o + 11, secs / 3600);
+  o[13] = ':';
+  put2(o + 14, secs / 60 % 60);
+  o[16] = ':';
+  put2(o + 17, secs % 60);
+  uint32_t p = 19;
+  if (frac) {
+    uint32_t digits = 7;
+    while (frac % 10 == 0) { frac /= 10; --digits; }
+    o[p] = '.';
+    for (uint32_t j = digits; j > 0; --j) { o[p + j] = (uint8_t)('0' + frac % 10); frac /= 10; }
+    p += 1 + digits;
+  }
+  if (kind == 1) {
+    o[p++] = 'Z';
+  } else if (kind >= 2) {
+    int32_t off = local_offset_min;
+    o[p++] = off < 0 ? '-' : '+';
+    if (off < 0) off = -off;
+    put2(o + p, (uint32_t)off / 60);
+    o[p + 2] = ':';
+    put2(o + p + 3, (uint32_t)off % 60);
+    p += 5;
+  }
+  return p;
+}
+
+constexpr int kJsonThreads = 128;            // records per CTA
+constexpr int kJsonStageBytes = 56 * 1024;   // shared-memory staging per CTA (4 CTAs per SM)
+
+struct JsonRecord {
+  uint32_t row;
+  uint64_t created, due;
+  EscEntry s[3];
+  bool completed, overdue, live;
+};
+
+__device__ __forceinline__ JsonRecord json_load(const JsonParams& p, int64_t i) {
+  JsonRecord r;
+  r.live = i < p.n;
+  r.row = 0;
+  r.created = r.due = 0;
+  r.completed = r.overdue = false;
+#pragma unroll
+  for (int c = 0; c < 3; ++c) r.s[c].word_off = r.s[c].len = 0;
+  if (!r.live) return r;
+  r.row = p.rows[i];
+  r.created = ld_gather_u64(p.created_raw + r.row);
+  r.due = ld_gather_u64(p.due_raw + r.row);
+  r.completed = (p.completed[r.row >> 5] >> (r.row & 31)) & 1u;
+  r.overdue = (p.overdue[r.row >> 5] >> (r.row & 31)) & 1u;
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    if (p.ref[c]) {
+      const uint32_t k = p.ref[c][r.row];
+      if (k < p.dict_n[c]) r.s[c] = p.entry[c][k];
+    }
+  }
+  return r;
+}
+
+__device__ __forceinline__ uint32_t json_record_len(const JsonParams& p, const JsonRecord& r, int64_t i) {
+  if (!r.live) return 0;
+  return kJsonFixed + r.s[0].len + r.s[1].len + r.s[2].len + datetime_len(r.created) + datetime_len(r.due) +
+         (r.completed ? 4u : 5u) + (r.overdue ? 4u : 5u) + (i == p.n - 1 ? 1u : 0u);
+}
+
+// K6a: size of every CTA's piece of the text
+__global__ void __launch_bounds__(kJsonThreads) json_len_kernel(JsonParams p) {
+  __shared__ uint32_t s_warp[32];
+  const int64_t i = (int64_t)blockIdx.x * kJsonThreads + threadIdx.x;
+  const JsonRecord r = json_load(p, i);
+  uint32_t tot;
+  block_exclusive_scan(json_record_len(p, r, i), s_warp, &tot);
+  if (threadIdx.x == 0) p.block_base[blockIdx.x] = tot;
+}
+
+__device__ __forceinline__ uint8_t* put_lit(uint8_t* o, int start, int n) {
+  for (int j = 0; j < n; ++j) o[j] = (uint8_t)kJsonLit[start + j];
+  return o + n;
+}
+
+__device__ __forceinline__ uint8_t* put_esc(uint8_t* o, const uint32_t* pool, EscEntry e) {
+  const uint32_t* w = pool + e.word_off;
+  uint32_t j = 0;
+  for (; j + 4 <= e.len; j += 4) {
+    const uint32_t v = __ldg(w + (j >> 2));
+    o[j] = (uint8_t)v;
+    o[j + 1] = (uint8_t)(v >> 8);
+    o[j + 2] = (uint8_t)(v >> 16);
+    o[j + 3] = (uint8_t)(v >> 24);
+  }
+  if (j < e.len) {
+    uint32_t v = __ldg(w + (j >> 2));
+    for (; j < e.len; ++j, v >>= 8) o[j] = (uint8_t)v;
+  }
+  return o + e.len;
+}
+
+__device__ uint8_t* json_write_record(const JsonParams& p, const JsonRecord& r, uint4 id, int64_t i, uint8_t* o) {
+  *o++ = i == 0 ? '[' : ',';
+  o = put_lit(o, 0, 11);
+  const uint32_t w[4] = {id.x, id.y, id.z, id.w};  // canonical bytes 0..15 in memory order
+#pragma unroll
+  for (int b = 0; b < 16; ++b) {
+    if (b == 4 || b == 6 || b == 8 || b == 10) *o++ = '-';
+    const uint32_t byte = (w[b >> 2] >> (8 * (b & 3))) & 0xFF;
+    *o++ = hex_lower(byte >> 4);
+    *o++ = hex_lower(byte & 15);
+  }
+  o = put_lit(o, 11, 14);
+  o = put_esc(o, p.esc_pool[0], r.s[0]);
+  o = put_lit(o, 25, 19);
+  o = put_esc(o, p.esc_pool[1], r.s[1]);
+  o = put_lit(o, 44, 19);
+  o += datetime_write(r.created, p.local_offset_min, o);
+  o = put_lit(o, 63, 17);
+  o += datetime_write(r.due, p.local_offset_min, o);
+  o = put_lit(o, 80, 20);
+  o = put_esc(o, p.esc_pool[2], r.s[2]);
+  o = put_lit(o, 100, 16);
+  o = r.completed ? put_lit(o, 129, 4) : put_lit(o, 133, 5);
+  o = put_lit(o, 116, 13);
+  o = r.overdue ? put_lit(o, 129, 4) : put_lit(o, 133, 5);
+  *o++ = '}';
+  if (i == p.n - 1) *o++ = ']';
+  return o;
+}
+
+// K6b: every thread formats one record; the CTA's piece of the text is contiguous in the output,
+// so it is staged in shared memory (shifted so that 16-byte chunks of both line up) and flushed
+// with 16-byte stores.  A CTA whose piece does not fit the staging area (very long strings)
+// writes straight to global memory instead.
+__global__ void __launch_bounds__(kJsonThreads) json_emit_kernel(JsonParams p) {
+  extern __shared__ __align__(16) uint8_t s_stage[];
+  __shared__ uint32_t s_warp[32];
+  const int64_t i = (int64_t)blockIdx.x * kJsonThreads + threadIdx.x;
+  const JsonRecord r = json_load(p, i);
+  uint4 id = make_uint4(0, 0, 0, 0);
+  if (r.live) id = p.ids[i];
+  uint32_t total;
+  const uint32_t local = block_exclusive_scan(json_record_len(p, r, i), s_warp, &total);
+  const uint64_t base = p.block_base[blockIdx.x];
+  const uint32_t shift = (uint32_t)(base & 15u);
+  const bool staged = shift + total <= (uint32_t)kJsonStageBytes;
+  if (r.live) json_write_record(p, r, id, i, staged ? s_stage + shift + local : p.out + base + local);
+  if (!staged) return;
+  __syncthreads();
+  uint8_t* dst = p.out + (base - shift);
+  const uint32_t lo = shift, hi = shift + total;
+  for (uint32_t a = threadIdx.x * 16; a < hi; a += kJsonThreads * 16) {
+    if (a >= lo && a + 16 <= hi) {
+      *reinterpret_cast<uint4*>(dst + a) = *reinterpret_cast<const uint4*>(s_stage + a);
+    } else {
+      for (uint32_t e = a > lo ? a : lo; e < a + 16 && e < hi; ++e) dst[e] = s_stage[e];
+    }
+  }
+}
+
+}  // namespace tt

@@ -20,6 +20,7 @@
 
 #include "../../include/tasktable.h"
 #include "creator.cuh"
+#include "json.cuh"
 #include "order.cuh"
 #include "point.cuh"
 #include "sweep.cuh"
@@ -126,6 +127,26 @@ struct tt_table {
   uint32_t* h_qcount = nullptr;
   tt_op_stats last_op = {};
   tt::SortScratch sort;  // K5 radix sort buffers, grow-only
+
+  // payload: TaskName and TaskAssignedTo as dictionary-encoded string columns.  No kernel of the
+  // sweep or the filter reads them; they exist so a result can be written out as JSON (K6).
+  // ref == 0xFFFFFFFF (rows inserted later, or no payload loaded) prints an empty string.
+  struct StrColumn {
+    uint32_t* ref = nullptr;  // [n_pad]
+    uint32_t n = 0;           // dictionary entries
+    uint32_t* off = nullptr;  // [n + 1]
+    uint8_t* pool = nullptr;
+  } name_col, assignee_col;
+  // escaped dictionaries for K6, built on first use: [name, creator, assignee][response, document]
+  struct EscCache {
+    tt::EscEntry* entry = nullptr;
+    uint32_t* pool = nullptr;
+    uint32_t n = 0;
+    bool ready = false;
+  } esc[3][2];
+  uint64_t* json_blocks = nullptr;  // K6 block sums / bases
+  int64_t json_blocks_cap = 0;
+  tt_json_stats last_json = {};
 };
 
 // One device allocation, shared by the results that point into it (a batch of creator queries
@@ -186,6 +207,21 @@ void free_columns(tt_table* t) {
   cudaFree(t->tile_words);
   cudaFree(t->group_sum);
   cudaFree(t->hit_list);
+  for (tt_table::StrColumn* c : {&t->name_col, &t->assignee_col}) {
+    cudaFree(c->ref);
+    cudaFree(c->off);
+    cudaFree(c->pool);
+    *c = tt_table::StrColumn();
+  }
+  for (auto& per_col : t->esc)
+    for (auto& e : per_col) {
+      cudaFree(e.entry);
+      cudaFree(e.pool);
+      e = tt_table::EscCache();
+    }
+  cudaFree(t->json_blocks);
+  t->json_blocks = nullptr;
+  t->json_blocks_cap = 0;
   t->due_code = t->completed = t->overdue = nullptr;
   t->creator_hash = nullptr;
   t->task_id = nullptr;
@@ -1333,6 +1369,8 @@ int32_t grow_rows(tt_table* t) {
   if ((rc = grow_buffer(t, &t->created_raw, old_pad, np, 0))) return rc;
   if ((rc = grow_buffer(t, &t->due_raw, old_pad, np, 0))) return rc;
   if ((rc = grow_buffer(t, &t->creator_ref, old_pad, np, 0))) return rc;
+  if (t->name_col.ref && (rc = grow_buffer(t, &t->name_col.ref, old_pad, np, 0xFF))) return rc;
+  if (t->assignee_col.ref && (rc = grow_buffer(t, &t->assignee_col.ref, old_pad, np, 0xFF))) return rc;
   cudaFree(t->tile_words);
   cudaFree(t->group_sum);
   t->tile_words = t->group_sum = nullptr;
@@ -1730,6 +1768,324 @@ int32_t tt_expand_hits(int32_t device, const uint32_t* d_tile_count, int64_t n_t
   tt::tile_offsets_kernel<<<groups, tt::kTilesPerGroup, 0, stream>>>(d_tile_count, group_sum, nt, tile_first);
   tt::expand_hits16_kernel<<<(nt + 7) / 8, 256, 0, stream>>>(d_tile_count, tile_first, nt, d_off16, d_rows_out);
   TT_CUDA(cudaGetLastError());
+  return TT_OK;
+}
+
+}  // extern "C"
+
+// ---- payload strings and the JSON form of a result (K6, csrc/json.cuh) ----------------------------
+
+struct tt_json {
+  std::shared_ptr<TableCore> core;
+  uint8_t* d_text = nullptr;
+  int64_t bytes = 0;
+};
+
+namespace {
+
+__global__ void fill_payload_kernel(tt_synth_cfg cfg, uint64_t first_row, int64_t n, uint32_t* name_ref,
+                                    uint32_t* assignee_ref) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  name_ref[i] = tt_synth_name_ref(&cfg, first_row + (uint64_t)i);
+  assignee_ref[i] = tt_synth_assignee_ref(&cfg, first_row + (uint64_t)i);
+}
+
+int32_t check_strings(const tt_strings_view* v, int64_t n, const char* what) {
+  if (!v) return TT_OK;
+  if (n > 0 && !v->ref) return fail(TT_ERR_ARG, "%s: null ref column", what);
+  if (!v->off || (v->n_strings && v->off[v->n_strings] != 0 && !v->pool)) return fail(TT_ERR_ARG, "%s: dictionary missing", what);
+  for (uint32_t k = 0; k < v->n_strings; ++k)
+    if (v->off[k + 1] < v->off[k]) return fail(TT_ERR_ARG, "%s: offsets not ascending", what);
+  for (int64_t i = 0; i < n; ++i)
+    if (v->ref[i] >= v->n_strings && v->ref[i] != 0xFFFFFFFFu)
+      return fail(TT_ERR_ARG, "%s: ref[%lld] out of range", what, (long long)i);
+  return TT_OK;
+}
+
+void drop_column(tt_table::StrColumn* c) {
+  cudaFree(c->ref);
+  cudaFree(c->off);
+  cudaFree(c->pool);
+  *c = tt_table::StrColumn();
+}
+
+// Allocates one payload column (refs all "no string") and uploads its dictionary.
+int32_t set_column(tt_table* t, tt_table::StrColumn* c, int which, uint32_t n_strings, const uint32_t* off,
+                   const uint8_t* pool, const uint32_t* ref_host) {
+  drop_column(c);
+  for (auto& e : t->esc[which]) {
+    cudaFree(e.entry);
+    cudaFree(e.pool);
+    e = tt_table::EscCache();
+  }
+  const size_t bytes = n_strings ? off[n_strings] : 0;
+  TT_CUDA(cudaMalloc(&c->ref, (size_t)t->n_pad * 4));
+  TT_CUDA(cudaMalloc(&c->off, ((size_t)n_strings + 1) * 4));
+  TT_CUDA(cudaMalloc(&c->pool, std::max<size_t>(bytes, 16)));
+  TT_CUDA(cudaMemsetAsync(c->ref, 0xFF, (size_t)t->n_pad * 4, t->stream));
+  TT_CUDA(cudaMemcpyAsync(c->off, off, ((size_t)n_strings + 1) * 4, cudaMemcpyHostToDevice, t->stream));
+  if (bytes) TT_CUDA(cudaMemcpyAsync(c->pool, pool, bytes, cudaMemcpyHostToDevice, t->stream));
+  if (ref_host && t->n) TT_CUDA(cudaMemcpyAsync(c->ref, ref_host, (size_t)t->n * 4, cudaMemcpyHostToDevice, t->stream));
+  TT_CUDA(cudaStreamSynchronize(t->stream));
+  c->n = n_strings;
+  return TT_OK;
+}
+
+// Escaped form of one dictionary for one encoder, cached until the dictionary changes.
+int32_t prepare_escaped(tt_table* t, int which, int flavor, const uint32_t* off, const uint8_t* pool, uint32_t n,
+                        const char* what) {
+  tt_table::EscCache& e = t->esc[which][flavor];
+  if (e.ready && e.n == n) return TT_OK;
+  cudaFree(e.entry);
+  cudaFree(e.pool);
+  e = tt_table::EscCache();
+  if (n == 0) {
+    e.ready = true;
+    return TT_OK;
+  }
+  const uint32_t nb = (n + tt::kScanBlock - 1) / tt::kScanBlock;
+  uint32_t* d_len = nullptr;
+  uint64_t* d_blocks = nullptr;
+  uint32_t* d_err = nullptr;
+  auto cleanup = [&] {
+    cudaFree(d_len);
+    cudaFree(d_blocks);
+    cudaFree(d_err);
+  };
+  cudaError_t ce = cudaMalloc(&d_len, (size_t)n * 4);
+  if (ce == cudaSuccess) ce = cudaMalloc(&d_blocks, ((size_t)nb + 1) * 8);
+  if (ce == cudaSuccess) ce = cudaMalloc(&d_err, 8);
+  if (ce == cudaSuccess) ce = cudaMalloc(&e.entry, (size_t)n * sizeof(tt::EscEntry));
+  if (ce == cudaSuccess) ce = cudaMemsetAsync(d_err, 0, 8, t->stream);
+  if (ce != cudaSuccess) {
+    cleanup();
+    TT_CUDA(ce);
+  }
+  tt::esc_len_kernel<<<grid_for(n, 256), 256, 0, t->stream>>>(off, pool, n, flavor, d_len, d_err);
+  tt::esc_block_sum_kernel<<<nb, tt::kScanBlock, 0, t->stream>>>(d_len, n, d_blocks);
+  tt::scan_block_sums_kernel<<<1, 1024, 0, t->stream>>>(d_blocks, nb);
+  tt::esc_entries_kernel<<<nb, tt::kScanBlock, 0, t->stream>>>(d_len, n, d_blocks, e.entry);
+  uint32_t h_err[2] = {0, 0};
+  uint64_t words = 0;
+  ce = cudaGetLastError();
+  if (ce == cudaSuccess) ce = cudaMemcpyAsync(h_err, d_err, 8, cudaMemcpyDeviceToHost, t->stream);
+  if (ce == cudaSuccess) ce = cudaMemcpyAsync(&words, d_blocks + nb, 8, cudaMemcpyDeviceToHost, t->stream);
+  if (ce == cudaSuccess) ce = cudaStreamSynchronize(t->stream);
+  if (ce == cudaSuccess && !h_err[0] && words < (1ull << 32)) {
+    ce = cudaMalloc(&e.pool, std::max<size_t>((size_t)words * 4, 16));
+    if (ce == cudaSuccess) {
+      tt::esc_write_kernel<<<grid_for(n, 256), 256, 0, t->stream>>>(off, pool, n, flavor, e.entry, e.pool);
+      ce = cudaGetLastError();
+    }
+    if (ce == cudaSuccess) ce = cudaStreamSynchronize(t->stream);
+  }
+  cleanup();
+  if (ce != cudaSuccess || h_err[0] || words >= (1ull << 32)) {
+    cudaFree(e.entry);
+    cudaFree(e.pool);
+    e = tt_table::EscCache();
+    if (ce != cudaSuccess) TT_CUDA(ce);
+    if (h_err[0])
+      return fail(TT_ERR_ARG, "%s dictionary entry %u is not well-formed UTF-8 or escapes to more than %u bytes", what,
+                  h_err[1], tt::kEscMaxLen);
+    return fail(TT_ERR_ARG, "%s dictionary escapes to more than 16 GB", what);
+  }
+  e.n = n;
+  e.ready = true;
+  return TT_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int32_t tt_load_payload(tt_table* t, const tt_strings_view* task_name, const tt_strings_view* assigned_to) {
+  if (!t) return fail(TT_ERR_ARG, "null argument");
+  std::lock_guard<std::mutex> lk(t->mu);
+  DeviceGuard g(t->device);
+  if (t->n_pad == 0) return fail(TT_ERR_STATE, "load the rows first");
+  int32_t rc;
+  if ((rc = check_strings(task_name, t->n, "TaskName"))) return rc;
+  if ((rc = check_strings(assigned_to, t->n, "TaskAssignedTo"))) return rc;
+  if (task_name && (rc = set_column(t, &t->name_col, 0, task_name->n_strings, task_name->off, task_name->pool, task_name->ref)))
+    return rc;
+  if (assigned_to &&
+      (rc = set_column(t, &t->assignee_col, 2, assigned_to->n_strings, assigned_to->off, assigned_to->pool, assigned_to->ref)))
+    return rc;
+  return TT_OK;
+}
+
+int32_t tt_generate_payload(tt_table* t, const tt_synth_cfg* cfg, uint64_t first_row) {
+  if (!t || !cfg) return fail(TT_ERR_ARG, "null argument");
+  std::lock_guard<std::mutex> lk(t->mu);
+  DeviceGuard g(t->device);
+  if (t->n_pad == 0) return fail(TT_ERR_STATE, "generate the rows first");
+  // the two dictionaries are built on the host (ingest, not hot path); the refs on the device
+  std::vector<uint32_t> off;
+  std::vector<uint8_t> pool;
+  char buf[64];
+  auto build = [&](uint32_t n, int (*make)(uint32_t, char*)) {
+    off.assign((size_t)n + 1, 0);
+    pool.clear();
+    for (uint32_t k = 0; k < n; ++k) {
+      const int len = make(k, buf);
+      pool.insert(pool.end(), buf, buf + len);
+      off[k + 1] = (uint32_t)pool.size();
+    }
+  };
+  int32_t rc;
+  build(tt_synth_n_names(cfg), [](uint32_t k, char* o) { return tt_synth_name(k, o); });
+  if ((rc = set_column(t, &t->name_col, 0, tt_synth_n_names(cfg), off.data(), pool.data(), nullptr))) return rc;
+  build(TT_SYNTH_ASSIGNEES, [](uint32_t k, char* o) { return tt_synth_assignee(k, o); });
+  if ((rc = set_column(t, &t->assignee_col, 2, TT_SYNTH_ASSIGNEES, off.data(), pool.data(), nullptr))) return rc;
+  if (t->n) {
+    fill_payload_kernel<<<grid_for(t->n, 256), 256, 0, t->stream>>>(*cfg, first_row, t->n, t->name_col.ref, t->assignee_col.ref);
+    TT_CUDA(cudaGetLastError());
+    TT_CUDA(cudaStreamSynchronize(t->stream));
+  }
+  return TT_OK;
+}
+
+int32_t tt_result_json(tt_result* r, int32_t flavor, int32_t local_offset_min, tt_json** out) {
+  if (!r || !out) return fail(TT_ERR_ARG, "null argument");
+  *out = nullptr;
+  if (flavor != TT_JSON_RESPONSE && flavor != TT_JSON_DOCUMENT) return fail(TT_ERR_ARG, "flavor must be TT_JSON_RESPONSE or TT_JSON_DOCUMENT");
+  if (local_offset_min <= -24 * 60 || local_offset_min >= 24 * 60) return fail(TT_ERR_ARG, "local_offset_min out of range");
+  if (!r->core->alive) return fail(TT_ERR_STATE, "the table of this result has been destroyed");
+  tt_table* t = r->t;
+  std::lock_guard<std::mutex> lk(t->mu);
+  DeviceGuard g(t->device);
+  t->last_json = tt_json_stats{};
+  tt_json* j = new (std::nothrow) tt_json();
+  if (!j) return fail(TT_ERR_OOM, "out of host memory");
+  j->core = t->core;
+  const int64_t n = r->n;
+  if (n == 0) {  // "[]"
+    cudaError_t e = cudaMalloc(&j->d_text, 16);
+    if (e == cudaSuccess) e = cudaMemcpy(j->d_text, "[]", 2, cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) {
+      cudaFree(j->d_text);
+      delete j;
+      TT_CUDA(e);
+    }
+    j->bytes = 2;
+    t->last_json.bytes = 2;
+    *out = j;
+    return TT_OK;
+  }
+  int32_t rc = TT_OK;
+  if (t->name_col.ref) rc = prepare_escaped(t, 0, flavor, t->name_col.off, t->name_col.pool, t->name_col.n, "TaskName");
+  if (!rc) rc = prepare_escaped(t, 1, flavor, t->creator_off, t->creator_pool, t->n_creators, "TaskCreatedBy");
+  if (!rc && t->assignee_col.ref)
+    rc = prepare_escaped(t, 2, flavor, t->assignee_col.off, t->assignee_col.pool, t->assignee_col.n, "TaskAssignedTo");
+  if (rc) {
+    delete j;
+    return rc;
+  }
+  const int64_t nb = (n + tt::kJsonThreads - 1) / tt::kJsonThreads;
+  if (nb + 1 > t->json_blocks_cap) {
+    cudaFree(t->json_blocks);
+    t->json_blocks = nullptr;
+    t->json_blocks_cap = 0;
+    cudaError_t e = cudaMalloc(&t->json_blocks, (size_t)(nb + 1) * 8);
+    if (e != cudaSuccess) {
+      delete j;
+      TT_CUDA(e);
+    }
+    t->json_blocks_cap = nb + 1;
+  }
+  tt::JsonParams p = {};
+  p.rows = r->d_rows;
+  p.ids = r->d_ids;
+  p.n = n;
+  p.created_raw = t->created_raw;
+  p.due_raw = t->due_raw;
+  p.completed = t->completed;
+  p.overdue = t->overdue;
+  const uint32_t* refs[3] = {t->name_col.ref, t->creator_ref, t->assignee_col.ref};
+  const uint32_t dict_n[3] = {t->name_col.n, t->n_creators, t->assignee_col.n};
+  for (int c = 0; c < 3; ++c) {
+    const tt_table::EscCache& e = t->esc[c][flavor];
+    p.ref[c] = (refs[c] && e.ready && e.n) ? refs[c] : nullptr;
+    p.dict_n[c] = dict_n[c];
+    p.entry[c] = e.entry;
+    p.esc_pool[c] = e.pool;
+  }
+  p.local_offset_min = local_offset_min;
+  p.block_base = t->json_blocks;
+  static bool opted = false;
+  cudaError_t e = cudaSuccess;
+  if (!opted) {
+    e = cudaFuncSetAttribute(tt::json_emit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, tt::kJsonStageBytes);
+    opted = e == cudaSuccess;
+  }
+  uint64_t total = 0;
+  if (e == cudaSuccess) e = cudaEventRecord(t->ev0, t->stream);
+  if (e == cudaSuccess) {
+    tt::json_len_kernel<<<(unsigned)nb, tt::kJsonThreads, 0, t->stream>>>(p);
+    tt::scan_block_sums_kernel<<<1, 1024, 0, t->stream>>>(t->json_blocks, (uint32_t)nb);
+    e = cudaGetLastError();
+  }
+  if (e == cudaSuccess) e = cudaEventRecord(t->ev1, t->stream);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(&total, t->json_blocks + nb, 8, cudaMemcpyDeviceToHost, t->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(t->stream);
+  if (e == cudaSuccess) e = cudaMalloc(&j->d_text, (size_t)total + 16);
+  if (e == cudaSuccess) {
+    p.out = j->d_text;
+    tt::json_emit_kernel<<<(unsigned)nb, tt::kJsonThreads, tt::kJsonStageBytes, t->stream>>>(p);
+    e = cudaGetLastError();
+  }
+  if (e == cudaSuccess) e = cudaEventRecord(t->ev2, t->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(t->stream);
+  if (e != cudaSuccess) {
+    cudaFree(j->d_text);
+    delete j;
+    TT_CUDA(e);
+  }
+  j->bytes = (int64_t)total;
+  cudaEventElapsedTime(&t->last_json.size_ms, t->ev0, t->ev1);
+  cudaEventElapsedTime(&t->last_json.emit_ms, t->ev1, t->ev2);
+  t->last_json.bytes = j->bytes;
+  t->last_json.records = n;
+  t->last_json.launches = 3;
+  *out = j;
+  return TT_OK;
+}
+
+int32_t tt_json_size(const tt_json* j, int64_t* bytes) {
+  if (!j || !bytes) return fail(TT_ERR_ARG, "null argument");
+  *bytes = j->bytes;
+  return TT_OK;
+}
+
+int32_t tt_json_copy(tt_json* j, void* dst) {
+  if (!j || !dst) return fail(TT_ERR_ARG, "null argument");
+  DeviceGuard g(j->core->device);
+  TT_CUDA(cudaMemcpy(dst, j->d_text, (size_t)j->bytes, cudaMemcpyDefault));
+  return TT_OK;
+}
+
+int32_t tt_json_device(tt_json* j, const void** d_text) {
+  if (!j || !d_text) return fail(TT_ERR_ARG, "null argument");
+  *d_text = j->d_text;
+  return TT_OK;
+}
+
+int32_t tt_json_free(tt_json* j) {
+  if (!j) return TT_OK;
+  {
+    DeviceGuard g(j->core->device);
+    cudaFree(j->d_text);
+  }
+  delete j;
+  return TT_OK;
+}
+
+int32_t tt_last_json_stats(tt_table* t, tt_json_stats* out) {
+  if (!t || !out) return fail(TT_ERR_ARG, "null argument");
+  std::lock_guard<std::mutex> lk(t->mu);
+  *out = t->last_json;
   return TT_OK;
 }
 

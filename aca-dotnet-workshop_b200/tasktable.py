@@ -31,6 +31,9 @@ FIELD_COMPLETED = 3
 FIELD_OVERDUE = 4
 FIELD_CREATOR_REF = 5
 
+JSON_RESPONSE = 0  # TT_JSON_RESPONSE: the MVC output formatter's encoder
+JSON_DOCUMENT = 1  # TT_JSON_DOCUMENT: the encoder of Dapr's client bodies
+
 TICKS_PER_DAY = 864000000000
 DEFAULT_TODAY = 639295200000000000  # 2026-11-06T00:00:00
 DEFAULT_RUN_AT = DEFAULT_TODAY + 5 * 60 * 10_000_000
@@ -48,6 +51,8 @@ EXPORTS = [
     "tt_get_by_id", "tt_insert_task", "tt_update_task", "tt_mark_completed", "tt_delete_task", "tt_live_count",
     "tt_save_snapshot", "tt_load_snapshot", "tt_pack_hits", "tt_expand_hits",
     "tt_sweep_push", "tt_peer_alloc", "tt_peer_open", "tt_peer_close", "tt_peer_free",
+    "tt_load_payload", "tt_generate_payload", "tt_result_json", "tt_json_size", "tt_json_copy", "tt_json_device",
+    "tt_json_free", "tt_last_json_stats",
 ]
 
 
@@ -141,6 +146,16 @@ class DeviceView(C.Structure):
     ]
 
 
+class StringsView(C.Structure):
+    """tt_strings_view: a dictionary-encoded string column (host arrays)."""
+    _fields_ = [("ref", C.c_void_p), ("n_strings", C.c_uint32), ("off", C.c_void_p), ("pool", C.c_void_p)]
+
+
+class JsonStats(C.Structure):
+    _fields_ = [("size_ms", C.c_float), ("emit_ms", C.c_float), ("bytes", C.c_int64), ("records", C.c_int64),
+                ("launches", C.c_int32)]
+
+
 class PushTarget(C.Structure):
     """tt_push_target: where tt_sweep_push stores the compact hit list (device addresses)."""
     _fields_ = [("off16", C.c_void_p), ("tile_count", C.c_void_p), ("count", C.c_void_p)]
@@ -209,6 +224,14 @@ def lib():
     L.tt_peer_open.argtypes = [i32, P(PeerHandle), P(vp)]
     L.tt_peer_close.argtypes = [i32, vp]
     L.tt_peer_free.argtypes = [i32, vp]
+    L.tt_load_payload.argtypes = [vp, P(StringsView), P(StringsView)]
+    L.tt_generate_payload.argtypes = [vp, P(SynthCfg), u64]
+    L.tt_result_json.argtypes = [vp, i32, i32, P(vp)]
+    L.tt_json_size.argtypes = [vp, P(i64)]
+    L.tt_json_copy.argtypes = [vp, vp]
+    L.tt_json_device.argtypes = [vp, P(vp)]
+    L.tt_json_free.argtypes = [vp]
+    L.tt_last_json_stats.argtypes = [vp, P(JsonStats)]
     for name in EXPORTS:
         if name != "tt_last_error":
             getattr(L, name).restype = i32
@@ -255,6 +278,20 @@ class Result:
         _check(lib().tt_result_field(self._h, field, _ptr(out)))
         return out
 
+    def json(self, flavor=JSON_RESPONSE, local_offset_min=0):
+        """tt_result_json: the rows of this result as the JSON array the reference's controllers
+        return.  -> JsonText (the text stays on the device until .bytes() is called)."""
+        h = C.c_void_p(0)
+        _check(lib().tt_result_json(self._h, flavor, local_offset_min, C.byref(h)))
+        return JsonText(h)
+
+    def to_json(self, flavor=JSON_RESPONSE, local_offset_min=0):
+        j = self.json(flavor, local_offset_min)
+        try:
+            return j.bytes()
+        finally:
+            j.free()
+
     def digest(self):
         hi, lo, s = C.c_uint64(0), C.c_uint64(0), C.c_uint64(0)
         _check(lib().tt_result_digest(self._h, C.byref(hi), C.byref(lo), C.byref(s)))
@@ -270,6 +307,54 @@ class Result:
             self.free()
         except Exception:
             pass
+
+
+class JsonText:
+    """tt_json: a JSON text resident on the device."""
+
+    def __init__(self, handle):
+        self._h = handle
+        n = C.c_int64(0)
+        _check(lib().tt_json_size(self._h, C.byref(n)))
+        self.size = n.value
+
+    def bytes(self):
+        out = np.empty(self.size, dtype=np.uint8)
+        _check(lib().tt_json_copy(self._h, _ptr(out)))
+        return out.tobytes()
+
+    def copy_to(self, dst_ptr):
+        """dst_ptr: address of host (e.g. pinned) or device memory with room for .size bytes."""
+        _check(lib().tt_json_copy(self._h, dst_ptr))
+
+    def device_ptr(self):
+        p = C.c_void_p(0)
+        _check(lib().tt_json_device(self._h, C.byref(p)))
+        return p.value
+
+    def free(self):
+        if self._h:
+            lib().tt_json_free(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+def encode_strings(values):
+    """Dictionary-encodes one bytes value per row -> (ref uint32[n], off uint32[k+1], pool uint8[]), the
+    arrays a tt_strings_view points at."""
+    index, ref = {}, np.empty(len(values), dtype=np.uint32)
+    for i, v in enumerate(values):
+        ref[i] = index.setdefault(bytes(v), len(index))
+    keys = list(index.keys())
+    off = np.zeros(len(keys) + 1, dtype=np.uint32)
+    off[1:] = np.cumsum([len(k) for k in keys], dtype=np.uint64)
+    pool = np.frombuffer(b"".join(keys) or b"\0", dtype=np.uint8).copy()
+    return ref, off, pool
 
 
 def peer_alloc(device, nbytes):
@@ -333,6 +418,32 @@ class TaskTable:
                     _ptr(pool))
         _check(lib().tt_load_soa(self._h, C.byref(v)))
         return self
+
+    def load_payload(self, task_names=None, assigned_to=None):
+        """TaskName / TaskAssignedTo, one bytes value (UTF-8) per row; either may be None."""
+        keep, views = [], []
+        for values in (task_names, assigned_to):
+            if values is None:
+                views.append(None)
+                continue
+            ref, off, pool = encode_strings(values)
+            keep.append((ref, off, pool))
+            views.append(StringsView(_ptr(ref), len(off) - 1, _ptr(off), _ptr(pool)))
+        _check(lib().tt_load_payload(self._h, C.byref(views[0]) if views[0] else None,
+                                     C.byref(views[1]) if views[1] else None))
+        return self
+
+    def generate_payload(self, cfg, first_row):
+        """Synthetic TaskName / TaskAssignedTo for the rows generate() made (same cfg, same first_row)."""
+        if C.sizeof(cfg) != C.sizeof(SynthCfg):
+            raise TypeError("cfg must have the layout of tt_synth_cfg")
+        _check(lib().tt_generate_payload(self._h, C.cast(C.byref(cfg), C.POINTER(SynthCfg)), first_row))
+        return self
+
+    def last_json_stats(self):
+        st = JsonStats()
+        _check(lib().tt_last_json_stats(self._h, C.byref(st)))
+        return st
 
     def __len__(self):
         n = C.c_int64(0)

@@ -282,6 +282,51 @@ int32_t tt_peer_open(int32_t device, const tt_peer_handle* handle, void** d_ptr)
 int32_t tt_peer_close(int32_t device, void* d_ptr);
 int32_t tt_peer_free(int32_t device, void* d_ptr);
 
+/* ---- payload strings and the JSON form of a result ---------------------------
+ * TaskName and TaskAssignedTo (Api/Models/TaskModel.cs:6,10) are never read by the sweep or the
+ * filter; they are kept as dictionary-encoded string columns only so that a result can leave the
+ * GPU as the text the reference's controllers send.  Without a payload both print as "" (the
+ * reference's default, `= string.Empty`); rows added later by tt_insert_task print "" as well. */
+typedef struct tt_strings_view {
+  const uint32_t* ref;  /* one entry per row: index into the dictionary, 0xFFFFFFFF = empty string */
+  uint32_t n_strings;   /* dictionary entries                                                      */
+  const uint32_t* off;  /* n_strings + 1 byte offsets into pool                                    */
+  const uint8_t* pool;  /* UTF-8 (must be well formed; checked when the first JSON is produced)    */
+} tt_strings_view;
+/* Either view may be NULL (that column is left as it is).  Call after tt_load_soa / tt_generate. */
+int32_t tt_load_payload(tt_table* t, const tt_strings_view* task_name, const tt_strings_view* assigned_to);
+/* The synthetic payload of include/tt_synth.h for the rows tt_generate made (same cfg, same first_row):
+ * "Task number: {i}" names (Api/Services/FakeTasksManager.cs:16; one in eight with characters JSON must
+ * escape) and "assignee{0..49}@mail.com" (FakeTasksManager.cs:21). */
+int32_t tt_generate_payload(tt_table* t, const tt_synth_cfg* cfg, uint64_t first_row);
+
+/* tt_result_json writes the rows of a result, in result order, as the JSON array ASP.NET Core
+ * produces for the List<TaskModel> the controllers return (Api/Controllers/OverdueTasksController.cs:22-26,
+ * Api/Controllers/TasksController.cs:21-25): camelCase names in declaration order, no whitespace,
+ * Guid "D" form, DateTime as System.Text.Json prints it (docs/aca/05-aca-dapr-pubsubapi/index.md:60-69),
+ * isCompleted / isOverDue as they are in the table NOW.  `flavor` selects the string encoder:
+ * TT_JSON_RESPONSE = the MVC output formatter (UnsafeRelaxedJsonEscaping), TT_JSON_DOCUMENT = the
+ * bodies Dapr's client writes (SaveStateAsync / PublishEventAsync, Api/Services/TasksStoreManager.cs:35,155;
+ * JavaScriptEncoder.Default).  local_offset_min is the UTC offset printed for Kind = Local values.
+ * The text stays on the device until tt_json_copy (dst: host or device memory, tt_json_size bytes,
+ * no terminator). */
+#define TT_JSON_RESPONSE 0
+#define TT_JSON_DOCUMENT 1
+typedef struct tt_json tt_json;
+int32_t tt_result_json(tt_result* r, int32_t flavor, int32_t local_offset_min, tt_json** out);
+int32_t tt_json_size(const tt_json* j, int64_t* bytes);
+int32_t tt_json_copy(tt_json* j, void* dst);
+int32_t tt_json_device(tt_json* j, const void** d_text);
+int32_t tt_json_free(tt_json* j);
+typedef struct tt_json_stats {
+  float size_ms;   /* K6a: record sizes + offsets            */
+  float emit_ms;   /* K6b: formatting + write                */
+  int64_t bytes;   /* length of the text                     */
+  int64_t records;
+  int32_t launches;
+} tt_json_stats;
+int32_t tt_last_json_stats(tt_table* t, tt_json_stats* out);
+
 /* ---- snapshot ---------------------------------------------------------------------------------
  * Saves / restores the whole table (all columns, flags, creator dictionary, tombstones) as one
  * file in the device layout — the counterpart of the reference keeping its tasks in a state store

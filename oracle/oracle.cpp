@@ -117,7 +117,7 @@ std::string FormatSystemTextJson(const DateTime& v, int local_offset_min) {
   }
   if (v.Kind() == TT_KIND_UTC) {
     buf[n++] = 'Z';
-  } else if (v.Kind() == TT_KIND_LOCAL) {
+  } else if (v.Kind() >= TT_KIND_LOCAL) {  // 3 = Local with the ambiguous-DST bit
     int off = local_offset_min;
     char sign = off < 0 ? '-' : '+';
     if (off < 0) off = -off;
@@ -337,6 +337,88 @@ struct TasksStoreManager {
   }
 };
 
+// ---- System.Text.Json: List<TaskModel> as the reference sends it ---------------------------------
+// What the controllers return (Api/Controllers/OverdueTasksController.cs:22-26,
+// Api/Controllers/TasksController.cs:21-25) is serialised by ASP.NET Core's
+// SystemTextJsonOutputFormatter with JsonSerializerDefaults.Web: camelCase names, declaration
+// order (Api/Models/TaskModel.cs:5-12), no whitespace, and — because the app configures no
+// encoder — JavaScriptEncoder.UnsafeRelaxedJsonEscaping (flavor 0).  Dapr's client
+// (SaveStateAsync / PublishEventAsync, Api/Services/TasksStoreManager.cs:35,155) uses the same
+// options with the default encoder, JavaScriptEncoder.Default (flavor 1).
+// Third-party code absent from /root/reference: System.Text.Json / System.Text.Encodings.Web of
+// .NET 9 (global.json:3), Dapr.Client 1.14.0.  Their published behaviour, restated:
+//   * both encoders write \b \t \n \f \r as two characters, every other code unit they refuse as
+//     \uXXXX with upper-case hex, a supplementary-plane scalar as its two surrogates;
+//   * Default allows only Basic Latin (U+0020..U+007E) minus  " & ' + < > ` \  ; '\' is "\\", the
+//     quote is ";
+//   * UnsafeRelaxed writes \" and \\, and allows every other BMP code point that the encoder
+//     treats as defined: not a control (Cc), not a space separator other than U+0020 (Zs), not
+//     U+2028 / U+2029, not a surrogate, private-use or non-character code point.  Code points
+//     unassigned in the Unicode version .NET 9 carries are also refused by the real encoder;
+//     that table is not restated here (PARITY UNPINNED for such text).
+// Pins: the documented sample body docs/aca/05-aca-dapr-pubsubapi/index.md:60-69 (tests/test_oracle.py).
+bool JsonAllowed(char16_t c, int flavor) {
+  if (c < 0x20 || c == u'"' || c == u'\\' || c == 0x7F) return false;
+  if (c < 0x7F) {
+    if (flavor == 1) return !(c == u'&' || c == u'\'' || c == u'+' || c == u'<' || c == u'>' || c == u'`');
+    return true;
+  }
+  if (flavor == 1) return false;  // outside UnicodeRanges.BasicLatin
+  if (c <= 0x9F) return false;    // C1 controls
+  if (c == 0xA0 || c == 0x1680 || (c >= 0x2000 && c <= 0x200A) || c == 0x202F || c == 0x205F || c == 0x3000) return false;  // Zs
+  if (c == 0x2028 || c == 0x2029) return false;                                                                            // Zl, Zp
+  if (c >= 0xD800 && c <= 0xF8FF) return false;  // surrogates, private use
+  if ((c >= 0xFDD0 && c <= 0xFDEF) || c >= 0xFFFE) return false;  // non-characters
+  return true;
+}
+
+void JsonWriteString(std::string& out, const std::u16string& s, int flavor) {
+  static const char* HEX = "0123456789ABCDEF";
+  out.push_back('"');
+  for (char16_t c : s) {
+    if (JsonAllowed(c, flavor)) {  // UTF-8 of a BMP code unit
+      if (c < 0x80) out.push_back((char)c);
+      else if (c < 0x800) { out.push_back((char)(0xC0 | (c >> 6))); out.push_back((char)(0x80 | (c & 0x3F))); }
+      else { out.push_back((char)(0xE0 | (c >> 12))); out.push_back((char)(0x80 | ((c >> 6) & 0x3F))); out.push_back((char)(0x80 | (c & 0x3F))); }
+      continue;
+    }
+    switch (c) {
+      case u'\b': out += "\\b"; continue;
+      case u'\t': out += "\\t"; continue;
+      case u'\n': out += "\\n"; continue;
+      case u'\f': out += "\\f"; continue;
+      case u'\r': out += "\\r"; continue;
+      case u'\\': out += "\\\\"; continue;
+      case u'"': if (flavor == 0) { out += "\\\""; continue; } break;
+      default: break;
+    }
+    out += "\\u";
+    out.push_back(HEX[(c >> 12) & 15]);
+    out.push_back(HEX[(c >> 8) & 15]);
+    out.push_back(HEX[(c >> 4) & 15]);
+    out.push_back(HEX[c & 15]);
+  }
+  out.push_back('"');
+}
+
+void JsonWriteTaskModel(std::string& out, const TaskModel& t, int flavor, int local_offset_min) {
+  out += "{\"taskId\":\"";
+  out += t.TaskId.ToString();
+  out += "\",\"taskName\":";
+  JsonWriteString(out, t.TaskName, flavor);
+  out += ",\"taskCreatedBy\":";
+  JsonWriteString(out, t.TaskCreatedBy, flavor);
+  out += ",\"taskCreatedOn\":\"";
+  out += FormatSystemTextJson(t.TaskCreatedOn, local_offset_min);
+  out += "\",\"taskDueDate\":\"";
+  out += FormatSystemTextJson(t.TaskDueDate, local_offset_min);
+  out += "\",\"taskAssignedTo\":";
+  JsonWriteString(out, t.TaskAssignedTo, flavor);
+  out += t.IsCompleted ? ",\"isCompleted\":true" : ",\"isCompleted\":false";
+  out += t.IsOverDue ? ",\"isOverDue\":true" : ",\"isOverDue\":false";
+  out.push_back('}');
+}
+
 struct OracleTable {
   TaskList rows;  // every task ever added, by insertion index; owns the TaskModel objects
   TaskList live;  // the reference's _tasksList / the store's documents, in list order
@@ -371,9 +453,11 @@ TaskModel* SynthTask(const tt_synth_cfg* cfg, uint64_t grow) {
   char buf[48];
   int n = tt_synth_creator(r.creator, buf);
   t->TaskCreatedBy = Utf8ToUtf16(buf, n);
-  char name[48];
-  int nn = snprintf(name, sizeof name, "Task number: %llu", (unsigned long long)grow);
+  char name[64];
+  int nn = tt_synth_name(tt_synth_name_ref(cfg, grow), name);
   t->TaskName = Utf8ToUtf16(name, nn);
+  nn = tt_synth_assignee(tt_synth_assignee_ref(cfg, grow), name);
+  t->TaskAssignedTo = Utf8ToUtf16(name, nn);
   t->TaskCreatedOn = DateTime(r.created_raw);
   t->TaskDueDate = DateTime(r.due_raw);
   t->IsCompleted = r.completed;
@@ -647,6 +731,38 @@ int32_t orc_format_converter(uint64_t raw, char* out, int32_t cap) {
   std::string s = FormatConverter(DateTime(raw));
   snprintf(out, cap, "%s", s.c_str());
   return (int32_t)s.size();
+}
+
+// JsonSerializer.Serialize(List<TaskModel>) for the listed rows (insertion indices), in the given
+// order.  Returns the length; writes at most cap bytes.
+int64_t orc_serialize(orc_table* t, const uint32_t* rows, int64_t n, int32_t flavor, int32_t local_offset_min, char* out,
+                      int64_t cap) {
+  std::string s = "[";
+  for (int64_t i = 0; i < n; ++i) {
+    if (i) s.push_back(',');
+    JsonWriteTaskModel(s, *t->rows[rows[i]], flavor, local_offset_min);
+  }
+  s.push_back(']');
+  if (out && cap > 0) memcpy(out, s.data(), (size_t)std::min<int64_t>(cap, (int64_t)s.size()));
+  return (int64_t)s.size();
+}
+
+// UTF-8 of TaskName / TaskAssignedTo for one row (test bookkeeping: lets the tests load the same
+// strings into the device table).  which: 0 = TaskName, 2 = TaskAssignedTo.  Returns the length.
+int32_t orc_string_field(orc_table* t, int64_t row, int32_t which, char* out, int32_t cap) {
+  const std::u16string& s = which == 0 ? t->rows[row]->TaskName : which == 2 ? t->rows[row]->TaskAssignedTo : t->rows[row]->TaskCreatedBy;
+  std::string u;
+  for (size_t i = 0; i < s.size(); ++i) {
+    uint32_t c = s[i];
+    if (c >= 0xD800 && c <= 0xDBFF && i + 1 < s.size()) { c = 0x10000 + ((c - 0xD800) << 10) + (s[i + 1] - 0xDC00); ++i; }
+    if (c < 0x80) u.push_back((char)c);
+    else if (c < 0x800) { u.push_back((char)(0xC0 | (c >> 6))); u.push_back((char)(0x80 | (c & 0x3F))); }
+    else if (c < 0x10000) { u.push_back((char)(0xE0 | (c >> 12))); u.push_back((char)(0x80 | ((c >> 6) & 0x3F))); u.push_back((char)(0x80 | (c & 0x3F))); }
+    else { u.push_back((char)(0xF0 | (c >> 18))); u.push_back((char)(0x80 | ((c >> 12) & 0x3F))); u.push_back((char)(0x80 | ((c >> 6) & 0x3F))); u.push_back((char)(0x80 | (c & 0x3F))); }
+  }
+  int32_t n = (int32_t)std::min<size_t>(u.size(), (size_t)cap);
+  memcpy(out, u.data(), n);
+  return (int32_t)u.size();
 }
 
 void orc_guid_string(const uint8_t* id16, char* out37) {

@@ -117,6 +117,10 @@ def lib():
     L.orc_format_stj.argtypes = [u64, i32, C.c_char_p, i32]
     L.orc_format_converter.argtypes = [u64, C.c_char_p, i32]
     L.orc_guid_string.argtypes = [vp, C.c_char_p]
+    L.orc_serialize.argtypes = [vp, vp, i64, i32, i32, vp, i64]
+    L.orc_serialize.restype = i64
+    L.orc_string_field.argtypes = [vp, i64, i32, C.c_char_p, i32]
+    L.orc_string_field.restype = i32
     L.orc_stream_sweep.argtypes = [C.POINTER(SynthCfg), u64, u64, i32, i64, i64, i32, C.POINTER(StreamOut)]
     L.orc_soa_create.argtypes = [C.POINTER(SynthCfg), u64, i64, i32]
     L.orc_soa_create.restype = vp
@@ -129,6 +133,10 @@ def lib():
 
 def _ptr(a):
     return a.ctypes.data_as(C.c_void_p)
+
+
+JSON_RESPONSE = 0  # ASP.NET Core MVC output formatter (UnsafeRelaxedJsonEscaping)
+JSON_DOCUMENT = 1  # Dapr client bodies (JavaScriptEncoder.Default)
 
 
 class OracleTable:
@@ -238,9 +246,21 @@ class OracleTable:
         return ids, cr, du
 
     def created_by(self, row):
-        buf = C.create_string_buffer(256)
-        n = self._l.orc_created_by(self._h, row, buf, 256)
+        return self.string_field(row, 1)
+
+    def string_field(self, row, which):
+        """UTF-8 of TaskName (which=0), TaskCreatedBy (1) or TaskAssignedTo (2) of one row."""
+        buf = C.create_string_buffer(4096)
+        n = self._l.orc_string_field(self._h, row, which, buf, 4096)
         return buf.raw[:n]
+
+    def to_json(self, rows, flavor=JSON_RESPONSE, local_offset_min=0):
+        """JsonSerializer.Serialize(List<TaskModel>) of the listed rows, in that order (bytes)."""
+        rows = np.ascontiguousarray(rows, dtype=np.uint32)
+        need = self._l.orc_serialize(self._h, _ptr(rows), rows.size, flavor, local_offset_min, None, 0)
+        out = np.empty(need, dtype=np.uint8)
+        self._l.orc_serialize(self._h, _ptr(rows), rows.size, flavor, local_offset_min, _ptr(out), need)
+        return out.tobytes()
 
 
 def format_stj(raw, local_offset_min=0):

@@ -243,3 +243,56 @@ def test_point_operations_follow_the_two_implementations(oracle):
         assert row == 11 and t.get_yesterdays_due(oracle.MODE_FAKE, TODAY).tolist()[-1] == 11
         threw, listed, n_over = t.cron_job(mode, TODAY, TODAY + 3000000000)
         assert threw == (mode == oracle.MODE_FAKE) and n_over == listed.size
+
+
+# ---- the JSON form of a task list (System.Text.Json restatement) ------------------------------------
+def _doc_sample_table(oracle):
+    """the body documented at docs/aca/05-aca-dapr-pubsubapi/index.md:60-69"""
+    import uuid
+
+    def ticks(y, mo, d, h=0, mi=0, s=0, frac=0):
+        import datetime
+
+        days = (datetime.date(y, mo, d) - datetime.date(1, 1, 1)).days
+        return (days * 86400 + h * 3600 + mi * 60 + s) * 10_000_000 + frac
+
+    ot = oracle.OracleTable()
+    ot.add(np.frombuffer(uuid.UUID("fbc55b2c-d9fa-405e-aec8-22e53f4306dd").bytes, dtype=np.uint8).copy(),
+           b"Testing Pub Sub Publisher", b"user@mail.net", b"user2@mail.com",
+           ticks(2023, 2, 12, 0, 24, 37, 7361348) | (1 << 62), ticks(2023, 2, 20))
+    return ot
+
+
+def test_json_matches_the_documented_sample_body(oracle):
+    import json
+
+    ot = _doc_sample_table(oracle)
+    for flavor in (oracle.JSON_RESPONSE, oracle.JSON_DOCUMENT):
+        text = ot.to_json([0], flavor)
+        assert text == (b'[{"taskId":"fbc55b2c-d9fa-405e-aec8-22e53f4306dd","taskName":"Testing Pub Sub Publisher",'
+                        b'"taskCreatedBy":"user@mail.net","taskCreatedOn":"2023-02-12T00:24:37.7361348Z",'
+                        b'"taskDueDate":"2023-02-20T00:00:00","taskAssignedTo":"user2@mail.com",'
+                        b'"isCompleted":false,"isOverDue":false}]')
+        doc = json.loads(text)[0]
+        sample = {"taskId": "fbc55b2c-d9fa-405e-aec8-22e53f4306dd", "taskName": "Testing Pub Sub Publisher",
+                  "taskCreatedBy": "user@mail.net", "taskCreatedOn": "2023-02-12T00:24:37.7361348Z",
+                  "taskDueDate": "2023-02-20T00:00:00", "taskAssignedTo": "user2@mail.com"}
+        assert {k: doc[k] for k in sample} == sample
+
+
+def test_json_encoders_differ_where_dotnet_says_they_do(oracle):
+    import json
+    import uuid
+
+    ot = oracle.OracleTable()
+    name = "a\"b\\c<d>&'+`\t\x01\x7f caf\u00e9 \u2028 \U0001F600"
+    ot.add(np.frombuffer(uuid.UUID(int=5).bytes, dtype=np.uint8).copy(), name.encode(), b"c", b"", 0, 0)
+    relaxed = ot.to_json([0], oracle.JSON_RESPONSE).decode()
+    default = ot.to_json([0], oracle.JSON_DOCUMENT).decode()
+    assert '"taskName":"a\\"b\\\\c<d>&\'+`\\t\\u0001\\u007F caf\u00e9 \\u2028 \\uD83D\\uDE00"' in relaxed
+    assert ('"taskName":"a\\u0022b\\\\c\\u003Cd\\u003E\\u0026\\u0027\\u002B\\u0060\\t\\u0001\\u007F caf\\u00E9 \\u2028 '
+            '\\uD83D\\uDE00"') in default
+    assert json.loads(relaxed)[0]["taskName"] == json.loads(default)[0]["taskName"] == name
+    assert ot.to_json([], 0) == b"[]"
+    # 0001-01-01T00:00:00 with Kind Unspecified: no fraction, no suffix
+    assert '"taskCreatedOn":"0001-01-01T00:00:00","taskDueDate":"0001-01-01T00:00:00"' in relaxed
