@@ -30,6 +30,47 @@ namespace tt {
 constexpr int kJsonResponse = 0;
 constexpr int kJsonDocument = 1;
 
+// ---- L2 residency hints -----------------------------------------------------------------------
+// The escaped dictionaries (a few tens of MB) are re-read by every record while gigabytes of
+// output stream through the same 126 MB L2: dictionary loads ask to be evicted last, the output
+// stores and the one-shot loads to be evicted first.
+__device__ __forceinline__ uint64_t l2_evict_last_policy() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+__device__ __forceinline__ uint64_t l2_evict_first_policy() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+__device__ __forceinline__ uint32_t ld_hint_u32(const uint32_t* p, uint64_t pol) {
+  uint32_t v;
+  asm volatile("ld.global.nc.L2::cache_hint.u32 %0, [%1], %2;" : "=r"(v) : "l"(p), "l"(pol));
+  return v;
+}
+__device__ __forceinline__ uint4 ld_hint_v4(const uint4* p, uint64_t pol) {
+  uint4 v;
+  asm volatile("ld.global.nc.L2::cache_hint.v4.u32 {%0, %1, %2, %3}, [%4], %5;"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "l"(p), "l"(pol));
+  return v;
+}
+__device__ __forceinline__ uint64_t ld_hint_u64(const uint64_t* p, uint64_t pol) {
+  uint64_t v;
+  asm volatile("ld.global.nc.L2::cache_hint.u64 %0, [%1], %2;" : "=l"(v) : "l"(p), "l"(pol));
+  return v;
+}
+__device__ __forceinline__ void st_hint_v4(uint4* p, uint4 v, uint64_t pol) {
+  asm volatile("st.global.L2::cache_hint.v4.u32 [%0], {%1, %2, %3, %4}, %5;"
+               :
+               : "l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w), "l"(pol)
+               : "memory");
+}
+__device__ __forceinline__ void st_hint_u64(uint64_t* p, uint64_t v, uint64_t pol) {
+  asm volatile("st.global.L2::cache_hint.u64 [%0], %1, %2;" : : "l"(p), "l"(v), "l"(pol) : "memory");
+}
+
 // ---- escaping one Unicode scalar -----------------------------------------------------------
 // Returns how a scalar is written: 0 = as is, 1 = backslash + *short_ch, 2 = \uXXXX,
 // 3 = \uXXXX\uXXXX (surrogate pair).  System.Text.Json's published rules (assumptions of record in
@@ -123,12 +164,14 @@ __device__ uint32_t json_escape(const uint8_t* s, uint32_t len, int flavor, uint
   return o;
 }
 
-// One dictionary entry's escaped form: where it starts in the escaped pool (in 32-bit words, so
-// the emitter can read it with aligned word loads) and its length in bytes.
+// One dictionary entry's escaped form: where it starts in the escaped pool (in 32-bit words; every
+// entry starts on a 16-byte boundary so the emitter reads it with aligned 128-bit loads) and its
+// length in bytes.
 struct EscEntry {
   uint32_t word_off;
   uint32_t len;
 };
+__host__ __device__ __forceinline__ uint32_t esc_words(uint32_t len) { return ((len + 15u) >> 4) * 4u; }
 
 constexpr uint32_t kEscMaxLen = 1u << 20;  // longest escaped string the emitter accepts
 
@@ -157,7 +200,7 @@ __global__ void esc_write_kernel(const uint32_t* off, const uint8_t* pool, uint3
   uint8_t* dst = reinterpret_cast<uint8_t*>(esc_pool + entry[k].word_off);
   const uint32_t l = entry[k].len;
   if (l) json_escape<true>(pool + a, b - a, flavor, dst);
-  for (uint32_t j = l; j < ((l + 3) & ~3u); ++j) dst[j] = 0;  // padding of the last word
+  for (uint32_t j = l; j < ((l + 15) & ~15u); ++j) dst[j] = 0;  // padding of the last 16 bytes
 }
 
 // ---- a small generic scan: u32 weights -> u64 exclusive offsets ------------------------------
@@ -192,23 +235,31 @@ __device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t v, uint32_t* s
 __global__ void __launch_bounds__(kScanBlock) esc_block_sum_kernel(const uint32_t* len, uint32_t n, uint64_t* block_sum) {
   __shared__ uint32_t s_warp[32];
   const uint32_t k = blockIdx.x * kScanBlock + threadIdx.x;
-  const uint32_t w = k < n ? (len[k] + 3) >> 2 : 0u;
+  const uint32_t w = k < n ? esc_words(len[k]) : 0u;
   uint32_t tot;
   block_exclusive_scan(w, s_warp, &tot);
   if (threadIdx.x == 0) block_sum[blockIdx.x] = tot;
 }
 
-// in place: block_sum[b] <- sum of the blocks before b; block_sum[nb] <- total
+// in place: block_sum[b] <- sum of the blocks before b; block_sum[nb] <- total.  One CTA; every
+// thread owns kScanPerThread consecutive sums per round.
+constexpr int kScanPerThread = 8;
 __global__ void __launch_bounds__(1024) scan_block_sums_kernel(uint64_t* block_sum, uint32_t nb) {
   __shared__ uint64_t s_warp[32];
   __shared__ uint64_t s_carry;
   const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
   if (threadIdx.x == 0) s_carry = 0;
   __syncthreads();
-  for (uint32_t b0 = 0; b0 < nb; b0 += 1024) {
-    const uint32_t b = b0 + threadIdx.x;
-    const uint64_t v = b < nb ? block_sum[b] : 0ull;
-    uint64_t incl = v;
+  for (uint32_t b0 = 0; b0 < nb; b0 += 1024 * kScanPerThread) {
+    const uint32_t b = b0 + threadIdx.x * kScanPerThread;
+    uint64_t v[kScanPerThread];
+    uint64_t mine = 0;
+#pragma unroll
+    for (int k = 0; k < kScanPerThread; ++k) {
+      v[k] = b + k < nb ? block_sum[b + k] : 0ull;
+      mine += v[k];
+    }
+    uint64_t incl = mine;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
       uint64_t up = __shfl_up_sync(0xFFFFFFFFu, incl, d);
@@ -216,11 +267,15 @@ __global__ void __launch_bounds__(1024) scan_block_sums_kernel(uint64_t* block_s
     }
     if (lane == 31) s_warp[warp] = incl;
     __syncthreads();
-    uint64_t base = s_carry;
-    for (uint32_t w = 0; w < warp; ++w) base += s_warp[w];
-    if (b < nb) block_sum[b] = base + incl - v;
+    uint64_t run = s_carry + incl - mine;
+    for (uint32_t w = 0; w < warp; ++w) run += s_warp[w];
+#pragma unroll
+    for (int k = 0; k < kScanPerThread; ++k) {
+      if (b + k < nb) block_sum[b + k] = run;
+      run += v[k];
+    }
     __syncthreads();
-    if (threadIdx.x == 1023) s_carry = base + incl;
+    if (threadIdx.x == 1023) s_carry = run;
     __syncthreads();
   }
   if (threadIdx.x == 0) block_sum[nb] = s_carry;
@@ -231,7 +286,7 @@ __global__ void __launch_bounds__(kScanBlock) esc_entries_kernel(const uint32_t*
   __shared__ uint32_t s_warp[32];
   const uint32_t k = blockIdx.x * kScanBlock + threadIdx.x;
   const uint32_t l = k < n ? len[k] : 0u;
-  const uint32_t local = block_exclusive_scan((l + 3) >> 2, s_warp, nullptr);
+  const uint32_t local = block_exclusive_scan(esc_words(l), s_warp, nullptr);
   if (k < n) {
     EscEntry e;
     e.word_off = (uint32_t)(block_base[blockIdx.x] + local);
@@ -271,6 +326,8 @@ struct JsonParams {
   const uint32_t* esc_pool[3];
   int32_t local_offset_min;  // UTC offset used to print Kind = Local values
   uint64_t* block_base;      // [blocks + 1]
+  uint64_t* plan;            // [5][plan_stride]: what K6a gathered for every record, read back by K6b
+  int64_t plan_stride;
   uint8_t* out;
 };
 
@@ -345,34 +402,38 @@ __device__ uint32_t datetime_write(uint64_t raw, int32_t local_offset_min, uint8
 }
 
 constexpr int kJsonThreads = 128;            // records per CTA
-constexpr int kJsonStageBytes = 56 * 1024;   // shared-memory staging per CTA (4 CTAs per SM)
+constexpr int kJsonStageBytes = 44 * 1024;   // shared-memory staging per CTA (5 CTAs per SM)
 
 struct JsonRecord {
-  uint32_t row;
   uint64_t created, due;
   EscEntry s[3];
   bool completed, overdue, live;
 };
 
-__device__ __forceinline__ JsonRecord json_load(const JsonParams& p, int64_t i) {
+// K6a's gathers: five row-indexed columns, the two flag planes and three dictionary entries.
+__device__ __forceinline__ JsonRecord json_gather(const JsonParams& p, int64_t i, uint64_t keep) {
   JsonRecord r;
   r.live = i < p.n;
-  r.row = 0;
   r.created = r.due = 0;
   r.completed = r.overdue = false;
 #pragma unroll
   for (int c = 0; c < 3; ++c) r.s[c].word_off = r.s[c].len = 0;
   if (!r.live) return r;
-  r.row = p.rows[i];
-  r.created = ld_gather_u64(p.created_raw + r.row);
-  r.due = ld_gather_u64(p.due_raw + r.row);
-  r.completed = (p.completed[r.row >> 5] >> (r.row & 31)) & 1u;
-  r.overdue = (p.overdue[r.row >> 5] >> (r.row & 31)) & 1u;
+  const uint32_t row = p.rows[i];
+  r.created = ld_gather_u64(p.created_raw + row);
+  r.due = ld_gather_u64(p.due_raw + row);
+  uint32_t k[3] = {~0u, ~0u, ~0u};
+#pragma unroll
+  for (int c = 0; c < 3; ++c)
+    if (p.ref[c]) k[c] = p.ref[c][row];
+  r.completed = (p.completed[row >> 5] >> (row & 31)) & 1u;
+  r.overdue = (p.overdue[row >> 5] >> (row & 31)) & 1u;
 #pragma unroll
   for (int c = 0; c < 3; ++c) {
-    if (p.ref[c]) {
-      const uint32_t k = p.ref[c][r.row];
-      if (k < p.dict_n[c]) r.s[c] = p.entry[c][k];
+    if (k[c] < p.dict_n[c]) {
+      const uint64_t e = ld_hint_u64(reinterpret_cast<const uint64_t*>(p.entry[c] + k[c]), keep);
+      r.s[c].word_off = (uint32_t)e;
+      r.s[c].len = (uint32_t)(e >> 32);
     }
   }
   return r;
@@ -384,11 +445,49 @@ __device__ __forceinline__ uint32_t json_record_len(const JsonParams& p, const J
          (r.completed ? 4u : 5u) + (r.overdue ? 4u : 5u) + (i == p.n - 1 ? 1u : 0u);
 }
 
-// K6a: size of every CTA's piece of the text
+// The plan: 5 x u64 per record, one array per word (coalesced both ways).  Entry lengths are
+// < 2^21 (kEscMaxLen), so the two flags ride in bit 63 of words 2 and 3.
+__device__ __forceinline__ void json_plan_store(const JsonParams& p, int64_t i, const JsonRecord& r, uint64_t stream) {
+  uint64_t* w = p.plan + i;
+  st_hint_u64(w, r.created, stream);
+  st_hint_u64(w + p.plan_stride, r.due, stream);
+  st_hint_u64(w + 2 * p.plan_stride, r.s[0].word_off | ((uint64_t)r.s[0].len << 32) | ((uint64_t)r.completed << 63), stream);
+  st_hint_u64(w + 3 * p.plan_stride, r.s[1].word_off | ((uint64_t)r.s[1].len << 32) | ((uint64_t)r.overdue << 63), stream);
+  st_hint_u64(w + 4 * p.plan_stride, r.s[2].word_off | ((uint64_t)r.s[2].len << 32), stream);
+}
+
+__device__ __forceinline__ JsonRecord json_plan_load(const JsonParams& p, int64_t i, uint64_t stream) {
+  JsonRecord r;
+  r.live = i < p.n;
+  r.created = r.due = 0;
+  r.completed = r.overdue = false;
+#pragma unroll
+  for (int c = 0; c < 3; ++c) r.s[c].word_off = r.s[c].len = 0;
+  if (!r.live) return r;
+  const uint64_t* w = p.plan + i;
+  r.created = ld_hint_u64(w, stream);
+  r.due = ld_hint_u64(w + p.plan_stride, stream);
+  const uint64_t a = ld_hint_u64(w + 2 * p.plan_stride, stream), b = ld_hint_u64(w + 3 * p.plan_stride, stream),
+                 c = ld_hint_u64(w + 4 * p.plan_stride, stream);
+  r.s[0].word_off = (uint32_t)a;
+  r.s[0].len = (uint32_t)(a >> 32) & 0x7FFFFFFFu;
+  r.completed = a >> 63;
+  r.s[1].word_off = (uint32_t)b;
+  r.s[1].len = (uint32_t)(b >> 32) & 0x7FFFFFFFu;
+  r.overdue = b >> 63;
+  r.s[2].word_off = (uint32_t)c;
+  r.s[2].len = (uint32_t)(c >> 32);
+  return r;
+}
+
+// K6a: gathers every record's fields once (the scattered reads), keeps them as the plan, and
+// sizes every CTA's piece of the text
 __global__ void __launch_bounds__(kJsonThreads) json_len_kernel(JsonParams p) {
   __shared__ uint32_t s_warp[32];
+  const uint64_t keep = l2_evict_last_policy(), stream = l2_evict_first_policy();
   const int64_t i = (int64_t)blockIdx.x * kJsonThreads + threadIdx.x;
-  const JsonRecord r = json_load(p, i);
+  const JsonRecord r = json_gather(p, i, keep);
+  if (r.live) json_plan_store(p, i, r, stream);
   uint32_t tot;
   block_exclusive_scan(json_record_len(p, r, i), s_warp, &tot);
   if (threadIdx.x == 0) p.block_base[blockIdx.x] = tot;
@@ -399,24 +498,42 @@ __device__ __forceinline__ uint8_t* put_lit(uint8_t* o, int start, int n) {
   return o + n;
 }
 
-__device__ __forceinline__ uint8_t* put_esc(uint8_t* o, const uint32_t* pool, EscEntry e) {
-  const uint32_t* w = pool + e.word_off;
-  uint32_t j = 0;
-  for (; j + 4 <= e.len; j += 4) {
-    const uint32_t v = __ldg(w + (j >> 2));
-    o[j] = (uint8_t)v;
-    o[j + 1] = (uint8_t)(v >> 8);
-    o[j + 2] = (uint8_t)(v >> 16);
-    o[j + 3] = (uint8_t)(v >> 24);
-  }
-  if (j < e.len) {
-    uint32_t v = __ldg(w + (j >> 2));
-    for (; j < e.len; ++j, v >>= 8) o[j] = (uint8_t)v;
+// The first 32 bytes of an escaped string, fetched before any formatting starts: the three strings
+// of a record are six independent 128-bit loads in flight together instead of a chain of
+// dependent word loads (each an L2 round trip) in the middle of the byte stores.
+struct EscHead {
+  uint4 q0, q1;
+};
+
+__device__ __forceinline__ EscHead esc_prefetch(const uint32_t* pool, EscEntry e, uint64_t keep) {
+  EscHead h;
+  h.q0 = h.q1 = make_uint4(0, 0, 0, 0);
+  const uint4* q = reinterpret_cast<const uint4*>(pool + e.word_off);
+  if (e.len > 0) h.q0 = ld_hint_v4(q, keep);
+  if (e.len > 16) h.q1 = ld_hint_v4(q + 1, keep);
+  return h;
+}
+
+__device__ __forceinline__ uint8_t* put_esc(uint8_t* o, const uint32_t* pool, EscEntry e, const EscHead& h, uint64_t keep) {
+  const uint32_t w[8] = {h.q0.x, h.q0.y, h.q0.z, h.q0.w, h.q1.x, h.q1.y, h.q1.z, h.q1.w};
+#pragma unroll
+  for (int k = 0; k < 32; ++k)
+    if ((uint32_t)k < e.len) o[k] = (uint8_t)(w[k >> 2] >> (8 * (k & 3)));
+  if (e.len > 32) {  // long strings: the rest, 16 bytes at a time
+    const uint4* q = reinterpret_cast<const uint4*>(pool + e.word_off);
+    for (uint32_t j = 32; j < e.len; j += 16) {
+      const uint4 v = ld_hint_v4(q + (j >> 4), keep);
+      const uint32_t x[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+      for (int k = 0; k < 16; ++k)
+        if (j + k < e.len) o[j + k] = (uint8_t)(x[k >> 2] >> (8 * (k & 3)));
+    }
   }
   return o + e.len;
 }
 
-__device__ uint8_t* json_write_record(const JsonParams& p, const JsonRecord& r, uint4 id, int64_t i, uint8_t* o) {
+__device__ uint8_t* json_write_record(const JsonParams& p, const JsonRecord& r, uint4 id, int64_t i, uint8_t* o,
+                                      const EscHead& h0, const EscHead& h1, const EscHead& h2, uint64_t keep) {
   *o++ = i == 0 ? '[' : ',';
   o = put_lit(o, 0, 11);
   const uint32_t w[4] = {id.x, id.y, id.z, id.w};  // canonical bytes 0..15 in memory order
@@ -428,15 +545,15 @@ __device__ uint8_t* json_write_record(const JsonParams& p, const JsonRecord& r, 
     *o++ = hex_lower(byte & 15);
   }
   o = put_lit(o, 11, 14);
-  o = put_esc(o, p.esc_pool[0], r.s[0]);
+  o = put_esc(o, p.esc_pool[0], r.s[0], h0, keep);
   o = put_lit(o, 25, 19);
-  o = put_esc(o, p.esc_pool[1], r.s[1]);
+  o = put_esc(o, p.esc_pool[1], r.s[1], h1, keep);
   o = put_lit(o, 44, 19);
   o += datetime_write(r.created, p.local_offset_min, o);
   o = put_lit(o, 63, 17);
   o += datetime_write(r.due, p.local_offset_min, o);
   o = put_lit(o, 80, 20);
-  o = put_esc(o, p.esc_pool[2], r.s[2]);
+  o = put_esc(o, p.esc_pool[2], r.s[2], h2, keep);
   o = put_lit(o, 100, 16);
   o = r.completed ? put_lit(o, 129, 4) : put_lit(o, 133, 5);
   o = put_lit(o, 116, 13);
@@ -453,23 +570,27 @@ __device__ uint8_t* json_write_record(const JsonParams& p, const JsonRecord& r, 
 __global__ void __launch_bounds__(kJsonThreads) json_emit_kernel(JsonParams p) {
   extern __shared__ __align__(16) uint8_t s_stage[];
   __shared__ uint32_t s_warp[32];
+  const uint64_t keep = l2_evict_last_policy(), stream = l2_evict_first_policy();
   const int64_t i = (int64_t)blockIdx.x * kJsonThreads + threadIdx.x;
-  const JsonRecord r = json_load(p, i);
+  const JsonRecord r = json_plan_load(p, i, stream);
   uint4 id = make_uint4(0, 0, 0, 0);
   if (r.live) id = p.ids[i];
+  // the strings' first 32 bytes are requested now and land while the CTA does its scan
+  const EscHead h0 = esc_prefetch(p.esc_pool[0], r.s[0], keep), h1 = esc_prefetch(p.esc_pool[1], r.s[1], keep),
+                h2 = esc_prefetch(p.esc_pool[2], r.s[2], keep);
   uint32_t total;
   const uint32_t local = block_exclusive_scan(json_record_len(p, r, i), s_warp, &total);
   const uint64_t base = p.block_base[blockIdx.x];
   const uint32_t shift = (uint32_t)(base & 15u);
   const bool staged = shift + total <= (uint32_t)kJsonStageBytes;
-  if (r.live) json_write_record(p, r, id, i, staged ? s_stage + shift + local : p.out + base + local);
+  if (r.live) json_write_record(p, r, id, i, staged ? s_stage + shift + local : p.out + base + local, h0, h1, h2, keep);
   if (!staged) return;
   __syncthreads();
   uint8_t* dst = p.out + (base - shift);
   const uint32_t lo = shift, hi = shift + total;
   for (uint32_t a = threadIdx.x * 16; a < hi; a += kJsonThreads * 16) {
     if (a >= lo && a + 16 <= hi) {
-      *reinterpret_cast<uint4*>(dst + a) = *reinterpret_cast<const uint4*>(s_stage + a);
+      st_hint_v4(reinterpret_cast<uint4*>(dst + a), *reinterpret_cast<const uint4*>(s_stage + a), stream);
     } else {
       for (uint32_t e = a > lo ? a : lo; e < a + 16 && e < hi; ++e) dst[e] = s_stage[e];
     }

@@ -146,6 +146,8 @@ struct tt_table {
   } esc[3][2];
   uint64_t* json_blocks = nullptr;  // K6 block sums / bases
   int64_t json_blocks_cap = 0;
+  uint64_t* json_plan = nullptr;    // K6 plan: 5 words per record, grow-only
+  int64_t json_plan_cap = 0;
   tt_json_stats last_json = {};
 };
 
@@ -220,8 +222,9 @@ void free_columns(tt_table* t) {
       e = tt_table::EscCache();
     }
   cudaFree(t->json_blocks);
-  t->json_blocks = nullptr;
-  t->json_blocks_cap = 0;
+  cudaFree(t->json_plan);
+  t->json_blocks = t->json_plan = nullptr;
+  t->json_blocks_cap = t->json_plan_cap = 0;
   t->due_code = t->completed = t->overdue = nullptr;
   t->creator_hash = nullptr;
   t->task_id = nullptr;
@@ -1995,7 +1998,21 @@ int32_t tt_result_json(tt_result* r, int32_t flavor, int32_t local_offset_min, t
     }
     t->json_blocks_cap = nb + 1;
   }
+  if (n > t->json_plan_cap) {
+    cudaFree(t->json_plan);
+    t->json_plan = nullptr;
+    t->json_plan_cap = 0;
+    const int64_t want = round_up(n, 1024);
+    cudaError_t e = cudaMalloc(&t->json_plan, (size_t)want * 5 * 8);
+    if (e != cudaSuccess) {
+      delete j;
+      TT_CUDA(e);
+    }
+    t->json_plan_cap = want;
+  }
   tt::JsonParams p = {};
+  p.plan = t->json_plan;
+  p.plan_stride = t->json_plan_cap;
   p.rows = r->d_rows;
   p.ids = r->d_ids;
   p.n = n;

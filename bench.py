@@ -49,7 +49,7 @@ def parse():
     ap.add_argument("--cpu-sample-rows", type=int, default=8_000_000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--workload", default="sweep", choices=["sweep", "sweep10m", "creator", "mixed"],
+    ap.add_argument("--workload", default="sweep", choices=["sweep", "sweep10m", "creator", "mixed", "json"],
                     help="sweep = the headline (BASELINE.json metric); the others are the remaining configs of "
                          "SURVEY.md 8(d): sweep10m = config 2, creator = config 4, mixed = config 5 (per GPU)")
     return ap.parse_args()
@@ -485,6 +485,67 @@ def run_extra(args):
                              "frac": n * 8 / (sc * 1e-3) / 1e9 / peak, "kernel": "tt::creator_scan_kernel<true>",
                              "algorithmic_bytes": n * 8, "note": "8 B/row hash column; inputs 800 MB >> L2"},
                 "batch": batch}
+        print(json.dumps(line))
+        table.close()
+        return
+
+    if args.workload == "json":
+        # GetYesterdaysDueTasks (STORE) over the 1 B-task table, then the list as the
+        # JSON text OverdueTasksController.Get sends.  CPU beside it: the oracle's System.Text.Json
+        # restatement over a sample of the same list, one thread (JsonSerializer is sequential).
+        n = args.rows
+        cfg = pkg.default_cfg(SEED, n)
+        table = pkg.TaskTable(local).generate(cfg, 0, n).generate_payload(cfg, 0)
+        res = table.get_yesterdays_due(tt.MODE_STORE)
+        size_ms, emit_ms, wall, nbytes = [], [], [], 0
+        host = None
+        for i in range(args.warmup + args.steps):
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            j = res.json(tt.JSON_RESPONSE)
+            dt = time.perf_counter() - t0
+            st = table.last_json_stats()
+            nbytes = j.size
+            if host is None:
+                host = torch.empty(nbytes, dtype=torch.uint8).pin_memory()
+            if i == args.warmup + args.steps - 1:
+                t1 = time.perf_counter()
+                j.copy_to(host.data_ptr())
+                d2h_ms = (time.perf_counter() - t1) * 1e3
+            j.free()
+            if i >= args.warmup:
+                size_ms.append(st.size_ms)
+                emit_ms.append(st.emit_ms)
+                wall.append(dt * 1e3)
+        text = bytes(host.numpy()[:2000])
+        tail = bytes(host.numpy()[-200:])
+        ok = text.startswith(b'[{"taskId":"') and tail.endswith(b'}]')
+        cpu = None
+        if not args.no_cpu_baseline:
+            from oracle import oracle as orc
+
+            sample_rows = 4_000_000
+            ot = orc.OracleTable()
+            ot.add_synth(orc.default_cfg(SEED, n), 0, sample_rows)
+            listed = ot.get_yesterdays_due(orc.MODE_STORE)
+            t0 = time.perf_counter()
+            ref_text = ot.to_json(listed, orc.JSON_RESPONSE)
+            cdt = time.perf_counter() - t0
+            cpu = {"value": listed.size / cdt, "unit": "records/s", "cores": 1, "kind": "port",
+                   "sample": f"{listed.size} records ({len(ref_text)} bytes) of the same list, oracle restatement of "
+                             "System.Text.Json, 1 thread", "MBps": len(ref_text) / cdt / 1e6}
+            ot.close()
+        em = med(emit_ms)
+        line = {"metric": "overdue_list_json_records_per_sec", "workload": f"GetYesterdaysDueTasks (STORE) over {n} tasks "
+                "as the JSON array of OverdueTasksController.Get (MVC encoder)", "value": res.count / (med(wall) * 1e-3),
+                "unit": "records/s", "records": res.count, "bytes": nbytes, "bytes_per_record": nbytes / max(res.count, 1),
+                "size_ms": med(size_ms), "emit_ms": em, "wall_ms": med(wall), "d2h_ms_pinned": d2h_ms, "well_formed_ends": ok,
+                "roofline": {"bound": "hbm", "achieved": nbytes / (em * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                             "frac": nbytes / (em * 1e-3) / 1e9 / peak, "kernel": "tt::json_emit_kernel",
+                             "algorithmic_bytes": nbytes,
+                             "note": "output bytes only; each record also costs ~7 scattered 64 B DRAM reads "
+                                     "(dates, refs, dictionary entries, escaped strings)"},
+                "cpu_baseline": cpu}
         print(json.dumps(line))
         table.close()
         return

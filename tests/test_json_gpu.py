@@ -116,7 +116,7 @@ def test_escaping_and_date_forms(oracle, offset):
 
 
 def test_pieces_larger_than_the_staging_area_are_written_directly(oracle):
-    """128 records of > 700 bytes each exceed the 56 KB a CTA stages in shared memory"""
+    """128 records of > 700 bytes each exceed the 44 KB a CTA stages in shared memory"""
     ot = nasty_table(oracle, 400, long_names=True)
     table = with_payload(ot, load_from_oracle(ot))
     res = table.get_yesterdays_due(tt.MODE_FAKE)
