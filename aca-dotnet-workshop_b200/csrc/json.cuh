@@ -74,7 +74,7 @@ __device__ __forceinline__ void st_hint_u64(uint64_t* p, uint64_t v, uint64_t po
 // ---- escaping one Unicode scalar -----------------------------------------------------------
 // Returns how a scalar is written: 0 = as is, 1 = backslash + *short_ch, 2 = \uXXXX,
 // 3 = \uXXXX\uXXXX (surrogate pair).  System.Text.Json's published rules (assumptions of record in
-// DESIGN.md §8): both encoders escape controls, '"' and '\\' and every supplementary-plane
+// DESIGN.md §7): both encoders escape controls, '"' and '\\' and every supplementary-plane
 // scalar; Default additionally escapes the HTML-sensitive ASCII characters and everything
 // outside Basic Latin; UnsafeRelaxed keeps BMP text except controls, separators (Zs other than
 // U+0020, Zl, Zp), private-use and non-characters.
