@@ -1,0 +1,573 @@
+// ingest.cuh — K7: bulk load of the state store's documents into the SoA table.
+//
+// The step right before the path.  The reference keeps every task as one JSON
+// document under the key TaskId.ToString() (Api/Services/TasksStoreManager.cs:35 SaveStateAsync) and
+// gets them back as TaskModel objects through System.Text.Json (GetStateAsync<TaskModel> :50,
+// QueryStateAsync<TaskModel> :61,130; the queue handler receives the same shape,
+// Svc/Controllers/ExternalTasksProcessorController.cs:29-33).  K7a restates that deserialisation
+// for TaskModel (Api/Models/TaskModel.cs:5-12) with one thread per document:
+//   * members in any order, any JSON whitespace between tokens, unknown members skipped (nested
+//     objects / arrays included), a repeated member keeps its last value, a missing one keeps the
+//     default (Guid.Empty, DateTime.MinValue, false, "");
+//   * member names compared ignoring ASCII case (JsonSerializerDefaults.Web), escapes allowed;
+//   * taskId: the "D" form, hex in either case;  isCompleted / isOverDue: true | false;
+//   * taskCreatedOn / taskDueDate: ISO 8601 extended as System.Text.Json reads it — date only, or
+//     date 'T' hh:mm[:ss[.f…]] with an optional 'Z' (Kind Utc) or ±hh[:mm] offset (converted to the
+//     machine's local time, Kind Local); no suffix = Kind Unspecified; fractions beyond 7 digits
+//     are truncated;
+//   * strings: every JSON escape including \uXXXX surrogate pairs, unescaped IN PLACE in the
+//     device copy of the text (unescaping only shrinks); null reads as "".
+// A document may carry one leading '[' or ',' and one trailing ',' or ']' so that a JSON array
+// split at its element boundaries (the offsets K6 hands out) loads as it is.
+// Anything else marks the document bad: the load reports the first bad document and changes
+// nothing.
+//
+// The three string members are then dictionary-encoded on the device: the documents are sorted
+// by the 64-bit hash of the (unescaped) string with the table's own radix sort, neighbours with
+// equal hash AND equal bytes share a dictionary entry (exact confirm, like the creator filter),
+// a scan numbers the entries, and the refs are scattered back to document order.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/tt_synth.h"
+#include "json.cuh"
+#include "radix.cuh"
+#include "tt_bits.h"
+
+namespace tt {
+
+constexpr uint32_t kDocOk = 0;
+constexpr uint32_t kDocSyntax = 1;  // not the JSON object shape described above
+constexpr uint32_t kDocGuid = 2;    // taskId is not a "D" Guid
+constexpr uint32_t kDocDate = 3;    // a date System.Text.Json would reject
+constexpr uint32_t kDocString = 4;  // bad escape, raw control character or malformed UTF-8 in a string
+constexpr uint32_t kDocType = 5;    // a known member with a value of the wrong type
+
+struct DocCols {
+  uint4* id;
+  uint64_t* created;
+  uint64_t* due;
+  uint8_t* flags;  // bit 0 IsCompleted, bit 1 IsOverDue
+  uint64_t* str_start[3];  // 0 TaskName, 1 TaskCreatedBy, 2 TaskAssignedTo: offset of the unescaped bytes in the text
+  uint32_t* str_len[3];
+  uint64_t* str_hash[3];   // tt_hash64 of the unescaped bytes
+  uint32_t* status;
+};
+
+__device__ __forceinline__ bool is_ws(uint32_t c) { return c == ' ' || c == '\t' || c == '\n' || c == '\r'; }
+
+__device__ __forceinline__ const uint8_t* skip_ws(const uint8_t* p, const uint8_t* end) {
+  while (p < end && is_ws(*p)) ++p;
+  return p;
+}
+
+__device__ __forceinline__ int hex_val(uint32_t c) {
+  if (c >= '0' && c <= '9') return (int)c - '0';
+  c |= 0x20;
+  if (c >= 'a' && c <= 'f') return (int)c - 'a' + 10;
+  return -1;
+}
+
+// \uXXXX at r (after the 'u'); returns the code unit or -1
+__device__ __forceinline__ int read_u4(const uint8_t* r, const uint8_t* end) {
+  if (end - r < 4) return -1;
+  int v = 0;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const int h = hex_val(r[k]);
+    if (h < 0) return -1;
+    v = (v << 4) | h;
+  }
+  return v;
+}
+
+// One (possibly escaped) scalar of a JSON string starting at r (not the closing quote).  Writes its
+// UTF-8 bytes to out[0..*nout) and returns the pointer after it, or nullptr (bad string).
+__device__ const uint8_t* read_string_scalar(const uint8_t* r, const uint8_t* end, uint8_t* out, int* nout) {
+  uint32_t c = *r++;
+  if (c < 0x20) return nullptr;
+  if (c != '\\') {
+    int extra = 0;
+    if (c >= 0x80) {
+      if ((c >> 5) == 6) extra = 1;
+      else if ((c >> 4) == 14) extra = 2;
+      else if ((c >> 3) == 30) extra = 3;
+      else return nullptr;
+      if (end - r < extra) return nullptr;
+    }
+    out[0] = (uint8_t)c;
+    for (int j = 0; j < extra; ++j) {
+      const uint32_t d = r[j];
+      if ((d >> 6) != 2) return nullptr;
+      out[1 + j] = (uint8_t)d;
+    }
+    *nout = 1 + extra;
+    return r + extra;
+  }
+  if (r >= end) return nullptr;
+  c = *r++;
+  uint32_t cp;
+  switch (c) {
+    case '"': cp = '"'; break;
+    case '\\': cp = '\\'; break;
+    case '/': cp = '/'; break;
+    case 'b': cp = 8; break;
+    case 'f': cp = 12; break;
+    case 'n': cp = 10; break;
+    case 'r': cp = 13; break;
+    case 't': cp = 9; break;
+    case 'u': {
+      int u = read_u4(r, end);
+      if (u < 0) return nullptr;
+      r += 4;
+      cp = (uint32_t)u;
+      if (cp >= 0xD800 && cp <= 0xDBFF) {  // high surrogate: the low one must follow as \uXXXX
+        if (end - r < 6 || r[0] != '\\' || r[1] != 'u') return nullptr;
+        const int lo = read_u4(r + 2, end);
+        if (lo < 0xDC00 || lo > 0xDFFF) return nullptr;
+        r += 6;
+        cp = 0x10000 + ((cp - 0xD800) << 10) + ((uint32_t)lo - 0xDC00);
+      } else if (cp >= 0xDC00 && cp <= 0xDFFF) {
+        return nullptr;
+      }
+      break;
+    }
+    default: return nullptr;
+  }
+  if (cp < 0x80) { out[0] = (uint8_t)cp; *nout = 1; }
+  else if (cp < 0x800) { out[0] = (uint8_t)(0xC0 | (cp >> 6)); out[1] = (uint8_t)(0x80 | (cp & 0x3F)); *nout = 2; }
+  else if (cp < 0x10000) {
+    out[0] = (uint8_t)(0xE0 | (cp >> 12)); out[1] = (uint8_t)(0x80 | ((cp >> 6) & 0x3F)); out[2] = (uint8_t)(0x80 | (cp & 0x3F));
+    *nout = 3;
+  } else {
+    out[0] = (uint8_t)(0xF0 | (cp >> 18)); out[1] = (uint8_t)(0x80 | ((cp >> 12) & 0x3F));
+    out[2] = (uint8_t)(0x80 | ((cp >> 6) & 0x3F)); out[3] = (uint8_t)(0x80 | (cp & 0x3F));
+    *nout = 4;
+  }
+  return r;
+}
+
+// A string value, unescaped in place.  p = first byte after the opening quote.  Returns the
+// pointer after the closing quote (nullptr = bad string); [*start, *start + *len) holds the bytes.
+__device__ const uint8_t* read_string_inplace(uint8_t* p, const uint8_t* end, uint8_t** start, uint32_t* len) {
+  const uint8_t* r = p;
+  uint8_t* w = p;
+  while (true) {
+    if (r >= end) return nullptr;
+    if (*r == '"') break;
+    uint8_t tmp[4];
+    int n = 0;
+    const uint8_t* nr = read_string_scalar(r, end, tmp, &n);
+    if (!nr) return nullptr;
+    if (w != r || *r == '\\')  // nothing moves until the first escape has been seen
+      for (int j = 0; j < n; ++j) w[j] = tmp[j];
+    w += n;
+    r = nr;
+  }
+  *start = p;
+  *len = (uint32_t)(w - p);
+  return r + 1;
+}
+
+// A short string (member name, Guid, date) unescaped into a local buffer.  *len = cap + 1 when it
+// does not fit.  Returns the pointer after the closing quote, nullptr = bad string.
+template <int CAP>
+__device__ const uint8_t* read_string_local(const uint8_t* p, const uint8_t* end, uint8_t (&buf)[CAP], int* len) {
+  const uint8_t* r = p;
+  int n = 0;
+  while (true) {
+    if (r >= end) return nullptr;
+    if (*r == '"') break;
+    uint8_t tmp[4];
+    int k = 0;
+    r = read_string_scalar(r, end, tmp, &k);
+    if (!r) return nullptr;
+    for (int j = 0; j < k; ++j) {
+      if (n < CAP) buf[n] = tmp[j];
+      ++n;
+    }
+  }
+  *len = n > CAP ? CAP + 1 : n;
+  return r + 1;
+}
+
+// Skips any JSON value structurally (strings with their escapes, nesting by depth).
+__device__ const uint8_t* skip_value(const uint8_t* p, const uint8_t* end) {
+  int depth = 0;
+  while (p < end) {
+    const uint32_t c = *p;
+    if (c == '"') {
+      ++p;
+      while (true) {
+        if (p >= end) return nullptr;
+        const uint32_t d = *p++;
+        if (d == '"') break;
+        if (d == '\\') {
+          if (p >= end) return nullptr;
+          ++p;
+        }
+      }
+      if (depth == 0) return p;
+    } else if (c == '{' || c == '[') {
+      ++depth;
+      ++p;
+    } else if (c == '}' || c == ']') {
+      if (depth == 0) return nullptr;
+      ++p;
+      if (--depth == 0) return p;
+    } else if (depth == 0) {
+      // number or literal: runs to the next delimiter
+      const uint8_t* q = p;
+      while (q < end && !is_ws(*q) && *q != ',' && *q != '}' && *q != ']') ++q;
+      return q == p ? nullptr : q;
+    } else {
+      ++p;
+    }
+  }
+  return nullptr;
+}
+
+__device__ __forceinline__ bool lit_eq(const uint8_t* p, const uint8_t* end, const char* lit, int n) {
+  if (end - p < n) return false;
+  for (int j = 0; j < n; ++j)
+    if (p[j] != (uint8_t)lit[j]) return false;
+  return true;
+}
+
+// 0 taskId, 1 taskName, 2 taskCreatedBy, 3 taskCreatedOn, 4 taskDueDate, 5 taskAssignedTo,
+// 6 isCompleted, 7 isOverDue, -1 unknown.  ASCII case-insensitive.
+__device__ int member_of(const uint8_t* name, int len) {
+  const char* names[8] = {"taskid", "taskname", "taskcreatedby", "taskcreatedon", "taskduedate", "taskassignedto",
+                          "iscompleted", "isoverdue"};
+  const int lens[8] = {6, 8, 13, 13, 11, 14, 11, 9};
+  for (int m = 0; m < 8; ++m) {
+    if (lens[m] != len) continue;
+    bool same = true;
+    for (int j = 0; j < len && same; ++j) {
+      uint32_t c = name[j];
+      if (c >= 'A' && c <= 'Z') c |= 0x20;
+      same = c == (uint8_t)names[m][j];
+    }
+    if (same) return m;
+  }
+  return -1;
+}
+
+// "xxxxxxxx-xxxx-xxxx-xxxx-xxxxxxxxxxxx" -> the 16 canonical bytes packed in memory order
+__device__ bool parse_guid(const uint8_t* s, int len, uint4* out) {
+  if (len != 36) return false;
+  uint32_t w[4] = {0, 0, 0, 0};
+  int b = 0;
+  for (int i = 0; i < 36;) {
+    if (i == 8 || i == 13 || i == 18 || i == 23) {
+      if (s[i] != '-') return false;
+      ++i;
+      continue;
+    }
+    const int hi = hex_val(s[i]), lo = hex_val(s[i + 1]);
+    if (hi < 0 || lo < 0) return false;
+    w[b >> 2] |= (uint32_t)((hi << 4) | lo) << (8 * (b & 3));
+    ++b;
+    i += 2;
+  }
+  *out = make_uint4(w[0], w[1], w[2], w[3]);
+  return true;
+}
+
+__device__ __forceinline__ int two_digits(const uint8_t* s) {
+  const int a = (int)s[0] - '0', b = (int)s[1] - '0';
+  if (a < 0 || a > 9 || b < 0 || b > 9) return -1;
+  return a * 10 + b;
+}
+
+// System.Text.Json's DateTime reader (ISO 8601-1 extended profile), see the header comment.
+__device__ bool parse_datetime(const uint8_t* s, int len, int32_t local_offset_min, uint64_t* raw) {
+  if (len < 10 || len > 48) return false;
+  const int yh = two_digits(s), yl = two_digits(s + 2), mo = two_digits(s + 5), d = two_digits(s + 8);
+  if (yh < 0 || yl < 0 || mo < 0 || d < 0 || s[4] != '-' || s[7] != '-') return false;
+  const int y = yh * 100 + yl;
+  if (y < 1 || mo < 1 || mo > 12 || d < 1) return false;
+  const bool leap = (y % 4 == 0 && y % 100 != 0) || y % 400 == 0;
+  const int dim = mo == 2 ? (leap ? 29 : 28) : (mo == 4 || mo == 6 || mo == 9 || mo == 11) ? 30 : 31;
+  if (d > dim) return false;
+  // days since 0001-01-01 (proleptic Gregorian)
+  const int yy = mo <= 2 ? y - 1 : y;
+  const int era = yy / 400;
+  const int yoe = yy - era * 400;
+  const int doy = (153 * (mo + (mo > 2 ? -3 : 9)) + 2) / 5 + d - 1;
+  const int doe = yoe * 365 + yoe / 4 - yoe / 100 + doy;
+  const int64_t days = (int64_t)era * 146097 + doe - 306;
+  int64_t ticks = days * 864000000000ll;
+  uint32_t kind = 0;
+  int i = 10;
+  if (i < len) {
+    if (s[i] != 'T' || len < 16) return false;
+    const int hh = two_digits(s + 11), mi = two_digits(s + 14);
+    if (hh < 0 || hh > 23 || mi < 0 || mi > 59 || s[13] != ':') return false;
+    int ss = 0;
+    int64_t frac = 0;
+    i = 16;
+    if (i < len && s[i] == ':') {
+      if (len < 19) return false;
+      ss = two_digits(s + 17);
+      if (ss < 0 || ss > 59) return false;
+      i = 19;
+      if (i < len && (s[i] == '.' || s[i] == ',')) {
+        ++i;
+        int nd = 0;
+        while (i < len && s[i] >= '0' && s[i] <= '9') {
+          if (nd < 7) frac = frac * 10 + (s[i] - '0');
+          ++nd;
+          ++i;
+        }
+        if (nd == 0 || nd > 16) return false;
+        for (; nd < 7; ++nd) frac *= 10;
+      }
+    }
+    ticks += ((int64_t)hh * 3600 + mi * 60 + ss) * 10000000ll + frac;
+    if (i < len) {
+      if (s[i] == 'Z') {
+        kind = 1;
+        ++i;
+      } else if (s[i] == '+' || s[i] == '-') {
+        const bool neg = s[i] == '-';
+        if (len - i < 3) return false;
+        const int oh = two_digits(s + i + 1);
+        int om = 0;
+        i += 3;
+        if (i < len) {
+          if (s[i] != ':' || len - i < 3) return false;
+          om = two_digits(s + i + 1);
+          i += 3;
+        }
+        if (oh < 0 || oh > 14 || om < 0 || om > 59) return false;
+        const int off = (oh * 60 + om) * (neg ? -1 : 1);
+        // the instant, shown on the machine's local clock (DateTimeOffset.LocalDateTime), Kind Local
+        ticks += (int64_t)(local_offset_min - off) * 600000000ll;
+        kind = 2;
+      }
+      if (i != len) return false;
+    }
+  }
+  if (ticks < 0 || ticks > 3155378975999999999ll) return false;
+  *raw = (uint64_t)ticks | ((uint64_t)kind << 62);
+  return true;
+}
+
+// K7a: one thread per document.
+__global__ void __launch_bounds__(128) doc_parse_kernel(uint8_t* text, const uint64_t* doc_off, int64_t n,
+                                                        int32_t local_offset_min, DocCols out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  uint8_t* const base = text;
+  const uint8_t* p = text + doc_off[i];
+  const uint8_t* const end = text + doc_off[i + 1];
+  uint4 id = make_uint4(0, 0, 0, 0);
+  uint64_t created = 0, due = 0;
+  uint32_t flags = 0;
+  uint8_t* sstart[3] = {base, base, base};
+  uint32_t slen[3] = {0, 0, 0};
+  uint32_t status = kDocOk;
+
+  p = skip_ws(p, end);
+  if (p < end && (*p == '[' || *p == ',')) p = skip_ws(p + 1, end);
+  if (p >= end || *p != '{') status = kDocSyntax;
+  else ++p;
+  bool first = true;
+  while (status == kDocOk) {
+    p = skip_ws(p, end);
+    if (p >= end) { status = kDocSyntax; break; }
+    if (*p == '}') { ++p; break; }
+    if (!first) {
+      if (*p != ',') { status = kDocSyntax; break; }
+      p = skip_ws(p + 1, end);
+      if (p >= end) { status = kDocSyntax; break; }
+    }
+    first = false;
+    if (*p != '"') { status = kDocSyntax; break; }
+    uint8_t name[16];
+    int nlen = 0;
+    p = read_string_local(p + 1, end, name, &nlen);
+    if (!p) { status = kDocString; break; }
+    const int m = nlen <= 16 ? member_of(name, nlen) : -1;
+    p = skip_ws(p, end);
+    if (p >= end || *p != ':') { status = kDocSyntax; break; }
+    p = skip_ws(p + 1, end);
+    if (p >= end) { status = kDocSyntax; break; }
+    if (m < 0) {
+      p = skip_value(p, end);
+      if (!p) status = kDocSyntax;
+      continue;
+    }
+    if (m == 6 || m == 7) {
+      const uint32_t bit = m == 6 ? 1u : 2u;
+      if (lit_eq(p, end, "true", 4)) { flags |= bit; p += 4; }
+      else if (lit_eq(p, end, "false", 5)) { flags &= ~bit; p += 5; }
+      else status = kDocType;
+      continue;
+    }
+    if (m == 1 || m == 2 || m == 5) {
+      const int c = m == 1 ? 0 : m == 2 ? 1 : 2;
+      if (lit_eq(p, end, "null", 4)) { slen[c] = 0; sstart[c] = base; p += 4; continue; }
+      if (*p != '"') { status = kDocType; continue; }
+      p = read_string_inplace(const_cast<uint8_t*>(p) + 1, end, &sstart[c], &slen[c]);
+      if (!p) status = kDocString;
+      continue;
+    }
+    // taskId and the two dates: short strings parsed from a local copy
+    if (*p != '"') { status = kDocType; continue; }
+    uint8_t buf[48];
+    int blen = 0;
+    p = read_string_local(p + 1, end, buf, &blen);
+    if (!p) { status = kDocString; continue; }
+    if (m == 0) {
+      if (!parse_guid(buf, blen, &id)) status = kDocGuid;
+    } else {
+      uint64_t raw = 0;
+      if (blen > 48 || !parse_datetime(buf, blen, local_offset_min, &raw)) status = kDocDate;
+      else if (m == 3) created = raw;
+      else due = raw;
+    }
+  }
+  if (status == kDocOk) {
+    p = skip_ws(p, end);
+    if (p < end && (*p == ',' || *p == ']')) p = skip_ws(p + 1, end);
+    if (p != end) status = kDocSyntax;
+  }
+  out.status[i] = status;
+  out.id[i] = id;
+  out.created[i] = created;
+  out.due[i] = due;
+  out.flags[i] = (uint8_t)flags;
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    out.str_start[c][i] = (uint64_t)(sstart[c] - base);
+    out.str_len[c][i] = slen[c];
+    out.str_hash[c][i] = status == kDocOk ? tt_hash64(sstart[c], slen[c]) : 0ull;
+  }
+}
+
+// first bad document: err[0] = min index (init ~0), err[1] = its reason (written by the owner of the min in a second pass)
+__global__ void doc_first_bad_kernel(const uint32_t* status, int64_t n, unsigned long long* err) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n && status[i] != kDocOk) atomicMin(err, (unsigned long long)i);
+}
+
+// The fixed-width columns of the table from the parsed documents (a warp covers one flag word).
+__global__ void doc_fill_kernel(DocCols d, int64_t n, uint32_t* due_code, uint32_t* completed, uint32_t* overdue,
+                                uint64_t* creator_hash, uint4* task_id, uint64_t* created_raw, uint64_t* due_raw) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const bool live = i < n;
+  uint32_t f = 0;
+  if (live) {
+    f = d.flags[i];
+    const uint64_t du = d.due[i];
+    due_code[i] = tt_pack_due(du);
+    due_raw[i] = du;
+    created_raw[i] = d.created[i];
+    task_id[i] = d.id[i];
+    creator_hash[i] = d.str_hash[1][i];
+  }
+  const uint32_t cw = __ballot_sync(0xFFFFFFFFu, f & 1u), ow = __ballot_sync(0xFFFFFFFFu, f & 2u);
+  if ((threadIdx.x & 31) == 0 && i < ((n + 31) & ~31ll)) {
+    completed[i >> 5] = cw;
+    overdue[i >> 5] = ow;
+  }
+}
+
+// rows whose TaskId is not above the previous row's (0 everywhere = the table is in TaskId order)
+__global__ void doc_id_order_kernel(const uint4* id, int64_t n, unsigned long long* out_of_order) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < 1 || i >= n) return;
+  const uint4 a = id[i - 1], b = id[i];
+  const uint32_t x[4] = {a.x, a.y, a.z, a.w}, y[4] = {b.x, b.y, b.z, b.w};
+  int cmp = 0;
+  for (int k = 0; k < 4 && cmp == 0; ++k) {
+    const uint32_t u = __byte_perm(x[k], 0, 0x0123), v = __byte_perm(y[k], 0, 0x0123);  // canonical order is big-endian
+    cmp = u < v ? -1 : u > v ? 1 : 0;
+  }
+  if (cmp >= 0) atomicAdd(out_of_order, 1ull);
+}
+
+// ---- dictionary encoding of one string member ------------------------------------------------
+__global__ void dict_keys_kernel(const uint64_t* hash, int64_t n, unsigned long long* keys, uint32_t* vals) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) {
+    keys[i] = hash[i];
+    vals[i] = (uint32_t)i;
+  }
+}
+
+__device__ __forceinline__ bool same_string(const uint8_t* text, uint64_t a, uint32_t la, uint64_t b, uint32_t lb) {
+  if (la != lb) return false;
+  for (uint32_t j = 0; j < la; ++j)
+    if (text[a + j] != text[b + j]) return false;
+  return true;
+}
+
+// position `pos` of the hash-sorted order starts a new dictionary entry unless its string equals
+// its left neighbour's (hash first, then length and bytes)
+__device__ __forceinline__ uint32_t dict_is_head(const unsigned long long* keys, const uint32_t* docs, const uint8_t* text,
+                                                 const uint64_t* start, const uint32_t* len, int64_t pos) {
+  if (pos == 0) return 1u;
+  if (keys[pos] != keys[pos - 1]) return 1u;
+  const uint32_t a = docs[pos - 1], b = docs[pos];
+  return same_string(text, start[a], len[a], start[b], len[b]) ? 0u : 1u;
+}
+
+__global__ void __launch_bounds__(kScanBlock) dict_head_sum_kernel(const unsigned long long* keys, const uint32_t* docs,
+                                                                   const uint8_t* text, const uint64_t* start,
+                                                                   const uint32_t* len, int64_t n, uint64_t* block_sum) {
+  __shared__ uint32_t s_warp[32];
+  const int64_t pos = (int64_t)blockIdx.x * kScanBlock + threadIdx.x;
+  const uint32_t h = pos < n ? dict_is_head(keys, docs, text, start, len, pos) : 0u;
+  uint32_t tot;
+  block_exclusive_scan(h, s_warp, &tot);
+  if (threadIdx.x == 0) block_sum[blockIdx.x] = tot;
+}
+
+// entry number of every position; ref[doc] = entry; the head of an entry records its document
+__global__ void __launch_bounds__(kScanBlock) dict_assign_kernel(const unsigned long long* keys, const uint32_t* docs,
+                                                                 const uint8_t* text, const uint64_t* start,
+                                                                 const uint32_t* len, int64_t n, const uint64_t* block_base,
+                                                                 uint32_t* ref, uint32_t* entry_doc) {
+  __shared__ uint32_t s_warp[32];
+  const int64_t pos = (int64_t)blockIdx.x * kScanBlock + threadIdx.x;
+  const uint32_t h = pos < n ? dict_is_head(keys, docs, text, start, len, pos) : 0u;
+  const uint32_t before = block_exclusive_scan(h, s_warp, nullptr);
+  if (pos >= n) return;
+  const uint32_t entry = (uint32_t)block_base[blockIdx.x] + before + h - 1u;
+  const uint32_t doc = docs[pos];
+  ref[doc] = entry;
+  if (h) entry_doc[entry] = doc;
+}
+
+__global__ void __launch_bounds__(kScanBlock) dict_len_sum_kernel(const uint32_t* entry_doc, const uint32_t* len, uint32_t k,
+                                                                  uint64_t* block_sum) {
+  __shared__ uint32_t s_warp[32];
+  const uint32_t e = blockIdx.x * kScanBlock + threadIdx.x;
+  const uint32_t l = e < k ? len[entry_doc[e]] : 0u;
+  uint32_t tot;
+  block_exclusive_scan(l, s_warp, &tot);
+  if (threadIdx.x == 0) block_sum[blockIdx.x] = tot;
+}
+
+// off[e] for every entry (off[k] = total is written by the host) and the bytes of the pool
+__global__ void __launch_bounds__(kScanBlock) dict_build_kernel(const uint32_t* entry_doc, const uint64_t* start,
+                                                                const uint32_t* len, const uint8_t* text, uint32_t k,
+                                                                const uint64_t* block_base, uint32_t* off, uint8_t* pool) {
+  __shared__ uint32_t s_warp[32];
+  const uint32_t e = blockIdx.x * kScanBlock + threadIdx.x;
+  const uint32_t doc = e < k ? entry_doc[e] : 0u;
+  const uint32_t l = e < k ? len[doc] : 0u;
+  const uint32_t before = block_exclusive_scan(l, s_warp, nullptr);
+  if (e >= k) return;
+  const uint32_t o = (uint32_t)block_base[blockIdx.x] + before;
+  off[e] = o;
+  const uint8_t* src = text + start[doc];
+  for (uint32_t j = 0; j < l; ++j) pool[o + j] = src[j];
+}
+
+}  // namespace tt

@@ -328,6 +328,7 @@ struct JsonParams {
   uint64_t* block_base;      // [blocks + 1]
   uint64_t* plan;            // [5][plan_stride]: what K6a gathered for every record, read back by K6b
   int64_t plan_stride;
+  uint64_t* rec_off;         // [n]: where every record's piece starts in the text (may be null)
   uint8_t* out;
 };
 
@@ -583,6 +584,7 @@ __global__ void __launch_bounds__(kJsonThreads) json_emit_kernel(JsonParams p) {
   const uint64_t base = p.block_base[blockIdx.x];
   const uint32_t shift = (uint32_t)(base & 15u);
   const bool staged = shift + total <= (uint32_t)kJsonStageBytes;
+  if (r.live && p.rec_off) st_hint_u64(p.rec_off + i, base + local, stream);
   if (r.live) json_write_record(p, r, id, i, staged ? s_stage + shift + local : p.out + base + local, h0, h1, h2, keep);
   if (!staged) return;
   __syncthreads();

@@ -20,6 +20,7 @@
 
 #include "../../include/tasktable.h"
 #include "creator.cuh"
+#include "ingest.cuh"
 #include "json.cuh"
 #include "order.cuh"
 #include "point.cuh"
@@ -1782,6 +1783,8 @@ struct tt_json {
   std::shared_ptr<TableCore> core;
   uint8_t* d_text = nullptr;
   int64_t bytes = 0;
+  uint64_t* d_off = nullptr;  // [records + 1]
+  int64_t records = 0;
 };
 
 namespace {
@@ -2048,8 +2051,11 @@ int32_t tt_result_json(tt_result* r, int32_t flavor, int32_t local_offset_min, t
   if (e == cudaSuccess) e = cudaMemcpyAsync(&total, t->json_blocks + nb, 8, cudaMemcpyDeviceToHost, t->stream);
   if (e == cudaSuccess) e = cudaStreamSynchronize(t->stream);
   if (e == cudaSuccess) e = cudaMalloc(&j->d_text, (size_t)total + 16);
+  if (e == cudaSuccess) e = cudaMalloc(&j->d_off, ((size_t)n + 1) * 8);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(j->d_off + n, &total, 8, cudaMemcpyHostToDevice, t->stream);
   if (e == cudaSuccess) {
     p.out = j->d_text;
+    p.rec_off = j->d_off;
     tt::json_emit_kernel<<<(unsigned)nb, tt::kJsonThreads, tt::kJsonStageBytes, t->stream>>>(p);
     e = cudaGetLastError();
   }
@@ -2057,10 +2063,12 @@ int32_t tt_result_json(tt_result* r, int32_t flavor, int32_t local_offset_min, t
   if (e == cudaSuccess) e = cudaStreamSynchronize(t->stream);
   if (e != cudaSuccess) {
     cudaFree(j->d_text);
+    cudaFree(j->d_off);
     delete j;
     TT_CUDA(e);
   }
   j->bytes = (int64_t)total;
+  j->records = n;
   cudaEventElapsedTime(&t->last_json.size_ms, t->ev0, t->ev1);
   cudaEventElapsedTime(&t->last_json.emit_ms, t->ev1, t->ev2);
   t->last_json.bytes = j->bytes;
@@ -2089,11 +2097,24 @@ int32_t tt_json_device(tt_json* j, const void** d_text) {
   return TT_OK;
 }
 
+int32_t tt_json_offsets(tt_json* j, uint64_t* dst) {
+  if (!j || !dst) return fail(TT_ERR_ARG, "null argument");
+  DeviceGuard g(j->core->device);
+  if (j->records == 0) {  // "[]": no records, off[0] = the length of the text
+    const uint64_t len = (uint64_t)j->bytes;
+    TT_CUDA(cudaMemcpy(dst, &len, 8, cudaMemcpyDefault));
+    return TT_OK;
+  }
+  TT_CUDA(cudaMemcpy(dst, j->d_off, ((size_t)j->records + 1) * 8, cudaMemcpyDefault));
+  return TT_OK;
+}
+
 int32_t tt_json_free(tt_json* j) {
   if (!j) return TT_OK;
   {
     DeviceGuard g(j->core->device);
     cudaFree(j->d_text);
+    cudaFree(j->d_off);
   }
   delete j;
   return TT_OK;
@@ -2107,6 +2128,256 @@ int32_t tt_last_json_stats(tt_table* t, tt_json_stats* out) {
 }
 
 }  // extern "C"
+
+// ---- bulk load of JSON documents (K7, csrc/ingest.cuh) ---------------------------------------------
+
+namespace {
+
+// Everything tt_load_documents allocates besides the table itself; freed on every exit path.
+struct IngestScratch {
+  std::vector<void*> blocks;
+  template <typename T>
+  cudaError_t get(T** p, size_t count) {
+    void* q = nullptr;
+    cudaError_t e = cudaMalloc(&q, std::max<size_t>(count * sizeof(T), 16));
+    if (e == cudaSuccess) blocks.push_back(q);
+    *p = static_cast<T*>(q);
+    return e;
+  }
+  ~IngestScratch() {
+    for (void* b : blocks) cudaFree(b);
+  }
+};
+
+// Dictionary-encodes one string member of the parsed documents: ref[doc] and a fresh dictionary
+// (off / pool, allocated here and handed to the caller).
+int32_t encode_member(tt_table* t, IngestScratch& sc, const tt::DocCols& d, int c, const uint8_t* text, int64_t n,
+                      uint32_t* ref_out, uint32_t** off_out, uint8_t** pool_out, uint32_t* k_out, uint64_t* bytes_out,
+                      int* launches) {
+  cudaStream_t st = t->stream;
+  cudaError_t e = t->sort.reserve(n);
+  if (e != cudaSuccess) TT_CUDA(e);
+  tt::dict_keys_kernel<<<grid_for(n, 256), 256, 0, st>>>(d.str_hash[c], n, t->sort.keys[0], t->sort.vals[0]);
+  int w = 0;
+  e = tt::radix_sort_pairs(st, t->sort, n, 64, &w);
+  if (e != cudaSuccess) TT_CUDA(e);
+  const unsigned long long* keys = t->sort.keys[w];
+  const uint32_t* docs = t->sort.vals[w];
+  const uint32_t nb = (uint32_t)((n + tt::kScanBlock - 1) / tt::kScanBlock);
+  uint64_t* blocks = nullptr;
+  uint32_t* entry_doc = nullptr;
+  TT_CUDA(sc.get(&blocks, (size_t)nb + 1));
+  TT_CUDA(sc.get(&entry_doc, (size_t)n));
+  tt::dict_head_sum_kernel<<<nb, tt::kScanBlock, 0, st>>>(keys, docs, text, d.str_start[c], d.str_len[c], n, blocks);
+  tt::scan_block_sums_kernel<<<1, 1024, 0, st>>>(blocks, nb);
+  tt::dict_assign_kernel<<<nb, tt::kScanBlock, 0, st>>>(keys, docs, text, d.str_start[c], d.str_len[c], n, blocks, ref_out,
+                                                         entry_doc);
+  uint64_t k64 = 0;
+  TT_CUDA(cudaGetLastError());
+  TT_CUDA(cudaMemcpyAsync(&k64, blocks + nb, 8, cudaMemcpyDeviceToHost, st));
+  TT_CUDA(cudaStreamSynchronize(st));
+  const uint32_t k = (uint32_t)k64;
+  const uint32_t kb = (k + tt::kScanBlock - 1) / tt::kScanBlock;
+  uint64_t* lblocks = nullptr;
+  TT_CUDA(sc.get(&lblocks, (size_t)kb + 1));
+  tt::dict_len_sum_kernel<<<kb, tt::kScanBlock, 0, st>>>(entry_doc, d.str_len[c], k, lblocks);
+  tt::scan_block_sums_kernel<<<1, 1024, 0, st>>>(lblocks, kb);
+  uint64_t bytes = 0;
+  TT_CUDA(cudaGetLastError());
+  TT_CUDA(cudaMemcpyAsync(&bytes, lblocks + kb, 8, cudaMemcpyDeviceToHost, st));
+  TT_CUDA(cudaStreamSynchronize(st));
+  if (bytes >= (1ull << 32)) return fail(TT_ERR_ARG, "the distinct strings of one member exceed 4 GB");
+  uint32_t* off = nullptr;
+  uint8_t* pool = nullptr;
+  TT_CUDA(cudaMalloc(&off, ((size_t)k + 1) * 4));
+  cudaError_t e2 = cudaMalloc(&pool, std::max<uint64_t>(bytes, 16));
+  if (e2 != cudaSuccess) {
+    cudaFree(off);
+    TT_CUDA(e2);
+  }
+  tt::dict_build_kernel<<<kb, tt::kScanBlock, 0, st>>>(entry_doc, d.str_start[c], d.str_len[c], text, k, lblocks, off, pool);
+  const uint32_t total32 = (uint32_t)bytes;
+  e2 = cudaGetLastError();
+  if (e2 == cudaSuccess) e2 = cudaMemcpyAsync(off + k, &total32, 4, cudaMemcpyHostToDevice, st);
+  if (e2 == cudaSuccess) e2 = cudaStreamSynchronize(st);
+  if (e2 != cudaSuccess) {
+    cudaFree(off);
+    cudaFree(pool);
+    TT_CUDA(e2);
+  }
+  *off_out = off;
+  *pool_out = pool;
+  *k_out = k;
+  *bytes_out = bytes;
+  *launches += 7 + 4 * 8;
+  return TT_OK;
+}
+
+}  // namespace
+
+extern "C" int32_t tt_load_documents(tt_table* t, const void* docs, const uint64_t* doc_off, int64_t n,
+                                     int32_t local_offset_min, tt_ingest_stats* stats) {
+  if (!t || n < 0 || (n > 0 && (!docs || !doc_off))) return fail(TT_ERR_ARG, "bad argument");
+  if (local_offset_min <= -24 * 60 || local_offset_min >= 24 * 60) return fail(TT_ERR_ARG, "local_offset_min out of range");
+  tt_ingest_stats local_stats;
+  if (!stats) stats = &local_stats;
+  memset(stats, 0, sizeof *stats);
+  stats->first_bad = -1;
+  for (int64_t i = 0; i < n; ++i)
+    if (doc_off[i + 1] < doc_off[i]) return fail(TT_ERR_ARG, "doc_off not ascending at %lld", (long long)i);
+  std::lock_guard<std::mutex> lk(t->mu);
+  DeviceGuard g(t->device);
+  if (t->n_pad != 0) return fail(TT_ERR_STATE, "table already holds %lld rows", (long long)t->n);
+  if (n > kMaxRows) return fail(TT_ERR_ARG, "row count %lld outside [0, 2^31]", (long long)n);
+  cudaStream_t st = t->stream;
+  IngestScratch sc;
+  const uint64_t first = n ? doc_off[0] : 0, bytes = n ? doc_off[n] - first : 0;
+  uint8_t* text = nullptr;
+  uint64_t* d_off = nullptr;
+  tt::DocCols d = {};
+  unsigned long long* d_err = nullptr;
+  TT_CUDA(sc.get(&text, (size_t)bytes + 16));
+  TT_CUDA(sc.get(&d_off, (size_t)n + 1));
+  TT_CUDA(sc.get(&d.id, (size_t)n));
+  TT_CUDA(sc.get(&d.created, (size_t)n));
+  TT_CUDA(sc.get(&d.due, (size_t)n));
+  TT_CUDA(sc.get(&d.flags, (size_t)n));
+  TT_CUDA(sc.get(&d.status, (size_t)n));
+  for (int c = 0; c < 3; ++c) {
+    TT_CUDA(sc.get(&d.str_start[c], (size_t)n));
+    TT_CUDA(sc.get(&d.str_len[c], (size_t)n));
+    TT_CUDA(sc.get(&d.str_hash[c], (size_t)n));
+  }
+  TT_CUDA(sc.get(&d_err, 2));
+  stats->n_docs = n;
+  if (n == 0) {
+    int32_t rc = alloc_columns(t, 0);
+    if (rc) return rc;
+    static const uint32_t zero_off[1] = {0};
+    if ((rc = upload_dictionary(t, 0, zero_off, nullptr))) return rc;
+    TT_CUDA(cudaStreamSynchronize(st));
+    t->ids_sorted = true;
+    return TT_OK;
+  }
+  // the text (host or device memory) and the offsets, rebased to the start of the copy
+  TT_CUDA(cudaMemcpyAsync(text, static_cast<const uint8_t*>(docs) + first, bytes, cudaMemcpyDefault, st));
+  {
+    std::vector<uint64_t> rebased((size_t)n + 1);
+    for (int64_t i = 0; i <= n; ++i) rebased[i] = doc_off[i] - first;
+    TT_CUDA(cudaMemcpyAsync(d_off, rebased.data(), ((size_t)n + 1) * 8, cudaMemcpyHostToDevice, st));
+    TT_CUDA(cudaStreamSynchronize(st));
+  }
+  const unsigned long long none = ~0ull;
+  TT_CUDA(cudaMemcpyAsync(d_err, &none, 8, cudaMemcpyHostToDevice, st));
+  TT_CUDA(cudaEventRecord(t->ev0, st));
+  tt::doc_parse_kernel<<<grid_for(n, 128), 128, 0, st>>>(text, d_off, n, local_offset_min, d);
+  tt::doc_first_bad_kernel<<<grid_for(n, 256), 256, 0, st>>>(d.status, n, d_err);
+  TT_CUDA(cudaGetLastError());
+  TT_CUDA(cudaEventRecord(t->ev1, st));
+  unsigned long long bad = none;
+  TT_CUDA(cudaMemcpyAsync(&bad, d_err, 8, cudaMemcpyDeviceToHost, st));
+  TT_CUDA(cudaStreamSynchronize(st));
+  stats->launches = 2;
+  if (bad != none) {
+    uint32_t reason = 0;
+    TT_CUDA(cudaMemcpy(&reason, d.status + bad, 4, cudaMemcpyDeviceToHost));
+    stats->first_bad = (int64_t)bad;
+    stats->first_bad_reason = (int32_t)reason;
+    static const char* why[] = {"", "not a JSON object of the TaskModel shape", "taskId is not a \"D\" Guid",
+                                "a date System.Text.Json would reject", "a malformed string (escape, control character or UTF-8)",
+                                "a known member with a value of the wrong type"};
+    return fail(TT_ERR_ARG, "document %lld: %s; nothing was loaded", (long long)bad, why[reason < 6 ? reason : 1]);
+  }
+  int32_t rc = alloc_columns(t, n);
+  if (rc) return rc;
+  auto undo = [&](int32_t code) {
+    free_columns(t);
+    return code;
+  };
+  const int64_t threads = round_up(n, 32);
+  tt::doc_fill_kernel<<<grid_for(threads, 256), 256, 0, st>>>(d, n, t->due_code, t->completed, t->overdue, t->creator_hash,
+                                                             t->task_id, t->created_raw, t->due_raw);
+  stats->launches += 1;
+  // the three string members -> refs + dictionaries
+  uint32_t* off[3] = {nullptr, nullptr, nullptr};
+  uint8_t* pool[3] = {nullptr, nullptr, nullptr};
+  uint32_t k[3] = {0, 0, 0};
+  uint64_t pbytes[3] = {0, 0, 0};
+  uint32_t* refs[3] = {nullptr, t->creator_ref, nullptr};
+  for (int c = 0; c < 3 && rc == TT_OK; c += 2) {  // payload ref columns (name, assignee)
+    cudaError_t e = cudaMalloc(&refs[c], (size_t)t->n_pad * 4);
+    if (e == cudaSuccess) e = cudaMemsetAsync(refs[c], 0xFF, (size_t)t->n_pad * 4, st);
+    if (e != cudaSuccess) {
+      cudaGetLastError();
+      rc = fail(TT_ERR_OOM, "payload column: %s", cudaGetErrorString(e));
+    }
+  }
+  for (int c = 0; c < 3 && rc == TT_OK; ++c)
+    rc = encode_member(t, sc, d, c, text, n, refs[c], &off[c], &pool[c], &k[c], &pbytes[c], &stats->launches);
+  if (rc != TT_OK) {
+    for (int c = 0; c < 3; ++c) {
+      cudaFree(off[c]);
+      cudaFree(pool[c]);
+    }
+    cudaFree(refs[0]);
+    cudaFree(refs[2]);
+    return undo(rc);
+  }
+  t->name_col.ref = refs[0];
+  t->name_col.n = k[0];
+  t->name_col.off = off[0];
+  t->name_col.pool = pool[0];
+  t->assignee_col.ref = refs[2];
+  t->assignee_col.n = k[2];
+  t->assignee_col.off = off[2];
+  t->assignee_col.pool = pool[2];
+  t->n_creators = k[1];
+  t->creator_off = off[1];
+  t->creator_pool = pool[1];
+  t->pool_bytes = pbytes[1];
+  t->creator_off_cap = (size_t)k[1] + 1;
+  t->creator_pool_cap = std::max<uint64_t>(pbytes[1], 16);
+  // is the table in TaskId order?  (then lookups by id search it directly)
+  const unsigned long long zero = 0;
+  unsigned long long unordered = 0;
+  cudaError_t e = cudaMemcpyAsync(d_err, &zero, 8, cudaMemcpyHostToDevice, st);
+  if (e == cudaSuccess) {
+    tt::doc_id_order_kernel<<<grid_for(n, 256), 256, 0, st>>>(t->task_id, n, d_err);
+    e = cudaGetLastError();
+  }
+  if (e == cudaSuccess) e = cudaEventRecord(t->ev2, st);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(&unordered, d_err, 8, cudaMemcpyDeviceToHost, st);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    return undo(fail(TT_ERR_CUDA, "document load: %s", cudaGetErrorString(e)));
+  }
+  stats->launches += 1;
+  t->ids_sorted = unordered == 0;
+  if (!t->ids_sorted) {
+    // the TaskId index is built on the host, like tt_load_soa does (ingest path)
+    std::vector<uint8_t> ids((size_t)n * 16);
+    std::vector<uint32_t> order((size_t)n);
+    e = cudaMemcpy(ids.data(), t->task_id, ids.size(), cudaMemcpyDeviceToHost);
+    for (int64_t i = 0; i < n; ++i) order[i] = (uint32_t)i;
+    const uint8_t* q = ids.data();
+    std::stable_sort(order.begin(), order.end(),
+                     [q](uint32_t a, uint32_t b) { return memcmp(q + 16 * (size_t)a, q + 16 * (size_t)b, 16) < 0; });
+    if (e == cudaSuccess) e = cudaMalloc(&t->id_order, (size_t)n * 4);
+    if (e == cudaSuccess) e = cudaMemcpy(t->id_order, order.data(), (size_t)n * 4, cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) {
+      cudaGetLastError();
+      return undo(fail(TT_ERR_CUDA, "TaskId index: %s", cudaGetErrorString(e)));
+    }
+  }
+  cudaEventElapsedTime(&stats->parse_ms, t->ev0, t->ev1);
+  cudaEventElapsedTime(&stats->encode_ms, t->ev1, t->ev2);
+  stats->n_names = k[0];
+  stats->n_creators = k[1];
+  stats->n_assignees = k[2];
+  stats->text_bytes = (int64_t)bytes;
+  return TT_OK;
+}
 
 // ---- the sweep with its working memory in a fixed device array ---------------------------------
 //

@@ -52,7 +52,7 @@ EXPORTS = [
     "tt_save_snapshot", "tt_load_snapshot", "tt_pack_hits", "tt_expand_hits",
     "tt_sweep_push", "tt_peer_alloc", "tt_peer_open", "tt_peer_close", "tt_peer_free",
     "tt_load_payload", "tt_generate_payload", "tt_result_json", "tt_json_size", "tt_json_copy", "tt_json_device",
-    "tt_json_free", "tt_last_json_stats",
+    "tt_json_free", "tt_last_json_stats", "tt_json_offsets", "tt_load_documents",
 ]
 
 
@@ -156,6 +156,12 @@ class JsonStats(C.Structure):
                 ("launches", C.c_int32)]
 
 
+class IngestStats(C.Structure):
+    _fields_ = [("n_docs", C.c_int64), ("text_bytes", C.c_int64), ("first_bad", C.c_int64), ("first_bad_reason", C.c_int32),
+                ("n_names", C.c_uint32), ("n_creators", C.c_uint32), ("n_assignees", C.c_uint32),
+                ("parse_ms", C.c_float), ("encode_ms", C.c_float), ("launches", C.c_int32)]
+
+
 class PushTarget(C.Structure):
     """tt_push_target: where tt_sweep_push stores the compact hit list (device addresses)."""
     _fields_ = [("off16", C.c_void_p), ("tile_count", C.c_void_p), ("count", C.c_void_p)]
@@ -232,6 +238,8 @@ def lib():
     L.tt_json_device.argtypes = [vp, P(vp)]
     L.tt_json_free.argtypes = [vp]
     L.tt_last_json_stats.argtypes = [vp, P(JsonStats)]
+    L.tt_json_offsets.argtypes = [vp, vp]
+    L.tt_load_documents.argtypes = [vp, vp, vp, i64, i32, P(IngestStats)]
     for name in EXPORTS:
         if name != "tt_last_error":
             getattr(L, name).restype = i32
@@ -331,6 +339,12 @@ class JsonText:
         p = C.c_void_p(0)
         _check(lib().tt_json_device(self._h, C.byref(p)))
         return p.value
+
+    def offsets(self, records):
+        """Where every record's piece of the text starts (uint64[records + 1], the last = .size)."""
+        out = np.empty(records + 1, dtype=np.uint64)
+        _check(lib().tt_json_offsets(self._h, _ptr(out)))
+        return out
 
     def free(self):
         if self._h:
@@ -432,6 +446,23 @@ class TaskTable:
         _check(lib().tt_load_payload(self._h, C.byref(views[0]) if views[0] else None,
                                      C.byref(views[1]) if views[1] else None))
         return self
+
+    def load_documents(self, text, doc_off, local_offset_min=0, allow_bad=False):
+        """tt_load_documents: fills this (empty) table from JSON documents.  text: bytes / uint8 array, or
+        a device address (int); doc_off: n + 1 offsets.  -> IngestStats (with allow_bad a rejected load
+        returns its stats instead of raising)."""
+        off = np.ascontiguousarray(doc_off, dtype=np.uint64)
+        keep = None
+        if isinstance(text, int):
+            ptr = text
+        else:
+            keep = np.frombuffer(bytes(text), dtype=np.uint8) if not isinstance(text, np.ndarray) else text
+            ptr = _ptr(keep) if keep.size else None
+        st = IngestStats()
+        rc = lib().tt_load_documents(self._h, ptr, _ptr(off), off.size - 1, local_offset_min, C.byref(st))
+        if not (allow_bad and rc == TT_ERR_ARG and st.first_bad >= 0):
+            _check(rc)
+        return st
 
     def generate_payload(self, cfg, first_row):
         """Synthetic TaskName / TaskAssignedTo for the rows generate() made (same cfg, same first_row)."""

@@ -327,6 +327,37 @@ typedef struct tt_json_stats {
 } tt_json_stats;
 int32_t tt_last_json_stats(tt_table* t, tt_json_stats* out);
 
+/* ---- bulk load from the state store's documents -----------------------------
+ * The reference stores every task as one JSON document under the key TaskId.ToString()
+ * (Api/Services/TasksStoreManager.cs:35) and reads them back through System.Text.Json
+ * (GetStateAsync<TaskModel> :50, QueryStateAsync<TaskModel> :61,130).  tt_load_documents parses n
+ * such documents on the device — one thread per document, members in any order, whitespace,
+ * unknown members, every string escape, the date forms System.Text.Json accepts, names matched
+ * ignoring ASCII case — and fills an EMPTY table with them in document order: the fixed columns,
+ * and TaskName / TaskCreatedBy / TaskAssignedTo dictionary-encoded on the device (hash sort +
+ * exact confirm).  Document i is docs[doc_off[i] .. doc_off[i+1]); it may carry one leading '['
+ * or ',' and one trailing ',' or ']' (a JSON array cut at its element boundaries, which is what
+ * tt_json_offsets returns for a tt_result_json text).  docs may be host or device memory, doc_off
+ * is host memory.  local_offset_min: the machine's UTC offset, used for dates that carry an
+ * offset (System.Text.Json turns them into local time, Kind = Local).
+ * If any document is malformed the call fails with TT_ERR_ARG, stats->first_bad / first_bad_reason
+ * say which and why, and the table stays empty.  A null string member loads as "". */
+typedef struct tt_ingest_stats {
+  int64_t n_docs;
+  int64_t text_bytes;
+  int64_t first_bad;         /* -1 when every document parsed */
+  int32_t first_bad_reason;  /* 1 shape, 2 Guid, 3 date, 4 string, 5 value type */
+  uint32_t n_names, n_creators, n_assignees; /* dictionary sizes */
+  float parse_ms;            /* K7a */
+  float encode_ms;           /* column fill + the three dictionary encodings */
+  int32_t launches;
+} tt_ingest_stats;
+int32_t tt_load_documents(tt_table* t, const void* docs, const uint64_t* doc_off, int64_t n, int32_t local_offset_min,
+                          tt_ingest_stats* stats);
+/* Byte offsets of the records of a tt_result_json text: off[i] = where record i's piece starts (its
+ * leading '[' or ','), off[n] = the length of the text; n + 1 values copied to dst (host or device). */
+int32_t tt_json_offsets(tt_json* j, uint64_t* dst);
+
 /* ---- snapshot ---------------------------------------------------------------------------------
  * Saves / restores the whole table (all columns, flags, creator dictionary, tombstones) as one
  * file in the device layout — the counterpart of the reference keeping its tasks in a state store

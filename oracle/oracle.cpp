@@ -419,6 +419,285 @@ void JsonWriteTaskModel(std::string& out, const TaskModel& t, int flavor, int lo
   out.push_back('}');
 }
 
+// ---- System.Text.Json: one stored document back into a TaskModel --------------------------------
+// What GetStateAsync<TaskModel> / QueryStateAsync<TaskModel> (Api/Services/TasksStoreManager.cs:50,61,130)
+// and the queue handler's [FromBody] TaskModel (Svc/Controllers/ExternalTasksProcessorController.cs:29)
+// do with a document: JsonSerializer.Deserialize<TaskModel> with JsonSerializerDefaults.Web.
+// Restated behaviour of System.Text.Json (.NET 9, not under /root/reference):
+//   * the text must be one JSON value; here it has to be an object (anything else throws);
+//   * property names are matched ignoring case (PropertyNameCaseInsensitive), unknown ones are
+//     skipped, a repeated one overwrites, a missing one leaves the initialiser's value;
+//   * Guid: exactly the 36-character "D" form; bool: the literals; string: any JSON string or null;
+//   * DateTime: ISO 8601-1 extended profile — YYYY-MM-DD, optionally 'T'hh:mm[:ss[.fraction]] and
+//     'Z' (Kind Utc) or (+|-)hh[:mm] (the instant in local time, Kind Local), else Kind Unspecified;
+//     1..16 fraction digits, those beyond 100 ns dropped;
+//   * lone surrogate escapes, raw control characters in strings, trailing commas and comments throw.
+// This restatement builds a small value tree first and maps its members afterwards (the product
+// streams through the text once); a null string member is stored as the empty string here and
+// there, which the reference would keep as null.
+struct JsonNode {
+  enum Type { Null, Bool, Number, String, Array, Object } type = Null;
+  bool b = false;
+  std::string text;  // String: unescaped UTF-8; Number: the literal
+  std::vector<std::pair<std::string, JsonNode>> members;
+  std::vector<JsonNode> items;
+};
+
+struct JsonParseError {};
+
+struct JsonText {
+  const char* p;
+  const char* end;
+  void Ws() { while (p < end && (*p == ' ' || *p == '\t' || *p == '\n' || *p == '\r')) ++p; }
+  char Peek() { if (p >= end) throw JsonParseError(); return *p; }
+  void Expect(char c) { if (p >= end || *p != c) throw JsonParseError(); ++p; }
+  static int Hex(char c) {
+    if (c >= '0' && c <= '9') return c - '0';
+    if (c >= 'a' && c <= 'f') return c - 'a' + 10;
+    if (c >= 'A' && c <= 'F') return c - 'A' + 10;
+    throw JsonParseError();
+  }
+  uint32_t Unit() {
+    if (end - p < 4) throw JsonParseError();
+    uint32_t v = 0;
+    for (int i = 0; i < 4; ++i) v = v * 16 + Hex(p[i]);
+    p += 4;
+    return v;
+  }
+  static void Append(std::string& s, uint32_t cp) {
+    if (cp < 0x80) s.push_back((char)cp);
+    else if (cp < 0x800) { s.push_back((char)(0xC0 | (cp >> 6))); s.push_back((char)(0x80 | (cp & 63))); }
+    else if (cp < 0x10000) { s.push_back((char)(0xE0 | (cp >> 12))); s.push_back((char)(0x80 | ((cp >> 6) & 63))); s.push_back((char)(0x80 | (cp & 63))); }
+    else { s.push_back((char)(0xF0 | (cp >> 18))); s.push_back((char)(0x80 | ((cp >> 12) & 63))); s.push_back((char)(0x80 | ((cp >> 6) & 63))); s.push_back((char)(0x80 | (cp & 63))); }
+  }
+  std::string Str() {
+    Expect('"');
+    std::string s;
+    while (true) {
+      if (p >= end) throw JsonParseError();
+      unsigned char c = (unsigned char)*p++;
+      if (c == '"') return s;
+      if (c < 0x20) throw JsonParseError();
+      if (c == '\\') {
+        if (p >= end) throw JsonParseError();
+        char e = *p++;
+        switch (e) {
+          case '"': s.push_back('"'); break;
+          case '\\': s.push_back('\\'); break;
+          case '/': s.push_back('/'); break;
+          case 'b': s.push_back('\b'); break;
+          case 'f': s.push_back('\f'); break;
+          case 'n': s.push_back('\n'); break;
+          case 'r': s.push_back('\r'); break;
+          case 't': s.push_back('\t'); break;
+          case 'u': {
+            uint32_t u = Unit();
+            if (u >= 0xDC00 && u <= 0xDFFF) throw JsonParseError();
+            if (u >= 0xD800 && u <= 0xDBFF) {
+              if (end - p < 2 || p[0] != '\\' || p[1] != 'u') throw JsonParseError();
+              p += 2;
+              uint32_t lo = Unit();
+              if (lo < 0xDC00 || lo > 0xDFFF) throw JsonParseError();
+              u = 0x10000 + ((u - 0xD800) << 10) + (lo - 0xDC00);
+            }
+            Append(s, u);
+            break;
+          }
+          default: throw JsonParseError();
+        }
+        continue;
+      }
+      if (c >= 0x80) {  // a well-formed multi-byte sequence
+        int extra = (c >> 5) == 6 ? 1 : (c >> 4) == 14 ? 2 : (c >> 3) == 30 ? 3 : -1;
+        if (extra < 0 || end - p < extra) throw JsonParseError();
+        s.push_back((char)c);
+        for (int i = 0; i < extra; ++i) {
+          unsigned char d = (unsigned char)*p++;
+          if ((d >> 6) != 2) throw JsonParseError();
+          s.push_back((char)d);
+        }
+        continue;
+      }
+      s.push_back((char)c);
+    }
+  }
+  JsonNode Value() {
+    Ws();
+    JsonNode n;
+    char c = Peek();
+    if (c == '{') {
+      ++p;
+      n.type = JsonNode::Object;
+      Ws();
+      if (Peek() == '}') { ++p; return n; }
+      while (true) {
+        Ws();
+        std::string k = Str();
+        Ws();
+        Expect(':');
+        n.members.emplace_back(std::move(k), Value());
+        Ws();
+        if (Peek() == ',') { ++p; continue; }
+        Expect('}');
+        return n;
+      }
+    }
+    if (c == '[') {
+      ++p;
+      n.type = JsonNode::Array;
+      Ws();
+      if (Peek() == ']') { ++p; return n; }
+      while (true) {
+        n.items.push_back(Value());
+        Ws();
+        if (Peek() == ',') { ++p; continue; }
+        Expect(']');
+        return n;
+      }
+    }
+    if (c == '"') { n.type = JsonNode::String; n.text = Str(); return n; }
+    auto word = [&](const char* w) { size_t l = strlen(w); if ((size_t)(end - p) < l || memcmp(p, w, l) != 0) throw JsonParseError(); p += l; };
+    if (c == 't') { word("true"); n.type = JsonNode::Bool; n.b = true; return n; }
+    if (c == 'f') { word("false"); n.type = JsonNode::Bool; n.b = false; return n; }
+    if (c == 'n') { word("null"); n.type = JsonNode::Null; return n; }
+    if (c == '-' || (c >= '0' && c <= '9')) {
+      n.type = JsonNode::Number;
+      while (p < end && (*p == '-' || *p == '+' || *p == '.' || *p == 'e' || *p == 'E' || (*p >= '0' && *p <= '9'))) n.text.push_back(*p++);
+      return n;
+    }
+    throw JsonParseError();
+  }
+};
+
+bool IEquals(const std::string& a, const char* b) {
+  size_t n = strlen(b);
+  if (a.size() != n) return false;
+  for (size_t i = 0; i < n; ++i) {
+    char x = a[i], y = b[i];
+    if (x >= 'A' && x <= 'Z') x = (char)(x - 'A' + 'a');
+    if (y >= 'A' && y <= 'Z') y = (char)(y - 'A' + 'a');
+    if (x != y) return false;
+  }
+  return true;
+}
+
+int Digits(const std::string& s, size_t at, int n) {
+  if (at + n > s.size()) throw JsonParseError();
+  int v = 0;
+  for (int i = 0; i < n; ++i) {
+    char c = s[at + i];
+    if (c < '0' || c > '9') throw JsonParseError();
+    v = v * 10 + (c - '0');
+  }
+  return v;
+}
+
+// Utf8JsonReader.GetDateTime
+DateTime JsonReadDateTime(const std::string& s, int local_offset_min) {
+  static const int kCum[12] = {0, 31, 59, 90, 120, 151, 181, 212, 243, 273, 304, 334};
+  if (s.size() < 10 || s.size() > 48) throw JsonParseError();
+  int y = Digits(s, 0, 4), mo = Digits(s, 5, 2), d = Digits(s, 8, 2);
+  if (s[4] != '-' || s[7] != '-' || y < 1 || mo < 1 || mo > 12 || d < 1) throw JsonParseError();
+  bool leap = (y % 4 == 0 && y % 100 != 0) || y % 400 == 0;
+  int dim = (mo == 2) ? (leap ? 29 : 28) : ((mo == 4 || mo == 6 || mo == 9 || mo == 11) ? 30 : 31);
+  if (d > dim) throw JsonParseError();
+  int64_t py = y - 1;
+  int64_t days = py * 365 + py / 4 - py / 100 + py / 400 + kCum[mo - 1] + ((leap && mo > 2) ? 1 : 0) + (d - 1);
+  int64_t ticks = days * kTicksPerDay;
+  uint32_t kind = TT_KIND_UNSPECIFIED;
+  size_t i = 10;
+  if (i < s.size()) {
+    if (s[i] != 'T') throw JsonParseError();
+    int hh = Digits(s, 11, 2), mi = Digits(s, 14, 2), ss = 0;
+    if (s[13] != ':' || hh > 23 || mi > 59) throw JsonParseError();
+    int64_t frac = 0;
+    i = 16;
+    if (i < s.size() && s[i] == ':') {
+      ss = Digits(s, 17, 2);
+      if (ss > 59) throw JsonParseError();
+      i = 19;
+      if (i < s.size() && (s[i] == '.' || s[i] == ',')) {
+        ++i;
+        int nd = 0;
+        while (i < s.size() && s[i] >= '0' && s[i] <= '9') {
+          if (nd < 7) frac = frac * 10 + (s[i] - '0');
+          ++nd;
+          ++i;
+        }
+        if (nd == 0 || nd > 16) throw JsonParseError();
+        while (nd++ < 7) frac *= 10;
+      }
+    }
+    ticks += ((int64_t)hh * 3600 + mi * 60 + ss) * kTicksPerSecond + frac;
+    if (i < s.size()) {
+      if (s[i] == 'Z') {
+        kind = TT_KIND_UTC;
+        ++i;
+      } else if (s[i] == '+' || s[i] == '-') {
+        int sign = s[i] == '-' ? -1 : 1;
+        int oh = Digits(s, i + 1, 2), om = 0;
+        i += 3;
+        if (i < s.size()) {
+          if (s[i] != ':') throw JsonParseError();
+          om = Digits(s, i + 1, 2);
+          i += 3;
+        }
+        if (oh > 14 || om > 59) throw JsonParseError();
+        // DateTimeOffset(...).LocalDateTime: the same instant on the local clock
+        ticks += (int64_t)(local_offset_min - sign * (oh * 60 + om)) * 60 * kTicksPerSecond;
+        kind = TT_KIND_LOCAL;
+      }
+      if (i != s.size()) throw JsonParseError();
+    }
+  }
+  if (ticks < 0 || ticks > 3155378975999999999LL) throw JsonParseError();
+  return DateTime(ticks, kind);
+}
+
+Guid JsonReadGuid(const std::string& s) {
+  if (s.size() != 36) throw JsonParseError();
+  Guid g;
+  int b = 0;
+  for (size_t i = 0; i < 36;) {
+    if (i == 8 || i == 13 || i == 18 || i == 23) {
+      if (s[i] != '-') throw JsonParseError();
+      ++i;
+      continue;
+    }
+    g.b[b++] = (uint8_t)(JsonText::Hex(s[i]) * 16 + JsonText::Hex(s[i + 1]));
+    i += 2;
+  }
+  return g;
+}
+
+// JsonSerializer.Deserialize<TaskModel>(text, web options); throws JsonParseError like JsonException
+TaskModel DeserializeTaskModel(const char* p, const char* end, int local_offset_min) {
+  JsonText t{p, end};
+  JsonNode root = t.Value();
+  t.Ws();
+  if (t.p != end || root.type != JsonNode::Object) throw JsonParseError();
+  TaskModel m;  // initialisers: Guid.Empty, string.Empty, default(DateTime), false
+  memset(m.TaskId.b, 0, 16);
+  auto str = [](const JsonNode& v) {
+    if (v.type == JsonNode::Null) return std::u16string();
+    if (v.type != JsonNode::String) throw JsonParseError();
+    return Utf8ToUtf16(v.text.data(), (int)v.text.size());
+  };
+  for (auto& kv : root.members) {
+    const std::string& k = kv.first;
+    const JsonNode& v = kv.second;
+    if (IEquals(k, "taskId")) { if (v.type != JsonNode::String) throw JsonParseError(); m.TaskId = JsonReadGuid(v.text); }
+    else if (IEquals(k, "taskName")) m.TaskName = str(v);
+    else if (IEquals(k, "taskCreatedBy")) m.TaskCreatedBy = str(v);
+    else if (IEquals(k, "taskAssignedTo")) m.TaskAssignedTo = str(v);
+    else if (IEquals(k, "taskCreatedOn")) { if (v.type != JsonNode::String) throw JsonParseError(); m.TaskCreatedOn = JsonReadDateTime(v.text, local_offset_min); }
+    else if (IEquals(k, "taskDueDate")) { if (v.type != JsonNode::String) throw JsonParseError(); m.TaskDueDate = JsonReadDateTime(v.text, local_offset_min); }
+    else if (IEquals(k, "isCompleted")) { if (v.type != JsonNode::Bool) throw JsonParseError(); m.IsCompleted = v.b; }
+    else if (IEquals(k, "isOverDue")) { if (v.type != JsonNode::Bool) throw JsonParseError(); m.IsOverDue = v.b; }
+  }
+  return m;
+}
+
 struct OracleTable {
   TaskList rows;  // every task ever added, by insertion index; owns the TaskModel objects
   TaskList live;  // the reference's _tasksList / the store's documents, in list order
@@ -763,6 +1042,45 @@ int32_t orc_string_field(orc_table* t, int64_t row, int32_t which, char* out, in
   int32_t n = (int32_t)std::min<size_t>(u.size(), (size_t)cap);
   memcpy(out, u.data(), n);
   return (int32_t)u.size();
+}
+
+// Loads n stored documents (document i = text[off[i], off[i+1])) as the reference would
+// deserialise them, in order.  A document may be one element of a JSON array cut at its element
+// boundaries: one leading '[' or ',' and one trailing ',' or ']' are ignored.  Returns -1, or the
+// index of the first document System.Text.Json would reject (nothing is added then).
+int64_t orc_add_documents(orc_table* t, const char* text, const uint64_t* off, int64_t n, int32_t local_offset_min) {
+  std::vector<TaskModel*> fresh;
+  fresh.reserve(n);
+  for (int64_t i = 0; i < n; ++i) {
+    const char* p = text + off[i];
+    const char* end = text + off[i + 1];
+    auto ws = [](char c) { return c == ' ' || c == '\t' || c == '\n' || c == '\r'; };
+    while (p < end && ws(*p)) ++p;
+    if (p < end && (*p == '[' || *p == ',')) ++p;
+    while (end > p && ws(end[-1])) --end;
+    if (end > p && (end[-1] == ',' || end[-1] == ']')) --end;
+    try {
+      fresh.push_back(new TaskModel(DeserializeTaskModel(p, end, local_offset_min)));
+    } catch (const JsonParseError&) {
+      for (TaskModel* m : fresh) delete m;
+      return i;
+    }
+  }
+  for (TaskModel* m : fresh) t->Add(m);
+  return -1;
+}
+
+// One document per listed row, concatenated; off receives n + 1 offsets.  Returns the total length.
+int64_t orc_serialize_documents(orc_table* t, const uint32_t* rows, int64_t n, int32_t flavor, int32_t local_offset_min,
+                                char* out, int64_t cap, uint64_t* off) {
+  std::string s;
+  for (int64_t i = 0; i < n; ++i) {
+    if (off) off[i] = s.size();
+    JsonWriteTaskModel(s, *t->rows[rows[i]], flavor, local_offset_min);
+  }
+  if (off) off[n] = s.size();
+  if (out && cap > 0) memcpy(out, s.data(), (size_t)std::min<int64_t>(cap, (int64_t)s.size()));
+  return (int64_t)s.size();
 }
 
 void orc_guid_string(const uint8_t* id16, char* out37) {

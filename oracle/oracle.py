@@ -121,6 +121,10 @@ def lib():
     L.orc_serialize.restype = i64
     L.orc_string_field.argtypes = [vp, i64, i32, C.c_char_p, i32]
     L.orc_string_field.restype = i32
+    L.orc_add_documents.argtypes = [vp, vp, vp, i64, i32]
+    L.orc_add_documents.restype = i64
+    L.orc_serialize_documents.argtypes = [vp, vp, i64, i32, i32, vp, i64, vp]
+    L.orc_serialize_documents.restype = i64
     L.orc_stream_sweep.argtypes = [C.POINTER(SynthCfg), u64, u64, i32, i64, i64, i32, C.POINTER(StreamOut)]
     L.orc_soa_create.argtypes = [C.POINTER(SynthCfg), u64, i64, i32]
     L.orc_soa_create.restype = vp
@@ -253,6 +257,22 @@ class OracleTable:
         buf = C.create_string_buffer(4096)
         n = self._l.orc_string_field(self._h, row, which, buf, 4096)
         return buf.raw[:n]
+
+    def add_documents(self, text, off, local_offset_min=0):
+        """JsonSerializer.Deserialize<TaskModel> of every document text[off[i]:off[i+1]], appended in order.
+        Returns -1, or the index of the first document the reference would reject (nothing is added)."""
+        buf = np.frombuffer(bytes(text) + b"\0", dtype=np.uint8)
+        off = np.ascontiguousarray(off, dtype=np.uint64)
+        return int(self._l.orc_add_documents(self._h, _ptr(buf), _ptr(off), off.size - 1, local_offset_min))
+
+    def to_documents(self, rows, flavor=JSON_DOCUMENT, local_offset_min=0):
+        """One stored document per listed row -> (bytes, offsets uint64[n + 1])."""
+        rows = np.ascontiguousarray(rows, dtype=np.uint32)
+        off = np.zeros(rows.size + 1, dtype=np.uint64)
+        need = self._l.orc_serialize_documents(self._h, _ptr(rows), rows.size, flavor, local_offset_min, None, 0, None)
+        out = np.empty(max(need, 1), dtype=np.uint8)
+        self._l.orc_serialize_documents(self._h, _ptr(rows), rows.size, flavor, local_offset_min, _ptr(out), need, _ptr(off))
+        return out[:need].tobytes(), off
 
     def to_json(self, rows, flavor=JSON_RESPONSE, local_offset_min=0):
         """JsonSerializer.Serialize(List<TaskModel>) of the listed rows, in that order (bytes)."""

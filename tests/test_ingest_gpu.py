@@ -1,0 +1,176 @@
+"""K7 — tt_load_documents: the state store's JSON documents parsed and dictionary-encoded on the device,
+against the oracle's restatement of JsonSerializer.Deserialize<TaskModel> (oracle.cpp DeserializeTaskModel).
+Equality is checked through everything the table can say about its rows: both sweeps, the flag planes,
+creator filters and the JSON text of every row (K6), which carries all eight members."""
+import json
+import uuid
+
+import numpy as np
+import pytest
+
+from helpers import tt
+
+pytestmark = pytest.mark.gpu
+DAY = tt.TICKS_PER_DAY
+
+
+def same_table(oracle, ot, table, creators, offset=0):
+    assert len(table) == len(ot)
+    for mode in (tt.MODE_FAKE, tt.MODE_STORE):
+        res = table.get_yesterdays_due(mode)
+        listed = ot.get_yesterdays_due(mode)
+        assert res.rows().tolist() == listed.tolist()
+        ids_all, _, _ = ot.export()
+        assert (res.ids() == ids_all[listed]).all()
+        assert res.to_json(tt.JSON_RESPONSE, offset) == ot.to_json(listed, tt.JSON_RESPONSE, offset)
+    c, o = ot.flags()
+    gc, go = table.flags_bytes()
+    assert (gc == c).all() and (go == o).all()
+    seen = 0
+    for who in creators:
+        res = table.get_by_creator(who)
+        listed = ot.get_by_creator(oracle.MODE_FAKE, who)
+        assert res.rows().tolist() == listed.tolist()
+        for flavor in (tt.JSON_RESPONSE, tt.JSON_DOCUMENT):
+            assert res.to_json(flavor, offset) == ot.to_json(listed, flavor, offset)
+        seen += res.count
+    return seen
+
+
+@pytest.mark.parametrize("flavor", [tt.JSON_RESPONSE, tt.JSON_DOCUMENT])
+def test_documents_written_by_the_reference_load_back(oracle, flavor):
+    n = 60_000
+    cfg = oracle.default_cfg(0xD0C, n, n_creators=7, n_names=300)
+    src = oracle.OracleTable()
+    src.add_synth(cfg, 0, n)
+    text, off = src.to_documents(np.arange(n), flavor, 120)
+    ot = oracle.OracleTable()
+    assert ot.add_documents(text, off, 120) == -1
+    table = tt.TaskTable(0)
+    st = table.load_documents(text, off, 120)
+    assert (st.n_docs, st.first_bad, st.text_bytes) == (n, -1, len(text))
+    assert (st.n_creators, st.n_names, st.n_assignees) == (7, 300, 50)
+    creators = [src.created_by(i) for i in range(40)]
+    assert same_table(oracle, ot, table, set(creators), 120) == n  # the 7 creators cover every row
+    # the loaded table behaves like any other: a cron tick marks what it lists
+    res, n_marked, _ = table.sweep(tt.MODE_STORE)
+    _, listed, n_over = ot.cron_job(tt.MODE_STORE)
+    assert res.count == listed.size == n_marked == n_over > 500
+    assert (table.flags_bytes()[1] == ot.flags()[1]).all()
+    table.close()
+
+
+HAND = [
+    # member order, whitespace, unknown members (nested, with braces inside strings), upper-case names
+    b' {\r\n "ISCOMPLETED" : true ,\t"extra": {"a": [1, 2.5e3, {"b": "}]\\"{"}], "c": null},\n'
+    b'  "taskId":"FBC55B2C-d9fa-405e-AEC8-22e53f4306dd", "TaskName":"order and case", "taskCreatedBy":"a@b",'
+    b' "taskCreatedOn":"2023-02-12T00:24:37.7361348Z", "taskDueDate":"2026-11-05", "taskAssignedTo":"x", "isOverDue":false } ',
+    # escapes in values and in a member name, surrogate pair, solidus, every short escape
+    b'{"taskId":"00000000-0000-0000-0000-000000000002","task\\u004eame":"q\\"b\\\\s\\/\\b\\f\\n\\r\\t\\u00e9\\u4e2d\\ud83d\\ude00 end",'
+    b'"taskCreatedBy":"a@b","taskCreatedOn":"2024-02-29T23:59:59","taskDueDate":"2026-11-05T00:00:00","taskAssignedTo":"caf\xc3\xa9 \xe4\xb8\xad \xf0\x9f\x98\x80"}',
+    # repeated member: the last value wins; null strings; missing members keep their defaults
+    b'{"taskName":"first","taskName":"second","taskCreatedBy":null,"taskAssignedTo":null,"isCompleted":true,"isCompleted":false}',
+    # date forms: no seconds, comma fraction, 16 fraction digits, offsets with and without minutes
+    b'{"taskId":"00000000-0000-0000-0000-000000000004","taskCreatedBy":"a@b","taskCreatedOn":"2020-01-01T10:30","taskDueDate":"2026-11-05T00:00:00,5"}',
+    b'{"taskId":"00000000-0000-0000-0000-000000000005","taskCreatedBy":"c@d","taskCreatedOn":"2020-01-01T10:30:15.1234567890123456","taskDueDate":"2026-11-05T02:00:00+02:00"}',
+    b'{"taskId":"00000000-0000-0000-0000-000000000006","taskCreatedBy":"c@d","taskCreatedOn":"2020-01-01T10:30:15.1-05","taskDueDate":"2026-11-04T18:30:00-05:30"}',
+    b'{"taskId":"00000000-0000-0000-0000-000000000007","taskCreatedBy":"c@d","taskCreatedOn":"0001-01-01T00:00:00","taskDueDate":"9999-12-31T23:59:59.9999999"}',
+    b'{}',
+    b' [ {"taskCreatedBy":"a@b","isOverDue":true} , ',
+    b',{"taskCreatedBy":"a@b","taskDueDate":"2026-11-05T00:00:00Z"}]',
+]
+
+
+def pack(docs):
+    off = np.zeros(len(docs) + 1, dtype=np.uint64)
+    off[1:] = np.cumsum([len(d) for d in docs])
+    return b"".join(docs), off
+
+
+@pytest.mark.parametrize("offset", [0, 120])
+def test_handwritten_documents(oracle, offset):
+    text, off = pack(HAND)
+    ot = oracle.OracleTable()
+    assert ot.add_documents(text, off, offset) == -1
+    table = tt.TaskTable(0)
+    st = table.load_documents(text, off, offset)
+    assert st.n_docs == len(HAND) and st.n_creators == 3  # "a@b", "c@d" and "" (null / missing)
+    assert same_table(oracle, ot, table, [b"a@b", b"c@d", b""], offset) == len(HAND)
+    doc = json.loads(table.get_by_creator(b"a@b").to_json())
+    assert {d["taskName"] for d in doc} >= {"order and case", "q\"b\\s/\b\f\n\r\té中\U0001F600 end", ""}
+    table.close()
+
+
+BAD = [
+    (b'{"taskId":"fbc55b2c-d9fa-405e-aec8-22e53f4306d"}', 2),              # 35 characters
+    (b'{"taskId":"{fbc55b2c-d9fa-405e-aec8-22e53f4306dd}"}', 2),            # "B" form
+    (b'{"taskDueDate":"2026-02-30"}', 3),                                   # no such day
+    (b'{"taskDueDate":"2026-11-05T24:00:00"}', 3),
+    (b'{"taskDueDate":"2026-11-05 00:00:00"}', 3),                          # blank instead of T
+    (b'{"taskDueDate":"2026-11-05T00:00:00.Z"}', 3),                        # empty fraction
+    (b'{"taskName":"bad \\x escape"}', 4),
+    (b'{"taskName":"lone \\ud83d surrogate"}', 4),
+    (b'{"taskName":"raw \x01 control"}', 4),
+    (b'{"taskName":"cut \xe4\xb8"}', 4),
+    (b'{"isCompleted":"true"}', 5),
+    (b'{"taskName":5}', 5),
+    (b'{"taskId":null}', 5),
+    (b'{"taskName":"x",}', 1),                                              # trailing comma
+    (b'{"taskName":"x"} extra', 1),
+    (b'["taskName"]', 1),
+    (b'{"taskName" "x"}', 1),
+    (b'', 1),
+]
+
+
+def test_rejected_documents_leave_the_table_empty(oracle):
+    good = b'{"taskCreatedBy":"a@b"}'
+    for bad, reason in BAD:
+        docs = [good, good, bad, good]
+        text, off = pack(docs)
+        assert oracle.OracleTable().add_documents(text, off) == 2, bad
+        table = tt.TaskTable(0)
+        st = table.load_documents(text, off, allow_bad=True)
+        assert (st.first_bad, st.first_bad_reason) == (2, reason), bad
+        with pytest.raises(tt.TaskTableError):
+            table.load_documents(text, off)
+        assert len(table) == 0
+        st = table.load_documents(*pack([good, good, good]))  # and the table can still be loaded
+        assert st.n_docs == 3 and table.get_by_creator(b"a@b").count == 3
+        table.close()
+
+
+def test_empty_load(oracle):
+    table = tt.TaskTable(0)
+    st = table.load_documents(b"", [0])
+    assert st.n_docs == 0 and len(table) == 0 and table.get_yesterdays_due(tt.MODE_STORE).count == 0
+    table.close()
+
+
+def test_device_text_round_trip_at_scale(oracle):
+    """every row of a 1.5 M-row table listed, written as documents by K6 on the device, loaded by K7
+    straight from device memory, and written again: the two texts must be identical"""
+    n = 1_500_000
+    cfg = oracle.default_cfg(0xD0D, n, n_creators=20_000, ppm_due_yesterday=1_000_000, ppm_adversarial=0)
+    a = tt.TaskTable(0).generate(cfg, 0, n).generate_payload(cfg, 0)
+    res = a.get_yesterdays_due(tt.MODE_FAKE)
+    assert res.count == n
+    j = res.json(tt.JSON_DOCUMENT)
+    off = j.offsets(n)
+    assert off[0] == 0 and off[-1] == j.size and (np.diff(off.astype(np.int64)) > 160).all()
+    b = tt.TaskTable(0)
+    st = b.load_documents(j.device_ptr(), off)
+    assert (st.n_docs, st.first_bad, st.n_assignees) == (n, -1, 50) and st.n_creators <= 20_000
+    want = j.bytes()
+    j.free()
+    resb = b.get_yesterdays_due(tt.MODE_FAKE)
+    assert resb.count == n and (resb.ids() == res.ids()).all()
+    assert resb.to_json(tt.JSON_DOCUMENT) == want
+    assert b.count_flags() == a.count_flags()
+    ra, ma, _ = a.sweep(tt.MODE_STORE)
+    rb, mb, _ = b.sweep(tt.MODE_STORE)
+    assert ma == mb > 100_000 and (ra.rows() == rb.rows()).all()
+    who = json.loads(want[: off[1]].lstrip(b"[").rstrip(b","))["taskCreatedBy"].encode()
+    assert a.get_by_creator(who).rows().tolist() == b.get_by_creator(who).rows().tolist()
+    a.close()
+    b.close()
