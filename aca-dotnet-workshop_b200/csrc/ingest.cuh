@@ -155,13 +155,23 @@ __device__ const uint8_t* read_string_inplace(uint8_t* p, const uint8_t* end, ui
   const uint8_t* r = p;
   uint8_t* w = p;
   while (true) {
+    // fast path: a run of plain ASCII (the common case) moves one byte per step, or not at all
+    // while nothing has been unescaped yet
+    uint32_t c = 0;
+    while (r < end) {
+      c = *r;
+      if (c == '"' || c == '\\' || c < 0x20 || c >= 0x80) break;
+      if (w != r) *w = (uint8_t)c;
+      ++w;
+      ++r;
+    }
     if (r >= end) return nullptr;
-    if (*r == '"') break;
+    if (c == '"') break;
     uint8_t tmp[4];
     int n = 0;
     const uint8_t* nr = read_string_scalar(r, end, tmp, &n);
     if (!nr) return nullptr;
-    if (w != r || *r == '\\')  // nothing moves until the first escape has been seen
+    if (w != r || c == '\\')  // nothing moves until the first escape has been seen
       for (int j = 0; j < n; ++j) w[j] = tmp[j];
     w += n;
     r = nr;
@@ -251,6 +261,53 @@ __device__ int member_of(const uint8_t* name, int len) {
       same = c == (uint8_t)names[m][j];
     }
     if (same) return m;
+  }
+  return -1;
+}
+
+// The member name whose opening quote is at p - 1, matched straight from the text when it holds
+// no escape (the usual case): its length and one discriminating character pick the only
+// candidate, then every character is compared (ASCII case folded).  *after = past the closing
+// quote.  Returns the member number, -1 unknown, -2 bad string, -3 "has an escape, take the slow path".
+__constant__ char kMemberNames[8][16] = {"taskid", "taskname", "taskcreatedby", "taskcreatedon", "taskduedate",
+                                         "taskassignedto", "iscompleted", "isoverdue"};
+__device__ int member_fast(const uint8_t* p, const uint8_t* end, const uint8_t** after) {
+  const uint8_t* q = p;
+  while (q < end) {
+    const uint32_t c = *q;
+    if (c == '"') break;
+    if (c == '\\') return -3;
+    if (c < 0x20) return -2;
+    ++q;
+  }
+  if (q >= end) return -2;
+  *after = q + 1;
+  const int len = (int)(q - p);
+  int m;
+  switch (len) {
+    case 6: m = 0; break;
+    case 8: m = 1; break;
+    case 9: m = 7; break;
+    case 11: m = (p[0] | 0x20) == 't' ? 4 : 6; break;
+    case 13: m = (p[12] | 0x20) == 'y' ? 2 : 3; break;
+    case 14: m = 5; break;
+    default: return -1;
+  }
+  for (int j = 0; j < len; ++j) {
+    uint32_t c = p[j];
+    if (c >= 'A' && c <= 'Z') c |= 0x20;
+    if (c != (uint8_t)kMemberNames[m][j]) return -1;
+  }
+  return m;
+}
+
+// The closing quote of a short string value that holds no escape: returns its length, or -1 when
+// a backslash or control character comes first or it is longer than `limit`.
+__device__ __forceinline__ int plain_string_len(const uint8_t* p, const uint8_t* end, int limit) {
+  for (int j = 0; j <= limit && p + j < end; ++j) {
+    const uint32_t c = p[j];
+    if (c == '"') return j;
+    if (c == '\\' || c < 0x20) return -1;
   }
   return -1;
 }
@@ -387,12 +444,16 @@ __global__ void __launch_bounds__(128) doc_parse_kernel(uint8_t* text, const uin
     }
     first = false;
     if (*p != '"') { status = kDocSyntax; break; }
-    uint8_t name[16];
-    int nlen = 0;
-    p = read_string_local(p + 1, end, name, &nlen);
-    if (!p) { status = kDocString; break; }
-    const int m = nlen <= 16 ? member_of(name, nlen) : -1;
-    p = skip_ws(p, end);
+    const uint8_t* after = nullptr;
+    int m = member_fast(p + 1, end, &after);
+    if (m == -3) {  // an escaped name: unescape it into a local buffer first
+      uint8_t name[16];
+      int nlen = 0;
+      after = read_string_local(p + 1, end, name, &nlen);
+      m = !after ? -2 : nlen <= 16 ? member_of(name, nlen) : -1;
+    }
+    if (m == -2) { status = kDocString; break; }
+    p = skip_ws(after, end);
     if (p >= end || *p != ':') { status = kDocSyntax; break; }
     p = skip_ws(p + 1, end);
     if (p >= end) { status = kDocSyntax; break; }
@@ -418,6 +479,19 @@ __global__ void __launch_bounds__(128) doc_parse_kernel(uint8_t* text, const uin
     }
     // taskId and the two dates: short strings parsed from a local copy
     if (*p != '"') { status = kDocType; continue; }
+    const int plain = plain_string_len(p + 1, end, 48);
+    if (plain >= 0) {  // no escape inside: parsed where it lies
+      if (m == 0) {
+        if (!parse_guid(p + 1, plain, &id)) status = kDocGuid;
+      } else {
+        uint64_t raw = 0;
+        if (!parse_datetime(p + 1, plain, local_offset_min, &raw)) status = kDocDate;
+        else if (m == 3) created = raw;
+        else due = raw;
+      }
+      p += plain + 2;
+      continue;
+    }
     uint8_t buf[48];
     int blen = 0;
     p = read_string_local(p + 1, end, buf, &blen);
@@ -489,6 +563,19 @@ __global__ void doc_id_order_kernel(const uint4* id, int64_t n, unsigned long lo
     cmp = u < v ? -1 : u > v ? 1 : 0;
   }
   if (cmp >= 0) atomicAdd(out_of_order, 1ull);
+}
+
+// Sort keys for the TaskId index: the low (half = 0) or high 8 canonical bytes of rows[i]'s id as a
+// big-endian number.  Two stable 64-bit radix sorts, low half first, order the rows by TaskId.
+__global__ void id_half_keys_kernel(const uint4* id, const uint32_t* rows, int64_t n, int half, unsigned long long* keys,
+                                    uint32_t* vals) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint32_t r = rows ? rows[i] : (uint32_t)i;
+  const uint4 v = id[r];
+  const uint32_t a = half ? v.x : v.z, b = half ? v.y : v.w;
+  keys[i] = ((unsigned long long)__byte_perm(a, 0, 0x0123) << 32) | __byte_perm(b, 0, 0x0123);
+  vals[i] = r;
 }
 
 // ---- dictionary encoding of one string member ------------------------------------------------

@@ -2355,20 +2355,31 @@ extern "C" int32_t tt_load_documents(tt_table* t, const void* docs, const uint64
   stats->launches += 1;
   t->ids_sorted = unordered == 0;
   if (!t->ids_sorted) {
-    // the TaskId index is built on the host, like tt_load_soa does (ingest path)
-    std::vector<uint8_t> ids((size_t)n * 16);
-    std::vector<uint32_t> order((size_t)n);
-    e = cudaMemcpy(ids.data(), t->task_id, ids.size(), cudaMemcpyDeviceToHost);
-    for (int64_t i = 0; i < n; ++i) order[i] = (uint32_t)i;
-    const uint8_t* q = ids.data();
-    std::stable_sort(order.begin(), order.end(),
-                     [q](uint32_t a, uint32_t b) { return memcmp(q + 16 * (size_t)a, q + 16 * (size_t)b, 16) < 0; });
+    // the TaskId index (rows in TaskId order): two stable 64-bit radix sorts on the device, the low
+    // 8 bytes first, then the high 8 bytes of the rows in that order
+    e = t->sort.reserve(n);
+    int w = 0;
+    if (e == cudaSuccess) {
+      tt::id_half_keys_kernel<<<grid_for(n, 256), 256, 0, st>>>(t->task_id, nullptr, n, 0, t->sort.keys[0], t->sort.vals[0]);
+      e = tt::radix_sort_pairs(st, t->sort, n, 64, &w);
+    }
+    if (e == cudaSuccess) {
+      tt::id_half_keys_kernel<<<grid_for(n, 256), 256, 0, st>>>(t->task_id, t->sort.vals[w], n, 1, t->sort.keys[w ^ 1],
+                                                                t->sort.vals[w ^ 1]);
+      if (w == 0) {  // radix_sort_pairs starts from buffer pair 0
+        std::swap(t->sort.keys[0], t->sort.keys[1]);
+        std::swap(t->sort.vals[0], t->sort.vals[1]);
+      }
+      e = tt::radix_sort_pairs(st, t->sort, n, 64, &w);
+    }
     if (e == cudaSuccess) e = cudaMalloc(&t->id_order, (size_t)n * 4);
-    if (e == cudaSuccess) e = cudaMemcpy(t->id_order, order.data(), (size_t)n * 4, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(t->id_order, t->sort.vals[w], (size_t)n * 4, cudaMemcpyDeviceToDevice, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
     if (e != cudaSuccess) {
       cudaGetLastError();
       return undo(fail(TT_ERR_CUDA, "TaskId index: %s", cudaGetErrorString(e)));
     }
+    stats->launches += 2 + 2 * 4 * 8;
   }
   cudaEventElapsedTime(&stats->parse_ms, t->ev0, t->ev1);
   cudaEventElapsedTime(&stats->encode_ms, t->ev1, t->ev2);

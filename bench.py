@@ -49,7 +49,7 @@ def parse():
     ap.add_argument("--cpu-sample-rows", type=int, default=8_000_000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--workload", default="sweep", choices=["sweep", "sweep10m", "creator", "mixed", "json"],
+    ap.add_argument("--workload", default="sweep", choices=["sweep", "sweep10m", "creator", "mixed", "json", "ingest"],
                     help="sweep = the headline (BASELINE.json metric); the others are the remaining configs of "
                          "SURVEY.md 8(d): sweep10m = config 2, creator = config 4, mixed = config 5 (per GPU)")
     return ap.parse_args()
@@ -548,6 +548,60 @@ def run_extra(args):
                 "cpu_baseline": cpu}
         print(json.dumps(line))
         table.close()
+        return
+
+    if args.workload == "ingest":
+        # the documents of the overdue list of the 1 B-task table (written by K6 with the
+        # encoder Dapr's client uses) parsed and dictionary-encoded into a fresh table, straight from HBM.
+        n = args.rows
+        cfg = pkg.default_cfg(SEED, n)
+        src = pkg.TaskTable(local).generate(cfg, 0, n).generate_payload(cfg, 0)
+        res = src.get_yesterdays_due(tt.MODE_STORE)
+        j = res.json(tt.JSON_DOCUMENT)
+        off = j.offsets(res.count)
+        parse, encode, wall = [], [], []
+        for i in range(args.warmup + args.steps):
+            dst = pkg.TaskTable(local)
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            st = dst.load_documents(j.device_ptr(), off)
+            dt = time.perf_counter() - t0
+            if i >= args.warmup:
+                parse.append(st.parse_ms)
+                encode.append(st.encode_ms)
+                wall.append(dt * 1e3)
+            if i == args.warmup + args.steps - 1:
+                back = dst.get_yesterdays_due(tt.MODE_STORE)
+                same = back.count == res.count and back.digest()[:2] == res.digest()[:2]
+            dst.close()
+        cpu = None
+        if not args.no_cpu_baseline:
+            from oracle import oracle as orc
+
+            ot = orc.OracleTable()
+            ot.add_synth(orc.default_cfg(SEED, n), 0, 4_000_000)
+            listed = ot.get_yesterdays_due(orc.MODE_STORE)
+            text, doff = ot.to_documents(listed, orc.JSON_DOCUMENT)
+            fresh = orc.OracleTable()
+            t0 = time.perf_counter()
+            assert fresh.add_documents(text, doff) == -1
+            cdt = time.perf_counter() - t0
+            cpu = {"value": listed.size / cdt, "unit": "documents/s", "cores": 1, "kind": "port",
+                   "sample": f"{listed.size} documents ({len(text)} bytes) of the same list, oracle restatement of "
+                             "JsonSerializer.Deserialize<TaskModel>, 1 thread", "MBps": len(text) / cdt / 1e6}
+        pm = med(parse)
+        line = {"metric": "document_ingest_docs_per_sec", "workload": f"{res.count} stored documents ({j.size} bytes, the "
+                f"overdue list of a {n}-task table) -> SoA table, text resident in HBM", "value": res.count / (med(wall) * 1e-3),
+                "unit": "documents/s", "documents": res.count, "bytes": j.size, "parse_ms": pm, "encode_ms": med(encode),
+                "wall_ms": med(wall), "dictionaries": {"names": st.n_names, "creators": st.n_creators, "assignees": st.n_assignees},
+                "launches": st.launches, "reloaded_table_lists_the_same_tasks": bool(same),
+                "roofline": {"bound": "hbm", "achieved": j.size / (pm * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                             "frac": j.size / (pm * 1e-3) / 1e9 / peak, "kernel": "tt::doc_parse_kernel",
+                             "algorithmic_bytes": j.size, "note": "text bytes read by the parse kernel"},
+                "cpu_baseline": cpu}
+        print(json.dumps(line))
+        j.free()
+        src.close()
         return
 
     if args.workload == "mixed":

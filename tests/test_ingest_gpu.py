@@ -174,3 +174,34 @@ def test_device_text_round_trip_at_scale(oracle):
     assert a.get_by_creator(who).rows().tolist() == b.get_by_creator(who).rows().tolist()
     a.close()
     b.close()
+
+
+def test_documents_out_of_taskid_order_get_a_device_built_index(oracle):
+    """a list ordered by TaskCreatedOn is not in TaskId order: lookups by id then go through the index
+    tt_load_documents builds with two radix sorts on the device"""
+    n = 120_000
+    cfg = oracle.default_cfg(0xD0E, n, n_creators=11, ppm_due_yesterday=700_000, ppm_completed=0)
+    src = oracle.OracleTable()
+    src.add_synth(cfg, 0, n)
+    listed = src.get_yesterdays_due(oracle.MODE_STORE)  # ascending TaskCreatedOn
+    assert listed.size > 50_000 and (np.diff(listed.astype(np.int64)) < 0).any()
+    text, off = src.to_documents(listed, tt.JSON_DOCUMENT)
+    ot = oracle.OracleTable()
+    assert ot.add_documents(text, off) == -1
+    table = tt.TaskTable(0)
+    table.load_documents(text, off)
+    ids, _, _ = ot.export()
+    rng = np.random.default_rng(3)
+    pick = rng.choice(len(ot), size=5000, replace=False)
+    for r in pick[:50]:
+        got = table.get_by_id(ids[r])
+        assert got.rows().tolist() == [int(r)]
+    unknown = np.frombuffer(uuid.UUID(int=12345).bytes, dtype=np.uint8).copy()
+    assert table.get_by_id(unknown).count == 0
+    marked, missing = table.mark_overdue(tt.MODE_STORE, np.concatenate([ids[pick], unknown[None, :]]))
+    ot.mark_overdue(oracle.MODE_STORE, ids[pick])
+    assert (marked, missing) == (5000, 1)
+    assert (table.flags_bytes()[1] == ot.flags()[1]).all()
+    assert table.mark_completed(ids[pick[7]]) and ot.mark_completed(oracle.MODE_STORE, ids[pick[7]])
+    assert (table.flags_bytes()[0] == ot.flags()[0]).all()
+    table.close()
