@@ -11,6 +11,7 @@ from .tasktable import (  # noqa: F401
     MODE_FAKE,
     MODE_STORE,
     SWEEP_LIST_ONLY,
+    SWEEP_DUE_ON_OR_BEFORE,
     SWEEP_MARK,
     TICKS_PER_DAY,
     DEFAULT_TODAY,

@@ -162,7 +162,12 @@ __device__ __forceinline__ void emit_tile(const SweepParams& p, const PendingTil
   }
 }
 
-template <bool USE_FLAGS, bool MARK, int THREADS, int CTAS_PER_SM>
+// RANGE    : the generalised predicate of SURVEY.md §8 f4 — "due on or before yesterday" instead of
+//            "due exactly yesterday at 00:00:00": every live row whose due DAY is <= yesterday
+//            matches, whatever its time of day or Kind (padding rows and tombstones carry bits
+//            above bit 24 and never match).  No reference counterpart: it covers the cases the
+//            tutorial says its exact match leaves out (docs/aca/07-aca-cron-bindings/index.md:106).
+template <bool USE_FLAGS, bool MARK, int THREADS, int CTAS_PER_SM, bool RANGE = false>
 __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) sweep_kernel(SweepParams p) {
   constexpr int kWarps = THREADS / 32;
   __shared__ uint32_t s_wtot[kWarps];
@@ -198,8 +203,15 @@ __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) sweep_kernel(SweepParams
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       const uint4 v = ld.v[j];
-      uint32_t nib = ((v.x & p.mask) == p.yesterday ? 1u : 0u) | ((v.y & p.mask) == p.yesterday ? 2u : 0u) |
-                     ((v.z & p.mask) == p.yesterday ? 4u : 0u) | ((v.w & p.mask) == p.yesterday ? 8u : 0u);
+      uint32_t nib;
+      if (RANGE) {
+        // valid codes are < 2^25; (code & day mask) <= yesterday  <=>  the due date's day has passed
+        auto due = [&](uint32_t c) { return c < (1u << 25) && (c & TT_DUE_DAY_MASK) <= p.yesterday; };
+        nib = (due(v.x) ? 1u : 0u) | (due(v.y) ? 2u : 0u) | (due(v.z) ? 4u : 0u) | (due(v.w) ? 8u : 0u);
+      } else {
+        nib = ((v.x & p.mask) == p.yesterday ? 1u : 0u) | ((v.y & p.mask) == p.yesterday ? 2u : 0u) |
+              ((v.z & p.mask) == p.yesterday ? 4u : 0u) | ((v.w & p.mask) == p.yesterday ? 8u : 0u);
+      }
       packed |= nib << (4 * j);
     }
     const uint32_t cw = ld.cw, ow = ld.ow;

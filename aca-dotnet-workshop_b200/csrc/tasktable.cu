@@ -415,9 +415,14 @@ int32_t sweep_run(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_
     return fail(TT_ERR_ARG, "first_row must be a multiple of %d inside the table", TT_TILE_ROWS);
   if (cap < 0) return fail(TT_ERR_ARG, "negative capacity");
   const bool mark = (flags & TT_SWEEP_MARK) != 0;
+  const bool range = (flags & TT_SWEEP_DUE_ON_OR_BEFORE) != 0;
   // ScheduledTasksManagerController.cs:34 — runAt.Date > TaskDueDate.Date; for listed rows the
-  // right-hand side is yesterday's day number (see sweep.cuh).
+  // right-hand side is yesterday's day number (see sweep.cuh).  In range mode the listed rows have
+  // different due days: the predicate is uniform only while runAt is past yesterday, which is the
+  // cron's situation (it runs at 00:05 of today); a clock that far behind is refused.
   const bool survive = run_at_utc_ticks / TT_TICKS_PER_DAY > (int64_t)yesterday;
+  if (range && mark && !survive)
+    return fail(TT_ERR_ARG, "range sweep: run_at_utc_ticks must lie after yesterday (runAt.Date > TaskDueDate.Date would differ per row)");
   if (t->n == 0 || first_row >= t->n) {
     st->resume_row = t->n;
     return TT_OK;
@@ -464,13 +469,19 @@ int32_t sweep_run(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_
   if (listing) TT_CUDA(cudaMemsetAsync(t->group_sum, 0, (size_t)n_groups * 4, stream));
   const unsigned grid = (unsigned)std::min<int64_t>(num_tiles, (int64_t)t->sm_count * tt::kSweepCtasPerSm);
   TT_CUDA(cudaEventRecord(t->ev0, stream));
-  if (mode == TT_MODE_STORE) {
-    if (p.mark_enable)
-      tt::sweep_kernel<true, true, tt::kSweepThreads, tt::kSweepCtasPerSm><<<grid, tt::kSweepThreads, 0, stream>>>(p);
-    else
-      tt::sweep_kernel<true, false, tt::kSweepThreads, tt::kSweepCtasPerSm><<<grid, tt::kSweepThreads, 0, stream>>>(p);
+  constexpr int kT = tt::kSweepThreads, kC = tt::kSweepCtasPerSm;
+  if (range) {
+    if (mode == TT_MODE_STORE) {
+      if (p.mark_enable) tt::sweep_kernel<true, true, kT, kC, true><<<grid, kT, 0, stream>>>(p);
+      else tt::sweep_kernel<true, false, kT, kC, true><<<grid, kT, 0, stream>>>(p);
+    } else {
+      tt::sweep_kernel<false, false, kT, kC, true><<<grid, kT, 0, stream>>>(p);
+    }
+  } else if (mode == TT_MODE_STORE) {
+    if (p.mark_enable) tt::sweep_kernel<true, true, kT, kC><<<grid, kT, 0, stream>>>(p);
+    else tt::sweep_kernel<true, false, kT, kC><<<grid, kT, 0, stream>>>(p);
   } else {
-    tt::sweep_kernel<false, false, tt::kSweepThreads, tt::kSweepCtasPerSm><<<grid, tt::kSweepThreads, 0, stream>>>(p);
+    tt::sweep_kernel<false, false, kT, kC><<<grid, kT, 0, stream>>>(p);
   }
   TT_CUDA(cudaGetLastError());
   TT_CUDA(cudaEventRecord(t->ev1, stream));
@@ -836,6 +847,46 @@ int32_t tt_sweep(tt_table* t, int32_t mode, int64_t today_local_ticks, int64_t r
   *out = r;
   if (n_marked) *n_marked = st.n_marked;
   if (mode == TT_MODE_FAKE && r->n > 0 && run_at_utc_ticks / TT_TICKS_PER_DAY > today_local_ticks / TT_TICKS_PER_DAY - 1)
+    return fail(TT_ERR_NOT_IMPLEMENTED,
+                "FAKE mode: MarkOverdueTasks throws NotImplementedException (FakeTasksManager.cs:104); %lld tasks listed",
+                (long long)r->n);
+  return TT_OK;
+}
+
+int32_t tt_get_due_on_or_before(tt_table* t, int32_t mode, int64_t today_local_ticks, tt_result** out) {
+  if (!t || !out) return fail(TT_ERR_ARG, "null argument");
+  *out = nullptr;
+  std::lock_guard<std::mutex> lk(t->mu);
+  DeviceGuard g(t->device);
+  tt_sweep_stats st;
+  tt_result* r = nullptr;
+  int32_t rc = sweep_owned(t, mode, TT_SWEEP_LIST_ONLY | TT_SWEEP_DUE_ON_OR_BEFORE, today_local_ticks, 0, &r, &st);
+  if (rc) return rc;
+  if (mode == TT_MODE_STORE && r->n > 1) {  // the store-backed list is ordered by TaskCreatedOn (TasksStoreManager.cs:136)
+    rc = tt::order_by_created(t->stream, t->sort, t->created_raw, t->task_id, r->d_rows, r->d_ids, r->n, /*descending=*/false);
+    if (rc != 0) {
+      result_release(r);
+      return fail(TT_ERR_CUDA, "order_by_created failed: %s", cudaGetErrorString((cudaError_t)rc));
+    }
+  }
+  *out = r;
+  return TT_OK;
+}
+
+int32_t tt_sweep_backlog(tt_table* t, int32_t mode, int64_t today_local_ticks, int64_t run_at_utc_ticks, tt_result** out,
+                         int64_t* n_marked) {
+  if (!t || !out) return fail(TT_ERR_ARG, "null argument");
+  *out = nullptr;
+  if (n_marked) *n_marked = 0;
+  std::lock_guard<std::mutex> lk(t->mu);
+  DeviceGuard g(t->device);
+  tt_sweep_stats st;
+  tt_result* r = nullptr;
+  int32_t rc = sweep_owned(t, mode, TT_SWEEP_MARK | TT_SWEEP_DUE_ON_OR_BEFORE, today_local_ticks, run_at_utc_ticks, &r, &st);
+  if (rc) return rc;
+  *out = r;
+  if (n_marked) *n_marked = st.n_marked;
+  if (mode == TT_MODE_FAKE && r->n > 0)
     return fail(TT_ERR_NOT_IMPLEMENTED,
                 "FAKE mode: MarkOverdueTasks throws NotImplementedException (FakeTasksManager.cs:104); %lld tasks listed",
                 (long long)r->n);

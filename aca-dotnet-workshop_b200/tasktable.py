@@ -16,6 +16,7 @@ MODE_FAKE = 0
 MODE_STORE = 1
 SWEEP_LIST_ONLY = 0
 SWEEP_MARK = 1
+SWEEP_DUE_ON_OR_BEFORE = 2  # TT_SWEEP_DUE_ON_OR_BEFORE: the generalised predicate (OR it into the flags)
 
 TT_OK = 0
 TT_ERR_ARG = -1
@@ -53,6 +54,7 @@ EXPORTS = [
     "tt_sweep_push", "tt_peer_alloc", "tt_peer_open", "tt_peer_close", "tt_peer_free",
     "tt_load_payload", "tt_generate_payload", "tt_result_json", "tt_json_size", "tt_json_copy", "tt_json_device",
     "tt_json_free", "tt_last_json_stats", "tt_json_offsets", "tt_load_documents",
+    "tt_get_due_on_or_before", "tt_sweep_backlog",
 ]
 
 
@@ -238,6 +240,8 @@ def lib():
     L.tt_json_device.argtypes = [vp, P(vp)]
     L.tt_json_free.argtypes = [vp]
     L.tt_last_json_stats.argtypes = [vp, P(JsonStats)]
+    L.tt_get_due_on_or_before.argtypes = [vp, i32, i64, P(vp)]
+    L.tt_sweep_backlog.argtypes = [vp, i32, i64, i64, P(vp), P(i64)]
     L.tt_json_offsets.argtypes = [vp, vp]
     L.tt_load_documents.argtypes = [vp, vp, vp, i64, i32, P(IngestStats)]
     for name in EXPORTS:
@@ -486,6 +490,19 @@ class TaskTable:
         r = C.c_void_p()
         _check(lib().tt_get_yesterdays_due(self._h, mode, today, C.byref(r)))
         return Result(r)
+
+    def get_due_on_or_before(self, mode, today=DEFAULT_TODAY):
+        """tt_get_due_on_or_before: GetYesterdaysDueTasks with the generalised predicate (an extension)."""
+        h = C.c_void_p(0)
+        _check(lib().tt_get_due_on_or_before(self._h, mode, today, C.byref(h)))
+        return Result(h)
+
+    def sweep_backlog(self, mode, today=DEFAULT_TODAY, run_at=DEFAULT_RUN_AT):
+        """tt_sweep_backlog: the fused cron tick with the generalised predicate -> (Result, n_marked, threw)."""
+        h, marked = C.c_void_p(0), C.c_int64(0)
+        rc = lib().tt_sweep_backlog(self._h, mode, today, run_at, C.byref(h), C.byref(marked))
+        _check(rc, allow=(TT_ERR_NOT_IMPLEMENTED,))
+        return Result(h), marked.value, rc == TT_ERR_NOT_IMPLEMENTED
 
     def mark_overdue(self, mode, ids16):
         ids = np.ascontiguousarray(ids16, dtype=np.uint8).reshape(-1, 16)

@@ -120,6 +120,13 @@ int32_t tt_mark_overdue(tt_table* t, int32_t mode, const uint8_t* ids16, int64_t
 int32_t tt_sweep(tt_table* t, int32_t mode, int64_t today_local_ticks, int64_t run_at_utc_ticks, tt_result** out,
                  int64_t* n_marked);
 
+/* The two calls above with the generalised predicate TT_SWEEP_DUE_ON_OR_BEFORE (see below): what
+ * GetYesterdaysDueTasks / the cron tick would be if they asked for "due yesterday or earlier and
+ * still pending".  No reference counterpart; same modes, order and errors. */
+int32_t tt_get_due_on_or_before(tt_table* t, int32_t mode, int64_t today_local_ticks, tt_result** out);
+int32_t tt_sweep_backlog(tt_table* t, int32_t mode, int64_t today_local_ticks, int64_t run_at_utc_ticks, tt_result** out,
+                         int64_t* n_marked);
+
 /* ITasksManager.GetTasksByCreator (ITasksManager.cs:7; FakeTasksManager.cs:68-72,
  * TasksStoreManager.cs:54-69): ordinal byte-exact match of TaskCreatedBy (64-bit hash scan,
  * then the candidate's string is compared), descending TaskCreatedOn, ties in row order. */
@@ -215,6 +222,14 @@ typedef struct tt_sweep_stats {
 
 #define TT_SWEEP_MARK 1     /* apply the cron predicate and set IsOverDue (the fused tick)      */
 #define TT_SWEEP_LIST_ONLY 0 /* GetYesterdaysDueTasks only                                        */
+#define TT_SWEEP_DUE_ON_OR_BEFORE 2 /* OR it in: list (and mark) every task whose due DATE is yesterday or
+                                       earlier, whatever its time of day or Kind — the backlog the exact
+                                       "due yesterday at 00:00:00" match leaves behind when a cron run was
+                                       missed or a due date carries a time (the edge cases
+                                       docs/aca/07-aca-cron-bindings/index.md:106 mentions).  An extension:
+                                       the reference has no such query.  Flag tests of
+                                       STORE mode still apply; with TT_SWEEP_MARK, run_at must lie after
+                                       yesterday. */
 
 int32_t tt_sweep_device(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_ticks,
                         int64_t run_at_utc_ticks, int64_t first_row, uint32_t* d_rows, void* d_ids, int64_t cap,

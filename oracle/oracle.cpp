@@ -871,6 +871,43 @@ int32_t orc_cron_job(orc_table* t, int32_t mode, int64_t today_local_ticks, int6
   return status;
 }
 
+// ---- EXTENSION (no reference counterpart) ------------------------------------------
+// The generalised predicate: "due yesterday or earlier" instead of "due exactly yesterday at
+// 00:00:00".  Written as the two managers would write it, one LINQ clause changed —
+//   FAKE : _tasksList.Where(t => t.TaskDueDate.Date <= DateTime.Today.AddDays(-1).Date).ToList()
+//   STORE: the same date test in place of the store-side EQ, then :133-136 unchanged
+//          (IsCompleted == false && IsOverDue == false, OrderBy(TaskCreatedOn))
+// — followed by the unchanged cron handler (ScheduledTasksManagerController.cs:28-45).  It covers what
+// docs/aca/07-aca-cron-bindings/index.md:106 calls the edge cases of the simple implementation.
+int64_t orc_backlog(orc_table* t, int32_t mode, int32_t mark, int64_t today_local_ticks, int64_t run_at_utc_ticks,
+                    int64_t* n_overdue, int32_t* threw, uint32_t* out_rows, int64_t cap) {
+  const DateTime yesterday = DateTime(today_local_ticks, TT_KIND_LOCAL).AddDays(-1).Date();
+  const DateTime runAt(run_at_utc_ticks, TT_KIND_UTC);
+  std::vector<TaskModel*> list;
+  for (TaskModel* x : t->live) {
+    if (x->TaskDueDate.Date() > yesterday) continue;
+    if (mode == ORC_MODE_STORE && !(x->IsCompleted == false && x->IsOverDue == false)) continue;
+    list.push_back(x);
+  }
+  if (mode == ORC_MODE_STORE)
+    std::stable_sort(list.begin(), list.end(),
+                     [](const TaskModel* a, const TaskModel* b) { return a->TaskCreatedOn.Ticks() < b->TaskCreatedOn.Ticks(); });
+  std::vector<int64_t> rows;
+  std::vector<TaskModel*> overdue;
+  for (TaskModel* x : list) {
+    rows.push_back(x->row);
+    if (runAt.Date() > x->TaskDueDate.Date()) overdue.push_back(x);
+  }
+  *n_overdue = (int64_t)overdue.size();
+  *threw = 0;
+  if (mark && !overdue.empty()) {
+    if (mode == ORC_MODE_FAKE) *threw = 1;  // FakeTasksManager.MarkOverdueTasks throws (:104)
+    else
+      for (TaskModel* x : overdue) x->IsOverDue = true;  // TasksStoreManager.cs:146
+  }
+  return Emit(rows, out_rows, cap);
+}
+
 // ITasksManager.MarkOverdueTasks(list) addressed by TaskId.  Returns 0, or 1 if it threw
 // (FAKE).  *n_missing = ids with no stored record.
 int32_t orc_mark_overdue(orc_table* t, int32_t mode, const uint8_t* ids16, int64_t n, int64_t* n_missing) {

@@ -95,6 +95,8 @@ def lib():
     L.orc_get_yesterdays_due.restype = i64
     L.orc_cron_job.argtypes = [vp, i32, i64, i64, i32, i32, C.POINTER(i64), C.POINTER(i64), vp, i64]
     L.orc_cron_job.restype = i32
+    L.orc_backlog.argtypes = [vp, i32, i32, i64, i64, C.POINTER(i64), C.POINTER(i32), vp, i64]
+    L.orc_backlog.restype = i64
     L.orc_mark_overdue.argtypes = [vp, i32, vp, i64, C.POINTER(i64)]
     L.orc_mark_overdue.restype = i32
     L.orc_get_by_creator.argtypes = [vp, i32, C.c_char_p, i32, vp, i64]
@@ -187,6 +189,15 @@ class OracleTable:
         st = self._l.orc_cron_job(self._h, mode, today, run_at, local_offset_min, int(string_eq), C.byref(nl),
                                   C.byref(no), _ptr(out), len(out))
         return bool(st), out[: nl.value].copy(), no.value
+
+    def backlog(self, mode, mark=False, today=DEFAULT_TODAY, run_at=DEFAULT_RUN_AT):
+        """EXTENSION: tasks due yesterday or earlier [and pending, STORE]; with mark, the cron
+        handler's filter + MarkOverdueTasks.  -> (rows in list order, n_overdue, threw)."""
+        n = len(self)
+        out = np.empty(max(n, 1), dtype=np.uint32)
+        n_over, threw = C.c_int64(0), C.c_int32(0)
+        k = self._l.orc_backlog(self._h, mode, 1 if mark else 0, today, run_at, C.byref(n_over), C.byref(threw), _ptr(out), n)
+        return out[:k].copy(), n_over.value, bool(threw.value)
 
     def mark_overdue(self, mode, ids16):
         ids = np.ascontiguousarray(ids16, dtype=np.uint8).reshape(-1, 16)
