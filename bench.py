@@ -328,7 +328,7 @@ def run_b200(args):
         med = lambda xs: sorted(xs)[len(xs) // 2]
         kms, sms, gms = med(kernel_ms), med(sweep_ms), med(gather_ms)
         # Dominant kernel = K1 sweep_kernel: it reads 4.25 B/task and writes one u32 row per hit.
-        # K2+K3 (row order + TaskId gather) read 4 B + 16 B and write 4 B + 16 B per hit.
+        # K2+K3g (row order + TaskId gather) read 4 B + 16 B and write 4 B + 16 B per hit.
         # The whole step is SURVEY.md 8(d)'s figure: 4.25 B/task + 36 B/hit (+ the 8 B/hit of the
         # intermediate list, which is not counted).
         sweep_bytes = n_rows * BYTES_PER_TASK + hits * 4.0
@@ -363,7 +363,7 @@ def run_b200(args):
                          "traffic": traffic, "kernel": "tt::sweep_kernel<true,true,256,4> (K1, dominant)",
                          "kernel_ms": sms, "algorithmic_bytes": sweep_bytes,
                          "bytes_per_unit": "4.25 B/task + 4 B/hit", "peak_source": peak_src,
-                         "step": {"kernels": "K1 sweep + K2 tile_offsets + K3 place_hits", "ms": kms,
+                         "step": {"kernels": "K1 sweep_kernel + K2 tile_offsets_kernel + K3g place_group_kernel", "ms": kms,
                                   "algorithmic_bytes": step_bytes, "bytes_per_unit": "4.25 B/task + 36 B/hit",
                                   "achieved": step_gbs, "frac": step_gbs / peak},
                          "place_kernels": {"ms": gms, "achieved": place_gbs,

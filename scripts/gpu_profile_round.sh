@@ -13,8 +13,10 @@ timeout 600 python bench.py --impl reference > gpurun_out/bench_reference.log 2>
 timeout 600 python bench.py --workload creator > gpurun_out/bench_creator.log 2>&1
 timeout 600 python bench.py --workload sweep10m --steps 20 --warmup 5 > gpurun_out/bench_10m.log 2>&1
 timeout 600 python bench.py --workload mixed --steps 10 --warmup 3 > gpurun_out/bench_mixed.log 2>&1
+timeout 600 python bench.py --workload json --steps 5 --warmup 2 > gpurun_out/bench_json.log 2>&1
+timeout 600 python bench.py --workload ingest --steps 3 --warmup 1 > gpurun_out/bench_ingest.log 2>&1
 timeout 600 python bench.py --steps 5 --warmup 3 --no-cpu-baseline --no-e2e > gpurun_out/plain.log 2>&1 && \
 timeout 900 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none -c 40 --csv --log-file gpurun_out/launches.csv python bench.py --steps 5 --warmup 3 --no-cpu-baseline --no-e2e > gpurun_out/ncu1.log 2>&1
 timeout 600 python bench.py --steps 5 --warmup 3 --no-cpu-baseline --no-e2e > gpurun_out/plain2.log 2>&1 && \
-timeout 1200 ncu --set full --clock-control none --import-source on -k regex:"sweep_kernel|place_hits" -s 9 -c 2 -o gpurun_out/prof_sweep python bench.py --steps 5 --warmup 3 --no-cpu-baseline --no-e2e > gpurun_out/ncu2.log 2>&1
+timeout 1200 ncu --set full --clock-control none --import-source on -k regex:"sweep_kernel|place_group" -s 9 -c 2 -o gpurun_out/prof_sweep python bench.py --steps 5 --warmup 3 --no-cpu-baseline --no-e2e > gpurun_out/ncu2.log 2>&1
 ls -la gpurun_out
