@@ -205,3 +205,30 @@ def test_documents_out_of_taskid_order_get_a_device_built_index(oracle):
     assert table.mark_completed(ids[pick[7]]) and ot.mark_completed(oracle.MODE_STORE, ids[pick[7]])
     assert (table.flags_bytes()[0] == ot.flags()[0]).all()
     table.close()
+
+
+def test_documents_from_the_reference_tutorial(oracle):
+    """the golden fixture tests/golden/reference_doc_samples.json through K7 and back out through K6"""
+    import os
+
+    here = os.path.dirname(os.path.abspath(__file__))
+    samples = json.load(open(os.path.join(here, "golden", "reference_doc_samples.json")))
+    text, off = pack([s["text"].encode() for s in samples])
+    table = tt.TaskTable(0)
+    st = table.load_documents(text, off)
+    assert st.n_docs == len(samples) and st.first_bad == -1
+    ot = oracle.OracleTable()
+    assert ot.add_documents(text, off) == -1
+    defaults = {"taskId": "00000000-0000-0000-0000-000000000000", "taskName": "", "taskCreatedBy": "",
+                "taskCreatedOn": "0001-01-01T00:00:00", "taskDueDate": "0001-01-01T00:00:00", "taskAssignedTo": "",
+                "isCompleted": False, "isOverDue": False}
+    seen = 0
+    for who in {s["members"]["taskCreatedBy"].encode() for s in samples}:
+        res = table.get_by_creator(who)
+        listed = ot.get_by_creator(oracle.MODE_FAKE, who)
+        assert res.rows().tolist() == listed.tolist()
+        for row, doc in zip(res.rows(), json.loads(res.to_json())):
+            assert doc == {**defaults, **samples[int(row)]["members"]}, samples[int(row)]["source"]
+            seen += 1
+    assert seen == len(samples)
+    table.close()
