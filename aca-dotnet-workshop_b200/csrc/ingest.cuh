@@ -414,13 +414,18 @@ __device__ bool parse_datetime(const uint8_t* s, int len, int32_t local_offset_m
 }
 
 // K7a: one thread per document.
-__global__ void __launch_bounds__(128) doc_parse_kernel(uint8_t* text, const uint64_t* doc_off, int64_t n,
-                                                        int32_t local_offset_min, DocCols out) {
+// `text` holds the caller's bytes [window_first, window_first + bytes); doc_off are the caller's offsets.  A document
+// whose range is not inside that window, or runs backwards, is a bad document.
+__global__ void __launch_bounds__(128) doc_parse_kernel(uint8_t* text, const uint64_t* doc_off, uint64_t window_first,
+                                                        uint64_t bytes, int64_t n, int32_t local_offset_min,
+                                                        DocCols out) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   uint8_t* const base = text;
-  const uint8_t* p = text + doc_off[i];
-  const uint8_t* const end = text + doc_off[i + 1];
+  const uint64_t a = doc_off[i], b = doc_off[i + 1];
+  const bool in_window = a >= window_first && b >= a && b - window_first <= bytes;
+  const uint8_t* p = text + (in_window ? a - window_first : 0);
+  const uint8_t* const end = text + (in_window ? b - window_first : 0);
   uint4 id = make_uint4(0, 0, 0, 0);
   uint64_t created = 0, due = 0;
   uint32_t flags = 0;
@@ -430,7 +435,7 @@ __global__ void __launch_bounds__(128) doc_parse_kernel(uint8_t* text, const uin
 
   p = skip_ws(p, end);
   if (p < end && (*p == '[' || *p == ',')) p = skip_ws(p + 1, end);
-  if (p >= end || *p != '{') status = kDocSyntax;
+  if (!in_window || p >= end || *p != '{') status = kDocSyntax;
   else ++p;
   bool first = true;
   while (status == kDocOk) {

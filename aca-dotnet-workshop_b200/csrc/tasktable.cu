@@ -2274,15 +2274,29 @@ extern "C" int32_t tt_load_documents(tt_table* t, const void* docs, const uint64
   if (!stats) stats = &local_stats;
   memset(stats, 0, sizeof *stats);
   stats->first_bad = -1;
-  for (int64_t i = 0; i < n; ++i)
-    if (doc_off[i + 1] < doc_off[i]) return fail(TT_ERR_ARG, "doc_off not ascending at %lld", (long long)i);
   std::lock_guard<std::mutex> lk(t->mu);
   DeviceGuard g(t->device);
   if (t->n_pad != 0) return fail(TT_ERR_STATE, "table already holds %lld rows", (long long)t->n);
   if (n > kMaxRows) return fail(TT_ERR_ARG, "row count %lld outside [0, 2^31]", (long long)n);
   cudaStream_t st = t->stream;
   IngestScratch sc;
-  const uint64_t first = n ? doc_off[0] : 0, bytes = n ? doc_off[n] - first : 0;
+  // the offsets may live in host or device memory; only the two ends are needed here, the kernel
+  // checks every document's range against them
+  uint64_t ends[2] = {0, 0};
+  if (n) {
+    cudaPointerAttributes attr;
+    const bool on_device = cudaPointerGetAttributes(&attr, doc_off) == cudaSuccess && attr.type == cudaMemoryTypeDevice;
+    cudaGetLastError();
+    if (on_device) {
+      TT_CUDA(cudaMemcpy(&ends[0], doc_off, 8, cudaMemcpyDeviceToHost));
+      TT_CUDA(cudaMemcpy(&ends[1], doc_off + n, 8, cudaMemcpyDeviceToHost));
+    } else {
+      ends[0] = doc_off[0];
+      ends[1] = doc_off[n];
+    }
+    if (ends[1] < ends[0]) return fail(TT_ERR_ARG, "doc_off[n] < doc_off[0]");
+  }
+  const uint64_t first = ends[0], bytes = ends[1] - ends[0];
   uint8_t* text = nullptr;
   uint64_t* d_off = nullptr;
   tt::DocCols d = {};
@@ -2310,18 +2324,13 @@ extern "C" int32_t tt_load_documents(tt_table* t, const void* docs, const uint64
     t->ids_sorted = true;
     return TT_OK;
   }
-  // the text (host or device memory) and the offsets, rebased to the start of the copy
+  // the device's own copy of the text (it is unescaped in place) and of the offsets
   TT_CUDA(cudaMemcpyAsync(text, static_cast<const uint8_t*>(docs) + first, bytes, cudaMemcpyDefault, st));
-  {
-    std::vector<uint64_t> rebased((size_t)n + 1);
-    for (int64_t i = 0; i <= n; ++i) rebased[i] = doc_off[i] - first;
-    TT_CUDA(cudaMemcpyAsync(d_off, rebased.data(), ((size_t)n + 1) * 8, cudaMemcpyHostToDevice, st));
-    TT_CUDA(cudaStreamSynchronize(st));
-  }
+  TT_CUDA(cudaMemcpyAsync(d_off, doc_off, ((size_t)n + 1) * 8, cudaMemcpyDefault, st));
   const unsigned long long none = ~0ull;
   TT_CUDA(cudaMemcpyAsync(d_err, &none, 8, cudaMemcpyHostToDevice, st));
   TT_CUDA(cudaEventRecord(t->ev0, st));
-  tt::doc_parse_kernel<<<grid_for(n, 128), 128, 0, st>>>(text, d_off, n, local_offset_min, d);
+  tt::doc_parse_kernel<<<grid_for(n, 128), 128, 0, st>>>(text, d_off, first, bytes, n, local_offset_min, d);
   tt::doc_first_bad_kernel<<<grid_for(n, 256), 256, 0, st>>>(d.status, n, d_err);
   TT_CUDA(cudaGetLastError());
   TT_CUDA(cudaEventRecord(t->ev1, st));

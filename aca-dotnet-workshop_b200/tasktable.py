@@ -344,6 +344,10 @@ class JsonText:
         _check(lib().tt_json_device(self._h, C.byref(p)))
         return p.value
 
+    def offsets_to(self, dst_ptr):
+        """tt_json_offsets into caller memory (host or device address): records + 1 uint64 values."""
+        _check(lib().tt_json_offsets(self._h, dst_ptr))
+
     def offsets(self, records):
         """Where every record's piece of the text starts (uint64[records + 1], the last = .size)."""
         out = np.empty(records + 1, dtype=np.uint64)
@@ -453,9 +457,14 @@ class TaskTable:
 
     def load_documents(self, text, doc_off, local_offset_min=0, allow_bad=False):
         """tt_load_documents: fills this (empty) table from JSON documents.  text: bytes / uint8 array, or
-        a device address (int); doc_off: n + 1 offsets.  -> IngestStats (with allow_bad a rejected load
+        a device address (int); doc_off: n + 1 offsets (array-like), or (device address, n).  -> IngestStats (with allow_bad a rejected load
         returns its stats instead of raising)."""
-        off = np.ascontiguousarray(doc_off, dtype=np.uint64)
+        if isinstance(doc_off, tuple):  # (device address of uint64[n + 1], n): offsets already on the device
+            off_ptr, n_docs = doc_off
+            off = None
+        else:
+            off = np.ascontiguousarray(doc_off, dtype=np.uint64)
+            off_ptr, n_docs = _ptr(off), off.size - 1
         keep = None
         if isinstance(text, int):
             ptr = text
@@ -463,7 +472,7 @@ class TaskTable:
             keep = np.frombuffer(bytes(text), dtype=np.uint8) if not isinstance(text, np.ndarray) else text
             ptr = _ptr(keep) if keep.size else None
         st = IngestStats()
-        rc = lib().tt_load_documents(self._h, ptr, _ptr(off), off.size - 1, local_offset_min, C.byref(st))
+        rc = lib().tt_load_documents(self._h, ptr, off_ptr, n_docs, local_offset_min, C.byref(st))
         if not (allow_bad and rc == TT_ERR_ARG and st.first_bad >= 0):
             _check(rc)
         return st

@@ -352,8 +352,9 @@ int32_t tt_last_json_stats(tt_table* t, tt_json_stats* out);
  * and TaskName / TaskCreatedBy / TaskAssignedTo dictionary-encoded on the device (hash sort +
  * exact confirm).  Document i is docs[doc_off[i] .. doc_off[i+1]); it may carry one leading '['
  * or ',' and one trailing ',' or ']' (a JSON array cut at its element boundaries, which is what
- * tt_json_offsets returns for a tt_result_json text).  docs may be host or device memory, doc_off
- * is host memory.  local_offset_min: the machine's UTC offset, used for dates that carry an
+ * tt_json_offsets returns for a tt_result_json text).  docs and doc_off may each be host or device
+ * memory (offsets that run backwards or outside [doc_off[0], doc_off[n]] make that document bad).
+ * local_offset_min: the machine's UTC offset, used for dates that carry an
  * offset (System.Text.Json turns them into local time, Kind = Local).
  * If any document is malformed the call fails with TT_ERR_ARG, stats->first_bad / first_bad_reason
  * say which and why, and the table stays empty.  A null string member loads as "". */

@@ -140,6 +140,20 @@ def test_rejected_documents_leave_the_table_empty(oracle):
         table.close()
 
 
+def test_offsets_that_do_not_describe_the_text_are_bad_documents(oracle):
+    good = b'{"taskCreatedBy":"a@b"}'
+    text, off = pack([good] * 4)
+    for broken, bad in ((off.copy(), 1), (off.copy(), 2)):
+        if bad == 1:
+            broken[2] = broken[1] - 3        # runs backwards: documents 1 ends before it starts
+        else:
+            broken[3] = broken[4] + 1000     # document 2 would end beyond the text
+        table = tt.TaskTable(0)
+        st = table.load_documents(text, broken, allow_bad=True)
+        assert st.first_bad == bad and st.first_bad_reason == 1 and len(table) == 0
+        table.close()
+
+
 def test_empty_load(oracle):
     table = tt.TaskTable(0)
     st = table.load_documents(b"", [0])
@@ -158,8 +172,11 @@ def test_device_text_round_trip_at_scale(oracle):
     j = res.json(tt.JSON_DOCUMENT)
     off = j.offsets(n)
     assert off[0] == 0 and off[-1] == j.size and (np.diff(off.astype(np.int64)) > 160).all()
+    import torch
+
+    off_dev = torch.from_numpy(off.astype(np.int64)).cuda()  # offsets may live on the device as well
     b = tt.TaskTable(0)
-    st = b.load_documents(j.device_ptr(), off)
+    st = b.load_documents(j.device_ptr(), (off_dev.data_ptr(), n))
     assert (st.n_docs, st.first_bad, st.n_assignees) == (n, -1, 50) and st.n_creators <= 20_000
     want = j.bytes()
     j.free()
