@@ -402,6 +402,16 @@ bool place_by_group() {
   return by_group;
 }
 
+// Persistent CTAs per SM for K1 (TT_SWEEP_CTAS=1..4, read once; the kernel is built for up to 4).
+int sweep_ctas_per_sm() {
+  static const int ctas = [] {
+    const char* e = getenv("TT_SWEEP_CTAS");
+    const int v = e ? atoi(e) : tt::kSweepCtasPerSm;
+    return v >= 1 && v <= tt::kSweepCtasPerSm ? v : tt::kSweepCtasPerSm;
+  }();
+  return ctas;
+}
+
 // Launches the sweep kernel over rows [first_row, n) on `stream`, waits, fills *st.
 int32_t sweep_run(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_ticks, int64_t run_at_utc_ticks,
                   int64_t first_row, uint32_t* d_rows, uint4* d_ids, int64_t cap, tt_sweep_stats* st,
@@ -467,7 +477,7 @@ int32_t sweep_run(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_
   TT_CUDA(cudaMemcpyAsync(t->ctl, t->h_ctl, sizeof init, cudaMemcpyHostToDevice, stream));
   const unsigned n_groups = (num_tiles + tt::kTilesPerGroup - 1) / tt::kTilesPerGroup;
   if (listing) TT_CUDA(cudaMemsetAsync(t->group_sum, 0, (size_t)n_groups * 4, stream));
-  const unsigned grid = (unsigned)std::min<int64_t>(num_tiles, (int64_t)t->sm_count * tt::kSweepCtasPerSm);
+  const unsigned grid = (unsigned)std::min<int64_t>(num_tiles, (int64_t)t->sm_count * sweep_ctas_per_sm());
   TT_CUDA(cudaEventRecord(t->ev0, stream));
   constexpr int kT = tt::kSweepThreads, kC = tt::kSweepCtasPerSm;
   if (range) {

@@ -99,6 +99,44 @@ int main(int argc, char** argv) {
       }
       printf("%-40s total %8.3f ms (K1 %.3f, K3 %.3f)\n", mode == 0 ? "K1 alone" : mode == 1 ? "K3 alone" : "K1 || K3 on two streams", best, bk1, bk3);
     }
+    // ---- the same question with room left on every SM: K1 at 3 or 2 CTAs per SM (it needs the whole
+    // register file at 4) next to the tile-ordered K3g, launched in either order ----
+    PushTarget none = {nullptr, nullptr, nullptr};
+    const unsigned ggrid = (p.num_tiles + kGroupTiles - 1) / kGroupTiles;
+    for (int k1ctas = 4; k1ctas >= 2; --k1ctas) {
+      for (int order = 0; order < 2; ++order) {
+        float best = 1e9f, bk1 = 0, bk3 = 0;
+        for (int r = 0; r < 4; ++r) {
+          cudaMemset(over2, 0, NP / 8);
+          SweepCtl init; init.tile_counter = 0; init.pad = 0; init.cursor = 0; init.stored = ~0ull;
+          cudaMemcpy(ctl2, &init, sizeof init, cudaMemcpyHostToDevice); cudaMemset(gsum2, 0, 4096);
+          cudaDeviceSynchronize();
+          cudaEventRecord(e0, s1); cudaEventRecord(e2, s2);
+          if (order == 0) sweep_kernel<true, true, 256, 4><<<148 * k1ctas, 256, 0, s1>>>(p2);
+          place_group_kernel<8192><<<ggrid, kGroupThreads, 0, s2>>>(ctl, rows, p.tile_slot, p.tile_count, tfirst, p.num_tiles, ids, out_rows, out_ids, none);
+          if (order == 1) sweep_kernel<true, true, 256, 4><<<148 * k1ctas, 256, 0, s1>>>(p2);
+          cudaEventRecord(e1, s1); cudaEventRecord(e3, s2);
+          cudaDeviceSynchronize();
+          float k1, k3; cudaEventElapsedTime(&k1, e0, e1); cudaEventElapsedTime(&k3, e2, e3);
+          float tot = std::max(k1, k3);
+          if (tot < best) { best = tot; bk1 = k1; bk3 = k3; }
+        }
+        printf("K1 x%d/SM || K3g, %s first:            total %8.3f ms (K1 %.3f, K3g %.3f)\n", k1ctas, order == 0 ? "K1" : "K3g", best, bk1, bk3);
+      }
+    }
+    {
+      float best = 1e9f;
+      for (int r = 0; r < 4; ++r) {
+        cudaDeviceSynchronize();
+        cudaEventRecord(e2, s2);
+        place_group_kernel<8192><<<ggrid, kGroupThreads, 0, s2>>>(ctl, rows, p.tile_slot, p.tile_count, tfirst, p.num_tiles, ids, out_rows, out_ids, none);
+        cudaEventRecord(e3, s2);
+        cudaDeviceSynchronize();
+        float k3; cudaEventElapsedTime(&k3, e2, e3);
+        best = std::min(best, k3);
+      }
+      printf("K3g alone                                 total %8.3f ms\n", best);
+    }
   }
   return 0;
 }
