@@ -342,19 +342,19 @@ __global__ void __launch_bounds__(kPlaceThreads) place_hits_kernel(const SweepCt
 }
 
 // K3g: the same placement, driven by the tiles in row order instead of by the hits in list order,
-// and fused with the cross-shard exchange.  One CTA owns kGroupTiles consecutive
-// tiles: their hits are consecutive in the row-ordered list (from tile_first[first tile]), so hit
-// h of the group is found with 7 compares against the group's prefix counts, read from the tile's
-// slot of the unordered list (coalesced), its TaskId gathered, and both written at base + h
-// (coalesced).  While the CTA waits for the 16-byte gathers it also builds the COMPACT form of the
+// and fused with the cross-shard exchange.  One CTA owns GT consecutive tiles
+// (GT = 1 and one hit per thread is what ships: measured fastest, see sweep_run): their hits are
+// consecutive in the row-ordered list (from tile_first[first tile]), so hit h of the group is
+// found with GT - 1 compares against the group's prefix counts, read from the tile's slot of the
+// unordered list (coalesced), its TaskId gathered, and both written at base + h (coalesced).  While the CTA waits for the 16-byte gathers it also builds the COMPACT form of the
 // hits — a 13-bit in-tile offset per hit plus one count per tile — in shared memory and stores it
 // with 16-byte vectors into `push`, which may be this GPU's memory or the root GPU's receive
 // buffer mapped over NVLink (tt_peer_open): the exchange then costs no pass of its own and no
 // collective, only a barrier after the kernel.  Remote stores are fire-and-forget; the vector
 // stores keep the NVLink packets at full size (2-byte scalar stores would send 64 B per warp).
-constexpr int kGroupTiles = 8;
+constexpr int kGroupTiles = 1;    // defaults of the template; sweep_run picks the shape
 constexpr int kGroupThreads = 256;
-constexpr int kGroupUnroll = 4;
+constexpr int kGroupUnroll = 1;
 constexpr int kGroupStage = 4096;  // offsets staged per group; denser groups store theirs directly
 
 struct PushTarget {
@@ -363,29 +363,29 @@ struct PushTarget {
   unsigned long long* count;  // [1] hits stored
 };
 
-template <int TILE_ROWS>
+template <int TILE_ROWS, int GT = kGroupTiles, int UNROLL = kGroupUnroll>
 __global__ void __launch_bounds__(kGroupThreads) place_group_kernel(const SweepCtl* ctl, const uint32_t* list,
                                                                     const uint32_t* tile_slot,
                                                                     const uint32_t* tile_count,
                                                                     const uint32_t* tile_first, uint32_t num_tiles,
                                                                     const uint4* task_id, uint32_t* out_rows,
                                                                     uint4* out_ids, PushTarget push) {
-  __shared__ uint32_t s_slot[kGroupTiles];
-  __shared__ uint32_t s_pre[kGroupTiles + 1];
+  __shared__ uint32_t s_slot[GT];
+  __shared__ uint32_t s_pre[GT + 1];
   __shared__ __align__(16) uint16_t s_off[kGroupStage + 8];
   const uint32_t tid = threadIdx.x;
-  const uint32_t t0 = blockIdx.x * kGroupTiles;
+  const uint32_t t0 = blockIdx.x * GT;
   if (tid < 32) {
     const uint32_t t = t0 + tid;
-    const bool live = tid < kGroupTiles && t < num_tiles;
+    const bool live = tid < GT && t < num_tiles;
     const uint32_t c = live ? tile_count[t] : 0u;
     uint32_t incl = c;
 #pragma unroll
-    for (int d = 1; d < kGroupTiles; d <<= 1) {
+    for (int d = 1; d < GT; d <<= 1) {
       uint32_t up = __shfl_up_sync(0xFFFFFFFFu, incl, d);
       if (tid >= (uint32_t)d) incl += up;
     }
-    if (tid < kGroupTiles) {
+    if (tid < GT) {
       s_slot[tid] = live ? tile_slot[t] : 0u;
       s_pre[tid + 1] = incl;
       if (live && push.tile_count) push.tile_count[t] = c;
@@ -399,32 +399,32 @@ __global__ void __launch_bounds__(kGroupThreads) place_group_kernel(const SweepC
     }
   }
   __syncthreads();
-  const uint32_t total = s_pre[kGroupTiles];
+  const uint32_t total = s_pre[GT];
   if (total == 0) return;
   const uint32_t base = tile_first[t0];
   const uint32_t shift = base & 7u;  // staged index = list index - (base - shift): 16-byte chunks line up
   const bool staged = push.off16 != nullptr && total <= (uint32_t)kGroupStage;
 
-  for (uint32_t h0 = tid; h0 < total; h0 += kGroupThreads * kGroupUnroll) {
-    uint32_t r[kGroupUnroll];
-    uint4 id[kGroupUnroll];
+  for (uint32_t h0 = tid; h0 < total; h0 += kGroupThreads * UNROLL) {
+    uint32_t r[UNROLL];
+    uint4 id[UNROLL];
 #pragma unroll
-    for (int j = 0; j < kGroupUnroll; ++j) {
+    for (int j = 0; j < UNROLL; ++j) {
       const uint32_t h = h0 + j * kGroupThreads;
       r[j] = 0;
       if (h < total) {
         uint32_t k = 0;
 #pragma unroll
-        for (int q = 1; q < kGroupTiles; ++q) k += h >= s_pre[q] ? 1u : 0u;
+        for (int q = 1; q < GT; ++q) k += h >= s_pre[q] ? 1u : 0u;
         r[j] = list[s_slot[k] + (h - s_pre[k])];
       }
     }
     if (out_ids) {
 #pragma unroll
-      for (int j = 0; j < kGroupUnroll; ++j) id[j] = ld_gather_v4(task_id + r[j]);
+      for (int j = 0; j < UNROLL; ++j) id[j] = ld_gather_v4(task_id + r[j]);
     }
 #pragma unroll
-    for (int j = 0; j < kGroupUnroll; ++j) {
+    for (int j = 0; j < UNROLL; ++j) {
       const uint32_t h = h0 + j * kGroupThreads;
       if (h < total) {
         const uint16_t off = (uint16_t)(r[j] & (TILE_ROWS - 1));

@@ -503,10 +503,25 @@ int32_t sweep_run(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_
     if (push || place_by_group()) {
       // K3g: tile-ordered placement, optionally fused with the push of the compact form (sweep.cuh)
       const tt::PushTarget none = {nullptr, nullptr, nullptr};
-      const unsigned ggrid = (num_tiles + tt::kGroupTiles - 1) / tt::kGroupTiles;
-      tt::place_group_kernel<TT_TILE_ROWS><<<ggrid, tt::kGroupThreads, 0, stream>>>(
-          t->ctl, t->hit_list, p.tile_slot, p.tile_count, tile_first, num_tiles, t->task_id, d_rows, d_ids,
-          push ? *push : none);
+      // Tiles per CTA and gathers per thread, measured on B200 at 25 M hits (plain placement): 1 tile x 1
+      // gather 0.439 ms, 2 x 2 0.464, 4 x 4 0.474, 8 x 4 0.488, 16 x 4 0.503, 1 tile on 128 threads x 2 0.470 —
+      // one tile per CTA, one hit per thread wins: all of a tile's gathers fall into one 128 KB span of the
+      // TaskId column and are in flight together.  With the push fused in (2 GPUs): 1 x 1 0.472 ms, 2 x 2
+      // 0.486, 4 x 4 0.497, 8 x 4 0.509 — the larger contiguous pieces of a bigger group do not pay.
+      // TT_PLACE_VARIANT / TT_PUSH_VARIANT (read once) pick another shape for A/B runs: 1 = 1 x 1,
+      // 2 = 2 x 2, 4 = 4 x 4, 8 = 8 x 4.
+      static const int plain_variant = [] { const char* e = getenv("TT_PLACE_VARIANT"); return e ? atoi(e) : 1; }();
+      static const int push_variant = [] { const char* e = getenv("TT_PUSH_VARIANT"); return e ? atoi(e) : 1; }();
+#define TT_PLACE_LAUNCH(GT, UN)                                                                                     \
+  tt::place_group_kernel<TT_TILE_ROWS, GT, UN><<<(num_tiles + GT - 1) / GT, tt::kGroupThreads, 0, stream>>>(            \
+      t->ctl, t->hit_list, p.tile_slot, p.tile_count, tile_first, num_tiles, t->task_id, d_rows, d_ids, push ? *push : none)
+      switch (push ? push_variant : plain_variant) {
+        case 2: TT_PLACE_LAUNCH(2, 2); break;
+        case 4: TT_PLACE_LAUNCH(4, 4); break;
+        case 8: TT_PLACE_LAUNCH(8, 4); break;
+        default: TT_PLACE_LAUNCH(1, 1); break;
+      }
+#undef TT_PLACE_LAUNCH
     } else {
       const int64_t per_cta = (int64_t)tt::kPlaceThreads * tt::kPlaceUnroll;
       const unsigned pgrid =
