@@ -50,7 +50,7 @@ __global__ void emit_rows_ids_kernel(const uint32_t* rows_sorted, const uint4* t
   if (i < n) {
     const uint32_t r = rows_sorted[i];
     rows_out[i] = r;
-    ids_out[i] = ld_gather_v4(task_id + r);
+    if (ids_out) ids_out[i] = ld_gather_v4(task_id + r);
   }
 }
 

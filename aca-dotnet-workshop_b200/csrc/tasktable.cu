@@ -145,6 +145,12 @@ struct tt_table {
     uint32_t n = 0;
     bool ready = false;
   } esc[3][2];
+  // tt_tick_host: transfer streams, events and the two device staging buffers of the pipelined tick
+  cudaStream_t tick_up = nullptr, tick_down = nullptr;
+  cudaEvent_t tick_up_ev[2] = {nullptr, nullptr}, tick_down_ev[2] = {nullptr, nullptr}, tick_done_ev = nullptr;
+  uint32_t* tick_rows[2] = {nullptr, nullptr};
+  void* tick_ids[2] = {nullptr, nullptr};
+  int64_t tick_cap[2] = {0, 0};
   uint64_t* json_blocks = nullptr;  // K6 block sums / bases
   int64_t json_blocks_cap = 0;
   uint64_t* json_plan = nullptr;    // K6 plan: 5 words per record, grow-only
@@ -415,7 +421,7 @@ int sweep_ctas_per_sm() {
 // Launches the sweep kernel over rows [first_row, n) on `stream`, waits, fills *st.
 int32_t sweep_run(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_ticks, int64_t run_at_utc_ticks,
                   int64_t first_row, uint32_t* d_rows, uint4* d_ids, int64_t cap, tt_sweep_stats* st,
-                  cudaStream_t stream, const tt::PushTarget* push = nullptr) {
+                  cudaStream_t stream, const tt::PushTarget* push = nullptr, int64_t row_end = -1) {
   memset(st, 0, sizeof *st);
   if (mode != TT_MODE_FAKE && mode != TT_MODE_STORE) return fail(TT_ERR_ARG, "mode must be TT_MODE_FAKE or TT_MODE_STORE");
   uint32_t yesterday = 0;
@@ -438,7 +444,16 @@ int32_t sweep_run(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_
     return TT_OK;
   }
   const uint32_t first_tile = (uint32_t)(first_row / TT_TILE_ROWS);
-  const uint32_t num_tiles = (uint32_t)(t->n_pad / TT_TILE_ROWS) - first_tile;
+  uint32_t num_tiles = (uint32_t)(t->n_pad / TT_TILE_ROWS) - first_tile;
+  if (row_end >= 0) {  // a chunk [first_row, row_end) of the table, whole tiles
+    if (row_end % TT_TILE_ROWS != 0 || row_end < first_row || row_end > t->n_pad)
+      return fail(TT_ERR_ARG, "row_end must be a tile multiple in [first_row, padded rows]");
+    num_tiles = (uint32_t)((row_end - first_row) / TT_TILE_ROWS);
+    if (num_tiles == 0) {
+      st->resume_row = row_end;
+      return TT_OK;
+    }
+  }
 
   // scratch for the unordered hit list K1 writes before K3 puts it in row order
   const bool listing = d_rows != nullptr || push != nullptr;
@@ -541,7 +556,7 @@ int32_t sweep_run(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_
   st->n_listed = (int64_t)t->h_ctl->cursor;
   const bool complete = t->h_ctl->stored == ~0ull;
   st->n_stored = listing ? (complete ? st->n_listed : (int64_t)t->h_ctl->stored) : 0;
-  st->resume_row = complete ? t->n : first_row;
+  st->resume_row = complete ? (row_end >= 0 ? std::min<int64_t>(row_end, t->n) : t->n) : first_row;
   st->n_marked = p.mark_enable ? (listing ? st->n_stored : st->n_listed) : 0;
   if (!complete)
     return fail(TT_ERR_CAPACITY, "%lld hits do not fit in %lld (%lld stored%s)", (long long)st->n_listed,
@@ -718,6 +733,15 @@ int32_t tt_destroy(tt_table* t) {
     cudaEventDestroy(t->ev0);
     cudaEventDestroy(t->ev1);
     cudaEventDestroy(t->ev2);
+    for (int k = 0; k < 2; ++k) {
+      cudaFree(t->tick_rows[k]);
+      cudaFree(t->tick_ids[k]);
+      if (t->tick_up_ev[k]) cudaEventDestroy(t->tick_up_ev[k]);
+      if (t->tick_down_ev[k]) cudaEventDestroy(t->tick_down_ev[k]);
+    }
+    if (t->tick_done_ev) cudaEventDestroy(t->tick_done_ev);
+    if (t->tick_up) cudaStreamDestroy(t->tick_up);
+    if (t->tick_down) cudaStreamDestroy(t->tick_down);
     cudaStreamDestroy(t->stream);
   }
   delete t;
@@ -2472,6 +2496,148 @@ extern "C" int32_t tt_load_documents(tt_table* t, const void* docs, const uint64
   stats->n_creators = k[1];
   stats->n_assignees = k[2];
   stats->text_bytes = (int64_t)bytes;
+  return TT_OK;
+}
+
+// ---- the cron tick for a caller whose state and results live in host memory ---------------------------
+namespace {
+
+// (Re)allocates staging buffer `buf` of the pipelined tick for `want` hits, keeping its first `keep`.
+int32_t tick_stage_grow(tt_table* t, int buf, int64_t want, int64_t keep, bool with_ids) {
+  uint32_t* rows = nullptr;
+  void* ids = nullptr;
+  TT_CUDA(cudaMalloc(&rows, (size_t)want * 4));
+  if (with_ids) {
+    cudaError_t e = cudaMalloc(&ids, (size_t)want * 16);
+    if (e != cudaSuccess) {
+      cudaFree(rows);
+      TT_CUDA(e);
+    }
+  }
+  if (keep > 0) {
+    cudaMemcpyAsync(rows, t->tick_rows[buf], (size_t)keep * 4, cudaMemcpyDeviceToDevice, t->stream);
+    if (with_ids && t->tick_ids[buf]) cudaMemcpyAsync(ids, t->tick_ids[buf], (size_t)keep * 16, cudaMemcpyDeviceToDevice, t->stream);
+    cudaStreamSynchronize(t->stream);
+  }
+  cudaFree(t->tick_rows[buf]);
+  cudaFree(t->tick_ids[buf]);
+  t->tick_rows[buf] = rows;
+  t->tick_ids[buf] = ids;
+  t->tick_cap[buf] = want;
+  return TT_OK;
+}
+
+}  // namespace
+
+extern "C" int32_t tt_tick_host(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_ticks, int64_t run_at_utc_ticks,
+                                const uint8_t* h_completed_bits, const uint8_t* h_overdue_bits, uint32_t* h_rows,
+                                uint8_t* h_ids16, int64_t cap, int32_t chunks, tt_sweep_stats* stats) {
+  if (!t || !stats || !h_rows || cap < 0) return fail(TT_ERR_ARG, "bad argument");
+  memset(stats, 0, sizeof *stats);
+  if (chunks <= 0) chunks = 8;
+  std::lock_guard<std::mutex> lk(t->mu);
+  DeviceGuard g(t->device);
+  if (t->n == 0) return TT_OK;
+  const bool with_ids = h_ids16 != nullptr;
+  // lazily created: two transfer streams and their events
+  if (!t->tick_up) {
+    TT_CUDA(cudaStreamCreateWithFlags(&t->tick_up, cudaStreamNonBlocking));
+    TT_CUDA(cudaStreamCreateWithFlags(&t->tick_down, cudaStreamNonBlocking));
+    for (int k = 0; k < 2; ++k) {
+      TT_CUDA(cudaEventCreateWithFlags(&t->tick_up_ev[k], cudaEventDisableTiming));
+      TT_CUDA(cudaEventCreateWithFlags(&t->tick_down_ev[k], cudaEventDisableTiming));
+    }
+    TT_CUDA(cudaEventCreateWithFlags(&t->tick_done_ev, cudaEventDisableTiming));
+  }
+  const int64_t tiles = t->n_pad / TT_TILE_ROWS;
+  const int64_t chunk_rows = (tiles + chunks - 1) / chunks * TT_TILE_ROWS;
+  // two device staging buffers (grow-only, kept between calls); a first guess of 1/16 of a chunk's rows
+  int32_t rc = TT_OK;
+  for (int k = 0; k < 2 && rc == TT_OK; ++k)
+    if (t->tick_cap[k] < std::max<int64_t>(65536, chunk_rows / 16) || (with_ids && !t->tick_ids[k]))
+      rc = tick_stage_grow(t, k, std::max<int64_t>({65536, chunk_rows / 16, t->tick_cap[k]}), 0, with_ids);
+  if (rc) return rc;
+  // work that may still be running on the table's own stream comes first
+  TT_CUDA(cudaEventRecord(t->tick_done_ev, t->stream));
+  TT_CUDA(cudaStreamWaitEvent(t->tick_up, t->tick_done_ev, 0));
+  auto upload = [&](int c) -> int32_t {  // flag planes of chunk c, host -> device, on the upload stream
+    const int64_t r0 = (int64_t)c * chunk_rows, r1 = std::min<int64_t>(r0 + chunk_rows, t->n_pad);
+    if (r0 < r1 && r0 < t->n) {
+      const size_t b0 = (size_t)r0 / 8, nb = (size_t)(std::min<int64_t>(r1, t->n) + 7) / 8 - b0;
+      if (h_completed_bits)
+        TT_CUDA(cudaMemcpyAsync(reinterpret_cast<uint8_t*>(t->completed) + b0, h_completed_bits + b0, nb, cudaMemcpyHostToDevice, t->tick_up));
+      if (h_overdue_bits)
+        TT_CUDA(cudaMemcpyAsync(reinterpret_cast<uint8_t*>(t->overdue) + b0, h_overdue_bits + b0, nb, cudaMemcpyHostToDevice, t->tick_up));
+    }
+    TT_CUDA(cudaEventRecord(t->tick_up_ev[c & 1], t->tick_up));
+    return TT_OK;
+  };
+  int64_t total = 0;
+  bool overflow = false;
+  if ((rc = upload(0))) return rc;
+  for (int c = 0; c < chunks; ++c) {
+    const int64_t r0 = (int64_t)c * chunk_rows, r1 = std::min<int64_t>(r0 + chunk_rows, t->n_pad);
+    if (r0 >= r1) break;
+    TT_CUDA(cudaStreamWaitEvent(t->stream, t->tick_up_ev[c & 1], 0));
+    if (c + 1 < chunks && (rc = upload(c + 1))) return rc;  // the next chunk's planes travel while this one is swept
+    const int buf = c & 1;
+    // the staging buffer is free once the download that used it two chunks ago has finished
+    TT_CUDA(cudaEventSynchronize(t->tick_down_ev[buf]));
+    // Sweep the chunk into the staging buffer.  If its hits do not fit, the buffer is regrown: a listing
+    // sweep changed nothing and starts again; a marking sweep has stored and marked a row-ordered subset,
+    // which is kept while the rest is appended, and the two runs are merged by a sort afterwards.
+    int64_t have = 0, listed = 0;
+    bool merged = false;
+    for (int pass = 0;; ++pass) {
+      if (pass == 16) return fail(TT_ERR_STATE, "tick did not converge on chunk %d", c);
+      tt_sweep_stats st;
+      rc = sweep_run(t, mode, flags, today_local_ticks, run_at_utc_ticks, r0, t->tick_rows[buf] + have,
+                     with_ids ? (uint4*)t->tick_ids[buf] + have : nullptr, t->tick_cap[buf] - have, &st, t->stream, nullptr, r1);
+      if (rc != TT_OK && rc != TT_ERR_CAPACITY) return rc;
+      stats->kernel_ms += st.kernel_ms;
+      stats->sweep_ms += st.sweep_ms;
+      stats->gather_ms += st.gather_ms;
+      stats->launches += st.launches;
+      stats->n_marked += st.n_marked;
+      if (rc == TT_OK) {
+        have += st.n_stored;
+        listed += st.n_listed;
+        break;
+      }
+      const bool mutated = st.n_marked > 0;
+      if (mutated) {
+        have += st.n_stored;
+        listed += st.n_stored;
+        merged = true;
+      }
+      const int64_t want = have + (st.n_listed - (mutated ? st.n_stored : 0)) + 1024;
+      if ((rc = tick_stage_grow(t, buf, want, have, with_ids))) return rc;
+    }
+    if (merged && have > 1) {
+      int e = tt::sort_rows_and_gather(t->stream, t->sort, t->task_id, t->tick_rows[buf], (uint4*)t->tick_ids[buf], have);
+      if (e != 0) return fail(TT_ERR_CUDA, "sort_rows_and_gather: %s", cudaGetErrorString((cudaError_t)e));
+      stats->launches += 2 + 4 * 4;
+    }
+    stats->n_listed += listed;
+    const int64_t room = std::max<int64_t>(0, cap - total), take = std::min(have, room);
+    if (take < have) overflow = true;
+    if (take > 0) {
+      TT_CUDA(cudaEventRecord(t->tick_done_ev, t->stream));  // sweep_run has synchronised; the event orders the copy
+      TT_CUDA(cudaStreamWaitEvent(t->tick_down, t->tick_done_ev, 0));
+      TT_CUDA(cudaMemcpyAsync(h_rows + total, t->tick_rows[buf], (size_t)take * 4, cudaMemcpyDeviceToHost, t->tick_down));
+      if (with_ids)
+        TT_CUDA(cudaMemcpyAsync(h_ids16 + (size_t)total * 16, t->tick_ids[buf], (size_t)take * 16, cudaMemcpyDeviceToHost, t->tick_down));
+    }
+    total += take;
+    stats->n_stored = total;
+    TT_CUDA(cudaEventRecord(t->tick_down_ev[buf], t->tick_down));
+  }
+  TT_CUDA(cudaStreamSynchronize(t->tick_down));
+  TT_CUDA(cudaStreamSynchronize(t->tick_up));
+  stats->resume_row = t->n;
+  if (overflow)
+    return fail(TT_ERR_CAPACITY, "%lld hits do not fit in the host buffers (%lld); the first %lld were delivered",
+                (long long)stats->n_listed, (long long)cap, (long long)total);
   return TT_OK;
 }
 

@@ -54,7 +54,7 @@ EXPORTS = [
     "tt_sweep_push", "tt_peer_alloc", "tt_peer_open", "tt_peer_close", "tt_peer_free",
     "tt_load_payload", "tt_generate_payload", "tt_result_json", "tt_json_size", "tt_json_copy", "tt_json_device",
     "tt_json_free", "tt_last_json_stats", "tt_json_offsets", "tt_load_documents",
-    "tt_get_due_on_or_before", "tt_sweep_backlog",
+    "tt_get_due_on_or_before", "tt_sweep_backlog", "tt_tick_host",
 ]
 
 
@@ -242,6 +242,7 @@ def lib():
     L.tt_last_json_stats.argtypes = [vp, P(JsonStats)]
     L.tt_get_due_on_or_before.argtypes = [vp, i32, i64, P(vp)]
     L.tt_sweep_backlog.argtypes = [vp, i32, i64, i64, P(vp), P(i64)]
+    L.tt_tick_host.argtypes = [vp, i32, i32, i64, i64, vp, vp, vp, vp, i64, i32, P(SweepStats)]
     L.tt_json_offsets.argtypes = [vp, vp]
     L.tt_load_documents.argtypes = [vp, vp, vp, i64, i32, P(IngestStats)]
     for name in EXPORTS:
@@ -610,6 +611,17 @@ class TaskTable:
         st = SweepStats()
         rc = lib().tt_sweep_push(self._h, mode, flags, today, run_at, d_rows, d_ids, cap, C.byref(target), C.byref(st),
                                  stream)
+        _check(rc, allow=(TT_ERR_CAPACITY,) if allow_capacity else ())
+        return st, rc
+
+    def tick_host(self, mode, flags, h_completed, h_overdue, h_rows, h_ids, cap, chunks=0, today=DEFAULT_TODAY,
+                  run_at=DEFAULT_RUN_AT, allow_capacity=False):
+        """tt_tick_host: the tick with the flag planes coming from host memory and the hits going to host
+        memory, transfers pipelined with the kernels.  All four buffers are host ADDRESSES (ints; pinned
+        memory recommended), h_completed / h_overdue / h_ids may be None.  -> (SweepStats, rc)."""
+        st = SweepStats()
+        rc = lib().tt_tick_host(self._h, mode, flags, today, run_at, h_completed, h_overdue, h_rows, h_ids, cap, chunks,
+                                C.byref(st))
         _check(rc, allow=(TT_ERR_CAPACITY,) if allow_capacity else ())
         return st, rc
 

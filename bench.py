@@ -49,6 +49,7 @@ def parse():
     ap.add_argument("--cpu-sample-rows", type=int, default=8_000_000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--e2e-chunks", type=int, default=0, help="row ranges tt_tick_host pipelines over (0 = the library's 8)")
     ap.add_argument("--workload", default="sweep", choices=["sweep", "sweep10m", "creator", "mixed", "json", "ingest"],
                     help="sweep = the headline (BASELINE.json metric); the others are the remaining configs of "
                          "SURVEY.md 8(d): sweep10m = config 2, creator = config 4, mixed = config 5 (per GPU)")
@@ -291,6 +292,9 @@ def run_b200(args):
     value = n_total * args.steps / (total_ms * 1e-3)
 
     # ---- e2e: the reference-facing call with host buffers on both sides ----
+    # tt_tick_host: both flag planes come from pinned host memory, the listed rows + TaskIds go back to
+    # pinned host memory; the library pipelines upload / kernels / download over chunks of the table.
+    # Beside it, the same work as separate calls (tt_restore_flags, tt_sweep, tt_result_rows / _ids).
     e2e = None
     if not args.no_e2e:
         h_comp = torch.empty(nbytes, dtype=torch.uint8).pin_memory()
@@ -300,28 +304,45 @@ def run_b200(args):
         h_rows = torch.empty(cap, dtype=torch.int32).pin_memory()
         h_ids = torch.empty((cap, 16), dtype=torch.uint8).pin_memory()
         e_steps = max(1, min(args.steps, 10))
-        e_total, d2h = 0.0, 0
-        for i in range(2 + e_steps):
-            barrier()
-            t0 = time.perf_counter()
-            # host -> device: the mutable task state (both flag planes) arrives from pinned host memory
+
+        def pipelined():
+            st, _ = table.tick_host(tt.MODE_STORE, tt.SWEEP_MARK, h_comp.data_ptr(), h_over.data_ptr(), h_rows.data_ptr(),
+                                    h_ids.data_ptr(), cap, args.e2e_chunks)
+            return st.n_stored
+
+        def sequential():
             tt._check(tt.lib().tt_restore_flags(table._h, h_comp.data_ptr(), h_over.data_ptr()))
             res, n_marked, _ = table.sweep(tt.MODE_STORE)
-            # device -> host: the listed TaskIds and rows, as the controller would serialise them
             tt._check(tt.lib().tt_result_rows(res._h, h_rows.data_ptr()))
             tt._check(tt.lib().tt_result_ids(res._h, h_ids.data_ptr()))
             cnt = res.count
             res.free()
-            barrier()
-            if i >= 2:
-                e_total += time.perf_counter() - t0
-                d2h = cnt * 20 + 8
-        et = torch.tensor([e_total], dtype=torch.float64, device=dev)
-        if world > 1:
-            dist.all_reduce(et, op=dist.ReduceOp.MAX)
-        e2e = {"value": n_total * e_steps / float(et.item()), "unit": UNIT, "h2d_bytes_per_step": 2 * nbytes,
-               "d2h_bytes_per_step": d2h, "steps": e_steps,
-               "what": "tt_restore_flags(pinned host planes) + tt_sweep + tt_result_rows/ids into pinned host, per rank"}
+            return cnt
+
+        def timed(fn):
+            total, cnt = 0.0, 0
+            for i in range(2 + e_steps):
+                barrier()
+                t0 = time.perf_counter()
+                cnt = fn()
+                barrier()
+                if i >= 2:
+                    total += time.perf_counter() - t0
+            et = torch.tensor([total], dtype=torch.float64, device=dev)
+            if world > 1:
+                dist.all_reduce(et, op=dist.ReduceOp.MAX)
+            return n_total * e_steps / float(et.item()), cnt
+
+        v_pipe, cnt = timed(pipelined)
+        assert cnt == hits, (cnt, hits)
+        v_seq, cnt2 = timed(sequential)
+        assert cnt2 == hits, (cnt2, hits)
+        e2e = {"value": v_pipe, "unit": UNIT, "h2d_bytes_per_step": 2 * nbytes, "d2h_bytes_per_step": cnt * 20,
+               "steps": e_steps, "chunks": args.e2e_chunks or 8,
+               "what": "tt_tick_host per rank: pinned host flag planes -> device, the tick, hit rows + TaskIds -> pinned host, "
+                       "the three stages pipelined over chunks of the table on three streams",
+               "sequential": {"value": v_seq, "what": "the same bytes as separate calls: tt_restore_flags + tt_sweep + "
+                                                      "tt_result_rows + tt_result_ids"}}
 
     if rank == 0:
         peak, peak_src = peaks()

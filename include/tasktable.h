@@ -235,6 +235,22 @@ int32_t tt_sweep_device(tt_table* t, int32_t mode, int32_t flags, int64_t today_
                         int64_t run_at_utc_ticks, int64_t first_row, uint32_t* d_rows, void* d_ids, int64_t cap,
                         tt_sweep_stats* h_stats, void* stream);
 
+/* ---- the tick for a caller whose task state and results live in HOST memory -------------------
+ * The whole of Svc/Controllers/ScheduledTasksManagerController.cs:19-46 as tt_sweep does it, but with
+ * the two flag planes arriving from host memory and the listed rows + TaskIds delivered into host
+ * memory, the three stages pipelined over `chunks` row ranges of the table (0 = 8): while chunk c is
+ * swept on the table's stream, chunk c+1's planes are uploaded on a second stream and chunk c-1's
+ * hits are downloaded on a third, so the PCIe link works in both directions under the kernels.
+ * h_completed_bits / h_overdue_bits: the layout of tt_snapshot_flags, either may be NULL (that plane
+ * stays as it is on the device); h_rows: uint32[cap]; h_ids16: 16*cap bytes or NULL.  Use pinned
+ * memory: pageable buffers make the copies synchronous and the stages stop overlapping.
+ * The rows arrive in ascending row order (tt_sweep's order).  stats->n_listed / n_stored / n_marked as
+ * in tt_sweep_device; the timing fields are sums over the chunks.  TT_ERR_CAPACITY if the hits do not
+ * fit in cap (the first cap are delivered; a marking tick has marked all it listed). */
+int32_t tt_tick_host(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_ticks, int64_t run_at_utc_ticks,
+                     const uint8_t* h_completed_bits, const uint8_t* h_overdue_bits, uint32_t* h_rows, uint8_t* h_ids16,
+                     int64_t cap, int32_t chunks, tt_sweep_stats* stats);
+
 /* Device addresses of the table's columns, for callers that exchange shard results over
  * NCCL or reset state between benchmark steps.  Any out pointer may be NULL. */
 typedef struct tt_device_view {
