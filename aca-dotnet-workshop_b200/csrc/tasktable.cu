@@ -521,12 +521,14 @@ int32_t sweep_run(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_
       // Tiles per CTA and gathers per thread, measured on B200 at 25 M hits (plain placement): 1 tile x 1
       // gather 0.439 ms, 2 x 2 0.464, 4 x 4 0.474, 8 x 4 0.488, 16 x 4 0.503, 1 tile on 128 threads x 2 0.470 —
       // one tile per CTA, one hit per thread wins: all of a tile's gathers fall into one 128 KB span of the
-      // TaskId column and are in flight together.  With the push fused in (2 GPUs): 1 x 1 0.472 ms, 2 x 2
-      // 0.486, 4 x 4 0.497, 8 x 4 0.509 — the larger contiguous pieces of a bigger group do not pay.
-      // TT_PLACE_VARIANT / TT_PUSH_VARIANT (read once) pick another shape for A/B runs: 1 = 1 x 1,
-      // 2 = 2 x 2, 4 = 4 x 4, 8 = 8 x 4.
+      // TaskId column and are in flight together.  With the push fused in, the shape that is best on
+      // one GPU is the worst at scale: K3g time on 2 GPUs 1 x 1 0.472 ms, 8 x 4 0.509; but the whole
+      // tick on 8 GPUs (rank 0 takes the stores of 7 peers) 1 x 1 1.683 ms, 2 x 2 1.511, 4 x 4 1.393,
+      // 8 x 4 1.349 — larger contiguous pieces mean fewer, larger NVLink packets into rank 0, so the
+      // push keeps 8 x 4.  TT_PLACE_VARIANT / TT_PUSH_VARIANT (read once) pick another shape for A/B
+      // runs: 1 = 1 x 1, 2 = 2 x 2, 4 = 4 x 4, 8 = 8 x 4.
       static const int plain_variant = [] { const char* e = getenv("TT_PLACE_VARIANT"); return e ? atoi(e) : 1; }();
-      static const int push_variant = [] { const char* e = getenv("TT_PUSH_VARIANT"); return e ? atoi(e) : 1; }();
+      static const int push_variant = [] { const char* e = getenv("TT_PUSH_VARIANT"); return e ? atoi(e) : 8; }();
 #define TT_PLACE_LAUNCH(GT, UN)                                                                                     \
   tt::place_group_kernel<TT_TILE_ROWS, GT, UN><<<(num_tiles + GT - 1) / GT, tt::kGroupThreads, 0, stream>>>(            \
       t->ctl, t->hit_list, p.tile_slot, p.tile_count, tile_first, num_tiles, t->task_id, d_rows, d_ids, push ? *push : none)

@@ -90,6 +90,7 @@ class TaskTableLibrary {
     TT_BIND(tt_result_free);
     TT_BIND(tt_get_by_id); TT_BIND(tt_insert_task); TT_BIND(tt_update_task); TT_BIND(tt_mark_completed);
     TT_BIND(tt_delete_task);
+    TT_BIND(tt_load_payload); TT_BIND(tt_result_json); TT_BIND(tt_json_size); TT_BIND(tt_json_copy); TT_BIND(tt_json_free);
 #undef TT_BIND
   }
   ~TaskTableLibrary() { if (h_) dlclose(h_); }
@@ -111,6 +112,11 @@ class TaskTableLibrary {
   decltype(&::tt_update_task) tt_update_task;
   decltype(&::tt_mark_completed) tt_mark_completed;
   decltype(&::tt_delete_task) tt_delete_task;
+  decltype(&::tt_load_payload) tt_load_payload;
+  decltype(&::tt_result_json) tt_result_json;
+  decltype(&::tt_json_size) tt_json_size;
+  decltype(&::tt_json_copy) tt_json_copy;
+  decltype(&::tt_json_free) tt_json_free;
 
  private:
   void* must(const char* name) {
@@ -157,6 +163,12 @@ class GpuTasksManager : public ITasksManager {
     tt_soa_view v{n, ids.data(), created.data(), due.data(), comp.data(), over.data(), ref.data(),
                   (uint32_t)creators_.size(), off.data(), pool.data()};
     check(lib_->tt_load_soa(table_, &v));
+    // TaskName / TaskAssignedTo go to the device too (dictionary-encoded), so that a controller can send
+    // the device-made response text instead of materialising TaskModel objects (OverdueTasksGet below)
+    Encoded names = encode(names_), assignees = encode(assignees_);
+    tt_strings_view nv{names.ref.data(), (uint32_t)(names.off.size() - 1), names.off.data(), names.pool.data()};
+    tt_strings_view av{assignees.ref.data(), (uint32_t)(assignees.off.size() - 1), assignees.off.data(), assignees.pool.data()};
+    check(lib_->tt_load_payload(table_, &nv, &av));
   }
   ~GpuTasksManager() override { if (table_) lib_->tt_destroy(table_); }
 
@@ -241,6 +253,25 @@ class GpuTasksManager : public ITasksManager {
   }
 
   // The whole tick as one device pass (tt_sweep).  Returns the listed tasks; *n_marked = rows set.
+  // The body OverdueTasksController.Get (Api/Controllers/OverdueTasksController.cs:22-26) sends for
+  // `return await _tasksManager.GetYesterdaysDueTasks();`, written on the device: no TaskModel objects
+  // are built on the host.  Tasks created after construction print "" for TaskName / TaskAssignedTo.
+  std::string OverdueTasksGet(int32_t local_offset_min = 0) {
+    tt_result* r = nullptr;
+    check(lib_->tt_get_yesterdays_due(table_, mode_, clock_->today_local_ticks, &r));
+    tt_json* j = nullptr;
+    int32_t rc = lib_->tt_result_json(r, TT_JSON_RESPONSE, local_offset_min, &j);
+    lib_->tt_result_free(r);
+    check(rc);
+    int64_t n = 0;
+    check(lib_->tt_json_size(j, &n));
+    std::string body((size_t)n, '\0');
+    rc = lib_->tt_json_copy(j, &body[0]);
+    lib_->tt_json_free(j);
+    check(rc);
+    return body;
+  }
+
   std::vector<TaskModel> SweepOverdueTasks(int64_t* n_marked) {
     tt_result* r = nullptr;
     int32_t rc = lib_->tt_sweep(table_, mode_, clock_->today_local_ticks, clock_->utc_now_ticks, &r, n_marked);
@@ -263,6 +294,26 @@ class GpuTasksManager : public ITasksManager {
     return g;
   }
   uint64_t guid_state_ = 0x1234;
+
+  struct Encoded {
+    std::vector<uint32_t> ref, off{0};
+    std::vector<uint8_t> pool;
+  };
+  static Encoded encode(const std::vector<std::string>& values) {
+    Encoded e;
+    std::map<std::string, uint32_t> dict;
+    for (const std::string& s : values) {
+      auto it = dict.find(s);
+      if (it == dict.end()) {
+        it = dict.emplace(s, (uint32_t)(e.off.size() - 1)).first;
+        e.pool.insert(e.pool.end(), s.begin(), s.end());
+        e.off.push_back((uint32_t)e.pool.size());
+      }
+      e.ref.push_back(it->second);
+    }
+    if (e.pool.empty()) e.pool.push_back(0);
+    return e;
+  }
 
   void check(int32_t rc) {
     if (rc == TT_OK) return;

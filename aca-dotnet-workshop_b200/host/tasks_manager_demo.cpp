@@ -50,6 +50,7 @@ int main(int argc, char** argv) {
       printf("%s due:", mode == TT_MODE_STORE ? "STORE" : "FAKE");
       for (const TaskModel& t : manager.GetYesterdaysDueTasks()) printf(" %s", t.TaskName.c_str());
       printf("\n");
+      if (mode == TT_MODE_STORE) printf("GET api/overduetasks: %s\n", manager.OverdueTasksGet().c_str());
       try {
         size_t n = CheckOverDueTasksJob(manager, clock);
         printf("cron marked %zu\n", n);

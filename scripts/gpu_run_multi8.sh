@@ -9,9 +9,11 @@ run() { # name, nproc, extra args
   name=$1; n=$2; shift 2
   timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 29533 bench.py --gpus $n --steps 10 --warmup 3 "$@" > gpurun_out/$name.log 2>&1; echo "rc=$?" >> gpurun_out/$name.log
 }
+timeout 600 python bench.py --steps 10 --warmup 3 --no-cpu-baseline > gpurun_out/bench_n1.log 2>&1
 for n in 2 4 8; do
   if [ $n -le $N ]; then run bench_n$n $n; fi
 done
+TT_PUSH_VARIANT=8 run bench_push8x4_n$N $N --no-e2e
 run bench_compact_n$N $N --no-e2e --exchange compact
 run bench_none_n$N $N --no-e2e --exchange none
 run bench_strong_n$N $N --no-e2e --scaling strong

@@ -9,7 +9,9 @@ pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 PKG = os.path.join(ROOT, "aca-dotnet-workshop_b200")
 
+# the GET body is what the oracle's restatement of the MVC serializer prints for Task 8, Task 0, Task 9
 EXPECTED = """STORE due: Task 8 Task 0 Task 9
+GET api/overduetasks: [{"taskId":"09090909-0909-4009-8009-090909090909","taskName":"Task 8","taskCreatedBy":"ann@x.io","taskCreatedOn":"2026-10-07T00:00:00.000001Z","taskDueDate":"2026-11-05T00:00:00","taskAssignedTo":"x@y.z","isCompleted":false,"isOverDue":false},{"taskId":"01010101-0101-4001-8001-010101010101","taskName":"Task 0","taskCreatedBy":"ann@x.io","taskCreatedOn":"2026-10-07T00:00:00.00005Z","taskDueDate":"2026-11-05T00:00:00","taskAssignedTo":"x@y.z","isCompleted":false,"isOverDue":false},{"taskId":"0a0a0a0a-0a0a-400a-800a-0a0a0a0a0a0a","taskName":"Task 9","taskCreatedBy":"bob@x.io","taskCreatedOn":"2026-10-07T00:00:00.00005Z","taskDueDate":"2026-11-05T00:00:00","taskAssignedTo":"x@y.z","isCompleted":false,"isOverDue":false}]
 cron marked 3
 after:
 ann: Task 0* Task 4 Task 2 Task 10 Task 6 Task 8*
