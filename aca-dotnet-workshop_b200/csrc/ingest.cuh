@@ -271,7 +271,43 @@ __device__ int member_of(const uint8_t* name, int len) {
 // quote.  Returns the member number, -1 unknown, -2 bad string, -3 "has an escape, take the slow path".
 __constant__ char kMemberNames[8][16] = {"taskid", "taskname", "taskcreatedby", "taskcreatedon", "taskduedate",
                                          "taskassignedto", "iscompleted", "isoverdue"};
+__constant__ int kMemberLens[8] = {6, 8, 13, 13, 11, 14, 11, 9};
 __device__ int member_fast(const uint8_t* p, const uint8_t* end, const uint8_t** after) {
+  // One pass for the names the reference writes: "task?..." / "is?..." — the character after the
+  // common prefix names the only candidate and so the length; the closing quote must sit right
+  // behind it and every character must match.  Anything else takes the general route below.
+  if (end - p >= 16) {
+    int m = -1;
+    const uint32_t c0 = p[0] | 0x20u;
+    if (c0 == 't') {
+      switch (p[4] | 0x20u) {
+        case 'i': m = 0; break;
+        case 'n': m = 1; break;
+        case 'c': m = (p[12] | 0x20u) == 'y' ? 2 : 3; break;
+        case 'd': m = 4; break;
+        case 'a': m = 5; break;
+        default: break;
+      }
+    } else if (c0 == 'i') {
+      m = (p[2] | 0x20u) == 'c' ? 6 : 7;
+    }
+    if (m >= 0) {
+      const int len = kMemberLens[m];
+      if (p[len] == '"') {
+        bool same = true;
+        for (int j = 0; j < len; ++j) {
+          uint32_t c = p[j];
+          if (c >= 'A' && c <= 'Z') c |= 0x20;
+          same = same && c == (uint8_t)kMemberNames[m][j];
+        }
+        if (same) {
+          *after = p + len + 1;
+          return m;
+        }
+      }
+    }
+  }
+  // general route: find the closing quote, then compare against the candidate of that length
   const uint8_t* q = p;
   while (q < end) {
     const uint32_t c = *q;
@@ -484,6 +520,10 @@ __global__ void __launch_bounds__(128) doc_parse_kernel(uint8_t* text, const uin
     }
     // taskId and the two dates: short strings parsed from a local copy
     if (*p != '"') { status = kDocType; continue; }
+    if (m == 0 && end - p > 37 && p[37] == '"' && parse_guid(p + 1, 36, &id)) {  // the usual 36 plain characters
+      p += 38;
+      continue;
+    }
     const int plain = plain_string_len(p + 1, end, 48);
     if (plain >= 0) {  // no escape inside: parsed where it lies
       if (m == 0) {
