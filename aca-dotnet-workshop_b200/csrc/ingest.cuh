@@ -649,25 +649,28 @@ __device__ __forceinline__ uint32_t dict_is_head(const unsigned long long* keys,
   return same_string(text, start[a], len[a], start[b], len[b]) ? 0u : 1u;
 }
 
+// The head test is the expensive part (two scattered strings per position): it is done once here,
+// kept as one byte per position, and only read again by dict_assign_kernel.
 __global__ void __launch_bounds__(kScanBlock) dict_head_sum_kernel(const unsigned long long* keys, const uint32_t* docs,
                                                                    const uint8_t* text, const uint64_t* start,
-                                                                   const uint32_t* len, int64_t n, uint64_t* block_sum) {
+                                                                   const uint32_t* len, int64_t n, uint8_t* head,
+                                                                   uint64_t* block_sum) {
   __shared__ uint32_t s_warp[32];
   const int64_t pos = (int64_t)blockIdx.x * kScanBlock + threadIdx.x;
   const uint32_t h = pos < n ? dict_is_head(keys, docs, text, start, len, pos) : 0u;
+  if (pos < n) head[pos] = (uint8_t)h;
   uint32_t tot;
   block_exclusive_scan(h, s_warp, &tot);
   if (threadIdx.x == 0) block_sum[blockIdx.x] = tot;
 }
 
 // entry number of every position; ref[doc] = entry; the head of an entry records its document
-__global__ void __launch_bounds__(kScanBlock) dict_assign_kernel(const unsigned long long* keys, const uint32_t* docs,
-                                                                 const uint8_t* text, const uint64_t* start,
-                                                                 const uint32_t* len, int64_t n, const uint64_t* block_base,
-                                                                 uint32_t* ref, uint32_t* entry_doc) {
+__global__ void __launch_bounds__(kScanBlock) dict_assign_kernel(const uint32_t* docs, const uint8_t* head, int64_t n,
+                                                                 const uint64_t* block_base, uint32_t* ref,
+                                                                 uint32_t* entry_doc) {
   __shared__ uint32_t s_warp[32];
   const int64_t pos = (int64_t)blockIdx.x * kScanBlock + threadIdx.x;
-  const uint32_t h = pos < n ? dict_is_head(keys, docs, text, start, len, pos) : 0u;
+  const uint32_t h = pos < n ? head[pos] : 0u;
   const uint32_t before = block_exclusive_scan(h, s_warp, nullptr);
   if (pos >= n) return;
   const uint32_t entry = (uint32_t)block_base[blockIdx.x] + before + h - 1u;

@@ -2270,10 +2270,11 @@ int32_t encode_member(tt_table* t, IngestScratch& sc, const tt::DocCols& d, int 
   uint32_t* entry_doc = nullptr;
   TT_CUDA(sc.get(&blocks, (size_t)nb + 1));
   TT_CUDA(sc.get(&entry_doc, (size_t)n));
-  tt::dict_head_sum_kernel<<<nb, tt::kScanBlock, 0, st>>>(keys, docs, text, d.str_start[c], d.str_len[c], n, blocks);
+  uint8_t* head = nullptr;
+  TT_CUDA(sc.get(&head, (size_t)n));
+  tt::dict_head_sum_kernel<<<nb, tt::kScanBlock, 0, st>>>(keys, docs, text, d.str_start[c], d.str_len[c], n, head, blocks);
   tt::scan_block_sums_kernel<<<1, 1024, 0, st>>>(blocks, nb);
-  tt::dict_assign_kernel<<<nb, tt::kScanBlock, 0, st>>>(keys, docs, text, d.str_start[c], d.str_len[c], n, blocks, ref_out,
-                                                         entry_doc);
+  tt::dict_assign_kernel<<<nb, tt::kScanBlock, 0, st>>>(docs, head, n, blocks, ref_out, entry_doc);
   uint64_t k64 = 0;
   TT_CUDA(cudaGetLastError());
   TT_CUDA(cudaMemcpyAsync(&k64, blocks + nb, 8, cudaMemcpyDeviceToHost, st));
