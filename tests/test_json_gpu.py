@@ -178,3 +178,37 @@ def test_larger_list_and_device_copy(oracle):
     assert int(buf[j.size]) == 0 and got == ot.to_json(rows, tt.JSON_RESPONSE) and b'"isOverDue":true' in got
     j.free()
     table.close()
+
+
+def test_every_unicode_scalar_value(oracle):
+    """all 1 112 064 Unicode scalar values (U+0000..U+10FFFF without the surrogates), 16 per TaskName, through
+    both encoders: the product's escaping rule must agree with the oracle's on every one of them"""
+    scalars = [c for c in range(0x110000) if not 0xD800 <= c <= 0xDFFF]
+    names = ["".join(map(chr, scalars[i:i + 16])).encode("utf-8") for i in range(0, len(scalars), 16)]
+    n = len(names)
+    ot = oracle.OracleTable()
+    ids = np.zeros((n, 16), dtype=np.uint8)
+    ids[:, 12:] = np.arange(1, n + 1, dtype=">u4").view(np.uint8).reshape(n, 4)
+    due = tt.DEFAULT_TODAY - DAY
+    for i, name in enumerate(names):
+        ot.add(ids[i], name, b"u@x", b"", (700_000 * DAY + i) | KIND_UTC, due)
+    table = tt.TaskTable(0).load_soa(ids, np.array([(700_000 * DAY + i) | KIND_UTC for i in range(n)], dtype=np.uint64),
+                                     np.full(n, due, dtype=np.uint64), np.zeros(n, dtype=np.uint8), np.zeros(n, dtype=np.uint8),
+                                     np.zeros(n, dtype=np.uint32), [b"u@x"])
+    table.load_payload(names, [b""] * n)
+    res = table.get_yesterdays_due(tt.MODE_FAKE)
+    listed = ot.get_yesterdays_due(tt.MODE_FAKE)
+    assert res.count == n == listed.size
+    for flavor in FLAVORS:
+        got, want = res.to_json(flavor), ot.to_json(listed, flavor)
+        assert got == want
+    back = json.loads(got)
+    assert back[0]["taskName"] == names[0].decode() and back[-1]["taskName"] == names[-1].decode()
+    # and the reader takes every one of them back: K6's documents through K7 print the same text again
+    j = res.json(tt.JSON_DOCUMENT)
+    again = tt.TaskTable(0)
+    again.load_documents(j.device_ptr(), j.offsets(n))
+    assert again.get_yesterdays_due(tt.MODE_FAKE).to_json(tt.JSON_DOCUMENT) == j.bytes()
+    j.free()
+    again.close()
+    table.close()
