@@ -212,3 +212,45 @@ def test_every_unicode_scalar_value(oracle):
     j.free()
     again.close()
     table.close()
+
+
+def test_calendar_edges(oracle):
+    """every day of the years where the Gregorian rules bite (1, 4, 100, 400, 1600, 1900, 2000, 2024, 2100, 9999)
+    and every 97th day of the whole DateTime range, printed by K6 and read back by K7"""
+    import datetime
+
+    first = datetime.date(1, 1, 1)
+    days = set(range(0, 3_652_059, 97))
+    for y in (1, 4, 100, 400, 1600, 1900, 2000, 2024, 2100, 9999):
+        d0 = (datetime.date(y, 1, 1) - first).days
+        days.update(range(d0, d0 + (366 if y % 4 == 0 and (y % 100 != 0 or y % 400 == 0) else 365)))
+    days = sorted(days)
+    n = len(days)
+    ids = np.zeros((n, 16), dtype=np.uint8)
+    ids[:, 12:] = np.arange(1, n + 1, dtype=">u4").view(np.uint8).reshape(n, 4)
+    due = tt.DEFAULT_TODAY - DAY
+    created = np.array([d * DAY + (d * 7919 % DAY if d % 3 else 0) for d in days], dtype=np.uint64)
+    created |= np.array([[0, KIND_UTC, KIND_LOCAL][d % 3] for d in days], dtype=np.uint64)
+    ot = oracle.OracleTable()
+    for i in range(n):
+        ot.add(ids[i], b"", b"u@x", b"", int(created[i]), due)
+    table = tt.TaskTable(0).load_soa(ids, created, np.full(n, due, dtype=np.uint64), np.zeros(n, dtype=np.uint8),
+                                     np.zeros(n, dtype=np.uint8), np.zeros(n, dtype=np.uint32), [b"u@x"])
+    res = table.get_yesterdays_due(tt.MODE_FAKE)
+    listed = ot.get_yesterdays_due(tt.MODE_FAKE)
+    assert res.count == n
+    for offset in (0, 60):
+        got = res.to_json(tt.JSON_RESPONSE, offset)
+        assert got == ot.to_json(listed, tt.JSON_RESPONSE, offset)
+    # spot checks against Python's own calendar
+    docs = json.loads(res.to_json(tt.JSON_RESPONSE, 0))
+    for k in (0, n // 3, n // 2, n - 1):
+        want = (first + datetime.timedelta(days=days[k])).isoformat()
+        assert docs[k]["taskCreatedOn"].startswith(f"{want}T"), (docs[k]["taskCreatedOn"], want)
+    j = res.json(tt.JSON_DOCUMENT, 60)
+    again = tt.TaskTable(0)
+    again.load_documents(j.device_ptr(), j.offsets(n), 60)
+    assert again.get_yesterdays_due(tt.MODE_FAKE).to_json(tt.JSON_DOCUMENT, 60) == j.bytes()
+    j.free()
+    again.close()
+    table.close()

@@ -325,3 +325,14 @@ def test_documents_from_the_reference_tutorial_deserialise_as_documented(oracle)
                 "isCompleted": False, "isOverDue": False}
     for s, doc in zip(samples, back):
         assert doc == {**defaults, **s["members"]}, s["source"]
+
+
+def test_dates_agree_with_an_independent_calendar(oracle):
+    """the restated DateTime -> text conversion against Python's proleptic Gregorian calendar (the same
+    calendar .NET's DateTime uses): every 13th day of 0001-01-01 .. 9999-12-31 and both ends"""
+    first = dt.date(1, 1, 1)
+    day = 864_000_000_000
+    for d in list(range(0, 3_652_059, 13)) + [3_652_058]:
+        want = (first + dt.timedelta(days=d)).isoformat()
+        assert oracle.format_stj(d * day + 1) == f"{want}T00:00:00.0000001"
+        assert oracle.format_converter(d * day + 86_399 * 10_000_000) == f"{want}T23:59:59"
