@@ -8,8 +8,10 @@
 //  and no .NET runtime exists on this box or the GPU box, so this
 // restatement cannot be checked against a run of the reference.  It is written line by line
 // from the cited C# and from documented .NET 9 BCL behaviour; the only
-// pins are the JSON date samples in the workshop docs (docs/aca/05-aca-dapr-pubsubapi/index.md:65-66)
-// and the seed-row shape (Api/Services/FakeTasksManager.cs:12-24), both covered in tests/.
+// pins are the JSON bodies the workshop docs show (docs/aca/05-aca-dapr-pubsubapi/index.md:60-69 and
+// three more, tests/golden/reference_doc_samples.json), the seed-row shape
+// (Api/Services/FakeTasksManager.cs:12-24), Python's calendar for the date arithmetic and Python's
+// JSON reader for the escapes, all covered in tests/test_oracle.py.
 //
 // Reference files restated here (paths under /root/reference):
 //   Api = TasksTracker.TasksManager.Backend.Api, Svc = TasksTracker.Processor.Backend.Svc
