@@ -336,3 +336,26 @@ def test_dates_agree_with_an_independent_calendar(oracle):
         want = (first + dt.timedelta(days=d)).isoformat()
         assert oracle.format_stj(d * day + 1) == f"{want}T00:00:00.0000001"
         assert oracle.format_converter(d * day + 86_399 * 10_000_000) == f"{want}T23:59:59"
+
+
+def test_every_scalar_survives_an_independent_json_reader(oracle):
+    """all Unicode scalar values, 16 per TaskName, written by both restated encoders and read by Python's
+    json module (an independent reader): whatever is escaped, the text is JSON and means the same string;
+    the restated reader takes its own documents back unchanged"""
+    import json
+
+    scalars = [c for c in range(0x110000) if not 0xD800 <= c <= 0xDFFF]
+    names = ["".join(map(chr, scalars[i:i + 16])) for i in range(0, len(scalars), 16)]
+    ot = oracle.OracleTable()
+    zero = np.zeros(16, dtype=np.uint8)
+    for nm in names:
+        ot.add(zero, nm.encode(), b"u@x", b"", 0, 0)
+    rows = np.arange(len(names))
+    for flavor in (oracle.JSON_RESPONSE, oracle.JSON_DOCUMENT):
+        text = ot.to_json(rows, flavor)
+        assert [d["taskName"] for d in json.loads(text)] == names
+        if flavor == oracle.JSON_DOCUMENT:
+            assert max(text) < 0x7F and min(text) >= 0x20  # Default encoder: plain printable ASCII only
+        docs, off = ot.to_documents(rows, flavor)
+        again = oracle.OracleTable()
+        assert again.add_documents(docs, off) == -1 and again.to_json(rows, flavor) == text
