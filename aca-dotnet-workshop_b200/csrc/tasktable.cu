@@ -128,6 +128,7 @@ struct tt_table {
   uint32_t* h_qcount = nullptr;
   tt_op_stats last_op = {};
   tt::SortScratch sort;  // K5 radix sort buffers, grow-only
+  bool creator_smem_opted = false, json_smem_opted = false;  // large dynamic shared memory enabled on this device
 
   // payload: TaskName and TaskAssignedTo as dictionary-encoded string columns.  No kernel of the
   // sweep or the filter reads them; they exist so a result can be written out as JSON (K6).
@@ -1130,13 +1131,12 @@ int32_t tt_get_by_creators(tt_table* t, const char* const* utf8, const int32_t* 
   qs.slots = slots;
   qs.nq = nu;
   const size_t smem = nu == 1 ? 0 : (size_t)slots * 12;
-  static bool opted = false;
-  if (!opted) {
+  if (!t->creator_smem_opted) {  // a per-device attribute: kept with the table, which lives on one device
     TT_CUDA(cudaFuncSetAttribute(tt::creator_scan_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)tt::kMaxSlots * 12));
     TT_CUDA(cudaFuncSetAttribute(tt::order_lists_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  tt::kListOrderCap * 12));
-    opted = true;
+    t->creator_smem_opted = true;
   }
 
   // ---- K4: one pass over the hash column for the whole batch.  First into per-query lists (one
@@ -2136,11 +2136,10 @@ int32_t tt_result_json(tt_result* r, int32_t flavor, int32_t local_offset_min, t
   }
   p.local_offset_min = local_offset_min;
   p.block_base = t->json_blocks;
-  static bool opted = false;
   cudaError_t e = cudaSuccess;
-  if (!opted) {
+  if (!t->json_smem_opted) {  // a per-device attribute
     e = cudaFuncSetAttribute(tt::json_emit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, tt::kJsonStageBytes);
-    opted = e == cudaSuccess;
+    t->json_smem_opted = e == cudaSuccess;
   }
   uint64_t total = 0;
   if (e == cudaSuccess) e = cudaEventRecord(t->ev0, t->stream);
