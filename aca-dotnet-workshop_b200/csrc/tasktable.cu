@@ -138,6 +138,13 @@ struct tt_table {
     uint32_t n = 0;           // dictionary entries
     uint32_t* off = nullptr;  // [n + 1]
     uint8_t* pool = nullptr;
+    // single-row updates (tt_set_task_strings): device capacities and a host mirror built on first use
+    size_t off_cap = 0, pool_cap = 0;
+    uint64_t pool_bytes = 0;
+    bool mirrored = false;
+    std::vector<uint32_t> h_off;
+    std::vector<uint8_t> h_pool;
+    std::unordered_map<std::string, uint32_t> h_index;
   } name_col, assignee_col;
   // escaped dictionaries for K6, built on first use: [name, creator, assignee][response, document]
   struct EscCache {
@@ -1937,6 +1944,59 @@ int32_t set_column(tt_table* t, tt_table::StrColumn* c, int which, uint32_t n_st
   if (ref_host && t->n) TT_CUDA(cudaMemcpyAsync(c->ref, ref_host, (size_t)t->n * 4, cudaMemcpyHostToDevice, t->stream));
   TT_CUDA(cudaStreamSynchronize(t->stream));
   c->n = n_strings;
+  c->off_cap = (size_t)n_strings + 1;
+  c->pool_cap = std::max<size_t>(bytes, 16);
+  c->pool_bytes = bytes;
+  return TT_OK;
+}
+
+// Dictionary index of a TaskName / TaskAssignedTo value, appending it (host mirror and device arrays)
+// if it is new.  Same scheme as intern_creator; the column is created empty if the table has none.
+int32_t intern_string(tt_table* t, tt_table::StrColumn* c, int which, const char* utf8, int32_t len, uint32_t* ref) {
+  int32_t rc;
+  if (!c->ref) {
+    static const uint32_t zero_off[1] = {0};
+    if ((rc = set_column(t, c, which, 0, zero_off, nullptr, nullptr))) return rc;
+  }
+  if (!c->mirrored) {
+    c->h_off.assign((size_t)c->n + 1, 0);
+    c->h_pool.assign((size_t)c->pool_bytes, 0);
+    TT_CUDA(cudaMemcpy(c->h_off.data(), c->off, ((size_t)c->n + 1) * 4, cudaMemcpyDeviceToHost));
+    if (c->pool_bytes) TT_CUDA(cudaMemcpy(c->h_pool.data(), c->pool, (size_t)c->pool_bytes, cudaMemcpyDeviceToHost));
+    c->h_index.clear();
+    c->h_index.reserve((size_t)c->n * 2 + 16);
+    for (uint32_t k = 0; k < c->n; ++k)
+      c->h_index.emplace(std::string((const char*)c->h_pool.data() + c->h_off[k], c->h_off[k + 1] - c->h_off[k]), k);
+    c->mirrored = true;
+  }
+  std::string key(utf8 ? utf8 : "", (size_t)len);
+  auto it = c->h_index.find(key);
+  if (it != c->h_index.end()) {
+    *ref = it->second;
+    return TT_OK;
+  }
+  if (c->n == 0xFFFFFFFEu || c->pool_bytes + (uint64_t)len >= (1ull << 32)) return fail(TT_ERR_OOM, "string dictionary is full");
+  const uint32_t k = c->n, start = (uint32_t)c->pool_bytes;
+  if ((size_t)k + 2 > c->off_cap) {
+    const size_t want = std::max<size_t>(2 * c->off_cap, 1024);
+    if ((rc = grow_buffer(t, &c->off, (size_t)k + 1, want, 0))) return rc;
+    c->off_cap = want;
+  }
+  if (c->pool_bytes + (size_t)len > c->pool_cap) {
+    const size_t want = std::max<size_t>(2 * c->pool_cap, (size_t)c->pool_bytes + (size_t)len + 65536);
+    if ((rc = grow_buffer(t, &c->pool, (size_t)c->pool_bytes, want, 0))) return rc;
+    c->pool_cap = want;
+  }
+  const uint32_t tail[2] = {start, start + (uint32_t)len};
+  TT_CUDA(cudaMemcpyAsync(c->off + k, tail, 8, cudaMemcpyHostToDevice, t->stream));
+  if (len) TT_CUDA(cudaMemcpyAsync(c->pool + start, key.data(), (size_t)len, cudaMemcpyHostToDevice, t->stream));
+  TT_CUDA(cudaStreamSynchronize(t->stream));
+  c->h_pool.insert(c->h_pool.end(), key.begin(), key.end());
+  c->h_off.push_back(start + (uint32_t)len);
+  c->h_index.emplace(std::move(key), k);
+  c->n = k + 1;
+  c->pool_bytes += (uint64_t)len;
+  *ref = k;
   return TT_OK;
 }
 
@@ -2052,6 +2112,32 @@ int32_t tt_generate_payload(tt_table* t, const tt_synth_cfg* cfg, uint64_t first
     TT_CUDA(cudaGetLastError());
     TT_CUDA(cudaStreamSynchronize(t->stream));
   }
+  return TT_OK;
+}
+
+int32_t tt_set_task_strings(tt_table* t, const uint8_t* id16, const char* task_name, int32_t name_len,
+                            const char* assigned_to, int32_t assigned_len, int32_t* found) {
+  if (!t || !id16 || name_len < -1 || assigned_len < -1 || (name_len > 0 && !task_name) || (assigned_len > 0 && !assigned_to))
+    return fail(TT_ERR_ARG, "bad argument");
+  if (found) *found = 0;
+  std::lock_guard<std::mutex> lk(t->mu);
+  DeviceGuard g(t->device);
+  if (t->n_pad == 0) return TT_OK;
+  int64_t row = -1;
+  int32_t rc = find_row(t, id16, &row);
+  if (rc) return rc;
+  if (row < 0) return TT_OK;
+  const char* text[2] = {task_name, assigned_to};
+  const int32_t lens[2] = {name_len, assigned_len};
+  tt_table::StrColumn* cols[2] = {&t->name_col, &t->assignee_col};
+  for (int c = 0; c < 2; ++c) {
+    if (lens[c] < 0) continue;  // -1: leave this member as it is
+    uint32_t ref = 0;
+    if ((rc = intern_string(t, cols[c], c == 0 ? 0 : 2, text[c], lens[c], &ref))) return rc;
+    TT_CUDA(cudaMemcpyAsync(cols[c]->ref + row, &ref, 4, cudaMemcpyHostToDevice, t->stream));
+    TT_CUDA(cudaStreamSynchronize(t->stream));
+  }
+  if (found) *found = 1;
   return TT_OK;
 }
 
@@ -2434,14 +2520,16 @@ extern "C" int32_t tt_load_documents(tt_table* t, const void* docs, const uint64
     cudaFree(refs[2]);
     return undo(rc);
   }
-  t->name_col.ref = refs[0];
-  t->name_col.n = k[0];
-  t->name_col.off = off[0];
-  t->name_col.pool = pool[0];
-  t->assignee_col.ref = refs[2];
-  t->assignee_col.n = k[2];
-  t->assignee_col.off = off[2];
-  t->assignee_col.pool = pool[2];
+  tt_table::StrColumn* cols[3] = {&t->name_col, nullptr, &t->assignee_col};
+  for (int c = 0; c < 3; c += 2) {
+    cols[c]->ref = refs[c];
+    cols[c]->n = k[c];
+    cols[c]->off = off[c];
+    cols[c]->pool = pool[c];
+    cols[c]->off_cap = (size_t)k[c] + 1;
+    cols[c]->pool_cap = std::max<uint64_t>(pbytes[c], 16);
+    cols[c]->pool_bytes = pbytes[c];
+  }
   t->n_creators = k[1];
   t->creator_off = off[1];
   t->creator_pool = pool[1];

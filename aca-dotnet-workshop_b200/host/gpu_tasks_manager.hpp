@@ -90,7 +90,7 @@ class TaskTableLibrary {
     TT_BIND(tt_result_free);
     TT_BIND(tt_get_by_id); TT_BIND(tt_insert_task); TT_BIND(tt_update_task); TT_BIND(tt_mark_completed);
     TT_BIND(tt_delete_task);
-    TT_BIND(tt_load_payload); TT_BIND(tt_result_json); TT_BIND(tt_json_size); TT_BIND(tt_json_copy); TT_BIND(tt_json_free);
+    TT_BIND(tt_load_payload); TT_BIND(tt_set_task_strings); TT_BIND(tt_result_json); TT_BIND(tt_json_size); TT_BIND(tt_json_copy); TT_BIND(tt_json_free);
 #undef TT_BIND
   }
   ~TaskTableLibrary() { if (h_) dlclose(h_); }
@@ -113,6 +113,7 @@ class TaskTableLibrary {
   decltype(&::tt_mark_completed) tt_mark_completed;
   decltype(&::tt_delete_task) tt_delete_task;
   decltype(&::tt_load_payload) tt_load_payload;
+  decltype(&::tt_set_task_strings) tt_set_task_strings;
   decltype(&::tt_result_json) tt_result_json;
   decltype(&::tt_json_size) tt_json_size;
   decltype(&::tt_json_copy) tt_json_copy;
@@ -216,6 +217,8 @@ class GpuTasksManager : public ITasksManager {
     if (!known) creators_.push_back(createdBy);  // the library appends new creators in the same order
     names_.push_back(taskName);
     assignees_.push_back(assignedTo);
+    check(lib_->tt_set_task_strings(table_, id.data(), taskName.data(), (int32_t)taskName.size(), assignedTo.data(),
+                                    (int32_t)assignedTo.size(), nullptr));
     return id;
   }
 
@@ -235,6 +238,8 @@ class GpuTasksManager : public ITasksManager {
     }
     names_[row] = taskName;
     assignees_[row] = assignedTo;
+    check(lib_->tt_set_task_strings(table_, taskId.data(), taskName.data(), (int32_t)taskName.size(), assignedTo.data(),
+                                    (int32_t)assignedTo.size(), nullptr));
     int32_t found = 0;
     check(lib_->tt_update_task(table_, taskId.data(), dueDate.dateData, &found));
     return found != 0;
@@ -255,7 +260,7 @@ class GpuTasksManager : public ITasksManager {
   // The whole tick as one device pass (tt_sweep).  Returns the listed tasks; *n_marked = rows set.
   // The body OverdueTasksController.Get (Api/Controllers/OverdueTasksController.cs:22-26) sends for
   // `return await _tasksManager.GetYesterdaysDueTasks();`, written on the device: no TaskModel objects
-  // are built on the host.  Tasks created after construction print "" for TaskName / TaskAssignedTo.
+  // are built on the host (CreateNewTask / UpdateTask keep the device's strings current).
   std::string OverdueTasksGet(int32_t local_offset_min = 0) {
     tt_result* r = nullptr;
     check(lib_->tt_get_yesterdays_due(table_, mode_, clock_->today_local_ticks, &r));

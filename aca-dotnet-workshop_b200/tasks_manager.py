@@ -71,6 +71,8 @@ class GpuTasksManager:
             refs,
             self._creators,
         )
+        if tasks:
+            self._table.load_payload([n.encode("utf-8") for n in self._names], [a.encode("utf-8") for a in self._assignees])
 
     @property
     def table(self):
@@ -108,6 +110,7 @@ class GpuTasksManager:
             self._creator_lookup.add(b)
         row = self._table.insert_task(task_id.bytes, self._utc_now(), dueDate, b)
         assert row == len(self._names)
+        self._table.set_task_strings(task_id.bytes, taskName.encode("utf-8"), assignedTo.encode("utf-8"))
         self._names.append(taskName)
         self._assignees.append(assignedTo)
         return task_id
@@ -129,6 +132,7 @@ class GpuTasksManager:
             return False
         self._names[int(rows[0])] = taskName
         self._assignees[int(rows[0])] = assignedTo
+        self._table.set_task_strings(taskId.bytes, taskName.encode("utf-8"), assignedTo.encode("utf-8"))
         return self._table.update_task(taskId.bytes, dueDate)
 
     # ITasksManager.cs:11
@@ -157,6 +161,22 @@ class GpuTasksManager:
     # ITasksManager.cs:7
     def GetTasksByCreator(self, createdBy: str) -> List[TaskModel]:
         return self._materialise(self._table.get_by_creator(createdBy))
+
+    # What the two list endpoints send, written on the device (tt_result_json): the body of
+    # OverdueTasksController.Get (Api/Controllers/OverdueTasksController.cs:22-26) and of
+    # TasksController.Get (Api/Controllers/TasksController.cs:21-25); no TaskModel objects are built.
+    def OverdueTasksGet(self, today_local_ticks=tt.DEFAULT_TODAY, local_offset_min=0) -> bytes:
+        return self._json(self._table.get_yesterdays_due(self.mode, today_local_ticks), local_offset_min)
+
+    def TasksGet(self, createdBy: str, local_offset_min=0) -> bytes:
+        return self._json(self._table.get_by_creator(createdBy), local_offset_min)
+
+    @staticmethod
+    def _json(result, local_offset_min):
+        try:
+            return result.to_json(tt.JSON_RESPONSE, local_offset_min)
+        finally:
+            result.free()
 
     # Svc/Controllers/ScheduledTasksManagerController.cs:19-46, unfused: three calls like the reference
     def CheckOverDueTasksJob(self, run_at_utc_ticks=tt.DEFAULT_RUN_AT, today_local_ticks=tt.DEFAULT_TODAY) -> int:

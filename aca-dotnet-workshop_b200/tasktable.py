@@ -54,7 +54,7 @@ EXPORTS = [
     "tt_sweep_push", "tt_peer_alloc", "tt_peer_open", "tt_peer_close", "tt_peer_free",
     "tt_load_payload", "tt_generate_payload", "tt_result_json", "tt_json_size", "tt_json_copy", "tt_json_device",
     "tt_json_free", "tt_last_json_stats", "tt_json_offsets", "tt_load_documents",
-    "tt_get_due_on_or_before", "tt_sweep_backlog", "tt_tick_host",
+    "tt_get_due_on_or_before", "tt_sweep_backlog", "tt_tick_host", "tt_set_task_strings",
 ]
 
 
@@ -243,6 +243,7 @@ def lib():
     L.tt_get_due_on_or_before.argtypes = [vp, i32, i64, P(vp)]
     L.tt_sweep_backlog.argtypes = [vp, i32, i64, i64, P(vp), P(i64)]
     L.tt_tick_host.argtypes = [vp, i32, i32, i64, i64, vp, vp, vp, vp, i64, i32, P(SweepStats)]
+    L.tt_set_task_strings.argtypes = [vp, vp, C.c_char_p, i32, C.c_char_p, i32, P(i32)]
     L.tt_json_offsets.argtypes = [vp, vp]
     L.tt_load_documents.argtypes = [vp, vp, vp, i64, i32, P(IngestStats)]
     for name in EXPORTS:
@@ -573,6 +574,14 @@ class TaskTable:
         f = C.c_int32(0)
         a = self._id(task_id)
         _check(lib().tt_update_task(self._h, _ptr(a), due_raw, C.byref(f)))
+        return bool(f.value)
+
+    def set_task_strings(self, task_id, task_name=None, assigned_to=None):
+        """TaskName / TaskAssignedTo of one task (bytes, UTF-8); None leaves that member as it is."""
+        f = C.c_int32(0)
+        a = self._id(task_id)
+        _check(lib().tt_set_task_strings(self._h, _ptr(a), task_name, -1 if task_name is None else len(task_name),
+                                         assigned_to, -1 if assigned_to is None else len(assigned_to), C.byref(f)))
         return bool(f.value)
 
     def mark_completed(self, task_id):

@@ -317,7 +317,8 @@ int32_t tt_peer_free(int32_t device, void* d_ptr);
  * TaskName and TaskAssignedTo (Api/Models/TaskModel.cs:6,10) are never read by the sweep or the
  * filter; they are kept as dictionary-encoded string columns only so that a result can leave the
  * GPU as the text the reference's controllers send.  Without a payload both print as "" (the
- * reference's default, `= string.Empty`); rows added later by tt_insert_task print "" as well. */
+ * reference's default, `= string.Empty`); rows added later by tt_insert_task print "" until
+ * tt_set_task_strings gives them their strings. */
 typedef struct tt_strings_view {
   const uint32_t* ref;  /* one entry per row: index into the dictionary, 0xFFFFFFFF = empty string */
   uint32_t n_strings;   /* dictionary entries                                                      */
@@ -330,6 +331,13 @@ int32_t tt_load_payload(tt_table* t, const tt_strings_view* task_name, const tt_
  * "Task number: {i}" names (Api/Services/FakeTasksManager.cs:16; one in eight with characters JSON must
  * escape) and "assignee{0..49}@mail.com" (FakeTasksManager.cs:21). */
 int32_t tt_generate_payload(tt_table* t, const tt_synth_cfg* cfg, uint64_t first_row);
+
+/* TaskName / TaskAssignedTo of ONE task, for the single-row methods that set them: CreateNewTask
+ * (ITasksManager.cs:9; after tt_insert_task) and UpdateTask (ITasksManager.cs:10; FakeTasksManager.cs:92-94,
+ * TasksStoreManager.cs:91-93).  A length of -1 leaves that member as it is.  New strings are appended to the
+ * column's dictionary (the column is created if the table had no payload).  *found as in tt_update_task. */
+int32_t tt_set_task_strings(tt_table* t, const uint8_t* id16, const char* task_name, int32_t name_len,
+                            const char* assigned_to, int32_t assigned_len, int32_t* found);
 
 /* tt_result_json writes the rows of a result, in result order, as the JSON array ASP.NET Core
  * produces for the List<TaskModel> the controllers return (Api/Controllers/OverdueTasksController.cs:22-26,

@@ -160,3 +160,44 @@ def test_snapshot_roundtrip(oracle, tmp_path):
         tt.TaskTable(0).load_snapshot(str(tmp_path / "missing.snap"))
     table.close()
     again.close()
+
+
+def test_list_endpoints_follow_single_row_edits(oracle):
+    """the device-made response bodies (GpuTasksManager.OverdueTasksGet / TasksGet = tt_result_json) after
+    CreateNewTask, UpdateTask, MarkTaskCompleted and DeleteTask, against the oracle doing the same edits
+    (FakeTasksManager.cs:32-100) and serialising the same lists"""
+    import importlib
+
+    pkg = importlib.import_module("aca-dotnet-workshop_b200")
+    guids = [uuid.UUID(int=(k + 1) << 64 | 0x4000_8000_0000_0000_0000 | k) for k in range(8)]
+    it = iter(guids)
+    clock = [tt.DEFAULT_RUN_AT]
+    seed = [pkg.TaskModel(next(it), f"seed {k}", "ann@x.io", (TODAY - 5000 + k) | (1 << 62), YDAY, "bob \"b\" <x>")
+            for k in range(3)]
+    mgr = pkg.GpuTasksManager(seed, mode=tt.MODE_FAKE, new_guid=lambda: next(it), utc_now=lambda: clock[0] | (1 << 62))
+    ot = oracle.OracleTable()
+    for t in seed:
+        ot.add(t.TaskId.bytes, t.TaskName, t.TaskCreatedBy, t.TaskAssignedTo, t.TaskCreatedOn, t.TaskDueDate)
+
+    def same():
+        assert mgr.OverdueTasksGet() == ot.to_json(ot.get_yesterdays_due(oracle.MODE_FAKE), oracle.JSON_RESPONSE)
+        for who in ("ann@x.io", "dan@x.io", "nobody"):
+            assert mgr.TasksGet(who) == ot.to_json(ot.get_by_creator(oracle.MODE_FAKE, who.encode()), oracle.JSON_RESPONSE)
+
+    same()
+    clock[0] += 77
+    new = mgr.CreateNewTask("caf\u00e9 & co", "dan@x.io", "eve+1@x.io", YDAY)          # a name the table has not seen
+    ot.add(new.bytes, "caf\u00e9 & co", "dan@x.io", "eve+1@x.io", clock[0] | (1 << 62), YDAY)
+    same()
+    clock[0] += 5
+    again = mgr.CreateNewTask("seed 1", "ann@x.io", "bob \"b\" <x>", TODAY)             # strings it already has
+    ot.add(again.bytes, "seed 1", "ann@x.io", "bob \"b\" <x>", clock[0] | (1 << 62), TODAY)
+    same()
+    assert mgr.UpdateTask(seed[0].TaskId, "renamed \\ task", "", YDAY)
+    assert ot.update_task(oracle.MODE_FAKE, seed[0].TaskId.bytes, "renamed \\ task", "", YDAY)
+    same()
+    assert mgr.MarkTaskCompleted(seed[1].TaskId) and ot.mark_completed(oracle.MODE_FAKE, seed[1].TaskId.bytes)
+    assert mgr.DeleteTask(seed[2].TaskId) and ot.delete_task(oracle.MODE_FAKE, seed[2].TaskId.bytes)
+    same()
+    assert b'"taskName":"renamed \\\\ task"' in mgr.TasksGet("ann@x.io") and b'"isCompleted":true' in mgr.TasksGet("ann@x.io")
+    mgr.close()
