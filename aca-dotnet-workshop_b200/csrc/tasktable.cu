@@ -1760,6 +1760,7 @@ int32_t tt_save_snapshot(tt_table* t, const char* path) {
   h.n_creators = t->n_creators;
   h.ids_sorted = t->ids_sorted ? 1u : 0u;
   h.tile_rows = TT_TILE_ROWS;
+  h.reserved = (t->name_col.ref ? 1u : 0u) | (t->assignee_col.ref ? 2u : 0u);
   int32_t rc = fwrite(&h, sizeof h, 1, f) == 1 ? TT_OK : fail(TT_ERR_STATE, "short write to snapshot");
   const size_t np = (size_t)t->n_pad;
   if (!rc) rc = snap_write(f, t->due_code, np * 4, stage, t->stream);
@@ -1772,6 +1773,18 @@ int32_t tt_save_snapshot(tt_table* t, const char* path) {
   if (!rc) rc = snap_write(f, t->creator_ref, np * 4, stage, t->stream);
   if (!rc) rc = snap_write(f, t->creator_off, ((size_t)t->n_creators + 1) * 4, stage, t->stream);
   if (!rc && t->pool_bytes) rc = snap_write(f, t->creator_pool, t->pool_bytes, stage, t->stream);
+  // optional payload columns (header.reserved bit 0 = TaskName, bit 1 = TaskAssignedTo), each as
+  // [entries u32][pool bytes u64][ref x n_pad][off x entries+1][pool]
+  const tt_table::StrColumn* cols[2] = {&t->name_col, &t->assignee_col};
+  for (int c = 0; c < 2 && !rc; ++c) {
+    if (!cols[c]->ref) continue;
+    const uint32_t k = cols[c]->n;
+    const uint64_t pb = cols[c]->pool_bytes;
+    if (fwrite(&k, 4, 1, f) != 1 || fwrite(&pb, 8, 1, f) != 1) rc = fail(TT_ERR_STATE, "short write to snapshot");
+    if (!rc) rc = snap_write(f, cols[c]->ref, np * 4, stage, t->stream);
+    if (!rc) rc = snap_write(f, cols[c]->off, ((size_t)k + 1) * 4, stage, t->stream);
+    if (!rc && pb) rc = snap_write(f, cols[c]->pool, (size_t)pb, stage, t->stream);
+  }
   cudaFreeHost(stage);
   if (fclose(f) != 0 && !rc) rc = fail(TT_ERR_STATE, "closing %s failed", path);
   return rc;
@@ -1823,6 +1836,31 @@ int32_t tt_load_snapshot(tt_table* t, const char* path) {
   }
   if (!rc) rc = snap_read(f, t->creator_off, ((size_t)h.n_creators + 1) * 4, stage, t->stream);
   if (!rc && h.pool_bytes) rc = snap_read(f, t->creator_pool, h.pool_bytes, stage, t->stream);
+  tt_table::StrColumn* cols[2] = {&t->name_col, &t->assignee_col};
+  for (int c = 0; c < 2 && !rc; ++c) {
+    if (!(h.reserved & (1u << c))) continue;
+    uint32_t k = 0;
+    uint64_t pb = 0;
+    if (fread(&k, 4, 1, f) != 1 || fread(&pb, 8, 1, f) != 1 || pb >= (1ull << 32)) {
+      rc = fail(TT_ERR_ARG, "%s: truncated payload section", path);
+      break;
+    }
+    cudaError_t e = cudaMalloc(&cols[c]->ref, np * 4);
+    if (e == cudaSuccess) e = cudaMalloc(&cols[c]->off, ((size_t)k + 1) * 4);
+    if (e == cudaSuccess) e = cudaMalloc(&cols[c]->pool, std::max<uint64_t>(pb, 16));
+    if (e != cudaSuccess) {
+      cudaGetLastError();
+      rc = fail(TT_ERR_OOM, "payload column: %s", cudaGetErrorString(e));
+      break;
+    }
+    cols[c]->n = k;
+    cols[c]->off_cap = (size_t)k + 1;
+    cols[c]->pool_cap = std::max<uint64_t>(pb, 16);
+    cols[c]->pool_bytes = pb;
+    rc = snap_read(f, cols[c]->ref, np * 4, stage, t->stream);
+    if (!rc) rc = snap_read(f, cols[c]->off, ((size_t)k + 1) * 4, stage, t->stream);
+    if (!rc && pb) rc = snap_read(f, cols[c]->pool, (size_t)pb, stage, t->stream);
+  }
   cudaFreeHost(stage);
   fclose(f);
   if (rc) {

@@ -402,9 +402,8 @@ int32_t tt_json_offsets(tt_json* j, uint64_t* dst);
  * Saves / restores the whole table (all columns, flags, creator dictionary, tombstones) as one
  * file in the device layout — the counterpart of the reference keeping its tasks in a state store
  * across restarts (Api/Services/TasksStoreManager.cs:35 SaveStateAsync).  tt_load_snapshot needs
- * an empty table on the same kind of build (same tile size).  The optional payload columns
- * (TaskName / TaskAssignedTo, tt_load_payload) are not part of the file: load them again after
- * tt_load_snapshot, or keep the documents and use tt_load_documents. */
+ * an empty table on the same kind of build (same tile size).  The payload columns (TaskName /
+ * TaskAssignedTo), when the table has them, are part of the file. */
 int32_t tt_save_snapshot(tt_table* t, const char* path);
 int32_t tt_load_snapshot(tt_table* t, const char* path);
 

@@ -201,3 +201,29 @@ def test_list_endpoints_follow_single_row_edits(oracle):
     same()
     assert b'"taskName":"renamed \\\\ task"' in mgr.TasksGet("ann@x.io") and b'"isCompleted":true' in mgr.TasksGet("ann@x.io")
     mgr.close()
+
+
+def test_snapshot_carries_the_payload(oracle, tmp_path):
+    """TaskName / TaskAssignedTo survive save -> load: the reloaded table prints the same JSON, single-row
+    string edits included, and can take further edits (its dictionaries are live again)"""
+    n = 50_000
+    cfg = oracle.default_cfg(56, n, n_creators=20, n_names=500)
+    table = tt.TaskTable(0).generate(cfg, 0, n).generate_payload(cfg, 0)
+    who = b"user0000003@mail3.example"
+    first = table.get_by_creator(who)
+    ids = first.ids()
+    assert first.count > 1000 and table.set_task_strings(ids[0], b"edited \"name\"", None)
+    want = table.get_by_creator(who).to_json(tt.JSON_DOCUMENT)
+    path = str(tmp_path / "payload.snap")
+    table.save_snapshot(path)
+    again = tt.TaskTable(0).load_snapshot(path)
+    assert again.get_by_creator(who).to_json(tt.JSON_DOCUMENT) == want and b"edited \\u0022name\\u0022" in want
+    assert again.set_task_strings(ids[1], b"after reload", b"new assignee") and table.set_task_strings(ids[1], b"after reload", b"new assignee")
+    assert again.get_by_creator(who).to_json(tt.JSON_RESPONSE) == table.get_by_creator(who).to_json(tt.JSON_RESPONSE)
+    # a table without payload still saves and loads (and prints empty strings)
+    bare = tt.TaskTable(0).generate(cfg, 0, 1000)
+    bare.save_snapshot(path)
+    bare2 = tt.TaskTable(0).load_snapshot(path)
+    assert bare2.get_by_creator(who).to_json() == bare.get_by_creator(who).to_json()
+    for t in (table, again, bare, bare2):
+        t.close()
