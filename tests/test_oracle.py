@@ -359,3 +359,32 @@ def test_every_scalar_survives_an_independent_json_reader(oracle):
         docs, off = ot.to_documents(rows, flavor)
         again = oracle.OracleTable()
         assert again.add_documents(docs, off) == -1 and again.to_json(rows, flavor) == text
+
+
+def test_restated_reader_on_handwritten_and_malformed_documents(oracle):
+    """the same hand-written and malformed documents the GPU loader is tested with (tests/test_ingest_gpu.py),
+    through the oracle alone: what it accepts, what it rejects, and what it makes of the accepted ones"""
+    import json
+
+    from test_ingest_gpu import BAD, HAND, pack
+
+    ot = oracle.OracleTable()
+    assert ot.add_documents(*pack(HAND), 120) == -1 and len(ot) == len(HAND)
+    docs = json.loads(ot.to_json(np.arange(len(HAND)), oracle.JSON_RESPONSE, 120))
+    assert docs[0]["taskId"] == "fbc55b2c-d9fa-405e-aec8-22e53f4306dd" and docs[0]["isCompleted"] is True
+    assert docs[1]["taskName"] == "q\"b\\s/\b\f\n\r\t\u00e9\u4e2d\U0001F600 end"
+    assert docs[2]["taskName"] == "second" and docs[2]["taskCreatedBy"] == "" and docs[2]["isCompleted"] is False
+    assert docs[3]["taskCreatedOn"] == "2020-01-01T10:30:00" and docs[3]["taskDueDate"] == "2026-11-05T00:00:00.5"
+    assert docs[4]["taskCreatedOn"] == "2020-01-01T10:30:15.1234567"          # 16 digits truncated to 100 ns
+    assert docs[4]["taskDueDate"] == "2026-11-05T02:00:00+02:00"              # +02:00 read on a +02:00 clock: same wall time
+    assert docs[5]["taskCreatedOn"] == "2020-01-01T17:30:15.1+02:00"          # 10:30:15.1-05 is 15:30:15.1Z
+    assert docs[5]["taskDueDate"] == "2026-11-05T02:00:00+02:00"              # 18:30-05:30 is midnight UTC
+    assert docs[6]["taskDueDate"] == "9999-12-31T23:59:59.9999999"
+    assert docs[7] == {"taskId": "00000000-0000-0000-0000-000000000000", "taskName": "", "taskCreatedBy": "",
+                       "taskCreatedOn": "0001-01-01T00:00:00", "taskDueDate": "0001-01-01T00:00:00", "taskAssignedTo": "",
+                       "isCompleted": False, "isOverDue": False}
+    assert docs[8]["isOverDue"] is True and docs[9]["taskDueDate"] == "2026-11-05T00:00:00Z"
+    good = b'{"taskCreatedBy":"a@b"}'
+    for bad, _ in BAD:
+        fresh = oracle.OracleTable()
+        assert fresh.add_documents(*pack([good, bad, good])) == 1 and len(fresh) == 0, bad
