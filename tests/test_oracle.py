@@ -388,3 +388,27 @@ def test_restated_reader_on_handwritten_and_malformed_documents(oracle):
     for bad, _ in BAD:
         fresh = oracle.OracleTable()
         assert fresh.add_documents(*pack([good, bad, good])) == 1 and len(fresh) == 0, bad
+
+
+def test_backlog_extension_known_answers(oracle):
+    """the generalised predicate (oracle.cpp orc_backlog; an extension): twelve hand-checked rows"""
+    import uuid
+
+    day = 864_000_000_000
+    today = oracle.DEFAULT_TODAY
+    y = today - day
+    dues = [y, y + 1, y | (1 << 62), (y + 5 * 36_000_000_000) | (2 << 62), y - 400 * day, 1 * day, 0,
+            today, today + 1, today + 30 * day, y + day - 1, y - 1]
+    ot = oracle.OracleTable()
+    for i, d in enumerate(dues):
+        ot.add(uuid.UUID(int=i + 1).bytes, "n", "c@d", "a", (700_000 * day + (len(dues) - i)) | (1 << 62), d,
+               completed=(i == 4), overdue=(i == 6))
+    rows, n_over, threw = ot.backlog(oracle.MODE_FAKE)
+    assert rows.tolist() == [0, 1, 2, 3, 4, 5, 6, 10, 11] and n_over == 9 and not threw   # list order, no flag test
+    rows, n_over, threw = ot.backlog(oracle.MODE_STORE)
+    assert rows.tolist() == [11, 10, 5, 3, 2, 1, 0] and n_over == 7                       # pending only, by TaskCreatedOn
+    rows, n_over, threw = ot.backlog(oracle.MODE_FAKE, mark=True)
+    assert threw and ot.flags()[1].tolist() == [0] * 6 + [1] + [0] * 5                    # FAKE's Mark throws, nothing changes
+    rows, n_over, threw = ot.backlog(oracle.MODE_STORE, mark=True)
+    assert not threw and n_over == 7 and ot.flags()[1].tolist() == [1, 1, 1, 1, 0, 1, 1, 0, 0, 0, 1, 1]
+    assert ot.backlog(oracle.MODE_STORE)[0].size == 0                                      # idempotent
