@@ -5,7 +5,7 @@ CSRC := $(PKG)/csrc
 LIB := $(PKG)/libtasktable.so
 NVFLAGS := -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -Xcompiler -fPIC,-Wall \
            -Xptxas -v --expt-relaxed-constexpr
-HDRS := $(wildcard $(CSRC)/*.cuh $(CSRC)/*.h include/*.h)
+HDRS := $(wildcard $(CSRC)/*.cuh $(CSRC)/*.inc $(CSRC)/*.h include/*.h)
 
 all: $(LIB) oracle/liboracle.so $(PKG)/host/tasks_manager_demo
 

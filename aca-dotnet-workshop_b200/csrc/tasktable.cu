@@ -1421,468 +1421,9 @@ int32_t tt_get_device_view(tt_table* t, tt_device_view* out) {
 
 }  // extern "C"
 
-// ---- single-row operations (ITasksManager.cs:8-12) ----------------------------------------------
+#include "api_point.inc"
 
-namespace {
-
-uint4 id_to_uint4(const uint8_t* id16) {
-  uint4 v;
-  memcpy(&v, id16, 16);
-  return v;
-}
-
-// Row of the first live task with this id, or -1.
-int32_t find_row(tt_table* t, const uint8_t* id16, int64_t* row) {
-  *row = -1;
-  if (t->n == 0) return TT_OK;
-  TT_CUDA(cudaMemsetAsync(t->d_small, 0xFF, 8, t->stream));
-  const int sorted = (t->ids_sorted || t->id_order) ? 1 : 0;
-  const unsigned grid = sorted ? 1u : (unsigned)std::min<int64_t>(grid_for(t->n, 256), (int64_t)t->sm_count * 8);
-  tt::find_id_kernel<<<grid, 256, 0, t->stream>>>(id_to_uint4(id16), t->task_id, t->creator_ref,
-                                                   t->ids_sorted ? nullptr : t->id_order, t->n, sorted,
-                                                   reinterpret_cast<unsigned int*>(t->d_small));
-  TT_CUDA(cudaGetLastError());
-  TT_CUDA(cudaMemcpyAsync(t->h_small, t->d_small, 8, cudaMemcpyDeviceToHost, t->stream));
-  TT_CUDA(cudaStreamSynchronize(t->stream));
-  const uint32_t r = (uint32_t)(t->h_small[0] & 0xFFFFFFFFull);
-  if (r != 0xFFFFFFFFu) *row = r;
-  return TT_OK;
-}
-
-int32_t poke(tt_table* t, const tt::RowPoke& p) {
-  tt::poke_row_kernel<<<1, 1, 0, t->stream>>>(p, t->due_code, t->completed, t->overdue, t->creator_hash, t->task_id,
-                                             t->created_raw, t->due_raw, t->creator_ref);
-  TT_CUDA(cudaGetLastError());
-  TT_CUDA(cudaStreamSynchronize(t->stream));
-  return TT_OK;
-}
-
-template <typename T>
-int32_t grow_buffer(tt_table* t, T** buf, size_t old_count, size_t new_count, int fill) {
-  T* fresh = nullptr;
-  TT_CUDA(cudaMalloc(&fresh, new_count * sizeof(T)));
-  TT_CUDA(cudaMemsetAsync(fresh, fill, new_count * sizeof(T), t->stream));
-  if (*buf && old_count) TT_CUDA(cudaMemcpyAsync(fresh, *buf, old_count * sizeof(T), cudaMemcpyDeviceToDevice, t->stream));
-  TT_CUDA(cudaStreamSynchronize(t->stream));
-  cudaFree(*buf);
-  *buf = fresh;
-  return TT_OK;
-}
-
-// Doubles the row capacity (simple and unoptimised: every column is reallocated and copied).
-int32_t grow_rows(tt_table* t) {
-  const int64_t old_pad = t->n_pad, np = std::max<int64_t>(2 * old_pad, TT_TILE_ROWS);
-  if (np > kMaxRows) return fail(TT_ERR_OOM, "table is at its maximum of 2^31 rows");
-  int32_t rc;
-  if ((rc = grow_buffer(t, &t->due_code, old_pad, np, 0xFF))) return rc;
-  if ((rc = grow_buffer(t, &t->completed, old_pad / 32, np / 32, 0))) return rc;
-  if ((rc = grow_buffer(t, &t->overdue, old_pad / 32, np / 32, 0))) return rc;
-  if ((rc = grow_buffer(t, &t->creator_hash, old_pad, np, 0))) return rc;
-  if ((rc = grow_buffer(t, &t->task_id, old_pad, np, 0))) return rc;
-  if ((rc = grow_buffer(t, &t->created_raw, old_pad, np, 0))) return rc;
-  if ((rc = grow_buffer(t, &t->due_raw, old_pad, np, 0))) return rc;
-  if ((rc = grow_buffer(t, &t->creator_ref, old_pad, np, 0))) return rc;
-  if (t->name_col.ref && (rc = grow_buffer(t, &t->name_col.ref, old_pad, np, 0xFF))) return rc;
-  if (t->assignee_col.ref && (rc = grow_buffer(t, &t->assignee_col.ref, old_pad, np, 0xFF))) return rc;
-  cudaFree(t->tile_words);
-  cudaFree(t->group_sum);
-  t->tile_words = t->group_sum = nullptr;
-  t->n_tiles = np / TT_TILE_ROWS;
-  t->n_groups = (t->n_tiles + tt::kTilesPerGroup - 1) / tt::kTilesPerGroup;
-  TT_CUDA(cudaMalloc(&t->tile_words, 3 * t->n_tiles * 4));
-  TT_CUDA(cudaMalloc(&t->group_sum, t->n_groups * 4));
-  t->n_pad = np;
-  return TT_OK;
-}
-
-// Host mirror of the creator dictionary, built once from the device copy.
-int32_t mirror_dictionary(tt_table* t) {
-  if (t->dict_mirrored) return TT_OK;
-  t->h_creator_off.assign((size_t)t->n_creators + 1, 0);
-  t->h_creator_pool.assign(t->pool_bytes, 0);
-  if (t->n_creators) {
-    TT_CUDA(cudaMemcpy(t->h_creator_off.data(), t->creator_off, ((size_t)t->n_creators + 1) * 4, cudaMemcpyDeviceToHost));
-    if (t->pool_bytes) TT_CUDA(cudaMemcpy(t->h_creator_pool.data(), t->creator_pool, t->pool_bytes, cudaMemcpyDeviceToHost));
-  }
-  t->h_creator_index.clear();
-  t->h_creator_index.reserve((size_t)t->n_creators * 2 + 16);
-  for (uint32_t k = 0; k < t->n_creators; ++k)
-    t->h_creator_index.emplace(std::string((const char*)t->h_creator_pool.data() + t->h_creator_off[k],
-                                           t->h_creator_off[k + 1] - t->h_creator_off[k]), k);
-  t->dict_mirrored = true;
-  return TT_OK;
-}
-
-// Dictionary index of a creator string, appending it (host mirror and device arrays) if new.
-int32_t intern_creator(tt_table* t, const char* utf8, int32_t len, uint32_t* ref) {
-  int32_t rc = mirror_dictionary(t);
-  if (rc) return rc;
-  std::string key(utf8 ? utf8 : "", (size_t)len);
-  auto it = t->h_creator_index.find(key);
-  if (it != t->h_creator_index.end()) {
-    *ref = it->second;
-    return TT_OK;
-  }
-  if (t->n_creators == 0xFFFFFFFEu) return fail(TT_ERR_OOM, "creator dictionary is full");
-  const uint32_t k = t->n_creators;
-  const uint32_t start = (uint32_t)t->pool_bytes;
-  if ((size_t)k + 2 > t->creator_off_cap) {
-    const size_t want = std::max<size_t>(2 * t->creator_off_cap, 1024);
-    if ((rc = grow_buffer(t, &t->creator_off, (size_t)k + 1, want, 0))) return rc;
-    t->creator_off_cap = want;
-  }
-  if (t->pool_bytes + (size_t)len > t->creator_pool_cap) {
-    const size_t want = std::max<size_t>(2 * t->creator_pool_cap, t->pool_bytes + (size_t)len + 65536);
-    if ((rc = grow_buffer(t, &t->creator_pool, (size_t)t->pool_bytes, want, 0))) return rc;
-    t->creator_pool_cap = want;
-  }
-  if (t->h_creator_off.empty()) t->h_creator_off.push_back(0);
-  t->h_creator_pool.insert(t->h_creator_pool.end(), key.begin(), key.end());
-  t->h_creator_off.push_back(start + (uint32_t)len);
-  const uint32_t tail[2] = {start, start + (uint32_t)len};
-  TT_CUDA(cudaMemcpyAsync(t->creator_off + k, tail, 8, cudaMemcpyHostToDevice, t->stream));
-  if (len) TT_CUDA(cudaMemcpyAsync(t->creator_pool + start, key.data(), (size_t)len, cudaMemcpyHostToDevice, t->stream));
-  TT_CUDA(cudaStreamSynchronize(t->stream));
-  t->h_creator_index.emplace(std::move(key), k);
-  t->n_creators = k + 1;
-  t->pool_bytes += (uint64_t)len;
-  *ref = k;
-  return TT_OK;
-}
-
-}  // namespace
-
-extern "C" {
-
-int32_t tt_get_by_id(tt_table* t, const uint8_t* id16, tt_result** out) {
-  if (!t || !id16 || !out) return fail(TT_ERR_ARG, "null argument");
-  *out = nullptr;
-  std::lock_guard<std::mutex> lk(t->mu);
-  DeviceGuard g(t->device);
-  int64_t row = -1;
-  int32_t rc = find_row(t, id16, &row);
-  if (rc) return rc;
-  tt_result* r = nullptr;
-  rc = result_alloc(t, 1, &r);
-  if (rc) return rc;
-  if (row >= 0) {
-    const uint32_t r32 = (uint32_t)row;
-    cudaError_t e = cudaMemcpyAsync(r->d_rows, &r32, 4, cudaMemcpyHostToDevice, t->stream);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(r->d_ids, id16, 16, cudaMemcpyHostToDevice, t->stream);
-    if (e == cudaSuccess) e = cudaStreamSynchronize(t->stream);
-    if (e != cudaSuccess) {
-      result_release(r);
-      TT_CUDA(e);
-    }
-    r->n = 1;
-  }
-  *out = r;
-  return TT_OK;
-}
-
-int32_t tt_mark_completed(tt_table* t, const uint8_t* id16, int32_t* found) {
-  if (!t || !id16) return fail(TT_ERR_ARG, "null argument");
-  if (found) *found = 0;
-  std::lock_guard<std::mutex> lk(t->mu);
-  DeviceGuard g(t->device);
-  int64_t row = -1;
-  int32_t rc = find_row(t, id16, &row);
-  if (rc || row < 0) return rc;
-  tt::RowPoke p = {};
-  p.row = (uint32_t)row;
-  p.set_completed = 1;
-  p.completed = 1;
-  if ((rc = poke(t, p))) return rc;
-  if (found) *found = 1;
-  return TT_OK;
-}
-
-int32_t tt_update_task(tt_table* t, const uint8_t* id16, uint64_t due_raw, int32_t* found) {
-  if (!t || !id16) return fail(TT_ERR_ARG, "null argument");
-  if (found) *found = 0;
-  std::lock_guard<std::mutex> lk(t->mu);
-  DeviceGuard g(t->device);
-  int64_t row = -1;
-  int32_t rc = find_row(t, id16, &row);
-  if (rc || row < 0) return rc;
-  tt::RowPoke p = {};
-  p.row = (uint32_t)row;
-  p.set_due = 1;
-  p.due_raw = due_raw;
-  p.due_code = tt_pack_due(due_raw);
-  if ((rc = poke(t, p))) return rc;
-  if (found) *found = 1;
-  return TT_OK;
-}
-
-int32_t tt_delete_task(tt_table* t, const uint8_t* id16, int32_t* found) {
-  if (!t || !id16) return fail(TT_ERR_ARG, "null argument");
-  if (found) *found = 0;
-  std::lock_guard<std::mutex> lk(t->mu);
-  DeviceGuard g(t->device);
-  int64_t row = -1;
-  int32_t rc = find_row(t, id16, &row);
-  if (rc || row < 0) return rc;
-  // the row stays as a tombstone: it can match no sweep, no creator and no id any more
-  tt::RowPoke p = {};
-  p.row = (uint32_t)row;
-  p.set_due = p.set_creator = p.set_completed = p.set_overdue = 1;
-  p.due_raw = 0;
-  p.due_code = TT_DUE_PAD;
-  p.creator_ref = tt::kRowDeleted;
-  p.creator_hash = 0;
-  if ((rc = poke(t, p))) return rc;
-  t->n_live -= 1;
-  if (found) *found = 1;
-  return TT_OK;
-}
-
-int32_t tt_insert_task(tt_table* t, const uint8_t* id16, uint64_t created_raw, uint64_t due_raw, const char* created_by,
-                       int32_t len, int64_t* row_out) {
-  if (!t || !id16 || len < 0 || (len > 0 && !created_by)) return fail(TT_ERR_ARG, "bad argument");
-  std::lock_guard<std::mutex> lk(t->mu);
-  DeviceGuard g(t->device);
-  int32_t rc;
-  if (t->n_pad == 0) {
-    if ((rc = alloc_columns(t, 0))) return rc;
-    static const uint32_t zero_off[1] = {0};
-    if ((rc = upload_dictionary(t, 0, zero_off, nullptr))) return rc;
-    TT_CUDA(cudaStreamSynchronize(t->stream));
-    t->ids_sorted = true;
-  }
-  if (t->n >= kMaxRows) return fail(TT_ERR_OOM, "table is at its maximum of 2^31 rows");
-  if (t->n == t->n_pad && (rc = grow_rows(t))) return rc;
-  uint32_t ref = 0;
-  if ((rc = intern_creator(t, created_by, len, &ref))) return rc;
-  // does the table stay in TaskId order?  (then lookups keep using the binary search)
-  if (t->ids_sorted && t->n > 0) {
-    if (!t->last_id_known) {
-      TT_CUDA(cudaMemcpy(t->last_id, t->task_id + (t->n - 1), 16, cudaMemcpyDeviceToHost));
-      t->last_id_known = true;
-    }
-    if (memcmp(t->last_id, id16, 16) >= 0) t->ids_sorted = false;
-  }
-  if (!t->ids_sorted && t->id_order) {  // the TaskId index no longer covers every row: scan instead
-    cudaFree(t->id_order);
-    t->id_order = nullptr;
-  }
-  memcpy(t->last_id, id16, 16);
-  t->last_id_known = true;
-  tt::RowPoke p = {};
-  p.row = (uint32_t)t->n;
-  p.set_id = p.set_created = p.set_due = p.set_creator = p.set_completed = p.set_overdue = 1;
-  p.id = id_to_uint4(id16);
-  p.created_raw = created_raw;
-  p.due_raw = due_raw;
-  p.due_code = tt_pack_due(due_raw);
-  p.creator_ref = ref;
-  p.creator_hash = tt_hash64((const uint8_t*)created_by, (uint32_t)len);
-  if ((rc = poke(t, p))) return rc;
-  if (row_out) *row_out = t->n;
-  t->n += 1;
-  t->n_live += 1;
-  return TT_OK;
-}
-
-int32_t tt_live_count(tt_table* t, int64_t* n) {
-  if (!t || !n) return fail(TT_ERR_ARG, "null argument");
-  *n = t->n_live;
-  return TT_OK;
-}
-
-}  // extern "C"
-
-// ---- snapshot: the table as a file (checkpoint / resume) ------------------
-//
-// The reference keeps its tasks in a state store (Dapr SaveStateAsync, TasksStoreManager.cs:35)
-// or loses them on restart (FakeTasksManager).  The resident table is saved column by column in
-// its device layout, so loading is a straight copy: no re-encoding, no re-hashing.
-
-namespace {
-
-struct SnapshotHeader {
-  char magic[8];  // "TTSNAP01"
-  int64_t n, n_pad, n_live;
-  uint64_t pool_bytes;
-  uint32_t n_creators;
-  uint32_t ids_sorted;
-  uint32_t tile_rows;
-  uint32_t reserved;
-};
-
-constexpr size_t kSnapChunk = 64u << 20;
-
-int32_t snap_write(FILE* f, const void* dev, size_t bytes, void* stage, cudaStream_t stream) {
-  const unsigned char* p = static_cast<const unsigned char*>(dev);
-  for (size_t off = 0; off < bytes; off += kSnapChunk) {
-    const size_t m = std::min(kSnapChunk, bytes - off);
-    TT_CUDA(cudaMemcpyAsync(stage, p + off, m, cudaMemcpyDeviceToHost, stream));
-    TT_CUDA(cudaStreamSynchronize(stream));
-    if (fwrite(stage, 1, m, f) != m) return fail(TT_ERR_STATE, "short write to snapshot");
-  }
-  return TT_OK;
-}
-
-int32_t snap_read(FILE* f, void* dev, size_t bytes, void* stage, cudaStream_t stream) {
-  unsigned char* p = static_cast<unsigned char*>(dev);
-  for (size_t off = 0; off < bytes; off += kSnapChunk) {
-    const size_t m = std::min(kSnapChunk, bytes - off);
-    if (fread(stage, 1, m, f) != m) return fail(TT_ERR_STATE, "snapshot is truncated");
-    TT_CUDA(cudaMemcpyAsync(p + off, stage, m, cudaMemcpyHostToDevice, stream));
-    TT_CUDA(cudaStreamSynchronize(stream));
-  }
-  return TT_OK;
-}
-
-}  // namespace
-
-extern "C" {
-
-int32_t tt_save_snapshot(tt_table* t, const char* path) {
-  if (!t || !path) return fail(TT_ERR_ARG, "null argument");
-  std::lock_guard<std::mutex> lk(t->mu);
-  DeviceGuard g(t->device);
-  if (t->n_pad == 0) return fail(TT_ERR_STATE, "the table is empty");
-  FILE* f = fopen(path, "wb");
-  if (!f) return fail(TT_ERR_ARG, "cannot open %s for writing", path);
-  void* stage = nullptr;
-  if (cudaMallocHost(&stage, kSnapChunk) != cudaSuccess) {
-    cudaGetLastError();
-    fclose(f);
-    return fail(TT_ERR_OOM, "no pinned staging buffer");
-  }
-  SnapshotHeader h = {};
-  memcpy(h.magic, "TTSNAP01", 8);
-  h.n = t->n;
-  h.n_pad = t->n_pad;
-  h.n_live = t->n_live;
-  h.pool_bytes = t->pool_bytes;
-  h.n_creators = t->n_creators;
-  h.ids_sorted = t->ids_sorted ? 1u : 0u;
-  h.tile_rows = TT_TILE_ROWS;
-  h.reserved = (t->name_col.ref ? 1u : 0u) | (t->assignee_col.ref ? 2u : 0u);
-  int32_t rc = fwrite(&h, sizeof h, 1, f) == 1 ? TT_OK : fail(TT_ERR_STATE, "short write to snapshot");
-  const size_t np = (size_t)t->n_pad;
-  if (!rc) rc = snap_write(f, t->due_code, np * 4, stage, t->stream);
-  if (!rc) rc = snap_write(f, t->completed, np / 8, stage, t->stream);
-  if (!rc) rc = snap_write(f, t->overdue, np / 8, stage, t->stream);
-  if (!rc) rc = snap_write(f, t->creator_hash, np * 8, stage, t->stream);
-  if (!rc) rc = snap_write(f, t->task_id, np * 16, stage, t->stream);
-  if (!rc) rc = snap_write(f, t->created_raw, np * 8, stage, t->stream);
-  if (!rc) rc = snap_write(f, t->due_raw, np * 8, stage, t->stream);
-  if (!rc) rc = snap_write(f, t->creator_ref, np * 4, stage, t->stream);
-  if (!rc) rc = snap_write(f, t->creator_off, ((size_t)t->n_creators + 1) * 4, stage, t->stream);
-  if (!rc && t->pool_bytes) rc = snap_write(f, t->creator_pool, t->pool_bytes, stage, t->stream);
-  // optional payload columns (header.reserved bit 0 = TaskName, bit 1 = TaskAssignedTo), each as
-  // [entries u32][pool bytes u64][ref x n_pad][off x entries+1][pool]
-  const tt_table::StrColumn* cols[2] = {&t->name_col, &t->assignee_col};
-  for (int c = 0; c < 2 && !rc; ++c) {
-    if (!cols[c]->ref) continue;
-    const uint32_t k = cols[c]->n;
-    const uint64_t pb = cols[c]->pool_bytes;
-    if (fwrite(&k, 4, 1, f) != 1 || fwrite(&pb, 8, 1, f) != 1) rc = fail(TT_ERR_STATE, "short write to snapshot");
-    if (!rc) rc = snap_write(f, cols[c]->ref, np * 4, stage, t->stream);
-    if (!rc) rc = snap_write(f, cols[c]->off, ((size_t)k + 1) * 4, stage, t->stream);
-    if (!rc && pb) rc = snap_write(f, cols[c]->pool, (size_t)pb, stage, t->stream);
-  }
-  cudaFreeHost(stage);
-  if (fclose(f) != 0 && !rc) rc = fail(TT_ERR_STATE, "closing %s failed", path);
-  return rc;
-}
-
-int32_t tt_load_snapshot(tt_table* t, const char* path) {
-  if (!t || !path) return fail(TT_ERR_ARG, "null argument");
-  std::lock_guard<std::mutex> lk(t->mu);
-  DeviceGuard g(t->device);
-  if (t->n_pad != 0) return fail(TT_ERR_STATE, "table already holds %lld rows", (long long)t->n);
-  FILE* f = fopen(path, "rb");
-  if (!f) return fail(TT_ERR_ARG, "cannot open %s", path);
-  SnapshotHeader h;
-  if (fread(&h, sizeof h, 1, f) != 1 || memcmp(h.magic, "TTSNAP01", 8) != 0 || h.tile_rows != TT_TILE_ROWS ||
-      h.n < 0 || h.n > h.n_pad || h.n_pad % TT_TILE_ROWS != 0 || h.n_pad > kMaxRows) {
-    fclose(f);
-    return fail(TT_ERR_ARG, "%s is not a task table snapshot", path);
-  }
-  void* stage = nullptr;
-  if (cudaMallocHost(&stage, kSnapChunk) != cudaSuccess) {
-    cudaGetLastError();
-    fclose(f);
-    return fail(TT_ERR_OOM, "no pinned staging buffer");
-  }
-  int32_t rc = alloc_columns(t, h.n_pad);  // exactly the saved capacity
-  const size_t np = (size_t)h.n_pad;
-  if (!rc) rc = snap_read(f, t->due_code, np * 4, stage, t->stream);
-  if (!rc) rc = snap_read(f, t->completed, np / 8, stage, t->stream);
-  if (!rc) rc = snap_read(f, t->overdue, np / 8, stage, t->stream);
-  if (!rc) rc = snap_read(f, t->creator_hash, np * 8, stage, t->stream);
-  if (!rc) rc = snap_read(f, t->task_id, np * 16, stage, t->stream);
-  if (!rc) rc = snap_read(f, t->created_raw, np * 8, stage, t->stream);
-  if (!rc) rc = snap_read(f, t->due_raw, np * 8, stage, t->stream);
-  if (!rc) rc = snap_read(f, t->creator_ref, np * 4, stage, t->stream);
-  if (!rc) {
-    t->n = h.n;
-    t->n_live = h.n_live;
-    t->n_creators = h.n_creators;
-    t->pool_bytes = h.pool_bytes;
-    t->creator_off_cap = (size_t)h.n_creators + 1;
-    t->creator_pool_cap = std::max<uint64_t>(h.pool_bytes, 16);
-    t->ids_sorted = h.ids_sorted != 0;
-    cudaError_t e = cudaMalloc(&t->creator_off, t->creator_off_cap * 4);
-    if (e == cudaSuccess) e = cudaMalloc(&t->creator_pool, t->creator_pool_cap);
-    if (e != cudaSuccess) {
-      cudaGetLastError();
-      rc = fail(TT_ERR_OOM, "creator dictionary: %s", cudaGetErrorString(e));
-    }
-  }
-  if (!rc) rc = snap_read(f, t->creator_off, ((size_t)h.n_creators + 1) * 4, stage, t->stream);
-  if (!rc && h.pool_bytes) rc = snap_read(f, t->creator_pool, h.pool_bytes, stage, t->stream);
-  tt_table::StrColumn* cols[2] = {&t->name_col, &t->assignee_col};
-  for (int c = 0; c < 2 && !rc; ++c) {
-    if (!(h.reserved & (1u << c))) continue;
-    uint32_t k = 0;
-    uint64_t pb = 0;
-    if (fread(&k, 4, 1, f) != 1 || fread(&pb, 8, 1, f) != 1 || pb >= (1ull << 32)) {
-      rc = fail(TT_ERR_ARG, "%s: truncated payload section", path);
-      break;
-    }
-    cudaError_t e = cudaMalloc(&cols[c]->ref, np * 4);
-    if (e == cudaSuccess) e = cudaMalloc(&cols[c]->off, ((size_t)k + 1) * 4);
-    if (e == cudaSuccess) e = cudaMalloc(&cols[c]->pool, std::max<uint64_t>(pb, 16));
-    if (e != cudaSuccess) {
-      cudaGetLastError();
-      rc = fail(TT_ERR_OOM, "payload column: %s", cudaGetErrorString(e));
-      break;
-    }
-    cols[c]->n = k;
-    cols[c]->off_cap = (size_t)k + 1;
-    cols[c]->pool_cap = std::max<uint64_t>(pb, 16);
-    cols[c]->pool_bytes = pb;
-    rc = snap_read(f, cols[c]->ref, np * 4, stage, t->stream);
-    if (!rc) rc = snap_read(f, cols[c]->off, ((size_t)k + 1) * 4, stage, t->stream);
-    if (!rc && pb) rc = snap_read(f, cols[c]->pool, (size_t)pb, stage, t->stream);
-  }
-  cudaFreeHost(stage);
-  fclose(f);
-  if (rc) {
-    free_columns(t);
-    return rc;
-  }
-  if (!t->ids_sorted && t->n > 0) {
-    // rebuild the TaskId index on the host (ingest path, like tt_load_soa)
-    std::vector<uint8_t> ids((size_t)t->n * 16);
-    TT_CUDA(cudaMemcpy(ids.data(), t->task_id, ids.size(), cudaMemcpyDeviceToHost));
-    std::vector<uint32_t> order((size_t)t->n);
-    for (int64_t i = 0; i < t->n; ++i) order[i] = (uint32_t)i;
-    const uint8_t* p = ids.data();
-    std::stable_sort(order.begin(), order.end(),
-                     [p](uint32_t a, uint32_t b) { return memcmp(p + 16 * (size_t)a, p + 16 * (size_t)b, 16) < 0; });
-    TT_CUDA(cudaMalloc(&t->id_order, (size_t)t->n * 4));
-    TT_CUDA(cudaMemcpy(t->id_order, order.data(), (size_t)t->n * 4, cudaMemcpyHostToDevice));
-  }
-  return TT_OK;
-}
-
-}  // extern "C"
+#include "api_snapshot.inc"
 
 // ---- compact hit lists for the cross-shard exchange ------------------------------------------------
 
@@ -1924,850 +1465,11 @@ int32_t tt_expand_hits(int32_t device, const uint32_t* d_tile_count, int64_t n_t
 
 }  // extern "C"
 
-// ---- payload strings and the JSON form of a result (K6, csrc/json.cuh) ----------------------------
+#include "api_json.inc"
 
-struct tt_json {
-  std::shared_ptr<TableCore> core;
-  uint8_t* d_text = nullptr;
-  int64_t bytes = 0;
-  uint64_t* d_off = nullptr;  // [records + 1]
-  int64_t records = 0;
-};
+#include "api_ingest.inc"
 
-namespace {
-
-__global__ void fill_payload_kernel(tt_synth_cfg cfg, uint64_t first_row, int64_t n, uint32_t* name_ref,
-                                    uint32_t* assignee_ref) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  name_ref[i] = tt_synth_name_ref(&cfg, first_row + (uint64_t)i);
-  assignee_ref[i] = tt_synth_assignee_ref(&cfg, first_row + (uint64_t)i);
-}
-
-int32_t check_strings(const tt_strings_view* v, int64_t n, const char* what) {
-  if (!v) return TT_OK;
-  if (n > 0 && !v->ref) return fail(TT_ERR_ARG, "%s: null ref column", what);
-  if (!v->off || (v->n_strings && v->off[v->n_strings] != 0 && !v->pool)) return fail(TT_ERR_ARG, "%s: dictionary missing", what);
-  for (uint32_t k = 0; k < v->n_strings; ++k)
-    if (v->off[k + 1] < v->off[k]) return fail(TT_ERR_ARG, "%s: offsets not ascending", what);
-  for (int64_t i = 0; i < n; ++i)
-    if (v->ref[i] >= v->n_strings && v->ref[i] != 0xFFFFFFFFu)
-      return fail(TT_ERR_ARG, "%s: ref[%lld] out of range", what, (long long)i);
-  return TT_OK;
-}
-
-void drop_column(tt_table::StrColumn* c) {
-  cudaFree(c->ref);
-  cudaFree(c->off);
-  cudaFree(c->pool);
-  *c = tt_table::StrColumn();
-}
-
-// Allocates one payload column (refs all "no string") and uploads its dictionary.
-int32_t set_column(tt_table* t, tt_table::StrColumn* c, int which, uint32_t n_strings, const uint32_t* off,
-                   const uint8_t* pool, const uint32_t* ref_host) {
-  drop_column(c);
-  for (auto& e : t->esc[which]) {
-    cudaFree(e.entry);
-    cudaFree(e.pool);
-    e = tt_table::EscCache();
-  }
-  const size_t bytes = n_strings ? off[n_strings] : 0;
-  TT_CUDA(cudaMalloc(&c->ref, (size_t)t->n_pad * 4));
-  TT_CUDA(cudaMalloc(&c->off, ((size_t)n_strings + 1) * 4));
-  TT_CUDA(cudaMalloc(&c->pool, std::max<size_t>(bytes, 16)));
-  TT_CUDA(cudaMemsetAsync(c->ref, 0xFF, (size_t)t->n_pad * 4, t->stream));
-  TT_CUDA(cudaMemcpyAsync(c->off, off, ((size_t)n_strings + 1) * 4, cudaMemcpyHostToDevice, t->stream));
-  if (bytes) TT_CUDA(cudaMemcpyAsync(c->pool, pool, bytes, cudaMemcpyHostToDevice, t->stream));
-  if (ref_host && t->n) TT_CUDA(cudaMemcpyAsync(c->ref, ref_host, (size_t)t->n * 4, cudaMemcpyHostToDevice, t->stream));
-  TT_CUDA(cudaStreamSynchronize(t->stream));
-  c->n = n_strings;
-  c->off_cap = (size_t)n_strings + 1;
-  c->pool_cap = std::max<size_t>(bytes, 16);
-  c->pool_bytes = bytes;
-  return TT_OK;
-}
-
-// Dictionary index of a TaskName / TaskAssignedTo value, appending it (host mirror and device arrays)
-// if it is new.  Same scheme as intern_creator; the column is created empty if the table has none.
-int32_t intern_string(tt_table* t, tt_table::StrColumn* c, int which, const char* utf8, int32_t len, uint32_t* ref) {
-  int32_t rc;
-  if (!c->ref) {
-    static const uint32_t zero_off[1] = {0};
-    if ((rc = set_column(t, c, which, 0, zero_off, nullptr, nullptr))) return rc;
-  }
-  if (!c->mirrored) {
-    c->h_off.assign((size_t)c->n + 1, 0);
-    c->h_pool.assign((size_t)c->pool_bytes, 0);
-    TT_CUDA(cudaMemcpy(c->h_off.data(), c->off, ((size_t)c->n + 1) * 4, cudaMemcpyDeviceToHost));
-    if (c->pool_bytes) TT_CUDA(cudaMemcpy(c->h_pool.data(), c->pool, (size_t)c->pool_bytes, cudaMemcpyDeviceToHost));
-    c->h_index.clear();
-    c->h_index.reserve((size_t)c->n * 2 + 16);
-    for (uint32_t k = 0; k < c->n; ++k)
-      c->h_index.emplace(std::string((const char*)c->h_pool.data() + c->h_off[k], c->h_off[k + 1] - c->h_off[k]), k);
-    c->mirrored = true;
-  }
-  std::string key(utf8 ? utf8 : "", (size_t)len);
-  auto it = c->h_index.find(key);
-  if (it != c->h_index.end()) {
-    *ref = it->second;
-    return TT_OK;
-  }
-  if (c->n == 0xFFFFFFFEu || c->pool_bytes + (uint64_t)len >= (1ull << 32)) return fail(TT_ERR_OOM, "string dictionary is full");
-  const uint32_t k = c->n, start = (uint32_t)c->pool_bytes;
-  if ((size_t)k + 2 > c->off_cap) {
-    const size_t want = std::max<size_t>(2 * c->off_cap, 1024);
-    if ((rc = grow_buffer(t, &c->off, (size_t)k + 1, want, 0))) return rc;
-    c->off_cap = want;
-  }
-  if (c->pool_bytes + (size_t)len > c->pool_cap) {
-    const size_t want = std::max<size_t>(2 * c->pool_cap, (size_t)c->pool_bytes + (size_t)len + 65536);
-    if ((rc = grow_buffer(t, &c->pool, (size_t)c->pool_bytes, want, 0))) return rc;
-    c->pool_cap = want;
-  }
-  const uint32_t tail[2] = {start, start + (uint32_t)len};
-  TT_CUDA(cudaMemcpyAsync(c->off + k, tail, 8, cudaMemcpyHostToDevice, t->stream));
-  if (len) TT_CUDA(cudaMemcpyAsync(c->pool + start, key.data(), (size_t)len, cudaMemcpyHostToDevice, t->stream));
-  TT_CUDA(cudaStreamSynchronize(t->stream));
-  c->h_pool.insert(c->h_pool.end(), key.begin(), key.end());
-  c->h_off.push_back(start + (uint32_t)len);
-  c->h_index.emplace(std::move(key), k);
-  c->n = k + 1;
-  c->pool_bytes += (uint64_t)len;
-  *ref = k;
-  return TT_OK;
-}
-
-// Escaped form of one dictionary for one encoder, cached until the dictionary changes.
-int32_t prepare_escaped(tt_table* t, int which, int flavor, const uint32_t* off, const uint8_t* pool, uint32_t n,
-                        const char* what) {
-  tt_table::EscCache& e = t->esc[which][flavor];
-  if (e.ready && e.n == n) return TT_OK;
-  cudaFree(e.entry);
-  cudaFree(e.pool);
-  e = tt_table::EscCache();
-  if (n == 0) {
-    e.ready = true;
-    return TT_OK;
-  }
-  const uint32_t nb = (n + tt::kScanBlock - 1) / tt::kScanBlock;
-  uint32_t* d_len = nullptr;
-  uint64_t* d_blocks = nullptr;
-  uint32_t* d_err = nullptr;
-  auto cleanup = [&] {
-    cudaFree(d_len);
-    cudaFree(d_blocks);
-    cudaFree(d_err);
-  };
-  cudaError_t ce = cudaMalloc(&d_len, (size_t)n * 4);
-  if (ce == cudaSuccess) ce = cudaMalloc(&d_blocks, ((size_t)nb + 1) * 8);
-  if (ce == cudaSuccess) ce = cudaMalloc(&d_err, 8);
-  if (ce == cudaSuccess) ce = cudaMalloc(&e.entry, (size_t)n * sizeof(tt::EscEntry));
-  if (ce == cudaSuccess) ce = cudaMemsetAsync(d_err, 0, 8, t->stream);
-  if (ce != cudaSuccess) {
-    cleanup();
-    TT_CUDA(ce);
-  }
-  tt::esc_len_kernel<<<grid_for(n, 256), 256, 0, t->stream>>>(off, pool, n, flavor, d_len, d_err);
-  tt::esc_block_sum_kernel<<<nb, tt::kScanBlock, 0, t->stream>>>(d_len, n, d_blocks);
-  tt::scan_block_sums_kernel<<<1, 1024, 0, t->stream>>>(d_blocks, nb);
-  tt::esc_entries_kernel<<<nb, tt::kScanBlock, 0, t->stream>>>(d_len, n, d_blocks, e.entry);
-  uint32_t h_err[2] = {0, 0};
-  uint64_t words = 0;
-  ce = cudaGetLastError();
-  if (ce == cudaSuccess) ce = cudaMemcpyAsync(h_err, d_err, 8, cudaMemcpyDeviceToHost, t->stream);
-  if (ce == cudaSuccess) ce = cudaMemcpyAsync(&words, d_blocks + nb, 8, cudaMemcpyDeviceToHost, t->stream);
-  if (ce == cudaSuccess) ce = cudaStreamSynchronize(t->stream);
-  if (ce == cudaSuccess && !h_err[0] && words < (1ull << 32)) {
-    ce = cudaMalloc(&e.pool, std::max<size_t>((size_t)words * 4, 16));
-    if (ce == cudaSuccess) {
-      tt::esc_write_kernel<<<grid_for(n, 256), 256, 0, t->stream>>>(off, pool, n, flavor, e.entry, e.pool);
-      ce = cudaGetLastError();
-    }
-    if (ce == cudaSuccess) ce = cudaStreamSynchronize(t->stream);
-  }
-  cleanup();
-  if (ce != cudaSuccess || h_err[0] || words >= (1ull << 32)) {
-    cudaFree(e.entry);
-    cudaFree(e.pool);
-    e = tt_table::EscCache();
-    if (ce != cudaSuccess) TT_CUDA(ce);
-    if (h_err[0])
-      return fail(TT_ERR_ARG, "%s dictionary entry %u is not well-formed UTF-8 or escapes to more than %u bytes", what,
-                  h_err[1], tt::kEscMaxLen);
-    return fail(TT_ERR_ARG, "%s dictionary escapes to more than 16 GB", what);
-  }
-  e.n = n;
-  e.ready = true;
-  return TT_OK;
-}
-
-}  // namespace
-
-extern "C" {
-
-int32_t tt_load_payload(tt_table* t, const tt_strings_view* task_name, const tt_strings_view* assigned_to) {
-  if (!t) return fail(TT_ERR_ARG, "null argument");
-  std::lock_guard<std::mutex> lk(t->mu);
-  DeviceGuard g(t->device);
-  if (t->n_pad == 0) return fail(TT_ERR_STATE, "load the rows first");
-  int32_t rc;
-  if ((rc = check_strings(task_name, t->n, "TaskName"))) return rc;
-  if ((rc = check_strings(assigned_to, t->n, "TaskAssignedTo"))) return rc;
-  if (task_name && (rc = set_column(t, &t->name_col, 0, task_name->n_strings, task_name->off, task_name->pool, task_name->ref)))
-    return rc;
-  if (assigned_to &&
-      (rc = set_column(t, &t->assignee_col, 2, assigned_to->n_strings, assigned_to->off, assigned_to->pool, assigned_to->ref)))
-    return rc;
-  return TT_OK;
-}
-
-int32_t tt_generate_payload(tt_table* t, const tt_synth_cfg* cfg, uint64_t first_row) {
-  if (!t || !cfg) return fail(TT_ERR_ARG, "null argument");
-  std::lock_guard<std::mutex> lk(t->mu);
-  DeviceGuard g(t->device);
-  if (t->n_pad == 0) return fail(TT_ERR_STATE, "generate the rows first");
-  // the two dictionaries are built on the host (ingest, not hot path); the refs on the device
-  std::vector<uint32_t> off;
-  std::vector<uint8_t> pool;
-  char buf[64];
-  auto build = [&](uint32_t n, int (*make)(uint32_t, char*)) {
-    off.assign((size_t)n + 1, 0);
-    pool.clear();
-    for (uint32_t k = 0; k < n; ++k) {
-      const int len = make(k, buf);
-      pool.insert(pool.end(), buf, buf + len);
-      off[k + 1] = (uint32_t)pool.size();
-    }
-  };
-  int32_t rc;
-  build(tt_synth_n_names(cfg), [](uint32_t k, char* o) { return tt_synth_name(k, o); });
-  if ((rc = set_column(t, &t->name_col, 0, tt_synth_n_names(cfg), off.data(), pool.data(), nullptr))) return rc;
-  build(TT_SYNTH_ASSIGNEES, [](uint32_t k, char* o) { return tt_synth_assignee(k, o); });
-  if ((rc = set_column(t, &t->assignee_col, 2, TT_SYNTH_ASSIGNEES, off.data(), pool.data(), nullptr))) return rc;
-  if (t->n) {
-    fill_payload_kernel<<<grid_for(t->n, 256), 256, 0, t->stream>>>(*cfg, first_row, t->n, t->name_col.ref, t->assignee_col.ref);
-    TT_CUDA(cudaGetLastError());
-    TT_CUDA(cudaStreamSynchronize(t->stream));
-  }
-  return TT_OK;
-}
-
-int32_t tt_set_task_strings(tt_table* t, const uint8_t* id16, const char* task_name, int32_t name_len,
-                            const char* assigned_to, int32_t assigned_len, int32_t* found) {
-  if (!t || !id16 || name_len < -1 || assigned_len < -1 || (name_len > 0 && !task_name) || (assigned_len > 0 && !assigned_to))
-    return fail(TT_ERR_ARG, "bad argument");
-  if (found) *found = 0;
-  std::lock_guard<std::mutex> lk(t->mu);
-  DeviceGuard g(t->device);
-  if (t->n_pad == 0) return TT_OK;
-  int64_t row = -1;
-  int32_t rc = find_row(t, id16, &row);
-  if (rc) return rc;
-  if (row < 0) return TT_OK;
-  const char* text[2] = {task_name, assigned_to};
-  const int32_t lens[2] = {name_len, assigned_len};
-  tt_table::StrColumn* cols[2] = {&t->name_col, &t->assignee_col};
-  for (int c = 0; c < 2; ++c) {
-    if (lens[c] < 0) continue;  // -1: leave this member as it is
-    uint32_t ref = 0;
-    if ((rc = intern_string(t, cols[c], c == 0 ? 0 : 2, text[c], lens[c], &ref))) return rc;
-    TT_CUDA(cudaMemcpyAsync(cols[c]->ref + row, &ref, 4, cudaMemcpyHostToDevice, t->stream));
-    TT_CUDA(cudaStreamSynchronize(t->stream));
-  }
-  if (found) *found = 1;
-  return TT_OK;
-}
-
-int32_t tt_result_json(tt_result* r, int32_t flavor, int32_t local_offset_min, tt_json** out) {
-  if (!r || !out) return fail(TT_ERR_ARG, "null argument");
-  *out = nullptr;
-  if (flavor != TT_JSON_RESPONSE && flavor != TT_JSON_DOCUMENT) return fail(TT_ERR_ARG, "flavor must be TT_JSON_RESPONSE or TT_JSON_DOCUMENT");
-  if (local_offset_min <= -24 * 60 || local_offset_min >= 24 * 60) return fail(TT_ERR_ARG, "local_offset_min out of range");
-  if (!r->core->alive) return fail(TT_ERR_STATE, "the table of this result has been destroyed");
-  tt_table* t = r->t;
-  std::lock_guard<std::mutex> lk(t->mu);
-  DeviceGuard g(t->device);
-  t->last_json = tt_json_stats{};
-  tt_json* j = new (std::nothrow) tt_json();
-  if (!j) return fail(TT_ERR_OOM, "out of host memory");
-  j->core = t->core;
-  const int64_t n = r->n;
-  if (n == 0) {  // "[]"
-    cudaError_t e = cudaMalloc(&j->d_text, 16);
-    if (e == cudaSuccess) e = cudaMemcpy(j->d_text, "[]", 2, cudaMemcpyHostToDevice);
-    if (e != cudaSuccess) {
-      cudaFree(j->d_text);
-      delete j;
-      TT_CUDA(e);
-    }
-    j->bytes = 2;
-    t->last_json.bytes = 2;
-    *out = j;
-    return TT_OK;
-  }
-  int32_t rc = TT_OK;
-  if (t->name_col.ref) rc = prepare_escaped(t, 0, flavor, t->name_col.off, t->name_col.pool, t->name_col.n, "TaskName");
-  if (!rc) rc = prepare_escaped(t, 1, flavor, t->creator_off, t->creator_pool, t->n_creators, "TaskCreatedBy");
-  if (!rc && t->assignee_col.ref)
-    rc = prepare_escaped(t, 2, flavor, t->assignee_col.off, t->assignee_col.pool, t->assignee_col.n, "TaskAssignedTo");
-  if (rc) {
-    delete j;
-    return rc;
-  }
-  const int64_t nb = (n + tt::kJsonThreads - 1) / tt::kJsonThreads;
-  if (nb + 1 > t->json_blocks_cap) {
-    cudaFree(t->json_blocks);
-    t->json_blocks = nullptr;
-    t->json_blocks_cap = 0;
-    cudaError_t e = cudaMalloc(&t->json_blocks, (size_t)(nb + 1) * 8);
-    if (e != cudaSuccess) {
-      delete j;
-      TT_CUDA(e);
-    }
-    t->json_blocks_cap = nb + 1;
-  }
-  if (n > t->json_plan_cap) {
-    cudaFree(t->json_plan);
-    t->json_plan = nullptr;
-    t->json_plan_cap = 0;
-    const int64_t want = round_up(n, 1024);
-    cudaError_t e = cudaMalloc(&t->json_plan, (size_t)want * 5 * 8);
-    if (e != cudaSuccess) {
-      delete j;
-      TT_CUDA(e);
-    }
-    t->json_plan_cap = want;
-  }
-  tt::JsonParams p = {};
-  p.plan = t->json_plan;
-  p.plan_stride = t->json_plan_cap;
-  p.rows = r->d_rows;
-  p.ids = r->d_ids;
-  p.n = n;
-  p.created_raw = t->created_raw;
-  p.due_raw = t->due_raw;
-  p.completed = t->completed;
-  p.overdue = t->overdue;
-  const uint32_t* refs[3] = {t->name_col.ref, t->creator_ref, t->assignee_col.ref};
-  const uint32_t dict_n[3] = {t->name_col.n, t->n_creators, t->assignee_col.n};
-  for (int c = 0; c < 3; ++c) {
-    const tt_table::EscCache& e = t->esc[c][flavor];
-    p.ref[c] = (refs[c] && e.ready && e.n) ? refs[c] : nullptr;
-    p.dict_n[c] = dict_n[c];
-    p.entry[c] = e.entry;
-    p.esc_pool[c] = e.pool;
-  }
-  p.local_offset_min = local_offset_min;
-  p.block_base = t->json_blocks;
-  cudaError_t e = cudaSuccess;
-  if (!t->json_smem_opted) {  // a per-device attribute
-    e = cudaFuncSetAttribute(tt::json_emit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, tt::kJsonStageBytes);
-    t->json_smem_opted = e == cudaSuccess;
-  }
-  uint64_t total = 0;
-  if (e == cudaSuccess) e = cudaEventRecord(t->ev0, t->stream);
-  if (e == cudaSuccess) {
-    tt::json_len_kernel<<<(unsigned)nb, tt::kJsonThreads, 0, t->stream>>>(p);
-    tt::scan_block_sums_kernel<<<1, 1024, 0, t->stream>>>(t->json_blocks, (uint32_t)nb);
-    e = cudaGetLastError();
-  }
-  if (e == cudaSuccess) e = cudaEventRecord(t->ev1, t->stream);
-  if (e == cudaSuccess) e = cudaMemcpyAsync(&total, t->json_blocks + nb, 8, cudaMemcpyDeviceToHost, t->stream);
-  if (e == cudaSuccess) e = cudaStreamSynchronize(t->stream);
-  if (e == cudaSuccess) e = cudaMalloc(&j->d_text, (size_t)total + 16);
-  if (e == cudaSuccess) e = cudaMalloc(&j->d_off, ((size_t)n + 1) * 8);
-  if (e == cudaSuccess) e = cudaMemcpyAsync(j->d_off + n, &total, 8, cudaMemcpyHostToDevice, t->stream);
-  if (e == cudaSuccess) {
-    p.out = j->d_text;
-    p.rec_off = j->d_off;
-    tt::json_emit_kernel<<<(unsigned)nb, tt::kJsonThreads, tt::kJsonStageBytes, t->stream>>>(p);
-    e = cudaGetLastError();
-  }
-  if (e == cudaSuccess) e = cudaEventRecord(t->ev2, t->stream);
-  if (e == cudaSuccess) e = cudaStreamSynchronize(t->stream);
-  if (e != cudaSuccess) {
-    cudaFree(j->d_text);
-    cudaFree(j->d_off);
-    delete j;
-    TT_CUDA(e);
-  }
-  j->bytes = (int64_t)total;
-  j->records = n;
-  cudaEventElapsedTime(&t->last_json.size_ms, t->ev0, t->ev1);
-  cudaEventElapsedTime(&t->last_json.emit_ms, t->ev1, t->ev2);
-  t->last_json.bytes = j->bytes;
-  t->last_json.records = n;
-  t->last_json.launches = 3;
-  *out = j;
-  return TT_OK;
-}
-
-int32_t tt_json_size(const tt_json* j, int64_t* bytes) {
-  if (!j || !bytes) return fail(TT_ERR_ARG, "null argument");
-  *bytes = j->bytes;
-  return TT_OK;
-}
-
-int32_t tt_json_copy(tt_json* j, void* dst) {
-  if (!j || !dst) return fail(TT_ERR_ARG, "null argument");
-  DeviceGuard g(j->core->device);
-  TT_CUDA(cudaMemcpy(dst, j->d_text, (size_t)j->bytes, cudaMemcpyDefault));
-  return TT_OK;
-}
-
-int32_t tt_json_device(tt_json* j, const void** d_text) {
-  if (!j || !d_text) return fail(TT_ERR_ARG, "null argument");
-  *d_text = j->d_text;
-  return TT_OK;
-}
-
-int32_t tt_json_offsets(tt_json* j, uint64_t* dst) {
-  if (!j || !dst) return fail(TT_ERR_ARG, "null argument");
-  DeviceGuard g(j->core->device);
-  if (j->records == 0) {  // "[]": no records, off[0] = the length of the text
-    const uint64_t len = (uint64_t)j->bytes;
-    TT_CUDA(cudaMemcpy(dst, &len, 8, cudaMemcpyDefault));
-    return TT_OK;
-  }
-  TT_CUDA(cudaMemcpy(dst, j->d_off, ((size_t)j->records + 1) * 8, cudaMemcpyDefault));
-  return TT_OK;
-}
-
-int32_t tt_json_free(tt_json* j) {
-  if (!j) return TT_OK;
-  {
-    DeviceGuard g(j->core->device);
-    cudaFree(j->d_text);
-    cudaFree(j->d_off);
-  }
-  delete j;
-  return TT_OK;
-}
-
-int32_t tt_last_json_stats(tt_table* t, tt_json_stats* out) {
-  if (!t || !out) return fail(TT_ERR_ARG, "null argument");
-  std::lock_guard<std::mutex> lk(t->mu);
-  *out = t->last_json;
-  return TT_OK;
-}
-
-}  // extern "C"
-
-// ---- bulk load of JSON documents (K7, csrc/ingest.cuh) ---------------------------------------------
-
-namespace {
-
-// Everything tt_load_documents allocates besides the table itself; freed on every exit path.
-struct IngestScratch {
-  std::vector<void*> blocks;
-  template <typename T>
-  cudaError_t get(T** p, size_t count) {
-    void* q = nullptr;
-    cudaError_t e = cudaMalloc(&q, std::max<size_t>(count * sizeof(T), 16));
-    if (e == cudaSuccess) blocks.push_back(q);
-    *p = static_cast<T*>(q);
-    return e;
-  }
-  ~IngestScratch() {
-    for (void* b : blocks) cudaFree(b);
-  }
-};
-
-// Dictionary-encodes one string member of the parsed documents: ref[doc] and a fresh dictionary
-// (off / pool, allocated here and handed to the caller).
-int32_t encode_member(tt_table* t, IngestScratch& sc, const tt::DocCols& d, int c, const uint8_t* text, int64_t n,
-                      uint32_t* ref_out, uint32_t** off_out, uint8_t** pool_out, uint32_t* k_out, uint64_t* bytes_out,
-                      int* launches) {
-  cudaStream_t st = t->stream;
-  cudaError_t e = t->sort.reserve(n);
-  if (e != cudaSuccess) TT_CUDA(e);
-  tt::dict_keys_kernel<<<grid_for(n, 256), 256, 0, st>>>(d.str_hash[c], n, t->sort.keys[0], t->sort.vals[0]);
-  int w = 0;
-  e = tt::radix_sort_pairs(st, t->sort, n, 64, &w);
-  if (e != cudaSuccess) TT_CUDA(e);
-  const unsigned long long* keys = t->sort.keys[w];
-  const uint32_t* docs = t->sort.vals[w];
-  const uint32_t nb = (uint32_t)((n + tt::kScanBlock - 1) / tt::kScanBlock);
-  uint64_t* blocks = nullptr;
-  uint32_t* entry_doc = nullptr;
-  TT_CUDA(sc.get(&blocks, (size_t)nb + 1));
-  TT_CUDA(sc.get(&entry_doc, (size_t)n));
-  uint8_t* head = nullptr;
-  TT_CUDA(sc.get(&head, (size_t)n));
-  tt::dict_head_sum_kernel<<<nb, tt::kScanBlock, 0, st>>>(keys, docs, text, d.str_start[c], d.str_len[c], n, head, blocks);
-  tt::scan_block_sums_kernel<<<1, 1024, 0, st>>>(blocks, nb);
-  tt::dict_assign_kernel<<<nb, tt::kScanBlock, 0, st>>>(docs, head, n, blocks, ref_out, entry_doc);
-  uint64_t k64 = 0;
-  TT_CUDA(cudaGetLastError());
-  TT_CUDA(cudaMemcpyAsync(&k64, blocks + nb, 8, cudaMemcpyDeviceToHost, st));
-  TT_CUDA(cudaStreamSynchronize(st));
-  const uint32_t k = (uint32_t)k64;
-  const uint32_t kb = (k + tt::kScanBlock - 1) / tt::kScanBlock;
-  uint64_t* lblocks = nullptr;
-  TT_CUDA(sc.get(&lblocks, (size_t)kb + 1));
-  tt::dict_len_sum_kernel<<<kb, tt::kScanBlock, 0, st>>>(entry_doc, d.str_len[c], k, lblocks);
-  tt::scan_block_sums_kernel<<<1, 1024, 0, st>>>(lblocks, kb);
-  uint64_t bytes = 0;
-  TT_CUDA(cudaGetLastError());
-  TT_CUDA(cudaMemcpyAsync(&bytes, lblocks + kb, 8, cudaMemcpyDeviceToHost, st));
-  TT_CUDA(cudaStreamSynchronize(st));
-  if (bytes >= (1ull << 32)) return fail(TT_ERR_ARG, "the distinct strings of one member exceed 4 GB");
-  uint32_t* off = nullptr;
-  uint8_t* pool = nullptr;
-  TT_CUDA(cudaMalloc(&off, ((size_t)k + 1) * 4));
-  cudaError_t e2 = cudaMalloc(&pool, std::max<uint64_t>(bytes, 16));
-  if (e2 != cudaSuccess) {
-    cudaFree(off);
-    TT_CUDA(e2);
-  }
-  tt::dict_build_kernel<<<kb, tt::kScanBlock, 0, st>>>(entry_doc, d.str_start[c], d.str_len[c], text, k, lblocks, off, pool);
-  const uint32_t total32 = (uint32_t)bytes;
-  e2 = cudaGetLastError();
-  if (e2 == cudaSuccess) e2 = cudaMemcpyAsync(off + k, &total32, 4, cudaMemcpyHostToDevice, st);
-  if (e2 == cudaSuccess) e2 = cudaStreamSynchronize(st);
-  if (e2 != cudaSuccess) {
-    cudaFree(off);
-    cudaFree(pool);
-    TT_CUDA(e2);
-  }
-  *off_out = off;
-  *pool_out = pool;
-  *k_out = k;
-  *bytes_out = bytes;
-  *launches += 7 + 4 * 8;
-  return TT_OK;
-}
-
-}  // namespace
-
-extern "C" int32_t tt_load_documents(tt_table* t, const void* docs, const uint64_t* doc_off, int64_t n,
-                                     int32_t local_offset_min, tt_ingest_stats* stats) {
-  if (!t || n < 0 || (n > 0 && (!docs || !doc_off))) return fail(TT_ERR_ARG, "bad argument");
-  if (local_offset_min <= -24 * 60 || local_offset_min >= 24 * 60) return fail(TT_ERR_ARG, "local_offset_min out of range");
-  tt_ingest_stats local_stats;
-  if (!stats) stats = &local_stats;
-  memset(stats, 0, sizeof *stats);
-  stats->first_bad = -1;
-  std::lock_guard<std::mutex> lk(t->mu);
-  DeviceGuard g(t->device);
-  if (t->n_pad != 0) return fail(TT_ERR_STATE, "table already holds %lld rows", (long long)t->n);
-  if (n > kMaxRows) return fail(TT_ERR_ARG, "row count %lld outside [0, 2^31]", (long long)n);
-  cudaStream_t st = t->stream;
-  IngestScratch sc;
-  // the offsets may live in host or device memory; only the two ends are needed here, the kernel
-  // checks every document's range against them
-  uint64_t ends[2] = {0, 0};
-  if (n) {
-    cudaPointerAttributes attr;
-    const bool on_device = cudaPointerGetAttributes(&attr, doc_off) == cudaSuccess && attr.type == cudaMemoryTypeDevice;
-    cudaGetLastError();
-    if (on_device) {
-      TT_CUDA(cudaMemcpy(&ends[0], doc_off, 8, cudaMemcpyDeviceToHost));
-      TT_CUDA(cudaMemcpy(&ends[1], doc_off + n, 8, cudaMemcpyDeviceToHost));
-    } else {
-      ends[0] = doc_off[0];
-      ends[1] = doc_off[n];
-    }
-    if (ends[1] < ends[0]) return fail(TT_ERR_ARG, "doc_off[n] < doc_off[0]");
-  }
-  const uint64_t first = ends[0], bytes = ends[1] - ends[0];
-  uint8_t* text = nullptr;
-  uint64_t* d_off = nullptr;
-  tt::DocCols d = {};
-  unsigned long long* d_err = nullptr;
-  TT_CUDA(sc.get(&text, (size_t)bytes + 16));
-  TT_CUDA(sc.get(&d_off, (size_t)n + 1));
-  TT_CUDA(sc.get(&d.id, (size_t)n));
-  TT_CUDA(sc.get(&d.created, (size_t)n));
-  TT_CUDA(sc.get(&d.due, (size_t)n));
-  TT_CUDA(sc.get(&d.flags, (size_t)n));
-  TT_CUDA(sc.get(&d.status, (size_t)n));
-  for (int c = 0; c < 3; ++c) {
-    TT_CUDA(sc.get(&d.str_start[c], (size_t)n));
-    TT_CUDA(sc.get(&d.str_len[c], (size_t)n));
-    TT_CUDA(sc.get(&d.str_hash[c], (size_t)n));
-  }
-  TT_CUDA(sc.get(&d_err, 2));
-  stats->n_docs = n;
-  if (n == 0) {
-    int32_t rc = alloc_columns(t, 0);
-    if (rc) return rc;
-    static const uint32_t zero_off[1] = {0};
-    if ((rc = upload_dictionary(t, 0, zero_off, nullptr))) return rc;
-    TT_CUDA(cudaStreamSynchronize(st));
-    t->ids_sorted = true;
-    return TT_OK;
-  }
-  // the device's own copy of the text (it is unescaped in place) and of the offsets
-  TT_CUDA(cudaMemcpyAsync(text, static_cast<const uint8_t*>(docs) + first, bytes, cudaMemcpyDefault, st));
-  TT_CUDA(cudaMemcpyAsync(d_off, doc_off, ((size_t)n + 1) * 8, cudaMemcpyDefault, st));
-  const unsigned long long none = ~0ull;
-  TT_CUDA(cudaMemcpyAsync(d_err, &none, 8, cudaMemcpyHostToDevice, st));
-  TT_CUDA(cudaEventRecord(t->ev0, st));
-  tt::doc_parse_kernel<<<grid_for(n, 128), 128, 0, st>>>(text, d_off, first, bytes, n, local_offset_min, d);
-  tt::doc_first_bad_kernel<<<grid_for(n, 256), 256, 0, st>>>(d.status, n, d_err);
-  TT_CUDA(cudaGetLastError());
-  TT_CUDA(cudaEventRecord(t->ev1, st));
-  unsigned long long bad = none;
-  TT_CUDA(cudaMemcpyAsync(&bad, d_err, 8, cudaMemcpyDeviceToHost, st));
-  TT_CUDA(cudaStreamSynchronize(st));
-  stats->launches = 2;
-  if (bad != none) {
-    uint32_t reason = 0;
-    TT_CUDA(cudaMemcpy(&reason, d.status + bad, 4, cudaMemcpyDeviceToHost));
-    stats->first_bad = (int64_t)bad;
-    stats->first_bad_reason = (int32_t)reason;
-    static const char* why[] = {"", "not a JSON object of the TaskModel shape", "taskId is not a \"D\" Guid",
-                                "a date System.Text.Json would reject", "a malformed string (escape, control character or UTF-8)",
-                                "a known member with a value of the wrong type"};
-    return fail(TT_ERR_ARG, "document %lld: %s; nothing was loaded", (long long)bad, why[reason < 6 ? reason : 1]);
-  }
-  int32_t rc = alloc_columns(t, n);
-  if (rc) return rc;
-  auto undo = [&](int32_t code) {
-    free_columns(t);
-    return code;
-  };
-  const int64_t threads = round_up(n, 32);
-  tt::doc_fill_kernel<<<grid_for(threads, 256), 256, 0, st>>>(d, n, t->due_code, t->completed, t->overdue, t->creator_hash,
-                                                             t->task_id, t->created_raw, t->due_raw);
-  stats->launches += 1;
-  // the three string members -> refs + dictionaries
-  uint32_t* off[3] = {nullptr, nullptr, nullptr};
-  uint8_t* pool[3] = {nullptr, nullptr, nullptr};
-  uint32_t k[3] = {0, 0, 0};
-  uint64_t pbytes[3] = {0, 0, 0};
-  uint32_t* refs[3] = {nullptr, t->creator_ref, nullptr};
-  for (int c = 0; c < 3 && rc == TT_OK; c += 2) {  // payload ref columns (name, assignee)
-    cudaError_t e = cudaMalloc(&refs[c], (size_t)t->n_pad * 4);
-    if (e == cudaSuccess) e = cudaMemsetAsync(refs[c], 0xFF, (size_t)t->n_pad * 4, st);
-    if (e != cudaSuccess) {
-      cudaGetLastError();
-      rc = fail(TT_ERR_OOM, "payload column: %s", cudaGetErrorString(e));
-    }
-  }
-  for (int c = 0; c < 3 && rc == TT_OK; ++c)
-    rc = encode_member(t, sc, d, c, text, n, refs[c], &off[c], &pool[c], &k[c], &pbytes[c], &stats->launches);
-  if (rc != TT_OK) {
-    for (int c = 0; c < 3; ++c) {
-      cudaFree(off[c]);
-      cudaFree(pool[c]);
-    }
-    cudaFree(refs[0]);
-    cudaFree(refs[2]);
-    return undo(rc);
-  }
-  tt_table::StrColumn* cols[3] = {&t->name_col, nullptr, &t->assignee_col};
-  for (int c = 0; c < 3; c += 2) {
-    cols[c]->ref = refs[c];
-    cols[c]->n = k[c];
-    cols[c]->off = off[c];
-    cols[c]->pool = pool[c];
-    cols[c]->off_cap = (size_t)k[c] + 1;
-    cols[c]->pool_cap = std::max<uint64_t>(pbytes[c], 16);
-    cols[c]->pool_bytes = pbytes[c];
-  }
-  t->n_creators = k[1];
-  t->creator_off = off[1];
-  t->creator_pool = pool[1];
-  t->pool_bytes = pbytes[1];
-  t->creator_off_cap = (size_t)k[1] + 1;
-  t->creator_pool_cap = std::max<uint64_t>(pbytes[1], 16);
-  // is the table in TaskId order?  (then lookups by id search it directly)
-  const unsigned long long zero = 0;
-  unsigned long long unordered = 0;
-  cudaError_t e = cudaMemcpyAsync(d_err, &zero, 8, cudaMemcpyHostToDevice, st);
-  if (e == cudaSuccess) {
-    tt::doc_id_order_kernel<<<grid_for(n, 256), 256, 0, st>>>(t->task_id, n, d_err);
-    e = cudaGetLastError();
-  }
-  if (e == cudaSuccess) e = cudaEventRecord(t->ev2, st);
-  if (e == cudaSuccess) e = cudaMemcpyAsync(&unordered, d_err, 8, cudaMemcpyDeviceToHost, st);
-  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
-  if (e != cudaSuccess) {
-    cudaGetLastError();
-    return undo(fail(TT_ERR_CUDA, "document load: %s", cudaGetErrorString(e)));
-  }
-  stats->launches += 1;
-  t->ids_sorted = unordered == 0;
-  if (!t->ids_sorted) {
-    // the TaskId index (rows in TaskId order): two stable 64-bit radix sorts on the device, the low
-    // 8 bytes first, then the high 8 bytes of the rows in that order
-    e = t->sort.reserve(n);
-    int w = 0;
-    if (e == cudaSuccess) {
-      tt::id_half_keys_kernel<<<grid_for(n, 256), 256, 0, st>>>(t->task_id, nullptr, n, 0, t->sort.keys[0], t->sort.vals[0]);
-      e = tt::radix_sort_pairs(st, t->sort, n, 64, &w);
-    }
-    if (e == cudaSuccess) {
-      tt::id_half_keys_kernel<<<grid_for(n, 256), 256, 0, st>>>(t->task_id, t->sort.vals[w], n, 1, t->sort.keys[w ^ 1],
-                                                                t->sort.vals[w ^ 1]);
-      if (w == 0) {  // radix_sort_pairs starts from buffer pair 0
-        std::swap(t->sort.keys[0], t->sort.keys[1]);
-        std::swap(t->sort.vals[0], t->sort.vals[1]);
-      }
-      e = tt::radix_sort_pairs(st, t->sort, n, 64, &w);
-    }
-    if (e == cudaSuccess) e = cudaMalloc(&t->id_order, (size_t)n * 4);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(t->id_order, t->sort.vals[w], (size_t)n * 4, cudaMemcpyDeviceToDevice, st);
-    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
-    if (e != cudaSuccess) {
-      cudaGetLastError();
-      return undo(fail(TT_ERR_CUDA, "TaskId index: %s", cudaGetErrorString(e)));
-    }
-    stats->launches += 2 + 2 * 4 * 8;
-  }
-  cudaEventElapsedTime(&stats->parse_ms, t->ev0, t->ev1);
-  cudaEventElapsedTime(&stats->encode_ms, t->ev1, t->ev2);
-  stats->n_names = k[0];
-  stats->n_creators = k[1];
-  stats->n_assignees = k[2];
-  stats->text_bytes = (int64_t)bytes;
-  return TT_OK;
-}
-
-// ---- the cron tick for a caller whose state and results live in host memory ---------------------------
-namespace {
-
-// (Re)allocates staging buffer `buf` of the pipelined tick for `want` hits, keeping its first `keep`.
-int32_t tick_stage_grow(tt_table* t, int buf, int64_t want, int64_t keep, bool with_ids) {
-  uint32_t* rows = nullptr;
-  void* ids = nullptr;
-  TT_CUDA(cudaMalloc(&rows, (size_t)want * 4));
-  if (with_ids) {
-    cudaError_t e = cudaMalloc(&ids, (size_t)want * 16);
-    if (e != cudaSuccess) {
-      cudaFree(rows);
-      TT_CUDA(e);
-    }
-  }
-  if (keep > 0) {
-    cudaMemcpyAsync(rows, t->tick_rows[buf], (size_t)keep * 4, cudaMemcpyDeviceToDevice, t->stream);
-    if (with_ids && t->tick_ids[buf]) cudaMemcpyAsync(ids, t->tick_ids[buf], (size_t)keep * 16, cudaMemcpyDeviceToDevice, t->stream);
-    cudaStreamSynchronize(t->stream);
-  }
-  cudaFree(t->tick_rows[buf]);
-  cudaFree(t->tick_ids[buf]);
-  t->tick_rows[buf] = rows;
-  t->tick_ids[buf] = ids;
-  t->tick_cap[buf] = want;
-  return TT_OK;
-}
-
-}  // namespace
-
-extern "C" int32_t tt_tick_host(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_ticks, int64_t run_at_utc_ticks,
-                                const uint8_t* h_completed_bits, const uint8_t* h_overdue_bits, uint32_t* h_rows,
-                                uint8_t* h_ids16, int64_t cap, int32_t chunks, tt_sweep_stats* stats) {
-  if (!t || !stats || !h_rows || cap < 0) return fail(TT_ERR_ARG, "bad argument");
-  memset(stats, 0, sizeof *stats);
-  if (chunks <= 0) chunks = 8;
-  std::lock_guard<std::mutex> lk(t->mu);
-  DeviceGuard g(t->device);
-  if (t->n == 0) return TT_OK;
-  const bool with_ids = h_ids16 != nullptr;
-  // lazily created: two transfer streams and their events
-  if (!t->tick_up) {
-    TT_CUDA(cudaStreamCreateWithFlags(&t->tick_up, cudaStreamNonBlocking));
-    TT_CUDA(cudaStreamCreateWithFlags(&t->tick_down, cudaStreamNonBlocking));
-    for (int k = 0; k < 2; ++k) {
-      TT_CUDA(cudaEventCreateWithFlags(&t->tick_up_ev[k], cudaEventDisableTiming));
-      TT_CUDA(cudaEventCreateWithFlags(&t->tick_down_ev[k], cudaEventDisableTiming));
-    }
-    TT_CUDA(cudaEventCreateWithFlags(&t->tick_done_ev, cudaEventDisableTiming));
-  }
-  const int64_t tiles = t->n_pad / TT_TILE_ROWS;
-  const int64_t chunk_rows = (tiles + chunks - 1) / chunks * TT_TILE_ROWS;
-  // two device staging buffers (grow-only, kept between calls); a first guess of 1/16 of a chunk's rows
-  int32_t rc = TT_OK;
-  for (int k = 0; k < 2 && rc == TT_OK; ++k)
-    if (t->tick_cap[k] < std::max<int64_t>(65536, chunk_rows / 16) || (with_ids && !t->tick_ids[k]))
-      rc = tick_stage_grow(t, k, std::max<int64_t>({65536, chunk_rows / 16, t->tick_cap[k]}), 0, with_ids);
-  if (rc) return rc;
-  // work that may still be running on the table's own stream comes first
-  TT_CUDA(cudaEventRecord(t->tick_done_ev, t->stream));
-  TT_CUDA(cudaStreamWaitEvent(t->tick_up, t->tick_done_ev, 0));
-  auto upload = [&](int c) -> int32_t {  // flag planes of chunk c, host -> device, on the upload stream
-    const int64_t r0 = (int64_t)c * chunk_rows, r1 = std::min<int64_t>(r0 + chunk_rows, t->n_pad);
-    if (r0 < r1 && r0 < t->n) {
-      const size_t b0 = (size_t)r0 / 8, nb = (size_t)(std::min<int64_t>(r1, t->n) + 7) / 8 - b0;
-      if (h_completed_bits)
-        TT_CUDA(cudaMemcpyAsync(reinterpret_cast<uint8_t*>(t->completed) + b0, h_completed_bits + b0, nb, cudaMemcpyHostToDevice, t->tick_up));
-      if (h_overdue_bits)
-        TT_CUDA(cudaMemcpyAsync(reinterpret_cast<uint8_t*>(t->overdue) + b0, h_overdue_bits + b0, nb, cudaMemcpyHostToDevice, t->tick_up));
-    }
-    TT_CUDA(cudaEventRecord(t->tick_up_ev[c & 1], t->tick_up));
-    return TT_OK;
-  };
-  int64_t total = 0;
-  bool overflow = false;
-  if ((rc = upload(0))) return rc;
-  for (int c = 0; c < chunks; ++c) {
-    const int64_t r0 = (int64_t)c * chunk_rows, r1 = std::min<int64_t>(r0 + chunk_rows, t->n_pad);
-    if (r0 >= r1) break;
-    TT_CUDA(cudaStreamWaitEvent(t->stream, t->tick_up_ev[c & 1], 0));
-    if (c + 1 < chunks && (rc = upload(c + 1))) return rc;  // the next chunk's planes travel while this one is swept
-    const int buf = c & 1;
-    // the staging buffer is free once the download that used it two chunks ago has finished
-    TT_CUDA(cudaEventSynchronize(t->tick_down_ev[buf]));
-    // Sweep the chunk into the staging buffer.  If its hits do not fit, the buffer is regrown: a listing
-    // sweep changed nothing and starts again; a marking sweep has stored and marked a row-ordered subset,
-    // which is kept while the rest is appended, and the two runs are merged by a sort afterwards.
-    int64_t have = 0, listed = 0;
-    bool merged = false;
-    for (int pass = 0;; ++pass) {
-      if (pass == 16) return fail(TT_ERR_STATE, "tick did not converge on chunk %d", c);
-      tt_sweep_stats st;
-      rc = sweep_run(t, mode, flags, today_local_ticks, run_at_utc_ticks, r0, t->tick_rows[buf] + have,
-                     with_ids ? (uint4*)t->tick_ids[buf] + have : nullptr, t->tick_cap[buf] - have, &st, t->stream, nullptr, r1);
-      if (rc != TT_OK && rc != TT_ERR_CAPACITY) return rc;
-      stats->kernel_ms += st.kernel_ms;
-      stats->sweep_ms += st.sweep_ms;
-      stats->gather_ms += st.gather_ms;
-      stats->launches += st.launches;
-      stats->n_marked += st.n_marked;
-      if (rc == TT_OK) {
-        have += st.n_stored;
-        listed += st.n_listed;
-        break;
-      }
-      const bool mutated = st.n_marked > 0;
-      if (mutated) {
-        have += st.n_stored;
-        listed += st.n_stored;
-        merged = true;
-      }
-      const int64_t want = have + (st.n_listed - (mutated ? st.n_stored : 0)) + 1024;
-      if ((rc = tick_stage_grow(t, buf, want, have, with_ids))) return rc;
-    }
-    if (merged && have > 1) {
-      int e = tt::sort_rows_and_gather(t->stream, t->sort, t->task_id, t->tick_rows[buf], (uint4*)t->tick_ids[buf], have);
-      if (e != 0) return fail(TT_ERR_CUDA, "sort_rows_and_gather: %s", cudaGetErrorString((cudaError_t)e));
-      stats->launches += 2 + 4 * 4;
-    }
-    stats->n_listed += listed;
-    const int64_t room = std::max<int64_t>(0, cap - total), take = std::min(have, room);
-    if (take < have) overflow = true;
-    if (take > 0) {
-      TT_CUDA(cudaEventRecord(t->tick_done_ev, t->stream));  // sweep_run has synchronised; the event orders the copy
-      TT_CUDA(cudaStreamWaitEvent(t->tick_down, t->tick_done_ev, 0));
-      TT_CUDA(cudaMemcpyAsync(h_rows + total, t->tick_rows[buf], (size_t)take * 4, cudaMemcpyDeviceToHost, t->tick_down));
-      if (with_ids)
-        TT_CUDA(cudaMemcpyAsync(h_ids16 + (size_t)total * 16, t->tick_ids[buf], (size_t)take * 16, cudaMemcpyDeviceToHost, t->tick_down));
-    }
-    total += take;
-    stats->n_stored = total;
-    TT_CUDA(cudaEventRecord(t->tick_down_ev[buf], t->tick_down));
-  }
-  TT_CUDA(cudaStreamSynchronize(t->tick_down));
-  TT_CUDA(cudaStreamSynchronize(t->tick_up));
-  stats->resume_row = t->n;
-  if (overflow)
-    return fail(TT_ERR_CAPACITY, "%lld hits do not fit in the host buffers (%lld); the first %lld were delivered",
-                (long long)stats->n_listed, (long long)cap, (long long)total);
-  return TT_OK;
-}
+#include "api_tick.inc"
 
 // ---- the sweep with its working memory in a fixed device array ---------------------------------
 //

@@ -52,7 +52,7 @@ def test_product_does_not_reference_the_oracle():
     for base in ("aca-dotnet-workshop_b200", "include"):
         for dp, _, files in os.walk(os.path.join(ROOT, base)):
             for f in files:
-                if f.endswith((".py", ".cu", ".cuh", ".h", ".hpp", ".cpp")):
+                if f.endswith((".py", ".cu", ".cuh", ".inc", ".h", ".hpp", ".cpp")):
                     s = open(os.path.join(dp, f), errors="replace").read()
                     if re.search(r"liboracle|oracle\.py|from oracle|import oracle|oracle/", s):
                         bad.append(os.path.join(dp, f))
