@@ -17,6 +17,9 @@ from .tasktable import (  # noqa: F401
     DEFAULT_TODAY,
     DEFAULT_RUN_AT,
     DeviceView,
+    Exchange,
+    GResult,
+    ShardedTable,
     JSON_DOCUMENT,
     JSON_RESPONSE,
     JsonText,
@@ -31,4 +34,4 @@ from .tasktable import (  # noqa: F401
     lib_path,
 )
 from .tasks_manager import GpuTasksManager, TaskModel  # noqa: F401
-from .sharding import HitExchange, PushExchange, ShardPlan, exchange_hits, push_slot_layout, shard_rows  # noqa: F401
+from .sharding import HitExchange, ShardExchange, ShardPlan, exchange_hits, push_slot_layout, shard_rows  # noqa: F401

@@ -172,9 +172,12 @@ __device__ __forceinline__ int cmp_id(uint4 a, uint4 b) {
   return 0;
 }
 
-// counters[0] += ids found (bit set), counters[1] += ids with no row
-__global__ void mark_by_id_kernel(const uint4* ids, int64_t n_ids, const uint4* task_id, const uint32_t* id_order,
-                                  int64_t n_rows, uint32_t* overdue, unsigned long long* counters) {
+// counters[0] += ids found (bit set), counters[1] += ids with no live row.  Rows (or id_order)
+// ascend by TaskId; a deleted row keeps its id but carries creator_ref == 0xFFFFFFFF and is
+// passed over, like FirstOrDefault over the live list (FakeTasksManager.cs:76) / a missing key.
+__global__ void mark_by_id_kernel(const uint4* ids, int64_t n_ids, const uint4* task_id, const uint32_t* creator_ref,
+                                  const uint32_t* id_order, int64_t n_rows, uint32_t* overdue,
+                                  unsigned long long* counters) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n_ids) return;
   const uint4 key = ids[i];
@@ -185,11 +188,13 @@ __global__ void mark_by_id_kernel(const uint4* ids, int64_t n_ids, const uint4* 
     if (cmp_id(task_id[r], key) < 0) lo = mid + 1; else hi = mid;
   }
   bool hit = false;
-  if (lo < n_rows) {
+  for (; lo < n_rows; ++lo) {
     uint32_t r = id_order ? id_order[lo] : (uint32_t)lo;
-    if (cmp_id(task_id[r], key) == 0) {
+    if (cmp_id(task_id[r], key) != 0) break;
+    if (creator_ref[r] != 0xFFFFFFFFu) {
       atomicOr(overdue + (r >> 5), 1u << (r & 31));
       hit = true;
+      break;
     }
   }
   atomicAdd(counters + (hit ? 0 : 1), 1ull);

@@ -42,6 +42,13 @@ struct SweepCtl {
   unsigned long long stored;         // min slot of a tile that did not fit (= hits stored); ~0 if all fit
 };
 
+// What a tick reports to the host: written by sweep_tail_kernel into mapped pinned host memory,
+// so the call needs no device-to-host copy of its own.
+struct SweepOut {
+  unsigned long long cursor;
+  unsigned long long stored;
+};
+
 struct SweepParams {
   const uint32_t* due_code;
   const uint32_t* completed;
@@ -49,7 +56,8 @@ struct SweepParams {
   uint32_t* list;                    // unordered hit rows (scratch, cap entries); null = count only
   uint32_t* tile_slot;               // per tile: first slot in `list`
   uint32_t* tile_count;              // per tile: hits stored (0 if the tile did not fit)
-  uint32_t* group_sum;               // per kTilesPerGroup tiles: sum of tile_count (zeroed before launch)
+  uint32_t* group_sum;               // per kTilesPerGroup tiles: sum of tile_count (zero before launch)
+  uint32_t* sub_sum;                 // per kTilesPerSub tiles: the same at a finer grain (zero before launch); may be null
   SweepCtl* ctl;                     // tile_counter = cursor = 0, stored = ~0 before launch
   unsigned long long cap;            // capacity of `list` in hits
   uint32_t first_tile;
@@ -60,6 +68,7 @@ struct SweepParams {
 };
 
 constexpr int kTilesPerGroup = 1024;  // K2: one CTA per group of tiles
+constexpr int kTilesPerSub = 32;      // K3g finds a tile's offset from group sums + sub sums + <= 31 tile counts
 
 __device__ __forceinline__ uint4 ld_stream_v4(const uint4* p) {
   uint4 r;
@@ -156,7 +165,10 @@ __device__ __forceinline__ void emit_tile(const SweepParams& p, const PendingTil
     if (p.list) {
       p.tile_slot[t.rel] = slot;
       p.tile_count[t.rel] = fits ? t.total : 0u;
-      if (fits && t.total) atomicAdd(p.group_sum + t.rel / kTilesPerGroup, t.total);
+      if (fits && t.total) {
+        atomicAdd(p.group_sum + t.rel / kTilesPerGroup, t.total);
+        if (p.sub_sum) atomicAdd(p.sub_sum + t.rel / kTilesPerSub, t.total);
+      }
     }
     if (!fits) atomicMin(&p.ctl->stored, (unsigned long long)slot);
   }
@@ -358,20 +370,52 @@ constexpr int kGroupUnroll = 1;
 constexpr int kGroupStage = 4096;  // offsets staged per group; denser groups store theirs directly
 
 struct PushTarget {
-  uint16_t* off16;            // [cap] in-tile offsets of the row-ordered hits; 16-byte aligned; null = no push
-  uint32_t* tile_count;       // [num_tiles] hits per tile
-  unsigned long long* count;  // [1] hits stored
+  uint16_t* off16;              // [cap] in-tile offsets of the row-ordered hits; 16-byte aligned; null = no push
+  uint32_t* tile_count;         // [num_tiles] hits per tile
+  unsigned long long* count;    // [1] hits stored
+  uint4* ids;                   // [cap] TaskIds of the hits in row order, or null (the sharded GetYesterdaysDueTasks)
+  unsigned long long* created;  // [cap] TaskCreatedOn (.NET dateData) of the hits, or null (the cross-shard OrderBy)
+  uint32_t* tile_first;         // [num_tiles] offset of each tile's hits in the row-ordered list, or null
 };
 
+// What a sharded tick adds around K3g (shards.cuh): before it, wait until the root has finished
+// reading this shard's slot (wait_word >= wait_value); after it, publish `epoch` in the slot.
+struct ShardHook {
+  unsigned long long* epoch_word;
+  unsigned long long epoch;
+  const unsigned char* wait_slot0;  // null = no wait (the root's own shard)
+  unsigned long long wait_value;
+  unsigned long long timeout_ns;
+};
+
+// Where the row-ordered list of the CTA's first tile starts: hits stored in all earlier tiles =
+// whole groups (group_sum) + whole sub-groups of this group (sub_sum) + the <= 31 tiles of this
+// sub-group before t0 — about ten independent loads per lane of one warp and a warp sum, issued
+// together with the loads of the tile's own slot and count.  (Until round 2 a separate scan
+// kernel, K2 tile_offsets_kernel, produced these offsets between K1 and K3g.)
+__device__ __forceinline__ uint32_t tile_list_base(const uint32_t* group_sum, const uint32_t* sub_sum,
+                                                   const uint32_t* tile_count, uint32_t t0, uint32_t lane) {
+  const uint32_t g = t0 / kTilesPerGroup, s = t0 / kTilesPerSub;
+  uint32_t acc = 0;
+  for (uint32_t k = lane; k < g; k += 32) acc += group_sum[k];
+  const uint32_t s0 = g * (kTilesPerGroup / kTilesPerSub);
+  if (s0 + lane < s) acc += sub_sum[s0 + lane];
+  const uint32_t f = s * kTilesPerSub;
+  if (f + lane < t0) acc += tile_count[f + lane];
+  return warp_sum(acc);
+}
+
 template <int TILE_ROWS, int GT = kGroupTiles, int UNROLL = kGroupUnroll>
-__global__ void __launch_bounds__(kGroupThreads) place_group_kernel(const SweepCtl* ctl, const uint32_t* list,
-                                                                    const uint32_t* tile_slot,
+__global__ void __launch_bounds__(kGroupThreads) place_group_kernel(const uint32_t* list, const uint32_t* tile_slot,
                                                                     const uint32_t* tile_count,
-                                                                    const uint32_t* tile_first, uint32_t num_tiles,
-                                                                    const uint4* task_id, uint32_t* out_rows,
+                                                                    const uint32_t* group_sum, const uint32_t* sub_sum,
+                                                                    uint32_t num_tiles, const uint4* task_id,
+                                                                    const uint64_t* created_raw, uint32_t* out_rows,
                                                                     uint4* out_ids, PushTarget push) {
+  static_assert(kTilesPerSub % GT == 0 || GT % kTilesPerSub == 0, "a CTA's tiles must not straddle the prefix levels unevenly");
   __shared__ uint32_t s_slot[GT];
   __shared__ uint32_t s_pre[GT + 1];
+  __shared__ uint32_t s_base;
   __shared__ __align__(16) uint16_t s_off[kGroupStage + 8];
   const uint32_t tid = threadIdx.x;
   const uint32_t t0 = blockIdx.x * GT;
@@ -379,6 +423,8 @@ __global__ void __launch_bounds__(kGroupThreads) place_group_kernel(const SweepC
     const uint32_t t = t0 + tid;
     const bool live = tid < GT && t < num_tiles;
     const uint32_t c = live ? tile_count[t] : 0u;
+    const uint32_t slot = live ? tile_slot[t] : 0u;
+    const uint32_t base = tile_list_base(group_sum, sub_sum, tile_count, t0, tid);
     uint32_t incl = c;
 #pragma unroll
     for (int d = 1; d < GT; d <<= 1) {
@@ -386,28 +432,27 @@ __global__ void __launch_bounds__(kGroupThreads) place_group_kernel(const SweepC
       if (tid >= (uint32_t)d) incl += up;
     }
     if (tid < GT) {
-      s_slot[tid] = live ? tile_slot[t] : 0u;
+      s_slot[tid] = slot;
       s_pre[tid + 1] = incl;
       if (live && push.tile_count) push.tile_count[t] = c;
+      if (live && push.tile_first) push.tile_first[t] = base + incl - c;
     }
     if (tid == 0) {
       s_pre[0] = 0;
-      if (blockIdx.x == 0 && push.count) {
-        const unsigned long long st = ctl->stored;
-        *push.count = st == ~0ull ? ctl->cursor : st;
-      }
+      s_base = base;
     }
   }
   __syncthreads();
   const uint32_t total = s_pre[GT];
   if (total == 0) return;
-  const uint32_t base = tile_first[t0];
+  const uint32_t base = s_base;
   const uint32_t shift = base & 7u;  // staged index = list index - (base - shift): 16-byte chunks line up
   const bool staged = push.off16 != nullptr && total <= (uint32_t)kGroupStage;
 
   for (uint32_t h0 = tid; h0 < total; h0 += kGroupThreads * UNROLL) {
     uint32_t r[UNROLL];
     uint4 id[UNROLL];
+    unsigned long long cr[UNROLL];
 #pragma unroll
     for (int j = 0; j < UNROLL; ++j) {
       const uint32_t h = h0 + j * kGroupThreads;
@@ -419,9 +464,13 @@ __global__ void __launch_bounds__(kGroupThreads) place_group_kernel(const SweepC
         r[j] = list[s_slot[k] + (h - s_pre[k])];
       }
     }
-    if (out_ids) {
+    if (out_ids || push.ids) {
 #pragma unroll
       for (int j = 0; j < UNROLL; ++j) id[j] = ld_gather_v4(task_id + r[j]);
+    }
+    if (push.created) {
+#pragma unroll
+      for (int j = 0; j < UNROLL; ++j) cr[j] = ld_gather_u64(created_raw + r[j]);
     }
 #pragma unroll
     for (int j = 0; j < UNROLL; ++j) {
@@ -434,6 +483,8 @@ __global__ void __launch_bounds__(kGroupThreads) place_group_kernel(const SweepC
           push.off16[base + h] = off;
         if (out_rows) out_rows[base + h] = r[j];
         if (out_ids) out_ids[base + h] = id[j];
+        if (push.ids) push.ids[base + h] = id[j];
+        if (push.created) push.created[base + h] = cr[j];
       }
     }
   }
@@ -447,6 +498,38 @@ __global__ void __launch_bounds__(kGroupThreads) place_group_kernel(const SweepC
       *reinterpret_cast<uint4*>(dst + a) = *reinterpret_cast<const uint4*>(s_off + a);
     } else {
       for (uint32_t e = a > lo ? a : lo; e < a + 8 && e < hi; ++e) dst[e] = s_off[e];
+    }
+  }
+}
+
+// The tick's epilogue, one small CTA after the last kernel: reports the outcome (hit count,
+// stored count) into mapped pinned host memory and into the push target, puts the control block
+// and the partial sums back into their start state for the next tick (so a tick issues no
+// memset and no copy of its own), and — for a sharded table — publishes the tick's epoch in the
+// root GPU's slot: the kernel boundary has made this shard's stores into the root's memory
+// complete, the system-scope fence orders the epoch word after them, and the root waits on the
+// word (shard_wait_kernel) instead of on a collective.
+__global__ void sweep_tail_kernel(SweepCtl* ctl, SweepOut* out, uint32_t* group_sum, uint32_t n_groups, uint32_t* sub_sum,
+                                  uint32_t n_subs, unsigned long long* push_count, unsigned long long* epoch_word,
+                                  unsigned long long epoch) {
+  const unsigned long long cursor = ctl->cursor, stored = ctl->stored;
+  for (uint32_t k = threadIdx.x; k < n_groups; k += blockDim.x) group_sum[k] = 0;
+  if (sub_sum)
+    for (uint32_t k = threadIdx.x; k < n_subs; k += blockDim.x) sub_sum[k] = 0;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    ctl->tile_counter = 0;
+    ctl->pad = 0;
+    ctl->cursor = 0;
+    ctl->stored = ~0ull;
+    if (out) {
+      out->cursor = cursor;
+      out->stored = stored;
+    }
+    if (push_count) *push_count = stored == ~0ull ? cursor : stored;
+    if (epoch_word) {
+      __threadfence_system();
+      asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(epoch_word), "l"(epoch) : "memory");
     }
   }
 }

@@ -24,6 +24,7 @@
 #include "json.cuh"
 #include "order.cuh"
 #include "point.cuh"
+#include "shards.cuh"
 #include "sweep.cuh"
 #include "tt_bits.h"
 
@@ -109,8 +110,18 @@ struct tt_table {
   // sweep scratch: per-tile slot / count / final offset (3 words per tile), group sums, the
   // unordered hit list (grown on demand), and the control block with its pinned mirror
   uint32_t* tile_words = nullptr;   // [3][n_tiles]
-  uint32_t* group_sum = nullptr;    // [n_groups]
-  int64_t n_tiles = 0, n_groups = 0;
+  uint32_t* group_sum = nullptr;    // [n_groups] then [n_subs]: K1's partial sums of the per-tile counts
+  int64_t n_tiles = 0, n_groups = 0, n_subs = 0;
+  bool ctl_clean = false;           // control block and partial sums are in their start state (the last tick's tail kernel ran)
+  tt::SweepOut* h_out = nullptr;    // the tick's outcome: mapped pinned host memory the tail kernel writes
+  tt::SweepOut* d_out = nullptr;    // its device address
+  struct PendingSweep {             // a tick queued with TT_SWEEP_ASYNC and not yet collected by tt_sweep_wait
+    bool active = false, listing = false, timing = false, trivial = false;  // trivial: nothing was launched
+    uint32_t mark_enable = 0;
+    int64_t first_row = 0, row_end = -1, cap = 0;
+    int32_t launches = 0;
+    cudaStream_t stream = nullptr;
+  } pending;
   uint32_t* hit_list = nullptr;
   int64_t hit_list_cap = 0;
   tt::SweepCtl* ctl = nullptr;
@@ -247,8 +258,23 @@ void free_columns(tt_table* t) {
   t->creator_ref = t->creator_off = t->id_order = nullptr;
   t->creator_pool = nullptr;
   t->tile_words = t->group_sum = t->hit_list = nullptr;
-  t->n_tiles = t->n_groups = t->hit_list_cap = 0;
+  t->n_tiles = t->n_groups = t->n_subs = t->hit_list_cap = 0;
+  t->ctl_clean = false;
   t->n = t->n_pad = 0;
+}
+
+// Per-tile words and K1's partial sums for a table of np padded rows (the sweep's fixed scratch).
+int32_t alloc_sweep_scratch(tt_table* t, int64_t np) {
+  cudaFree(t->tile_words);
+  cudaFree(t->group_sum);
+  t->tile_words = t->group_sum = nullptr;
+  t->ctl_clean = false;
+  t->n_tiles = np / TT_TILE_ROWS;
+  t->n_groups = (t->n_tiles + tt::kTilesPerGroup - 1) / tt::kTilesPerGroup;
+  t->n_subs = (t->n_tiles + tt::kTilesPerSub - 1) / tt::kTilesPerSub;
+  TT_CUDA(cudaMalloc(&t->tile_words, 3 * t->n_tiles * 4));
+  TT_CUDA(cudaMalloc(&t->group_sum, (t->n_groups + t->n_subs) * 4));
+  return TT_OK;
 }
 
 int32_t alloc_columns(tt_table* t, int64_t n) {
@@ -263,10 +289,10 @@ int32_t alloc_columns(tt_table* t, int64_t n) {
   TT_CUDA(cudaMalloc(&t->created_raw, np * 8));
   TT_CUDA(cudaMalloc(&t->due_raw, np * 8));
   TT_CUDA(cudaMalloc(&t->creator_ref, np * 4));
-  t->n_tiles = np / TT_TILE_ROWS;
-  t->n_groups = (t->n_tiles + tt::kTilesPerGroup - 1) / tt::kTilesPerGroup;
-  TT_CUDA(cudaMalloc(&t->tile_words, 3 * t->n_tiles * 4));
-  TT_CUDA(cudaMalloc(&t->group_sum, t->n_groups * 4));
+  {
+    int32_t rc = alloc_sweep_scratch(t, np);
+    if (rc) return rc;
+  }
   // padding rows never match and carry no flags
   TT_CUDA(cudaMemsetAsync(t->due_code, 0xFF, np * 4, t->stream));
   TT_CUDA(cudaMemsetAsync(t->completed, 0, np / 8, t->stream));
@@ -426,11 +452,42 @@ int sweep_ctas_per_sm() {
   return ctas;
 }
 
+// Waits for the tick queued by sweep_run and turns the tail kernel's report into *st.
+int32_t sweep_finish(tt_table* t, tt_sweep_stats* st) {
+  const tt_table::PendingSweep pd = t->pending;
+  t->pending.active = false;
+  memset(st, 0, sizeof *st);
+  st->launches = pd.launches;
+  if (pd.trivial) {
+    st->resume_row = pd.row_end;
+    return TT_OK;
+  }
+  TT_CUDA(cudaStreamSynchronize(pd.stream));
+  t->ctl_clean = true;
+  if (pd.timing) {
+    TT_CUDA(cudaEventElapsedTime(&st->sweep_ms, t->ev0, t->ev1));
+    TT_CUDA(cudaEventElapsedTime(&st->gather_ms, t->ev1, t->ev2));
+    st->kernel_ms = st->sweep_ms + st->gather_ms;
+  }
+  const tt::SweepOut done = *t->h_out;
+  st->n_listed = (int64_t)done.cursor;
+  const bool complete = done.stored == ~0ull;
+  st->n_stored = pd.listing ? (complete ? st->n_listed : (int64_t)done.stored) : 0;
+  st->resume_row = complete ? (pd.row_end >= 0 ? std::min<int64_t>(pd.row_end, t->n) : t->n) : pd.first_row;
+  st->n_marked = pd.mark_enable ? (pd.listing ? st->n_stored : st->n_listed) : 0;
+  if (!complete)
+    return fail(TT_ERR_CAPACITY, "%lld hits do not fit in %lld (%lld stored%s)", (long long)st->n_listed,
+                (long long)pd.cap, (long long)st->n_stored, st->n_marked ? " and marked; call again for the rest" : "");
+  return TT_OK;
+}
+
 // Launches the sweep kernel over rows [first_row, n) on `stream`, waits, fills *st.
 int32_t sweep_run(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_ticks, int64_t run_at_utc_ticks,
                   int64_t first_row, uint32_t* d_rows, uint4* d_ids, int64_t cap, tt_sweep_stats* st,
-                  cudaStream_t stream, const tt::PushTarget* push = nullptr, int64_t row_end = -1) {
+                  cudaStream_t stream, const tt::PushTarget* push = nullptr, int64_t row_end = -1,
+                  const tt::ShardHook* hook = nullptr) {
   memset(st, 0, sizeof *st);
+  if (t->pending.active) return fail(TT_ERR_STATE, "a tick queued with TT_SWEEP_ASYNC is pending: call tt_sweep_wait first");
   if (mode != TT_MODE_FAKE && mode != TT_MODE_STORE) return fail(TT_ERR_ARG, "mode must be TT_MODE_FAKE or TT_MODE_STORE");
   uint32_t yesterday = 0;
   int32_t rc = check_clock(today_local_ticks, &yesterday);
@@ -447,20 +504,23 @@ int32_t sweep_run(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_
   const bool survive = run_at_utc_ticks / TT_TICKS_PER_DAY > (int64_t)yesterday;
   if (range && mark && !survive)
     return fail(TT_ERR_ARG, "range sweep: run_at_utc_ticks must lie after yesterday (runAt.Date > TaskDueDate.Date would differ per row)");
-  if (t->n == 0 || first_row >= t->n) {
-    st->resume_row = t->n;
+  auto nothing_to_do = [&](int64_t resume) {  // an empty range: no kernel runs, an async caller still gets its wait
+    st->resume_row = resume;
+    if (flags & TT_SWEEP_ASYNC) {
+      t->pending = tt_table::PendingSweep();
+      t->pending.active = t->pending.trivial = true;
+      t->pending.row_end = resume;
+    }
     return TT_OK;
-  }
+  };
+  if (t->n == 0 || first_row >= t->n) return nothing_to_do(t->n);
   const uint32_t first_tile = (uint32_t)(first_row / TT_TILE_ROWS);
   uint32_t num_tiles = (uint32_t)(t->n_pad / TT_TILE_ROWS) - first_tile;
   if (row_end >= 0) {  // a chunk [first_row, row_end) of the table, whole tiles
     if (row_end % TT_TILE_ROWS != 0 || row_end < first_row || row_end > t->n_pad)
       return fail(TT_ERR_ARG, "row_end must be a tile multiple in [first_row, padded rows]");
     num_tiles = (uint32_t)((row_end - first_row) / TT_TILE_ROWS);
-    if (num_tiles == 0) {
-      st->resume_row = row_end;
-      return TT_OK;
-    }
+    if (num_tiles == 0) return nothing_to_do(row_end);
   }
 
   // scratch for the unordered hit list K1 writes before K3 puts it in row order
@@ -482,6 +542,7 @@ int32_t sweep_run(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_
   p.tile_count = t->tile_words + t->n_tiles;
   uint32_t* tile_first = t->tile_words + 2 * t->n_tiles;
   p.group_sum = t->group_sum;
+  p.sub_sum = t->group_sum + t->n_groups;
   p.ctl = t->ctl;
   p.cap = listing ? (unsigned long long)cap : ~0ull;
   p.first_tile = first_tile;
@@ -491,17 +552,25 @@ int32_t sweep_run(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_
   // FAKE mode never mutates: MarkOverdueTasks throws before touching the list (FakeTasksManager.cs:104)
   p.mark_enable = (mark && survive && mode == TT_MODE_STORE) ? 1u : 0u;
 
-  tt::SweepCtl init;
-  init.tile_counter = 0;
-  init.pad = 0;
-  init.cursor = 0;
-  init.stored = ~0ull;
-  *t->h_ctl = init;
-  TT_CUDA(cudaMemcpyAsync(t->ctl, t->h_ctl, sizeof init, cudaMemcpyHostToDevice, stream));
+  // The control block and the partial sums are left in their start state by the previous tick's
+  // tail kernel; only the first tick of a table (or one after a failed call) sets them from the host.
+  const bool timing = (flags & TT_SWEEP_NO_TIMING) == 0;
+  const bool was_clean = t->ctl_clean;
+  t->ctl_clean = false;
+  if (!was_clean) {
+    tt::SweepCtl init;
+    init.tile_counter = 0;
+    init.pad = 0;
+    init.cursor = 0;
+    init.stored = ~0ull;
+    *t->h_ctl = init;
+    TT_CUDA(cudaMemcpyAsync(t->ctl, t->h_ctl, sizeof init, cudaMemcpyHostToDevice, stream));
+    TT_CUDA(cudaMemsetAsync(t->group_sum, 0, (size_t)(t->n_groups + t->n_subs) * 4, stream));
+  }
   const unsigned n_groups = (num_tiles + tt::kTilesPerGroup - 1) / tt::kTilesPerGroup;
-  if (listing) TT_CUDA(cudaMemsetAsync(t->group_sum, 0, (size_t)n_groups * 4, stream));
+  const unsigned n_subs = (num_tiles + tt::kTilesPerSub - 1) / tt::kTilesPerSub;
   const unsigned grid = (unsigned)std::min<int64_t>(num_tiles, (int64_t)t->sm_count * sweep_ctas_per_sm());
-  TT_CUDA(cudaEventRecord(t->ev0, stream));
+  if (timing) TT_CUDA(cudaEventRecord(t->ev0, stream));
   constexpr int kT = tt::kSweepThreads, kC = tt::kSweepCtasPerSm;
   if (range) {
     if (mode == TT_MODE_STORE) {
@@ -517,15 +586,20 @@ int32_t sweep_run(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_
     tt::sweep_kernel<false, false, kT, kC><<<grid, kT, 0, stream>>>(p);
   }
   TT_CUDA(cudaGetLastError());
-  TT_CUDA(cudaEventRecord(t->ev1, stream));
+  if (timing) TT_CUDA(cudaEventRecord(t->ev1, stream));
   st->launches = 1;
   if (listing) {
-    // K2 + K3: row order and TaskIds; the hit count is read from the control block on the device
-    tt::tile_offsets_kernel<<<n_groups, tt::kTilesPerGroup, 0, stream>>>(p.tile_count, p.group_sum, num_tiles, tile_first);
-    TT_CUDA(cudaGetLastError());
+    // K3: row order and TaskIds; the hit count is read from the control block on the device
     if (push || place_by_group()) {
-      // K3g: tile-ordered placement, optionally fused with the push of the compact form (sweep.cuh)
-      const tt::PushTarget none = {nullptr, nullptr, nullptr};
+      // K3g: tile-ordered placement, optionally fused with the push of the compact form (sweep.cuh); it
+      // derives every tile's offset in the row-ordered list from K1's partial sums itself (no K2)
+      const tt::PushTarget none = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+      if (hook && hook->wait_slot0) {  // the root must have read this shard's slot of the previous tick
+        tt::shard_wait_kernel<<<1, 32, 0, stream>>>(hook->wait_slot0, 0, 1, offsetof(tt::SlotHeader, consumed),
+                                                    hook->wait_value, hook->timeout_ns, nullptr, nullptr);
+        TT_CUDA(cudaGetLastError());
+        st->launches += 1;
+      }
       // Tiles per CTA and gathers per thread, measured on B200 at 25 M hits (plain placement): 1 tile x 1
       // gather 0.439 ms, 2 x 2 0.464, 4 x 4 0.474, 8 x 4 0.488, 16 x 4 0.503, 1 tile on 128 threads x 2 0.470 —
       // one tile per CTA, one hit per thread wins: all of a tile's gathers fall into one 128 KB span of the
@@ -539,7 +613,8 @@ int32_t sweep_run(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_
       static const int push_variant = [] { const char* e = getenv("TT_PUSH_VARIANT"); return e ? atoi(e) : 8; }();
 #define TT_PLACE_LAUNCH(GT, UN)                                                                                     \
   tt::place_group_kernel<TT_TILE_ROWS, GT, UN><<<(num_tiles + GT - 1) / GT, tt::kGroupThreads, 0, stream>>>(            \
-      t->ctl, t->hit_list, p.tile_slot, p.tile_count, tile_first, num_tiles, t->task_id, d_rows, d_ids, push ? *push : none)
+      t->hit_list, p.tile_slot, p.tile_count, p.group_sum, p.sub_sum, num_tiles, t->task_id, t->created_raw, d_rows,    \
+      d_ids, push ? *push : none)
       switch (push ? push_variant : plain_variant) {
         case 2: TT_PLACE_LAUNCH(2, 2); break;
         case 4: TT_PLACE_LAUNCH(4, 4); break;
@@ -547,31 +622,39 @@ int32_t sweep_run(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_
         default: TT_PLACE_LAUNCH(1, 1); break;
       }
 #undef TT_PLACE_LAUNCH
+      st->launches += 1;
     } else {
+      tt::tile_offsets_kernel<<<n_groups, tt::kTilesPerGroup, 0, stream>>>(p.tile_count, p.group_sum, num_tiles, tile_first);
+      TT_CUDA(cudaGetLastError());
       const int64_t per_cta = (int64_t)tt::kPlaceThreads * tt::kPlaceUnroll;
       const unsigned pgrid =
           (unsigned)std::max<int64_t>(1, std::min<int64_t>((cap + per_cta - 1) / per_cta, (int64_t)t->sm_count * 8));
       tt::place_hits_kernel<TT_TILE_ROWS><<<pgrid, tt::kPlaceThreads, 0, stream>>>(
           t->ctl, t->hit_list, p.tile_slot, tile_first, first_tile, t->task_id, d_rows, d_ids);
+      st->launches = 3;
     }
     TT_CUDA(cudaGetLastError());
-    st->launches = 3;
   }
-  TT_CUDA(cudaEventRecord(t->ev2, stream));
-  TT_CUDA(cudaMemcpyAsync(t->h_ctl, t->ctl, sizeof init, cudaMemcpyDeviceToHost, stream));
-  TT_CUDA(cudaStreamSynchronize(stream));
-  TT_CUDA(cudaEventElapsedTime(&st->sweep_ms, t->ev0, t->ev1));
-  TT_CUDA(cudaEventElapsedTime(&st->gather_ms, t->ev1, t->ev2));
-  st->kernel_ms = st->sweep_ms + st->gather_ms;
-  st->n_listed = (int64_t)t->h_ctl->cursor;
-  const bool complete = t->h_ctl->stored == ~0ull;
-  st->n_stored = listing ? (complete ? st->n_listed : (int64_t)t->h_ctl->stored) : 0;
-  st->resume_row = complete ? (row_end >= 0 ? std::min<int64_t>(row_end, t->n) : t->n) : first_row;
-  st->n_marked = p.mark_enable ? (listing ? st->n_stored : st->n_listed) : 0;
-  if (!complete)
-    return fail(TT_ERR_CAPACITY, "%lld hits do not fit in %lld (%lld stored%s)", (long long)st->n_listed,
-                (long long)cap, (long long)st->n_stored, st->n_marked ? " and marked; call again for the rest" : "");
-  return TT_OK;
+  // the epilogue: outcome -> mapped host memory (and the push target), scratch back to its start state,
+  // the epoch word of a sharded tick
+  tt::sweep_tail_kernel<<<1, 256, 0, stream>>>(t->ctl, t->d_out, t->group_sum, n_groups, p.sub_sum, n_subs,
+                                              push ? push->count : nullptr, hook ? hook->epoch_word : nullptr,
+                                              hook ? hook->epoch : 0);
+  TT_CUDA(cudaGetLastError());
+  st->launches += 1;
+  if (timing) TT_CUDA(cudaEventRecord(t->ev2, stream));
+  t->pending = tt_table::PendingSweep();
+  t->pending.active = true;
+  t->pending.listing = listing;
+  t->pending.timing = timing;
+  t->pending.mark_enable = p.mark_enable;
+  t->pending.first_row = first_row;
+  t->pending.row_end = row_end;
+  t->pending.cap = cap;
+  t->pending.launches = st->launches;
+  t->pending.stream = stream;
+  if (flags & TT_SWEEP_ASYNC) return TT_OK;  // the caller collects the outcome with tt_sweep_wait
+  return sweep_finish(t, st);
 }
 
 int32_t result_alloc(tt_table* t, int64_t cap, tt_result** out) {
@@ -680,6 +763,42 @@ int32_t sweep_owned(tt_table* t, int32_t mode, int32_t flags, int64_t today, int
   return fail(TT_ERR_STATE, "sweep did not converge");
 }
 
+// The TaskId index: rows in TaskId order (t->id_order) for a table whose rows are not.  Built on
+// the device by two stable 64-bit radix sorts, the low 8 canonical bytes first, then the high 8
+// bytes of the rows in that order.  No-op while the table itself is in TaskId order or the index
+// still covers every row (tt_insert_task drops it when it appends an out-of-order id).
+int32_t ensure_id_order(tt_table* t) {
+  if (t->ids_sorted || t->id_order || t->n == 0) return TT_OK;
+  const int64_t n = t->n;
+  cudaStream_t st = t->stream;
+  cudaError_t e = t->sort.reserve(n);
+  int w = 0;
+  if (e == cudaSuccess) {
+    tt::id_half_keys_kernel<<<grid_for(n, 256), 256, 0, st>>>(t->task_id, nullptr, n, 0, t->sort.keys[0], t->sort.vals[0]);
+    e = tt::radix_sort_pairs(st, t->sort, n, 64, &w);
+  }
+  if (e == cudaSuccess) {
+    tt::id_half_keys_kernel<<<grid_for(n, 256), 256, 0, st>>>(t->task_id, t->sort.vals[w], n, 1, t->sort.keys[w ^ 1],
+                                                              t->sort.vals[w ^ 1]);
+    if (w == 0) {  // radix_sort_pairs starts from buffer pair 0
+      std::swap(t->sort.keys[0], t->sort.keys[1]);
+      std::swap(t->sort.vals[0], t->sort.vals[1]);
+    }
+    e = tt::radix_sort_pairs(st, t->sort, n, 64, &w);
+  }
+  uint32_t* order = nullptr;
+  if (e == cudaSuccess) e = cudaMalloc(&order, (size_t)n * 4);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(order, t->sort.vals[w], (size_t)n * 4, cudaMemcpyDeviceToDevice, st);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+  if (e != cudaSuccess) {
+    cudaFree(order);
+    cudaGetLastError();
+    return fail(e == cudaErrorMemoryAllocation ? TT_ERR_OOM : TT_ERR_CUDA, "TaskId index: %s", cudaGetErrorString(e));
+  }
+  t->id_order = order;
+  return TT_OK;
+}
+
 }  // namespace
 
 // =============================================================================================
@@ -707,6 +826,8 @@ int32_t tt_create(int32_t device, tt_table** out) {
   TT_CUDA(cudaEventCreate(&t->ev2));
   TT_CUDA(cudaMalloc(&t->ctl, sizeof(tt::SweepCtl)));
   TT_CUDA(cudaMallocHost(&t->h_ctl, sizeof(tt::SweepCtl)));
+  TT_CUDA(cudaHostAlloc(&t->h_out, sizeof(tt::SweepOut), cudaHostAllocMapped));
+  TT_CUDA(cudaHostGetDevicePointer(&t->d_out, t->h_out, 0));
   TT_CUDA(cudaMalloc(&t->d_small, 16 * 8));
   TT_CUDA(cudaMallocHost(&t->h_small, 16 * 8));
   TT_CUDA(cudaMalloc(&t->d_qcount, tt::kMaxQueries * 4));
@@ -732,6 +853,7 @@ int32_t tt_destroy(tt_table* t) {
     free_columns(t);
     cudaFree(t->ctl);
     cudaFreeHost(t->h_ctl);
+    cudaFreeHost(t->h_out);
     cudaFree(t->d_small);
     cudaFreeHost(t->h_small);
     t->sort.release();
@@ -962,6 +1084,14 @@ int32_t tt_sweep_device(tt_table* t, int32_t mode, int32_t flags, int64_t today_
                    stream ? (cudaStream_t)stream : t->stream);
 }
 
+int32_t tt_sweep_wait(tt_table* t, tt_sweep_stats* h_stats) {
+  if (!t || !h_stats) return fail(TT_ERR_ARG, "null argument");
+  std::lock_guard<std::mutex> lk(t->mu);
+  DeviceGuard g(t->device);
+  if (!t->pending.active) return fail(TT_ERR_STATE, "no tick is pending on this table");
+  return sweep_finish(t, h_stats);
+}
+
 int32_t tt_sweep_push(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_ticks, int64_t run_at_utc_ticks,
                       uint32_t* d_rows, void* d_ids, int64_t cap, const tt_push_target* target, tt_sweep_stats* h_stats,
                       void* stream) {
@@ -975,6 +1105,9 @@ int32_t tt_sweep_push(tt_table* t, int32_t mode, int32_t flags, int64_t today_lo
   push.off16 = static_cast<uint16_t*>(target->off16);
   push.tile_count = static_cast<uint32_t*>(target->tile_count);
   push.count = static_cast<unsigned long long*>(target->count);
+  push.ids = nullptr;
+  push.created = nullptr;
+  push.tile_first = nullptr;
   return sweep_run(t, mode, flags, today_local_ticks, run_at_utc_ticks, 0, d_rows, (uint4*)d_ids, cap, h_stats,
                    stream ? (cudaStream_t)stream : t->stream, &push);
 }
@@ -1038,13 +1171,22 @@ int32_t tt_mark_overdue(tt_table* t, int32_t mode, const uint8_t* ids16, int64_t
   if (n == 0) return TT_OK;
   std::lock_guard<std::mutex> lk(t->mu);
   DeviceGuard g(t->device);
+  if (t->n == 0) {
+    if (n_missing) *n_missing = n;
+    return TT_OK;
+  }
+  // the kernel binary-searches rows in TaskId order: a table whose rows are not (every CreateNewTask
+  // with a fresh Guid breaks the order) gets its TaskId index rebuilt first
+  int32_t rc = ensure_id_order(t);
+  if (rc) return rc;
   uint4* d_ids = nullptr;
   TT_CUDA(cudaMalloc(&d_ids, n * 16));
   cudaError_t e = cudaMemcpyAsync(d_ids, ids16, n * 16, cudaMemcpyHostToDevice, t->stream);
   if (e == cudaSuccess) e = cudaMemsetAsync(t->d_small, 0, 16, t->stream);
   if (e == cudaSuccess) {
-    tt::mark_by_id_kernel<<<grid_for(n, 128), 128, 0, t->stream>>>(d_ids, n, t->task_id, t->id_order, t->n, t->overdue,
-                                                                   t->d_small);
+    tt::mark_by_id_kernel<<<grid_for(n, 128), 128, 0, t->stream>>>(d_ids, n, t->task_id, t->creator_ref,
+                                                                   t->ids_sorted ? nullptr : t->id_order, t->n,
+                                                                   t->overdue, t->d_small);
     e = cudaGetLastError();
   }
   if (e == cudaSuccess) e = cudaMemcpyAsync(t->h_small, t->d_small, 16, cudaMemcpyDeviceToHost, t->stream);
@@ -1471,6 +1613,8 @@ int32_t tt_expand_hits(int32_t device, const uint32_t* d_tile_count, int64_t n_t
 
 #include "api_tick.inc"
 
+#include "api_shards.inc"
+
 // ---- the sweep with its working memory in a fixed device array ---------------------------------
 //
 // For callers that cannot allocate (see include/tasktable.h).  Everything tt_sweep_device keeps
@@ -1537,6 +1681,14 @@ extern "C" int32_t tt_sweep_static(const tt_device_view* cols, int32_t mode, int
     h_stats->resume_row = 0;
     return TT_OK;
   }
+  int n_dev = 0;
+  TT_CUDA(cudaGetDeviceCount(&n_dev));
+  if (cols->device >= n_dev) return fail(TT_ERR_ARG, "device %d not in [0, %d)", cols->device, n_dev);
+  const bool mark = (flags & TT_SWEEP_MARK) != 0;
+  const bool range = (flags & TT_SWEEP_DUE_ON_OR_BEFORE) != 0;
+  const bool survive = run_at_utc_ticks / TT_TICKS_PER_DAY > (int64_t)yesterday;
+  if (range && mark && !survive)  // the same refusal as tt_sweep_device (sweep_run)
+    return fail(TT_ERR_ARG, "range sweep: run_at_utc_ticks must lie after yesterday (runAt.Date > TaskDueDate.Date would differ per row)");
   std::lock_guard<std::mutex> lk(g_static_mu);  // one sweep at a time owns the fixed array
   DeviceGuard g(cols->device);
   const int dev = cols->device;
@@ -1551,8 +1703,6 @@ extern "C" int32_t tt_sweep_static(const tt_device_view* cols, int32_t mode, int
   }
   unsigned char* base = g_static_addr[dev];
   cudaStream_t stream = (cudaStream_t)stream_;
-  const bool mark = (flags & TT_SWEEP_MARK) != 0;
-  const bool survive = run_at_utc_ticks / TT_TICKS_PER_DAY > (int64_t)yesterday;
   const bool listing = d_rows != nullptr;
   const uint32_t num_tiles = (uint32_t)(cols->n_padded / TT_TILE_ROWS);
 
@@ -1565,6 +1715,7 @@ extern "C" int32_t tt_sweep_static(const tt_device_view* cols, int32_t mode, int
   p.tile_count = p.tile_slot + kStaticTiles;
   uint32_t* tile_first = p.tile_slot + 2 * kStaticTiles;
   p.group_sum = reinterpret_cast<uint32_t*>(base + kStaticGroupOff);
+  p.sub_sum = nullptr;
   p.ctl = reinterpret_cast<tt::SweepCtl*>(base);
   p.cap = listing ? (unsigned long long)cap : ~0ull;
   p.first_tile = 0;
@@ -1573,35 +1724,66 @@ extern "C" int32_t tt_sweep_static(const tt_device_view* cols, int32_t mode, int
   p.yesterday = yesterday;
   p.mark_enable = (mark && survive && mode == TT_MODE_STORE) ? 1u : 0u;
 
+  // Once a kernel has been queued the shared array is in use on the caller's stream: every exit
+  // below first waits for the stream, so the lock is never released while kernels may still touch it.
+  cudaError_t e = cudaSuccess;
+  const char* what = "";
+  auto step = [&](const char* name) {
+    if (e == cudaSuccess) {
+      e = cudaGetLastError();
+      what = name;
+    }
+    return e == cudaSuccess;
+  };
   static_scratch_reset_kernel<<<1, 64, 0, stream>>>();
-  TT_CUDA(cudaGetLastError());
-  const unsigned grid = (unsigned)std::min<int64_t>(num_tiles, (int64_t)g_static_sms[dev] * tt::kSweepCtasPerSm);
-  if (mode == TT_MODE_STORE) {
-    if (p.mark_enable)
-      tt::sweep_kernel<true, true, tt::kSweepThreads, tt::kSweepCtasPerSm><<<grid, tt::kSweepThreads, 0, stream>>>(p);
-    else
-      tt::sweep_kernel<true, false, tt::kSweepThreads, tt::kSweepCtasPerSm><<<grid, tt::kSweepThreads, 0, stream>>>(p);
-  } else {
-    tt::sweep_kernel<false, false, tt::kSweepThreads, tt::kSweepCtasPerSm><<<grid, tt::kSweepThreads, 0, stream>>>(p);
+  constexpr int kT = tt::kSweepThreads, kC = tt::kSweepCtasPerSm;
+  const unsigned grid = (unsigned)std::min<int64_t>(num_tiles, (int64_t)g_static_sms[dev] * kC);
+  if (step("reset")) {
+    if (range) {
+      if (mode == TT_MODE_STORE) {
+        if (p.mark_enable) tt::sweep_kernel<true, true, kT, kC, true><<<grid, kT, 0, stream>>>(p);
+        else tt::sweep_kernel<true, false, kT, kC, true><<<grid, kT, 0, stream>>>(p);
+      } else {
+        tt::sweep_kernel<false, false, kT, kC, true><<<grid, kT, 0, stream>>>(p);
+      }
+    } else if (mode == TT_MODE_STORE) {
+      if (p.mark_enable) tt::sweep_kernel<true, true, kT, kC><<<grid, kT, 0, stream>>>(p);
+      else tt::sweep_kernel<true, false, kT, kC><<<grid, kT, 0, stream>>>(p);
+    } else {
+      tt::sweep_kernel<false, false, kT, kC><<<grid, kT, 0, stream>>>(p);
+    }
   }
-  TT_CUDA(cudaGetLastError());
   h_stats->launches = 2;
-  if (listing) {
+  if (step("sweep_kernel") && listing) {
     const unsigned n_groups = (num_tiles + tt::kTilesPerGroup - 1) / tt::kTilesPerGroup;
     tt::tile_offsets_kernel<<<n_groups, tt::kTilesPerGroup, 0, stream>>>(p.tile_count, p.group_sum, num_tiles, tile_first);
-    TT_CUDA(cudaGetLastError());
-    const int64_t per_cta = (int64_t)tt::kPlaceThreads * tt::kPlaceUnroll;
-    const unsigned pgrid = (unsigned)std::max<int64_t>(
-        1, std::min<int64_t>((cap + per_cta - 1) / per_cta, (int64_t)g_static_sms[dev] * 8));
-    tt::place_hits_kernel<TT_TILE_ROWS><<<pgrid, tt::kPlaceThreads, 0, stream>>>(
-        p.ctl, p.list, p.tile_slot, tile_first, 0, static_cast<const uint4*>(cols->task_id), d_rows,
-        static_cast<uint4*>(d_ids));
-    TT_CUDA(cudaGetLastError());
+    if (step("tile_offsets_kernel")) {
+      const int64_t per_cta = (int64_t)tt::kPlaceThreads * tt::kPlaceUnroll;
+      const unsigned pgrid = (unsigned)std::max<int64_t>(
+          1, std::min<int64_t>((cap + per_cta - 1) / per_cta, (int64_t)g_static_sms[dev] * 8));
+      tt::place_hits_kernel<TT_TILE_ROWS><<<pgrid, tt::kPlaceThreads, 0, stream>>>(
+          p.ctl, p.list, p.tile_slot, tile_first, 0, static_cast<const uint4*>(cols->task_id), d_rows,
+          static_cast<uint4*>(d_ids));
+      step("place_hits_kernel");
+    }
     h_stats->launches = 4;
   }
   tt::SweepCtl done;  // read back into the caller's stack: no pinned buffer is created for it
-  TT_CUDA(cudaMemcpyAsync(&done, base, sizeof done, cudaMemcpyDeviceToHost, stream));
-  TT_CUDA(cudaStreamSynchronize(stream));
+  done.cursor = 0;
+  done.stored = ~0ull;
+  if (e == cudaSuccess) {
+    e = cudaMemcpyAsync(&done, base, sizeof done, cudaMemcpyDeviceToHost, stream);
+    what = "copy of the control block";
+  }
+  const cudaError_t se = cudaStreamSynchronize(stream);
+  if (e == cudaSuccess && se != cudaSuccess) {
+    e = se;
+    what = "cudaStreamSynchronize";
+  }
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    return fail(TT_ERR_CUDA, "tt_sweep_static, %s: %s", what, cudaGetErrorString(e));
+  }
   h_stats->n_listed = (int64_t)done.cursor;
   const bool complete = done.stored == ~0ull;
   h_stats->n_stored = listing ? (complete ? h_stats->n_listed : (int64_t)done.stored) : 0;

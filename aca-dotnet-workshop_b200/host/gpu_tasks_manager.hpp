@@ -89,7 +89,7 @@ class TaskTableLibrary {
     TT_BIND(tt_result_count); TT_BIND(tt_result_rows); TT_BIND(tt_result_ids); TT_BIND(tt_result_field);
     TT_BIND(tt_result_free);
     TT_BIND(tt_get_by_id); TT_BIND(tt_insert_task); TT_BIND(tt_update_task); TT_BIND(tt_mark_completed);
-    TT_BIND(tt_delete_task);
+    TT_BIND(tt_delete_task); TT_BIND(tt_upsert_task);
     TT_BIND(tt_load_payload); TT_BIND(tt_set_task_strings); TT_BIND(tt_result_json); TT_BIND(tt_json_size); TT_BIND(tt_json_copy); TT_BIND(tt_json_free);
 #undef TT_BIND
   }
@@ -112,6 +112,7 @@ class TaskTableLibrary {
   decltype(&::tt_update_task) tt_update_task;
   decltype(&::tt_mark_completed) tt_mark_completed;
   decltype(&::tt_delete_task) tt_delete_task;
+  decltype(&::tt_upsert_task) tt_upsert_task;
   decltype(&::tt_load_payload) tt_load_payload;
   decltype(&::tt_set_task_strings) tt_set_task_strings;
   decltype(&::tt_result_json) tt_result_json;
@@ -188,7 +189,27 @@ class GpuTasksManager : public ITasksManager {
     }
     int64_t marked = 0, missing = 0;
     check(lib_->tt_mark_overdue(table_, mode_, ids.data(), (int64_t)overDueTasksList.size(), &marked, &missing));
+    last_mark_missing = missing;
+    if (missing == 0) return;
+    // SaveStateAsync is an upsert (TasksStoreManager.cs:147): a listed task the table does not hold is created
+    for (const TaskModel& t : overDueTasksList) {
+      tt_result* r = nullptr;
+      check(lib_->tt_get_by_id(table_, t.TaskId.data(), &r));
+      int64_t n = 0;
+      lib_->tt_result_count(r, &n);
+      lib_->tt_result_free(r);
+      if (n > 0) continue;
+      int64_t row = -1;
+      int32_t existed = 0;
+      check(lib_->tt_upsert_task(table_, t.TaskId.data(), t.TaskCreatedOn.dateData, t.TaskDueDate.dateData,
+                                 t.TaskCreatedBy.data(), (int32_t)t.TaskCreatedBy.size(), t.IsCompleted ? 1 : 0, 1, &row,
+                                 &existed));
+      int32_t found = 0;
+      check(lib_->tt_set_task_strings(table_, t.TaskId.data(), t.TaskName.data(), (int32_t)t.TaskName.size(),
+                                      t.TaskAssignedTo.data(), (int32_t)t.TaskAssignedTo.size(), &found));
+    }
   }
+  int64_t last_mark_missing = 0;  // ids of the last MarkOverdueTasks call that had to be created
 
   std::vector<TaskModel> GetTasksByCreator(const std::string& createdBy) override {
     tt_result* r = nullptr;

@@ -1,11 +1,11 @@
-"""TaskId-range sharding and the cross-shard exchange.
+"""TaskId-range sharding under one process per GPU.
 
 The table is sorted by TaskId, so an equal-width TaskId range is a contiguous block of rows:
-shard g of G owns global rows [g*N/G, (g+1)*N/G).  Every GPU sweeps its own shard with no
-data-path collective; afterwards only the per-shard hit counts (all-gather, 8 bytes per rank)
-and the hit identifiers (variable-length gather to the root) cross NVLink.  The exchange is
-written against torch.distributed so the same code runs over NCCL on GPUs and over gloo in
-the CPU tests.
+shard g of G owns global rows [g*N/G, (g+1)*N/G).  The exchange itself lives behind the C ABI
+(include/tasktable.h, tt_exchange_* / tt_shards_*): ShardExchange below only does the rendezvous.
+HitExchange / exchange_hits are the earlier NCCL forms (count all-gather + variable-length gather
+with grouped send/recv), kept as the fallback for boxes where CUDA IPC is not permitted and
+because they run over gloo in the CPU tests.
 """
 import os
 from dataclasses import dataclass
@@ -265,104 +265,69 @@ def push_slot_layout(n_tiles, cap):
     return o_cnt, o_off, o_off + up(2 * cap)
 
 
-class _DeviceSpan:
-    """Raw device memory as a __cuda_array_interface__ object, so torch can view it without copying."""
+class ShardExchange:
+    """One rank's end of the fused cross-shard exchange: tasktable.Exchange (C ABI: tt_exchange_*) plus the
+    rendezvous it needs under one-process-per-GPU — the root's 64-byte buffer handle is broadcast, every rank
+    learns the shards' first rows and the largest tile count.  That is ALL torch.distributed does here: a
+    tick stores its result into the root's slot from inside the placement kernel (over NVLink when the
+    slot is on another GPU), publishes an epoch word, and the root waits for the words on the device; no
+    collective runs in the tick.  Collective constructor: every rank must create it."""
 
-    def __init__(self, ptr, n, typestr):
-        self.__cuda_array_interface__ = {"shape": (n,), "typestr": typestr, "data": (ptr, False), "version": 3}
-
-
-class PushExchange:
-    """The exchange fused into the sweep (TaskTable.sweep_push, include/tasktable.h tt_sweep_push).
-
-    The root shard owns one receive buffer with a slot per shard (push_slot_layout); every other
-    process maps it with CUDA IPC.  A shard's sweep stores the compact form of its hit list
-    straight into its slot — over NVLink when the slot is on another GPU — from the same kernel
-    that puts its hits in row order and gathers their TaskIds, so the transfer hides behind that
-    kernel's HBM gathers and no collective moves data.  `fence()` (a one-word all-reduce, stream
-    ordered after the sweep) is the only cross-process step: when it returns on the root, every
-    slot is complete.  Collective constructor: every rank must create it."""
-
-    def __init__(self, plan, cap_per_rank, device_index, dst=0, group=None, tile_rows=8192):
+    def __init__(self, first_row, n_rows, cap_per_shard, device_index, flags=0, group=None, tile_rows=8192):
         from . import tasktable as tt
 
-        self._tt, self.plan, self.dst, self.group, self.device_index = tt, plan, dst, group, device_index
+        self._tt, self.group, self.device_index = tt, group, device_index
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
-        self.cap = (cap_per_rank + 7) // 8 * 8
-        rows_max = max(shard_rows(plan.n_total, self.world, r)[1] - shard_rows(plan.n_total, self.world, r)[0]
-                       for r in range(self.world))
-        self.n_tiles = max(1, -(-rows_max // tile_rows))
-        self.o_cnt, self.o_off, self.slot_bytes = push_slot_layout(self.n_tiles, self.cap)
-        self.owner = self.rank == dst
-        self.base = 0
+        self.cap = (cap_per_shard + 7) // 8 * 8
+        dev = torch.device("cuda", device_index)
+        mine = torch.tensor([first_row, -(-n_rows // tile_rows)], dtype=torch.int64, device=dev)
+        every = [torch.zeros(2, dtype=torch.int64, device=dev) for _ in range(self.world)]
+        if self.world > 1:
+            dist.all_gather(every, mine, group=group)
+        else:
+            every = [mine]
+        self.first_rows = [int(x[0].item()) for x in every]
+        self.max_tiles = max(1, max(int(x[1].item()) for x in every))
         payload = [None]
-        if self.owner:
+        self.ex = None
+        if self.rank == 0:
             try:
-                self.base, payload[0] = tt.peer_alloc(device_index, self.world * self.slot_bytes)
+                self.ex, payload[0] = tt.Exchange.create_root(device_index, self.world, self.cap, self.max_tiles, flags)
             except tt.TaskTableError as e:  # the other ranks are waiting in the broadcast: tell them
                 payload[0] = str(e)
         if self.world > 1:
-            dist.broadcast_object_list(payload, src=dst, group=group)
+            dist.broadcast_object_list(payload, src=0, group=group)
         if not isinstance(payload[0], bytes):
             raise RuntimeError(f"root could not allocate the receive buffer: {payload[0]}")
-        if not self.owner:
-            self.base = tt.peer_open(device_index, payload[0])
-        self.slot = self.base + self.rank * self.slot_bytes
-        self._flag = torch.zeros(1, dtype=torch.int32, device=torch.device("cuda", device_index))
-        self._scratch = None
+        if self.rank != 0:
+            self.ex = tt.Exchange.attach(device_index, self.rank, self.world, self.cap, self.max_tiles, flags, payload[0])
 
-    def sweep(self, table, mode, flags, d_rows, d_ids, stream=None, **kw):
-        """This shard's cron tick; its compact hit list lands in the root's slot.  -> SweepStats."""
-        st, _ = table.sweep_push(mode, flags, d_rows, d_ids, self.cap, self.slot + self.o_off, self.slot + self.o_cnt,
-                                 self.slot, stream=stream, **kw)
-        return st
+    def tick(self, table, mode, flags, **kw):
+        """This shard's cron tick (Exchange.tick).  -> (SweepStats, rc)."""
+        return self.ex.tick(table, mode, flags, **kw)
 
-    def fence(self):
-        """Stream-ordered after the sweep on every rank; afterwards the root may read all slots."""
-        if self.world > 1:
-            dist.all_reduce(self._flag, group=self.group)
+    def collect(self, order=0):
+        """root: every shard's list as one GResult (waits on the device for the shards' epoch words)."""
+        assert self.rank == 0
+        return self.ex.collect(order, self.first_rows)
 
-    # ---- root side -------------------------------------------------------------------------------
-    def _view(self, r, off, n, typestr, dtype):
-        assert self.owner
-        return torch.as_tensor(_DeviceSpan(self.base + r * self.slot_bytes + off, n, typestr),
-                               device=torch.device("cuda", self.device_index)).view(dtype)
-
-    def counts(self):
-        """root: hits stored by each shard (python list; reads the device)."""
-        return [int(self._view(r, 0, 1, "<i8", torch.int64).item()) for r in range(self.world)]
-
-    def shard_rows_local(self, r, count, stream=None):
-        """root: shard r's hit rows (shard-local, ascending) rebuilt from its slot."""
-        dev = torch.device("cuda", self.device_index)
-        if self._scratch is None:
-            self._scratch = torch.empty(self.n_tiles + self.n_tiles // 1024 + 8, dtype=torch.int32, device=dev)
-        out = torch.empty(max(count, 1), dtype=torch.int32, device=dev)
-        slot = self.base + r * self.slot_bytes
-        self._tt.expand_hits(self.device_index, slot + self.o_cnt, self.n_tiles, slot + self.o_off,
-                             self._scratch.data_ptr(), out.data_ptr(), stream)
-        torch.cuda.synchronize(dev)
-        return out[:count]
-
-    def global_rows(self, stream=None):
-        """root: all shards' hits as ascending global row numbers (int64)."""
-        parts = []
-        for r, c in enumerate(self.counts()):
-            local = self.shard_rows_local(r, c, stream)
-            parts.append((local.to(torch.int64) & 0xFFFFFFFF) + shard_rows(self.plan.n_total, self.world, r)[0])
-        return torch.cat(parts)
+    def release(self):
+        assert self.rank == 0
+        self.ex.release()
 
     def close(self):
-        if not self.base:
+        if self.ex is None:
             return
         if self.world > 1:
             dist.barrier(group=self.group)  # nobody may still be storing into the buffer
-        if self.owner:
-            self._tt.peer_free(self.device_index, self.base)
-        else:
-            self._tt.peer_close(self.device_index, self.base)
-        self.base = 0
+        if self.rank != 0:
+            self.ex.close()
+        if self.world > 1:
+            dist.barrier(group=self.group)  # the mappings are gone before the root frees the memory
+        if self.rank == 0:
+            self.ex.close()
+        self.ex = None
 
 
 def exchange_hits(local_rows, count, plan, ids=None, dst=0, group=None):

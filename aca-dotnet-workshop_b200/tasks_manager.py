@@ -148,15 +148,40 @@ class GpuTasksManager:
     def GetYesterdaysDueTasks(self, today_local_ticks=tt.DEFAULT_TODAY) -> List[TaskModel]:
         return self._materialise(self._table.get_yesterdays_due(self.mode, today_local_ticks))
 
-    # ITasksManager.cs:13
+    # ITasksManager.cs:13 — TasksStoreManager.cs:141-149: IsOverDue = true, then an upsert of the whole
+    # record under its TaskId.  The listed tasks that exist get their bit set in one kernel; an id the
+    # table does not hold is created from the caller's record, as SaveStateAsync would.
     def MarkOverdueTasks(self, overDueTasksList: List[TaskModel]) -> None:
         ids = np.frombuffer(b"".join(t.TaskId.bytes for t in overDueTasksList), dtype=np.uint8).reshape(-1, 16)
         if self.mode == tt.MODE_FAKE:
             self._table.mark_overdue(self.mode, ids)  # raises NotImplementedInReference
-        if len(overDueTasksList):
-            self._table.mark_overdue(self.mode, ids)
         for t in overDueTasksList:  # TasksStoreManager.cs:146 mutates the caller's objects too
             t.IsOverDue = True
+        if not overDueTasksList:
+            return
+        _, missing = self._table.mark_overdue(self.mode, ids)
+        self.last_mark_missing = missing
+        if missing:
+            for t in overDueTasksList:
+                res = self._table.get_by_id(t.TaskId.bytes)
+                known = res.count > 0
+                res.free()
+                if not known:
+                    self._upsert(t)
+
+    def _upsert(self, t: TaskModel) -> None:
+        b = t.TaskCreatedBy.encode("utf-8")
+        if b not in self._creator_set():
+            self._creators.append(b)
+            self._creator_lookup.add(b)
+        row, existed = self._table.upsert_task(t.TaskId.bytes, t.TaskCreatedOn, t.TaskDueDate, b, t.IsCompleted, t.IsOverDue)
+        if not existed:
+            assert row == len(self._names)
+            self._names.append(t.TaskName)
+            self._assignees.append(t.TaskAssignedTo)
+        else:
+            self._names[row], self._assignees[row] = t.TaskName, t.TaskAssignedTo
+        self._table.set_task_strings(t.TaskId.bytes, t.TaskName.encode("utf-8"), t.TaskAssignedTo.encode("utf-8"))
 
     # ITasksManager.cs:7
     def GetTasksByCreator(self, createdBy: str) -> List[TaskModel]:

@@ -17,6 +17,8 @@ MODE_STORE = 1
 SWEEP_LIST_ONLY = 0
 SWEEP_MARK = 1
 SWEEP_DUE_ON_OR_BEFORE = 2  # TT_SWEEP_DUE_ON_OR_BEFORE: the generalised predicate (OR it into the flags)
+SWEEP_NO_TIMING = 4         # TT_SWEEP_NO_TIMING: no CUDA events between the kernels, timing fields stay 0
+SWEEP_ASYNC = 8             # TT_SWEEP_ASYNC: queue the tick and return; sweep_wait() collects the outcome
 
 TT_OK = 0
 TT_ERR_ARG = -1
@@ -34,6 +36,13 @@ FIELD_CREATOR_REF = 5
 
 JSON_RESPONSE = 0  # TT_JSON_RESPONSE: the MVC output formatter's encoder
 JSON_DOCUMENT = 1  # TT_JSON_DOCUMENT: the encoder of Dapr's client bodies
+
+EXCHANGE_IDS = 1       # TT_EXCHANGE_IDS: the slots carry the hits' TaskIds
+EXCHANGE_CREATED = 2   # TT_EXCHANGE_CREATED: ... and their TaskCreatedOn (the cross-shard OrderBy)
+ORDER_ROWS = 0         # TT_ORDER_ROWS
+ORDER_CREATED_ASC = 1  # TT_ORDER_CREATED_ASC
+COLLECT_RELEASE = 0x100
+MAX_SHARDS = 32
 
 TICKS_PER_DAY = 864000000000
 DEFAULT_TODAY = 639295200000000000  # 2026-11-06T00:00:00
@@ -54,7 +63,17 @@ EXPORTS = [
     "tt_sweep_push", "tt_peer_alloc", "tt_peer_open", "tt_peer_close", "tt_peer_free",
     "tt_load_payload", "tt_generate_payload", "tt_result_json", "tt_json_size", "tt_json_copy", "tt_json_device",
     "tt_json_free", "tt_last_json_stats", "tt_json_offsets", "tt_load_documents",
-    "tt_get_due_on_or_before", "tt_sweep_backlog", "tt_tick_host", "tt_set_task_strings",
+    "tt_get_due_on_or_before", "tt_sweep_backlog", "tt_tick_host", "tt_set_task_strings", "tt_upsert_task",
+    "tt_sweep_wait",
+    "tt_exchange_create_root", "tt_exchange_attach", "tt_exchange_attach_local", "tt_exchange_destroy",
+    "tt_exchange_slot_bytes", "tt_exchange_tick", "tt_exchange_epoch", "tt_exchange_collect", "tt_exchange_release",
+    "tt_exchange_last_collect_ms",
+    "tt_gresult_count", "tt_gresult_shard_counts", "tt_gresult_rows", "tt_gresult_ids", "tt_gresult_digest", "tt_gresult_free",
+    "tt_shards_create", "tt_shards_destroy", "tt_shards_count", "tt_shards_table", "tt_shards_generate",
+    "tt_shards_generate_payload", "tt_shards_load_soa", "tt_shards_row_count", "tt_shards_get_yesterdays_due",
+    "tt_shards_get_due_on_or_before", "tt_shards_sweep", "tt_shards_mark_overdue", "tt_shards_get_by_creator",
+    "tt_shards_get_by_id", "tt_shards_insert_task", "tt_shards_update_task", "tt_shards_mark_completed",
+    "tt_shards_delete_task",
 ]
 
 
@@ -208,6 +227,7 @@ def lib():
     L.tt_get_by_id.argtypes = [vp, vp, P(vp)]
     L.tt_insert_task.argtypes = [vp, vp, u64, u64, C.c_char_p, i32, P(i64)]
     L.tt_update_task.argtypes = [vp, vp, u64, P(i32)]
+    L.tt_upsert_task.argtypes = [vp, vp, u64, u64, C.c_char_p, i32, i32, i32, P(i64), P(i32)]
     L.tt_mark_completed.argtypes = [vp, vp, P(i32)]
     L.tt_delete_task.argtypes = [vp, vp, P(i32)]
     L.tt_live_count.argtypes = [vp, P(i64)]
@@ -225,6 +245,7 @@ def lib():
     L.tt_count_flags.argtypes = [vp, P(i64), P(i64)]
     L.tt_result_digest.argtypes = [vp, P(u64), P(u64), P(u64)]
     L.tt_sweep_device.argtypes = [vp, i32, i32, i64, i64, i64, vp, vp, i64, P(SweepStats), vp]
+    L.tt_sweep_wait.argtypes = [vp, P(SweepStats)]
     L.tt_get_device_view.argtypes = [vp, P(DeviceView)]
     L.tt_sweep_static.argtypes = [P(DeviceView), i32, i32, i64, i64, vp, vp, i64, P(SweepStats), vp]
     L.tt_sweep_push.argtypes = [vp, i32, i32, i64, i64, vp, vp, i64, P(PushTarget), P(SweepStats), vp]
@@ -246,6 +267,40 @@ def lib():
     L.tt_set_task_strings.argtypes = [vp, vp, C.c_char_p, i32, C.c_char_p, i32, P(i32)]
     L.tt_json_offsets.argtypes = [vp, vp]
     L.tt_load_documents.argtypes = [vp, vp, vp, i64, i32, P(IngestStats)]
+    L.tt_exchange_create_root.argtypes = [i32, i32, i64, i64, i32, P(vp), P(PeerHandle)]
+    L.tt_exchange_attach.argtypes = [i32, i32, i32, i64, i64, i32, P(PeerHandle), P(vp)]
+    L.tt_exchange_attach_local.argtypes = [vp, i32, i32, P(vp)]
+    L.tt_exchange_destroy.argtypes = [vp]
+    L.tt_exchange_slot_bytes.argtypes = [vp, P(u64)]
+    L.tt_exchange_tick.argtypes = [vp, vp, i32, i32, i64, i64, vp, vp, P(SweepStats), vp]
+    L.tt_exchange_epoch.argtypes = [vp, P(u64)]
+    L.tt_exchange_collect.argtypes = [vp, i32, P(u64), u64, P(vp)]
+    L.tt_exchange_release.argtypes = [vp, u64]
+    L.tt_exchange_last_collect_ms.argtypes = [vp, P(C.c_float)]
+    L.tt_gresult_count.argtypes = [vp, P(i64)]
+    L.tt_gresult_shard_counts.argtypes = [vp, P(i64), i32]
+    L.tt_gresult_rows.argtypes = [vp, vp]
+    L.tt_gresult_ids.argtypes = [vp, vp]
+    L.tt_gresult_digest.argtypes = [vp, P(u64), P(u64), P(u64)]
+    L.tt_gresult_free.argtypes = [vp]
+    L.tt_shards_create.argtypes = [P(i32), i32, P(vp)]
+    L.tt_shards_destroy.argtypes = [vp]
+    L.tt_shards_count.argtypes = [vp, P(i32)]
+    L.tt_shards_table.argtypes = [vp, i32, P(vp), P(u64)]
+    L.tt_shards_generate.argtypes = [vp, P(SynthCfg), u64]
+    L.tt_shards_generate_payload.argtypes = [vp, P(SynthCfg), u64]
+    L.tt_shards_load_soa.argtypes = [vp, P(SoaView)]
+    L.tt_shards_row_count.argtypes = [vp, P(i64)]
+    L.tt_shards_get_yesterdays_due.argtypes = [vp, i32, i64, P(vp)]
+    L.tt_shards_get_due_on_or_before.argtypes = [vp, i32, i64, P(vp)]
+    L.tt_shards_sweep.argtypes = [vp, i32, i32, i64, i64, P(vp), P(i64)]
+    L.tt_shards_mark_overdue.argtypes = [vp, i32, vp, i64, P(i64), P(i64)]
+    L.tt_shards_get_by_creator.argtypes = [vp, C.c_char_p, i32, P(vp)]
+    L.tt_shards_get_by_id.argtypes = [vp, vp, P(vp)]
+    L.tt_shards_insert_task.argtypes = [vp, vp, u64, u64, C.c_char_p, i32, P(i32), P(i64)]
+    L.tt_shards_update_task.argtypes = [vp, vp, u64, P(i32)]
+    L.tt_shards_mark_completed.argtypes = [vp, vp, P(i32)]
+    L.tt_shards_delete_task.argtypes = [vp, vp, P(i32)]
     for name in EXPORTS:
         if name != "tt_last_error":
             getattr(L, name).restype = i32
@@ -418,6 +473,14 @@ class TaskTable:
         _check(lib().tt_create(device, C.byref(h)))
         self._h = h
         self.device = device
+        self._owned = True
+
+    @classmethod
+    def _borrowed(cls, handle, device):
+        """A table owned by someone else (a shard of a ShardedTable): close() does not destroy it."""
+        t = cls.__new__(cls)
+        t._h, t.device, t._owned = handle, device, False
+        return t
 
     # -- filling ---------------------------------------------------------------------------
     def generate(self, cfg, first_row, n_rows):
@@ -570,6 +633,15 @@ class TaskTable:
         _check(lib().tt_insert_task(self._h, _ptr(a), created_raw, due_raw, b, len(b), C.byref(row)))
         return row.value
 
+    def upsert_task(self, task_id, created_raw, due_raw, created_by, is_completed, is_overdue):
+        """tt_upsert_task: the state store's SaveStateAsync of a whole record -> (row, existed)."""
+        b = created_by.encode() if isinstance(created_by, str) else bytes(created_by)
+        row, existed = C.c_int64(-1), C.c_int32(0)
+        a = self._id(task_id)
+        _check(lib().tt_upsert_task(self._h, _ptr(a), created_raw, due_raw, b, len(b), int(bool(is_completed)),
+                                    int(bool(is_overdue)), C.byref(row), C.byref(existed)))
+        return row.value, bool(existed.value)
+
     def update_task(self, task_id, due_raw):
         f = C.c_int32(0)
         a = self._id(task_id)
@@ -608,6 +680,13 @@ class TaskTable:
         st = SweepStats()
         rc = lib().tt_sweep_device(self._h, mode, flags, today, run_at, first_row, d_rows, d_ids, cap, C.byref(st),
                                    stream)
+        _check(rc, allow=(TT_ERR_CAPACITY,) if allow_capacity else ())
+        return st, rc
+
+    def sweep_wait(self, allow_capacity=False):
+        """tt_sweep_wait: completes a tick queued with SWEEP_ASYNC -> (SweepStats, rc)."""
+        st = SweepStats()
+        rc = lib().tt_sweep_wait(self._h, C.byref(st))
         _check(rc, allow=(TT_ERR_CAPACITY,) if allow_capacity else ())
         return st, rc
 
@@ -690,7 +769,232 @@ class TaskTable:
 
     def close(self):
         if self._h:
-            lib().tt_destroy(self._h)
+            if self._owned:
+                lib().tt_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class GResult:
+    """tt_gresult: a list over the whole sharded table — global row numbers and TaskIds."""
+
+    def __init__(self, handle):
+        self._h = handle
+        n = C.c_int64(0)
+        _check(lib().tt_gresult_count(self._h, C.byref(n)))
+        self.count = n.value
+
+    def shard_counts(self):
+        out = (C.c_int64 * MAX_SHARDS)()
+        _check(lib().tt_gresult_shard_counts(self._h, out, MAX_SHARDS))
+        return list(out)
+
+    def rows(self):
+        out = np.empty(self.count, dtype=np.uint64)
+        _check(lib().tt_gresult_rows(self._h, _ptr(out)))
+        return out
+
+    def ids(self):
+        out = np.empty((self.count, 16), dtype=np.uint8)
+        _check(lib().tt_gresult_ids(self._h, _ptr(out)))
+        return out
+
+    def digest(self):
+        hi, lo, s = C.c_uint64(0), C.c_uint64(0), C.c_uint64(0)
+        _check(lib().tt_gresult_digest(self._h, C.byref(hi), C.byref(lo), C.byref(s)))
+        return hi.value, lo.value, s.value
+
+    def free(self):
+        if self._h:
+            lib().tt_gresult_free(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+class Exchange:
+    """tt_exchange: one shard's end of the cross-shard exchange (include/tasktable.h).  The root's owns the
+    receive buffer; the others map it — from another process through the 64-byte handle, inside one
+    process with attach_local."""
+
+    def __init__(self, handle, device, rank, world, root):
+        self._h, self.device, self.rank, self.world, self.root = handle, device, rank, world, root
+
+    @classmethod
+    def create_root(cls, device, world, cap_per_shard, max_tiles_per_shard, flags=0):
+        """-> (Exchange, handle bytes for the other processes)."""
+        h, ph = C.c_void_p(0), PeerHandle()
+        _check(lib().tt_exchange_create_root(device, world, cap_per_shard, max_tiles_per_shard, flags, C.byref(h), C.byref(ph)))
+        return cls(h, device, 0, world, True), bytes(ph.bytes)
+
+    @classmethod
+    def attach(cls, device, rank, world, cap_per_shard, max_tiles_per_shard, flags, handle_bytes):
+        ph = PeerHandle()
+        C.memmove(ph.bytes, handle_bytes, 64)
+        h = C.c_void_p(0)
+        _check(lib().tt_exchange_attach(device, rank, world, cap_per_shard, max_tiles_per_shard, flags, C.byref(ph), C.byref(h)))
+        return cls(h, device, rank, world, False)
+
+    def attach_local(self, device, rank):
+        h = C.c_void_p(0)
+        _check(lib().tt_exchange_attach_local(self._h, device, rank, C.byref(h)))
+        return Exchange(h, device, rank, self.world, False)
+
+    @property
+    def epoch(self):
+        e = C.c_uint64(0)
+        _check(lib().tt_exchange_epoch(self._h, C.byref(e)))
+        return e.value
+
+    @property
+    def slot_bytes(self):
+        b = C.c_uint64(0)
+        _check(lib().tt_exchange_slot_bytes(self._h, C.byref(b)))
+        return b.value
+
+    def tick(self, table, mode, flags, today=DEFAULT_TODAY, run_at=DEFAULT_RUN_AT, stream=None, allow_capacity=False,
+             d_rows=None, d_ids=None):
+        """This shard's cron tick; its result lands in its slot of the root's buffer.  -> (SweepStats, rc).
+        With SWEEP_ASYNC in flags the stats come from table.sweep_wait().  d_rows / d_ids: device addresses
+        for the shard's own copy of its list (optional)."""
+        st = SweepStats()
+        rc = lib().tt_exchange_tick(self._h, table._h, mode, flags, today, run_at, d_rows, d_ids, C.byref(st), stream)
+        _check(rc, allow=(TT_ERR_CAPACITY,) if allow_capacity else ())
+        return st, rc
+
+    def collect(self, order, first_rows, expected_epoch=None):
+        """root: waits (on the device) until every shard has published `expected_epoch` (default: this
+        shard's own epoch), -> GResult."""
+        fr = (C.c_uint64 * self.world)(*[int(x) for x in first_rows])
+        h = C.c_void_p(0)
+        _check(lib().tt_exchange_collect(self._h, order, fr, self.epoch if expected_epoch is None else expected_epoch, C.byref(h)))
+        return GResult(h)
+
+    def release(self, epoch=None):
+        _check(lib().tt_exchange_release(self._h, self.epoch if epoch is None else epoch))
+
+    def last_collect_ms(self):
+        ms = C.c_float(0)
+        _check(lib().tt_exchange_last_collect_ms(self._h, C.byref(ms)))
+        return ms.value
+
+    def close(self):
+        if self._h:
+            lib().tt_exchange_destroy(self._h)
+            self._h = None
+
+
+class ShardedTable:
+    """tt_shards: the task table split by TaskId range over several GPUs, driven from one process, behind
+    the same operations as TaskTable (the reference registers one ITasksManager, Api/Program.cs:13).
+    devices: one CUDA ordinal per shard (a device may repeat)."""
+
+    def __init__(self, devices):
+        arr = (C.c_int32 * len(devices))(*devices)
+        h = C.c_void_p(0)
+        _check(lib().tt_shards_create(arr, len(devices), C.byref(h)))
+        self._h, self.devices = h, list(devices)
+
+    def generate(self, cfg, n_total):
+        _check(lib().tt_shards_generate(self._h, C.cast(C.byref(cfg), C.POINTER(SynthCfg)), n_total))
+        return self
+
+    def load_soa(self, task_id, created_raw, due_raw, completed, overdue, creator_ref, creators):
+        n = len(created_raw)
+        ids = np.ascontiguousarray(task_id, dtype=np.uint8).reshape(n, 16) if n else np.zeros((0, 16), np.uint8)
+        cr = np.ascontiguousarray(created_raw, dtype=np.uint64)
+        du = np.ascontiguousarray(due_raw, dtype=np.uint64)
+        co = np.ascontiguousarray(completed, dtype=np.uint8)
+        ov = np.ascontiguousarray(overdue, dtype=np.uint8)
+        ref = np.ascontiguousarray(creator_ref, dtype=np.uint32)
+        off = np.zeros(len(creators) + 1, dtype=np.uint32)
+        off[1:] = np.cumsum([len(c) for c in creators], dtype=np.uint64) if creators else 0
+        pool = np.frombuffer(b"".join(creators) or b"\0", dtype=np.uint8).copy()
+        v = SoaView(n, _ptr(ids), _ptr(cr), _ptr(du), _ptr(co), _ptr(ov), _ptr(ref), len(creators), _ptr(off), _ptr(pool))
+        _check(lib().tt_shards_load_soa(self._h, C.byref(v)))
+        return self
+
+    def __len__(self):
+        n = C.c_int64(0)
+        _check(lib().tt_shards_row_count(self._h, C.byref(n)))
+        return n.value
+
+    def shard(self, g):
+        """-> (TaskTable of shard g, still owned by this object; global row of its first row)."""
+        h, first = C.c_void_p(0), C.c_uint64(0)
+        _check(lib().tt_shards_table(self._h, g, C.byref(h), C.byref(first)))
+        return TaskTable._borrowed(h, self.devices[g]), first.value
+
+    def get_yesterdays_due(self, mode, today=DEFAULT_TODAY):
+        h = C.c_void_p(0)
+        _check(lib().tt_shards_get_yesterdays_due(self._h, mode, today, C.byref(h)))
+        return GResult(h)
+
+    def get_due_on_or_before(self, mode, today=DEFAULT_TODAY):
+        h = C.c_void_p(0)
+        _check(lib().tt_shards_get_due_on_or_before(self._h, mode, today, C.byref(h)))
+        return GResult(h)
+
+    def sweep(self, mode, flags=0, today=DEFAULT_TODAY, run_at=DEFAULT_RUN_AT):
+        """-> (GResult in TaskId-range order, n_marked, threw)."""
+        h, marked = C.c_void_p(0), C.c_int64(0)
+        rc = _check(lib().tt_shards_sweep(self._h, mode, flags, today, run_at, C.byref(h), C.byref(marked)),
+                    allow=(TT_ERR_NOT_IMPLEMENTED,))
+        return GResult(h), marked.value, rc == TT_ERR_NOT_IMPLEMENTED
+
+    def mark_overdue(self, mode, ids16):
+        ids = np.ascontiguousarray(ids16, dtype=np.uint8).reshape(-1, 16)
+        marked, missing = C.c_int64(0), C.c_int64(0)
+        _check(lib().tt_shards_mark_overdue(self._h, mode, _ptr(ids), ids.shape[0], C.byref(marked), C.byref(missing)))
+        return marked.value, missing.value
+
+    def get_by_creator(self, created_by):
+        b = created_by.encode() if isinstance(created_by, str) else bytes(created_by)
+        h = C.c_void_p(0)
+        _check(lib().tt_shards_get_by_creator(self._h, b, len(b), C.byref(h)))
+        return GResult(h)
+
+    def get_by_id(self, task_id):
+        a = TaskTable._id(task_id)
+        h = C.c_void_p(0)
+        _check(lib().tt_shards_get_by_id(self._h, _ptr(a), C.byref(h)))
+        return GResult(h)
+
+    def insert_task(self, task_id, created_raw, due_raw, created_by):
+        """-> (shard, row inside that shard)."""
+        b = created_by.encode() if isinstance(created_by, str) else bytes(created_by)
+        a = TaskTable._id(task_id)
+        g, row = C.c_int32(-1), C.c_int64(-1)
+        _check(lib().tt_shards_insert_task(self._h, _ptr(a), created_raw, due_raw, b, len(b), C.byref(g), C.byref(row)))
+        return g.value, row.value
+
+    def _point(self, fn, task_id, *args):
+        f = C.c_int32(0)
+        a = TaskTable._id(task_id)
+        _check(fn(self._h, _ptr(a), *args, C.byref(f)))
+        return bool(f.value)
+
+    def update_task(self, task_id, due_raw):
+        return self._point(lib().tt_shards_update_task, task_id, due_raw)
+
+    def mark_completed(self, task_id):
+        return self._point(lib().tt_shards_mark_completed, task_id)
+
+    def delete_task(self, task_id):
+        return self._point(lib().tt_shards_delete_task, task_id)
+
+    def close(self):
+        if self._h:
+            lib().tt_shards_destroy(self._h)
             self._h = None
 
     def __del__(self):

@@ -38,15 +38,12 @@ def parse():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--rows", type=int, default=1_000_000_000, help="rows per GPU (weak) or in total (strong)")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
-    ap.add_argument("--exchange", default="push", choices=["push", "compact", "rows", "ids", "none"],
-                    help="how the shards' hit lists reach rank 0 (N > 1): push = the sweep's placement kernel stores "
-                         "the compact form (2-byte in-tile offsets + per-tile counts) straight into rank 0's buffer "
-                         "over NVLink (tt_sweep_push); compact / rows / ids = NCCL send/recv after the sweep of the "
-                         "compact form, the u32 row numbers, or rows + 16-byte TaskIds")
-    ap.add_argument("--exchange-mode", default="fixed", choices=["exact", "fixed"],
-                    help="exact: count all-gather, then count-sized send/recv; fixed: one grouped send/recv of "
-                         "capacity-sized buffers into fixed slots on rank 0")
-    ap.add_argument("--cpu-sample-rows", type=int, default=8_000_000)
+    ap.add_argument("--exchange", default="rows", choices=["rows", "ids"],
+                    help="what the shards' placement kernels store into rank 0's buffer over NVLink (N > 1, tt_exchange_*): "
+                         "rows = the compact row lists (2-byte in-tile offsets + per-tile counts), each shard keeping its "
+                         "TaskIds; ids = the 16-byte TaskIds as well")
+    ap.add_argument("--no-extra", action="store_true", help="N > 1: skip the strong-scaling / mixed / ids-at-root passes")
+    ap.add_argument("--cpu-sample-rows", type=int, default=10_000_000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--e2e-chunks", type=int, default=0, help="row ranges tt_tick_host pipelines over (0 = the library's 8)")
@@ -178,6 +175,116 @@ def run_reference(args):
 
 
 # --------------------------------------------------------------------------------------------------
+class ShardRun:
+    """One rank's shard of a synthetic table plus its end of the cross-shard exchange (C ABI: tt_exchange_*).
+    torch.distributed is used for the rendezvous only (the 64-byte handle of the root's buffer, barriers
+    between steps, max-over-ranks of the timings): the tick itself contains no collective."""
+
+    def __init__(self, pkg, torch, dist, dev, local, rank, world, n_total, first, n_rows, ex_flags, local_ids=True):
+        tt = pkg.tasktable
+        self.tt, self.torch, self.dist, self.rank, self.world, self.n_total, self.n_rows = tt, torch, dist, rank, world, n_total, n_rows
+        self.table = pkg.TaskTable(local).generate(pkg.default_cfg(SEED, n_total), first, n_rows)
+        self.nbytes = (n_rows + 7) // 8
+        self.pristine = torch.empty(self.nbytes, dtype=torch.uint8, device=dev)
+        tt._check(tt.lib().tt_snapshot_flags(self.table._h, None, self.pristine.data_ptr()))
+        self.cap = (int(n_rows * 0.032) + 65536 + 7) // 8 * 8
+        self.d_rows = torch.empty(self.cap, dtype=torch.int32, device=dev)
+        self.d_ids = torch.empty((self.cap, 16), dtype=torch.uint8, device=dev) if local_ids else None
+        self.stream = torch.cuda.Stream(device=dev)  # non-default: its handle is what the C ABI launches on
+        self.sx = pkg.ShardExchange(first, n_rows, self.cap, local, ex_flags) if world > 1 else None
+        self.ex = self.sx.ex if self.sx else None
+        self.first_rows = self.sx.first_rows if self.sx else [first]
+
+    def reset(self):
+        self.tt._check(self.tt.lib().tt_restore_flags(self.table._h, None, self.pristine.data_ptr()))
+
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def step(self, extra_flags):
+        """Queues this rank's tick; on the root also collects every shard's list.  -> collect ms (root) or None."""
+        tt = self.tt
+        flags = tt.SWEEP_MARK | tt.SWEEP_ASYNC | extra_flags
+        ids = self.d_ids.data_ptr() if self.d_ids is not None else None
+        if self.ex is None:
+            self.table.sweep_device(tt.MODE_STORE, flags, self.d_rows.data_ptr(), ids, self.cap, stream=self.stream.cuda_stream)
+            return None
+        self.ex.tick(self.table, tt.MODE_STORE, flags, stream=self.stream.cuda_stream, d_rows=self.d_rows.data_ptr(), d_ids=ids)
+        if self.rank == 0:
+            res = self.ex.collect(tt.ORDER_ROWS | tt.COLLECT_RELEASE, self.first_rows)
+            self.collected = res.count
+            res.free()
+            return self.ex.last_collect_ms()
+        return None
+
+    def timed(self, steps, warmup, clocks_for=None):
+        """-> dict(ms_per_step (max over ranks), hits (all shards), launches, kernel/sweep/gather medians of an
+        instrumented second pass, collect_ms on the root)."""
+        torch, tt = self.torch, self.tt
+        for _ in range(warmup):
+            self.reset()
+            self.barrier()
+            self.step(tt.SWEEP_NO_TIMING)
+            self.table.sweep_wait()
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+        hits = launches = 0
+        collect_ms = []
+        self.barrier()
+
+        def loop():
+            nonlocal hits, launches
+            for i in range(steps):
+                self.reset()     # untimed: the overdue plane goes back to its pre-tick state
+                self.barrier()
+                ev[i][0].record(self.stream)
+                c = self.step(tt.SWEEP_NO_TIMING)
+                ev[i][1].record(self.stream)
+                st, _ = self.table.sweep_wait()
+                hits = st.n_listed
+                launches += st.launches + (2 if c is not None else 0)
+                if c is not None:
+                    collect_ms.append(c)
+            self.barrier()
+
+        if clocks_for is not None:
+            with clocks_for:
+                loop()
+        else:
+            loop()
+        step_ms = [a.elapsed_time(b) for a, b in ev]
+        # per-kernel breakdown: a second, instrumented pass (the library records CUDA events between its
+        # kernels on the stream they run on); the headline steps above carry none
+        kms, sms, gms = [], [], []
+        for i in range(steps):
+            self.reset()
+            self.barrier()
+            self.step(0)
+            st, _ = self.table.sweep_wait()
+            kms.append(st.kernel_ms)
+            sms.append(st.sweep_ms)
+            gms.append(st.gather_ms)
+        self.barrier()
+        dev = self.pristine.device
+        total = torch.tensor([sum(step_ms)], dtype=torch.float64, device=dev)
+        hits_all = torch.tensor([hits], dtype=torch.int64, device=dev)
+        if self.world > 1:
+            self.dist.all_reduce(total, op=self.dist.ReduceOp.MAX)
+            self.dist.all_reduce(hits_all, op=self.dist.ReduceOp.SUM)
+        med = lambda xs: sorted(xs)[len(xs) // 2] if xs else None
+        return {"total_ms": float(total.item()), "ms_per_step": float(total.item()) / steps, "hits": int(hits_all.item()),
+                "hits_rank0": hits, "launches": launches, "kernel_ms": med(kms), "sweep_ms": med(sms), "gather_ms": med(gms),
+                "collect_ms": med(collect_ms), "step_ms_rank0": med(step_ms),
+                "collected": getattr(self, "collected", None)}
+
+    def close(self):
+        if self.sx is not None:
+            self.torch.cuda.synchronize()
+            self.sx.close()
+        self.table.close()
+
+
 def run_b200(args):
     import numpy as np
     import torch
@@ -203,93 +310,16 @@ def run_b200(args):
         n_total = args.rows
         first, last = pkg.shard_rows(n_total, world, rank)
         n_rows = last - first
-    plan = pkg.ShardPlan(n_total, world, rank)
-    cfg = pkg.default_cfg(SEED, n_total)
-    table = pkg.TaskTable(local).generate(cfg, first, n_rows)
-    nbytes = (n_rows + 7) // 8
-    pristine = torch.empty(nbytes, dtype=torch.uint8, device=dev)
-    tt._check(tt.lib().tt_snapshot_flags(table._h, None, pristine.data_ptr()))
-    cap = (int(n_rows * 0.032) + 65536 + 7) // 8 * 8
-    with_ids = args.exchange == "ids"
-    exchange = args.exchange if world > 1 else "none"
-    pex = None
-    if exchange == "push":
-        # every rank takes the same decision: the fused exchange needs the root's buffer mapped everywhere
-        try:
-            pex = pkg.PushExchange(plan, cap, local)
-            ok = 1
-        except Exception as e:  # noqa: BLE001 - e.g. CUDA IPC not permitted in this container
-            print(f"[rank {rank}] fused exchange unavailable ({e}); using the NCCL compact exchange", file=sys.stderr)
-            ok = 0
-        agree = torch.tensor([ok], dtype=torch.int32, device=dev)
-        dist.all_reduce(agree, op=dist.ReduceOp.MIN)
-        if int(agree.item()) == 0:
-            pex, exchange = None, "compact"
-    # the exchange owns the output buffers: on rank 0 the local hits land at offset 0 in place
-    ex = pkg.HitExchange(plan, cap, dev, with_ids=True, root_slots=(exchange != "push"))
-    d_rows, d_ids = ex.rows_all, ex.ids_all
-    ex.with_ids = with_ids
-    if exchange == "compact":
-        ex.enable_compact()
-    stream = torch.cuda.Stream(device=dev)  # non-default: its handle is what the C ABI launches on
-    torch.cuda.set_stream(stream)
-
-    def reset():
-        tt._check(tt.lib().tt_restore_flags(table._h, None, pristine.data_ptr()))
-
-    def step():
-        if exchange == "push":
-            st = pex.sweep(table, tt.MODE_STORE, tt.SWEEP_MARK, d_rows.data_ptr(), d_ids.data_ptr(),
-                           stream=stream.cuda_stream)
-            pex.fence()
-            return st, None
-        st, _ = table.sweep_device(tt.MODE_STORE, tt.SWEEP_MARK, d_rows.data_ptr(), d_ids.data_ptr(), cap,
-                                   stream=stream.cuda_stream)
-        out = None
-        if world > 1 and exchange == "compact":
-            table.pack_hits(d_rows.data_ptr(), st.n_stored, ex.off16_all.data_ptr(), ex.tile_counts_all.data_ptr(),
-                            stream=stream.cuda_stream)
-            out = ex.run_fixed_compact(st.n_stored)
-        elif world > 1 and exchange != "none":
-            out = ex.run_fixed(st.n_stored) if args.exchange_mode == "fixed" else ex.run(st.n_stored)
-        return st, out
+    with_root_ids = args.exchange == "ids"
+    run = ShardRun(pkg, torch, dist, dev, local, rank, world, n_total, first, n_rows,
+                   tt.EXCHANGE_IDS if with_root_ids else 0, local_ids=not with_root_ids)
+    clocks = ClockSampler(local)
+    head = run.timed(args.steps, args.warmup, clocks_for=clocks)
+    value = n_total * args.steps / (head["total_ms"] * 1e-3)
+    table, cap, nbytes, hits = run.table, run.cap, run.nbytes, head["hits_rank0"]
 
     def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    seen = 0
-    for w in range(args.warmup):
-        reset()
-        if w == args.warmup - 1 and world > 1 and exchange != "push":
-            ex.tune_send_cap(seen)  # the fixed exchange message: 1.1 x the largest count seen in warm-up
-        st_w, _ = step()
-        seen = max(seen, st_w.n_stored)
-    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    kernel_ms, sweep_ms, gather_ms, hits, launches = [], [], [], 0, 0
-    barrier()
-    with ClockSampler(local) as clocks:
-        for i in range(args.steps):
-            reset()          # untimed: the overdue plane goes back to its pre-tick state
-            barrier()
-            ev[i][0].record(stream)
-            st, out = step()
-            ev[i][1].record(stream)
-            kernel_ms.append(st.kernel_ms)
-            sweep_ms.append(st.sweep_ms)
-            gather_ms.append(st.gather_ms)
-            hits = st.n_listed
-            launches += st.launches + (1 if exchange == "compact" else 0)
-        barrier()
-    step_ms = [a.elapsed_time(b) for a, b in ev]
-    total_ms = torch.tensor([sum(step_ms)], dtype=torch.float64, device=dev)
-    hits_all = torch.tensor([hits], dtype=torch.int64, device=dev)
-    if world > 1:
-        dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
-        dist.all_reduce(hits_all, op=dist.ReduceOp.SUM)
-    total_ms = float(total_ms.item())
-    value = n_total * args.steps / (total_ms * 1e-3)
+        run.barrier()
 
     # ---- e2e: the reference-facing call with host buffers on both sides ----
     # tt_tick_host: both flag planes come from pinned host memory, the listed rows + TaskIds go back to
@@ -300,7 +330,7 @@ def run_b200(args):
         h_comp = torch.empty(nbytes, dtype=torch.uint8).pin_memory()
         h_over = torch.empty(nbytes, dtype=torch.uint8).pin_memory()
         tt._check(tt.lib().tt_snapshot_flags(table._h, h_comp.data_ptr(), None))
-        h_over.copy_(pristine)
+        h_over.copy_(run.pristine)
         h_rows = torch.empty(cap, dtype=torch.int32).pin_memory()
         h_ids = torch.empty((cap, 16), dtype=torch.uint8).pin_memory()
         e_steps = max(1, min(args.steps, 10))
@@ -344,12 +374,63 @@ def run_b200(args):
                "sequential": {"value": v_seq, "what": "the same bytes as separate calls: tt_restore_flags + tt_sweep + "
                                                       "tt_result_rows + tt_result_ids"}}
 
+    # ---- N > 1: the other driver-visible numbers, measured in the same run after the headline ----
+    extra = {}
+    if world > 1 and not args.no_extra:
+        run.close()
+        x_steps, x_warm = max(3, min(args.steps, 10)), max(3, min(args.warmup, 3))
+        if args.scaling == "weak" and not with_root_ids:
+            # the same weak-scaled tick with the 16-byte TaskIds ALSO delivered into the root's slots (fused into K3g)
+            r2 = ShardRun(pkg, torch, dist, dev, local, rank, world, n_total, first, n_rows, tt.EXCHANGE_IDS, local_ids=False)
+            m = r2.timed(x_steps, x_warm)
+            extra["ids_at_root_ms_per_step"] = m["ms_per_step"]
+            extra["ids_at_root_tasks_per_sec"] = n_total * x_steps / (m["total_ms"] * 1e-3)
+            r2.close()
+        # BASELINE.json config 3: ONE table of args.rows tasks sharded by TaskId range over the N GPUs
+        s_first, s_last = pkg.shard_rows(args.rows, world, rank)
+        r3 = ShardRun(pkg, torch, dist, dev, local, rank, world, args.rows, s_first, s_last - s_first, 0)
+        m = r3.timed(x_steps, x_warm)
+        extra["strong_ms_per_step"] = m["ms_per_step"]
+        extra["strong_tasks_per_sec"] = args.rows * x_steps / (m["total_ms"] * 1e-3)
+        extra["strong_n_total"] = args.rows
+        extra["strong_hits"] = m["hits"]
+        extra["strong_collect_ms"] = m["collect_ms"]
+        # BASELINE.json config 5: the tick, then 64 creator filters as one batch on every shard and the per-creator
+        # match counts summed over the shards (the one step of this path with a real reduction: NCCL all-reduce)
+        rng = np.random.default_rng(5)
+        names = [("user%07d@mail%d.example" % (k, k % 97)).encode() for k in rng.integers(0, 1_000_000, size=64)]
+        counts_dev = torch.zeros(64, dtype=torch.int64, device=dev)
+        counts_host = torch.zeros(64, dtype=torch.int64).pin_memory()
+        walls = []
+        for i in range(x_warm + x_steps):
+            r3.reset()
+            r3.barrier()
+            t0 = time.perf_counter()
+            r3.step(tt.SWEEP_NO_TIMING)
+            r3.table.sweep_wait()
+            rs = r3.table.get_by_creators(names)
+            for k, r in enumerate(rs):
+                counts_host[k] = r.count
+            counts_dev.copy_(counts_host, non_blocking=True)
+            dist.all_reduce(counts_dev)
+            r3.barrier()
+            dt = time.perf_counter() - t0
+            for r in rs:
+                r.free()
+            if i >= x_warm:
+                walls.append(dt * 1e3)
+        w = torch.tensor([sorted(walls)[len(walls) // 2]], dtype=torch.float64, device=dev)
+        dist.all_reduce(w, op=dist.ReduceOp.MAX)
+        extra["mixed_ms"] = float(w.item())
+        extra["mixed_creator_matches"] = int(counts_dev.sum().item())
+        r3.close()
+        run = None
+
     if rank == 0:
         peak, peak_src = peaks()
-        med = lambda xs: sorted(xs)[len(xs) // 2]
-        kms, sms, gms = med(kernel_ms), med(sweep_ms), med(gather_ms)
+        kms, sms, gms = head["kernel_ms"], head["sweep_ms"], head["gather_ms"]
         # Dominant kernel = K1 sweep_kernel: it reads 4.25 B/task and writes one u32 row per hit.
-        # K2+K3g (row order + TaskId gather) read 4 B + 16 B and write 4 B + 16 B per hit.
+        # K3g (row order + TaskId gather) reads 4 B + 16 B and writes 4 B + 16 B per hit.
         # The whole step is SURVEY.md 8(d)'s figure: 4.25 B/task + 36 B/hit (+ the 8 B/hit of the
         # intermediate list, which is not counted).
         sweep_bytes = n_rows * BYTES_PER_TASK + hits * 4.0
@@ -358,6 +439,8 @@ def run_b200(args):
         achieved = sweep_bytes / (sms * 1e-3) / 1e9
         step_gbs = step_bytes / (kms * 1e-3) / 1e9
         place_gbs = place_bytes / (gms * 1e-3) / 1e9 if gms > 0 else None
+        ms_per_step = head["ms_per_step"]
+        step_frac = step_bytes / (ms_per_step * 1e-3) / 1e9 / peak  # from the timed step, not from the kernel sum
         traffic = None
         tpath = os.path.join(ROOT, "profiles", "sweep_traffic.json")
         if os.path.exists(tpath):
@@ -367,49 +450,59 @@ def run_b200(args):
                     traffic = tj.get("dram_bytes_per_launch")
             except Exception:
                 pass
+        exchange = "none" if world == 1 else ("fused push of compact rows + TaskIds" if with_root_ids else "fused push of compact rows")
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": args.scaling,
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": args.scaling,
             "vs_baseline": None, "dtype": "u32", "data": "synthetic",
             "config": {
                 "workload": f"overdue sweep (cron tick, STORE semantics) over a synthetic {n_total}-task table, "
                             "config-5 mix: 5% due yesterday, 1% adversarial inexact, 50% completed",
-                "rows_per_gpu": n_rows, "n_total": n_total, "hits_per_step": int(hits_all.item()),
+                "rows_per_gpu": n_rows, "n_total": n_total, "hits_per_step": head["hits"],
                 "sharding": "TaskId range" if world > 1 else "single shard",
                 "exchange": exchange,
                 "l2": f"inputs {n_rows * BYTES_PER_TASK / 1e6:.0f} MB per step vs 126 MB L2; overdue plane rewritten between steps",
                 "reset": "overdue plane restored between steps outside the timed region (per-step CUDA events summed)",
+                "timed_region": "per step, CUDA events on the launching stream around the queued tick (tt_sweep_device / "
+                                "tt_exchange_tick with TT_SWEEP_ASYNC) and, on rank 0 at N > 1, the collect (device-side wait "
+                                "for every shard's epoch word + rebuilding the row numbers); max over ranks",
             },
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": traffic, "kernel": "tt::sweep_kernel<true,true,256,4> (K1, dominant)",
+                         "step_frac": step_frac, "step_achieved": step_frac * peak,
+                         "traffic": traffic,
+                         "traffic_source": "profiles/sweep_traffic.json: dram__bytes_read + dram__bytes_write of one ncu --set full "
+                                           "capture of this kernel at this size (not re-measured in this run)",
+                         "kernel": "tt::sweep_kernel<true,true,256,3,false> (K1, dominant)",
                          "kernel_ms": sms, "algorithmic_bytes": sweep_bytes,
                          "bytes_per_unit": "4.25 B/task + 4 B/hit", "peak_source": peak_src,
-                         "step": {"kernels": "K1 sweep_kernel + K2 tile_offsets_kernel + K3g place_group_kernel", "ms": kms,
+                         "step": {"kernels": "K1 sweep_kernel + K3g place_group_kernel + sweep_tail_kernel", "ms": kms,
                                   "algorithmic_bytes": step_bytes, "bytes_per_unit": "4.25 B/task + 36 B/hit",
-                                  "achieved": step_gbs, "frac": step_gbs / peak},
+                                  "achieved": step_gbs, "frac": step_gbs / peak,
+                                  "note": "frac here divides by the kernels' own time (instrumented pass); step_frac above "
+                                          "divides by ms_per_step"},
                          "place_kernels": {"ms": gms, "achieved": place_gbs,
                                            "frac": (place_gbs / peak) if place_gbs else None,
-                                           "note": "random 16 B TaskId gathers cost 64 B of DRAM each"}},
-            "gpu_launches": launches,
+                                           "note": "random 16 B TaskId gathers cost 64 B of DRAM and one row activation each"}},
+            "gpu_launches": head["launches"],
             "exchange": {"what": exchange,
-                         "transport": (None if world == 1 else "stores from the placement kernel into rank 0's HBM over "
-                                       "NVLink (CUDA IPC mapping) + one-word all-reduce" if exchange == "push"
-                                       else ex.transport),
-                         "mode": args.exchange_mode if world > 1 and exchange != "push" else None,
-                         "ms": med([a - b for a, b in zip(step_ms, kernel_ms)]),
-                         "note": "per-step time outside the three sweep kernels on rank 0: launch/sync overhead, "
-                                 "count all-gather and the hit id gather (N > 1)"},
+                         "transport": (None if world == 1 else "stores from the placement kernel into rank 0's HBM over NVLink "
+                                       "(CUDA IPC mapping), epoch word per shard, device-side wait on rank 0: no collective"),
+                         "collect_ms": head["collect_ms"], "rows_at_root": head["collected"],
+                         "ms": head["step_ms_rank0"] - kms,
+                         "note": "ms = rank 0's step time outside its own three kernels: launch gaps plus, at N > 1, waiting "
+                                 "for the slowest shard and rebuilding the row numbers (collect_ms, CUDA events on the root's "
+                                 "collect stream)"},
             "clocks": clocks.summary(),
         }
+        line.update(extra)
         if e2e:
             line["e2e"] = e2e
         if world == 1 and not args.no_cpu_baseline:
             base = cpu_reference_run(args.cpu_sample_rows, 3, 1)
             line["cpu_baseline"] = {k: base[k] for k in ("value", "unit", "cores", "kind", "sample", "parallel_soa")}
         print(json.dumps(line))
-    if pex:
-        pex.close()
-    table.close()
+    if run is not None:
+        run.close()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

@@ -107,7 +107,9 @@ int32_t tt_get_yesterdays_due(tt_table* t, int32_t mode, int64_t today_local_tic
 /* ITasksManager.MarkOverdueTasks (ITasksManager.cs:13; TasksStoreManager.cs:141-149): sets
  * IsOverDue for every listed TaskId that is in the table.  ids16 = 16*n bytes in canonical
  * order.  FAKE mode returns TT_ERR_NOT_IMPLEMENTED like the reference.  *n_missing counts ids
- * with no row (the reference would upsert a new document for them; this table does not). */
+ * with no live row: the reference's SaveStateAsync would create a document for them, which needs
+ * the whole record — call tt_upsert_task for those (the host mirrors do).  The table need not be
+ * in TaskId order: the TaskId index is rebuilt on the device when inserts have invalidated it. */
 int32_t tt_mark_overdue(tt_table* t, int32_t mode, const uint8_t* ids16, int64_t n, int64_t* n_marked,
                         int64_t* n_missing);
 
@@ -161,6 +163,12 @@ int32_t tt_get_by_id(tt_table* t, const uint8_t* id16, tt_result** out);
  * TasksStoreManager.cs:22-38): appends a pending task at the end of the list; *row = its row. */
 int32_t tt_insert_task(tt_table* t, const uint8_t* id16, uint64_t created_raw, uint64_t due_raw, const char* created_by_utf8,
                        int32_t len, int64_t* row);
+/* The state store's upsert, SaveStateAsync(key = TaskId.ToString(), whole record): what
+ * TasksStoreManager.MarkOverdueTasks does for every listed task (TasksStoreManager.cs:146-147) — a task
+ * with this id has every kernel-visible field overwritten (*existed = 1), otherwise the task is appended
+ * (*existed = 0); *row = its row.  The host mirrors use it for the ids tt_mark_overdue reports missing. */
+int32_t tt_upsert_task(tt_table* t, const uint8_t* id16, uint64_t created_raw, uint64_t due_raw, const char* created_by_utf8,
+                       int32_t len, int32_t is_completed, int32_t is_overdue, int64_t* row, int32_t* existed);
 /* ITasksManager.UpdateTask (ITasksManager.cs:10; FakeTasksManager.cs:87-100,
  * TasksStoreManager.cs:84-102): the due date is the only updated field a kernel reads. */
 int32_t tt_update_task(tt_table* t, const uint8_t* id16, uint64_t due_raw, int32_t* found);
@@ -231,9 +239,20 @@ typedef struct tt_sweep_stats {
                                        STORE mode still apply; with TT_SWEEP_MARK, run_at must lie after
                                        yesterday. */
 
+#define TT_SWEEP_NO_TIMING 4 /* OR it in: record no CUDA events between the kernels; the three timing fields of
+                                the stats stay 0 (the events cost a few microseconds of a tick)                 */
+
+#define TT_SWEEP_ASYNC 8     /* OR it in (tt_sweep_device, tt_sweep_push): queue the tick's kernels and return at
+                                once; h_stats is filled by tt_sweep_wait, which also reports TT_ERR_CAPACITY.  Until
+                                then no other call may be made on the table (another sweep is refused with
+                                TT_ERR_STATE).  The kernels report their outcome into mapped pinned memory, so the
+                                tick itself contains no copy and no host round trip.                            */
+
 int32_t tt_sweep_device(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_ticks,
                         int64_t run_at_utc_ticks, int64_t first_row, uint32_t* d_rows, void* d_ids, int64_t cap,
                         tt_sweep_stats* h_stats, void* stream);
+/* Completes a tick queued with TT_SWEEP_ASYNC: waits for its stream, fills h_stats. */
+int32_t tt_sweep_wait(tt_table* t, tt_sweep_stats* h_stats);
 
 /* ---- the tick for a caller whose task state and results live in HOST memory -------------------
  * The whole of Svc/Controllers/ScheduledTasksManagerController.cs:19-46 as tt_sweep does it, but with
@@ -407,6 +426,104 @@ int32_t tt_json_offsets(tt_json* j, uint64_t* dst);
 int32_t tt_save_snapshot(tt_table* t, const char* path);
 int32_t tt_load_snapshot(tt_table* t, const char* path);
 
+/* ---- the table sharded by TaskId range over several GPUs ------------------------
+ * The reference registers ONE manager (Api/Program.cs:13) and its methods return ONE ordered list
+ * (Api/Services/ITasksManager.cs:7,14); these entry points give the same contract over G shards.
+ *
+ * Layer 1, tt_exchange_*: one exchange object per shard.  The root shard's exchange owns a receive
+ * buffer in its GPU's HBM with one slot per shard; a shard in another process maps it through the
+ * 64-byte handle (CUDA IPC), a shard in the same process attaches to the root's object.
+ * tt_exchange_tick is the shard's cron tick (Svc/Controllers/ScheduledTasksManagerController.cs:19-46)
+ * whose placement kernel stores the result straight into the shard's slot — per tile a hit count and
+ * a list offset, per hit a 13-bit in-tile offset and, if the exchange was made for them, the TaskId
+ * (TT_EXCHANGE_IDS) and TaskCreatedOn (TT_EXCHANGE_CREATED) — over NVLink when the slot is on another
+ * GPU; its last kernel publishes the tick's epoch in the slot.  No collective is involved: on the root,
+ * tt_exchange_collect waits for the epoch words ON THE DEVICE (bounded by TT_SHARD_TIMEOUT_MS,
+ * default 10 s: a shard that never ticks gives TT_ERR_STATE, not a hung GPU), lays the slots end to
+ * end and rebuilds the row numbers.  Every shard must tick once per collect; expected_epoch is the
+ * number of ticks made so far (tt_exchange_epoch).  A shard does not overwrite its slot before the
+ * root has released the previous epoch (tt_exchange_release, or TT_COLLECT_RELEASE).
+ *
+ * order = TT_ORDER_ROWS: the shards' row-ordered lists end to end — shards are TaskId ranges, so this
+ * is the order of FakeTasksManager.GetYesterdaysDueTasks (Api/Services/FakeTasksManager.cs:107-112)
+ * over a table kept in TaskId order.  The result is a view of the exchange's buffers until it is first
+ * read; read or free it before the next tick.  order = TT_ORDER_CREATED_ASC: OrderBy(TaskCreatedOn)
+ * over the hits of all shards (Api/Services/TasksStoreManager.cs:136), stable, ties in TaskId-range
+ * order: one radix sort of the pushed ticks on the root.  first_rows[r] = global row of shard r's
+ * first row (what the result's row numbers are relative to). */
+typedef struct tt_exchange tt_exchange;
+typedef struct tt_gresult tt_gresult;
+#define TT_EXCHANGE_IDS 1
+#define TT_EXCHANGE_CREATED 2
+#define TT_ORDER_ROWS 0
+#define TT_ORDER_CREATED_ASC 1
+#define TT_COLLECT_RELEASE 0x100 /* OR into order (TT_ORDER_ROWS only): release the epoch inside the collect; the
+                                    result's TaskIds must then be read before any shard's next tick reaches K3g  */
+int32_t tt_exchange_create_root(int32_t device, int32_t world, int64_t cap_per_shard, int64_t max_tiles_per_shard,
+                                int32_t flags, tt_exchange** out, tt_peer_handle* handle /* may be NULL */);
+int32_t tt_exchange_attach(int32_t device, int32_t rank, int32_t world, int64_t cap_per_shard, int64_t max_tiles_per_shard,
+                           int32_t flags, const tt_peer_handle* handle, tt_exchange** out);
+int32_t tt_exchange_attach_local(tt_exchange* root, int32_t device, int32_t rank, tt_exchange** out);
+int32_t tt_exchange_destroy(tt_exchange* ex);
+int32_t tt_exchange_slot_bytes(const tt_exchange* ex, uint64_t* bytes);
+/* flags: TT_SWEEP_* as for tt_sweep_device (TT_SWEEP_ASYNC: finish with tt_sweep_wait on the table).
+ * d_rows / d_ids: the shard's own copy of its list (uint32[cap], 16 B x cap; device memory), either
+ * may be NULL.  TT_ERR_CAPACITY if the shard's hits do not fit in cap_per_shard (the slot then holds a
+ * subset). */
+int32_t tt_exchange_tick(tt_exchange* ex, tt_table* t, int32_t mode, int32_t flags, int64_t today_local_ticks,
+                         int64_t run_at_utc_ticks, uint32_t* d_rows, void* d_ids, tt_sweep_stats* h_stats, void* stream);
+int32_t tt_exchange_epoch(const tt_exchange* ex, uint64_t* epoch);
+int32_t tt_exchange_collect(tt_exchange* root, int32_t order, const uint64_t* first_rows, uint64_t expected_epoch,
+                            tt_gresult** out);
+int32_t tt_exchange_release(tt_exchange* root, uint64_t epoch);
+/* Device time of the last collect on this root (wait for the slowest shard + rebuilding the rows). */
+int32_t tt_exchange_last_collect_ms(const tt_exchange* root, float* ms);
+
+int32_t tt_gresult_count(const tt_gresult* r, int64_t* n);
+int32_t tt_gresult_shard_counts(const tt_gresult* r, int64_t* counts, int32_t n_shards);
+int32_t tt_gresult_rows(tt_gresult* r, uint64_t* out);   /* global row numbers, result order            */
+int32_t tt_gresult_ids(tt_gresult* r, uint8_t* out16);   /* TaskIds, 16 bytes each, result order        */
+int32_t tt_gresult_digest(tt_gresult* r, uint64_t* xor_id_hi, uint64_t* xor_id_lo, uint64_t* sum_rows);
+int32_t tt_gresult_free(tt_gresult* r);
+
+/* Layer 2, tt_shards_*: the whole ITasksManager (Api/Services/ITasksManager.cs:5-15) over G shards
+ * driven from ONE process — what a C# host registers as its singleton.  devices[g] holds shard g (a
+ * device may appear more than once).  Shard g owns the g-th TaskId range: equal-width ranges of the
+ * 128-bit id space for tt_shards_load_soa and for tables filled by inserts; for tt_shards_generate
+ * the g-th equal share of the synthetic rows (whose ids grow with the row).  Global row numbers count
+ * the shards' rows end to end.  The list calls size the exchange with a count-only pass (K1 alone)
+ * and grow it on demand.  Lists are ordered as the reference orders them: GetYesterdaysDueTasks by
+ * TaskCreatedOn in STORE mode (TasksStoreManager.cs:136) and in TaskId-range order in FAKE mode;
+ * GetTasksByCreator by TaskCreatedOn descending (FakeTasksManager.cs:70, TasksStoreManager.cs:66);
+ * ties keep TaskId-range order.  The single-row methods go to the shard that owns the id's range. */
+typedef struct tt_shards tt_shards;
+int32_t tt_shards_create(const int32_t* devices, int32_t n_shards, tt_shards** out);
+int32_t tt_shards_destroy(tt_shards* s);
+int32_t tt_shards_count(const tt_shards* s, int32_t* n_shards);
+/* Shard `shard`'s table (still owned by s; for state access such as tt_snapshot_flags) and the global
+ * row number of its first row.  Either out pointer may be NULL. */
+int32_t tt_shards_table(tt_shards* s, int32_t shard, tt_table** out, uint64_t* first_row);
+int32_t tt_shards_generate(tt_shards* s, const tt_synth_cfg* cfg, uint64_t n_total);
+int32_t tt_shards_generate_payload(tt_shards* s, const tt_synth_cfg* cfg, uint64_t n_total);
+int32_t tt_shards_load_soa(tt_shards* s, const tt_soa_view* v);
+int32_t tt_shards_row_count(tt_shards* s, int64_t* n);
+int32_t tt_shards_get_yesterdays_due(tt_shards* s, int32_t mode, int64_t today_local_ticks, tt_gresult** out);
+int32_t tt_shards_get_due_on_or_before(tt_shards* s, int32_t mode, int64_t today_local_ticks, tt_gresult** out);
+/* The cron tick over all shards (tt_sweep; flags = 0 or TT_SWEEP_DUE_ON_OR_BEFORE): *out lists what
+ * GetYesterdaysDueTasks returned, in TaskId-range order; FAKE mode with survivors returns
+ * TT_ERR_NOT_IMPLEMENTED with the list produced and nothing changed. */
+int32_t tt_shards_sweep(tt_shards* s, int32_t mode, int32_t flags, int64_t today_local_ticks, int64_t run_at_utc_ticks,
+                        tt_gresult** out, int64_t* n_marked);
+int32_t tt_shards_mark_overdue(tt_shards* s, int32_t mode, const uint8_t* ids16, int64_t n, int64_t* n_marked,
+                               int64_t* n_missing);
+int32_t tt_shards_get_by_creator(tt_shards* s, const char* utf8, int32_t len, tt_gresult** out);
+int32_t tt_shards_get_by_id(tt_shards* s, const uint8_t* id16, tt_gresult** out);
+int32_t tt_shards_insert_task(tt_shards* s, const uint8_t* id16, uint64_t created_raw, uint64_t due_raw,
+                              const char* created_by_utf8, int32_t len, int32_t* shard, int64_t* local_row);
+int32_t tt_shards_update_task(tt_shards* s, const uint8_t* id16, uint64_t due_raw, int32_t* found);
+int32_t tt_shards_mark_completed(tt_shards* s, const uint8_t* id16, int32_t* found);
+int32_t tt_shards_delete_task(tt_shards* s, const uint8_t* id16, int32_t* found);
+
 /* ---- sweep without any allocation ----------------------------------------------------------
  * This entry point has no counterpart in the reference.  It exists for hosts that cannot let a
  * library allocate device memory while they are serving: a process that handed the whole GPU to
@@ -425,8 +542,10 @@ int32_t tt_load_snapshot(tt_table* t, const char* path);
  *          arrays in the same layout: padded to a multiple of 8192 rows, padding rows with
  *          due_code 0xFFFFFFFF and zero flag bits).  cols->device must own the memory.
  * d_rows : uint32[cap] device memory, d_ids: 16*cap bytes or NULL; d_rows == NULL counts only.
- * Results, error codes and the meaning of TT_ERR_CAPACITY are those of tt_sweep_device; the
- * timing fields of h_stats stay 0 (timing would need events).
+ * Results, error codes, the flags (TT_SWEEP_MARK, TT_SWEEP_DUE_ON_OR_BEFORE) and the meaning of
+ * TT_ERR_CAPACITY are those of tt_sweep_device; the timing fields of h_stats stay 0 (timing would
+ * need events).  The call does not lock the table the columns came from: fetch the view again
+ * after anything that can move the columns (tt_insert_task growing the table, a reload).
  *
  * The first call on each device looks up the device address of the fixed array; make that first
  * call before any stream capture is started.  All calls share the array and it keeps whatever

@@ -64,29 +64,52 @@ def main():
         ok2 = cdev.tolist() == counts and bool((g2 == glob).all())
         print("compact exchange", "agrees" if ok2 else "DIFFERS")
         assert ok2
-    # the fused exchange: a fresh copy of the shard, swept by tt_sweep_push straight into rank 0's buffer
+    # the fused exchange behind the C ABI (tt_exchange_*): a fresh copy of the shard, ticked straight into rank 0's
+    # buffer with TaskIds and creation times; rank 0 waits for the epoch words on the device
     table_p = pkg.TaskTable(local).generate(cfg, plan.first_row, plan.n_rows)
-    pex = pkg.PushExchange(plan, cap, local)
-    p_rows = torch.empty(pex.cap, dtype=torch.int32, device=dev)
-    p_ids = torch.empty((pex.cap, 16), dtype=torch.uint8, device=dev)
-    for tick in range(2):  # the second tick finds nothing: the slots must be overwritten, not appended to
-        stp = pex.sweep(table_p, tt.MODE_STORE, tt.SWEEP_MARK, p_rows.data_ptr(), p_ids.data_ptr(), stream=stream.cuda_stream)
-        pex.fence()
-        torch.cuda.synchronize()
-        ok3 = True
-        if tick == 0:
-            ok3 = (stp.n_stored == st.n_stored and bool((p_rows[: stp.n_stored] == d_rows[: st.n_stored]).all())
-                   and bool((p_ids[: stp.n_stored] == d_ids[: st.n_stored]).all()))
-            if rank == 0:
-                ok3 = ok3 and pex.counts() == counts and bool((pex.global_rows(stream.cuda_stream) == glob).all())
-        else:
-            ok3 = stp.n_listed == 0 and (rank != 0 or pex.counts() == [0] * world)
-        if rank == 0:
-            print("fused push exchange tick", tick, "agrees" if ok3 else "DIFFERS")
-        assert ok3
+    sx = pkg.ShardExchange(plan.first_row, plan.n_rows, cap, local, tt.EXCHANGE_IDS | tt.EXCHANGE_CREATED)
+    p_rows = torch.empty(sx.cap, dtype=torch.int32, device=dev)
+    p_ids = torch.empty((sx.cap, 16), dtype=torch.uint8, device=dev)
+    for tick in range(3):  # the later ticks find nothing: the slots must be overwritten, not appended to
         dist.barrier()
+        stp, _ = sx.tick(table_p, tt.MODE_STORE, tt.SWEEP_MARK | tt.SWEEP_ASYNC, stream=stream.cuda_stream,
+                         d_rows=p_rows.data_ptr(), d_ids=p_ids.data_ptr())
+        ok3 = True
+        if rank == 0:
+            res = sx.collect(tt.ORDER_ROWS if tick != 1 else tt.ORDER_CREATED_ASC)
+            if tick == 0:
+                ok3 = (res.shard_counts()[:world] == counts and bool((torch.from_numpy(res.rows().astype(np.int64)) == glob.cpu()).all())
+                       and bool((torch.from_numpy(res.ids()) == gids.cpu()).all()))
+            else:
+                ok3 = res.count == 0
+            res.free()
+            sx.release()
+        stp, _ = table_p.sweep_wait()
+        if tick == 0:
+            ok3 = ok3 and (stp.n_stored == st.n_stored and bool((p_rows[: stp.n_stored] == d_rows[: st.n_stored]).all())
+                           and bool((p_ids[: stp.n_stored] == d_ids[: st.n_stored]).all()))
+        else:
+            ok3 = ok3 and stp.n_listed == 0
+        if rank == 0:
+            print("fused exchange (tt_exchange_*) tick", tick, "agrees" if ok3 else "DIFFERS")
+        assert ok3
     assert table_p.count_flags() == table.count_flags()
-    pex.close()
+    # the cross-shard OrderBy(TaskCreatedOn) on an unmarked copy: same hits, creation times ascending
+    table_q = pkg.TaskTable(local).generate(cfg, plan.first_row, plan.n_rows)
+    dist.barrier()
+    sx.tick(table_q, tt.MODE_STORE, tt.SWEEP_LIST_ONLY)
+    if rank == 0:
+        res = sx.collect(tt.ORDER_CREATED_ASC)
+        rows_o = res.rows().astype(np.int64)
+        okq = res.count == sum(counts) and bool((np.sort(rows_o) == glob.cpu().numpy()).all())
+        idmap = {int(r): i for i, r in enumerate(glob.cpu().numpy())}
+        okq = okq and bool((res.ids() == gids.cpu().numpy()[[idmap[int(r)] for r in rows_o]]).all())
+        print("cross-shard order", "agrees" if okq else "DIFFERS")
+        assert okq
+        res.free()
+        sx.release()
+    sx.close()
+    table_q.close()
     table_p.close()
     ok = True
     if rank == 0:

@@ -227,3 +227,66 @@ def test_snapshot_carries_the_payload(oracle, tmp_path):
     assert bare2.get_by_creator(who).to_json() == bare.get_by_creator(who).to_json()
     for t in (table, again, bare, bare2):
         t.close()
+
+
+def test_mark_overdue_after_creates_with_fresh_guids(oracle):
+    """The reference's everyday flow: CreateNewTask with Guid.NewGuid() ids (which break the table's TaskId
+    order), then the cron job — GET the list, POST it back to MarkOverdueTasks (TasksStoreManager.cs:141-149).
+    tt_mark_overdue has to find the new rows too (it rebuilds the TaskId index), pass over deleted rows, and
+    report ids it does not hold."""
+    rng = np.random.default_rng(5)
+    n0 = 30_000
+    cfg = oracle.default_cfg(1234, n0, n_creators=30)
+    ot = oracle.OracleTable()
+    ot.add_synth(cfg, 0, n0)
+    table = load_from_oracle(ot)
+    fresh = []
+    for i in range(400):
+        tid = uuid.UUID(int=int.from_bytes(rng.bytes(16), "big"), version=4).bytes
+        created = (TODAY - int(rng.integers(1, 10**9))) | (1 << 62)
+        due = YDAY if i % 2 == 0 else TODAY
+        who = b"creator%d@example.org" % (i % 7)
+        assert table.insert_task(tid, created, due, who) == ot.add(tid, "t", who, "a", created, due)
+        fresh.append(tid)
+    # one of the new tasks is deleted again: its row keeps the id as a tombstone
+    gone = fresh[10]
+    assert table.delete_task(gone) and ot.delete_task(tt.MODE_STORE, gone)
+    listed = ot.get_yesterdays_due(tt.MODE_STORE)
+    res = table.get_yesterdays_due(tt.MODE_STORE)
+    assert res.rows().tolist() == listed.tolist() and (listed >= n0).sum() == 199
+    ids = res.ids()
+    unknown = uuid.uuid4().bytes
+    post = np.concatenate([ids, np.frombuffer(unknown + gone, dtype=np.uint8).reshape(2, 16)])
+    marked, missing = table.mark_overdue(tt.MODE_STORE, post)
+    threw, want_missing = ot.mark_overdue(tt.MODE_STORE, post)
+    assert not threw and (marked, missing) == (len(listed), 2) and want_missing == 2
+    # (the oracle's store upserted two documents for the unknown ids; they are not rows of the list)
+    c, o = ot.flags()
+    gc, go = table.flags_bytes()
+    assert (gc == c).all() and (go == o).all()
+    # a second insert drops the index again; marking still works
+    extra = uuid.uuid4().bytes
+    table.insert_task(extra, TODAY | (1 << 62), YDAY, b"late@example.org")
+    assert table.mark_overdue(tt.MODE_STORE, np.frombuffer(extra, dtype=np.uint8)) == (1, 0)
+    assert table.get_yesterdays_due(tt.MODE_STORE).count == 0
+    table.close()
+
+
+def test_manager_mirror_mark_overdue_upserts_unknown_tasks(oracle):
+    """MarkOverdueTasks is an upsert of the whole record (SaveStateAsync, TasksStoreManager.cs:147): a listed task
+    the store does not hold is created from the caller's copy, with IsOverDue = true."""
+    import importlib
+
+    pkg = importlib.import_module("aca-dotnet-workshop_b200")
+    mgr = pkg.GpuTasksManager([], mode=tt.MODE_STORE)
+    a = mgr.CreateNewTask("kept", "ann@x.io", "bob@x.io", YDAY)
+    listed = mgr.GetYesterdaysDueTasks()
+    assert [t.TaskId for t in listed] == [a]
+    ghost = pkg.TaskModel(uuid.uuid4(), "ghost", "zed@x.io", (TODAY - 77) | (1 << 62), YDAY, "amy@x.io", True, False)
+    mgr.MarkOverdueTasks(listed + [ghost])
+    assert mgr.last_mark_missing == 1 and ghost.IsOverDue
+    back = mgr.GetTaskById(ghost.TaskId)
+    assert back == ghost and mgr.GetTaskById(a).IsOverDue
+    assert [t.TaskName for t in mgr.GetTasksByCreator("zed@x.io")] == ["ghost"]
+    assert mgr.GetYesterdaysDueTasks() == []
+    mgr.table.close()

@@ -67,6 +67,44 @@ def test_static_sweep_matches_the_ordinary_entry_point_twice(oracle):
     table.close()
 
 
+def test_static_sweep_honours_the_backlog_flag(oracle):
+    """TT_SWEEP_DUE_ON_OR_BEFORE through the fixed-array entry point: the same list, marks and refusals as
+    tt_sweep_device gives for that flag (it was silently ignored before round 2)."""
+    import torch
+
+    n, cap = 2_000_000, tt.STATIC_MAX_HITS
+    ref_table, table = make_table(oracle, n, 4242), make_table(oracle, n, 4242)
+    rows = torch.zeros(cap, dtype=torch.int32, device="cuda")
+    ids = torch.zeros((cap, 16), dtype=torch.uint8, device="cuda")
+    flags = tt.SWEEP_LIST_ONLY | tt.SWEEP_DUE_ON_OR_BEFORE
+    exact, _ = ref_table.sweep_device(tt.MODE_STORE, tt.SWEEP_LIST_ONLY, None, None, 0)
+    a, _ = ref_table.sweep_device(tt.MODE_STORE, flags, rows.data_ptr(), ids.data_ptr(), cap)
+    want_rows, want_ids = fetch(rows, ids, a.n_stored)
+    assert a.n_stored > 4 * exact.n_listed  # the backlog is far larger than the exact match
+    for call in range(2):
+        rows.zero_()
+        ids.zero_()
+        b, _ = table.sweep_static(tt.MODE_STORE, flags, rows.data_ptr(), ids.data_ptr(), cap)
+        got_rows, got_ids = fetch(rows, ids, b.n_stored)
+        assert (b.n_listed, b.n_stored, b.n_marked) == (a.n_listed, a.n_stored, 0), call
+        assert (got_rows == want_rows).all() and (got_ids == want_ids).all(), call
+    mflags = tt.SWEEP_MARK | tt.SWEEP_DUE_ON_OR_BEFORE
+    am, _ = ref_table.sweep_device(tt.MODE_STORE, mflags, rows.data_ptr(), None, cap)
+    bm, _ = table.sweep_static(tt.MODE_STORE, mflags, rows.data_ptr(), None, cap)
+    assert (bm.n_listed, bm.n_stored, bm.n_marked) == (am.n_listed, am.n_stored, am.n_marked) and bm.n_marked == a.n_stored
+    assert (table.snapshot_flags()[1] == ref_table.snapshot_flags()[1]).all()
+    fa, _ = ref_table.sweep_device(tt.MODE_FAKE, flags, None, None, 0)
+    fb, _ = table.sweep_static(tt.MODE_FAKE, flags, None, None, 0)
+    assert fa.n_listed == fb.n_listed > a.n_listed
+    # a marking backlog sweep with the clock behind yesterday is refused by both
+    for call in (ref_table.sweep_device, table.sweep_static):
+        with pytest.raises(tt.TaskTableError) as e:
+            call(tt.MODE_STORE, mflags, rows.data_ptr(), None, cap, run_at=tt.DEFAULT_TODAY - 2 * tt.TICKS_PER_DAY)
+        assert e.value.code == tt.TT_ERR_ARG
+    ref_table.close()
+    table.close()
+
+
 def test_static_sweep_capacity_behaviour_matches(oracle):
     import torch
 
