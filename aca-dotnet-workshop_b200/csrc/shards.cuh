@@ -112,8 +112,8 @@ struct SlotLayout {
 // Rebuilds shard-local row numbers for every slot at once: grid (tiles / 8, world), one warp per
 // tile.  rows_out is the concatenated list (slot r starts at meta->base[r]).
 __global__ void __launch_bounds__(256) shard_expand_kernel(const unsigned char* base, SlotLayout lay, uint32_t max_tiles,
-                                                            const CollectMeta* meta, uint32_t* rows_out) {
-  const uint32_t r = blockIdx.y;
+                                                            const CollectMeta* meta, uint32_t* rows_out, uint32_t first_slot) {
+  const uint32_t r = blockIdx.y + first_slot;  // first_slot = 1: the root's own placement kernel wrote slot 0's rows in place
   const uint32_t t = blockIdx.x * 8 + (threadIdx.x >> 5);
   if (t >= max_tiles) return;
   const unsigned char* slot = base + (size_t)r * lay.bytes;

@@ -211,7 +211,10 @@ class ShardRun:
         if self.ex is None:
             self.table.sweep_device(tt.MODE_STORE, flags, self.d_rows.data_ptr(), ids, self.cap, stream=self.stream.cuda_stream)
             return None
-        self.ex.tick(self.table, tt.MODE_STORE, flags, stream=self.stream.cuda_stream, d_rows=self.d_rows.data_ptr(), d_ids=ids)
+        # every shard keeps its own row list (and TaskIds); the root's placement kernel writes its rows straight
+        # into the end-to-end list the collect builds, so it needs no second copy
+        own_rows = None if self.rank == 0 else self.d_rows.data_ptr()
+        self.ex.tick(self.table, tt.MODE_STORE, flags, stream=self.stream.cuda_stream, d_rows=own_rows, d_ids=ids)
         if self.rank == 0:
             res = self.ex.collect(tt.ORDER_ROWS | tt.COLLECT_RELEASE, self.first_rows)
             self.collected = res.count

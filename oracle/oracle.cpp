@@ -1194,6 +1194,73 @@ void orc_stream_sweep(const tt_synth_cfg* cfg, uint64_t first_row, uint64_t n, i
   }
 }
 
+// The creator filter at full size (BASELINE.json config 4: 100 M rows, 1 M creators): for every query the
+// rows whose TaskCreatedBy equals it — FakeTasksManager.cs:70 `t.TaskCreatedBy.Equals(createdBy)`, ordinal
+// UTF-16 equality (TasksStoreManager.cs:56-59 asks the store for the same EQ) — summarised order-free: count,
+// XOR of TaskIds, sum / min / max of the row numbers.  Rows are generated on the fly; each row's creator
+// STRING is built and looked up among the query strings (no shortcut through the generator's index).
+typedef struct orc_creator_out {
+  int64_t count;
+  uint64_t xor_id_hi, xor_id_lo;
+  uint64_t sum_rows;
+  int64_t min_row, max_row;  // -1 when there is no match
+} orc_creator_out;
+
+void orc_stream_creators(const tt_synth_cfg* cfg, uint64_t first_row, uint64_t n, const char* pool, const uint32_t* off,
+                         int32_t nq, int32_t threads, orc_creator_out* out) {
+  if (threads < 1) threads = 1;
+  std::unordered_map<std::u16string, std::vector<int32_t>> index;  // a query string may be asked more than once
+  for (int32_t q = 0; q < nq; ++q) index[Utf8ToUtf16(pool + off[q], (int32_t)(off[q + 1] - off[q]))].push_back(q);
+  std::vector<std::vector<orc_creator_out>> part(threads);
+  std::vector<std::thread> workers;
+  for (int th = 0; th < threads; ++th) {
+    workers.emplace_back([&, th]() {
+      std::vector<orc_creator_out> o(nq);
+      for (auto& x : o) {
+        memset(&x, 0, sizeof x);
+        x.min_row = x.max_row = -1;
+      }
+      const uint64_t lo = n * th / threads, hi = n * (th + 1) / threads;
+      char buf[48];
+      std::u16string who;
+      for (uint64_t i = lo; i < hi; ++i) {
+        const tt_synth_row r = tt_synth_make(cfg, first_row + i);
+        const int len = tt_synth_creator(r.creator, buf);
+        who.assign(buf, buf + len);  // the generator's creator strings are ASCII
+        auto it = index.find(who);
+        if (it == index.end()) continue;
+        for (int32_t q : it->second) {
+          orc_creator_out& x = o[q];
+          x.count++;
+          x.xor_id_hi ^= r.id_hi;
+          x.xor_id_lo ^= r.id_lo;
+          x.sum_rows += i;
+          if (x.min_row < 0) x.min_row = (int64_t)i;
+          x.max_row = (int64_t)i;
+        }
+      }
+      part[th] = std::move(o);
+    });
+  }
+  for (auto& w : workers) w.join();
+  for (int32_t q = 0; q < nq; ++q) {
+    orc_creator_out t;
+    memset(&t, 0, sizeof t);
+    t.min_row = t.max_row = -1;
+    for (int th = 0; th < threads; ++th) {
+      const orc_creator_out& x = part[th][q];
+      if (x.count == 0) continue;
+      t.count += x.count;
+      t.xor_id_hi ^= x.xor_id_hi;
+      t.xor_id_lo ^= x.xor_id_lo;
+      t.sum_rows += x.sum_rows;
+      if (t.min_row < 0) t.min_row = x.min_row;  // the threads' ranges ascend
+      t.max_row = x.max_row;
+    }
+    out[q] = t;
+  }
+}
+
 // ---- "best-effort CPU" context number: the same sweep over SoA columns on all cores -------
 // (not the reference's algorithm layout; reported beside the LINQ-faithful number)
 typedef struct orc_soa {

@@ -128,6 +128,8 @@ def lib():
     L.orc_serialize_documents.argtypes = [vp, vp, i64, i32, i32, vp, i64, vp]
     L.orc_serialize_documents.restype = i64
     L.orc_stream_sweep.argtypes = [C.POINTER(SynthCfg), u64, u64, i32, i64, i64, i32, C.POINTER(StreamOut)]
+    L.orc_stream_creators.argtypes = [C.POINTER(SynthCfg), u64, u64, C.c_char_p, C.c_void_p, i32, i32, C.c_void_p]
+    L.orc_stream_creators.restype = None
     L.orc_soa_create.argtypes = [C.POINTER(SynthCfg), u64, i64, i32]
     L.orc_soa_create.restype = vp
     L.orc_soa_destroy.argtypes = [vp]
@@ -318,6 +320,23 @@ def stream_sweep(cfg, first_row, n, mode, today=DEFAULT_TODAY, run_at=DEFAULT_RU
     lib().orc_stream_sweep(C.byref(cfg), first_row, n, mode, today, run_at, threads or (os.cpu_count() or 1),
                            C.byref(out))
     return out
+
+
+class CreatorOut(C.Structure):
+    _fields_ = [("count", C.c_int64), ("xor_id_hi", C.c_uint64), ("xor_id_lo", C.c_uint64), ("sum_rows", C.c_uint64),
+                ("min_row", C.c_int64), ("max_row", C.c_int64)]
+
+
+def stream_creators(cfg, first_row, n, queries, threads=None):
+    """GetTasksByCreator for every query over rows generated on the fly (no table is stored): per query the
+    order-free summary (count, XOR of TaskIds, sum / min / max of the rows).  queries: list of bytes."""
+    qs = [q.encode() if isinstance(q, str) else bytes(q) for q in queries]
+    off = np.zeros(len(qs) + 1, dtype=np.uint32)
+    off[1:] = np.cumsum([len(q) for q in qs], dtype=np.uint64) if qs else 0
+    pool = b"".join(qs) or b"\0"
+    out = (CreatorOut * len(qs))()
+    lib().orc_stream_creators(C.byref(cfg), first_row, n, pool, _ptr(off), len(qs), threads or (os.cpu_count() or 1), out)
+    return list(out)
 
 
 class SoaTable:

@@ -412,3 +412,28 @@ def test_backlog_extension_known_answers(oracle):
     rows, n_over, threw = ot.backlog(oracle.MODE_STORE, mark=True)
     assert not threw and n_over == 7 and ot.flags()[1].tolist() == [1, 1, 1, 1, 0, 1, 1, 0, 0, 0, 1, 1]
     assert ot.backlog(oracle.MODE_STORE)[0].size == 0                                      # idempotent
+
+
+def test_streaming_creator_filter_agrees_with_the_list_oracle(oracle):
+    """orc_stream_creators (the full-size checker of the GPU creator filter) against GetTasksByCreator over a
+    stored List<TaskModel> of the same synthetic rows."""
+    n = 300_000
+    cfg = oracle.default_cfg(0x5EED0003, n, n_creators=3000)
+    ot = oracle.OracleTable()
+    ot.add_synth(cfg, 0, n)
+    ids, _, _ = ot.export()
+    queries = [ot.created_by(i) for i in (0, 5, 77, 5)] + [b"nobody@example.org", ot.created_by(9).upper()]
+    for threads in (1, 3):
+        out = oracle.stream_creators(cfg, 0, n, queries, threads=threads)
+        for q, o in zip(queries, out):
+            want = ot.get_by_creator(oracle.MODE_FAKE, q)
+            assert o.count == len(want)
+            if len(want):
+                sel = ids[want]
+                hi = int(np.bitwise_xor.reduce(np.ascontiguousarray(sel[:, :8]).view(">u8").ravel().astype(np.uint64)))
+                lo = int(np.bitwise_xor.reduce(np.ascontiguousarray(sel[:, 8:]).view(">u8").ravel().astype(np.uint64)))
+                assert (o.xor_id_hi, o.xor_id_lo) == (hi, lo)
+                assert (o.sum_rows, o.min_row, o.max_row) == (int(want.astype(np.uint64).sum()), want.min(), want.max())
+            else:
+                assert (o.min_row, o.max_row) == (-1, -1)
+    assert out[4].count == out[5].count == 0 and out[1].count == out[3].count > 50
