@@ -12,7 +12,7 @@ all: $(LIB) oracle/liboracle.so $(PKG)/host/tasks_manager_demo
 $(LIB): $(CSRC)/tasktable.cu $(HDRS)
 	$(NVCC) $(NVFLAGS) -shared -o $@ $(CSRC)/tasktable.cu 2> $(CSRC)/ptxas.log || (cat $(CSRC)/ptxas.log; false)
 
-oracle/liboracle.so: oracle/oracle.cpp include/tt_synth.h
+oracle/liboracle.so: oracle/oracle.cpp include/tt_synth.h include/tt_bmp_defined.h
 	g++ -O2 -std=c++17 -fPIC -shared -pthread -o $@ oracle/oracle.cpp
 
 $(PKG)/host/tasks_manager_demo: $(wildcard $(PKG)/host/*.cpp $(PKG)/host/*.hpp) include/tasktable.h

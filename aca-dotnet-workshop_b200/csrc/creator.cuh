@@ -65,7 +65,7 @@ __device__ __forceinline__ void creator_confirm(uint32_t row, uint32_t q, int64_
   if ((int64_t)row >= n) return;  // padding row
   atomicAdd(out.counters + 1, 1ull);
   const uint32_t ref = creator_ref[row];
-  if (ref == 0xFFFFFFFFu) return;  // deleted row (point.cuh)
+  if (ref >= 0xFFFFFFFEu) return;  // deleted row (point.cuh), or a task whose TaskCreatedBy is null: no string equals it
   const uint32_t off = creator_off[ref];
   const uint32_t len = creator_off[ref + 1] - off;
   const uint32_t qoff = qs.off[q];

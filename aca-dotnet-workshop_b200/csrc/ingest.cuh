@@ -16,7 +16,7 @@
 //     machine's local time, Kind Local); no suffix = Kind Unspecified; fractions beyond 7 digits
 //     are truncated;
 //   * strings: every JSON escape including \uXXXX surrogate pairs, unescaped IN PLACE in the
-//     device copy of the text (unescaping only shrinks); null reads as "".
+//     device copy of the text (unescaping only shrinks); null stays null (the ref becomes kRefNull).
 // A document may carry one leading '[' or ',' and one trailing ',' or ']' so that a JSON array
 // split at its element boundaries (the offsets K6 hands out) loads as it is.
 // Anything else marks the document bad: the load reports the first bad document and changes
@@ -512,7 +512,9 @@ __global__ void __launch_bounds__(128) doc_parse_kernel(uint8_t* text, const uin
     }
     if (m == 1 || m == 2 || m == 5) {
       const int c = m == 1 ? 0 : m == 2 ? 1 : 2;
-      if (lit_eq(p, end, "null", 4)) { slen[c] = 0; sstart[c] = base; p += 4; continue; }
+      // null stays null (flag bits 4..6 of the document's flag byte); a later repeat of the member overwrites it
+      if (lit_eq(p, end, "null", 4)) { slen[c] = 0; sstart[c] = base; flags |= 16u << c; p += 4; continue; }
+      flags &= ~(16u << c);
       if (*p != '"') { status = kDocType; continue; }
       p = read_string_inplace(const_cast<uint8_t*>(p) + 1, end, &sstart[c], &slen[c]);
       if (!p) status = kDocString;
@@ -594,6 +596,12 @@ __global__ void doc_fill_kernel(DocCols d, int64_t n, uint32_t* due_code, uint32
     completed[i >> 5] = cw;
     overdue[i >> 5] = ow;
   }
+}
+
+// A string member that was null in the document: its ref becomes the null sentinel (json.cuh kRefNull).
+__global__ void doc_null_refs_kernel(const uint8_t* flags, int member, int64_t n, uint32_t* ref) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n && (flags[i] & (16u << member))) ref[i] = 0xFFFFFFFEu;
 }
 
 // rows whose TaskId is not above the previous row's (0 everywhere = the table is in TaskId order)

@@ -23,6 +23,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "../../include/tt_bmp_defined.h"
 #include "sweep.cuh"
 
 namespace tt {
@@ -71,13 +72,18 @@ __device__ __forceinline__ void st_hint_u64(uint64_t* p, uint64_t v, uint64_t po
   asm volatile("st.global.L2::cache_hint.u64 [%0], %1, %2;" : : "l"(p), "l"(v), "l"(pol) : "memory");
 }
 
+// BMP code points System.Text.Encodings.Web treats as defined (ForbidUndefinedCharacters): generated from an
+// independent copy of the Unicode Character Database, include/tt_bmp_defined.h.
+TT_BMP_TABLE kBmpDefined[2048] = {TT_BMP_DEFINED_WORDS};
+
 // ---- escaping one Unicode scalar -----------------------------------------------------------
 // Returns how a scalar is written: 0 = as is, 1 = backslash + *short_ch, 2 = \uXXXX,
 // 3 = \uXXXX\uXXXX (surrogate pair).  System.Text.Json's published rules (assumptions of record in
 // DESIGN.md §7): both encoders escape controls, '"' and '\\' and every supplementary-plane
 // scalar; Default additionally escapes the HTML-sensitive ASCII characters and everything
-// outside Basic Latin; UnsafeRelaxed keeps BMP text except controls, separators (Zs other than
-// U+0020, Zl, Zp), private-use and non-characters.
+// outside Basic Latin; UnsafeRelaxed keeps a BMP code point only if the encoder's table calls it
+// defined — a letter, mark, number, punctuation or symbol, or U+0020: controls, format characters,
+// the other separators, surrogates, private use and unassigned code points are escaped.
 __device__ __forceinline__ int json_escape_kind(uint32_t cp, int flavor, uint8_t* short_ch) {
   if (cp < 0x20) {
     switch (cp) {
@@ -99,12 +105,8 @@ __device__ __forceinline__ int json_escape_kind(uint32_t cp, int flavor, uint8_t
     return 0;
   }
   if (cp >= 0x10000) return 3;
-  if (flavor == kJsonDocument || cp <= 0x9F) return 2;
-  if (cp == 0xA0 || cp == 0x1680 || (cp >= 0x2000 && cp <= 0x200A) || cp == 0x2028 || cp == 0x2029 || cp == 0x202F ||
-      cp == 0x205F || cp == 0x3000)
-    return 2;
-  if ((cp >= 0xD800 && cp <= 0xF8FF) || (cp >= 0xFDD0 && cp <= 0xFDEF) || cp >= 0xFFFE) return 2;
-  return 0;
+  if (flavor == kJsonDocument) return 2;
+  return (kBmpDefined[cp >> 5] >> (cp & 31)) & 1u ? 0 : 2;
 }
 
 __device__ __forceinline__ uint8_t hex_upper(uint32_t x) { return (uint8_t)(x < 10 ? '0' + x : 'A' + x - 10); }
@@ -405,6 +407,13 @@ __device__ uint32_t datetime_write(uint64_t raw, int32_t local_offset_min, uint8
 constexpr int kJsonThreads = 128;            // records per CTA
 constexpr int kJsonStageBytes = 44 * 1024;   // shared-memory staging per CTA (5 CTAs per SM)
 
+// A string member that holds null (a C# string may: `"taskName":null` in a stored document) is written
+// as the literal null, as JsonSerializer does.  Its ref in the row's string column is kRefNull; in a
+// record's plan it travels as an entry with this word offset and length 2 (= "null" minus the two quotes
+// the surrounding literals carry).
+constexpr uint32_t kRefNull = 0xFFFFFFFEu;
+constexpr uint32_t kNullWordOff = 0xFFFFFFFFu;
+
 struct JsonRecord {
   uint64_t created, due;
   EscEntry s[3];
@@ -435,6 +444,9 @@ __device__ __forceinline__ JsonRecord json_gather(const JsonParams& p, int64_t i
       const uint64_t e = ld_hint_u64(reinterpret_cast<const uint64_t*>(p.entry[c] + k[c]), keep);
       r.s[c].word_off = (uint32_t)e;
       r.s[c].len = (uint32_t)(e >> 32);
+    } else if (k[c] == kRefNull) {
+      r.s[c].word_off = kNullWordOff;
+      r.s[c].len = 2;
     }
   }
   return r;
@@ -510,6 +522,7 @@ __device__ __forceinline__ EscHead esc_prefetch(const uint32_t* pool, EscEntry e
   EscHead h;
   h.q0 = h.q1 = make_uint4(0, 0, 0, 0);
   const uint4* q = reinterpret_cast<const uint4*>(pool + e.word_off);
+  if (e.word_off == kNullWordOff) return h;
   if (e.len > 0) h.q0 = ld_hint_v4(q, keep);
   if (e.len > 16) h.q1 = ld_hint_v4(q + 1, keep);
   return h;
@@ -533,6 +546,21 @@ __device__ __forceinline__ uint8_t* put_esc(uint8_t* o, const uint32_t* pool, Es
   return o + e.len;
 }
 
+// One string member and the literal that follows it.  The literals carry the quotes (`...":"` before,
+// `","next":"` after); a null member takes the opening quote back and skips the closing one.
+__device__ __forceinline__ uint8_t* put_member(uint8_t* o, const uint32_t* pool, EscEntry e, const EscHead& h, uint64_t keep,
+                                               int next_lit, int next_len) {
+  if (e.word_off == kNullWordOff) {
+    o[-1] = 'n';
+    o[0] = 'u';
+    o[1] = 'l';
+    o[2] = 'l';
+    return put_lit(o + 3, next_lit + 1, next_len - 1);
+  }
+  o = put_esc(o, pool, e, h, keep);
+  return put_lit(o, next_lit, next_len);
+}
+
 __device__ uint8_t* json_write_record(const JsonParams& p, const JsonRecord& r, uint4 id, int64_t i, uint8_t* o,
                                       const EscHead& h0, const EscHead& h1, const EscHead& h2, uint64_t keep) {
   *o++ = i == 0 ? '[' : ',';
@@ -546,16 +574,14 @@ __device__ uint8_t* json_write_record(const JsonParams& p, const JsonRecord& r, 
     *o++ = hex_lower(byte & 15);
   }
   o = put_lit(o, 11, 14);
-  o = put_esc(o, p.esc_pool[0], r.s[0], h0, keep);
-  o = put_lit(o, 25, 19);
-  o = put_esc(o, p.esc_pool[1], r.s[1], h1, keep);
-  o = put_lit(o, 44, 19);
+  o = put_member(o, p.esc_pool[0], r.s[0], h0, keep, 25, 19);
+  o = put_member(o, p.esc_pool[1], r.s[1], h1, keep, 44, 19);
   o += datetime_write(r.created, p.local_offset_min, o);
   o = put_lit(o, 63, 17);
   o += datetime_write(r.due, p.local_offset_min, o);
   o = put_lit(o, 80, 20);
-  o = put_esc(o, p.esc_pool[2], r.s[2], h2, keep);
-  o = put_lit(o, 100, 16);
+  o = put_member(o, p.esc_pool[2], r.s[2], h2, keep, 100, 16);
+
   o = r.completed ? put_lit(o, 129, 4) : put_lit(o, 133, 5);
   o = put_lit(o, 116, 13);
   o = r.overdue ? put_lit(o, 129, 4) : put_lit(o, 133, 5);

@@ -5,6 +5,7 @@
 // usable every call fails with TT_ERR_CUDA.
 
 #include <cuda_runtime.h>
+#include <unistd.h>
 
 #include <algorithm>
 #include <cstdarg>
@@ -12,6 +13,7 @@
 #include <cstring>
 #include <atomic>
 #include <memory>
+#include <condition_variable>
 #include <mutex>
 #include <new>
 #include <string>
@@ -138,6 +140,22 @@ struct tt_table {
   uint32_t* d_qcount = nullptr;  // per-query match counts (kMaxQueries words) + pinned mirror
   uint32_t* h_qcount = nullptr;
   tt_op_stats last_op = {};
+  // Request combining for GetTasksByCreator: request threads that arrive while a table pass is running queue
+  // their query; whoever finds no pass running takes everything queued (up to kMaxQueries) as ONE batch —
+  // one read of the hash column answers all of them — and hands each waiter its own result.
+  struct CreatorRequest {
+    const char* utf8;
+    int32_t len;
+    tt_result* out = nullptr;
+    int32_t rc = TT_OK;
+    std::string err;
+    bool done = false;
+  };
+  std::mutex cq_mu;
+  std::condition_variable cq_cv;
+  std::vector<CreatorRequest*> cq;
+  bool cq_busy = false;
+  int64_t cq_batches = 0, cq_requests = 0;  // passes made / requests answered through the queue
   tt::SortScratch sort;  // K5 radix sort buffers, grow-only
   bool creator_smem_opted = false, json_smem_opted = false;  // large dynamic shared memory enabled on this device
 
@@ -1401,11 +1419,67 @@ int32_t tt_get_by_creators(tt_table* t, const char* const* utf8, const int32_t* 
   return TT_OK;
 }
 
+// ITasksManager.GetTasksByCreator for one request thread.  The reference's manager is a singleton shared by all
+// request threads (Api/Program.cs:13), so many of these calls arrive at once: they are combined (see
+// tt_table::CreatorRequest) instead of queueing behind each other for a table pass each.
 int32_t tt_get_by_creator(tt_table* t, const char* utf8, int32_t len, tt_result** out) {
-  if (!out) return fail(TT_ERR_ARG, "bad argument");
-  const char* q[1] = {utf8 ? utf8 : ""};
-  const int32_t l[1] = {len};
-  return tt_get_by_creators(t, q, l, 1, out);
+  if (!t || !out) return fail(TT_ERR_ARG, "bad argument");
+  *out = nullptr;
+  if (len < 0 || (len > 0 && !utf8)) return fail(TT_ERR_ARG, "bad query");
+  tt_table::CreatorRequest me;
+  me.utf8 = utf8 ? utf8 : "";
+  me.len = len;
+  std::unique_lock<std::mutex> lk(t->cq_mu);
+  t->cq.push_back(&me);
+  while (!me.done) {
+    if (t->cq_busy) {
+      t->cq_cv.wait(lk);
+      continue;
+    }
+    // nobody is scanning: this thread takes what is queued (its own request included unless the queue is
+    // longer than a batch) and answers all of it with one pass
+    t->cq_busy = true;
+    const size_t take = std::min<size_t>(t->cq.size(), (size_t)tt::kMaxQueries);
+    std::vector<tt_table::CreatorRequest*> batch(t->cq.begin(), t->cq.begin() + take);
+    t->cq.erase(t->cq.begin(), t->cq.begin() + take);
+    lk.unlock();
+    std::vector<const char*> q(take);
+    std::vector<int32_t> l(take);
+    std::vector<tt_result*> res(take, nullptr);
+    for (size_t i = 0; i < take; ++i) {
+      q[i] = batch[i]->utf8;
+      l[i] = batch[i]->len;
+    }
+    const int32_t rc = tt_get_by_creators(t, q.data(), l.data(), (int32_t)take, res.data());
+    const std::string err = rc ? g_err : std::string();
+    lk.lock();
+    for (size_t i = 0; i < take; ++i) {
+      batch[i]->out = res[i];
+      batch[i]->rc = rc;
+      batch[i]->err = err;
+      batch[i]->done = true;
+    }
+    t->cq_batches += 1;
+    t->cq_requests += (int64_t)take;
+    t->cq_busy = false;
+    t->cq_cv.notify_all();
+  }
+  lk.unlock();
+  if (me.rc) {
+    g_err = me.err;
+    return me.rc;
+  }
+  *out = me.out;
+  return TT_OK;
+}
+
+// How often concurrent GetTasksByCreator calls shared a table pass: *requests answered by *passes passes.
+int32_t tt_creator_combining_stats(tt_table* t, int64_t* passes, int64_t* requests) {
+  if (!t) return fail(TT_ERR_ARG, "null argument");
+  std::lock_guard<std::mutex> lk(t->cq_mu);
+  if (passes) *passes = t->cq_batches;
+  if (requests) *requests = t->cq_requests;
+  return TT_OK;
 }
 
 int32_t tt_last_op_stats(tt_table* t, tt_op_stats* out) {

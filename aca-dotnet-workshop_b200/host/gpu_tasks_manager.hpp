@@ -365,7 +365,7 @@ class GpuTasksManager : public ITasksManager {
     for (int64_t i = 0; i < n; ++i) {
       memcpy(out[i].TaskId.data(), &ids[16 * i], 16);
       out[i].TaskName = names_[rows[i]];
-      out[i].TaskCreatedBy = creators_[ref[i]];
+      out[i].TaskCreatedBy = ref[i] < creators_.size() ? creators_[ref[i]] : std::string();  // 0xFFFFFFFE: a null string
       out[i].TaskCreatedOn.dateData = created[i];
       out[i].TaskDueDate.dateData = due[i];
       out[i].TaskAssignedTo = assignees_[rows[i]];

@@ -94,6 +94,8 @@ class GpuTasksManager:
         return out
 
     def _creator_name(self, ref):
+        if ref == 0xFFFFFFFE:  # the stored document said "taskCreatedBy": null
+            return None
         return self._creators[ref].decode("utf-8")
 
     # ITasksManager.cs:8

@@ -47,7 +47,7 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--e2e-chunks", type=int, default=0, help="row ranges tt_tick_host pipelines over (0 = the library's 8)")
-    ap.add_argument("--workload", default="sweep", choices=["sweep", "sweep10m", "creator", "mixed", "json", "ingest"],
+    ap.add_argument("--workload", default="sweep", choices=["sweep", "sweep10m", "creator", "creator-threads", "mixed", "json", "ingest"],
                     help="sweep = the headline (BASELINE.json metric); the others are the remaining configs of "
                          "SURVEY.md 8(d): sweep10m = config 2, creator = config 4, mixed = config 5 (per GPU)")
     return ap.parse_args()
@@ -602,6 +602,70 @@ def run_extra(args):
                              "frac": n * 8 / (sc * 1e-3) / 1e9 / peak, "kernel": "tt::creator_scan_kernel<true>",
                              "algorithmic_bytes": n * 8, "note": "8 B/row hash column; inputs 800 MB >> L2"},
                 "batch": batch}
+        print(json.dumps(line))
+        table.close()
+        return
+
+    if args.workload == "creator-threads":
+        # GetTasksByCreator from 64 request threads at once against the config-4 table (the reference's manager is a
+        # singleton shared by every ASP.NET request thread, Api/Program.cs:13), beside one thread issuing the same
+        # queries one after the other.  Concurrent calls are combined into shared table passes by the library.
+        n, n_creators = 100_000_000, 1_000_000
+        cfg = pkg.default_cfg(0x5EED0003, n, n_creators=n_creators)
+        table = pkg.TaskTable(0).generate(cfg, 0, n)
+        rng = np.random.default_rng(64)
+        names = [("user%07d@mail%d.example" % (k, k % 97)).encode() for k in rng.integers(0, n_creators, size=64 * 50)]
+
+        def issue(qs, lat):
+            for q in qs:
+                t0 = time.perf_counter()
+                r = table.get_by_creator(q)
+                lat.append((time.perf_counter() - t0) * 1e3)
+                r.free()
+
+        issue(names[:20], [])  # warm-up
+        lat1 = []
+        t0 = time.perf_counter()
+        issue(names[:400], lat1)
+        single = 400 / (time.perf_counter() - t0)
+        p0, r0 = table.creator_combining_stats()
+        lats = [[] for _ in range(64)]
+        ths = [threading.Thread(target=issue, args=(names[i * 50:(i + 1) * 50], lats[i])) for i in range(64)]
+        t0 = time.perf_counter()
+        for th in ths:
+            th.start()
+        for th in ths:
+            th.join()
+        wall = time.perf_counter() - t0
+        p1, r1 = table.creator_combining_stats()
+        lat64 = sorted(x for l in lats for x in l)
+        lat1.sort()
+        pct = lambda xs, p: xs[min(len(xs) - 1, int(len(xs) * p))]
+        cpu = None
+        if not args.no_cpu_baseline:
+            from oracle import oracle as orc
+
+            sample, sample_creators = 10_000_000, 100_000
+            ot = orc.OracleTable()
+            ot.add_synth(orc.default_cfg(0x5EED0003, sample, n_creators=sample_creators), 0, sample)
+            qs = [("user%07d@mail%d.example" % (k, k % 97)).encode() for k in rng.integers(0, sample_creators, size=5)]
+            t0 = time.perf_counter()
+            for q in qs:
+                ot.get_by_creator(orc.MODE_FAKE, q)
+            cdt = (time.perf_counter() - t0) / len(qs)
+            cpu = {"value": sample / cdt, "unit": "rows/s", "cores": 1, "kind": "port", "ms_per_query": cdt * 1e3,
+                   "sample": f"FakeTasksManager.GetTasksByCreator (LINQ Where + OrderByDescending, restated) over a {sample}-task "
+                             f"List<TaskModel> with {sample_creators} creators, 1 thread"}
+            ot.close()
+        line = {"metric": "creator_queries_per_sec", "workload": "config 4 table (100M tasks, 1M creators): GetTasksByCreator from "
+                "64 request threads x 50 queries, beside 1 thread x 400 queries", "value": 64 * 50 / wall, "unit": "queries/s",
+                "threads": 64, "p50_ms": pct(lat64, 0.5), "p99_ms": pct(lat64, 0.99),
+                "table_passes": p1 - p0, "requests": r1 - r0, "requests_per_pass": (r1 - r0) / max(1, p1 - p0),
+                "single_thread": {"value": single, "unit": "queries/s", "p50_ms": pct(lat1, 0.5), "p99_ms": pct(lat1, 0.99)},
+                "speedup_vs_single_thread": 64 * 50 / wall / single,
+                "note": "Python request threads (ctypes releases the GIL inside the call); concurrent calls are combined "
+                        "into one batch per table pass (tt_creator_combining_stats)",
+                "cpu_baseline": cpu}
         print(json.dumps(line))
         table.close()
         return

@@ -18,7 +18,8 @@
  *
  * Thread safety: one tt_table may be shared by all request threads (the reference registers
  * its manager as a singleton, Api/Program.cs:13); calls on the same table are serialised by
- * an internal lock.  tt_result objects are independent of the lock once returned.
+ * an internal lock, except that concurrent tt_get_by_creator calls are COMBINED into shared table
+ * passes (tt_creator_combining_stats).  tt_result objects are independent of the lock once returned.
  *
  * There is no CPU fallback: every operation runs as CUDA kernels on the table's device and
  * fails with TT_ERR_CUDA if no device is usable.
@@ -133,6 +134,12 @@ int32_t tt_sweep_backlog(tt_table* t, int32_t mode, int64_t today_local_ticks, i
  * TasksStoreManager.cs:54-69): ordinal byte-exact match of TaskCreatedBy (64-bit hash scan,
  * then the candidate's string is compared), descending TaskCreatedOn, ties in row order. */
 int32_t tt_get_by_creator(tt_table* t, const char* utf8, int32_t len, tt_result** out);
+/* The reference's manager is a singleton shared by every ASP.NET request thread (Api/Program.cs:13), so
+ * tt_get_by_creator calls arrive concurrently.  They do not queue for one table pass each: calls that
+ * arrive while a pass is running are combined, and the next pass answers all of them at once (the batch
+ * kernel of tt_get_by_creators reads the hash column once for up to 1024 creators).  These counters say
+ * how many passes answered how many requests.  No reference counterpart. */
+int32_t tt_creator_combining_stats(tt_table* t, int64_t* passes, int64_t* requests);
 
 /* The same for a batch of creators in ONE pass over the table (the hash column is read once for
  * all of them): out[i] receives the result of query i, nq <= 1024.  No reference counterpart as
@@ -265,7 +272,10 @@ int32_t tt_sweep_wait(tt_table* t, tt_sweep_stats* h_stats);
  * memory: pageable buffers make the copies synchronous and the stages stop overlapping.
  * The rows arrive in ascending row order (tt_sweep's order).  stats->n_listed / n_stored / n_marked as
  * in tt_sweep_device; the timing fields are sums over the chunks.  TT_ERR_CAPACITY if the hits do not
- * fit in cap (the first cap are delivered; a marking tick has marked all it listed). */
+ * fit in cap (the first cap are delivered; a marking tick has marked all it listed — the device's overdue
+ * plane is then ahead of the caller's: read it back with tt_snapshot_flags before the next tick uploads
+ * the host copy again).  On every return, error returns included, no transfer to or from the caller's
+ * buffers is still running. */
 int32_t tt_tick_host(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_ticks, int64_t run_at_utc_ticks,
                      const uint8_t* h_completed_bits, const uint8_t* h_overdue_bits, uint32_t* h_rows, uint8_t* h_ids16,
                      int64_t cap, int32_t chunks, tt_sweep_stats* stats);
@@ -339,7 +349,7 @@ int32_t tt_peer_free(int32_t device, void* d_ptr);
  * reference's default, `= string.Empty`); rows added later by tt_insert_task print "" until
  * tt_set_task_strings gives them their strings. */
 typedef struct tt_strings_view {
-  const uint32_t* ref;  /* one entry per row: index into the dictionary, 0xFFFFFFFF = empty string */
+  const uint32_t* ref;  /* one entry per row: index into the dictionary, 0xFFFFFFFF = empty string, 0xFFFFFFFE = null */
   uint32_t n_strings;   /* dictionary entries                                                      */
   const uint32_t* off;  /* n_strings + 1 byte offsets into pool                                    */
   const uint8_t* pool;  /* UTF-8 (must be well formed; checked when the first JSON is produced)    */
@@ -353,7 +363,8 @@ int32_t tt_generate_payload(tt_table* t, const tt_synth_cfg* cfg, uint64_t first
 
 /* TaskName / TaskAssignedTo of ONE task, for the single-row methods that set them: CreateNewTask
  * (ITasksManager.cs:9; after tt_insert_task) and UpdateTask (ITasksManager.cs:10; FakeTasksManager.cs:92-94,
- * TasksStoreManager.cs:91-93).  A length of -1 leaves that member as it is.  New strings are appended to the
+ * TasksStoreManager.cs:91-93).  A length of -1 leaves that member as it is, -2 sets it to null (a C# string may
+ * hold null; it is then written as the JSON literal null).  New strings are appended to the
  * column's dictionary (the column is created if the table had no payload).  *found as in tt_update_task. */
 int32_t tt_set_task_strings(tt_table* t, const uint8_t* id16, const char* task_name, int32_t name_len,
                             const char* assigned_to, int32_t assigned_len, int32_t* found);
@@ -400,7 +411,10 @@ int32_t tt_last_json_stats(tt_table* t, tt_json_stats* out);
  * local_offset_min: the machine's UTC offset, used for dates that carry an
  * offset (System.Text.Json turns them into local time, Kind = Local).
  * If any document is malformed the call fails with TT_ERR_ARG, stats->first_bad / first_bad_reason
- * say which and why, and the table stays empty.  A null string member loads as "". */
+ * say which and why, and the table stays empty.  A string member that is null in its document stays
+ * null (a missing one is "", TaskModel.cs:6,7,10): it prints as null again, and a task whose
+ * TaskCreatedBy is null matches no creator (the store's EQ filter; TT_FIELD_CREATOR_REF gives
+ * 0xFFFFFFFE for it). */
 typedef struct tt_ingest_stats {
   int64_t n_docs;
   int64_t text_bytes;

@@ -43,6 +43,7 @@
 #include <vector>
 
 #include "../include/tt_synth.h"
+#include "../include/tt_bmp_defined.h"
 
 namespace {
 
@@ -183,6 +184,10 @@ struct TaskModel {
   std::u16string TaskAssignedTo;
   bool IsCompleted = false;
   bool IsOverDue = false;
+  // A C# string may hold null: the initialisers (= string.Empty, TaskModel.cs:6,7,10) only apply when a
+  // document does not mention the member; `"taskName":null` deserialises to null and serialises back as null.
+  // Bit 0 TaskName, bit 1 TaskCreatedBy, bit 2 TaskAssignedTo (the std::u16string is then empty and unused).
+  uint8_t null_strings = 0;
   int64_t row = -1;  // insertion index; test bookkeeping, not a reference field
   bool deleted = false;  // bookkeeping: removed from the list / store
 };
@@ -248,8 +253,10 @@ struct FakeTasksManager {
   // :68-72  Where(TaskCreatedBy.Equals(createdBy)).OrderByDescending(TaskCreatedOn).ToList()
   TaskList GetTasksByCreator(const std::u16string& createdBy) const {
     TaskList tasksList;
-    for (TaskModel* t : _tasksList)
+    for (TaskModel* t : _tasksList) {
+      if (t->null_strings & 2) throw NullReferenceException();  // t.TaskCreatedBy.Equals(...) on a null string
       if (OrdinalEquals(t->TaskCreatedBy, createdBy)) tasksList.push_back(t);
+    }
     // OrderByDescending is a stable sort: equal keys keep source order
     std::stable_sort(tasksList.begin(), tasksList.end(), [](const TaskModel* a, const TaskModel* b) {
       return a->TaskCreatedOn.Ticks() > b->TaskCreatedOn.Ticks();
@@ -330,8 +337,10 @@ struct TasksStoreManager {
   // :54-69
   std::vector<TaskModel> GetTasksByCreator(const std::u16string& createdBy) const {
     std::vector<TaskModel> tasksList;
-    for (const TaskModel* t : *docs)
+    for (const TaskModel* t : *docs) {
+      if (t->null_strings & 2) continue;  // the store's EQ on a JSON null matches no string
       if (OrdinalEquals(t->TaskCreatedBy, createdBy)) tasksList.push_back(*t);
+    }
     std::stable_sort(tasksList.begin(), tasksList.end(), [](const TaskModel& a, const TaskModel& b) {
       return a.TaskCreatedOn.Ticks() > b.TaskCreatedOn.Ticks();                       // :66 OrderByDescending
     });
@@ -354,10 +363,12 @@ struct TasksStoreManager {
 //   * Default allows only Basic Latin (U+0020..U+007E) minus  " & ' + < > ` \  ; '\' is "\\", the
 //     quote is ";
 //   * UnsafeRelaxed writes \" and \\, and allows every other BMP code point that the encoder
-//     treats as defined: not a control (Cc), not a space separator other than U+0020 (Zs), not
-//     U+2028 / U+2029, not a surrogate, private-use or non-character code point.  Code points
-//     unassigned in the Unicode version .NET 9 carries are also refused by the real encoder;
-//     that table is not restated here (PARITY UNPINNED for such text).
+//     treats as defined (TextEncoderSettings.ForbidUndefinedCharacters): general category letter,
+//     mark, number, punctuation or symbol, or U+0020 — so controls (Cc), format characters (Cf),
+//     the other separators (Zs, Zl, Zp), surrogates, private use and unassigned code points are
+//     escaped.  The table is include/tt_bmp_defined.h, generated from Python's unicodedata
+//     (scripts/gen_unicode_bitmap.py; its Unicode version is older than the one .NET 9 carries,
+//     code points assigned in between differ — the one remaining assumption for such text).
 // Pins: the documented sample body docs/aca/05-aca-dapr-pubsubapi/index.md:60-69 (tests/test_oracle.py).
 bool JsonAllowed(char16_t c, int flavor) {
   if (c < 0x20 || c == u'"' || c == u'\\' || c == 0x7F) return false;
@@ -366,12 +377,8 @@ bool JsonAllowed(char16_t c, int flavor) {
     return true;
   }
   if (flavor == 1) return false;  // outside UnicodeRanges.BasicLatin
-  if (c <= 0x9F) return false;    // C1 controls
-  if (c == 0xA0 || c == 0x1680 || (c >= 0x2000 && c <= 0x200A) || c == 0x202F || c == 0x205F || c == 0x3000) return false;  // Zs
-  if (c == 0x2028 || c == 0x2029) return false;                                                                            // Zl, Zp
-  if (c >= 0xD800 && c <= 0xF8FF) return false;  // surrogates, private use
-  if ((c >= 0xFDD0 && c <= 0xFDEF) || c >= 0xFFFE) return false;  // non-characters
-  return true;
+  static const uint32_t kDefined[2048] = {TT_BMP_DEFINED_WORDS};
+  return (kDefined[c >> 5] >> (c & 31)) & 1u;
 }
 
 void JsonWriteString(std::string& out, const std::u16string& s, int flavor) {
@@ -406,16 +413,20 @@ void JsonWriteString(std::string& out, const std::u16string& s, int flavor) {
 void JsonWriteTaskModel(std::string& out, const TaskModel& t, int flavor, int local_offset_min) {
   out += "{\"taskId\":\"";
   out += t.TaskId.ToString();
+  auto str = [&](const std::u16string& v, int bit) {
+    if (t.null_strings & bit) out += "null";  // JsonSerializer writes a null string as the literal
+    else JsonWriteString(out, v, flavor);
+  };
   out += "\",\"taskName\":";
-  JsonWriteString(out, t.TaskName, flavor);
+  str(t.TaskName, 1);
   out += ",\"taskCreatedBy\":";
-  JsonWriteString(out, t.TaskCreatedBy, flavor);
+  str(t.TaskCreatedBy, 2);
   out += ",\"taskCreatedOn\":\"";
   out += FormatSystemTextJson(t.TaskCreatedOn, local_offset_min);
   out += "\",\"taskDueDate\":\"";
   out += FormatSystemTextJson(t.TaskDueDate, local_offset_min);
   out += "\",\"taskAssignedTo\":";
-  JsonWriteString(out, t.TaskAssignedTo, flavor);
+  str(t.TaskAssignedTo, 4);
   out += t.IsCompleted ? ",\"isCompleted\":true" : ",\"isCompleted\":false";
   out += t.IsOverDue ? ",\"isOverDue\":true" : ",\"isOverDue\":false";
   out.push_back('}');
@@ -435,8 +446,7 @@ void JsonWriteTaskModel(std::string& out, const TaskModel& t, int flavor, int lo
 //     1..16 fraction digits, those beyond 100 ns dropped;
 //   * lone surrogate escapes, raw control characters in strings, trailing commas and comments throw.
 // This restatement builds a small value tree first and maps its members afterwards (the product
-// streams through the text once); a null string member is stored as the empty string here and
-// there, which the reference would keep as null.
+// streams through the text once); a null string member stays null (TaskModel::null_strings).
 struct JsonNode {
   enum Type { Null, Bool, Number, String, Array, Object } type = Null;
   bool b = false;
@@ -680,8 +690,12 @@ TaskModel DeserializeTaskModel(const char* p, const char* end, int local_offset_
   if (t.p != end || root.type != JsonNode::Object) throw JsonParseError();
   TaskModel m;  // initialisers: Guid.Empty, string.Empty, default(DateTime), false
   memset(m.TaskId.b, 0, 16);
-  auto str = [](const JsonNode& v) {
-    if (v.type == JsonNode::Null) return std::u16string();
+  auto str = [&m](const JsonNode& v, uint8_t bit) {
+    m.null_strings = (uint8_t)(m.null_strings & ~bit);  // a repeated member overwrites, null-ness included
+    if (v.type == JsonNode::Null) {
+      m.null_strings |= bit;
+      return std::u16string();
+    }
     if (v.type != JsonNode::String) throw JsonParseError();
     return Utf8ToUtf16(v.text.data(), (int)v.text.size());
   };
@@ -689,9 +703,9 @@ TaskModel DeserializeTaskModel(const char* p, const char* end, int local_offset_
     const std::string& k = kv.first;
     const JsonNode& v = kv.second;
     if (IEquals(k, "taskId")) { if (v.type != JsonNode::String) throw JsonParseError(); m.TaskId = JsonReadGuid(v.text); }
-    else if (IEquals(k, "taskName")) m.TaskName = str(v);
-    else if (IEquals(k, "taskCreatedBy")) m.TaskCreatedBy = str(v);
-    else if (IEquals(k, "taskAssignedTo")) m.TaskAssignedTo = str(v);
+    else if (IEquals(k, "taskName")) m.TaskName = str(v, 1);
+    else if (IEquals(k, "taskCreatedBy")) m.TaskCreatedBy = str(v, 2);
+    else if (IEquals(k, "taskAssignedTo")) m.TaskAssignedTo = str(v, 4);
     else if (IEquals(k, "taskCreatedOn")) { if (v.type != JsonNode::String) throw JsonParseError(); m.TaskCreatedOn = JsonReadDateTime(v.text, local_offset_min); }
     else if (IEquals(k, "taskDueDate")) { if (v.type != JsonNode::String) throw JsonParseError(); m.TaskDueDate = JsonReadDateTime(v.text, local_offset_min); }
     else if (IEquals(k, "isCompleted")) { if (v.type != JsonNode::Bool) throw JsonParseError(); m.IsCompleted = v.b; }
@@ -942,7 +956,11 @@ int64_t orc_get_by_creator(orc_table* t, int32_t mode, const char* utf8, int32_t
   std::vector<int64_t> rows;
   if (mode == ORC_MODE_FAKE) {
     FakeTasksManager m{t->live};
-    for (TaskModel* x : m.GetTasksByCreator(createdBy)) rows.push_back(x->row);
+    try {
+      for (TaskModel* x : m.GetTasksByCreator(createdBy)) rows.push_back(x->row);
+    } catch (const NullReferenceException&) {
+      return -2;  // a task whose TaskCreatedBy is null: the in-memory manager's lambda throws
+    }
   } else {
     TasksStoreManager m{&t->live, &t->keys, &t->rows};
     for (const TaskModel& x : m.GetTasksByCreator(createdBy)) rows.push_back(x.row);

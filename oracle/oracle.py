@@ -211,6 +211,8 @@ class OracleTable:
         cb = created_by.encode() if isinstance(created_by, str) else bytes(created_by)
         out = np.empty(len(self), dtype=np.uint32)
         n = self._l.orc_get_by_creator(self._h, mode, cb, len(cb), _ptr(out), len(out))
+        if n == -2:  # FakeTasksManager.cs:70 calls .Equals on a null TaskCreatedBy
+            raise RuntimeError("NullReferenceException")
         return out[:n].copy()
 
     def flags(self):

@@ -29,7 +29,7 @@ def same_table(oracle, ot, table, creators, offset=0):
     seen = 0
     for who in creators:
         res = table.get_by_creator(who)
-        listed = ot.get_by_creator(oracle.MODE_FAKE, who)
+        listed = ot.get_by_creator(oracle.MODE_STORE, who)  # (the in-memory manager throws on a null TaskCreatedBy)
         assert res.rows().tolist() == listed.tolist()
         for flavor in (tt.JSON_RESPONSE, tt.JSON_DOCUMENT):
             assert res.to_json(flavor, offset) == ot.to_json(listed, flavor, offset)
@@ -94,10 +94,25 @@ def test_handwritten_documents(oracle, offset):
     assert ot.add_documents(text, off, offset) == -1
     table = tt.TaskTable(0)
     st = table.load_documents(text, off, offset)
-    assert st.n_docs == len(HAND) and st.n_creators == 3  # "a@b", "c@d" and "" (null / missing)
-    assert same_table(oracle, ot, table, [b"a@b", b"c@d", b""], offset) == len(HAND)
+    assert st.n_docs == len(HAND) and st.n_creators == 3  # "a@b", "c@d" and "" (missing; a null shares its slot)
+    # document 2's TaskCreatedBy is null: no creator query finds it, not even the empty string
+    assert same_table(oracle, ot, table, [b"a@b", b"c@d", b""], offset) == len(HAND) - 1
     doc = json.loads(table.get_by_creator(b"a@b").to_json())
     assert {d["taskName"] for d in doc} >= {"order and case", "q\"b\\s/\b\f\n\r\té中\U0001F600 end", ""}
+    # null string members stay null (System.Text.Json keeps them; the initialisers only cover missing members)
+    for flavor in (tt.JSON_RESPONSE, tt.JSON_DOCUMENT):
+        text2 = table.get_by_id(bytes(16)).to_json(flavor, offset)
+        assert text2 == ot.to_json(np.array([2], dtype=np.uint32), flavor, offset)
+        row2 = json.loads(text2)[0]
+        assert row2["taskName"] == "second" and row2["taskCreatedBy"] is None and row2["taskAssignedTo"] is None
+    assert table.get_by_id(bytes(16)).field(tt.FIELD_CREATOR_REF).tolist() == [0xFFFFFFFE]
+    # and survive a trip through the device's own writer and reader
+    everything = table.get_due_on_or_before(tt.MODE_FAKE, tt.DEFAULT_TODAY + 10**6 * tt.TICKS_PER_DAY)
+    j = everything.json(tt.JSON_DOCUMENT, offset)
+    again = tt.TaskTable(0)
+    again.load_documents(j.bytes(), j.offsets(everything.count), offset)
+    assert again.get_due_on_or_before(tt.MODE_FAKE, tt.DEFAULT_TODAY + 10**6 * tt.TICKS_PER_DAY).to_json(tt.JSON_DOCUMENT, offset) == j.bytes()
+    again.close()
     table.close()
 
 
@@ -242,7 +257,7 @@ def test_documents_from_the_reference_tutorial(oracle):
     seen = 0
     for who in {s["members"]["taskCreatedBy"].encode() for s in samples}:
         res = table.get_by_creator(who)
-        listed = ot.get_by_creator(oracle.MODE_FAKE, who)
+        listed = ot.get_by_creator(oracle.MODE_STORE, who)  # (the in-memory manager throws on a null TaskCreatedBy)
         assert res.rows().tolist() == listed.tolist()
         for row, doc in zip(res.rows(), json.loads(res.to_json())):
             assert doc == {**defaults, **samples[int(row)]["members"]}, samples[int(row)]["source"]

@@ -7,6 +7,7 @@ import datetime as dt
 import os
 
 import numpy as np
+import pytest
 
 TPD = 864000000000
 
@@ -373,7 +374,11 @@ def test_restated_reader_on_handwritten_and_malformed_documents(oracle):
     docs = json.loads(ot.to_json(np.arange(len(HAND)), oracle.JSON_RESPONSE, 120))
     assert docs[0]["taskId"] == "fbc55b2c-d9fa-405e-aec8-22e53f4306dd" and docs[0]["isCompleted"] is True
     assert docs[1]["taskName"] == "q\"b\\s/\b\f\n\r\t\u00e9\u4e2d\U0001F600 end"
-    assert docs[2]["taskName"] == "second" and docs[2]["taskCreatedBy"] == "" and docs[2]["isCompleted"] is False
+    assert docs[2]["taskName"] == "second" and docs[2]["isCompleted"] is False
+    assert docs[2]["taskCreatedBy"] is None and docs[2]["taskAssignedTo"] is None  # null stays null; missing members are ""
+    assert ot.get_by_creator(oracle.MODE_STORE, b"").tolist() == [7]               # the store's EQ "" does not match a null
+    with pytest.raises(RuntimeError):                                              # FakeTasksManager.cs:70: .Equals on null
+        ot.get_by_creator(oracle.MODE_FAKE, b"a@b")
     assert docs[3]["taskCreatedOn"] == "2020-01-01T10:30:00" and docs[3]["taskDueDate"] == "2026-11-05T00:00:00.5"
     assert docs[4]["taskCreatedOn"] == "2020-01-01T10:30:15.1234567"          # 16 digits truncated to 100 ns
     assert docs[4]["taskDueDate"] == "2026-11-05T02:00:00+02:00"              # +02:00 read on a +02:00 clock: same wall time
@@ -437,3 +442,82 @@ def test_streaming_creator_filter_agrees_with_the_list_oracle(oracle):
             else:
                 assert (o.min_row, o.max_row) == (-1, -1)
     assert out[4].count == out[5].count == 0 and out[1].count == out[3].count > 50
+
+
+def expected_relaxed(s):
+    """JavaScriptEncoder.UnsafeRelaxedJsonEscaping on a string, computed from Python's own Unicode database
+    (not from the table the oracle and the device share): \\" \\\\ and the five short escapes, a BMP code point as
+    it is when its general category is a letter, mark, number, punctuation or symbol (or it is U+0020), anything
+    else as \\uXXXX in upper-case hex, supplementary scalars as their two surrogates."""
+    import unicodedata
+
+    short = {'"': '\\"', "\\": "\\\\", "\b": "\\b", "\t": "\\t", "\n": "\\n", "\f": "\\f", "\r": "\\r"}
+    out = []
+    for ch in s:
+        cp = ord(ch)
+        if ch in short:
+            out.append(short[ch])
+        elif cp >= 0x10000:
+            v = cp - 0x10000
+            out.append("\\u%04X\\u%04X" % (0xD800 + (v >> 10), 0xDC00 + (v & 0x3FF)))
+        elif cp == 0x20 or unicodedata.category(ch)[0] in "LMNPS":
+            out.append(ch)
+        else:
+            out.append("\\u%04X" % cp)
+    return "".join(out)
+
+
+def test_relaxed_encoder_against_the_unicode_database(oracle):
+    """every BMP scalar and a sample of the astral ones through the restated UnsafeRelaxedJsonEscaping, against
+    expected_relaxed(); and the generated table (include/tt_bmp_defined.h) is up to date with this Python's UCD"""
+    import subprocess
+    import sys
+    import unicodedata
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    header = open(os.path.join(root, "include", "tt_bmp_defined.h")).read()
+    assert f'TT_BMP_UNICODE_VERSION "{unicodedata.unidata_version}"' in header, "run scripts/gen_unicode_bitmap.py"
+    scalars = [c for c in range(0x10000) if not 0xD800 <= c <= 0xDFFF] + list(range(0x10000, 0x110000, 4099))
+    names = ["".join(map(chr, scalars[i:i + 32])) for i in range(0, len(scalars), 32)]
+    ot = oracle.OracleTable()
+    zero = np.zeros(16, dtype=np.uint8)
+    for nm in names:
+        ot.add(zero, nm.encode(), b"", b"", 0, 0)
+    text = ot.to_json(np.arange(len(names)), oracle.JSON_RESPONSE).decode()
+    pieces = text.split('","taskCreatedBy":"')
+    assert len(pieces) == len(names) + 1
+    for nm, piece in zip(names, pieces):
+        assert piece[piece.index('"taskName":"') + 12:] == expected_relaxed(nm)
+    # spot checks of the classes the round-1 restatement got wrong or right
+    for cp, raw_ok in ((0xAD, False), (0x200B, False), (0xFEFF, False), (0x378, False), (0xA0, False), (0x2028, False),
+                       (0xE000, False), (0xFFFE, False), (0xE9, True), (0x4E2D, True), (0x20AC, True), (0x300, True),
+                       (0x3C, True), (0x2B, True), (0x27, True)):
+        ch = chr(cp)
+        assert (expected_relaxed(ch) == ch) == raw_ok, hex(ord(ch))
+
+
+def test_documented_dotnet_known_answers(oracle):
+    """Facts the .NET documentation states, used as known answers for the restated BCL pieces:
+    DateTime.UnixEpoch.Ticks and DateTime.MaxValue.Ticks (System.DateTime reference pages), DateTime(2000,1,1).Ticks,
+    TimeSpan.TicksPerDay; Guid.ToByteArray() byte order against ToString("D") (System.Guid.ToByteArray remarks: the
+    first three groups are little-endian in the array) — this library keeps ids in the order of the "D" string;
+    the JavaScriptEncoder.Default escapes the System.Text.Json character-encoding article lists
+    (< > & ' + as \\u003C \\u003E \\u0026 \\u0027 \\u002B, non-ASCII as \\uXXXX, the quote as \\u0022) and the relaxed
+    encoder's \\" ."""
+    import uuid
+
+    assert TPD == 864_000_000_000
+    assert ticks(1970, 1, 1) == 621_355_968_000_000_000            # DateTime.UnixEpoch.Ticks
+    assert ticks(2000, 1, 1) == 630_822_816_000_000_000
+    assert ticks(9999, 12, 31, 23, 59, 59, 9_999_999) == 3_155_378_975_999_999_999  # DateTime.MaxValue.Ticks
+    assert oracle.format_stj(raw(3_155_378_975_999_999_999, UTC)) == "9999-12-31T23:59:59.9999999Z"
+    assert oracle.format_stj(raw(621_355_968_000_000_000, UTC)) == "1970-01-01T00:00:00Z"
+    # Guid "00112233-4455-6677-8899-aabbccddeeff": ToByteArray() gives 33 22 11 00 55 44 77 66 88 99 aa bb cc dd ee ff;
+    # the canonical (string-order) bytes kept here are Python's UUID.bytes, the .NET array is UUID.bytes_le
+    u = uuid.UUID("00112233-4455-6677-8899-aabbccddeeff")
+    assert u.bytes_le.hex() == "33221100554477668899aabbccddeeff"
+    assert oracle.guid_string(u.bytes) == "00112233-4455-6677-8899-aabbccddeeff"
+    ot = oracle.OracleTable()
+    ot.add(np.frombuffer(u.bytes, dtype=np.uint8).copy(), "<a href='x'>+&é\"".encode(), b"", b"", 0, 0)
+    assert b'"taskName":"\\u003Ca href=\\u0027x\\u0027\\u003E\\u002B\\u0026\\u00E9\\u0022"' in ot.to_json([0], oracle.JSON_DOCUMENT)
+    assert '"taskName":"<a href=\'x\'>+&é\\""'.encode() in ot.to_json([0], oracle.JSON_RESPONSE)

@@ -229,6 +229,61 @@ def test_snapshot_carries_the_payload(oracle, tmp_path):
         t.close()
 
 
+def test_snapshot_is_replaced_atomically_and_checked_on_load(oracle, tmp_path):
+    """A save goes to <path>.tmp and is renamed over <path>; a load refuses a file that is cut short, whose bytes
+    changed, or whose references point outside their dictionaries, and leaves the table empty and usable; files
+    written before the trailer existed (magic TTSNAP01) still load."""
+    import os
+
+    n = 20_000
+    cfg = oracle.default_cfg(91, n, n_creators=12, n_names=40)
+    table = tt.TaskTable(0).generate(cfg, 0, n).generate_payload(cfg, 0)
+    path = str(tmp_path / "t.snap")
+    table.save_snapshot(path)
+    assert not os.path.exists(path + ".tmp")
+    good = open(path, "rb").read()
+    assert good[:8] == b"TTSNAP02" and good[-24:-16] == b"TTSNEND2"
+    want = table.get_yesterdays_due(tt.MODE_STORE).ids()
+    # a save that cannot finish (the directory of the temporary file is gone) leaves the old file alone
+    with pytest.raises(tt.TaskTableError):
+        table.save_snapshot(str(tmp_path / "no" / "such" / "dir.snap"))
+    assert open(path, "rb").read() == good
+
+    def refused(blob, code):
+        bad = str(tmp_path / "bad.snap")
+        open(bad, "wb").write(blob)
+        t2 = tt.TaskTable(0)
+        with pytest.raises(tt.TaskTableError) as e:
+            t2.load_snapshot(bad)
+        assert e.value.code == code and len(t2) == 0
+        t2.load_snapshot(path)  # the table is still empty and takes the good file
+        assert (t2.get_yesterdays_due(tt.MODE_STORE).ids() == want).all()
+        t2.close()
+
+    refused(good[: len(good) // 2], tt.TT_ERR_STATE)                     # cut short
+    refused(good[:-24], tt.TT_ERR_STATE)                                  # trailer missing
+    flipped = bytearray(good)
+    flipped[len(good) // 3] ^= 0x40
+    refused(bytes(flipped), tt.TT_ERR_STATE)                              # one bit changed: checksum
+    # an old-format file (no trailer, so no checksum) with a creator_ref beyond the dictionary: caught by the check
+    # of the references on the device
+    head = 56
+    np_rows = int.from_bytes(good[16:24], "little")
+    ref_off = head + np_rows * 4 + 2 * (np_rows // 8) + np_rows * 8 + np_rows * 16 + np_rows * 8 + np_rows * 8
+    old = bytearray(b"TTSNAP01" + good[8:-24])
+    t3 = tt.TaskTable(0).load_snapshot(_write(tmp_path / "old.snap", bytes(old)))
+    assert (t3.get_yesterdays_due(tt.MODE_STORE).ids() == want).all()
+    t3.close()
+    old[ref_off + 4 * 7: ref_off + 4 * 7 + 4] = (1000).to_bytes(4, "little")
+    refused(bytes(old), tt.TT_ERR_ARG)
+    table.close()
+
+
+def _write(path, blob):
+    open(path, "wb").write(blob)
+    return str(path)
+
+
 def test_mark_overdue_after_creates_with_fresh_guids(oracle):
     """The reference's everyday flow: CreateNewTask with Guid.NewGuid() ids (which break the table's TaskId
     order), then the cron job — GET the list, POST it back to MarkOverdueTasks (TasksStoreManager.cs:141-149).

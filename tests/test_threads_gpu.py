@@ -54,3 +54,42 @@ def test_concurrent_calls_on_one_table(oracle):
     assert not errors, errors
     assert (table.flags_bytes()[1] == ot.flags()[1]).all()
     table.close()
+
+
+def test_concurrent_creator_requests_share_table_passes(oracle):
+    """GetTasksByCreator from many request threads at once: requests that arrive while a pass over the table is
+    running are answered together by the next pass.  Every thread still gets exactly its own creator's list."""
+    n = 4_000_000
+    cfg = oracle.default_cfg(321, n, n_creators=2000)
+    ot = oracle.OracleTable()
+    ot.add_synth(cfg, 0, n)
+    table = tt.TaskTable(0).generate(cfg, 0, n)
+    creators = [ot.created_by(k) for k in range(200)] + [b"nobody@example.org"]
+    want = {c: ot.get_by_creator(oracle.MODE_STORE, c).tolist() for c in set(creators)}
+    errors, per_thread = [], 40
+    start = threading.Barrier(32)
+
+    def request_thread(seed):
+        rng = np.random.default_rng(seed)
+        try:
+            start.wait()
+            for _ in range(per_thread):
+                c = creators[int(rng.integers(0, len(creators)))]
+                res = table.get_by_creator(c)
+                assert res.rows().tolist() == want[c]
+                res.free()
+        except Exception as e:  # noqa: BLE001
+            errors.append(repr(e))
+
+    threads = [threading.Thread(target=request_thread, args=(s,)) for s in range(32)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert not errors, errors[:3]
+    passes, requests = table.creator_combining_stats()
+    assert requests == 32 * per_thread and 0 < passes < requests  # some passes answered several requests
+    # a bad request in the queue fails alone at the door, not inside somebody else's batch
+    with pytest.raises(tt.TaskTableError):
+        tt._check(tt.lib().tt_get_by_creator(table._h, None, 5, None))
+    table.close()
