@@ -19,14 +19,31 @@
 
 namespace tt {
 
+// keys[i] = the sort key of rows[i], vals[i] = the row; mm[0] / mm[1] collect the smallest / largest key
+// (preset to ~0 / 0), which tell the sort how many digits actually vary.  Grid-stride over a bounded grid:
+// the min / max cost one pair of atomics per warp of the GRID, not of the list (one pair per 32 hits on two
+// addresses took longer than the gathers).
 __global__ void order_keys_kernel(const uint32_t* rows, const uint64_t* created_raw, unsigned long long* keys,
-                                  uint32_t* vals, int64_t n, int descending) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) {
+                                  uint32_t* vals, int64_t n, int descending, unsigned long long* mm) {
+  unsigned long long lo = ~0ull, hi = 0;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     const uint32_t r = rows[i];
     uint64_t k = ld_gather_u64(created_raw + r) & TT_TICKS_MASK;
-    keys[i] = descending ? (~k & TT_TICKS_MASK) : k;
+    k = descending ? (~k & TT_TICKS_MASK) : k;
+    keys[i] = k;
     vals[i] = r;
+    lo = k < lo ? k : lo;
+    hi = k > hi ? k : hi;
+  }
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) {
+    const unsigned long long a = __shfl_xor_sync(0xFFFFFFFFu, lo, d), b = __shfl_xor_sync(0xFFFFFFFFu, hi, d);
+    lo = a < lo ? a : lo;
+    hi = b > hi ? b : hi;
+  }
+  if ((threadIdx.x & 31) == 0 && lo <= hi) {
+    atomicMin(mm + 0, lo);
+    atomicMax(mm + 1, hi);
   }
 }
 
@@ -85,11 +102,14 @@ inline int order_by_created(cudaStream_t stream, SortScratch& sc, const uint64_t
   cudaError_t e = sc.reserve(n);
   if (e != cudaSuccess) return (int)e;
   const unsigned grid = (unsigned)((n + 255) / 256);
-  order_keys_kernel<<<grid, 256, 0, stream>>>(d_rows, created_raw, sc.keys[0], sc.vals[0], n, descending ? 1 : 0);
+  e = radix_minmax_reset(stream, sc);
+  if (e != cudaSuccess) return (int)e;
+  order_keys_kernel<<<grid < 148u * 16u ? grid : 148u * 16u, 256, 0, stream>>>(d_rows, created_raw, sc.keys[0], sc.vals[0], n,
+                                                                               descending ? 1 : 0, sc.mm);
   e = cudaGetLastError();
   if (e != cudaSuccess) return (int)e;
   int bits = 62, w = 0;
-  e = radix_significant_bits(stream, sc, n, &bits);
+  e = radix_bits_from_minmax(stream, sc, &bits);
   if (e != cudaSuccess) return (int)e;
   e = radix_sort_pairs(stream, sc, n, bits, &w);
   if (e != cudaSuccess) return (int)e;

@@ -3,9 +3,9 @@
 // (Api/Services/TasksStoreManager.cs:136,66; Api/Services/FakeTasksManager.cs:70), so the sort
 // must be stable too: equal TaskCreatedOn values keep their list order.
 //
-// One pass per 8-bit digit, four launches per pass:
-//   radix_hist_kernel    per-tile digit counts, digit-major
-//   group_reduce_kernel + tile_offsets_kernel (sweep.cuh)  exclusive scan of those counts
+// One pass per 8-bit digit, three launches per pass:
+//   radix_hist_kernel    per-tile digit counts, digit-major (shared-memory atomics), and the scan's carries
+//   tile_offsets_kernel (sweep.cuh)  exclusive scan of those counts
 //   radix_scatter_kernel stable scatter: inside a tile every warp owns a contiguous chunk and
 //                        walks it 32 elements at a time; eight ballots (one per digit bit) group
 //                        the lanes of a round by digit, the group leader bumps the warp's digit
@@ -42,24 +42,43 @@ __device__ __forceinline__ uint32_t digit_peers(uint32_t d, uint32_t live) {
 }
 
 // hist[d * num_tiles + tile] = elements of `tile` whose digit is d (digit-major, the order of
-// the exclusive scan that turns counts into output offsets).
+// the exclusive scan that turns counts into output offsets).  The scan's carries are accumulated on the
+// way: group_sum[e / 1024] += hist entry e (zeroed by the caller), so no separate reduction pass runs.
+// LOW_ENTROPY = false: plain shared-memory atomics (the counts need no order).  LOW_ENTROPY = true: the
+// pass's digit has only a few significant bits (the top digit of the keys), nearly every key of a tile
+// falls into the same few bins and plain atomics would serialise, so the lanes of a warp are grouped by
+// digit first (ballots) and each group adds once.
+template <bool LOW_ENTROPY>
 __global__ void __launch_bounds__(kRadixThreads) radix_hist_kernel(const unsigned long long* keys, int64_t n, int shift,
-                                                                    uint32_t* hist, uint32_t num_tiles) {
+                                                                    uint32_t* hist, uint32_t num_tiles, uint32_t* group_sum) {
   __shared__ uint32_t s_hist[kRadixDigits];
   const uint32_t tile = blockIdx.x;
   s_hist[threadIdx.x] = 0;
   __syncthreads();
   const int64_t base = (int64_t)tile * kRadixTile;
+  unsigned long long k[kRadixItems];
+#pragma unroll
+  for (int r = 0; r < kRadixItems; ++r) {
+    const int64_t i = base + r * kRadixThreads + threadIdx.x;
+    k[r] = i < n ? keys[i] : 0ull;
+  }
 #pragma unroll
   for (int r = 0; r < kRadixItems; ++r) {
     const int64_t i = base + r * kRadixThreads + threadIdx.x;
     const bool valid = i < n;
-    const uint32_t d = valid ? (uint32_t)(keys[i] >> shift) & 255u : 0u;
-    const uint32_t peers = digit_peers(d, __ballot_sync(0xFFFFFFFFu, valid));
-    if (valid && (threadIdx.x & 31u) == (uint32_t)(__ffs(peers) - 1)) atomicAdd(&s_hist[d], (uint32_t)__popc(peers));
+    const uint32_t d = (uint32_t)(k[r] >> shift) & 255u;
+    if (LOW_ENTROPY) {
+      const uint32_t peers = digit_peers(d, __ballot_sync(0xFFFFFFFFu, valid));
+      if (valid && (threadIdx.x & 31u) == (uint32_t)(__ffs(peers) - 1)) atomicAdd(&s_hist[d], (uint32_t)__popc(peers));
+    } else if (valid) {
+      atomicAdd(&s_hist[d], 1u);
+    }
   }
   __syncthreads();
-  hist[threadIdx.x * num_tiles + tile] = s_hist[threadIdx.x];
+  const uint32_t c = s_hist[threadIdx.x];
+  const uint32_t e = threadIdx.x * num_tiles + tile;
+  hist[e] = c;
+  if (c) atomicAdd(group_sum + e / kTilesPerGroup, c);
 }
 
 // group_sum[g] = sum of counts[g*1024 .. g*1024+1023] (the scan kernel's carries)
@@ -245,8 +264,12 @@ inline cudaError_t radix_sort_pairs(cudaStream_t stream, SortScratch& s, int64_t
   const uint32_t groups = (entries + kTilesPerGroup - 1) / kTilesPerGroup;
   int cur = 0;
   for (int shift = 0; shift < bits; shift += 8) {
-    radix_hist_kernel<<<tiles, kRadixThreads, 0, stream>>>(s.keys[cur], n, shift, s.hist, tiles);
-    group_reduce_kernel<<<groups, kTilesPerGroup, 0, stream>>>(s.hist, entries, s.group_sum);
+    cudaError_t em = cudaMemsetAsync(s.group_sum, 0, (size_t)groups * 4, stream);
+    if (em != cudaSuccess) return em;
+    if (bits - shift < 6)
+      radix_hist_kernel<true><<<tiles, kRadixThreads, 0, stream>>>(s.keys[cur], n, shift, s.hist, tiles, s.group_sum);
+    else
+      radix_hist_kernel<false><<<tiles, kRadixThreads, 0, stream>>>(s.keys[cur], n, shift, s.hist, tiles, s.group_sum);
     tile_offsets_kernel<<<groups, kTilesPerGroup, 0, stream>>>(s.hist, s.group_sum, entries, s.offsets);
     radix_scatter_kernel<<<tiles, kRadixThreads, 0, stream>>>(s.keys[cur], s.vals[cur], s.keys[cur ^ 1], s.vals[cur ^ 1], n,
                                                               shift, s.offsets, tiles);
@@ -258,15 +281,27 @@ inline cudaError_t radix_sort_pairs(cudaStream_t stream, SortScratch& s, int64_t
   return cudaSuccess;
 }
 
+// s.mm = {~0, 0}: the start state of a min / max collected by the kernel that produces the keys.
+inline cudaError_t radix_minmax_reset(cudaStream_t stream, SortScratch& s) {
+  static const unsigned long long init[2] = {~0ull, 0ull};
+  return cudaMemcpyAsync(s.mm, init, 16, cudaMemcpyHostToDevice, stream);
+}
+
+inline cudaError_t radix_bits_from_minmax(cudaStream_t stream, SortScratch& s, int* bits);
+
 // Number of low bits on which the keys in s.keys[0][0..n) can differ (synchronises the stream).
 inline cudaError_t radix_significant_bits(cudaStream_t stream, SortScratch& s, int64_t n, int* bits) {
-  const unsigned long long init[2] = {~0ull, 0ull};
-  cudaError_t e = cudaMemcpyAsync(s.mm, init, 16, cudaMemcpyHostToDevice, stream);
+  cudaError_t e = radix_minmax_reset(stream, s);
   if (e != cudaSuccess) return e;
   const unsigned grid = (unsigned)((n + 255) / 256 < 1184 ? (n + 255) / 256 : 1184);
   radix_minmax_kernel<<<grid ? grid : 1, 256, 0, stream>>>(s.keys[0], n, s.mm);
+  return radix_bits_from_minmax(stream, s, bits);
+}
+
+// The same from a min / max already collected in s.mm (synchronises the stream).
+inline cudaError_t radix_bits_from_minmax(cudaStream_t stream, SortScratch& s, int* bits) {
   unsigned long long mm[2];
-  e = cudaMemcpyAsync(mm, s.mm, 16, cudaMemcpyDeviceToHost, stream);
+  cudaError_t e = cudaMemcpyAsync(mm, s.mm, 16, cudaMemcpyDeviceToHost, stream);
   if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
   if (e != cudaSuccess) return e;
   unsigned long long diff = mm[0] ^ mm[1];

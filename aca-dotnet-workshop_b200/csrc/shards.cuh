@@ -122,7 +122,21 @@ __global__ void __launch_bounds__(256) shard_expand_kernel(const unsigned char* 
   const uint32_t first = reinterpret_cast<const uint32_t*>(slot + lay.tile_first)[t];
   const uint16_t* src = reinterpret_cast<const uint16_t*>(slot + lay.off16) + first;
   uint32_t* dst = rows_out + meta->base[r] + first;
-  for (uint32_t k = threadIdx.x & 31u; k < cnt; k += 32) dst[k] = t * TT_TILE_ROWS + src[k];
+  // all of a lane's loads go out before its first store: a tile of the usual density (about 200 hits) is in
+  // flight at once instead of one 64-byte piece per warp (measured at 8 GPUs: the dependent form ran at 2.7 TB/s)
+  const uint32_t lane = threadIdx.x & 31u, row0 = t * TT_TILE_ROWS;
+  uint16_t v[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const uint32_t k = lane + 32u * j;
+    v[j] = k < cnt ? src[k] : (uint16_t)0;
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const uint32_t k = lane + 32u * j;
+    if (k < cnt) dst[k] = row0 + v[j];
+  }
+  for (uint32_t k = lane + 256u; k < cnt; k += 32) dst[k] = row0 + src[k];  // denser tiles: the rest
 }
 
 // Sort keys of the cross-shard OrderBy(TaskCreatedOn): key = the pushed ticks, value = position in

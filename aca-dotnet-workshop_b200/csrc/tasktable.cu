@@ -724,8 +724,10 @@ void result_release(tt_result* r) { delete r; }  // the block goes with its last
 // small the result is regrown to the exact size and the sweep runs again: from scratch if the
 // first pass changed nothing, otherwise for the hits the first pass did not reach (the rows it
 // marked no longer match), after which the two row-ordered runs are merged by a sort.
+// with_ids = false: the TaskIds are not gathered here — the caller re-orders the list and gathers them in the
+// final order (a gather per hit saved).
 int32_t sweep_owned(tt_table* t, int32_t mode, int32_t flags, int64_t today, int64_t run_at, tt_result** out,
-                    tt_sweep_stats* total) {
+                    tt_sweep_stats* total, bool with_ids = true) {
   memset(total, 0, sizeof *total);
   tt_result* r = nullptr;
   int64_t guess = std::min<int64_t>(t->n, std::max<int64_t>(65536, t->n / 16));
@@ -734,7 +736,8 @@ int32_t sweep_owned(tt_table* t, int32_t mode, int32_t flags, int64_t today, int
   bool merged = false;
   for (int pass = 0; pass < 8; ++pass) {
     tt_sweep_stats st;
-    rc = sweep_run(t, mode, flags, today, run_at, 0, r->d_rows + r->n, r->d_ids + r->n, r->cap - r->n, &st, t->stream);
+    rc = sweep_run(t, mode, flags, today, run_at, 0, r->d_rows + r->n, with_ids ? r->d_ids + r->n : nullptr, r->cap - r->n, &st,
+                   t->stream);
     total->kernel_ms += st.kernel_ms;
     total->sweep_ms += st.sweep_ms;
     total->gather_ms += st.gather_ms;
@@ -747,7 +750,7 @@ int32_t sweep_owned(tt_table* t, int32_t mode, int32_t flags, int64_t today, int
     if (rc == TT_OK) {
       r->n += st.n_stored;
       if (merged && r->n > 1) {
-        int e = tt::sort_rows_and_gather(t->stream, t->sort, t->task_id, r->d_rows, r->d_ids, r->n);
+        int e = tt::sort_rows_and_gather(t->stream, t->sort, t->task_id, r->d_rows, with_ids ? r->d_ids : nullptr, r->n);
         if (e != 0) {
           result_release(r);
           return fail(TT_ERR_CUDA, "sort_rows_and_gather: %s", cudaGetErrorString((cudaError_t)e));
@@ -769,7 +772,7 @@ int32_t sweep_owned(tt_table* t, int32_t mode, int32_t flags, int64_t today, int
     }
     if (keep) {
       cudaMemcpyAsync(g->d_rows, r->d_rows, keep * 4, cudaMemcpyDeviceToDevice, t->stream);
-      cudaMemcpyAsync(g->d_ids, r->d_ids, keep * 16, cudaMemcpyDeviceToDevice, t->stream);
+      if (with_ids) cudaMemcpyAsync(g->d_ids, r->d_ids, keep * 16, cudaMemcpyDeviceToDevice, t->stream);
       cudaStreamSynchronize(t->stream);
       merged = true;
     }
@@ -1018,9 +1021,9 @@ int32_t tt_get_yesterdays_due(tt_table* t, int32_t mode, int64_t today_local_tic
   DeviceGuard g(t->device);
   tt_sweep_stats st;
   tt_result* r = nullptr;
-  int32_t rc = sweep_owned(t, mode, TT_SWEEP_LIST_ONLY, today_local_ticks, 0, &r, &st);
+  int32_t rc = sweep_owned(t, mode, TT_SWEEP_LIST_ONLY, today_local_ticks, 0, &r, &st, mode != TT_MODE_STORE);
   if (rc) return rc;
-  if (mode == TT_MODE_STORE && r->n > 1) {
+  if (mode == TT_MODE_STORE && r->n > 0) {
     // TasksStoreManager.cs:136 — OrderBy(TaskCreatedOn), stable; ties keep row order
     rc = tt::order_by_created(t->stream, t->sort, t->created_raw, t->task_id, r->d_rows, r->d_ids, r->n, /*descending=*/false);
     if (rc != 0) {
@@ -1059,9 +1062,10 @@ int32_t tt_get_due_on_or_before(tt_table* t, int32_t mode, int64_t today_local_t
   DeviceGuard g(t->device);
   tt_sweep_stats st;
   tt_result* r = nullptr;
-  int32_t rc = sweep_owned(t, mode, TT_SWEEP_LIST_ONLY | TT_SWEEP_DUE_ON_OR_BEFORE, today_local_ticks, 0, &r, &st);
+  int32_t rc = sweep_owned(t, mode, TT_SWEEP_LIST_ONLY | TT_SWEEP_DUE_ON_OR_BEFORE, today_local_ticks, 0, &r, &st,
+                           mode != TT_MODE_STORE);
   if (rc) return rc;
-  if (mode == TT_MODE_STORE && r->n > 1) {  // the store-backed list is ordered by TaskCreatedOn (TasksStoreManager.cs:136)
+  if (mode == TT_MODE_STORE && r->n > 0) {  // the store-backed list is ordered by TaskCreatedOn (TasksStoreManager.cs:136)
     rc = tt::order_by_created(t->stream, t->sort, t->created_raw, t->task_id, r->d_rows, r->d_ids, r->n, /*descending=*/false);
     if (rc != 0) {
       result_release(r);
