@@ -63,6 +63,64 @@ __device__ __forceinline__ const uint8_t* skip_ws(const uint8_t* p, const uint8_
   return p;
 }
 
+// ---- eight bytes at a time -----------------------------------------------------------------------
+// The parser is one thread per document, and a byte-at-a-time state machine is a chain of dependent
+// one-byte loads (an L1 round trip each: ncu's source page put most stall samples on the compare after
+// LDG.E.U8).  The hot loops therefore look at eight bytes per step.
+//
+// load8: the eight bytes starting at p, any alignment, little-endian (two aligned 64-bit loads and a
+// funnel shift).  It may read up to 15 bytes past p + 8 rounded up — the device copy of the text is
+// allocated with 16 bytes of slack, and bytes beyond the caller's `end` are masked off by the callers.
+__device__ __forceinline__ uint64_t load8(const uint8_t* p) {
+  const uint64_t* q = reinterpret_cast<const uint64_t*>(reinterpret_cast<uintptr_t>(p) & ~(uintptr_t)7);
+  const uint32_t sh = (uint32_t)(reinterpret_cast<uintptr_t>(p) & 7u) * 8u;
+  const uint64_t lo = q[0], hi = q[1];
+  return sh ? (lo >> sh) | (hi << (64u - sh)) : lo;
+}
+
+constexpr uint64_t kOnes = 0x0101010101010101ull, kHighs = 0x8080808080808080ull;
+
+// High bit set in every byte of x that equals c (exact for the LOWEST such byte; bytes above a match may be
+// flagged by the borrow, which is harmless where only the first flagged byte is used).
+__device__ __forceinline__ uint64_t bytes_eq(uint64_t x, uint32_t c) {
+  const uint64_t y = x ^ (kOnes * c);
+  return (y - kOnes) & ~y & kHighs;
+}
+
+// High bit set in the first byte of x that a plain string run must stop at: '"', '\\', a control
+// character (< 0x20) or a non-ASCII byte (>= 0x80); possibly in later bytes too.
+__device__ __forceinline__ uint64_t string_special(uint64_t x) {
+  return (x & kHighs) | ((x - kOnes * 0x20u) & ~x & kHighs) | bytes_eq(x, '"') | bytes_eq(x, '\\');
+}
+
+// Number of leading bytes of [r, end) that are plain string bytes (none of the above).
+__device__ __forceinline__ uint32_t plain_run(const uint8_t* r, const uint8_t* end) {
+  uint32_t n = 0;
+  while (r + n < end) {
+    const uint32_t left = (uint32_t)min((ptrdiff_t)8, end - (r + n));
+    const uint64_t m = string_special(load8(r + n));
+    if (m) {
+      const uint32_t k = (uint32_t)(__ffsll((long long)m) - 1) >> 3;
+      return n + (k < left ? k : left);
+    }
+    n += left;
+    if (left < 8) break;
+  }
+  return n;
+}
+
+// tt_hash64 (include/tt_synth.h) of [p, p + len), reading eight bytes per step: the same value.
+__device__ __forceinline__ uint64_t hash_text(const uint8_t* p, uint32_t len) {
+  uint64_t h = tt_mix64(0x7461736B73ULL ^ (uint64_t)len);
+  for (uint32_t i = 0; i < len; i += 8) {
+    uint64_t c = load8(p + i);
+    const uint32_t m = len - i;
+    if (m < 8) c &= (1ull << (8 * m)) - 1;
+    h = tt_mix64(h ^ c);
+  }
+  return h;
+}
+
 __device__ __forceinline__ int hex_val(uint32_t c) {
   if (c >= '0' && c <= '9') return (int)c - '0';
   c |= 0x20;
@@ -158,12 +216,19 @@ __device__ const uint8_t* read_string_inplace(uint8_t* p, const uint8_t* end, ui
     // fast path: a run of plain ASCII (the common case) moves one byte per step, or not at all
     // while nothing has been unescaped yet
     uint32_t c = 0;
-    while (r < end) {
-      c = *r;
-      if (c == '"' || c == '\\' || c < 0x20 || c >= 0x80) break;
-      if (w != r) *w = (uint8_t)c;
-      ++w;
-      ++r;
+    if (w == r) {  // nothing has been unescaped yet: the run stays where it is, eight bytes per step
+      const uint32_t run = plain_run(r, end);
+      r += run;
+      w += run;
+      if (r < end) c = *r;
+    } else {
+      while (r < end) {
+        c = *r;
+        if (c == '"' || c == '\\' || c < 0x20 || c >= 0x80) break;
+        *w = (uint8_t)c;
+        ++w;
+        ++r;
+      }
     }
     if (r >= end) return nullptr;
     if (c == '"') break;
@@ -272,38 +337,53 @@ __device__ int member_of(const uint8_t* name, int len) {
 __constant__ char kMemberNames[8][16] = {"taskid", "taskname", "taskcreatedby", "taskcreatedon", "taskduedate",
                                          "taskassignedto", "iscompleted", "isoverdue"};
 __constant__ int kMemberLens[8] = {6, 8, 13, 13, 11, 14, 11, 9};
+// the names as two little-endian words each (bytes 0..7 and 8..15, zero padded)
+constexpr uint64_t name_word(const char* s, int from) {
+  uint64_t w = 0;
+  int n = 0;
+  while (s[n]) ++n;
+  for (int k = 0; k < 8; ++k)
+    if (from + k < n) w |= (uint64_t)(uint8_t)s[from + k] << (8 * k);
+  return w;
+}
+__constant__ uint64_t kMemberWord0[8] = {name_word("taskid", 0),       name_word("taskname", 0),    name_word("taskcreatedby", 0),
+                                         name_word("taskcreatedon", 0), name_word("taskduedate", 0), name_word("taskassignedto", 0),
+                                         name_word("iscompleted", 0),   name_word("isoverdue", 0)};
+__constant__ uint64_t kMemberWord1[8] = {name_word("taskid", 8),       name_word("taskname", 8),    name_word("taskcreatedby", 8),
+                                         name_word("taskcreatedon", 8), name_word("taskduedate", 8), name_word("taskassignedto", 8),
+                                         name_word("iscompleted", 8),   name_word("isoverdue", 8)};
 __device__ int member_fast(const uint8_t* p, const uint8_t* end, const uint8_t** after) {
   // One pass for the names the reference writes: "task?..." / "is?..." — the character after the
   // common prefix names the only candidate and so the length; the closing quote must sit right
   // behind it and every character must match.  Anything else takes the general route below.
   if (end - p >= 16) {
     int m = -1;
-    const uint32_t c0 = p[0] | 0x20u;
+    const uint64_t r0 = load8(p), r1 = load8(p + 8);  // the whole name and its closing quote: no byte loads below
+    const uint64_t f0 = r0 | (kOnes * 0x20u), f1 = r1 | (kOnes * 0x20u);
+    const uint32_t c0 = (uint32_t)f0 & 0xFF;
     if (c0 == 't') {
-      switch (p[4] | 0x20u) {
+      switch ((uint32_t)(f0 >> 32) & 0xFF) {
         case 'i': m = 0; break;
         case 'n': m = 1; break;
-        case 'c': m = (p[12] | 0x20u) == 'y' ? 2 : 3; break;
+        case 'c': m = ((uint32_t)(f1 >> 32) & 0xFF) == 'y' ? 2 : 3; break;
         case 'd': m = 4; break;
         case 'a': m = 5; break;
         default: break;
       }
     } else if (c0 == 'i') {
-      m = (p[2] | 0x20u) == 'c' ? 6 : 7;
+      m = ((uint32_t)(f0 >> 16) & 0xFF) == 'c' ? 6 : 7;
     }
     if (m >= 0) {
+      // folded to lower case by OR 0x20 (exact for a comparison with letters: only a letter can fold into a
+      // letter) and compared a word at a time
       const int len = kMemberLens[m];
-      if (p[len] == '"') {
-        bool same = true;
-        for (int j = 0; j < len; ++j) {
-          uint32_t c = p[j];
-          if (c >= 'A' && c <= 'Z') c |= 0x20;
-          same = same && c == (uint8_t)kMemberNames[m][j];
-        }
-        if (same) {
-          *after = p + len + 1;
-          return m;
-        }
+      const uint64_t w0 = kMemberWord0[m], w1 = kMemberWord1[m];
+      const uint64_t m0 = len >= 8 ? ~0ull : (1ull << (8 * len)) - 1;
+      const uint64_t m1 = len > 8 ? (1ull << (8 * (len - 8))) - 1 : 0ull;
+      const uint32_t closing = (uint32_t)((len < 8 ? r0 >> (8 * len) : r1 >> (8 * (len - 8))) & 0xFF);
+      if (closing == '"' && ((f0 ^ w0) & m0) == 0 && ((f1 ^ w1) & m1) == 0) {
+        *after = p + len + 1;
+        return m;
       }
     }
   }
@@ -340,16 +420,45 @@ __device__ int member_fast(const uint8_t* p, const uint8_t* end, const uint8_t**
 // The closing quote of a short string value that holds no escape: returns its length, or -1 when
 // a backslash or control character comes first or it is longer than `limit`.
 __device__ __forceinline__ int plain_string_len(const uint8_t* p, const uint8_t* end, int limit) {
-  for (int j = 0; j <= limit && p + j < end; ++j) {
-    const uint32_t c = p[j];
-    if (c == '"') return j;
-    if (c == '\\' || c < 0x20) return -1;
-  }
-  return -1;
+  // a non-ASCII byte also ends the run: such a value takes the general route, which refuses it as a Guid / date
+  const uint8_t* stop = end - p > limit + 1 ? p + limit + 1 : end;
+  const uint32_t run = plain_run(p, stop);
+  return p + run < stop && p[run] == '"' ? (int)run : -1;
 }
 
+// The first 48 bytes of a short string value (a Guid, a date) held in six registers: the parsers below index it
+// like an array; an index known at compile time costs a shift, a computed one five selects — no memory access.
+struct Chars48 {
+  uint64_t w[6];
+  __device__ __forceinline__ void load(const uint8_t* p, const uint8_t* end) {
+#pragma unroll
+    for (int k = 0; k < 6; ++k) w[k] = p + 8 * k < end ? load8(p + 8 * k) : 0ull;
+  }
+  __device__ __forceinline__ uint32_t operator[](int i) const {
+    const uint64_t x = i < 8 ? w[0] : i < 16 ? w[1] : i < 24 ? w[2] : i < 32 ? w[3] : i < 40 ? w[4] : w[5];
+    return (uint32_t)(x >> ((i & 7) * 8)) & 0xFFu;
+  }
+  // index of the first byte a plain run stops at ('"', '\\', control, non-ASCII), 48 if there is none
+  __device__ __forceinline__ int first_special() const {
+    int at = 48;
+#pragma unroll
+    for (int k = 5; k >= 0; --k) {
+      const uint64_t m = string_special(w[k]);
+      if (m) at = 8 * k + ((__ffsll((long long)m) - 1) >> 3);
+    }
+    return at;
+  }
+};
+
+// the same interface over bytes in memory (the slow path's local buffer)
+struct CharsMem {
+  const uint8_t* p;
+  __device__ __forceinline__ uint32_t operator[](int i) const { return p[i]; }
+};
+
 // "xxxxxxxx-xxxx-xxxx-xxxx-xxxxxxxxxxxx" -> the 16 canonical bytes packed in memory order
-__device__ bool parse_guid(const uint8_t* s, int len, uint4* out) {
+template <typename S>
+__device__ __forceinline__ bool parse_guid(const S& s, int len, uint4* out) {
   if (len != 36) return false;
   uint32_t w[4] = {0, 0, 0, 0};
   int b = 0;
@@ -369,16 +478,18 @@ __device__ bool parse_guid(const uint8_t* s, int len, uint4* out) {
   return true;
 }
 
-__device__ __forceinline__ int two_digits(const uint8_t* s) {
-  const int a = (int)s[0] - '0', b = (int)s[1] - '0';
+template <typename S>
+__device__ __forceinline__ int two_digits(const S& s, int at) {
+  const int a = (int)s[at] - '0', b = (int)s[at + 1] - '0';
   if (a < 0 || a > 9 || b < 0 || b > 9) return -1;
   return a * 10 + b;
 }
 
 // System.Text.Json's DateTime reader (ISO 8601-1 extended profile), see the header comment.
-__device__ bool parse_datetime(const uint8_t* s, int len, int32_t local_offset_min, uint64_t* raw) {
+template <typename S>
+__device__ bool parse_datetime(const S& s, int len, int32_t local_offset_min, uint64_t* raw) {
   if (len < 10 || len > 48) return false;
-  const int yh = two_digits(s), yl = two_digits(s + 2), mo = two_digits(s + 5), d = two_digits(s + 8);
+  const int yh = two_digits(s, 0), yl = two_digits(s, 2), mo = two_digits(s, 5), d = two_digits(s, 8);
   if (yh < 0 || yl < 0 || mo < 0 || d < 0 || s[4] != '-' || s[7] != '-') return false;
   const int y = yh * 100 + yl;
   if (y < 1 || mo < 1 || mo > 12 || d < 1) return false;
@@ -397,14 +508,14 @@ __device__ bool parse_datetime(const uint8_t* s, int len, int32_t local_offset_m
   int i = 10;
   if (i < len) {
     if (s[i] != 'T' || len < 16) return false;
-    const int hh = two_digits(s + 11), mi = two_digits(s + 14);
+    const int hh = two_digits(s, 11), mi = two_digits(s, 14);
     if (hh < 0 || hh > 23 || mi < 0 || mi > 59 || s[13] != ':') return false;
     int ss = 0;
     int64_t frac = 0;
     i = 16;
     if (i < len && s[i] == ':') {
       if (len < 19) return false;
-      ss = two_digits(s + 17);
+      ss = two_digits(s, 17);
       if (ss < 0 || ss > 59) return false;
       i = 19;
       if (i < len && (s[i] == '.' || s[i] == ',')) {
@@ -427,12 +538,12 @@ __device__ bool parse_datetime(const uint8_t* s, int len, int32_t local_offset_m
       } else if (s[i] == '+' || s[i] == '-') {
         const bool neg = s[i] == '-';
         if (len - i < 3) return false;
-        const int oh = two_digits(s + i + 1);
+        const int oh = two_digits(s, i + 1);
         int om = 0;
         i += 3;
         if (i < len) {
           if (s[i] != ':' || len - i < 3) return false;
-          om = two_digits(s + i + 1);
+          om = two_digits(s, i + 1);
           i += 3;
         }
         if (oh < 0 || oh > 14 || om < 0 || om > 59) return false;
@@ -522,17 +633,20 @@ __global__ void __launch_bounds__(128) doc_parse_kernel(uint8_t* text, const uin
     }
     // taskId and the two dates: short strings parsed from a local copy
     if (*p != '"') { status = kDocType; continue; }
-    if (m == 0 && end - p > 37 && p[37] == '"' && parse_guid(p + 1, 36, &id)) {  // the usual 36 plain characters
+    Chars48 cs;  // the value's first 48 bytes in registers: Guid and dates are parsed without another load
+    cs.load(p + 1, end);
+    if (m == 0 && end - p > 37 && cs[36] == '"' && parse_guid(cs, 36, &id)) {  // the usual 36 plain characters
       p += 38;
       continue;
     }
-    const int plain = plain_string_len(p + 1, end, 48);
+    int plain = cs.first_special();
+    if (plain >= 48 || p + 1 + plain >= end || cs[plain] != '"') plain = plain_string_len(p + 1, end, 48);
     if (plain >= 0) {  // no escape inside: parsed where it lies
       if (m == 0) {
-        if (!parse_guid(p + 1, plain, &id)) status = kDocGuid;
+        if (!parse_guid(cs, plain, &id)) status = kDocGuid;
       } else {
         uint64_t raw = 0;
-        if (!parse_datetime(p + 1, plain, local_offset_min, &raw)) status = kDocDate;
+        if (!parse_datetime(cs, plain, local_offset_min, &raw)) status = kDocDate;
         else if (m == 3) created = raw;
         else due = raw;
       }
@@ -543,11 +657,12 @@ __global__ void __launch_bounds__(128) doc_parse_kernel(uint8_t* text, const uin
     int blen = 0;
     p = read_string_local(p + 1, end, buf, &blen);
     if (!p) { status = kDocString; continue; }
+    const CharsMem bs{buf};
     if (m == 0) {
-      if (!parse_guid(buf, blen, &id)) status = kDocGuid;
+      if (!parse_guid(bs, blen, &id)) status = kDocGuid;
     } else {
       uint64_t raw = 0;
-      if (blen > 48 || !parse_datetime(buf, blen, local_offset_min, &raw)) status = kDocDate;
+      if (blen > 48 || !parse_datetime(bs, blen, local_offset_min, &raw)) status = kDocDate;
       else if (m == 3) created = raw;
       else due = raw;
     }
@@ -566,7 +681,7 @@ __global__ void __launch_bounds__(128) doc_parse_kernel(uint8_t* text, const uin
   for (int c = 0; c < 3; ++c) {
     out.str_start[c][i] = (uint64_t)(sstart[c] - base);
     out.str_len[c][i] = slen[c];
-    out.str_hash[c][i] = status == kDocOk ? tt_hash64(sstart[c], slen[c]) : 0ull;
+    out.str_hash[c][i] = status == kDocOk ? hash_text(sstart[c], slen[c]) : 0ull;
   }
 }
 
