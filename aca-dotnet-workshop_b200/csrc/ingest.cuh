@@ -746,6 +746,14 @@ __global__ void id_half_keys_kernel(const uint4* id, const uint32_t* rows, int64
   vals[i] = r;
 }
 
+// positions of a sorted key array whose key equals its left neighbour's (0 = all keys distinct)
+__global__ void adjacent_equal_kernel(const unsigned long long* keys, int64_t n, unsigned long long* count) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const bool same = i >= 1 && i < n && keys[i] == keys[i - 1];
+  const uint32_t m = __ballot_sync(0xFFFFFFFFu, same);
+  if ((threadIdx.x & 31) == 0 && m) atomicAdd(count, (unsigned long long)__popc(m));
+}
+
 // ---- dictionary encoding of one string member ------------------------------------------------
 __global__ void dict_keys_kernel(const uint64_t* hash, int64_t n, unsigned long long* keys, uint32_t* vals) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -755,10 +763,14 @@ __global__ void dict_keys_kernel(const uint64_t* hash, int64_t n, unsigned long 
   }
 }
 
+// Byte equality of two strings of the text, eight bytes per step (both words of a step are requested together).
 __device__ __forceinline__ bool same_string(const uint8_t* text, uint64_t a, uint32_t la, uint64_t b, uint32_t lb) {
   if (la != lb) return false;
-  for (uint32_t j = 0; j < la; ++j)
-    if (text[a + j] != text[b + j]) return false;
+  for (uint32_t j = 0; j < la; j += 8) {
+    uint64_t x = load8(text + a + j) ^ load8(text + b + j);
+    if (la - j < 8) x &= (1ull << (8 * (la - j))) - 1;
+    if (x) return false;
+  }
   return true;
 }
 

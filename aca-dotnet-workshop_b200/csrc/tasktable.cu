@@ -785,27 +785,44 @@ int32_t sweep_owned(tt_table* t, int32_t mode, int32_t flags, int64_t today, int
 }
 
 // The TaskId index: rows in TaskId order (t->id_order) for a table whose rows are not.  Built on
-// the device by two stable 64-bit radix sorts, the low 8 canonical bytes first, then the high 8
-// bytes of the rows in that order.  No-op while the table itself is in TaskId order or the index
-// still covers every row (tt_insert_task drops it when it appends an out-of-order id).
+// the device: one stable 64-bit radix sort of the HIGH 8 canonical bytes orders the rows whenever those
+// are all distinct (Guid.NewGuid() ids: 58 random bits up there) — a count of equal neighbours checks it;
+// otherwise two sorts, the low 8 bytes first, then the high 8 bytes of the rows in that order.  No-op while
+// the table itself is in TaskId order or the index still covers every row (tt_insert_task drops it when
+// it appends an out-of-order id).
 int32_t ensure_id_order(tt_table* t) {
   if (t->ids_sorted || t->id_order || t->n == 0) return TT_OK;
   const int64_t n = t->n;
   cudaStream_t st = t->stream;
   cudaError_t e = t->sort.reserve(n);
   int w = 0;
+  unsigned long long ties = 1;
   if (e == cudaSuccess) {
-    tt::id_half_keys_kernel<<<grid_for(n, 256), 256, 0, st>>>(t->task_id, nullptr, n, 0, t->sort.keys[0], t->sort.vals[0]);
+    tt::id_half_keys_kernel<<<grid_for(n, 256), 256, 0, st>>>(t->task_id, nullptr, n, 1, t->sort.keys[0], t->sort.vals[0]);
     e = tt::radix_sort_pairs(st, t->sort, n, 64, &w);
   }
+  if (e == cudaSuccess) e = cudaMemsetAsync(t->d_small, 0, 8, st);
   if (e == cudaSuccess) {
-    tt::id_half_keys_kernel<<<grid_for(n, 256), 256, 0, st>>>(t->task_id, t->sort.vals[w], n, 1, t->sort.keys[w ^ 1],
-                                                              t->sort.vals[w ^ 1]);
-    if (w == 0) {  // radix_sort_pairs starts from buffer pair 0
+    tt::adjacent_equal_kernel<<<grid_for(n, 256), 256, 0, st>>>(t->sort.keys[w], n, t->d_small);
+    e = cudaMemcpyAsync(&ties, t->d_small, 8, cudaMemcpyDeviceToHost, st);
+  }
+  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+  if (e == cudaSuccess && ties != 0) {  // some ids share their high half: the full two-key sort
+    if (w != 0) {  // radix_sort_pairs starts from buffer pair 0
       std::swap(t->sort.keys[0], t->sort.keys[1]);
       std::swap(t->sort.vals[0], t->sort.vals[1]);
     }
+    tt::id_half_keys_kernel<<<grid_for(n, 256), 256, 0, st>>>(t->task_id, nullptr, n, 0, t->sort.keys[0], t->sort.vals[0]);
     e = tt::radix_sort_pairs(st, t->sort, n, 64, &w);
+    if (e == cudaSuccess) {
+      tt::id_half_keys_kernel<<<grid_for(n, 256), 256, 0, st>>>(t->task_id, t->sort.vals[w], n, 1, t->sort.keys[w ^ 1],
+                                                                t->sort.vals[w ^ 1]);
+      if (w == 0) {
+        std::swap(t->sort.keys[0], t->sort.keys[1]);
+        std::swap(t->sort.vals[0], t->sort.vals[1]);
+      }
+      e = tt::radix_sort_pairs(st, t->sort, n, 64, &w);
+    }
   }
   uint32_t* order = nullptr;
   if (e == cudaSuccess) e = cudaMalloc(&order, (size_t)n * 4);
