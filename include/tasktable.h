@@ -478,6 +478,8 @@ int32_t tt_exchange_create_root(int32_t device, int32_t world, int64_t cap_per_s
 int32_t tt_exchange_attach(int32_t device, int32_t rank, int32_t world, int64_t cap_per_shard, int64_t max_tiles_per_shard,
                            int32_t flags, const tt_peer_handle* handle, tt_exchange** out);
 int32_t tt_exchange_attach_local(tt_exchange* root, int32_t device, int32_t rank, tt_exchange** out);
+/* Destroy the shards' exchanges before the root's, and read or free every result of tt_exchange_collect first (an
+ * unread TT_ORDER_ROWS result still points into the root's buffers). */
 int32_t tt_exchange_destroy(tt_exchange* ex);
 int32_t tt_exchange_slot_bytes(const tt_exchange* ex, uint64_t* bytes);
 /* flags: TT_SWEEP_* as for tt_sweep_device (TT_SWEEP_ASYNC: finish with tt_sweep_wait on the table).

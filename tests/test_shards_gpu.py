@@ -299,3 +299,21 @@ def test_exchange_across_two_processes(oracle, tmp_path):
             child.kill()
     root.close()
     table.close()
+
+
+def test_sharded_manager_with_empty_shards(oracle):
+    """Two tasks in a four-shard manager: two shards hold nothing, yet every list call still gets an answer from
+    each of them (an empty shard publishes "no hits" for the tick)."""
+    st = tt.ShardedTable([0] * 4)
+    assert st.get_yesterdays_due(tt.MODE_STORE).count == 0 and st.sweep(tt.MODE_STORE)[0].count == 0
+    a = bytes([0x10]) + bytes(15)   # shard 0
+    b = bytes([0xF0]) + bytes(15)   # shard 3
+    assert st.insert_task(b, (TODAY - 5) | (1 << 62), YDAY, b"x@y")[0] == 3
+    assert st.insert_task(a, (TODAY - 9) | (1 << 62), YDAY, b"x@y")[0] == 0
+    res = st.get_yesterdays_due(tt.MODE_STORE)   # created order: a (older) first, although b was inserted first
+    assert res.count == 2 and [bytes(i) for i in res.ids()] == [a, b] and res.rows().tolist() == [0, 1]
+    assert res.shard_counts()[:4] == [1, 0, 0, 1]
+    assert [bytes(i) for i in st.get_by_creator(b"x@y").ids()] == [b, a]   # descending
+    res, n_marked, _ = st.sweep(tt.MODE_STORE)
+    assert res.count == 2 and n_marked == 2 and st.get_yesterdays_due(tt.MODE_STORE).count == 0
+    st.close()
