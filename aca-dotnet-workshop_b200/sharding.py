@@ -279,16 +279,16 @@ class ShardExchange:
         self._tt, self.group, self.device_index = tt, group, device_index
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
-        self.cap = (cap_per_shard + 7) // 8 * 8
         dev = torch.device("cuda", device_index)
-        mine = torch.tensor([first_row, -(-n_rows // tile_rows)], dtype=torch.int64, device=dev)
-        every = [torch.zeros(2, dtype=torch.int64, device=dev) for _ in range(self.world)]
+        mine = torch.tensor([first_row, -(-n_rows // tile_rows), (cap_per_shard + 7) // 8 * 8], dtype=torch.int64, device=dev)
+        every = [torch.zeros(3, dtype=torch.int64, device=dev) for _ in range(self.world)]
         if self.world > 1:
             dist.all_gather(every, mine, group=group)
         else:
             every = [mine]
         self.first_rows = [int(x[0].item()) for x in every]
         self.max_tiles = max(1, max(int(x[1].item()) for x in every))
+        self.cap = max(int(x[2].item()) for x in every)  # shards need not be the same size: the slots fit the largest
         payload = [None]
         self.ex = None
         if self.rank == 0:

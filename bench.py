@@ -42,6 +42,10 @@ def parse():
                     help="what the shards' placement kernels store into rank 0's buffer over NVLink (N > 1, tt_exchange_*): "
                          "rows = the compact row lists (2-byte in-tile offsets + per-tile counts), each shard keeping its "
                          "TaskIds; ids = the 16-byte TaskIds as well")
+    ap.add_argument("--root-share", type=float, default=0.0,
+                    help="N > 1: rank 0's shard as a fraction of an equal share (rank 0 also collects every shard's list, "
+                         "so its TaskId range is made smaller and the other ranks split the rest equally); 0 = the "
+                         "measured default for N (1.0 / 0.9 / 0.8 / 0.72 at 1 / 2 / 4 / 8 GPUs)")
     ap.add_argument("--no-extra", action="store_true", help="N > 1: skip the strong-scaling / mixed / ids-at-root passes")
     ap.add_argument("--cpu-sample-rows", type=int, default=10_000_000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -307,12 +311,20 @@ def run_b200(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
-    if args.scaling == "weak":
-        n_total, n_rows, first = args.rows * world, args.rows, args.rows * rank
-    else:
-        n_total = args.rows
-        first, last = pkg.shard_rows(n_total, world, rank)
-        n_rows = last - first
+    share = args.root_share if args.root_share > 0 else {1: 1.0, 2: 0.9, 4: 0.8, 8: 0.72}.get(world, 0.72)
+
+    def shard_of(total, r):
+        """[first, last) rows of rank r: TaskId-range shards; rank 0's range is `share` of an equal one (whole tiles)."""
+        if world == 1:
+            return 0, total
+        root = int(total / world * share) // 8192 * 8192
+        rest = total - root
+        cut = lambda k: root + rest * k // (world - 1)   # k = 0 .. world - 1 over the other ranks
+        return (0, root) if r == 0 else (cut(r - 1), cut(r))
+
+    n_total = args.rows * world if args.scaling == "weak" else args.rows
+    first, last = shard_of(n_total, rank)
+    n_rows = last - first
     with_root_ids = args.exchange == "ids"
     run = ShardRun(pkg, torch, dist, dev, local, rank, world, n_total, first, n_rows,
                    tt.EXCHANGE_IDS if with_root_ids else 0, local_ids=not with_root_ids)
@@ -390,7 +402,7 @@ def run_b200(args):
             extra["ids_at_root_tasks_per_sec"] = n_total * x_steps / (m["total_ms"] * 1e-3)
             r2.close()
         # BASELINE.json config 3: ONE table of args.rows tasks sharded by TaskId range over the N GPUs
-        s_first, s_last = pkg.shard_rows(args.rows, world, rank)
+        s_first, s_last = shard_of(args.rows, rank)
         r3 = ShardRun(pkg, torch, dist, dev, local, rank, world, args.rows, s_first, s_last - s_first, 0)
         m = r3.timed(x_steps, x_warm)
         extra["strong_ms_per_step"] = m["ms_per_step"]
@@ -461,8 +473,10 @@ def run_b200(args):
             "config": {
                 "workload": f"overdue sweep (cron tick, STORE semantics) over a synthetic {n_total}-task table, "
                             "config-5 mix: 5% due yesterday, 1% adversarial inexact, 50% completed",
-                "rows_per_gpu": n_rows, "n_total": n_total, "hits_per_step": head["hits"],
-                "sharding": "TaskId range" if world > 1 else "single shard",
+                "rows_per_gpu": n_total // world, "rows_rank0": n_rows, "root_share": share if world > 1 else None,
+                "n_total": n_total, "hits_per_step": head["hits"],
+                "sharding": ("TaskId ranges; rank 0, which also collects every shard's list, owns root_share of an equal "
+                             "range, the other ranks split the rest equally") if world > 1 else "single shard",
                 "exchange": exchange,
                 "l2": f"inputs {n_rows * BYTES_PER_TASK / 1e6:.0f} MB per step vs 126 MB L2; overdue plane rewritten between steps",
                 "reset": "overdue plane restored between steps outside the timed region (per-step CUDA events summed)",
