@@ -416,7 +416,8 @@ __global__ void __launch_bounds__(kGroupThreads) place_group_kernel(const uint32
   __shared__ uint32_t s_slot[GT];
   __shared__ uint32_t s_pre[GT + 1];
   __shared__ uint32_t s_base;
-  __shared__ __align__(16) uint16_t s_off[kGroupStage + 8];
+  constexpr int kStage = GT * 512 > kGroupStage ? GT * 512 : kGroupStage;  // about 2.5 x the usual hits of GT tiles
+  __shared__ __align__(16) uint16_t s_off[kStage + 8];
   const uint32_t tid = threadIdx.x;
   const uint32_t t0 = blockIdx.x * GT;
   if (tid < 32) {
@@ -447,7 +448,7 @@ __global__ void __launch_bounds__(kGroupThreads) place_group_kernel(const uint32
   if (total == 0) return;
   const uint32_t base = s_base;
   const uint32_t shift = base & 7u;  // staged index = list index - (base - shift): 16-byte chunks line up
-  const bool staged = push.off16 != nullptr && total <= (uint32_t)kGroupStage;
+  const bool staged = push.off16 != nullptr && total <= (uint32_t)kStage;
 
   for (uint32_t h0 = tid; h0 < total; h0 += kGroupThreads * UNROLL) {
     uint32_t r[UNROLL];

@@ -637,6 +637,8 @@ int32_t sweep_run(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_
         case 2: TT_PLACE_LAUNCH(2, 2); break;
         case 4: TT_PLACE_LAUNCH(4, 4); break;
         case 8: TT_PLACE_LAUNCH(8, 4); break;
+        case 16: TT_PLACE_LAUNCH(16, 4); break;
+        case 32: TT_PLACE_LAUNCH(32, 4); break;
         default: TT_PLACE_LAUNCH(1, 1); break;
       }
 #undef TT_PLACE_LAUNCH
