@@ -67,7 +67,7 @@ def main():
     # the fused exchange behind the C ABI (tt_exchange_*): a fresh copy of the shard, ticked straight into rank 0's
     # buffer with TaskIds and creation times; rank 0 waits for the epoch words on the device
     table_p = pkg.TaskTable(local).generate(cfg, plan.first_row, plan.n_rows)
-    sx = pkg.ShardExchange(plan.first_row, plan.n_rows, cap, local, tt.EXCHANGE_IDS | tt.EXCHANGE_CREATED | tt.EXCHANGE_GAP8)
+    sx = pkg.ShardExchange(plan.first_row, plan.n_rows, cap, local, tt.EXCHANGE_IDS | tt.EXCHANGE_CREATED)
     p_rows = torch.empty(sx.cap, dtype=torch.int32, device=dev)
     p_ids = torch.empty((sx.cap, 16), dtype=torch.uint8, device=dev)
     for tick in range(3):  # the later ticks find nothing: the slots must be overwritten, not appended to
