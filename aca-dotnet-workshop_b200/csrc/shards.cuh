@@ -30,8 +30,7 @@ struct SlotHeader {
   unsigned long long epoch;     // ticks this shard has published (written last, release at system scope)
   unsigned long long count;     // hits stored in the slot by the current tick
   unsigned long long consumed;  // slot 0 only: epochs the root has finished reading
-  unsigned long long n_ovf;     // one-byte form: entries of the slot's overflow list for the current tick
-  unsigned long long pad[28];
+  unsigned long long pad[29];
 };
 static_assert(sizeof(SlotHeader) == 256, "slot header is 256 bytes");
 
@@ -107,9 +106,6 @@ struct SlotLayout {
   size_t off16;       // u16[cap]
   size_t ids;         // uint4[cap], 0 = not exchanged
   size_t created;     // u64[cap],  0 = not exchanged
-  size_t ovf;         // GapOverflow[ovf_cap], 0 = the two-byte form is in use
-  uint32_t ovf_cap;   // 32 per tile: an entry stands for a distance of more than 255 rows inside one 8192-row tile
-  uint32_t gap8;      // 1: the off16 region holds one gap byte per hit (sweep.cuh PushTarget::gap8) instead of u16 offsets
   size_t bytes;       // slot stride
 };
 
@@ -124,38 +120,11 @@ __global__ void __launch_bounds__(256) shard_expand_kernel(const unsigned char* 
   const uint32_t cnt = reinterpret_cast<const uint32_t*>(slot + lay.tile_count)[t];
   if (cnt == 0) return;
   const uint32_t first = reinterpret_cast<const uint32_t*>(slot + lay.tile_first)[t];
-  uint32_t* dst = rows_out + meta->base[r] + first;
-  const uint32_t lane = threadIdx.x & 31u, row0 = t * TT_TILE_ROWS;
-  if (lay.gap8) {
-    // one gap byte per hit: offset of hit k = (sum of (byte + 1) over the tile's hits up to k) - 1; a warp scans 32 hits
-    // per step and carries the running sum (distances above 255 are added by shard_gap_fix_kernel afterwards)
-    const uint8_t* g = slot + lay.off16 + first;
-    uint32_t carry = 0;
-    for (uint32_t k0 = 0; k0 < cnt; k0 += 256) {
-      uint32_t v[8];
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const uint32_t k = k0 + 32u * j + lane;
-        v[j] = k < cnt ? (uint32_t)g[k] + 1u : 0u;
-      }
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        uint32_t incl = v[j];
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-          const uint32_t up = __shfl_up_sync(0xFFFFFFFFu, incl, d);
-          if (lane >= (uint32_t)d) incl += up;
-        }
-        const uint32_t k = k0 + 32u * j + lane;
-        if (k < cnt) dst[k] = row0 + carry + incl - 1u;
-        carry += __shfl_sync(0xFFFFFFFFu, incl, 31);
-      }
-    }
-    return;
-  }
   const uint16_t* src = reinterpret_cast<const uint16_t*>(slot + lay.off16) + first;
+  uint32_t* dst = rows_out + meta->base[r] + first;
   // all of a lane's loads go out before its first store: a tile of the usual density (about 200 hits) is in
   // flight at once instead of one 64-byte piece per warp (measured at 8 GPUs: the dependent form ran at 2.7 TB/s)
+  const uint32_t lane = threadIdx.x & 31u, row0 = t * TT_TILE_ROWS;
   uint16_t v[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
@@ -168,26 +137,6 @@ __global__ void __launch_bounds__(256) shard_expand_kernel(const unsigned char* 
     if (k < cnt) dst[k] = row0 + v[j];
   }
   for (uint32_t k = lane + 256u; k < cnt; k += 32) dst[k] = row0 + src[k];  // denser tiles: the rest
-}
-
-// One-byte form, second step: every overflow entry {tile, k, m} moves hit k of its tile and all later hits of that
-// tile up by 255 * m rows.  One warp per entry; several entries of one tile overlap, hence the atomic adds.
-__global__ void __launch_bounds__(256) shard_gap_fix_kernel(const unsigned char* base, SlotLayout lay, const CollectMeta* meta,
-                                                             uint32_t* rows_out, uint32_t first_slot) {
-  const uint32_t r = blockIdx.y + first_slot;
-  const unsigned char* slot = base + (size_t)r * lay.bytes;
-  const unsigned long long have = reinterpret_cast<const SlotHeader*>(slot)->n_ovf;
-  const uint32_t n = have < lay.ovf_cap ? (uint32_t)have : lay.ovf_cap;
-  const GapOverflow* list = reinterpret_cast<const GapOverflow*>(slot + lay.ovf);
-  const uint32_t* tile_count = reinterpret_cast<const uint32_t*>(slot + lay.tile_count);
-  const uint32_t* tile_first = reinterpret_cast<const uint32_t*>(slot + lay.tile_first);
-  const uint32_t lane = threadIdx.x & 31u, warps = gridDim.x * (blockDim.x >> 5);
-  for (uint32_t e = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); e < n; e += warps) {
-    const GapOverflow o = list[e];
-    const uint32_t cnt = tile_count[o.tile];
-    uint32_t* dst = rows_out + meta->base[r] + tile_first[o.tile];
-    for (uint32_t k = o.k + lane; k < cnt; k += 32) atomicAdd(dst + k, 255u * o.m);
-  }
 }
 
 // Sort keys of the cross-shard OrderBy(TaskCreatedOn): key = the pushed ticks, value = position in

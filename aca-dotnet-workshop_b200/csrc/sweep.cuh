@@ -376,20 +376,6 @@ struct PushTarget {
   uint4* ids;                   // [cap] TaskIds of the hits in row order, or null (the sharded GetYesterdaysDueTasks)
   unsigned long long* created;  // [cap] TaskCreatedOn (.NET dateData) of the hits, or null (the cross-shard OrderBy)
   uint32_t* tile_first;         // [num_tiles] offset of each tile's hits in the row-ordered list, or null
-  // The one-byte form of the offsets (instead of off16): per hit, in row order, the distance to the previous hit
-  // of its tile (the first hit: to the tile's start) minus one, modulo 255.  A distance above 255 — one hit in
-  // about 600 at 2.5 % density — leaves an entry {tile, hit index in the tile, multiples of 255} in a list of
-  // THIS GPU (local atomics); the tail kernel forwards the list.  Half the bytes on the wire of the two-byte form.
-  uint8_t* gap8;                // [cap + 16]; 16-byte aligned; null = not used
-  struct GapOverflow* ovf;      // this GPU's list and its counter (count at ovf_count), ovf_cap entries
-  unsigned int* ovf_count;
-  uint32_t ovf_cap;
-};
-
-struct GapOverflow {
-  uint32_t tile;  // tile number inside the shard
-  uint16_t k;     // index of the hit among the tile's hits: its row and every later one of the tile move up
-  uint16_t m;     // by 255 * m
 };
 
 // What a sharded tick adds around K3g (shards.cuh): before it, wait until the root has finished
@@ -400,8 +386,6 @@ struct ShardHook {
   const unsigned char* wait_slot0;  // null = no wait (the root's own shard)
   unsigned long long wait_value;
   unsigned long long timeout_ns;
-  struct GapOverflow* ovf_remote;          // one-byte form: the slot's overflow list and its count (null otherwise)
-  unsigned long long* ovf_remote_count;
 };
 
 // Where the row-ordered list of the CTA's first tile starts: hits stored in all earlier tiles =
@@ -463,29 +447,22 @@ __global__ void __launch_bounds__(kGroupThreads) place_group_kernel(const uint32
   const uint32_t total = s_pre[GT];
   if (total == 0) return;
   const uint32_t base = s_base;
-  const bool bytes = push.gap8 != nullptr;
-  const uint32_t shift = bytes ? base & 15u : base & 7u;  // staged index = list index - (base - shift): 16-byte chunks line up
-  const bool staged = (push.off16 != nullptr || bytes) && total <= (uint32_t)kStage;
-  uint8_t* const s_gap = reinterpret_cast<uint8_t*>(s_off);  // the same staging area, one byte per hit
+  const uint32_t shift = base & 7u;  // staged index = list index - (base - shift): 16-byte chunks line up
+  const bool staged = push.off16 != nullptr && total <= (uint32_t)kStage;
 
   for (uint32_t h0 = tid; h0 < total; h0 += kGroupThreads * UNROLL) {
-    uint32_t r[UNROLL], prev[UNROLL], kt[UNROLL];
+    uint32_t r[UNROLL];
     uint4 id[UNROLL];
     unsigned long long cr[UNROLL];
 #pragma unroll
     for (int j = 0; j < UNROLL; ++j) {
       const uint32_t h = h0 + j * kGroupThreads;
       r[j] = 0;
-      prev[j] = ~0u;  // "the row before the tile's first"
-      kt[j] = 0;
       if (h < total) {
         uint32_t k = 0;
 #pragma unroll
         for (int q = 1; q < GT; ++q) k += h >= s_pre[q] ? 1u : 0u;
-        const uint32_t at = h - s_pre[k];
-        r[j] = list[s_slot[k] + at];
-        if (bytes && at) prev[j] = list[s_slot[k] + at - 1];  // a tile's hits ascend in K1's list
-        kt[j] = k | (at << 8);
+        r[j] = list[s_slot[k] + (h - s_pre[k])];
       }
     }
     if (out_ids || push.ids) {
@@ -501,29 +478,10 @@ __global__ void __launch_bounds__(kGroupThreads) place_group_kernel(const uint32
       const uint32_t h = h0 + j * kGroupThreads;
       if (h < total) {
         const uint16_t off = (uint16_t)(r[j] & (TILE_ROWS - 1));
-        if (bytes) {
-          const uint32_t before = prev[j] == ~0u ? ~0u : prev[j] & (TILE_ROWS - 1);  // -1 for the tile's first hit
-          const uint32_t gap = off - before - 1u;                                      // distance - 1, 0 .. TILE_ROWS - 1
-          const uint8_t b = (uint8_t)(gap % 255u);
-          if (gap >= 255u) {
-            const unsigned int e = atomicAdd(push.ovf_count, 1u);
-            if (e < push.ovf_cap) {
-              GapOverflow o;
-              o.tile = t0 + (kt[j] & 0xFFu);
-              o.k = (uint16_t)(kt[j] >> 8);
-              o.m = (uint16_t)(gap / 255u);
-              push.ovf[e] = o;
-            }
-          }
-          if (staged)
-            s_gap[shift + h] = b;
-          else
-            push.gap8[base + h] = b;
-        } else if (staged) {
+        if (staged)
           s_off[shift + h] = off;
-        } else if (push.off16) {
+        else if (push.off16)
           push.off16[base + h] = off;
-        }
         if (out_rows) out_rows[base + h] = r[j];
         if (out_ids) out_ids[base + h] = id[j];
         if (push.ids) push.ids[base + h] = id[j];
@@ -533,18 +491,6 @@ __global__ void __launch_bounds__(kGroupThreads) place_group_kernel(const uint32
   }
   if (!staged) return;
   __syncthreads();
-  if (bytes) {
-    uint8_t* dst8 = push.gap8 + (base - shift);
-    const uint32_t lo8 = shift, hi8 = shift + total;
-    for (uint32_t a = tid * 16; a < hi8; a += kGroupThreads * 16) {
-      if (a >= lo8 && a + 16 <= hi8) {
-        *reinterpret_cast<uint4*>(dst8 + a) = *reinterpret_cast<const uint4*>(s_gap + a);
-      } else {
-        for (uint32_t e = a > lo8 ? a : lo8; e < a + 16 && e < hi8; ++e) dst8[e] = s_gap[e];
-      }
-    }
-    return;
-  }
   uint16_t* dst = push.off16 + (base - shift);
   const uint32_t lo = shift, hi = shift + total;  // staged entries [lo, hi) are valid
   for (uint32_t v = tid; v * 8 < hi; v += kGroupThreads) {
@@ -564,29 +510,10 @@ __global__ void __launch_bounds__(kGroupThreads) place_group_kernel(const uint32
 // root GPU's slot: the kernel boundary has made this shard's stores into the root's memory
 // complete, the system-scope fence orders the epoch word after them, and the root waits on the
 // word (shard_wait_kernel) instead of on a collective.
-// What the tail forwards for the one-byte form: this GPU's overflow list -> the slot (possibly on another GPU).
-struct TailOverflow {
-  const GapOverflow* local;
-  unsigned int* local_count;  // reset to 0 afterwards
-  uint32_t cap;
-  GapOverflow* remote;
-  unsigned long long* remote_count;
-};
-
 __global__ void sweep_tail_kernel(SweepCtl* ctl, SweepOut* out, uint32_t* group_sum, uint32_t n_groups, uint32_t* sub_sum,
                                   uint32_t n_subs, unsigned long long* push_count, unsigned long long* epoch_word,
-                                  unsigned long long epoch, TailOverflow ovf) {
+                                  unsigned long long epoch) {
   const unsigned long long cursor = ctl->cursor, stored = ctl->stored;
-  if (ovf.local_count) {
-    const unsigned int have = *ovf.local_count;
-    const unsigned int n = have < ovf.cap ? have : ovf.cap;
-    for (unsigned int e = threadIdx.x; e < n; e += blockDim.x) ovf.remote[e] = ovf.local[e];
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      *ovf.remote_count = have;  // above cap = the list did not fit: the collect refuses the slot
-      *ovf.local_count = 0;
-    }
-  }
   for (uint32_t k = threadIdx.x; k < n_groups; k += blockDim.x) group_sum[k] = 0;
   if (sub_sum)
     for (uint32_t k = threadIdx.x; k < n_subs; k += blockDim.x) sub_sum[k] = 0;

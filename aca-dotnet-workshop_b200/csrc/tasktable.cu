@@ -114,9 +114,6 @@ struct tt_table {
   uint32_t* tile_words = nullptr;   // [3][n_tiles]
   uint32_t* group_sum = nullptr;    // [n_groups] then [n_subs]: K1's partial sums of the per-tile counts
   int64_t n_tiles = 0, n_groups = 0, n_subs = 0;
-  tt::GapOverflow* ovf_list = nullptr;  // sharded ticks in the one-byte form: this GPU's overflow list (32 per tile)
-  unsigned int* ovf_count = nullptr;    // and its counter (zero between ticks: the tail kernel resets it)
-  int64_t ovf_cap = 0;
   bool ctl_clean = false;           // control block and partial sums are in their start state (the last tick's tail kernel ran)
   tt::SweepOut* h_out = nullptr;    // the tick's outcome: mapped pinned host memory the tail kernel writes
   tt::SweepOut* d_out = nullptr;    // its device address
@@ -256,11 +253,6 @@ void free_columns(tt_table* t) {
   cudaFree(t->tile_words);
   cudaFree(t->group_sum);
   cudaFree(t->hit_list);
-  cudaFree(t->ovf_list);
-  cudaFree(t->ovf_count);
-  t->ovf_list = nullptr;
-  t->ovf_count = nullptr;
-  t->ovf_cap = 0;
   for (tt_table::StrColumn* c : {&t->name_col, &t->assignee_col}) {
     cudaFree(c->ref);
     cudaFree(c->off);
@@ -665,17 +657,9 @@ int32_t sweep_run(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_
   }
   // the epilogue: outcome -> mapped host memory (and the push target), scratch back to its start state,
   // the epoch word of a sharded tick
-  tt::TailOverflow tail_ovf = {nullptr, nullptr, 0, nullptr, nullptr};
-  if (push && push->gap8 && hook && hook->ovf_remote) {
-    tail_ovf.local = push->ovf;
-    tail_ovf.local_count = push->ovf_count;
-    tail_ovf.cap = push->ovf_cap;
-    tail_ovf.remote = hook->ovf_remote;
-    tail_ovf.remote_count = hook->ovf_remote_count;
-  }
   tt::sweep_tail_kernel<<<1, 256, 0, stream>>>(t->ctl, t->d_out, t->group_sum, n_groups, p.sub_sum, n_subs,
                                               push ? push->count : nullptr, hook ? hook->epoch_word : nullptr,
-                                              hook ? hook->epoch : 0, tail_ovf);
+                                              hook ? hook->epoch : 0);
   TT_CUDA(cudaGetLastError());
   st->launches += 1;
   if (timing) TT_CUDA(cudaEventRecord(t->ev2, stream));
@@ -1165,10 +1149,6 @@ int32_t tt_sweep_push(tt_table* t, int32_t mode, int32_t flags, int64_t today_lo
   push.ids = nullptr;
   push.created = nullptr;
   push.tile_first = nullptr;
-  push.gap8 = nullptr;
-  push.ovf = nullptr;
-  push.ovf_count = nullptr;
-  push.ovf_cap = 0;
   return sweep_run(t, mode, flags, today_local_ticks, run_at_utc_ticks, 0, d_rows, (uint4*)d_ids, cap, h_stats,
                    stream ? (cudaStream_t)stream : t->stream, &push);
 }

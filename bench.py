@@ -38,10 +38,10 @@ def parse():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--rows", type=int, default=1_000_000_000, help="rows per GPU (weak) or in total (strong)")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
-    ap.add_argument("--exchange", default="rows", choices=["rows", "rows16", "ids"],
+    ap.add_argument("--exchange", default="rows", choices=["rows", "ids"],
                     help="what the shards' placement kernels store into rank 0's buffer over NVLink (N > 1, tt_exchange_*): "
-                         "rows = the compact row lists (one gap byte per hit + per-tile counts), each shard keeping its "
-                         "TaskIds; rows16 = the same as 2-byte in-tile offsets; ids = the 16-byte TaskIds as well")
+                         "rows = the compact row lists (2-byte in-tile offsets + per-tile counts), each shard keeping its "
+                         "TaskIds; ids = the 16-byte TaskIds as well")
     ap.add_argument("--root-share", type=float, default=0.0,
                     help="N > 1: rank 0's shard as a fraction of an equal share (rank 0 also collects every shard's list, "
                          "so its TaskId range can be made smaller while the other ranks split the rest equally); 0 = 1.0, equal "
@@ -328,9 +328,8 @@ def run_b200(args):
     first, last = shard_of(n_total, rank)
     n_rows = last - first
     with_root_ids = args.exchange == "ids"
-    form = 0 if args.exchange == "rows16" else tt.EXCHANGE_GAP8
     run = ShardRun(pkg, torch, dist, dev, local, rank, world, n_total, first, n_rows,
-                   (tt.EXCHANGE_IDS if with_root_ids else 0) | form, local_ids=not with_root_ids)
+                   tt.EXCHANGE_IDS if with_root_ids else 0, local_ids=not with_root_ids)
     clocks = ClockSampler(local)
     head = run.timed(args.steps, args.warmup, clocks_for=clocks)
     value = n_total * args.steps / (head["total_ms"] * 1e-3)
@@ -399,14 +398,14 @@ def run_b200(args):
         x_steps, x_warm = max(3, min(args.steps, 10)), max(3, min(args.warmup, 3))
         if args.scaling == "weak" and not with_root_ids:
             # the same weak-scaled tick with the 16-byte TaskIds ALSO delivered into the root's slots (fused into K3g)
-            r2 = ShardRun(pkg, torch, dist, dev, local, rank, world, n_total, first, n_rows, tt.EXCHANGE_IDS | form, local_ids=False)
+            r2 = ShardRun(pkg, torch, dist, dev, local, rank, world, n_total, first, n_rows, tt.EXCHANGE_IDS, local_ids=False)
             m = r2.timed(x_steps, x_warm)
             extra["ids_at_root_ms_per_step"] = m["ms_per_step"]
             extra["ids_at_root_tasks_per_sec"] = n_total * x_steps / (m["total_ms"] * 1e-3)
             r2.close()
         # BASELINE.json config 3: ONE table of args.rows tasks sharded by TaskId range over the N GPUs
         s_first, s_last = shard_of(args.rows, rank)
-        r3 = ShardRun(pkg, torch, dist, dev, local, rank, world, args.rows, s_first, s_last - s_first, form)
+        r3 = ShardRun(pkg, torch, dist, dev, local, rank, world, args.rows, s_first, s_last - s_first, 0)
         m = r3.timed(x_steps, x_warm)
         extra["strong_ms_per_step"] = m["ms_per_step"]
         extra["strong_tasks_per_sec"] = args.rows * x_steps / (m["total_ms"] * 1e-3)
@@ -468,8 +467,7 @@ def run_b200(args):
                     traffic = tj.get("dram_bytes_per_launch")
             except Exception:
                 pass
-        exchange = "none" if world == 1 else (("fused push of compact rows" + (" (2-byte offsets)" if form == 0 else " (1 gap byte per hit)"))
-                                              + (" + TaskIds" if with_root_ids else ""))
+        exchange = "none" if world == 1 else ("fused push of compact rows + TaskIds" if with_root_ids else "fused push of compact rows")
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": args.scaling,

@@ -469,10 +469,6 @@ typedef struct tt_exchange tt_exchange;
 typedef struct tt_gresult tt_gresult;
 #define TT_EXCHANGE_IDS 1
 #define TT_EXCHANGE_CREATED 2
-#define TT_EXCHANGE_GAP8 4 /* the slots carry ONE byte per hit instead of two: the distance to the tile's previous hit
-                              (minus one, modulo 255), distances above 255 in a short side list — half the bytes over
-                              NVLink; meant for lists denser than about one hit in 64 rows (sparser lists make the side
-                              list long; the two-byte form is the better one there).  Results are the same. */
 #define TT_ORDER_ROWS 0
 #define TT_ORDER_CREATED_ASC 1
 #define TT_COLLECT_RELEASE 0x100 /* OR into order (TT_ORDER_ROWS only): release the epoch inside the collect; the

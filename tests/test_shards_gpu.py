@@ -162,11 +162,9 @@ def test_load_soa_partitions_by_equal_width_id_ranges(oracle):
     st.close()
 
 
-@pytest.mark.parametrize("form", [0, tt.EXCHANGE_GAP8])
-def test_exchange_objects_in_one_process(oracle, form):
+def test_exchange_objects_in_one_process(oracle):
     """The lower layer, as bench.py drives it: explicit exchange objects, asynchronous ticks, a collect that
-    waits on the epoch words, views that expire, a slot that is too small, a shard that never ticks — with the
-    hits travelling as two-byte in-tile offsets and as one gap byte each."""
+    waits on the epoch words, views that expire, a slot that is too small, a shard that never ticks."""
     n, world = 400_000, 2
     cfg = oracle.default_cfg(31, n, n_creators=10)
     ot = oracle.OracleTable()
@@ -174,7 +172,7 @@ def test_exchange_objects_in_one_process(oracle, form):
     bounds = [0, n // 2, n]
     tables = [tt.TaskTable(0).generate(cfg, bounds[g], bounds[g + 1] - bounds[g]) for g in range(world)]
     tiles = max((len(t) + 8191) // 8192 for t in tables)
-    root, handle = tt.Exchange.create_root(0, world, 16384, tiles, tt.EXCHANGE_IDS | form)
+    root, handle = tt.Exchange.create_root(0, world, 16384, tiles, tt.EXCHANGE_IDS)
     assert len(handle) == 64 and any(handle) and root.slot_bytes % 256 == 0
     ex = [root, root.attach_local(0, 1)]
     want = np.sort(ot.get_yesterdays_due(tt.MODE_STORE))
@@ -213,7 +211,7 @@ def test_exchange_objects_in_one_process(oracle, form):
     for x in (ex[1], root):
         x.close()
     # slots too small for the hits: TT_ERR_CAPACITY from the tick, a row-ordered subset in the slot
-    small, _ = tt.Exchange.create_root(0, 1, 1024, tiles, form)
+    small, _ = tt.Exchange.create_root(0, 1, 1024, tiles, 0)
     st, rc = small.tick(tables[0], tt.MODE_STORE, tt.SWEEP_LIST_ONLY, allow_capacity=True)
     assert rc == tt.TT_ERR_CAPACITY and 0 < st.n_stored <= 1024 < st.n_listed
     part = small.collect(tt.ORDER_ROWS, [0])
@@ -319,34 +317,3 @@ def test_sharded_manager_with_empty_shards(oracle):
     res, n_marked, _ = st.sweep(tt.MODE_STORE)
     assert res.count == 2 and n_marked == 2 and st.get_yesterdays_due(tt.MODE_STORE).count == 0
     st.close()
-
-
-@pytest.mark.parametrize("ppm", [300, 3_000, 120_000, 1_000_000])
-def test_one_byte_form_at_every_density(oracle, ppm):
-    """TT_EXCHANGE_GAP8 from very sparse lists (nearly every distance between hits exceeds 255 rows: the side list
-    carries them) to every row a hit (all gap bytes zero), three shards, ragged sizes; the same list as the two-byte form
-    and as the oracle."""
-    n, world = 530_000, 3
-    cfg = oracle.default_cfg(77 + ppm, n, n_creators=10, ppm_due_yesterday=ppm, ppm_adversarial=0, ppm_completed=0, ppm_overdue_past=0)
-    ot = oracle.OracleTable()
-    ot.add_synth(cfg, 0, n)
-    want = np.sort(ot.get_yesterdays_due(tt.MODE_STORE))
-    assert len(want) > 100
-    bounds = [0, 170_001, 390_000, n]
-    tables = [tt.TaskTable(0).generate(cfg, bounds[g], bounds[g + 1] - bounds[g]) for g in range(world)]
-    tiles = max((len(t) + 8191) // 8192 for t in tables)
-    cap = (max(len(t) for t in tables) + 7) // 8 * 8
-    ids_all, _, _ = ot.export()
-    for form in (tt.EXCHANGE_GAP8, 0):
-        root, _ = tt.Exchange.create_root(0, world, cap, tiles, tt.EXCHANGE_IDS | form)
-        ex = [root] + [root.attach_local(0, g) for g in range(1, world)]
-        for tick in range(2):
-            for g in range(world):
-                ex[g].tick(tables[g], tt.MODE_STORE, tt.SWEEP_LIST_ONLY)
-            res = root.collect(tt.ORDER_ROWS, bounds[:world])
-            assert res.count == len(want) and (res.rows() == want).all() and (res.ids() == ids_all[want]).all(), (form, tick)
-            root.release()
-        for x in ex[1:] + [root]:
-            x.close()
-    for t in tables:
-        t.close()
