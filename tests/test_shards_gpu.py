@@ -317,3 +317,32 @@ def test_sharded_manager_with_empty_shards(oracle):
     res, n_marked, _ = st.sweep(tt.MODE_STORE)
     assert res.count == 2 and n_marked == 2 and st.get_yesterdays_due(tt.MODE_STORE).count == 0
     st.close()
+
+
+@pytest.mark.parametrize("ppm", [300, 120_000, 1_000_000])
+def test_exchange_at_every_density(oracle, ppm):
+    """From a hit every few thousand rows (most tiles empty) to every row a hit (pieces beyond the staging area take the
+    direct path): three shards of ragged sizes, two ticks into the same slots."""
+    n, world = 530_000, 3
+    cfg = oracle.default_cfg(77 + ppm, n, n_creators=10, ppm_due_yesterday=ppm, ppm_adversarial=0, ppm_completed=0, ppm_overdue_past=0)
+    ot = oracle.OracleTable()
+    ot.add_synth(cfg, 0, n)
+    want = np.sort(ot.get_yesterdays_due(tt.MODE_STORE))
+    assert len(want) > 100
+    bounds = [0, 170_001, 390_000, n]
+    tables = [tt.TaskTable(0).generate(cfg, bounds[g], bounds[g + 1] - bounds[g]) for g in range(world)]
+    tiles = max((len(t) + 8191) // 8192 for t in tables)
+    cap = (max(len(t) for t in tables) + 7) // 8 * 8
+    ids_all, _, _ = ot.export()
+    root, _ = tt.Exchange.create_root(0, world, cap, tiles, tt.EXCHANGE_IDS)
+    ex = [root] + [root.attach_local(0, g) for g in range(1, world)]
+    for tick in range(2):
+        for g in range(world):
+            ex[g].tick(tables[g], tt.MODE_STORE, tt.SWEEP_LIST_ONLY)
+        res = root.collect(tt.ORDER_ROWS, bounds[:world])
+        assert res.count == len(want) and (res.rows() == want).all() and (res.ids() == ids_all[want]).all(), tick
+        root.release()
+    for x in ex[1:] + [root]:
+        x.close()
+    for t in tables:
+        t.close()
