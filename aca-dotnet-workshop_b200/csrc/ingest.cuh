@@ -563,7 +563,8 @@ __device__ bool parse_datetime(const S& s, int len, int32_t local_offset_min, ui
 // K7a: one thread per document.
 // `text` holds the caller's bytes [window_first, window_first + bytes); doc_off are the caller's offsets.  A document
 // whose range is not inside that window, or runs backwards, is a bad document.
-__global__ void __launch_bounds__(128) doc_parse_kernel(uint8_t* text, const uint64_t* doc_off, uint64_t window_first,
+template <int MIN_CTAS>
+__global__ void __launch_bounds__(128, MIN_CTAS) doc_parse_kernel(uint8_t* text, const uint64_t* doc_off, uint64_t window_first,
                                                         uint64_t bytes, int64_t n, int32_t local_offset_min,
                                                         DocCols out) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -838,6 +839,94 @@ __global__ void __launch_bounds__(kScanBlock) dict_build_kernel(const uint32_t* 
   off[e] = o;
   const uint8_t* src = text + start[doc];
   for (uint32_t j = 0; j < l; ++j) pool[o + j] = src[j];
+}
+
+// ---- dictionary encoding through a hash table (the usual path; the sorted one above is the fallback) ----
+// An open-addressed table of {hash, first document} with at most half its slots in use.  Every document
+// claims or finds the slot of its string's hash and leaves the SMALLEST document number there, so the
+// representative of a string, and with it the numbering of the dictionary (entries in order of first
+// appearance), does not depend on the order the threads ran in.  Two different strings with one 64-bit
+// hash would share a slot: the resolve pass compares every document's bytes with its representative's and
+// raises `clash`, and the caller then encodes the member by sorting instead.  `keep` masks the hash (all ones
+// in production; a test narrows it to make such clashes happen).
+struct DictSlot {
+  unsigned long long key;  // all ones = empty
+  uint32_t doc;            // all ones = none yet
+  uint32_t pad;
+};
+constexpr unsigned long long kDictEmpty = ~0ull;
+
+__device__ __forceinline__ unsigned long long dict_key(uint64_t h) { return h == kDictEmpty ? h - 1 : h; }
+__device__ __forceinline__ uint32_t dict_home(unsigned long long k, int bits) {
+  return (uint32_t)((k * 0x9E3779B97F4A7C15ull) >> (64 - bits));
+}
+
+__global__ void dict_insert_kernel(const uint64_t* hash, uint64_t keep, int64_t n, DictSlot* tab, int bits) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const unsigned long long k = dict_key(hash[i] & keep);
+  const uint32_t mask = (1u << bits) - 1u;
+  uint32_t pos = dict_home(k, bits);
+  for (;;) {
+    // Plain (L1-cached) reads before the atomics: a key never changes once set and a slot's document number only
+    // falls, so a stale value costs at most an atomic that was not needed — while 25 M documents that share 50
+    // strings would otherwise queue up on 50 addresses in L2.
+    unsigned long long cur = tab[pos].key;
+    if (cur == kDictEmpty) {
+      cur = atomicCAS(&tab[pos].key, kDictEmpty, k);
+      if (cur == kDictEmpty) cur = k;
+    }
+    if (cur == k) {
+      if (tab[pos].doc > (uint32_t)i) atomicMin(&tab[pos].doc, (uint32_t)i);
+      return;
+    }
+    pos = (pos + 1) & mask;
+  }
+}
+
+// rep[doc] = the first document with the same string; a document that is its own representative heads an
+// entry.  Per-CTA head counts go to block_sum (scanned by scan_block_sums_kernel).
+__global__ void __launch_bounds__(kScanBlock) dict_resolve_kernel(const uint64_t* hash, uint64_t keep, int64_t n, const DictSlot* tab, int bits,
+                                                                  const uint8_t* text, const uint64_t* start,
+                                                                  const uint32_t* len, uint32_t* rep, uint64_t* block_sum,
+                                                                  unsigned long long* clash) {
+  __shared__ uint32_t s_warp[32];
+  const int64_t i = (int64_t)blockIdx.x * kScanBlock + threadIdx.x;
+  uint32_t h = 0;
+  if (i < n) {
+    const unsigned long long k = dict_key(hash[i] & keep);
+    const uint32_t mask = (1u << bits) - 1u;
+    uint32_t pos = dict_home(k, bits);
+    while (tab[pos].key != k) pos = (pos + 1) & mask;
+    const uint32_t r = tab[pos].doc;
+    if (r != (uint32_t)i && !same_string(text, start[r], len[r], start[i], len[i])) atomicAdd(clash, 1ull);
+    rep[i] = r;
+    h = r == (uint32_t)i;
+  }
+  uint32_t tot;
+  block_exclusive_scan(h, s_warp, &tot);
+  if (threadIdx.x == 0) block_sum[blockIdx.x] = tot;
+}
+
+// heads take their entry numbers (in document order); ref[] of a head is final after this kernel
+__global__ void __launch_bounds__(kScanBlock) dict_number_kernel(const uint32_t* rep, int64_t n, const uint64_t* block_base,
+                                                                 uint32_t* ref, uint32_t* entry_doc) {
+  __shared__ uint32_t s_warp[32];
+  const int64_t i = (int64_t)blockIdx.x * kScanBlock + threadIdx.x;
+  const uint32_t h = i < n && rep[i] == (uint32_t)i;
+  const uint32_t before = block_exclusive_scan(h, s_warp, nullptr);
+  if (!h) return;
+  const uint32_t entry = (uint32_t)block_base[blockIdx.x] + before;
+  ref[i] = entry;
+  entry_doc[entry] = (uint32_t)i;
+}
+
+// every other document copies its representative's entry number
+__global__ void dict_follow_kernel(const uint32_t* rep, int64_t n, uint32_t* ref) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint32_t r = rep[i];
+  if (r != (uint32_t)i) ref[i] = ref[r];
 }
 
 }  // namespace tt

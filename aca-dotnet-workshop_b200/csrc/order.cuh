@@ -104,7 +104,8 @@ inline int sort_rows_and_gather(cudaStream_t stream, SortScratch& sc, const uint
 // Orders d_rows (ascending row order on entry, or any order with rows_unordered) by
 // TaskCreatedOn, stable, and rewrites d_rows / d_ids.  Returns 0 or a cudaError_t value.
 inline int order_by_created(cudaStream_t stream, SortScratch& sc, const uint64_t* created_raw, const uint4* task_id,
-                            uint32_t* d_rows, uint4* d_ids, int64_t n, bool descending, bool rows_unordered = false) {
+                            uint32_t* d_rows, uint4* d_ids, int64_t n, bool descending, bool rows_unordered = false,
+                            RadixSortInfo* info = nullptr) {
   if (n <= 0) return 0;
   if (rows_unordered) {
     int rc = sort_rows_and_gather(stream, sc, task_id, d_rows, d_ids, n);
@@ -119,10 +120,11 @@ inline int order_by_created(cudaStream_t stream, SortScratch& sc, const uint64_t
                                                                                descending ? 1 : 0, sc.mm);
   e = cudaGetLastError();
   if (e != cudaSuccess) return (int)e;
-  int bits = 62, w = 0;
-  e = radix_bits_from_minmax(stream, sc, &bits);
+  int w = 0;
+  unsigned long long mm[2];
+  e = radix_minmax_read(stream, sc, mm);
   if (e != cudaSuccess) return (int)e;
-  e = radix_sort_pairs(stream, sc, n, bits, &w);
+  e = radix_sort_by_prefix(stream, sc, n, mm[0], mm[1], &w, info);
   if (e != cudaSuccess) return (int)e;
   emit_rows_ids_kernel<<<grid, 256, 0, stream>>>(sc.vals[w], task_id, d_rows, d_ids, n);
   e = cudaGetLastError();

@@ -157,6 +157,7 @@ struct tt_table {
   bool cq_busy = false;
   int64_t cq_batches = 0, cq_requests = 0;  // passes made / requests answered through the queue
   tt::SortScratch sort;  // K5 radix sort buffers, grow-only
+  tt::RadixSortInfo last_order;  // how the last OrderBy(TaskCreatedOn) went (tt_last_order_info)
   bool creator_smem_opted = false, json_smem_opted = false;  // large dynamic shared memory enabled on this device
 
   // payload: TaskName and TaskAssignedTo as dictionary-encoded string columns.  No kernel of the
@@ -801,7 +802,7 @@ int32_t ensure_id_order(tt_table* t) {
   unsigned long long ties = 1;
   if (e == cudaSuccess) {
     tt::id_half_keys_kernel<<<grid_for(n, 256), 256, 0, st>>>(t->task_id, nullptr, n, 1, t->sort.keys[0], t->sort.vals[0]);
-    e = tt::radix_sort_pairs(st, t->sort, n, 64, &w);
+    e = tt::radix_sort_auto(st, t->sort, n, &w);  // random ids: five passes over the top 40 bits, a few hundred groups put right
   }
   if (e == cudaSuccess) e = cudaMemsetAsync(t->d_small, 0, 8, st);
   if (e == cudaSuccess) {
@@ -1044,7 +1045,8 @@ int32_t tt_get_yesterdays_due(tt_table* t, int32_t mode, int64_t today_local_tic
   if (rc) return rc;
   if (mode == TT_MODE_STORE && r->n > 0) {
     // TasksStoreManager.cs:136 — OrderBy(TaskCreatedOn), stable; ties keep row order
-    rc = tt::order_by_created(t->stream, t->sort, t->created_raw, t->task_id, r->d_rows, r->d_ids, r->n, /*descending=*/false);
+    rc = tt::order_by_created(t->stream, t->sort, t->created_raw, t->task_id, r->d_rows, r->d_ids, r->n, /*descending=*/false,
+                              /*rows_unordered=*/false, &t->last_order);
     if (rc != 0) {
       result_release(r);
       return fail(TT_ERR_CUDA, "order_by_created failed: %s", cudaGetErrorString((cudaError_t)rc));
@@ -1085,7 +1087,8 @@ int32_t tt_get_due_on_or_before(tt_table* t, int32_t mode, int64_t today_local_t
                            mode != TT_MODE_STORE);
   if (rc) return rc;
   if (mode == TT_MODE_STORE && r->n > 0) {  // the store-backed list is ordered by TaskCreatedOn (TasksStoreManager.cs:136)
-    rc = tt::order_by_created(t->stream, t->sort, t->created_raw, t->task_id, r->d_rows, r->d_ids, r->n, /*descending=*/false);
+    rc = tt::order_by_created(t->stream, t->sort, t->created_raw, t->task_id, r->d_rows, r->d_ids, r->n, /*descending=*/false,
+                              /*rows_unordered=*/false, &t->last_order);
     if (rc != 0) {
       result_release(r);
       return fail(TT_ERR_CUDA, "order_by_created failed: %s", cudaGetErrorString((cudaError_t)rc));
@@ -1502,6 +1505,16 @@ int32_t tt_creator_combining_stats(tt_table* t, int64_t* passes, int64_t* reques
   std::lock_guard<std::mutex> lk(t->cq_mu);
   if (passes) *passes = t->cq_batches;
   if (requests) *requests = t->cq_requests;
+  return TT_OK;
+}
+
+int32_t tt_last_order_info(tt_table* t, int32_t* key_bits, int32_t* passes, int64_t* groups_fixed, int32_t* fell_back) {
+  if (!t) return fail(TT_ERR_ARG, "null argument");
+  std::lock_guard<std::mutex> lk(t->mu);
+  if (key_bits) *key_bits = t->last_order.bits;
+  if (passes) *passes = t->last_order.passes;
+  if (groups_fixed) *groups_fixed = (int64_t)t->last_order.fixed;
+  if (fell_back) *fell_back = t->last_order.fell_back ? 1 : 0;
   return TT_OK;
 }
 

@@ -64,7 +64,7 @@ EXPORTS = [
     "tt_load_payload", "tt_generate_payload", "tt_result_json", "tt_json_size", "tt_json_copy", "tt_json_device",
     "tt_json_free", "tt_last_json_stats", "tt_json_offsets", "tt_load_documents",
     "tt_get_due_on_or_before", "tt_sweep_backlog", "tt_tick_host", "tt_set_task_strings", "tt_upsert_task",
-    "tt_sweep_wait", "tt_creator_combining_stats",
+    "tt_sweep_wait", "tt_creator_combining_stats", "tt_last_order_info",
     "tt_exchange_create_root", "tt_exchange_attach", "tt_exchange_attach_local", "tt_exchange_destroy",
     "tt_exchange_slot_bytes", "tt_exchange_tick", "tt_exchange_epoch", "tt_exchange_collect", "tt_exchange_release",
     "tt_exchange_last_collect_ms",
@@ -225,6 +225,7 @@ def lib():
     L.tt_get_by_creators.argtypes = [vp, P(C.c_char_p), P(i32), i32, P(vp)]
     L.tt_last_op_stats.argtypes = [vp, P(OpStats)]
     L.tt_creator_combining_stats.argtypes = [vp, P(i64), P(i64)]
+    L.tt_last_order_info.argtypes = [vp, P(C.c_int32), P(C.c_int32), P(i64), P(C.c_int32)]
     L.tt_get_by_id.argtypes = [vp, vp, P(vp)]
     L.tt_insert_task.argtypes = [vp, vp, u64, u64, C.c_char_p, i32, P(i64)]
     L.tt_update_task.argtypes = [vp, vp, u64, P(i32)]
@@ -614,6 +615,12 @@ class TaskTable:
         p, r = C.c_int64(0), C.c_int64(0)
         _check(lib().tt_creator_combining_stats(self._h, C.byref(p), C.byref(r)))
         return p.value, r.value
+
+    def last_order_info(self):
+        """-> (key bits, radix passes, groups put right after the prefix passes, fell back) of the last ordered list."""
+        b, p, f, fb = C.c_int32(0), C.c_int32(0), C.c_int64(0), C.c_int32(0)
+        _check(lib().tt_last_order_info(self._h, C.byref(b), C.byref(p), C.byref(f), C.byref(fb)))
+        return b.value, p.value, f.value, bool(fb.value)
 
     def last_op_stats(self):
         st = OpStats()

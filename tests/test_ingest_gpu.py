@@ -264,3 +264,25 @@ def test_documents_from_the_reference_tutorial(oracle):
             seen += 1
     assert seen == len(samples)
     table.close()
+
+
+@pytest.mark.parametrize("env", [{"TT_DICT_SORTED": "1"}, {"TT_DICT_KEY_BITS": "5"}, {}])
+def test_both_dictionary_encoders_give_the_same_table(oracle, env, monkeypatch):
+    """The hash-table encoder, the sorting encoder it falls back to, and the fall-back itself (hashes cut to 5 bits,
+    so that different strings meet in one slot of the table) load the same table."""
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    n = 40_000
+    cfg = oracle.default_cfg(0xD1C, n, n_creators=900, n_names=5_000)
+    src = oracle.OracleTable()
+    src.add_synth(cfg, 0, n)
+    text, off = src.to_documents(np.arange(n), tt.JSON_DOCUMENT, -300)
+    ot = oracle.OracleTable()
+    assert ot.add_documents(text, off, -300) == -1
+    table = tt.TaskTable(0)
+    st = table.load_documents(text, off, -300)
+    assert (st.n_docs, st.first_bad) == (n, -1)
+    assert (st.n_creators, st.n_names, st.n_assignees) == (900, 5_000, 50)
+    creators = {src.created_by(i) for i in range(0, n, 997)}
+    assert same_table(oracle, ot, table, creators, -300) > 40
+    table.close()

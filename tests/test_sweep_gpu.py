@@ -297,3 +297,67 @@ def test_compact_hit_list_roundtrip(oracle):
     torch.cuda.synchronize()
     assert (back[: st.n_stored].cpu().numpy().view(np.uint32) == want).all()
     table.close()
+
+
+def _ordered_list_of(oracle, created_ticks):
+    """A table whose rows are all due yesterday with the given creation times -> (oracle's ordered rows, table)."""
+    n = len(created_ticks)
+    cfg = oracle.default_cfg(5, n, n_creators=3, ppm_due_yesterday=1_000_000, ppm_adversarial=0, ppm_completed=0,
+                             ppm_overdue_past=0)
+    src = oracle.OracleTable()
+    src.add_synth(cfg, 0, n)
+    ids, _, due = src.export()
+    created = np.asarray(created_ticks, dtype=np.uint64) | np.uint64(1 << 62)  # Kind = Utc
+    ot = oracle.OracleTable()
+    for i in range(n):
+        ot.add(ids[i].tobytes(), "t", "c", "a", int(created[i]), int(due[i]))
+    table = tt.TaskTable(0).load_soa(ids, created, due, np.zeros(n, np.uint8), np.zeros(n, np.uint8), np.zeros(n, np.uint32),
+                                     [b"c"])
+    return ot.get_yesterdays_due(tt.MODE_STORE, TODAY), table
+
+
+def test_order_by_created_on_wide_keys_with_near_ties(oracle):
+    """Creation times that differ in more than 40 bits are sorted on their top 40 bits; groups that share a prefix and
+    came in out of order (here: bursts of tasks 1-200 ticks apart, shuffled) are put right afterwards."""
+    rng = np.random.default_rng(11)
+    base = 638_000_000_000_000_000
+    span = 1 << 52
+    n_bursts, n = 3_000, 60_000
+    starts = rng.integers(0, span, n_bursts, dtype=np.int64)
+    ticks = np.concatenate([rng.integers(0, span, n - 8 * n_bursts, dtype=np.int64),
+                            (starts[:, None] + rng.integers(0, 200, (n_bursts, 8), dtype=np.int64)).ravel(), [0, span - 1]])
+    ticks[:5000] = ticks[5000:10000]  # exact ties too
+    rng.shuffle(ticks)
+    want, table = _ordered_list_of(oracle, base + ticks)
+    res = table.get_yesterdays_due(tt.MODE_STORE, TODAY)
+    assert (res.rows() == want).all()
+    bits, passes, fixed, fell_back = table.last_order_info()
+    assert (bits, passes, fell_back) == (52, 5, False) and fixed > 1000
+    table.close()
+
+
+def test_order_by_created_falls_back_on_long_groups(oracle):
+    """Hundreds of distinct creation times inside one 40-bit prefix, out of order: ordinary passes finish the sort."""
+    rng = np.random.default_rng(12)
+    base = 638_000_000_000_000_000
+    span = 1 << 50
+    ticks = np.concatenate([rng.integers(0, span, 20_000, dtype=np.int64), 12345 + rng.permutation(700), [0, span - 1]])
+    rng.shuffle(ticks)
+    want, table = _ordered_list_of(oracle, base + ticks)
+    res = table.get_yesterdays_due(tt.MODE_STORE, TODAY)
+    assert (res.rows() == want).all()
+    bits, passes, _, fell_back = table.last_order_info()
+    assert bits == 50 and fell_back and passes == 12
+    table.close()
+
+
+def test_order_by_created_in_creation_order_needs_no_fixing(oracle):
+    """A table filled in creation order (dense timestamps, many ties) has no group out of order."""
+    ticks = 638_000_000_000_000_000 + np.cumsum(np.random.default_rng(13).integers(0, 3, 50_000)).astype(np.int64)
+    ticks[-1] += 1 << 45
+    want, table = _ordered_list_of(oracle, ticks)
+    res = table.get_yesterdays_due(tt.MODE_STORE, TODAY)
+    assert (res.rows() == want).all() and (want == np.arange(len(ticks))).all()
+    bits, passes, fixed, fell_back = table.last_order_info()
+    assert (bits, passes, fixed, fell_back) == (46, 5, 0, False)
+    table.close()
