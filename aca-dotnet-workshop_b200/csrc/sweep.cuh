@@ -31,6 +31,31 @@
 
 namespace tt {
 
+// Programmatic dependent launch: the three kernels of a tick are launched with
+// cudaLaunchAttributeProgrammaticStreamSerialization, so the next kernel's launch and its first CTAs' set-up
+// overlap the tail of the one before; a dependent kernel reads nothing its predecessor wrote before
+// grid_dependency_wait() returns (= the predecessor has completed and its writes are visible).  Both are
+// no-ops in a kernel launched the ordinary way.
+__device__ __forceinline__ void grid_dependency_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void grid_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_dependent(void (*kernel)(KArgs...), dim3 grid, dim3 block, cudaStream_t stream, bool programmatic,
+                                    Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = 0;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = programmatic ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
+
 constexpr int kSweepThreads = 256;
 constexpr int kSweepWarps = kSweepThreads / 32;
 constexpr int kSweepCtasPerSm = 3;  // measured: 0.648 ms per 1 B rows; 4 (64 registers) 0.680 ms; 2 0.803 ms
@@ -181,6 +206,7 @@ __device__ __forceinline__ void emit_tile(const SweepParams& p, const PendingTil
 //            tutorial says its exact match leaves out (docs/aca/07-aca-cron-bindings/index.md:106).
 template <bool USE_FLAGS, bool MARK, int THREADS, int CTAS_PER_SM, bool RANGE = false>
 __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) sweep_kernel(SweepParams p) {
+  grid_launch_dependents();  // the placement kernel's first CTAs may take their seats now (they wait for this grid's end)
   constexpr int kWarps = THREADS / 32;
   __shared__ uint32_t s_wtot[kWarps];
   __shared__ uint32_t s_tile;
@@ -413,6 +439,8 @@ __global__ void __launch_bounds__(kGroupThreads) place_group_kernel(const uint32
                                                                     const uint64_t* created_raw, uint32_t* out_rows,
                                                                     uint4* out_ids, PushTarget push) {
   static_assert(kTilesPerSub % GT == 0 || GT % kTilesPerSub == 0, "a CTA's tiles must not straddle the prefix levels unevenly");
+  grid_launch_dependents();
+  grid_dependency_wait();  // everything K1 wrote is visible from here on
   __shared__ uint32_t s_slot[GT];
   __shared__ uint32_t s_pre[GT + 1];
   __shared__ uint32_t s_base;
@@ -513,6 +541,7 @@ __global__ void __launch_bounds__(kGroupThreads) place_group_kernel(const uint32
 __global__ void sweep_tail_kernel(SweepCtl* ctl, SweepOut* out, uint32_t* group_sum, uint32_t n_groups, uint32_t* sub_sum,
                                   uint32_t n_subs, unsigned long long* push_count, unsigned long long* epoch_word,
                                   unsigned long long epoch) {
+  grid_dependency_wait();  // the placement kernel has finished with the partial sums this kernel clears
   const unsigned long long cursor = ctl->cursor, stored = ctl->stored;
   for (uint32_t k = threadIdx.x; k < n_groups; k += blockDim.x) group_sum[k] = 0;
   if (sub_sum)

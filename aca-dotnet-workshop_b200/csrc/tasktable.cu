@@ -574,6 +574,8 @@ int32_t sweep_run(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_
   // The control block and the partial sums are left in their start state by the previous tick's
   // tail kernel; only the first tick of a table (or one after a failed call) sets them from the host.
   const bool timing = (flags & TT_SWEEP_NO_TIMING) == 0;
+  // programmatic dependent launch of K3g and the tail kernel (sweep.cuh); TT_NO_PDL=1 launches them the ordinary way
+  static const bool pdl = getenv("TT_NO_PDL") == nullptr;
   const bool was_clean = t->ctl_clean;
   t->ctl_clean = false;
   if (!was_clean) {
@@ -631,9 +633,12 @@ int32_t sweep_run(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_
       static const int plain_variant = [] { const char* e = getenv("TT_PLACE_VARIANT"); return e ? atoi(e) : 1; }();
       static const int push_variant = [] { const char* e = getenv("TT_PUSH_VARIANT"); return e ? atoi(e) : 8; }();
 #define TT_PLACE_LAUNCH(GT, UN)                                                                                     \
-  tt::place_group_kernel<TT_TILE_ROWS, GT, UN><<<(num_tiles + GT - 1) / GT, tt::kGroupThreads, 0, stream>>>(            \
-      t->hit_list, p.tile_slot, p.tile_count, p.group_sum, p.sub_sum, num_tiles, t->task_id, t->created_raw, d_rows,    \
-      d_ids, push ? *push : none)
+  TT_CUDA(tt::launch_dependent(tt::place_group_kernel<TT_TILE_ROWS, GT, UN>, dim3((num_tiles + GT - 1) / GT),           \
+                               dim3(tt::kGroupThreads), stream, pdl, (const uint32_t*)t->hit_list,                      \
+                               (const uint32_t*)p.tile_slot, (const uint32_t*)p.tile_count,                             \
+                               (const uint32_t*)p.group_sum, (const uint32_t*)p.sub_sum, (uint32_t)num_tiles,           \
+                               (const uint4*)t->task_id, (const uint64_t*)t->created_raw, d_rows, d_ids,                \
+                               push ? *push : none))
       switch (push ? push_variant : plain_variant) {
         case 2: TT_PLACE_LAUNCH(2, 2); break;
         case 4: TT_PLACE_LAUNCH(4, 4); break;
@@ -658,10 +663,9 @@ int32_t sweep_run(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_
   }
   // the epilogue: outcome -> mapped host memory (and the push target), scratch back to its start state,
   // the epoch word of a sharded tick
-  tt::sweep_tail_kernel<<<1, 256, 0, stream>>>(t->ctl, t->d_out, t->group_sum, n_groups, p.sub_sum, n_subs,
-                                              push ? push->count : nullptr, hook ? hook->epoch_word : nullptr,
-                                              hook ? hook->epoch : 0);
-  TT_CUDA(cudaGetLastError());
+  TT_CUDA(tt::launch_dependent(tt::sweep_tail_kernel, dim3(1), dim3(256), stream, pdl, t->ctl, t->d_out, t->group_sum,
+                               (uint32_t)n_groups, p.sub_sum, (uint32_t)n_subs, push ? push->count : nullptr,
+                               hook ? hook->epoch_word : nullptr, hook ? hook->epoch : 0ull));
   st->launches += 1;
   if (timing) TT_CUDA(cudaEventRecord(t->ev2, stream));
   t->pending = tt_table::PendingSweep();
