@@ -39,6 +39,7 @@ struct CollectMeta {
   unsigned long long base[kMaxShards + 1];  // exclusive scan of the counts; base[world] = total
   unsigned int timed_out;                   // bit r set: shard r did not publish the epoch in time
   unsigned int pad;
+  unsigned long long done;                  // host copy only: number of the last collect whose kernels have all run
 };
 
 __device__ __forceinline__ unsigned long long ld_acquire_sys_u64(const unsigned long long* p) {
@@ -211,9 +212,15 @@ __global__ void shard_publish_empty_kernel(SlotHeader* hdr, unsigned long long e
 }
 
 // slot 0's `consumed` word: the root has finished reading epoch `value`
-__global__ void shard_consumed_kernel(SlotHeader* slot0, unsigned long long value) {
+// (and, for a collect that ends here, its number into the root's mapped host word, which the host watches)
+__global__ void shard_consumed_kernel(SlotHeader* slot0, unsigned long long value, unsigned long long* host_done = nullptr,
+                                      unsigned long long done = 0) {
   __threadfence_system();
   asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(&slot0->consumed), "l"(value) : "memory");
+  if (host_done) {
+    __threadfence_system();
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(host_done), "l"(done) : "memory");
+  }
 }
 
 // Creator filter across shards: one shard's matches (already ordered by that shard) as sort input on

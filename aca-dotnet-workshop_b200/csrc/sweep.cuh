@@ -72,6 +72,7 @@ struct SweepCtl {
 struct SweepOut {
   unsigned long long cursor;
   unsigned long long stored;
+  unsigned long long seq;  // the tick's number, written last: a host that reads it has the two words above
 };
 
 struct SweepParams {
@@ -540,7 +541,7 @@ __global__ void __launch_bounds__(kGroupThreads) place_group_kernel(const uint32
 // word (shard_wait_kernel) instead of on a collective.
 __global__ void sweep_tail_kernel(SweepCtl* ctl, SweepOut* out, uint32_t* group_sum, uint32_t n_groups, uint32_t* sub_sum,
                                   uint32_t n_subs, unsigned long long* push_count, unsigned long long* epoch_word,
-                                  unsigned long long epoch) {
+                                  unsigned long long epoch, unsigned long long seq) {
   grid_dependency_wait();  // the placement kernel has finished with the partial sums this kernel clears
   const unsigned long long cursor = ctl->cursor, stored = ctl->stored;
   for (uint32_t k = threadIdx.x; k < n_groups; k += blockDim.x) group_sum[k] = 0;
@@ -560,6 +561,10 @@ __global__ void sweep_tail_kernel(SweepCtl* ctl, SweepOut* out, uint32_t* group_
     if (epoch_word) {
       __threadfence_system();
       asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(epoch_word), "l"(epoch) : "memory");
+    }
+    if (out) {
+      __threadfence_system();
+      asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(&out->seq), "l"(seq) : "memory");
     }
   }
 }

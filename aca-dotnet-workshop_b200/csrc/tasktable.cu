@@ -12,6 +12,7 @@
 #include <cstdio>
 #include <cstring>
 #include <atomic>
+#include <chrono>
 #include <memory>
 #include <condition_variable>
 #include <mutex>
@@ -117,12 +118,14 @@ struct tt_table {
   bool ctl_clean = false;           // control block and partial sums are in their start state (the last tick's tail kernel ran)
   tt::SweepOut* h_out = nullptr;    // the tick's outcome: mapped pinned host memory the tail kernel writes
   tt::SweepOut* d_out = nullptr;    // its device address
+  uint64_t tick_seq = 0;            // ticks launched so far (the tail kernel reports the number back)
   struct PendingSweep {             // a tick queued with TT_SWEEP_ASYNC and not yet collected by tt_sweep_wait
     bool active = false, listing = false, timing = false, trivial = false;  // trivial: nothing was launched
     uint32_t mark_enable = 0;
     int64_t first_row = 0, row_end = -1, cap = 0;
     int32_t launches = 0;
     cudaStream_t stream = nullptr;
+    uint64_t seq = 0;  // the tick's number (0: nothing to watch for)
   } pending;
   uint32_t* hit_list = nullptr;
   int64_t hit_list_cap = 0;
@@ -481,7 +484,18 @@ int32_t sweep_finish(tt_table* t, tt_sweep_stats* st) {
     st->resume_row = pd.row_end;
     return TT_OK;
   }
-  TT_CUDA(cudaStreamSynchronize(pd.stream));
+  // An untimed tick ends when the tail kernel's last store — the tick's number, in mapped host memory — is seen:
+  // watching that word for a short while costs less than the wake-up of cudaStreamSynchronize (what is left of a
+  // 10 M-row tick is launch and wake-up time).  Long ticks, failed ones and timed ones wait on the stream.
+  bool seen = false;
+  if (!pd.timing && pd.seq) {
+    const volatile unsigned long long* word = &t->h_out->seq;
+    const auto t0 = std::chrono::steady_clock::now();
+    for (int spin = 0; !(seen = *word == pd.seq); ++spin)
+      if ((spin & 63) == 63 && std::chrono::steady_clock::now() - t0 > std::chrono::microseconds(150)) break;
+    if (seen) std::atomic_thread_fence(std::memory_order_acquire);
+  }
+  if (!seen) TT_CUDA(cudaStreamSynchronize(pd.stream));
   t->ctl_clean = true;
   if (pd.timing) {
     TT_CUDA(cudaEventElapsedTime(&st->sweep_ms, t->ev0, t->ev1));
@@ -665,7 +679,8 @@ int32_t sweep_run(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_
   // the epoch word of a sharded tick
   TT_CUDA(tt::launch_dependent(tt::sweep_tail_kernel, dim3(1), dim3(256), stream, pdl, t->ctl, t->d_out, t->group_sum,
                                (uint32_t)n_groups, p.sub_sum, (uint32_t)n_subs, push ? push->count : nullptr,
-                               hook ? hook->epoch_word : nullptr, hook ? hook->epoch : 0ull));
+                               hook ? hook->epoch_word : nullptr, hook ? hook->epoch : 0ull,
+                               (unsigned long long)++t->tick_seq));
   st->launches += 1;
   if (timing) TT_CUDA(cudaEventRecord(t->ev2, stream));
   t->pending = tt_table::PendingSweep();
@@ -678,6 +693,7 @@ int32_t sweep_run(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_
   t->pending.cap = cap;
   t->pending.launches = st->launches;
   t->pending.stream = stream;
+  t->pending.seq = t->tick_seq;
   if (flags & TT_SWEEP_ASYNC) return TT_OK;  // the caller collects the outcome with tt_sweep_wait
   return sweep_finish(t, st);
 }
@@ -872,6 +888,7 @@ int32_t tt_create(int32_t device, tt_table** out) {
   TT_CUDA(cudaMalloc(&t->ctl, sizeof(tt::SweepCtl)));
   TT_CUDA(cudaMallocHost(&t->h_ctl, sizeof(tt::SweepCtl)));
   TT_CUDA(cudaHostAlloc(&t->h_out, sizeof(tt::SweepOut), cudaHostAllocMapped));
+  memset(t->h_out, 0, sizeof(tt::SweepOut));
   TT_CUDA(cudaHostGetDevicePointer(&t->d_out, t->h_out, 0));
   TT_CUDA(cudaMalloc(&t->d_small, 16 * 8));
   TT_CUDA(cudaMallocHost(&t->h_small, 16 * 8));
