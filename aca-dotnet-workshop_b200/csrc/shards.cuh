@@ -104,68 +104,16 @@ __global__ void shard_wait_kernel(const unsigned char* base, size_t stride, int 
 struct SlotLayout {
   size_t tile_count;  // u32[max_tiles]
   size_t tile_first;  // u32[max_tiles]
-  size_t tile_slot;   // u32[max_tiles], early form only (0 otherwise): where a tile's run starts in off16
   size_t off16;       // u16[cap]
   size_t ids;         // uint4[cap], 0 = not exchanged
   size_t created;     // u64[cap],  0 = not exchanged
   size_t bytes;       // slot stride
 };
 
-// ---- early form (TT_EXCHANGE_EARLY): the root orders every slot's tiles ---------------------------------------
-// A shard's K1 stored each tile's in-tile offsets where its cursor atomic put them (tile_slot, tile_count); the
-// row-ordered position of a tile (tile_first) is the exclusive scan of the counts, done here on the root for slots
-// first_slot .. world-1 at once: grid (groups, slots).
-__global__ void __launch_bounds__(kTilesPerGroup) shard_group_sums_kernel(const unsigned char* base, SlotLayout lay,
-                                                                           uint32_t max_tiles, uint32_t first_slot,
-                                                                           uint32_t n_groups, uint32_t* sums) {
-  __shared__ uint32_t s_w[kTilesPerGroup / 32];
-  const uint32_t r = blockIdx.y + first_slot;
-  const uint32_t t = blockIdx.x * kTilesPerGroup + threadIdx.x;
-  const uint32_t* cnt = reinterpret_cast<const uint32_t*>(base + (size_t)r * lay.bytes + lay.tile_count);
-  uint32_t c = warp_sum(t < max_tiles ? cnt[t] : 0u);
-  if ((threadIdx.x & 31u) == 0) s_w[threadIdx.x >> 5] = c;
-  __syncthreads();
-  if (threadIdx.x < 32) {
-    c = warp_sum(s_w[threadIdx.x]);
-    if (threadIdx.x == 0) sums[blockIdx.y * n_groups + blockIdx.x] = c;
-  }
-}
-
-__global__ void __launch_bounds__(kTilesPerGroup) shard_tile_first_kernel(unsigned char* base, SlotLayout lay, uint32_t max_tiles,
-                                                                           uint32_t first_slot, uint32_t n_groups,
-                                                                           const uint32_t* sums) {
-  __shared__ uint32_t s_warp[kTilesPerGroup / 32];
-  __shared__ uint32_t s_carry;
-  const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
-  const uint32_t r = blockIdx.y + first_slot, g = blockIdx.x;
-  unsigned char* slot = base + (size_t)r * lay.bytes;
-  if (warp == 0) {
-    uint32_t c = 0;
-    for (uint32_t k = lane; k < g; k += 32) c += sums[blockIdx.y * n_groups + k];
-    c = warp_sum(c);
-    if (lane == 0) s_carry = c;
-  }
-  const uint32_t t = g * kTilesPerGroup + tid;
-  const uint32_t cnt = t < max_tiles ? reinterpret_cast<const uint32_t*>(slot + lay.tile_count)[t] : 0u;
-  uint32_t incl = cnt;
-#pragma unroll
-  for (int d = 1; d < 32; d <<= 1) {
-    uint32_t up = __shfl_up_sync(0xFFFFFFFFu, incl, d);
-    if (lane >= (uint32_t)d) incl += up;
-  }
-  if (lane == 31) s_warp[warp] = incl;
-  __syncthreads();
-  uint32_t wbase = 0;
-  for (uint32_t k = 0; k < warp; ++k) wbase += s_warp[k];
-  if (t < max_tiles) reinterpret_cast<uint32_t*>(slot + lay.tile_first)[t] = s_carry + wbase + incl - cnt;
-}
-
 // Rebuilds shard-local row numbers for every slot at once: grid (tiles / 8, world), one warp per
-// tile.  rows_out is the concatenated list (slot r starts at meta->base[r]).  A tile's offsets stand at
-// tile_first (row order: the placement kernel pushed them) or, in a slot filled the early way, at tile_slot.
+// tile.  rows_out is the concatenated list (slot r starts at meta->base[r]).
 __global__ void __launch_bounds__(256) shard_expand_kernel(const unsigned char* base, SlotLayout lay, uint32_t max_tiles,
-                                                            const CollectMeta* meta, uint32_t* rows_out, uint32_t first_slot,
-                                                            uint32_t first_early_slot) {
+                                                            const CollectMeta* meta, uint32_t* rows_out, uint32_t first_slot) {
   const uint32_t r = blockIdx.y + first_slot;  // first_slot = 1: the root's own placement kernel wrote slot 0's rows in place
   const uint32_t t = blockIdx.x * 8 + (threadIdx.x >> 5);
   if (t >= max_tiles) return;
@@ -173,8 +121,7 @@ __global__ void __launch_bounds__(256) shard_expand_kernel(const unsigned char* 
   const uint32_t cnt = reinterpret_cast<const uint32_t*>(slot + lay.tile_count)[t];
   if (cnt == 0) return;
   const uint32_t first = reinterpret_cast<const uint32_t*>(slot + lay.tile_first)[t];
-  const uint32_t from = r >= first_early_slot ? reinterpret_cast<const uint32_t*>(slot + lay.tile_slot)[t] : first;
-  const uint16_t* src = reinterpret_cast<const uint16_t*>(slot + lay.off16) + from;
+  const uint16_t* src = reinterpret_cast<const uint16_t*>(slot + lay.off16) + first;
   uint32_t* dst = rows_out + meta->base[r] + first;
   // all of a lane's loads go out before its first store: a tile of the usual density (about 200 hits) is in
   // flight at once instead of one 64-byte piece per warp (measured at 8 GPUs: the dependent form ran at 2.7 TB/s)

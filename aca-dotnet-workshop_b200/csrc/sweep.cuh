@@ -80,9 +80,6 @@ struct SweepParams {
   const uint32_t* completed;
   uint32_t* overdue;
   uint32_t* list;                    // unordered hit rows (scratch, cap entries); null = count only
-  uint16_t* list16;                  // PUSH16 builds only: the hits once more, as 13-bit in-tile offsets in cursor order,
-  uint32_t* push_tile_slot;          // with each tile's slot and count — all three in the shard's slot of the root GPU's
-  uint32_t* push_tile_count;         // buffer (csrc/shards.cuh, the early form)
   uint32_t* tile_slot;               // per tile: first slot in `list`
   uint32_t* tile_count;              // per tile: hits stored (0 if the tile did not fit)
   uint32_t* group_sum;               // per kTilesPerGroup tiles: sum of tile_count (zero before launch)
@@ -171,26 +168,13 @@ struct PendingTile {
   uint32_t total;   // hits in the whole tile
 };
 
-template <bool MARK, int THREADS, bool PUSH16 = false>
+template <bool MARK, int THREADS>
 __device__ __forceinline__ void emit_tile(const SweepParams& p, const PendingTile& t, uint32_t slot, uint32_t warp,
-                                          uint32_t lane, uint32_t tid, uint16_t* s_stage = nullptr,
-                                          uint32_t* s_flush = nullptr) {
+                                          uint32_t lane, uint32_t tid) {
   constexpr uint32_t kTileRows = (THREADS / 32) * TT_WARP_ROWS;
   const uint32_t tile = p.first_tile + t.rel;
   const bool fits = (unsigned long long)slot + t.total <= p.cap;
   if (fits) {
-    if (PUSH16) {
-      // staged in shared memory, shifted like the destination so that 16-byte pieces of both line up; the
-      // CTA flushes it with wide stores at the top of its next iteration (push16_flush)
-      uint16_t* dst = s_stage + (slot & 7u) + t.offset;
-      const uint32_t off0 = warp * TT_WARP_ROWS + lane * 32u;
-      uint32_t m = t.hits;
-      while (m) {
-        uint32_t b = __ffs(m) - 1;
-        m &= m - 1;
-        *dst++ = (uint16_t)(off0 + b);
-      }
-    }
     if (p.list) {
       uint32_t* dst = p.list + slot + t.offset;
       const uint32_t row0 = tile * kTileRows + warp * TT_WARP_ROWS + lane * 32u;
@@ -212,34 +196,7 @@ __device__ __forceinline__ void emit_tile(const SweepParams& p, const PendingTil
         if (p.sub_sum) atomicAdd(p.sub_sum + t.rel / kTilesPerSub, t.total);
       }
     }
-    if (PUSH16) {
-      p.push_tile_slot[t.rel] = slot;
-      p.push_tile_count[t.rel] = fits ? t.total : 0u;
-      s_flush[0] = slot;
-      s_flush[1] = fits ? t.total : 0u;
-    }
-    // (slots are handed out in cursor order, so the tiles that fit are exactly those below the smallest slot that
-    // did not: `stored` is both the cut and the count)
     if (!fits) atomicMin(&p.ctl->stored, (unsigned long long)slot);
-  }
-}
-
-// PUSH16: the staged offsets of the tile emitted one iteration ago go to the slot in the root GPU's memory —
-// consecutive threads store consecutive 16-byte pieces (a tile of the usual density is one 400-byte run: four
-// NVLink packets instead of a packet per lane), the ragged ends two bytes at a time.
-template <int THREADS>
-__device__ __forceinline__ void push16_flush(const SweepParams& p, const uint16_t* s_stage, const uint32_t* s_flush,
-                                             uint32_t tid) {
-  const uint32_t slot = s_flush[0], total = s_flush[1];
-  if (total == 0) return;
-  const uint32_t lo = slot & 7u, hi = lo + total;
-  uint16_t* dst = p.list16 + (slot - lo);  // 16-byte aligned: the slot's off16 area is, and (slot - lo) % 8 == 0
-  for (uint32_t a = tid * 8u; a < hi; a += THREADS * 8u) {
-    if (a >= lo && a + 8u <= hi) {
-      *reinterpret_cast<uint4*>(dst + a) = *reinterpret_cast<const uint4*>(s_stage + a);
-    } else {
-      for (uint32_t e = a > lo ? a : lo; e < a + 8u && e < hi; ++e) dst[e] = s_stage[e];
-    }
   }
 }
 
@@ -248,31 +205,20 @@ __device__ __forceinline__ void push16_flush(const SweepParams& p, const uint16_
 //            matches, whatever its time of day or Kind (padding rows and tombstones carry bits
 //            above bit 24 and never match).  No reference counterpart: it covers the cases the
 //            tutorial says its exact match leaves out (docs/aca/07-aca-cron-bindings/index.md:106).
-// PUSH16   : a shard's tick of an exchange made with TT_EXCHANGE_EARLY (csrc/shards.cuh): the hits leave this kernel
-//            ALSO as 13-bit in-tile offsets, in cursor order, straight into the shard's slot of the root GPU's buffer
-//            (list16, push_tile_slot, push_tile_count); the root puts every slot's tiles in order, and the placement
-//            kernel that follows on this GPU (for the shard's own list and TaskIds) pushes nothing.  The stores
-//            cross NVLink while K1 runs, not in a burst after it.
-template <bool USE_FLAGS, bool MARK, int THREADS, int CTAS_PER_SM, bool RANGE = false, bool PUSH16 = false>
+template <bool USE_FLAGS, bool MARK, int THREADS, int CTAS_PER_SM, bool RANGE = false>
 __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) sweep_kernel(SweepParams p) {
   grid_launch_dependents();  // the placement kernel's first CTAs may take their seats now (they wait for this grid's end)
   constexpr int kWarps = THREADS / 32;
-  constexpr uint32_t kTileRowsK = kWarps * TT_WARP_ROWS;
   __shared__ uint32_t s_wtot[kWarps];
   __shared__ uint32_t s_tile;
   __shared__ uint32_t s_slot;
-  __shared__ uint32_t s_flush[2];                                             // PUSH16: slot and count of the staged tile
-  __shared__ __align__(16) uint16_t s_stage[PUSH16 ? kTileRowsK + 8 : 8];     // PUSH16: its in-tile offsets
 
   const uint32_t tid = threadIdx.x;
   const uint32_t lane = tid & 31u;
   const uint32_t warp = tid >> 5;
   const uint32_t src_lane = tt_word_src_lane(lane);
 
-  if (tid == 0) {
-    s_tile = atomicAdd(&p.ctl->tile_counter, 1u);
-    s_flush[0] = s_flush[1] = 0;
-  }
+  if (tid == 0) s_tile = atomicAdd(&p.ctl->tile_counter, 1u);
   __syncthreads();
   uint32_t cur = s_tile;
   __syncthreads();  // s_tile is read before iteration 0 overwrites it
@@ -290,8 +236,6 @@ __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) sweep_kernel(SweepParams
     // claim the next tile now; its number is needed only after the barrier
     uint32_t claimed = 0;
     if (tid == 0) claimed = atomicAdd(&p.ctl->tile_counter, 1u);
-    // the tile staged by the previous iteration's emit leaves for the root while this tile's loads land
-    if (PUSH16) push16_flush<THREADS>(p, s_stage, s_flush, tid);
 
     // ---- predicate -> nibbles -> 32-row match word (waits for this tile's loads) ----
     uint32_t packed = 0;
@@ -346,8 +290,7 @@ __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) sweep_kernel(SweepParams
     }
     // ---- ask for this tile's slot (used next iteration), write the previous tile ----
     if (tid == 0) pend_slot = (uint32_t)atomicAdd(&p.ctl->cursor, (unsigned long long)total);
-    if (pend.rel != ~0u) emit_tile<MARK, THREADS, PUSH16>(p, pend, s_slot, warp, lane, tid, s_stage, s_flush);
-    else if (PUSH16 && tid == 0) s_flush[1] = 0;
+    if (pend.rel != ~0u) emit_tile<MARK, THREADS>(p, pend, s_slot, warp, lane, tid);
     pend.rel = rel;
     pend.hits = hits;
     pend.ow = ow;
@@ -359,14 +302,9 @@ __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) sweep_kernel(SweepParams
 
   // ---- drain: the last tile this CTA processed ----
   if (pend.rel != ~0u) {
-    if (PUSH16) push16_flush<THREADS>(p, s_stage, s_flush, tid);  // the tile staged by the loop's last iteration
     if (tid == 0) s_slot = pend_slot;
     __syncthreads();
-    emit_tile<MARK, THREADS, PUSH16>(p, pend, s_slot, warp, lane, tid, s_stage, s_flush);
-    if (PUSH16) {
-      __syncthreads();
-      push16_flush<THREADS>(p, s_stage, s_flush, tid);
-    }
+    emit_tile<MARK, THREADS>(p, pend, s_slot, warp, lane, tid);
   }
 }
 
@@ -465,8 +403,6 @@ struct PushTarget {
   uint4* ids;                   // [cap] TaskIds of the hits in row order, or null (the sharded GetYesterdaysDueTasks)
   unsigned long long* created;  // [cap] TaskCreatedOn (.NET dateData) of the hits, or null (the cross-shard OrderBy)
   uint32_t* tile_first;         // [num_tiles] offset of each tile's hits in the row-ordered list, or null
-  uint32_t* tile_slot;          // early form only: [num_tiles] offset of each tile's hits in off16 (cursor order)
-  int early;                    // 1: K1 itself stores off16 / tile_slot / tile_count (PUSH16); the placement kernel pushes nothing
 };
 
 // What a sharded tick adds around K3g (shards.cuh): before it, wait until the root has finished

@@ -558,10 +558,7 @@ int32_t sweep_run(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_
 
   // scratch for the unordered hit list K1 writes before K3 puts it in row order
   const bool listing = d_rows != nullptr || push != nullptr;
-  const bool early = push && push->early;  // the hits leave K1 for the root's slot; K3g (if a local list is wanted) pushes nothing
-  const bool place = listing && (!early || d_rows != nullptr);
-  const tt::PushTarget* push_k3 = early ? nullptr : push;  // what the placement kernel pushes: nothing after an early push
-  if (place && cap > t->hit_list_cap) {
+  if (listing && cap > t->hit_list_cap) {
     cudaFree(t->hit_list);
     t->hit_list = nullptr;
     t->hit_list_cap = 0;
@@ -573,10 +570,7 @@ int32_t sweep_run(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_
   p.due_code = t->due_code;
   p.completed = t->completed;
   p.overdue = t->overdue;
-  p.list = place ? t->hit_list : nullptr;
-  p.list16 = early ? push->off16 : nullptr;
-  p.push_tile_slot = early ? push->tile_slot : nullptr;
-  p.push_tile_count = early ? push->tile_count : nullptr;
+  p.list = listing ? t->hit_list : nullptr;
   p.tile_slot = t->tile_words;
   p.tile_count = t->tile_words + t->n_tiles;
   uint32_t* tile_first = t->tile_words + 2 * t->n_tiles;
@@ -613,27 +607,7 @@ int32_t sweep_run(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_
   const unsigned grid = (unsigned)std::min<int64_t>(num_tiles, (int64_t)t->sm_count * sweep_ctas_per_sm());
   if (timing) TT_CUDA(cudaEventRecord(t->ev0, stream));
   constexpr int kT = tt::kSweepThreads, kC = tt::kSweepCtasPerSm;
-  if (early) {
-    if (hook && hook->wait_slot0) {  // the root must have read this shard's slot of the previous tick before K1 writes it
-      tt::shard_wait_kernel<<<1, 32, 0, stream>>>(hook->wait_slot0, 0, 1, offsetof(tt::SlotHeader, consumed),
-                                                  hook->wait_value, hook->timeout_ns, nullptr, nullptr);
-      TT_CUDA(cudaGetLastError());
-      st->launches += 1;
-    }
-    if (range) {
-      if (mode == TT_MODE_STORE) {
-        if (p.mark_enable) tt::sweep_kernel<true, true, kT, kC, true, true><<<grid, kT, 0, stream>>>(p);
-        else tt::sweep_kernel<true, false, kT, kC, true, true><<<grid, kT, 0, stream>>>(p);
-      } else {
-        tt::sweep_kernel<false, false, kT, kC, true, true><<<grid, kT, 0, stream>>>(p);
-      }
-    } else if (mode == TT_MODE_STORE) {
-      if (p.mark_enable) tt::sweep_kernel<true, true, kT, kC, false, true><<<grid, kT, 0, stream>>>(p);
-      else tt::sweep_kernel<true, false, kT, kC, false, true><<<grid, kT, 0, stream>>>(p);
-    } else {
-      tt::sweep_kernel<false, false, kT, kC, false, true><<<grid, kT, 0, stream>>>(p);
-    }
-  } else if (range) {
+  if (range) {
     if (mode == TT_MODE_STORE) {
       if (p.mark_enable) tt::sweep_kernel<true, true, kT, kC, true><<<grid, kT, 0, stream>>>(p);
       else tt::sweep_kernel<true, false, kT, kC, true><<<grid, kT, 0, stream>>>(p);
@@ -648,14 +622,14 @@ int32_t sweep_run(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_
   }
   TT_CUDA(cudaGetLastError());
   if (timing) TT_CUDA(cudaEventRecord(t->ev1, stream));
-  st->launches += 1;
-  if (place) {
+  st->launches = 1;
+  if (listing) {
     // K3: row order and TaskIds; the hit count is read from the control block on the device
-    if (push_k3 || place_by_group()) {
+    if (push || place_by_group()) {
       // K3g: tile-ordered placement, optionally fused with the push of the compact form (sweep.cuh); it
       // derives every tile's offset in the row-ordered list from K1's partial sums itself (no K2)
-      const tt::PushTarget none = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0};
-      if (hook && hook->wait_slot0 && !early) {  // the root must have read this shard's slot of the previous tick
+      const tt::PushTarget none = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+      if (hook && hook->wait_slot0) {  // the root must have read this shard's slot of the previous tick
         tt::shard_wait_kernel<<<1, 32, 0, stream>>>(hook->wait_slot0, 0, 1, offsetof(tt::SlotHeader, consumed),
                                                     hook->wait_value, hook->timeout_ns, nullptr, nullptr);
         TT_CUDA(cudaGetLastError());
@@ -678,8 +652,8 @@ int32_t sweep_run(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_
                                (const uint32_t*)p.tile_slot, (const uint32_t*)p.tile_count,                             \
                                (const uint32_t*)p.group_sum, (const uint32_t*)p.sub_sum, (uint32_t)num_tiles,           \
                                (const uint4*)t->task_id, (const uint64_t*)t->created_raw, d_rows, d_ids,                \
-                               push_k3 ? *push_k3 : none))
-      switch (push_k3 ? push_variant : plain_variant) {
+                               push ? *push : none))
+      switch (push ? push_variant : plain_variant) {
         case 2: TT_PLACE_LAUNCH(2, 2); break;
         case 4: TT_PLACE_LAUNCH(4, 4); break;
         case 8: TT_PLACE_LAUNCH(8, 4); break;
@@ -697,7 +671,7 @@ int32_t sweep_run(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_
           (unsigned)std::max<int64_t>(1, std::min<int64_t>((cap + per_cta - 1) / per_cta, (int64_t)t->sm_count * 8));
       tt::place_hits_kernel<TT_TILE_ROWS><<<pgrid, tt::kPlaceThreads, 0, stream>>>(
           t->ctl, t->hit_list, p.tile_slot, tile_first, first_tile, t->task_id, d_rows, d_ids);
-      st->launches += 2;
+      st->launches = 3;
     }
     TT_CUDA(cudaGetLastError());
   }
@@ -1199,8 +1173,6 @@ int32_t tt_sweep_push(tt_table* t, int32_t mode, int32_t flags, int64_t today_lo
   push.ids = nullptr;
   push.created = nullptr;
   push.tile_first = nullptr;
-  push.tile_slot = nullptr;
-  push.early = 0;
   return sweep_run(t, mode, flags, today_local_ticks, run_at_utc_ticks, 0, d_rows, (uint4*)d_ids, cap, h_stats,
                    stream ? (cudaStream_t)stream : t->stream, &push);
 }

@@ -39,7 +39,6 @@ JSON_DOCUMENT = 1  # TT_JSON_DOCUMENT: the encoder of Dapr's client bodies
 
 EXCHANGE_IDS = 1       # TT_EXCHANGE_IDS: the slots carry the hits' TaskIds
 EXCHANGE_CREATED = 2   # TT_EXCHANGE_CREATED: ... and their TaskCreatedOn (the cross-shard OrderBy)
-EXCHANGE_EARLY = 4     # TT_EXCHANGE_EARLY: rows only; the shards' sweep kernels store into the slots while they run
 ORDER_ROWS = 0         # TT_ORDER_ROWS
 ORDER_CREATED_ASC = 1  # TT_ORDER_CREATED_ASC
 COLLECT_RELEASE = 0x100

@@ -38,12 +38,10 @@ def parse():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--rows", type=int, default=1_000_000_000, help="rows per GPU (weak) or in total (strong)")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
-    ap.add_argument("--exchange", default="rows", choices=["rows", "ids", "early"],
+    ap.add_argument("--exchange", default="rows", choices=["rows", "ids"],
                     help="what the shards' placement kernels store into rank 0's buffer over NVLink (N > 1, tt_exchange_*): "
                          "rows = the compact row lists (2-byte in-tile offsets + per-tile counts), each shard keeping its "
-                         "TaskIds; ids = the 16-byte TaskIds as well; early = the compact row lists again, but stored by the "
-                         "SWEEP kernels while they run (TT_EXCHANGE_EARLY: tile runs in cursor order, put in row order by "
-                         "rank 0), so that rank 0's NVLink intake is spread over the whole tick")
+                         "TaskIds; ids = the 16-byte TaskIds as well")
     ap.add_argument("--root-share", type=float, default=0.0,
                     help="N > 1: rank 0's shard as a fraction of an equal share (rank 0 also collects every shard's list, "
                          "so its TaskId range can be made smaller while the other ranks split the rest equally); 0 = 1.0, equal "
@@ -330,8 +328,8 @@ def run_b200(args):
     first, last = shard_of(n_total, rank)
     n_rows = last - first
     with_root_ids = args.exchange == "ids"
-    ex_main = {"rows": 0, "ids": tt.EXCHANGE_IDS, "early": tt.EXCHANGE_EARLY}[args.exchange]
-    run = ShardRun(pkg, torch, dist, dev, local, rank, world, n_total, first, n_rows, ex_main, local_ids=not with_root_ids)
+    run = ShardRun(pkg, torch, dist, dev, local, rank, world, n_total, first, n_rows,
+                   tt.EXCHANGE_IDS if with_root_ids else 0, local_ids=not with_root_ids)
     clocks = ClockSampler(local)
     head = run.timed(args.steps, args.warmup, clocks_for=clocks)
     value = n_total * args.steps / (head["total_ms"] * 1e-3)
@@ -407,8 +405,7 @@ def run_b200(args):
             r2.close()
         # BASELINE.json config 3: ONE table of args.rows tasks sharded by TaskId range over the N GPUs
         s_first, s_last = shard_of(args.rows, rank)
-        r3 = ShardRun(pkg, torch, dist, dev, local, rank, world, args.rows, s_first, s_last - s_first,
-                      tt.EXCHANGE_EARLY if args.exchange == "early" else 0)
+        r3 = ShardRun(pkg, torch, dist, dev, local, rank, world, args.rows, s_first, s_last - s_first, 0)
         m = r3.timed(x_steps, x_warm)
         extra["strong_ms_per_step"] = m["ms_per_step"]
         extra["strong_tasks_per_sec"] = args.rows * x_steps / (m["total_ms"] * 1e-3)
@@ -470,9 +467,7 @@ def run_b200(args):
                     traffic = tj.get("dram_bytes_per_launch")
             except Exception:
                 pass
-        exchange = "none" if world == 1 else ("fused push of compact rows + TaskIds" if with_root_ids else
-                                              "compact rows stored by the sweep kernels while they run, tiles ordered by rank 0"
-                                              if args.exchange == "early" else "fused push of compact rows")
+        exchange = "none" if world == 1 else ("fused push of compact rows + TaskIds" if with_root_ids else "fused push of compact rows")
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": args.scaling,

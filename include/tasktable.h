@@ -476,12 +476,6 @@ typedef struct tt_exchange tt_exchange;
 typedef struct tt_gresult tt_gresult;
 #define TT_EXCHANGE_IDS 1
 #define TT_EXCHANGE_CREATED 2
-#define TT_EXCHANGE_EARLY 4 /* row numbers only, and sent EARLY: a shard's sweep kernel itself stores every tile's in-tile
-                               offsets into the slot while it runs (in the order its tiles finished), and the root puts
-                               each slot's tiles in row order during the collect.  The shards' stores then cross NVLink
-                               during the whole sweep instead of in a burst after it; a shard's placement kernel (run
-                               when d_rows is given: its own list and TaskIds) pushes nothing.  Not combinable with the
-                               two flags above                                                                         */
 #define TT_ORDER_ROWS 0
 #define TT_ORDER_CREATED_ASC 1
 #define TT_COLLECT_RELEASE 0x100 /* OR into order (TT_ORDER_ROWS only): release the epoch inside the collect; the

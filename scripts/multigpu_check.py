@@ -111,33 +111,6 @@ def main():
     sx.close()
     table_q.close()
     table_p.close()
-    # the early form (TT_EXCHANGE_EARLY): K1 itself stores into rank 0's buffer while it runs, every shard still keeps
-    # its own row list and TaskIds, rank 0 puts the tiles of every slot in order
-    table_e = pkg.TaskTable(local).generate(cfg, plan.first_row, plan.n_rows)
-    se = pkg.ShardExchange(plan.first_row, plan.n_rows, cap, local, tt.EXCHANGE_EARLY)
-    for tick in range(2):
-        dist.barrier()
-        se.tick(table_e, tt.MODE_STORE, tt.SWEEP_MARK | tt.SWEEP_ASYNC | tt.SWEEP_NO_TIMING, stream=stream.cuda_stream,
-                d_rows=None if rank == 0 else p_rows.data_ptr(), d_ids=None if rank == 0 else p_ids.data_ptr())
-        oke = True
-        if rank == 0:
-            res = se.collect(tt.ORDER_ROWS | tt.COLLECT_RELEASE)
-            if tick == 0:
-                oke = res.shard_counts()[:world] == counts and bool((torch.from_numpy(res.rows().astype(np.int64)) == glob.cpu()).all())
-            else:
-                oke = res.count == 0
-        ste, _ = table_e.sweep_wait()
-        if tick == 0 and rank != 0:
-            oke = (ste.n_stored == st.n_stored and bool((p_rows[: ste.n_stored] == d_rows[: st.n_stored]).all())
-                   and bool((p_ids[: ste.n_stored] == d_ids[: st.n_stored]).all()))
-        elif tick == 1:
-            oke = oke and ste.n_listed == 0
-        if rank == 0:
-            print("early exchange tick", tick, "agrees" if oke else "DIFFERS")
-        assert oke
-    assert table_e.count_flags() == table.count_flags()
-    se.close()
-    table_e.close()
     ok = True
     if rank == 0:
         from oracle import oracle as orc

@@ -319,12 +319,10 @@ def test_sharded_manager_with_empty_shards(oracle):
     st.close()
 
 
-@pytest.mark.parametrize("form", [tt.EXCHANGE_IDS, tt.EXCHANGE_EARLY])
 @pytest.mark.parametrize("ppm", [300, 120_000, 1_000_000])
-def test_exchange_at_every_density(oracle, ppm, form):
+def test_exchange_at_every_density(oracle, ppm):
     """From a hit every few thousand rows (most tiles empty) to every row a hit (pieces beyond the staging area take the
-    direct path): three shards of ragged sizes, two ticks into the same slots — pushed by the placement kernel in row
-    order, or (early form) by the sweep kernel in the order its tiles finished and put in order by the root."""
+    direct path): three shards of ragged sizes, two ticks into the same slots."""
     n, world = 530_000, 3
     cfg = oracle.default_cfg(77 + ppm, n, n_creators=10, ppm_due_yesterday=ppm, ppm_adversarial=0, ppm_completed=0, ppm_overdue_past=0)
     ot = oracle.OracleTable()
@@ -336,109 +334,15 @@ def test_exchange_at_every_density(oracle, ppm, form):
     tiles = max((len(t) + 8191) // 8192 for t in tables)
     cap = (max(len(t) for t in tables) + 7) // 8 * 8
     ids_all, _, _ = ot.export()
-    root, _ = tt.Exchange.create_root(0, world, cap, tiles, form)
+    root, _ = tt.Exchange.create_root(0, world, cap, tiles, tt.EXCHANGE_IDS)
     ex = [root] + [root.attach_local(0, g) for g in range(1, world)]
     for tick in range(2):
         for g in range(world):
             ex[g].tick(tables[g], tt.MODE_STORE, tt.SWEEP_LIST_ONLY)
         res = root.collect(tt.ORDER_ROWS, bounds[:world])
-        assert res.count == len(want) and (res.rows() == want).all(), tick
-        if form == tt.EXCHANGE_IDS:
-            assert (res.ids() == ids_all[want]).all(), tick
+        assert res.count == len(want) and (res.rows() == want).all() and (res.ids() == ids_all[want]).all(), tick
         root.release()
     for x in ex[1:] + [root]:
         x.close()
     for t in tables:
         t.close()
-
-
-def test_early_exchange_marks_and_copes_with_small_slots(oracle):
-    """The early form through a marking tick (every shard's flag plane against the oracle's cron job, a second tick
-    lists nothing), and with slots too small for the hits: the tick says TT_ERR_CAPACITY, the root's list holds every
-    tile that fitted, in row order, and exactly those rows were marked."""
-    n, world = 450_000, 3
-    cfg = oracle.default_cfg(91, n, n_creators=10, ppm_due_yesterday=200_000)
-    ot = oracle.OracleTable()
-    ot.add_synth(cfg, 0, n)
-    bounds = [0, 140_000, 300_001, n]
-    tables = [tt.TaskTable(0).generate(cfg, bounds[g], bounds[g + 1] - bounds[g]) for g in range(world)]
-    tiles = max((len(t) + 8191) // 8192 for t in tables)
-    with pytest.raises(tt.TaskTableError):
-        tt.Exchange.create_root(0, world, 1024, tiles, tt.EXCHANGE_EARLY | tt.EXCHANGE_IDS)
-    # small slots first (listing only, nothing is marked yet)
-    small, _ = tt.Exchange.create_root(0, world, 4096, tiles, tt.EXCHANGE_EARLY)
-    sx = [small] + [small.attach_local(0, g) for g in range(1, world)]
-    want = np.sort(ot.get_yesterdays_due(tt.MODE_STORE))
-    stored = []
-    for g in range(world):
-        st, rc = sx[g].tick(tables[g], tt.MODE_STORE, tt.SWEEP_LIST_ONLY, allow_capacity=True)
-        assert rc == tt.TT_ERR_CAPACITY and 0 < st.n_stored <= 4096 < st.n_listed
-        stored.append(st.n_stored)
-    part = small.collect(tt.ORDER_ROWS | tt.COLLECT_RELEASE, bounds[:world])
-    rows = part.rows().astype(np.int64)
-    assert part.shard_counts()[:world] == stored and len(rows) == sum(stored)
-    assert np.isin(rows, want).all() and (np.diff(rows) > 0).all()
-    for x in sx[1:] + [small]:
-        x.close()
-    # the marking tick
-    cap = (max(len(t) for t in tables) + 7) // 8 * 8
-    root, _ = tt.Exchange.create_root(0, world, cap, tiles, tt.EXCHANGE_EARLY)
-    ex = [root] + [root.attach_local(0, g) for g in range(1, world)]
-    _, listed, n_over = ot.cron_job(tt.MODE_STORE)
-    for g in (2, 0, 1):
-        st, _ = ex[g].tick(tables[g], tt.MODE_STORE, tt.SWEEP_MARK)
-        assert st.n_marked == st.n_stored
-    res = root.collect(tt.ORDER_ROWS | tt.COLLECT_RELEASE, bounds[:world])
-    assert (res.rows() == np.sort(listed)).all() and res.count == n_over
-    c, o = ot.flags()
-    for g in range(world):
-        gc, go = tables[g].flags_bytes()
-        assert (gc == c[bounds[g]:bounds[g + 1]]).all() and (go == o[bounds[g]:bounds[g + 1]]).all()
-    for g in range(world):
-        ex[g].tick(tables[g], tt.MODE_STORE, tt.SWEEP_MARK)
-    assert root.collect(tt.ORDER_ROWS | tt.COLLECT_RELEASE, bounds[:world]).count == 0
-    for x in ex[1:] + [root]:
-        x.close()
-    for t in tables:
-        t.close()
-
-
-def test_early_exchange_across_two_processes(oracle, tmp_path):
-    """The early form with shard 1 in another process: its sweep kernel stores through the CUDA IPC mapping while it
-    runs, the root orders the tiles.  Two marking ticks (the second finds nothing and has to wait for the release)."""
-    n, seed = 500_000, 4712
-    cfg = oracle.default_cfg(seed, n, n_creators=10, ppm_created_dup=100_000)
-    ot = oracle.OracleTable()
-    ot.add_synth(cfg, 0, n)
-    half = n // 2
-    table = tt.TaskTable(0).generate(cfg, 0, half)
-    cap, tiles, flags = 32768, (n - half + 8191) // 8192, tt.EXCHANGE_EARLY
-    root, handle = tt.Exchange.create_root(0, 2, cap, tiles, flags)
-    script = tmp_path / "child.py"
-    script.write_text(CHILD)
-    repo = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    child = subprocess.Popen([sys.executable, str(script), repo, str(seed), str(n), str(half), str(n - half), str(cap), str(tiles),
-                              str(flags), "100000"], stdin=subprocess.PIPE, stdout=subprocess.PIPE, text=True)
-    try:
-        child.stdin.write(handle.hex() + "\n")
-        _, listed, n_over = ot.cron_job(tt.MODE_STORE)
-        child.stdin.write(f"{tt.MODE_STORE}\n")
-        child.stdin.flush()
-        st0, _ = root.tick(table, tt.MODE_STORE, tt.SWEEP_MARK)
-        theirs = [int(x) for x in child.stdout.readline().split()]
-        res = root.collect(tt.ORDER_ROWS | tt.COLLECT_RELEASE, [0, half])
-        assert res.count == n_over == st0.n_stored + theirs[0] and st0.n_marked + theirs[1] == n_over
-        assert (res.rows() == np.sort(listed)).all()
-        child.stdin.write(f"{tt.MODE_STORE}\n")
-        child.stdin.flush()
-        root.tick(table, tt.MODE_STORE, tt.SWEEP_MARK)
-        assert [int(x) for x in child.stdout.readline().split()] == [0, 0]
-        assert root.collect(tt.ORDER_ROWS | tt.COLLECT_RELEASE, [0, half]).count == 0
-        child.stdin.write("quit\n")
-        child.stdin.flush()
-        assert child.wait(timeout=60) == 0
-    finally:
-        if child.poll() is None:
-            child.kill()
-    root.close()
-    table.close()
