@@ -222,13 +222,16 @@ __device__ const uint8_t* read_string_inplace(uint8_t* p, const uint8_t* end, ui
       w += run;
       if (r < end) c = *r;
     } else {
-      while (r < end) {
-        c = *r;
-        if (c == '"' || c == '\\' || c < 0x20 || c >= 0x80) break;
-        *w = (uint8_t)c;
-        ++w;
-        ++r;
+      // behind an escape the run moves down (w < r): its length from word-wise tests, its bytes eight per load
+      const uint32_t run = plain_run(r, end);
+      for (uint32_t k = 0; k < run; k += 8) {
+        const uint64_t v = load8(r + k);
+        const uint32_t left = run - k < 8u ? run - k : 8u;
+        for (uint32_t j = 0; j < left; ++j) w[k + j] = (uint8_t)(v >> (8 * j));
       }
+      r += run;
+      w += run;
+      if (r < end) c = *r;
     }
     if (r >= end) return nullptr;
     if (c == '"') break;
@@ -478,6 +481,37 @@ __device__ __forceinline__ bool parse_guid(const S& s, int len, uint4* out) {
   return true;
 }
 
+// Eight ASCII hex digits (either case) -> their values as four bytes, the first pair in the lowest byte; false when a
+// byte is not a hex digit.  Per byte, without carries between bytes (every addend is below 0x80):
+// d = x ^ '0' is 0..9 for a digit, l = (x | 0x20) ^ 0x60 is 1..6 for a letter a-f / A-F.
+__device__ __forceinline__ bool hex8(uint64_t x, uint32_t* out) {
+  constexpr uint64_t k7F = kOnes * 0x7Fu;
+  const uint64_t d = x ^ (kOnes * 0x30u);
+  const uint64_t l = (x | (kOnes * 0x20u)) ^ (kOnes * 0x60u);
+  const uint64_t dig = ~(((d & k7F) + kOnes * 0x76u) | d) & kHighs;                                  // d <= 9
+  const uint64_t let = ~(((l & k7F) + kOnes * 0x79u) | l) & ((l & k7F) + k7F) & kHighs;              // 1 <= l <= 6
+  if ((dig | let) != kHighs) return false;
+  const uint64_t nib = (x & (kOnes * 0x0Fu)) + (let >> 7) * 9u;
+  const uint64_t y = (nib << 4) | (nib >> 8);  // even bytes: first digit of a pair << 4 | second
+  *out = __byte_perm((uint32_t)y, (uint32_t)(y >> 32), 0x6420);
+  return true;
+}
+
+// The usual Guid — 36 characters in registers: four words of eight hex digits each, cut out around the dashes.
+__device__ __forceinline__ bool parse_guid36(const Chars48& s, uint4* out) {
+  const uint64_t w0 = s.w[0], w1 = s.w[1], w2 = s.w[2], w3 = s.w[3], w4 = s.w[4];
+  const bool dashes = ((uint32_t)w1 & 0xFFu) == '-' && ((uint32_t)(w1 >> 40) & 0xFFu) == '-' &&
+                      ((uint32_t)(w2 >> 16) & 0xFFu) == '-' && (uint32_t)(w2 >> 56) == '-';
+  if (!dashes) return false;
+  const uint64_t h1 = ((w1 >> 8) & 0xFFFFFFFFull) | ((w1 >> 48) << 32) | (w2 << 48);  // characters 9-12, 14-15, 16-17
+  const uint64_t h2 = ((w2 >> 24) & 0xFFFFFFFFull) | (w3 << 32);                       // 19-22, 24-27
+  const uint64_t h3 = (w3 >> 32) | (w4 << 32);                                         // 28-35
+  uint4 id;
+  if (!hex8(w0, &id.x) || !hex8(h1, &id.y) || !hex8(h2, &id.z) || !hex8(h3, &id.w)) return false;
+  *out = id;
+  return true;
+}
+
 template <typename S>
 __device__ __forceinline__ int two_digits(const S& s, int at) {
   const int a = (int)s[at] - '0', b = (int)s[at + 1] - '0';
@@ -563,17 +597,49 @@ __device__ bool parse_datetime(const S& s, int len, int32_t local_offset_min, ui
 // K7a: one thread per document.
 // `text` holds the caller's bytes [window_first, window_first + bytes); doc_off are the caller's offsets.  A document
 // whose range is not inside that window, or runs backwards, is a bad document.
+//
+// Where the bytes come from.  Thread i reads document i, so the lanes of a warp read addresses ~300 bytes apart and
+// every load instruction is 32 separate L1 accesses: at ~100 loads per document the kernel was bound by the load/store
+// unit, not by instructions or DRAM (shorter instruction streams did not make it faster).  A warp's 32 documents are
+// one contiguous piece of the text (~9.4 KB), so the warp first copies that piece into its own part of shared memory
+// with coalesced 16-byte loads (same 16-byte alignment as in global memory), and every lane parses — and unescapes in
+// place — its document THERE; strings that were unescaped are copied back by their lane (few and short), offsets are
+// reported relative to the text as before.  A warp whose piece does not fit (stage_bytes per warp; very long
+// documents) or whose offsets are out of order parses in global memory as before.
 template <int MIN_CTAS>
 __global__ void __launch_bounds__(128, MIN_CTAS) doc_parse_kernel(uint8_t* text, const uint64_t* doc_off, uint64_t window_first,
                                                         uint64_t bytes, int64_t n, int32_t local_offset_min,
-                                                        DocCols out) {
+                                                        DocCols out, uint32_t stage_bytes) {
+  extern __shared__ __align__(16) uint8_t s_text[];
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  uint8_t* const base = text;
-  const uint64_t a = doc_off[i], b = doc_off[i + 1];
-  const bool in_window = a >= window_first && b >= a && b - window_first <= bytes;
-  const uint8_t* p = text + (in_window ? a - window_first : 0);
-  const uint8_t* const end = text + (in_window ? b - window_first : 0);
+  const uint32_t lane = threadIdx.x & 31u;
+  const bool live = i < n;
+  const uint64_t a = live ? doc_off[i] : 0, b = live ? doc_off[i + 1] : 0;
+  const bool in_window = live && a >= window_first && b >= a && b - window_first <= bytes;
+  // the warp's piece of the text: [lo, hi) relative to the window, copied from the 16-byte boundary below lo
+  uint64_t lo = in_window ? a - window_first : ~0ull, hi = in_window ? b - window_first : 0ull;
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) {
+    const uint64_t l2 = __shfl_xor_sync(0xFFFFFFFFu, lo, d), h2 = __shfl_xor_sync(0xFFFFFFFFu, hi, d);
+    lo = l2 < lo ? l2 : lo;
+    hi = h2 > hi ? h2 : hi;
+  }
+  const uint64_t span_start = lo & ~15ull;
+  const uint64_t copy_len = hi > span_start ? ((hi - span_start + 15) & ~15ull) : 0;
+  const bool staged = stage_bytes != 0 && __all_sync(0xFFFFFFFFu, !live || in_window) && lo != ~0ull &&
+                      copy_len + 16 <= stage_bytes;
+  uint8_t* const s_warp = s_text + (size_t)(threadIdx.x >> 5) * stage_bytes;
+  if (staged) {
+    const uint4* g = reinterpret_cast<const uint4*>(text + span_start);
+    uint4* d = reinterpret_cast<uint4*>(s_warp);
+    for (uint32_t o = lane; o < (uint32_t)(copy_len >> 4); o += 32) d[o] = g[o];
+    __syncwarp();
+  }
+  if (!live) return;
+  // `base`: the address offset 0 of the text has in the space this lane parses in
+  uint8_t* const base = staged ? s_warp - span_start : text;
+  const uint8_t* p = base + (in_window ? a - window_first : 0);
+  const uint8_t* const end = base + (in_window ? b - window_first : 0);
   uint4 id = make_uint4(0, 0, 0, 0);
   uint64_t created = 0, due = 0;
   uint32_t flags = 0;
@@ -581,22 +647,36 @@ __global__ void __launch_bounds__(128, MIN_CTAS) doc_parse_kernel(uint8_t* text,
   uint32_t slen[3] = {0, 0, 0};
   uint32_t status = kDocOk;
 
-  p = skip_ws(p, end);
-  if (p < end && (*p == '[' || *p == ',')) p = skip_ws(p + 1, end);
-  if (!in_window || p >= end || *p != '{') status = kDocSyntax;
+  // `peek`: the byte at p, or 0 at the end, whitespace skipped first — ONE load per token in the usual document (which has
+  // no whitespace); the value is kept in a register, because the text is also written through (unescaping in place) and
+  // the compiler would otherwise read *p again for every test.
+  auto peek = [&](const uint8_t*& q) -> uint32_t {
+    uint32_t c = q < end ? *q : 0u;
+    if (c <= ' ' && c != 0u) {
+      q = skip_ws(q, end);
+      c = q < end ? *q : 0u;
+    }
+    return c;
+  };
+  uint32_t c = peek(p);
+  if (c == '[' || c == ',') {
+    ++p;
+    c = peek(p);
+  }
+  if (!in_window || c != '{') status = kDocSyntax;
   else ++p;
   bool first = true;
   while (status == kDocOk) {
-    p = skip_ws(p, end);
-    if (p >= end) { status = kDocSyntax; break; }
-    if (*p == '}') { ++p; break; }
+    c = peek(p);
+    if (c == 0u) { status = kDocSyntax; break; }
+    if (c == '}') { ++p; break; }
     if (!first) {
-      if (*p != ',') { status = kDocSyntax; break; }
-      p = skip_ws(p + 1, end);
-      if (p >= end) { status = kDocSyntax; break; }
+      if (c != ',') { status = kDocSyntax; break; }
+      ++p;
+      c = peek(p);
     }
     first = false;
-    if (*p != '"') { status = kDocSyntax; break; }
+    if (c != '"') { status = kDocSyntax; break; }
     const uint8_t* after = nullptr;
     int m = member_fast(p + 1, end, &after);
     if (m == -3) {  // an escaped name: unescape it into a local buffer first
@@ -606,10 +686,11 @@ __global__ void __launch_bounds__(128, MIN_CTAS) doc_parse_kernel(uint8_t* text,
       m = !after ? -2 : nlen <= 16 ? member_of(name, nlen) : -1;
     }
     if (m == -2) { status = kDocString; break; }
-    p = skip_ws(after, end);
-    if (p >= end || *p != ':') { status = kDocSyntax; break; }
-    p = skip_ws(p + 1, end);
-    if (p >= end) { status = kDocSyntax; break; }
+    p = after;
+    if (peek(p) != ':') { status = kDocSyntax; break; }
+    ++p;
+    c = peek(p);
+    if (c == 0u) { status = kDocSyntax; break; }
     if (m < 0) {
       p = skip_value(p, end);
       if (!p) status = kDocSyntax;
@@ -617,26 +698,31 @@ __global__ void __launch_bounds__(128, MIN_CTAS) doc_parse_kernel(uint8_t* text,
     }
     if (m == 6 || m == 7) {
       const uint32_t bit = m == 6 ? 1u : 2u;
-      if (lit_eq(p, end, "true", 4)) { flags |= bit; p += 4; }
-      else if (lit_eq(p, end, "false", 5)) { flags &= ~bit; p += 5; }
+      if (c == 't' && lit_eq(p, end, "true", 4)) { flags |= bit; p += 4; }
+      else if (c == 'f' && lit_eq(p, end, "false", 5)) { flags &= ~bit; p += 5; }
       else status = kDocType;
       continue;
     }
     if (m == 1 || m == 2 || m == 5) {
-      const int c = m == 1 ? 0 : m == 2 ? 1 : 2;
+      const int col = m == 1 ? 0 : m == 2 ? 1 : 2;
       // null stays null (flag bits 4..6 of the document's flag byte); a later repeat of the member overwrites it
-      if (lit_eq(p, end, "null", 4)) { slen[c] = 0; sstart[c] = base; flags |= 16u << c; p += 4; continue; }
-      flags &= ~(16u << c);
-      if (*p != '"') { status = kDocType; continue; }
-      p = read_string_inplace(const_cast<uint8_t*>(p) + 1, end, &sstart[c], &slen[c]);
+      if (c == 'n' && lit_eq(p, end, "null", 4)) { slen[col] = 0; sstart[col] = base; flags |= 16u << col; p += 4; continue; }
+      flags &= ~(16u << col);
+      if (c != '"') { status = kDocType; continue; }
+      p = read_string_inplace(const_cast<uint8_t*>(p) + 1, end, &sstart[col], &slen[col]);
       if (!p) status = kDocString;
+      else if (staged && (uint32_t)(p - 1 - sstart[col]) != slen[col]) {
+        // unescaped (it shrank): the text in global memory gets the bytes later kernels read at this offset
+        uint8_t* g = text + (sstart[col] - base);
+        for (uint32_t j = 0; j < slen[col]; ++j) g[j] = sstart[col][j];
+      }
       continue;
     }
     // taskId and the two dates: short strings parsed from a local copy
-    if (*p != '"') { status = kDocType; continue; }
+    if (c != '"') { status = kDocType; continue; }
     Chars48 cs;  // the value's first 48 bytes in registers: Guid and dates are parsed without another load
     cs.load(p + 1, end);
-    if (m == 0 && end - p > 37 && cs[36] == '"' && parse_guid(cs, 36, &id)) {  // the usual 36 plain characters
+    if (m == 0 && end - p > 37 && cs[36] == '"' && parse_guid36(cs, &id)) {  // the usual 36 plain characters
       p += 38;
       continue;
     }
@@ -644,7 +730,7 @@ __global__ void __launch_bounds__(128, MIN_CTAS) doc_parse_kernel(uint8_t* text,
     if (plain >= 48 || p + 1 + plain >= end || cs[plain] != '"') plain = plain_string_len(p + 1, end, 48);
     if (plain >= 0) {  // no escape inside: parsed where it lies
       if (m == 0) {
-        if (!parse_guid(cs, plain, &id)) status = kDocGuid;
+        if (plain != 36 || !parse_guid36(cs, &id)) status = kDocGuid;
       } else {
         uint64_t raw = 0;
         if (!parse_datetime(cs, plain, local_offset_min, &raw)) status = kDocDate;
@@ -669,8 +755,11 @@ __global__ void __launch_bounds__(128, MIN_CTAS) doc_parse_kernel(uint8_t* text,
     }
   }
   if (status == kDocOk) {
-    p = skip_ws(p, end);
-    if (p < end && (*p == ',' || *p == ']')) p = skip_ws(p + 1, end);
+    c = peek(p);
+    if (c == ',' || c == ']') {
+      ++p;
+      peek(p);
+    }
     if (p != end) status = kDocSyntax;
   }
   out.status[i] = status;
