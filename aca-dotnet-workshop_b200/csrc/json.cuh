@@ -404,8 +404,9 @@ __device__ uint32_t datetime_write(uint64_t raw, int32_t local_offset_min, uint8
   return p;
 }
 
-constexpr int kJsonThreads = 128;            // records per CTA
-constexpr int kJsonStageBytes = 44 * 1024;   // shared-memory staging per CTA (5 CTAs per SM)
+constexpr int kJsonThreads = 128;            // records per CTA (the default; the kernels are built for 64 and 256 as well)
+constexpr int kJsonStagePerThread = 352;     // shared-memory staging per record: 44 KB per 128-thread CTA, 5 CTAs per SM
+constexpr int json_stage_bytes(int threads) { return threads * kJsonStagePerThread; }
 
 // A string member that holds null (a C# string may: `"taskName":null` in a stored document) is written
 // as the literal null, as JsonSerializer does.  Its ref in the row's string column is kRefNull; in a
@@ -495,10 +496,11 @@ __device__ __forceinline__ JsonRecord json_plan_load(const JsonParams& p, int64_
 
 // K6a: gathers every record's fields once (the scattered reads), keeps them as the plan, and
 // sizes every CTA's piece of the text
-__global__ void __launch_bounds__(kJsonThreads) json_len_kernel(JsonParams p) {
+template <int THREADS>
+__global__ void __launch_bounds__(THREADS) json_len_kernel(JsonParams p) {
   __shared__ uint32_t s_warp[32];
   const uint64_t keep = l2_evict_last_policy(), stream = l2_evict_first_policy();
-  const int64_t i = (int64_t)blockIdx.x * kJsonThreads + threadIdx.x;
+  const int64_t i = (int64_t)blockIdx.x * THREADS + threadIdx.x;
   const JsonRecord r = json_gather(p, i, keep);
   if (r.live) json_plan_store(p, i, r, stream);
   uint32_t tot;
@@ -594,11 +596,12 @@ __device__ uint8_t* json_write_record(const JsonParams& p, const JsonRecord& r, 
 // so it is staged in shared memory (shifted so that 16-byte chunks of both line up) and flushed
 // with 16-byte stores.  A CTA whose piece does not fit the staging area (very long strings)
 // writes straight to global memory instead.
-__global__ void __launch_bounds__(kJsonThreads) json_emit_kernel(JsonParams p) {
+template <int THREADS>
+__global__ void __launch_bounds__(THREADS) json_emit_kernel(JsonParams p) {
   extern __shared__ __align__(16) uint8_t s_stage[];
   __shared__ uint32_t s_warp[32];
   const uint64_t keep = l2_evict_last_policy(), stream = l2_evict_first_policy();
-  const int64_t i = (int64_t)blockIdx.x * kJsonThreads + threadIdx.x;
+  const int64_t i = (int64_t)blockIdx.x * THREADS + threadIdx.x;
   const JsonRecord r = json_plan_load(p, i, stream);
   uint4 id = make_uint4(0, 0, 0, 0);
   if (r.live) id = p.ids[i];
@@ -609,14 +612,14 @@ __global__ void __launch_bounds__(kJsonThreads) json_emit_kernel(JsonParams p) {
   const uint32_t local = block_exclusive_scan(json_record_len(p, r, i), s_warp, &total);
   const uint64_t base = p.block_base[blockIdx.x];
   const uint32_t shift = (uint32_t)(base & 15u);
-  const bool staged = shift + total <= (uint32_t)kJsonStageBytes;
+  const bool staged = shift + total <= (uint32_t)json_stage_bytes(THREADS);
   if (r.live && p.rec_off) st_hint_u64(p.rec_off + i, base + local, stream);
   if (r.live) json_write_record(p, r, id, i, staged ? s_stage + shift + local : p.out + base + local, h0, h1, h2, keep);
   if (!staged) return;
   __syncthreads();
   uint8_t* dst = p.out + (base - shift);
   const uint32_t lo = shift, hi = shift + total;
-  for (uint32_t a = threadIdx.x * 16; a < hi; a += kJsonThreads * 16) {
+  for (uint32_t a = threadIdx.x * 16; a < hi; a += THREADS * 16) {
     if (a >= lo && a + 16 <= hi) {
       st_hint_v4(reinterpret_cast<uint4*>(dst + a), *reinterpret_cast<const uint4*>(s_stage + a), stream);
     } else {

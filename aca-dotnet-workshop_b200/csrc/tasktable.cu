@@ -71,6 +71,10 @@ struct TableCore {
   std::mutex pool_mu;
   void* spare = nullptr;
   size_t spare_bytes = 0;
+  // the same for the text of a JSON emission (tt_result_json): sizing and emitting are two kernels with the allocation
+  // of the text between them, and cudaMalloc of gigabytes took longer than either kernel's launch gap
+  void* json_spare = nullptr;
+  size_t json_spare_bytes = 0;
 };
 
 struct tt_table {
@@ -908,6 +912,9 @@ int32_t tt_destroy(tt_table* t) {
     cudaFree(t->core->spare);
     t->core->spare = nullptr;
     t->core->spare_bytes = 0;
+    cudaFree(t->core->json_spare);
+    t->core->json_spare = nullptr;
+    t->core->json_spare_bytes = 0;
   }
   {
     DeviceGuard g(t->device);
