@@ -286,3 +286,25 @@ def test_both_dictionary_encoders_give_the_same_table(oracle, env, monkeypatch):
     creators = {src.created_by(i) for i in range(0, n, 997)}
     assert same_table(oracle, ot, table, creators, -300) > 40
     table.close()
+
+
+@pytest.mark.parametrize("stage", ["0", "4096", "11264"])
+def test_parser_staging_through_shared_memory_or_not(oracle, stage, monkeypatch):
+    """The parser reads a warp's 32 documents from a copy in shared memory; warps whose documents do not fit (here: a
+    4 KB stage, and documents with long names) and TT_PARSE_STAGE=0 read global memory.  Same table either way,
+    escapes (unescaped in the copy, written back) included."""
+    monkeypatch.setenv("TT_PARSE_STAGE", stage)
+    n = 30_000
+    cfg = oracle.default_cfg(0xD2C, n, n_creators=40, n_names=2_000)
+    src = oracle.OracleTable()
+    src.add_synth(cfg, 0, n)
+    for flavor in (tt.JSON_DOCUMENT, tt.JSON_RESPONSE):
+        text, off = src.to_documents(np.arange(n), flavor, 60)
+        ot = oracle.OracleTable()
+        assert ot.add_documents(text, off, 60) == -1
+        table = tt.TaskTable(0)
+        st = table.load_documents(text, off, 60)
+        assert (st.n_docs, st.first_bad, st.n_creators, st.n_names) == (n, -1, 40, 2_000)
+        creators = {src.created_by(i) for i in range(0, n, 1499)}
+        assert same_table(oracle, ot, table, creators, 60) > 20
+        table.close()
