@@ -132,6 +132,22 @@ inline int order_by_created(cudaStream_t stream, SortScratch& sc, const uint64_t
   return (int)(e != cudaSuccess ? e : s2);
 }
 
+// The same when the sort buffers are filled already — sc.keys[0] = the hits' ticks, sc.vals[0] = their rows, in row
+// order (the placement kernel of a listing sweep gathered them: sweep_owned, keys_too): min / max, the sort, and the
+// list written in its final order.
+inline int order_prefilled(cudaStream_t stream, SortScratch& sc, const uint4* task_id, uint32_t* d_rows, uint4* d_ids, int64_t n,
+                           RadixSortInfo* info = nullptr) {
+  if (n <= 0) return 0;
+  int w = 0;
+  cudaError_t e = radix_sort_auto(stream, sc, n, &w, info);
+  if (e != cudaSuccess) return (int)e;
+  const unsigned grid = (unsigned)((n + 255) / 256);
+  emit_rows_ids_kernel<<<grid, 256, 0, stream>>>(sc.vals[w], task_id, d_rows, d_ids, n);
+  e = cudaGetLastError();
+  cudaError_t s2 = cudaStreamSynchronize(stream);
+  return (int)(e != cudaSuccess ? e : s2);
+}
+
 // ---- ordering the creator filter's (query, row) pairs ------------------------------------------
 //
 // `.OrderByDescending(o => o.TaskCreatedOn)` per query (FakeTasksManager.cs:70,

@@ -403,6 +403,7 @@ struct PushTarget {
   uint4* ids;                   // [cap] TaskIds of the hits in row order, or null (the sharded GetYesterdaysDueTasks)
   unsigned long long* created;  // [cap] TaskCreatedOn (.NET dateData) of the hits, or null (the cross-shard OrderBy)
   uint32_t* tile_first;         // [num_tiles] offset of each tile's hits in the row-ordered list, or null
+  int created_as_key;           // 0: `created` receives the raw dateData; 1: its ticks (the sort key of OrderBy(TaskCreatedOn))
 };
 
 // What a sharded tick adds around K3g (shards.cuh): before it, wait until the root has finished
@@ -500,7 +501,10 @@ __global__ void __launch_bounds__(kGroupThreads) place_group_kernel(const uint32
     }
     if (push.created) {
 #pragma unroll
-      for (int j = 0; j < UNROLL; ++j) cr[j] = ld_gather_u64(created_raw + r[j]);
+      for (int j = 0; j < UNROLL; ++j) {
+        cr[j] = ld_gather_u64(created_raw + r[j]);
+        if (push.created_as_key) cr[j] &= TT_TICKS_MASK;
+      }
     }
 #pragma unroll
     for (int j = 0; j < UNROLL; ++j) {

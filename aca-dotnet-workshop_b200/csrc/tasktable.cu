@@ -632,7 +632,7 @@ int32_t sweep_run(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_
     if (push || place_by_group()) {
       // K3g: tile-ordered placement, optionally fused with the push of the compact form (sweep.cuh); it
       // derives every tile's offset in the row-ordered list from K1's partial sums itself (no K2)
-      const tt::PushTarget none = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+      const tt::PushTarget none = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0};
       if (hook && hook->wait_slot0) {  // the root must have read this shard's slot of the previous tick
         tt::shard_wait_kernel<<<1, 32, 0, stream>>>(hook->wait_slot0, 0, 1, offsetof(tt::SlotHeader, consumed),
                                                     hook->wait_value, hook->timeout_ns, nullptr, nullptr);
@@ -657,7 +657,7 @@ int32_t sweep_run(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_
                                (const uint32_t*)p.group_sum, (const uint32_t*)p.sub_sum, (uint32_t)num_tiles,           \
                                (const uint4*)t->task_id, (const uint64_t*)t->created_raw, d_rows, d_ids,                \
                                push ? *push : none))
-      switch (push ? push_variant : plain_variant) {
+      switch (push && push->off16 ? push_variant : plain_variant) {  // a push of creation times only stays on this GPU
         case 2: TT_PLACE_LAUNCH(2, 2); break;
         case 4: TT_PLACE_LAUNCH(4, 4); break;
         case 8: TT_PLACE_LAUNCH(8, 4); break;
@@ -753,9 +753,13 @@ void result_release(tt_result* r) { delete r; }  // the block goes with its last
 // marked no longer match), after which the two row-ordered runs are merged by a sort.
 // with_ids = false: the TaskIds are not gathered here — the caller re-orders the list and gathers them in the
 // final order (a gather per hit saved).
+// keys_too (listing sweeps only): the placement kernel also gathers every hit's TaskCreatedOn ticks — into
+// t->sort.keys[0], with the rows in t->sort.vals[0] instead of the result — so that OrderBy(TaskCreatedOn) starts
+// from a filled sort buffer instead of gathering the keys in a pass of its own.
 int32_t sweep_owned(tt_table* t, int32_t mode, int32_t flags, int64_t today, int64_t run_at, tt_result** out,
-                    tt_sweep_stats* total, bool with_ids = true) {
+                    tt_sweep_stats* total, bool with_ids = true, bool keys_too = false) {
   memset(total, 0, sizeof *total);
+  if (keys_too && ((flags & TT_SWEEP_MARK) || with_ids)) return fail(TT_ERR_ARG, "keys_too goes with a listing sweep without ids");
   tt_result* r = nullptr;
   int64_t guess = std::min<int64_t>(t->n, std::max<int64_t>(65536, t->n / 16));
   int32_t rc = result_alloc(t, guess, &r);
@@ -763,8 +767,19 @@ int32_t sweep_owned(tt_table* t, int32_t mode, int32_t flags, int64_t today, int
   bool merged = false;
   for (int pass = 0; pass < 8; ++pass) {
     tt_sweep_stats st;
-    rc = sweep_run(t, mode, flags, today, run_at, 0, r->d_rows + r->n, with_ids ? r->d_ids + r->n : nullptr, r->cap - r->n, &st,
-                   t->stream);
+    if (keys_too) {
+      const cudaError_t e = t->sort.reserve(r->cap);
+      if (e != cudaSuccess) {
+        result_release(r);
+        cudaGetLastError();
+        return fail(TT_ERR_OOM, "sort buffers: %s", cudaGetErrorString(e));
+      }
+      tt::PushTarget keys = {nullptr, nullptr, nullptr, nullptr, t->sort.keys[0], nullptr, 1};
+      rc = sweep_run(t, mode, flags, today, run_at, 0, t->sort.vals[0], nullptr, r->cap, &st, t->stream, &keys);
+    } else {
+      rc = sweep_run(t, mode, flags, today, run_at, 0, r->d_rows + r->n, with_ids ? r->d_ids + r->n : nullptr, r->cap - r->n,
+                     &st, t->stream);
+    }
     total->kernel_ms += st.kernel_ms;
     total->sweep_ms += st.sweep_ms;
     total->gather_ms += st.gather_ms;
@@ -1069,15 +1084,16 @@ int32_t tt_get_yesterdays_due(tt_table* t, int32_t mode, int64_t today_local_tic
   DeviceGuard g(t->device);
   tt_sweep_stats st;
   tt_result* r = nullptr;
-  int32_t rc = sweep_owned(t, mode, TT_SWEEP_LIST_ONLY, today_local_ticks, 0, &r, &st, mode != TT_MODE_STORE);
+  int32_t rc = sweep_owned(t, mode, TT_SWEEP_LIST_ONLY, today_local_ticks, 0, &r, &st, mode != TT_MODE_STORE,
+                           /*keys_too=*/mode == TT_MODE_STORE);
   if (rc) return rc;
   if (mode == TT_MODE_STORE && r->n > 0) {
-    // TasksStoreManager.cs:136 — OrderBy(TaskCreatedOn), stable; ties keep row order
-    rc = tt::order_by_created(t->stream, t->sort, t->created_raw, t->task_id, r->d_rows, r->d_ids, r->n, /*descending=*/false,
-                              /*rows_unordered=*/false, &t->last_order);
+    // TasksStoreManager.cs:136 — OrderBy(TaskCreatedOn), stable; ties keep row order (the sweep left ticks and rows
+    // in the sort buffers)
+    rc = tt::order_prefilled(t->stream, t->sort, t->task_id, r->d_rows, r->d_ids, r->n, &t->last_order);
     if (rc != 0) {
       result_release(r);
-      return fail(TT_ERR_CUDA, "order_by_created failed: %s", cudaGetErrorString((cudaError_t)rc));
+      return fail(TT_ERR_CUDA, "ordering by TaskCreatedOn failed: %s", cudaGetErrorString((cudaError_t)rc));
     }
   }
   *out = r;
@@ -1112,14 +1128,13 @@ int32_t tt_get_due_on_or_before(tt_table* t, int32_t mode, int64_t today_local_t
   tt_sweep_stats st;
   tt_result* r = nullptr;
   int32_t rc = sweep_owned(t, mode, TT_SWEEP_LIST_ONLY | TT_SWEEP_DUE_ON_OR_BEFORE, today_local_ticks, 0, &r, &st,
-                           mode != TT_MODE_STORE);
+                           mode != TT_MODE_STORE, /*keys_too=*/mode == TT_MODE_STORE);
   if (rc) return rc;
   if (mode == TT_MODE_STORE && r->n > 0) {  // the store-backed list is ordered by TaskCreatedOn (TasksStoreManager.cs:136)
-    rc = tt::order_by_created(t->stream, t->sort, t->created_raw, t->task_id, r->d_rows, r->d_ids, r->n, /*descending=*/false,
-                              /*rows_unordered=*/false, &t->last_order);
+    rc = tt::order_prefilled(t->stream, t->sort, t->task_id, r->d_rows, r->d_ids, r->n, &t->last_order);
     if (rc != 0) {
       result_release(r);
-      return fail(TT_ERR_CUDA, "order_by_created failed: %s", cudaGetErrorString((cudaError_t)rc));
+      return fail(TT_ERR_CUDA, "ordering by TaskCreatedOn failed: %s", cudaGetErrorString((cudaError_t)rc));
     }
   }
   *out = r;
@@ -1180,6 +1195,7 @@ int32_t tt_sweep_push(tt_table* t, int32_t mode, int32_t flags, int64_t today_lo
   push.ids = nullptr;
   push.created = nullptr;
   push.tile_first = nullptr;
+  push.created_as_key = 0;
   return sweep_run(t, mode, flags, today_local_ticks, run_at_utc_ticks, 0, d_rows, (uint4*)d_ids, cap, h_stats,
                    stream ? (cudaStream_t)stream : t->stream, &push);
 }
