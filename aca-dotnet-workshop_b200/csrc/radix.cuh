@@ -14,7 +14,7 @@
 //                        on high-entropy digits.)
 // Digits on which all keys agree are skipped (the caller passes the number of significant bits),
 // e.g. 7 passes instead of 8 for creation times that span two years.  radix_sort_by_prefix goes further
-// for wide keys: LSD passes over the top 40 significant bits of (key - smallest key) only, then a check of
+// for wide keys: LSD passes over the top 24-40 significant bits of (key - smallest key) only, then a check of
 // neighbours with equal prefixes, whose (rare) out-of-order groups are put right in place.
 #pragma once
 
@@ -329,11 +329,11 @@ inline cudaError_t radix_minmax_reset(cudaStream_t stream, SortScratch& s) {
   return cudaMemcpyAsync(s.mm, init, 16, cudaMemcpyHostToDevice, stream);
 }
 
-// ---- wide keys: sort the top 40 significant bits, then put right what the low bits disturb -----------------
-// After stable passes over bits [shift0, shift0 + 40) of (key - base0) the pairs are in order wherever the prefixes
+// ---- wide keys: sort a prefix of the significant bits, then put right what the low bits disturb ------------
+// After stable passes over the top `prefix` bits [shift0, bits) of (key - base0) the pairs are in order wherever the prefixes
 // differ.  Elements with EQUAL prefixes still stand in their input order: that is already the final order when they
 // are equal altogether (ties) or were ascending on input (a table filled in creation order), and otherwise the group
-// is tiny — 25 M keys drawn from two years of 100 ns ticks meet about 300 times in 2^40 prefixes.  One kernel looks
+// is tiny — 25 M keys drawn from two years of 100 ns ticks meet about 70 000 times in 2^32 prefixes.  One kernel looks
 // for neighbours that are out of order and reports the head of each such group (the thread at the group's FIRST
 // inversion does, so a group is reported once); a second kernel sorts every reported group by insertion (stable).
 // Groups longer than kFixMaxGroup or more reports than the list holds raise ctl[1]: the caller then finishes with
@@ -400,7 +400,7 @@ struct RadixSortInfo {
 };
 
 // Sorts the n pairs in (s.keys[0], s.vals[0]) by the whole key, stably, given the smallest and largest key.
-// *which = the buffer pair that holds the result.  Synchronises the stream when the keys are wider than 40 bits.
+// *which = the buffer pair that holds the result.  Synchronises the stream when the keys are wider than the prefix.
 inline cudaError_t radix_sort_by_prefix(cudaStream_t stream, SortScratch& s, int64_t n, unsigned long long lo,
                                         unsigned long long hi, int* which, RadixSortInfo* info = nullptr) {
   *which = 0;
@@ -415,16 +415,23 @@ inline cudaError_t radix_sort_by_prefix(cudaStream_t stream, SortScratch& s, int
     const char* e = getenv("TT_RADIX_PREFIX");
     return e && atoi(e) == 0;
   }();
-  if (bits <= 40 || no_prefix) {
+  // Width of the prefix: the fewest whole digits that keep the expected number of keys sharing a prefix with another
+  // key (n^2 / 2^(P+1) pairs for uniform keys) below n / 64 — P >= log2(n) + 5: 32 bits for 25 M keys (about 70 000
+  // pairs), 24 for 60 000.  Keys that crowd more than that only cost the fall-back's extra passes, never the order.
+  int log2n = 0;
+  while ((1ll << log2n) < n) ++log2n;
+  int prefix = (log2n + 5 + 7) / 8 * 8;
+  prefix = prefix < 16 ? 16 : prefix > 40 ? 40 : prefix;
+  if (bits <= prefix || no_prefix) {
     info->passes = (bits + 7) / 8;
     return radix_passes(stream, s, n, lo, 0, bits, which);
   }
-  const int shift0 = bits - 40;
+  const int shift0 = bits - prefix;
   cudaError_t e = radix_passes(stream, s, n, lo, shift0, bits, which);
   if (e != cudaSuccess) return e;
-  info->passes = 5;
+  info->passes = prefix / 8;
   const size_t tiles = (size_t)((s.cap + kRadixThreads * 8 - 1) / (kRadixThreads * 8));
-  const uint32_t list_cap = (uint32_t)std::min<size_t>(tiles * kRadixDigits, 1u << 20);
+  const uint32_t list_cap = (uint32_t)std::min<size_t>(tiles * kRadixDigits, 1u << 24);
   e = cudaMemsetAsync(s.mm, 0, 16, stream);
   if (e != cudaSuccess) return e;
   radix_fix_find_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(s.keys[*which], n, lo, shift0, s.hist, list_cap, s.mm);
@@ -437,7 +444,7 @@ inline cudaError_t radix_sort_by_prefix(cudaStream_t stream, SortScratch& s, int
   info->fixed = ctl[0];
   if (ctl[1]) {  // long or too many groups: low digits, then the prefix again (all passes stable)
     info->fell_back = true;
-    info->passes += (shift0 + 7) / 8 + 5;
+    info->passes += (shift0 + 7) / 8 + prefix / 8;
     e = radix_passes(stream, s, n, lo, 0, shift0, which);
     if (e == cudaSuccess) e = radix_passes(stream, s, n, lo, shift0, bits, which);
   }

@@ -142,8 +142,8 @@ int32_t tt_get_by_creator(tt_table* t, const char* utf8, int32_t len, tt_result*
 int32_t tt_creator_combining_stats(tt_table* t, int64_t* passes, int64_t* requests);
 /* How the last OrderBy(TaskCreatedOn) of this table (Api/Services/TasksStoreManager.cs:136; the ordered
  * tt_get_yesterdays_due / tt_get_due_on_or_before) was sorted: the bits in which the creation times of the
- * listed tasks differ, the radix passes run (5 over the top 40 of those bits when there are more than 40),
- * the groups of equal 40-bit prefixes that stood out of order afterwards and were put right in place, and
+ * listed tasks differ, the radix passes run (over a prefix of those bits only when they are many: the top 32 for
+ * 25 M tasks), the groups of equal prefixes that stood out of order afterwards and were put right in place, and
  * whether such groups were too long or too many, so that ordinary passes over every digit finished the job.
  * Any of the pointers may be null.  No reference counterpart. */
 int32_t tt_last_order_info(tt_table* t, int32_t* key_bits, int32_t* passes, int64_t* groups_fixed, int32_t* fell_back);
