@@ -19,45 +19,6 @@
 
 namespace tt {
 
-// keys[i] = the sort key of rows[i], vals[i] = the row; mm[0] / mm[1] collect the smallest / largest key
-// (preset to ~0 / 0), which tell the sort how many digits actually vary.  Grid-stride over a bounded grid:
-// the min / max cost one pair of atomics per warp of the GRID, not of the list (one pair per 32 hits on two
-// addresses took longer than the gathers).
-__global__ void order_keys_kernel(const uint32_t* rows, const uint64_t* created_raw, unsigned long long* keys,
-                                  uint32_t* vals, int64_t n, int descending, unsigned long long* mm) {
-  unsigned long long lo = ~0ull, hi = 0;
-  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t i0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i0 < n; i0 += 4 * stride) {
-    uint32_t r[4];
-    uint64_t k[4];
-#pragma unroll
-    for (int j = 0; j < 4; ++j) r[j] = i0 + j * stride < n ? rows[i0 + j * stride] : 0u;
-#pragma unroll
-    for (int j = 0; j < 4; ++j) k[j] = ld_gather_u64(created_raw + r[j]) & TT_TICKS_MASK;  // four gathers in flight
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const int64_t i = i0 + j * stride;
-      if (i < n) {
-        const uint64_t key = descending ? (~k[j] & TT_TICKS_MASK) : k[j];
-        keys[i] = key;
-        vals[i] = r[j];
-        lo = key < lo ? key : lo;
-        hi = key > hi ? key : hi;
-      }
-    }
-  }
-#pragma unroll
-  for (int d = 16; d > 0; d >>= 1) {
-    const unsigned long long a = __shfl_xor_sync(0xFFFFFFFFu, lo, d), b = __shfl_xor_sync(0xFFFFFFFFu, hi, d);
-    lo = a < lo ? a : lo;
-    hi = b > hi ? b : hi;
-  }
-  if ((threadIdx.x & 31) == 0 && lo <= hi) {
-    atomicMin(mm + 0, lo);
-    atomicMax(mm + 1, hi);
-  }
-}
-
 __global__ void row_keys_kernel(const uint32_t* rows, unsigned long long* keys, uint32_t* vals, int64_t n) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) {
@@ -101,40 +62,10 @@ inline int sort_rows_and_gather(cudaStream_t stream, SortScratch& sc, const uint
   return (int)(e != cudaSuccess ? e : s2);
 }
 
-// Orders d_rows (ascending row order on entry, or any order with rows_unordered) by
-// TaskCreatedOn, stable, and rewrites d_rows / d_ids.  Returns 0 or a cudaError_t value.
-inline int order_by_created(cudaStream_t stream, SortScratch& sc, const uint64_t* created_raw, const uint4* task_id,
-                            uint32_t* d_rows, uint4* d_ids, int64_t n, bool descending, bool rows_unordered = false,
-                            RadixSortInfo* info = nullptr) {
-  if (n <= 0) return 0;
-  if (rows_unordered) {
-    int rc = sort_rows_and_gather(stream, sc, task_id, d_rows, d_ids, n);
-    if (rc) return rc;
-  }
-  cudaError_t e = sc.reserve(n);
-  if (e != cudaSuccess) return (int)e;
-  const unsigned grid = (unsigned)((n + 255) / 256);
-  e = radix_minmax_reset(stream, sc);
-  if (e != cudaSuccess) return (int)e;
-  order_keys_kernel<<<grid < 148u * 16u ? grid : 148u * 16u, 256, 0, stream>>>(d_rows, created_raw, sc.keys[0], sc.vals[0], n,
-                                                                               descending ? 1 : 0, sc.mm);
-  e = cudaGetLastError();
-  if (e != cudaSuccess) return (int)e;
-  int w = 0;
-  unsigned long long mm[2];
-  e = radix_minmax_read(stream, sc, mm);
-  if (e != cudaSuccess) return (int)e;
-  e = radix_sort_by_prefix(stream, sc, n, mm[0], mm[1], &w, info);
-  if (e != cudaSuccess) return (int)e;
-  emit_rows_ids_kernel<<<grid, 256, 0, stream>>>(sc.vals[w], task_id, d_rows, d_ids, n);
-  e = cudaGetLastError();
-  cudaError_t s2 = cudaStreamSynchronize(stream);
-  return (int)(e != cudaSuccess ? e : s2);
-}
-
-// The same when the sort buffers are filled already — sc.keys[0] = the hits' ticks, sc.vals[0] = their rows, in row
-// order (the placement kernel of a listing sweep gathered them: sweep_owned, keys_too): min / max, the sort, and the
-// list written in its final order.
+// OrderBy(TaskCreatedOn), stable (TasksStoreManager.cs:136).  The sort buffers are filled already — sc.keys[0] = the
+// hits' ticks, sc.vals[0] = their rows, in row order (the placement kernel of a listing sweep gathered them:
+// sweep_owned, keys_too): min / max, the sort, and the list (rows and TaskIds) written in its final order.
+// Returns 0 or a cudaError_t value; synchronises the stream.
 inline int order_prefilled(cudaStream_t stream, SortScratch& sc, const uint4* task_id, uint32_t* d_rows, uint4* d_ids, int64_t n,
                            RadixSortInfo* info = nullptr) {
   if (n <= 0) return 0;
