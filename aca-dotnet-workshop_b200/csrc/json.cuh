@@ -508,14 +508,162 @@ __global__ void __launch_bounds__(THREADS) json_len_kernel(JsonParams p) {
   if (threadIdx.x == 0) p.block_base[blockIdx.x] = tot;
 }
 
-__device__ __forceinline__ uint8_t* put_lit(uint8_t* o, int start, int n) {
-  for (int j = 0; j < n; ++j) o[j] = (uint8_t)kJsonLit[start + j];
-  return o + n;
+// ---- word-wise assembly of a record -----------------------------------------------------------
+// A record is ~290 bytes at an arbitrary byte offset.  Written a byte at a time it costs a store (and a constant
+// load) per byte, all chained through the output pointer; JsonPacker assembles 32-bit words instead: `prev` holds the
+// last source word, whose top s / 8 bytes have not been written yet, and appending a word v is one funnel shift and one
+// aligned store — (v << s) | (prev >> (32 - s)).  Literals are compile-time words, the TaskId's hex digits and the
+// dates' digits are computed four characters at a time, escaped strings arrive as words from the dictionary pool.
+// Only a record's first and last word, which it shares with its neighbours, are written bytewise.
+struct JsonPacker {
+  uint32_t* wp;   // next aligned word of the output
+  uint32_t prev;  // its top s / 8 bytes are pending
+  uint32_t s;     // 8 * pending bytes, 0..24
+
+  // starts at byte address o with the record's first four bytes: only the bytes from o on are stored
+  __device__ __forceinline__ void start(uint8_t* o, uint32_t first) {
+    const uint32_t f = (uint32_t)(reinterpret_cast<uintptr_t>(o) & 3u);
+    wp = reinterpret_cast<uint32_t*>(o - f);
+    s = 8u * f;
+    const uint32_t out = first << s;
+    for (uint32_t b = f; b < 4u; ++b) reinterpret_cast<uint8_t*>(wp)[b] = (uint8_t)(out >> (8u * b));
+    ++wp;
+    prev = first;
+  }
+  __device__ __forceinline__ void word(uint32_t v) {
+    *wp++ = __funnelshift_l(prev, v, s);
+    prev = v;
+  }
+  // k = 1..3 bytes in the low end of v, zero above
+  __device__ __forceinline__ void part(uint32_t v, uint32_t k) {
+    const uint32_t out = __funnelshift_l(prev, v, s);
+    prev = __funnelshift_r(prev, v, 8u * k);
+    s += 8u * k;
+    if (s >= 32u) {
+      *wp++ = out;
+      s -= 32u;
+    }
+  }
+  // the pending bytes; returns the address after the record's last byte
+  __device__ __forceinline__ uint8_t* finish() {
+    uint8_t* o = reinterpret_cast<uint8_t*>(wp);
+    const uint32_t n = s >> 3;
+    const uint32_t tail = n ? prev >> (32u - s) : 0u;
+    for (uint32_t b = 0; b < n; ++b) o[b] = (uint8_t)(tail >> (8u * b));
+    return o + n;
+  }
+};
+
+// bytes [from, from + 4) of a literal as a little-endian word (zero beyond its end)
+template <int N>
+__host__ __device__ constexpr uint32_t lit_word(const char (&lit)[N], int from) {
+  uint32_t w = 0;
+  for (int k = 0; k < 4; ++k)
+    if (from + k < N - 1) w |= (uint32_t)(uint8_t)lit[from + k] << (8 * k);
+  return w;
+}
+
+// a literal as words, built at compile time
+template <int N>
+struct LitWords {
+  uint32_t w[(N + 2) / 4 + 1];
+};
+template <int N>
+__host__ __device__ constexpr LitWords<N> lit_words(const char (&lit)[N]) {
+  LitWords<N> r = {};
+  for (int j = 0; j * 4 < N - 1; ++j) r.w[j] = lit_word(lit, 4 * j);
+  return r;
+}
+
+// appends a literal: its whole words, then the 1..3 bytes that are left (lengths known at compile time)
+template <int N>
+__device__ __forceinline__ void pack_words(JsonPacker& k, const LitWords<N> lw) {
+  constexpr int len = N - 1;
+#pragma unroll
+  for (int j = 0; j < len / 4; ++j) k.word(lw.w[j]);
+  if constexpr (len % 4 != 0) k.part(lw.w[len / 4], (uint32_t)(len % 4));
+}
+#define TT_PACK_LIT(K, LIT)                    \
+  do {                                         \
+    constexpr auto lit_w_ = lit_words(LIT);    \
+    pack_words(K, lit_w_);                     \
+  } while (0)
+
+// four lower-case hex digits of two bytes (the byte in bits 0..7 first), as four characters
+__device__ __forceinline__ uint32_t hex4(uint32_t v) {
+  const uint32_t t = ((v & 0xF0u) >> 4) | ((v & 0x0Fu) << 8) | ((v & 0xF000u) << 4) | ((v & 0x0F00u) << 16);
+  return t + 0x30303030u + (((t + 0x06060606u) >> 4) & 0x01010101u) * 39u;
+}
+
+// two decimal digits of v < 100 as two characters (tens first)
+__device__ __forceinline__ uint32_t dec2(uint32_t v) {
+  const uint32_t t = v / 10u;
+  return (0x3030u + t) | ((v - 10u * t) << 8);
+}
+
+// "yyyy-MM-ddTHH:mm:ss[.fffffff][Z|+hh:mm]" (System.Text.Json's DateTime writer)
+__device__ __forceinline__ void pack_datetime(JsonPacker& k, uint64_t raw, int32_t local_offset_min) {
+  const uint64_t ticks = raw & 0x3FFFFFFFFFFFFFFFull;
+  const uint32_t kind = (uint32_t)(raw >> 62);
+  const uint64_t days = ticks / 864000000000ull;
+  const uint64_t tod = ticks % 864000000000ull;
+  // civil date from days since 0001-01-01 (proleptic Gregorian, era arithmetic)
+  const uint32_t z = (uint32_t)days + 306;  // days since 0000-03-01
+  const uint32_t era = z / 146097;
+  const uint32_t doe = z - era * 146097;
+  const uint32_t yoe = (doe - doe / 1460 + doe / 36524 - doe / 146096) / 365;
+  uint32_t y = yoe + era * 400;
+  const uint32_t doy = doe - (365 * yoe + yoe / 4 - yoe / 100);
+  const uint32_t mp = (5 * doy + 2) / 153;
+  const uint32_t d = doy - (153 * mp + 2) / 5 + 1;
+  const uint32_t m = mp < 10 ? mp + 3 : mp - 9;
+  if (m <= 2) y += 1;
+  const uint32_t secs = (uint32_t)(tod / 10000000ull);
+  uint32_t frac = (uint32_t)(tod % 10000000ull);
+  const uint32_t hh = secs / 3600, mi = secs / 60 % 60, ss = secs % 60;
+  const uint32_t dh = dec2(hh);
+  k.word(dec2(y / 100) | (dec2(y % 100) << 16));              // yyyy
+  k.word('-' | (dec2(m) << 8) | ((uint32_t)'-' << 24));       // -MM-
+  k.word(dec2(d) | ((uint32_t)'T' << 16) | (dh << 24));       // ddTH
+  k.word((dh >> 8) | ((uint32_t)':' << 8) | (dec2(mi) << 16));  // H:mm
+  k.part(':' | (dec2(ss) << 8), 3);                           // :ss
+  if (frac) {
+    uint32_t digits = 7;
+    while (frac % 10 == 0) { frac /= 10; --digits; }
+    // '.' and the digits, most significant first: eight characters at most
+    uint64_t txt = '.';
+    uint32_t pow = 1;
+    for (uint32_t j = 1; j < digits; ++j) pow *= 10;
+    for (uint32_t j = 0; j < digits; ++j) {
+      const uint32_t q = frac / pow;
+      txt |= (uint64_t)('0' + q) << (8 * (j + 1));
+      frac -= q * pow;
+      pow /= 10;
+    }
+    const uint32_t n = digits + 1;
+    if (n >= 4) {
+      k.word((uint32_t)txt);
+      if (n == 8) k.word((uint32_t)(txt >> 32));
+      else if (n > 4) k.part((uint32_t)(txt >> 32), n - 4);
+    } else {
+      k.part((uint32_t)txt, n);
+    }
+  }
+  if (kind == 1) {
+    k.part('Z', 1);
+  } else if (kind >= 2) {
+    int32_t off = local_offset_min;
+    const uint32_t sign = off < 0 ? '-' : '+';
+    if (off < 0) off = -off;
+    const uint32_t oh = dec2((uint32_t)off / 60), om = dec2((uint32_t)off % 60);
+    k.word(sign | (oh << 8) | ((uint32_t)':' << 24));  // +hh:
+    k.part(om, 2);                                     // mm
+  }
 }
 
 // The first 32 bytes of an escaped string, fetched before any formatting starts: the three strings
 // of a record are six independent 128-bit loads in flight together instead of a chain of
-// dependent word loads (each an L2 round trip) in the middle of the byte stores.
+// dependent word loads (each an L2 round trip) in the middle of the stores.
 struct EscHead {
   uint4 q0, q1;
 };
@@ -530,66 +678,70 @@ __device__ __forceinline__ EscHead esc_prefetch(const uint32_t* pool, EscEntry e
   return h;
 }
 
-__device__ __forceinline__ uint8_t* put_esc(uint8_t* o, const uint32_t* pool, EscEntry e, const EscHead& h, uint64_t keep) {
+// an escaped string: whole words, then its last 1..3 bytes (the pool pads every entry with zeros)
+__device__ __forceinline__ void pack_esc(JsonPacker& k, const uint32_t* pool, EscEntry e, const EscHead& h, uint64_t keep) {
   const uint32_t w[8] = {h.q0.x, h.q0.y, h.q0.z, h.q0.w, h.q1.x, h.q1.y, h.q1.z, h.q1.w};
+  const uint32_t nw = e.len >> 2, rest = e.len & 3u;
 #pragma unroll
-  for (int k = 0; k < 32; ++k)
-    if ((uint32_t)k < e.len) o[k] = (uint8_t)(w[k >> 2] >> (8 * (k & 3)));
-  if (e.len > 32) {  // long strings: the rest, 16 bytes at a time
-    const uint4* q = reinterpret_cast<const uint4*>(pool + e.word_off);
-    for (uint32_t j = 32; j < e.len; j += 16) {
-      const uint4 v = ld_hint_v4(q + (j >> 4), keep);
-      const uint32_t x[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-      for (int k = 0; k < 16; ++k)
-        if (j + k < e.len) o[j + k] = (uint8_t)(x[k >> 2] >> (8 * (k & 3)));
-    }
+  for (int j = 0; j < 8; ++j) {
+    if ((uint32_t)j < nw) k.word(w[j]);
+    else if ((uint32_t)j == nw && rest) k.part(w[j], rest);
   }
-  return o + e.len;
+  if (nw >= 8) {  // long strings: the words after the prefetched 32 bytes
+    const uint32_t* src = pool + e.word_off;
+    for (uint32_t j = 8; j < nw; ++j) k.word(ld_hint_u32(src + j, keep));
+    if (rest) k.part(ld_hint_u32(src + nw, keep), rest);
+  }
 }
 
-// One string member and the literal that follows it.  The literals carry the quotes (`...":"` before,
-// `","next":"` after); a null member takes the opening quote back and skips the closing one.
-__device__ __forceinline__ uint8_t* put_member(uint8_t* o, const uint32_t* pool, EscEntry e, const EscHead& h, uint64_t keep,
-                                               int next_lit, int next_len) {
+// One string member's value: "…" or, for a member that holds null, the literal null.
+__device__ __forceinline__ void pack_member(JsonPacker& k, const uint32_t* pool, EscEntry e, const EscHead& h, uint64_t keep) {
   if (e.word_off == kNullWordOff) {
-    o[-1] = 'n';
-    o[0] = 'u';
-    o[1] = 'l';
-    o[2] = 'l';
-    return put_lit(o + 3, next_lit + 1, next_len - 1);
+    k.word(lit_word("null", 0));
+    return;
   }
-  o = put_esc(o, pool, e, h, keep);
-  return put_lit(o, next_lit, next_len);
+  k.part('"', 1);
+  pack_esc(k, pool, e, h, keep);
+  k.part('"', 1);
 }
 
+// {"taskId":"<36>","taskName":…,"taskCreatedBy":…,"taskCreatedOn":"…","taskDueDate":"…","taskAssignedTo":…,
+//  "isCompleted":…,"isOverDue":…}  preceded by '[' or ',' and, for the last record, followed by ']'
 __device__ uint8_t* json_write_record(const JsonParams& p, const JsonRecord& r, uint4 id, int64_t i, uint8_t* o,
                                       const EscHead& h0, const EscHead& h1, const EscHead& h2, uint64_t keep) {
-  *o++ = i == 0 ? '[' : ',';
-  o = put_lit(o, 0, 11);
-  const uint32_t w[4] = {id.x, id.y, id.z, id.w};  // canonical bytes 0..15 in memory order
-#pragma unroll
-  for (int b = 0; b < 16; ++b) {
-    if (b == 4 || b == 6 || b == 8 || b == 10) *o++ = '-';
-    const uint32_t byte = (w[b >> 2] >> (8 * (b & 3))) & 0xFF;
-    *o++ = hex_lower(byte >> 4);
-    *o++ = hex_lower(byte & 15);
-  }
-  o = put_lit(o, 11, 14);
-  o = put_member(o, p.esc_pool[0], r.s[0], h0, keep, 25, 19);
-  o = put_member(o, p.esc_pool[1], r.s[1], h1, keep, 44, 19);
-  o += datetime_write(r.created, p.local_offset_min, o);
-  o = put_lit(o, 63, 17);
-  o += datetime_write(r.due, p.local_offset_min, o);
-  o = put_lit(o, 80, 20);
-  o = put_member(o, p.esc_pool[2], r.s[2], h2, keep, 100, 16);
-
-  o = r.completed ? put_lit(o, 129, 4) : put_lit(o, 133, 5);
-  o = put_lit(o, 116, 13);
-  o = r.overdue ? put_lit(o, 129, 4) : put_lit(o, 133, 5);
-  *o++ = '}';
-  if (i == p.n - 1) *o++ = ']';
-  return o;
+  JsonPacker k;
+  k.start(o, (i == 0 ? (uint32_t)'[' : (uint32_t)',') | (lit_word("{\"t", 0) << 8));  // [{"t  or  ,{"t
+  TT_PACK_LIT(k, "askId\":\"");
+  // canonical bytes 0..15 in memory order: 8-4-4-4-12 hex digits
+  const uint32_t a = hex4(id.y & 0xFFFFu), b = hex4(id.y >> 16), c = hex4(id.z & 0xFFFFu);
+  k.word(hex4(id.x & 0xFFFFu));
+  k.word(hex4(id.x >> 16));
+  k.word('-' | (a << 8));
+  k.word((a >> 24) | ((uint32_t)'-' << 8) | (b << 16));
+  k.word((b >> 16) | ((uint32_t)'-' << 16) | (c << 24));
+  k.word((c >> 8) | ((uint32_t)'-' << 24));
+  k.word(hex4(id.z >> 16));
+  k.word(hex4(id.w & 0xFFFFu));
+  k.word(hex4(id.w >> 16));
+  TT_PACK_LIT(k, "\",\"taskName\":");
+  pack_member(k, p.esc_pool[0], r.s[0], h0, keep);
+  TT_PACK_LIT(k, ",\"taskCreatedBy\":");
+  pack_member(k, p.esc_pool[1], r.s[1], h1, keep);
+  TT_PACK_LIT(k, ",\"taskCreatedOn\":\"");
+  pack_datetime(k, r.created, p.local_offset_min);
+  TT_PACK_LIT(k, "\",\"taskDueDate\":\"");
+  pack_datetime(k, r.due, p.local_offset_min);
+  TT_PACK_LIT(k, "\",\"taskAssignedTo\":");
+  pack_member(k, p.esc_pool[2], r.s[2], h2, keep);
+  TT_PACK_LIT(k, ",\"isCompleted\":");
+  if (r.completed) TT_PACK_LIT(k, "true");
+  else TT_PACK_LIT(k, "false");
+  TT_PACK_LIT(k, ",\"isOverDue\":");
+  if (r.overdue) TT_PACK_LIT(k, "true");
+  else TT_PACK_LIT(k, "false");
+  if (i == p.n - 1) TT_PACK_LIT(k, "}]");
+  else k.part('}', 1);
+  return k.finish();
 }
 
 // K6b: every thread formats one record; the CTA's piece of the text is contiguous in the output,
