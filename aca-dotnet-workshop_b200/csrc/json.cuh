@@ -14,10 +14,10 @@
 // Strings are dictionary-encoded on the device, so escaping is done ONCE per dictionary entry
 // (esc_len / esc_write kernels, cached in the table) and the per-hit work is pure copying:
 // K6a json_len_kernel sizes every record (dictionary lengths + date lengths), a two-level scan
-// turns the sizes into byte offsets, and K6b json_emit_kernel lets each thread format one
-// record into shared memory (literals from constant memory, TaskId hex, pre-escaped strings as
-// 32-bit words, dates, booleans); the CTA then streams its contiguous piece of the text to HBM
-// with 16-byte stores.  All byte work, HBM-bound: ≈270 B written per hit, ≈7 scattered reads.
+// turns the sizes into byte offsets, and K6b json_emit_kernel lets each thread assemble one
+// record in shared memory a 32-bit word at a time (JsonPacker: literals as compile-time words, TaskId
+// hex and date digits four characters at a time, pre-escaped strings as words); the CTA then streams
+// its contiguous piece of the text to HBM with 16-byte stores.  All byte work, HBM-bound: ≈270 B written per hit, ≈7 scattered reads.
 #pragma once
 
 #include <cuda_runtime.h>
@@ -110,8 +110,6 @@ __device__ __forceinline__ int json_escape_kind(uint32_t cp, int flavor, uint8_t
 }
 
 __device__ __forceinline__ uint8_t hex_upper(uint32_t x) { return (uint8_t)(x < 10 ? '0' + x : 'A' + x - 10); }
-__device__ __forceinline__ uint8_t hex_lower(uint32_t x) { return (uint8_t)(x < 10 ? '0' + x : 'a' + x - 10); }
-
 __device__ __forceinline__ void put_u4(uint8_t* o, uint32_t unit) {
   o[0] = '\\';
   o[1] = 'u';
@@ -301,17 +299,6 @@ __global__ void __launch_bounds__(kScanBlock) esc_entries_kernel(const uint32_t*
 // {"taskId":"<36>","taskName":"..","taskCreatedBy":"..","taskCreatedOn":"..","taskDueDate":"..",
 //  "taskAssignedTo":"..","isCompleted":false,"isOverDue":false}
 // preceded by '[' (first record) or ',' and, for the last record, followed by ']'.
-__constant__ char kJsonLit[] =
-    "{\"taskId\":\""            // 0, 11
-    "\",\"taskName\":\""        // 11, 14
-    "\",\"taskCreatedBy\":\""   // 25, 19
-    "\",\"taskCreatedOn\":\""   // 44, 19
-    "\",\"taskDueDate\":\""     // 63, 17
-    "\",\"taskAssignedTo\":\""  // 80, 20
-    "\",\"isCompleted\":"       // 100, 16
-    ",\"isOverDue\":"           // 116, 13
-    "true"                      // 129, 4
-    "false";                    // 133, 5
 constexpr uint32_t kJsonFixed = 1 + 11 + 36 + 14 + 19 + 19 + 17 + 20 + 16 + 13 + 1;  // lead + literals + id + '}'
 
 struct JsonParams {
@@ -344,64 +331,6 @@ __device__ __forceinline__ uint32_t datetime_len(uint64_t raw) {
     while (frac % 10 == 0) { frac /= 10; --l; }
   }
   return l + (kind == 1 ? 1u : kind >= 2 ? 6u : 0u);
-}
-
-__device__ __forceinline__ void put2(uint8_t* o, uint32_t v) {
-  o[0] = (uint8_t)('0' + v / 10);
-  o[1] = (uint8_t)('0' + v % 10);
-}
-
-// "yyyy-MM-ddTHH:mm:ss[.fffffff][Z|+hh:mm]" (System.Text.Json's DateTime writer); returns the length
-__device__ uint32_t datetime_write(uint64_t raw, int32_t local_offset_min, uint8_t* o) {
-  const uint64_t ticks = raw & 0x3FFFFFFFFFFFFFFFull;
-  const uint32_t kind = (uint32_t)(raw >> 62);
-  const uint64_t days = ticks / 864000000000ull;
-  const uint64_t tod = ticks % 864000000000ull;
-  // civil date from days since 0001-01-01 (proleptic Gregorian, era arithmetic)
-  const uint32_t z = (uint32_t)days + 306;  // days since 0000-03-01
-  const uint32_t era = z / 146097;
-  const uint32_t doe = z - era * 146097;
-  const uint32_t yoe = (doe - doe / 1460 + doe / 36524 - doe / 146096) / 365;
-  uint32_t y = yoe + era * 400;
-  const uint32_t doy = doe - (365 * yoe + yoe / 4 - yoe / 100);
-  const uint32_t mp = (5 * doy + 2) / 153;
-  const uint32_t d = doy - (153 * mp + 2) / 5 + 1;
-  const uint32_t m = mp < 10 ? mp + 3 : mp - 9;
-  if (m <= 2) y += 1;
-  const uint32_t secs = (uint32_t)(tod / 10000000ull);
-  uint32_t frac = (uint32_t)(tod % 10000000ull);
-  put2(o, y / 100);
-  put2(o + 2, y % 100);
-  o[4] = '-';
-  put2(o + 5, m);
-  o[7] = '-';
-  put2(o + 8, d);
-  o[10] = 'T';
-  put2(o + 11, secs / 3600);
-  o[13] = ':';
-  put2(o + 14, secs / 60 % 60);
-  o[16] = ':';
-  put2(o + 17, secs % 60);
-  uint32_t p = 19;
-  if (frac) {
-    uint32_t digits = 7;
-    while (frac % 10 == 0) { frac /= 10; --digits; }
-    o[p] = '.';
-    for (uint32_t j = digits; j > 0; --j) { o[p + j] = (uint8_t)('0' + frac % 10); frac /= 10; }
-    p += 1 + digits;
-  }
-  if (kind == 1) {
-    o[p++] = 'Z';
-  } else if (kind >= 2) {
-    int32_t off = local_offset_min;
-    o[p++] = off < 0 ? '-' : '+';
-    if (off < 0) off = -off;
-    put2(o + p, (uint32_t)off / 60);
-    o[p + 2] = ':';
-    put2(o + p + 3, (uint32_t)off % 60);
-    p += 5;
-  }
-  return p;
 }
 
 constexpr int kJsonThreads = 128;            // records per CTA (the default; the kernels are built for 64 and 256 as well)
