@@ -404,6 +404,7 @@ struct PushTarget {
   unsigned long long* created;  // [cap] TaskCreatedOn (.NET dateData) of the hits, or null (the cross-shard OrderBy)
   uint32_t* tile_first;         // [num_tiles] offset of each tile's hits in the row-ordered list, or null
   int created_as_key;           // 0: `created` receives the raw dateData; 1: its ticks (the sort key of OrderBy(TaskCreatedOn))
+  int shape;                    // tiles per placement CTA for this push (1, 2, 4, 8, 16, 32); 0 = the library's default
 };
 
 // What a sharded tick adds around K3g (shards.cuh): before it, wait until the root has finished

@@ -632,7 +632,7 @@ int32_t sweep_run(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_
     if (push || place_by_group()) {
       // K3g: tile-ordered placement, optionally fused with the push of the compact form (sweep.cuh); it
       // derives every tile's offset in the row-ordered list from K1's partial sums itself (no K2)
-      const tt::PushTarget none = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0};
+      const tt::PushTarget none = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0, 0};
       if (hook && hook->wait_slot0) {  // the root must have read this shard's slot of the previous tick
         tt::shard_wait_kernel<<<1, 32, 0, stream>>>(hook->wait_slot0, 0, 1, offsetof(tt::SlotHeader, consumed),
                                                     hook->wait_value, hook->timeout_ns, nullptr, nullptr);
@@ -649,7 +649,9 @@ int32_t sweep_run(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_
       // push keeps 8 x 4.  TT_PLACE_VARIANT / TT_PUSH_VARIANT (read once) pick another shape for A/B
       // runs: 1 = 1 x 1, 2 = 2 x 2, 4 = 4 x 4, 8 = 8 x 4.
       static const int plain_variant = [] { const char* e = getenv("TT_PLACE_VARIANT"); return e ? atoi(e) : 1; }();
-      static const int push_variant = [] { const char* e = getenv("TT_PUSH_VARIANT"); return e ? atoi(e) : 8; }();
+      const char* push_env = push ? getenv("TT_PUSH_VARIANT") : nullptr;  // read per tick: A/B scripts change it between runs
+      const int push_variant = push_env ? atoi(push_env) : 8;
+      const bool push_forced = push_env != nullptr;
 #define TT_PLACE_LAUNCH(GT, UN)                                                                                     \
   TT_CUDA(tt::launch_dependent(tt::place_group_kernel<TT_TILE_ROWS, GT, UN>, dim3((num_tiles + GT - 1) / GT),           \
                                dim3(tt::kGroupThreads), stream, pdl, (const uint32_t*)t->hit_list,                      \
@@ -657,7 +659,9 @@ int32_t sweep_run(tt_table* t, int32_t mode, int32_t flags, int64_t today_local_
                                (const uint32_t*)p.group_sum, (const uint32_t*)p.sub_sum, (uint32_t)num_tiles,           \
                                (const uint4*)t->task_id, (const uint64_t*)t->created_raw, d_rows, d_ids,                \
                                push ? *push : none))
-      switch (push && push->off16 ? push_variant : plain_variant) {  // a push of creation times only stays on this GPU
+      // (a push of creation times only stays on this GPU; a push to ONE receiver that takes nobody else's stores asks for
+      // the single-GPU shape: push->shape)
+      switch (push && push->off16 ? (push->shape && !push_forced ? push->shape : push_variant) : plain_variant) {
         case 2: TT_PLACE_LAUNCH(2, 2); break;
         case 4: TT_PLACE_LAUNCH(4, 4); break;
         case 8: TT_PLACE_LAUNCH(8, 4); break;
@@ -774,7 +778,7 @@ int32_t sweep_owned(tt_table* t, int32_t mode, int32_t flags, int64_t today, int
         cudaGetLastError();
         return fail(TT_ERR_OOM, "sort buffers: %s", cudaGetErrorString(e));
       }
-      tt::PushTarget keys = {nullptr, nullptr, nullptr, nullptr, t->sort.keys[0], nullptr, 1};
+      tt::PushTarget keys = {nullptr, nullptr, nullptr, nullptr, t->sort.keys[0], nullptr, 1, 0};
       rc = sweep_run(t, mode, flags, today, run_at, 0, t->sort.vals[0], nullptr, r->cap, &st, t->stream, &keys);
     } else {
       rc = sweep_run(t, mode, flags, today, run_at, 0, r->d_rows + r->n, with_ids ? r->d_ids + r->n : nullptr, r->cap - r->n,
@@ -1196,6 +1200,7 @@ int32_t tt_sweep_push(tt_table* t, int32_t mode, int32_t flags, int64_t today_lo
   push.created = nullptr;
   push.tile_first = nullptr;
   push.created_as_key = 0;
+  push.shape = 0;
   return sweep_run(t, mode, flags, today_local_ticks, run_at_utc_ticks, 0, d_rows, (uint4*)d_ids, cap, h_stats,
                    stream ? (cudaStream_t)stream : t->stream, &push);
 }

@@ -1,5 +1,5 @@
 """A/B of the cross-shard exchange forms under torchrun, several configurations in ONE launch (start-up is what an
-8-GPU call is charged for).  Each argument is form:share:scaling, e.g. rows:1.0:weak rows:0.8:weak ids:1.0:strong.
+8-GPU call is charged for).  Each argument is form:share:scaling[:shape], e.g. rows:1.0:weak rows:0.8:weak ids:1.0:strong rows:1.0:weak:4.
 Prints one JSON line per configuration (rank 0): the tick as bench.py times it (ShardRun.timed)."""
 import importlib
 import json
@@ -25,8 +25,12 @@ def main():
     rows = int(os.environ.get("AB_ROWS", "1000000000"))
     steps, warm = int(os.environ.get("AB_STEPS", "10")), 3
     for spec in sys.argv[1:]:
-        form, share, scaling = spec.split(":")
+        form, share, scaling, *more = spec.split(":")
         share = float(share)
+        if more:  # tiles per placement CTA of the fused push (TT_PUSH_VARIANT, read by the library at every tick)
+            os.environ["TT_PUSH_VARIANT"] = more[0]
+        else:
+            os.environ.pop("TT_PUSH_VARIANT", None)
         total = rows * world if scaling == "weak" else rows
         root = int(total / world * share) // 8192 * 8192
         rest = total - root
@@ -39,7 +43,7 @@ def main():
         dist.all_gather_object(every, {"k1_ms": m["sweep_ms"], "k3g_ms": m["gather_ms"], "step_ms": m["step_ms_rank0"]})
         if rank == 0:
             assert m["collected"] == m["hits"], (m["collected"], m["hits"])
-            print(json.dumps({"form": form, "root_share": share, "scaling": scaling, "n_gpus": world, "n_total": total,
+            print(json.dumps({"form": form, "push_shape": more[0] if more else "default", "root_share": share, "scaling": scaling, "n_gpus": world, "n_total": total,
                               "ms_per_step": m["ms_per_step"], "tasks_per_sec": total * steps / (m["total_ms"] * 1e-3),
                               "hits": m["hits"], "rank0": {"k1_ms": m["sweep_ms"], "k3g_ms": m["gather_ms"],
                                                            "collect_ms": m["collect_ms"], "step_ms": m["step_ms_rank0"]},
