@@ -641,8 +641,10 @@ __global__ void __launch_bounds__(128, MIN_CTAS) doc_parse_kernel(uint8_t* text,
       __syncwarp();
     }
   } else {
-    staged = false;  // the documents of a list lie anywhere: they are parsed in global memory (staging them one by one
-                     // cost more than it saved: 6.2 ms against 2.4 for 3.1 M documents)
+    // The documents of a list lie anywhere and are parsed in global memory.  Staging each on its own was measured twice
+    // (one after the other, and four documents' loads in flight): 10.8 ms for the whole parse against 6.8 — the documents
+    // that come here are the ones with escapes, whose unescaping wants many resident warps more than near bytes.
+    staged = false;
   }
   if (!live) return;
   // `base`: the address offset 0 of the text has in the space this lane parses in
@@ -784,6 +786,81 @@ __global__ void __launch_bounds__(128, MIN_CTAS) doc_parse_kernel(uint8_t* text,
   }
 }
 
+// The date form the serializer itself writes — yyyy-MM-ddTHH:mm:ss, then nothing, or .f to .fffffff, then nothing, Z or
+// ±hh:mm — parsed from the register window with fixed positions: separators and digits are checked a word at a time,
+// the two-digit numbers come out of one multiplication per word.  Same range checks and the same arithmetic as
+// parse_datetime; returns false for every other form (and for values out of range), which the caller then hands to
+// parse_datetime.
+__device__ __forceinline__ bool parse_datetime_fixed(const Chars48& s, int len, int32_t local_offset_min, uint64_t* raw) {
+  if (len < 19) return false;
+  constexpr uint64_t k7F = kOnes * 0x7Fu;
+  // pattern words: '0' where a digit stands, the separator itself elsewhere ("0000-00-", "00T00:00", ":00" + don't care)
+  constexpr uint64_t p0 = 0x2D30302D30303030ull, p1 = 0x30303A3030543030ull, p2 = 0x30303Aull;
+  const uint64_t x0 = s.w[0] ^ p0, x1 = s.w[1] ^ p1, x2 = (s.w[2] & 0xFFFFFFull) ^ p2;
+  // every byte must be 0..9 (separators: 0)
+  const uint64_t bad = ((((x0 & k7F) + kOnes * 0x76u) | x0) | (((x1 & k7F) + kOnes * 0x76u) | x1) | (((x2 & k7F) + kOnes * 0x76u) | x2)) & kHighs;
+  const uint64_t sep = (x0 & 0xFF0000FF00000000ull) | (x1 & 0x0000FF0000FF0000ull) | (x2 & 0xFFull);
+  if (bad | sep) return false;
+  const uint64_t t0 = x0 * 10u + (x0 >> 8), t1 = x1 * 10u + (x1 >> 8), t2 = x2 * 10u + (x2 >> 8);  // byte k = 10 d[k] + d[k+1]
+  const int yh = (int)(t0 & 0xFF), yl = (int)((t0 >> 16) & 0xFF), mo = (int)((t0 >> 40) & 0xFF);
+  const int d = (int)(t1 & 0xFF), hh = (int)((t1 >> 24) & 0xFF), mi = (int)((t1 >> 48) & 0xFF), ss = (int)((t2 >> 8) & 0xFF);
+  const int y = yh * 100 + yl;
+  if (y < 1 || mo < 1 || mo > 12 || d < 1) return false;
+  const bool leap = (y % 4 == 0 && y % 100 != 0) || y % 400 == 0;
+  const int dim = mo == 2 ? (leap ? 29 : 28) : (mo == 4 || mo == 6 || mo == 9 || mo == 11) ? 30 : 31;
+  if (d > dim || hh > 23 || mi > 59 || ss > 59) return false;
+  const int yy = mo <= 2 ? y - 1 : y;
+  const int era = yy / 400;
+  const int yoe = yy - era * 400;
+  const int doy = (153 * (mo + (mo > 2 ? -3 : 9)) + 2) / 5 + d - 1;
+  const int doe = yoe * 365 + yoe / 4 - yoe / 100 + doy;
+  const int64_t days = (int64_t)era * 146097 + doe - 306;
+  int64_t ticks = days * 864000000000ll + ((int64_t)hh * 3600 + mi * 60 + ss) * 10000000ll;
+  int at = 19;
+  if (len > 19 && ((uint32_t)(s.w[2] >> 24) & 0xFFu) == '.') {
+    // up to seven fraction digits at characters 20..26; an eighth digit means a longer fraction: not this form
+    const uint64_t f = ((s.w[2] >> 32) | (s.w[3] << 32)) ^ (kOnes * 0x30u);             // characters 20..27 as digit values
+    const uint64_t nondigit = ((((f & k7F) + kOnes * 0x76u) | f) & kHighs);
+    const int nd = nondigit ? (__ffsll((long long)nondigit) - 1) >> 3 : 8;
+    if (nd == 0 || nd > 7 || 20 + nd > len) return false;
+    int64_t frac = 0;
+#pragma unroll
+    for (int j = 0; j < 7; ++j) frac = j < nd ? frac * 10 + (int64_t)((f >> (8 * j)) & 0xFF) : frac * 10;
+    ticks += frac;
+    at = 20 + nd;
+  }
+  uint32_t kind = 0;
+  if (at < len) {
+    // the suffix: the (at most six) characters from `at` on
+    const int wi = at >> 3, sh = (at & 7) * 8;
+    const uint64_t lo = wi == 2 ? s.w[2] : wi == 3 ? s.w[3] : s.w[4], hi = wi == 2 ? s.w[3] : wi == 3 ? s.w[4] : s.w[5];
+    const uint64_t z = sh ? (lo >> sh) | (hi << (64 - sh)) : lo;
+    const uint32_t c0 = (uint32_t)z & 0xFFu;
+    if (len - at == 1 && c0 == 'Z') {
+      kind = 1;
+    } else if (len - at == 6 && (c0 == '+' || c0 == '-') && ((uint32_t)(z >> 24) & 0xFFu) == ':') {
+      const uint32_t a1 = ((uint32_t)(z >> 8) & 0xFFu) - '0', a2 = ((uint32_t)(z >> 16) & 0xFFu) - '0';
+      const uint32_t b1 = ((uint32_t)(z >> 32) & 0xFFu) - '0', b2 = ((uint32_t)(z >> 40) & 0xFFu) - '0';
+      if (a1 > 9 || a2 > 9 || b1 > 9 || b2 > 9) return false;
+      const int oh = (int)(a1 * 10 + a2), om = (int)(b1 * 10 + b2);
+      if (oh > 14 || om > 59) return false;
+      const int off = (oh * 60 + om) * (c0 == '-' ? -1 : 1);
+      ticks += (int64_t)(local_offset_min - off) * 600000000ll;
+      kind = 2;
+    } else {
+      return false;
+    }
+  }
+  if (ticks < 0 || ticks > 3155378975999999999ll) return false;
+  *raw = (uint64_t)ticks | ((uint64_t)kind << 62);
+  return true;
+}
+
+// parse_datetime out of line: the fast kernel calls it only for dates in another form
+__device__ __noinline__ bool parse_datetime_other(const Chars48* s, int len, int32_t local_offset_min, uint64_t* raw) {
+  return parse_datetime(*s, len, local_offset_min, raw);
+}
+
 // ---- K7a, the fast kernel: documents in the serializer's own shape -------------------------------------------------
 // What the state store holds was written by the reference's own serializer (JsonSerializer.Serialize(TaskModel), camelCase
 // names in declaration order, no whitespace).  For exactly that shape nothing has to be searched: every literal between the
@@ -883,7 +960,8 @@ __global__ void __launch_bounds__(128, MIN_CTAS) doc_parse_fast_kernel(uint8_t* 
   auto date_value = [&](uint64_t* raw) {
     cs.load(p, end);
     const int plain = cs.first_special();
-    ok = ok && plain < 48 && p + plain < end && cs[plain] == '"' && parse_datetime(cs, plain, local_offset_min, raw);
+    ok = ok && plain < 48 && p + plain < end && cs[plain] == '"' &&
+         (parse_datetime_fixed(cs, plain, local_offset_min, raw) || parse_datetime_other(&cs, plain, local_offset_min, raw));
     p += plain < 48 ? plain : 0;
   };
   auto bool_value = [&](uint32_t bit) {
