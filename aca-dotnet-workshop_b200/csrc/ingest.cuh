@@ -22,10 +22,15 @@
 // Anything else marks the document bad: the load reports the first bad document and changes
 // nothing.
 //
-// The three string members are then dictionary-encoded on the device: the documents are sorted
-// by the 64-bit hash of the (unescaped) string with the table's own radix sort, neighbours with
-// equal hash AND equal bytes share a dictionary entry (exact confirm, like the creator filter),
-// a scan numbers the entries, and the refs are scattered back to document order.
+// Two kernels share the work: doc_parse_fast_kernel takes the documents that are in exactly the shape the
+// reference's serializer writes (and judges no other), doc_parse_kernel — everything described above — takes
+// the rest.
+//
+// The three string members are then dictionary-encoded on the device through a hash table keyed by the
+// 64-bit hash of the (unescaped) string — the smallest document number of a string is its representative,
+// every document's bytes are compared with its representative's (exact confirm, like the creator filter),
+// a scan numbers the representatives in order of first appearance; two strings with one hash send the
+// member to the round-1 encoder (sort by hash, compare neighbours).
 #pragma once
 
 #include <cuda_runtime.h>
